@@ -1,0 +1,148 @@
+"""ctypes binding of the CPU ORACLE (oracle/libba_oracle.so).
+
+TEST INFRASTRUCTURE.  Import only from tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs — never from the sfm_b200 package."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libba_oracle.so")
+
+
+class OOptions(C.Structure):
+    _fields_ = [
+        ("max_num_iterations", C.c_int32), ("max_consecutive_invalid_steps", C.c_int32), ("jacobi_scaling", C.c_int32),
+        ("linear_solver", C.c_int32), ("dense_max_cams", C.c_int32), ("pcg_max_iterations", C.c_int32),
+        ("verbose", C.c_int32), ("num_threads", C.c_int32),
+        ("initial_trust_region_radius", C.c_double), ("max_trust_region_radius", C.c_double),
+        ("min_trust_region_radius", C.c_double), ("min_relative_decrease", C.c_double), ("min_lm_diagonal", C.c_double),
+        ("max_lm_diagonal", C.c_double), ("function_tolerance", C.c_double), ("gradient_tolerance", C.c_double),
+        ("parameter_tolerance", C.c_double), ("pcg_tolerance", C.c_double),
+    ]
+
+
+class OIteration(C.Structure):
+    _fields_ = [
+        ("cost", C.c_double), ("cost_change", C.c_double), ("gradient_max_norm", C.c_double), ("step_norm", C.c_double),
+        ("relative_decrease", C.c_double), ("trust_region_radius", C.c_double), ("model_cost_change", C.c_double),
+        ("step_is_valid", C.c_int32), ("step_is_successful", C.c_int32), ("linear_iterations", C.c_int32),
+        ("reserved0", C.c_int32),
+    ]
+
+    def as_dict(self):
+        return {f: getattr(self, f) for f, _ in self._fields_ if f != "reserved0"}
+
+
+class OSummary(C.Structure):
+    _fields_ = [
+        ("initial_cost", C.c_double), ("final_cost", C.c_double), ("rms_px", C.c_double),
+        ("num_iterations", C.c_int32), ("num_successful_steps", C.c_int32), ("termination_type", C.c_int32),
+        ("linear_solver_used", C.c_int32), ("total_linear_iterations", C.c_int32), ("n_threads", C.c_int32),
+        ("eval_seconds", C.c_double), ("linear_seconds", C.c_double), ("total_seconds", C.c_double),
+        ("trace", C.POINTER(OIteration)), ("trace_capacity", C.c_int32), ("trace_count", C.c_int32),
+    ]
+
+
+def build(force: bool = False) -> str:
+    if force or not os.path.exists(_SO) or any(
+        os.path.getmtime(os.path.join(_HERE, f)) > os.path.getmtime(_SO)
+        for f in ("ba_oracle.cpp", "ba_oracle_chol.cpp", "ba_oracle.h", "Makefile")
+    ):
+        subprocess.run(["make", "-C", _HERE], check=True, capture_output=True)
+    return _SO
+
+
+_lib = None
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int32)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(build())
+        _lib.ba_oracle_default_options.argtypes = [C.POINTER(OOptions)]
+        _lib.ba_oracle_eval.restype = C.c_int
+        _lib.ba_oracle_eval.argtypes = [C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp, _dp, _dp, _dp, C.c_int]
+        _lib.ba_oracle_schur.restype = C.c_int
+        _lib.ba_oracle_schur.argtypes = [C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp,
+                                         C.POINTER(OOptions), C.c_double, _dp, _dp, _dp, _dp, _dp, _dp, _dp]
+        _lib.ba_oracle_solve.restype = C.c_int
+        _lib.ba_oracle_solve.argtypes = [C.c_int, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp,
+                                         C.POINTER(OOptions), C.POINTER(OSummary)]
+        _lib.ba_oracle_cholesky.restype = C.c_int
+        _lib.ba_oracle_cholesky.argtypes = [_dp, C.c_int64, C.c_int]
+    return _lib
+
+
+def _d(a):
+    return None if a is None else a.ctypes.data_as(_dp)
+
+
+def _i(a):
+    return a.ctypes.data_as(_ip)
+
+
+def default_options(**kw) -> OOptions:
+    o = OOptions()
+    lib().ba_oracle_default_options(C.byref(o))
+    for k, v in kw.items():
+        if not hasattr(o, k):
+            raise AttributeError(k)
+        setattr(o, k, v)
+    return o
+
+
+def evaluate(prob, cam=None, pts=None, want_jac=True, threads=1):
+    """r [n,2], J [n,2,9], cost by dual numbers (reference functor CTracker.cpp:585-604)."""
+    cam = prob.cam if cam is None else cam
+    pts = prob.pts if pts is None else pts
+    n = prob.n_obs
+    r = np.empty((n, 2))
+    J = np.empty((n, 2, 9)) if want_jac else None
+    cost = C.c_double()
+    rc = lib().ba_oracle_eval(n, _d(prob.obs), _i(prob.cam_idx), _i(prob.pt_idx), prob.n_cams, _d(prob.K), _d(prob.dist),
+                              _d(cam), prob.n_pts, _d(pts), _d(r), _d(J), C.byref(cost), threads)
+    if rc:
+        raise RuntimeError(f"ba_oracle_eval -> {rc}")
+    return r, J, cost.value
+
+
+def schur(prob, radius=1e4, opts=None, cam=None, pts=None):
+    cam = prob.cam if cam is None else cam
+    pts = prob.pts if pts is None else pts
+    opts = opts or default_options()
+    nc, npt = prob.n_cams, prob.n_pts
+    out = dict(S=np.zeros((6 * nc, 6 * nc)), rhs=np.zeros(6 * nc), Hcc=np.zeros((nc, 6, 6)), gc=np.zeros((nc, 6)),
+               Hpp=np.zeros((npt, 3, 3)), gp=np.zeros((npt, 3)), scale=np.zeros(6 * nc + 3 * npt))
+    rc = lib().ba_oracle_schur(prob.n_obs, _d(prob.obs), _i(prob.cam_idx), _i(prob.pt_idx), nc, _d(prob.K), _d(prob.dist),
+                               _d(cam), npt, _d(pts), C.byref(opts), radius, _d(out["S"]), _d(out["rhs"]), _d(out["Hcc"]),
+                               _d(out["gc"]), _d(out["Hpp"]), _d(out["gp"]), _d(out["scale"]))
+    if rc:
+        raise RuntimeError(f"ba_oracle_schur -> {rc}")
+    return out
+
+
+def solve(prob, mode=2, opts=None, trace_capacity=64):
+    """In-place Ceres-semantics LM on copies; returns (cam, pts, summary dict, trace list)."""
+    opts = opts or default_options()
+    cam, pts = prob.cam.copy(), prob.pts.copy()
+    trace = (OIteration * trace_capacity)()
+    s = OSummary()
+    s.trace = C.cast(trace, C.POINTER(OIteration))
+    s.trace_capacity = trace_capacity
+    rc = lib().ba_oracle_solve(mode, prob.n_obs, _d(prob.obs), _i(prob.cam_idx), _i(prob.pt_idx), prob.n_cams, _d(prob.K),
+                               _d(prob.dist), _d(cam), prob.n_pts, _d(pts), C.byref(opts), C.byref(s))
+    if rc:
+        raise RuntimeError(f"ba_oracle_solve -> {rc}")
+    summ = {f: getattr(s, f) for f, _ in s._fields_ if f != "trace"}
+    return cam, pts, summ, [trace[i].as_dict() for i in range(s.trace_count)]
+
+
+def cholesky(A, threads=1):
+    L = np.array(A, dtype=np.float64, order="C")
+    rc = lib().ba_oracle_cholesky(_d(L), L.shape[0], threads)
+    return rc, np.tril(L)
