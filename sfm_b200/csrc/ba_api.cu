@@ -1,0 +1,388 @@
+// ba_api.cu — the extern "C" boundary declared in include/hsfm_ba.h.
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <unordered_map>
+
+#include "ba_internal.h"
+
+using namespace hsfm;
+
+struct hsfm_ba_ctx {
+  Ctx c;
+};
+
+namespace {
+
+double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+int check_device(int device_id) {
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) { cudaGetLastError(); return HSFM_BA_ERR_NO_DEVICE; }
+  if (device_id < 0 || device_id >= count) return HSFM_BA_ERR_ARG;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device_id) != cudaSuccess) return HSFM_BA_ERR_NO_DEVICE;
+  if (prop.major != 10) return HSFM_BA_ERR_NO_DEVICE;  // built for sm_100a only; no fallback path
+  return 0;
+}
+
+int valid_mode(int mode) { return mode >= 0 && mode <= 2; }
+
+int64_t global_obs(Ctx& c) {
+  // sum of the (already all-reduced) per-camera observation counts
+  std::vector<int> h((size_t)c.prob.n_cams);
+  if (c.prob.n_cams == 0) return 0;
+  cudaMemcpyAsync(h.data(), c.prob.cam_nobs, sizeof(int) * h.size(), cudaMemcpyDeviceToHost, c.stream);
+  cudaStreamSynchronize(c.stream);
+  int64_t t = 0;
+  for (int v : h) t += v;
+  return t;
+}
+
+}  // namespace
+
+extern "C" {
+
+int hsfm_ba_abi_version(void) { return HSFM_BA_ABI_VERSION; }
+
+const char* hsfm_ba_error_string(int code) {
+  static thread_local char buf[96];
+  switch (code) {
+    case HSFM_BA_OK: return "ok";
+    case HSFM_BA_ERR_ARG: return "invalid argument";
+    case HSFM_BA_ERR_NO_DEVICE: return "no usable sm_100 CUDA device (this library has no CPU path)";
+    case HSFM_BA_ERR_STATE: return "invalid call order / no resident problem";
+    case HSFM_BA_ERR_UNSUPPORTED: return "unsupported problem (a point with more than 256 observations, or sizes beyond int32)";
+    case HSFM_BA_ERR_NOMEM: return "out of device memory";
+    case HSFM_BA_ERR_COMM: return "NCCL unavailable or communicator initialisation failed";
+    default: break;
+  }
+  if (code >= 2000) { std::snprintf(buf, sizeof(buf), "NCCL error %d", code - 2000); return buf; }
+  if (code >= 1000) { std::snprintf(buf, sizeof(buf), "CUDA error %d: %s", code - 1000, cudaGetErrorString((cudaError_t)(code - 1000))); return buf; }
+  return "unknown error";
+}
+
+void hsfm_ba_default_options(hsfm_ba_options* o) {
+  if (!o) return;
+  std::memset(o, 0, sizeof(*o));
+  o->max_num_iterations = 50;
+  o->max_consecutive_invalid_steps = 5;
+  o->jacobi_scaling = 1;
+  o->linear_solver = HSFM_BA_LINEAR_AUTO;
+  o->dense_max_cams = 512;
+  o->pcg_max_iterations = 1000;
+  o->verbose = 0;
+  o->initial_trust_region_radius = 1e4;
+  o->max_trust_region_radius = 1e16;
+  o->min_trust_region_radius = 1e-32;
+  o->min_relative_decrease = 1e-3;
+  o->min_lm_diagonal = 1e-6;
+  o->max_lm_diagonal = 1e32;
+  o->function_tolerance = 1e-6;
+  o->gradient_tolerance = 1e-10;
+  o->parameter_tolerance = 1e-8;
+  o->pcg_tolerance = 1e-10;
+}
+
+int hsfm_ba_create(hsfm_ba_ctx** out, int device_id) {
+  if (!out) return HSFM_BA_ERR_ARG;
+  *out = nullptr;
+  int rc = check_device(device_id);
+  if (rc) return rc;
+  HSFM_CUDA(cudaSetDevice(device_id));
+  hsfm_ba_ctx* h = new (std::nothrow) hsfm_ba_ctx();
+  if (!h) return HSFM_BA_ERR_NOMEM;
+  h->c.device = device_id;
+  cudaError_t e = cudaStreamCreateWithFlags(&h->c.own_stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) { delete h; return 1000 + (int)e; }
+  h->c.stream = h->c.own_stream;
+  *out = h;
+  return 0;
+}
+
+void hsfm_ba_destroy(hsfm_ba_ctx* h) {
+  if (!h) return;
+  cudaSetDevice(h->c.device);
+  cudaStreamSynchronize(h->c.stream);
+  h->c.prob.release();
+  if (h->c.prob.S) { cudaFree(h->c.prob.S); h->c.prob.S = nullptr; }
+  h->c.comm.destroy();
+  if (h->c.own_stream) cudaStreamDestroy(h->c.own_stream);
+  delete h;
+}
+
+int hsfm_ba_set_stream(hsfm_ba_ctx* h, void* cuda_stream) {
+  if (!h) return HSFM_BA_ERR_ARG;
+  cudaStreamSynchronize(h->c.stream);
+  h->c.stream = cuda_stream ? (cudaStream_t)cuda_stream : h->c.own_stream;
+  return 0;
+}
+
+int hsfm_ba_comm_unique_id(void* unique_id_128) {
+  if (!unique_id_128) return HSFM_BA_ERR_ARG;
+  return comm_unique_id(unique_id_128);
+}
+
+int hsfm_ba_comm_init(hsfm_ba_ctx* h, const void* unique_id_128, int rank, int n_ranks) {
+  if (!h || n_ranks < 1 || rank < 0 || rank >= n_ranks) return HSFM_BA_ERR_ARG;
+  if (n_ranks > 1 && !unique_id_128) return HSFM_BA_ERR_ARG;
+  cudaSetDevice(h->c.device);
+  h->c.comm.destroy();
+  return comm_init(h->c.comm, unique_id_128, rank, n_ranks);
+}
+
+// ---- resident problem -------------------------------------------------------------------------
+
+int hsfm_ba_problem_upload(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
+                           int32_t n_cams, const double* K9, const double* dist, const double* cam_rt, int64_t n_pts, const double* pts) {
+  if (!h || !valid_mode(mode) || n_obs < 0 || n_cams < 0 || n_pts < 0) return HSFM_BA_ERR_ARG;
+  if (n_obs > 0 && (!obs_xy || !cam_idx || !pt_idx)) return HSFM_BA_ERR_ARG;
+  if (n_cams > 0 && (!K9 || !cam_rt)) return HSFM_BA_ERR_ARG;
+  if (n_pts > 0 && !pts) return HSFM_BA_ERR_ARG;
+  HSFM_CUDA(cudaSetDevice(h->c.device));
+  h->c.has_problem = false;
+  if (h->c.prob.S) { cudaFree(h->c.prob.S); h->c.prob.S = nullptr; h->c.prob.S_capacity = 0; }
+  double setup = 0, h2d = 0;
+  int rc = build_problem(h->c.prob, mode, n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, dist, cam_rt, n_pts, pts, h->c.comm, h->c.stream, &setup, &h2d);
+  if (rc) { h->c.prob.release(); return rc; }
+  launch_jacobi_scale(h->c.prob, false, h->c.stream);  // scale = 1 until a solve computes it
+  h->c.prob.scal_host[20] = setup;
+  h->c.prob.scal_host[21] = h2d;
+  h->c.has_problem = true;
+  return 0;
+}
+
+int hsfm_ba_problem_reset(hsfm_ba_ctx* h) {
+  if (!h || !h->c.has_problem) return HSFM_BA_ERR_STATE;
+  Problem& P = h->c.prob;
+  HSFM_CUDA(cudaSetDevice(h->c.device));
+  HSFM_CUDA(cudaMemcpyAsync(P.cam_x, P.cam_x0, sizeof(double) * 6 * P.n_cams, cudaMemcpyDeviceToDevice, h->c.stream));
+  HSFM_CUDA(cudaMemcpyAsync(P.pts_x, P.pts_x0, sizeof(double) * 3 * (size_t)P.n_pts, cudaMemcpyDeviceToDevice, h->c.stream));
+  HSFM_CUDA(cudaMemcpyAsync(P.pts_c, P.pts_x0, sizeof(double) * 3 * (size_t)P.n_pts, cudaMemcpyDeviceToDevice, h->c.stream));
+  return 0;
+}
+
+int hsfm_ba_problem_solve(hsfm_ba_ctx* h, const hsfm_ba_options* opts, hsfm_ba_summary* summary) {
+  if (!h || !opts) return HSFM_BA_ERR_ARG;
+  if (!h->c.has_problem) return HSFM_BA_ERR_STATE;
+  HSFM_CUDA(cudaSetDevice(h->c.device));
+  if (summary) { summary->setup_ms = h->c.prob.scal_host[20]; summary->h2d_ms = h->c.prob.scal_host[21]; }
+  int rc = lm_solve(h->c, *opts, summary);
+  if (rc) return rc;
+  if (summary) {
+    const int64_t n = global_obs(h->c);
+    summary->rms_px = n > 0 ? std::sqrt(2.0 * summary->final_cost / (double)n) : 0.0;
+  }
+  return 0;
+}
+
+int hsfm_ba_problem_eval(hsfm_ba_ctx* h, double* cost) {
+  if (!h || !h->c.has_problem) return HSFM_BA_ERR_STATE;
+  Problem& P = h->c.prob;
+  cudaStream_t s = h->c.stream;
+  HSFM_CUDA(cudaSetDevice(h->c.device));
+  launch_cam_prep(P, P.cam_x, nullptr, P.rows_x, s);
+  launch_rj(P, P.rows_x, P.pts_x, nullptr, true, true, s);
+  launch_finalize_scalars(P, s);
+  if (h->c.comm.n_ranks > 1) { int rc = h->c.comm.allreduce_sum(P.scal + S_COST, 1, s); if (rc) return rc; }
+  if (cost) {
+    HSFM_CUDA(cudaMemcpyAsync(P.scal_host, P.scal, sizeof(double) * 16, cudaMemcpyDeviceToHost, s));
+    HSFM_CUDA(cudaStreamSynchronize(s));
+    *cost = P.scal_host[S_COST];
+  }
+  return 0;
+}
+
+int hsfm_ba_problem_download(hsfm_ba_ctx* h, double* cam_rt, double* pts) {
+  if (!h || !h->c.has_problem) return HSFM_BA_ERR_STATE;
+  Problem& P = h->c.prob;
+  HSFM_CUDA(cudaSetDevice(h->c.device));
+  if (cam_rt) HSFM_CUDA(cudaMemcpyAsync(cam_rt, P.cam_x, sizeof(double) * 6 * P.n_cams, cudaMemcpyDeviceToHost, h->c.stream));
+  if (pts) HSFM_CUDA(cudaMemcpyAsync(pts, P.pts_x, sizeof(double) * 3 * (size_t)P.n_pts, cudaMemcpyDeviceToHost, h->c.stream));
+  HSFM_CUDA(cudaStreamSynchronize(h->c.stream));
+  return 0;
+}
+
+int64_t hsfm_ba_problem_algorithmic_bytes(hsfm_ba_ctx* h, const char* kernel) {
+  if (!h || !h->c.has_problem || !kernel) return 0;
+  const Problem& P = h->c.prob;
+  const int64_t N = P.n_obs, C = P.n_cams, Q = P.n_pts;
+  // SURVEY.md §8(d) / DESIGN.md §5
+  if (!std::strcmp(kernel, "rj")) return 184 * N + 88 * C + 24 * Q;              // obs 24 + r,J 160 per obs; unique parameters
+  if (!std::strcmp(kernel, "rj_form")) return 184 * N + 88 * C + 24 * Q + 72 * Q;  // + Hpp (48) and g_p (24) per point
+  if (!std::strcmp(kernel, "schur_matvec")) return 152 * N + 48 * Q + 96 * C;      // Jc 96 + Jp 48 + cam 4 + pt 4 ; Hpp^-1 ; p, q
+  if (!std::strcmp(kernel, "backsub")) return 168 * N + 120 * Q + 48 * C;          // + r 16 ; Hpp^-1 48, z_p 24, y_p 24, cand 24
+  if (!std::strcmp(kernel, "cam_form")) return 20 * N + 24 * Q + 88 * C + 216 * C; // obs_cs 16 + pt 4 ; point gather ; rows ; Hcc+gc out
+  if (!std::strcmp(kernel, "cost")) return 24 * N + 24 * Q + 88 * C;
+  return 0;
+}
+
+int hsfm_ba_problem_time_kernel(hsfm_ba_ctx* h, const char* kernel, int reps, double* ms) {
+  if (!h || !h->c.has_problem || !kernel || reps <= 0 || !ms) return HSFM_BA_ERR_ARG;
+  Problem& P = h->c.prob;
+  cudaStream_t s = h->c.stream;
+  HSFM_CUDA(cudaSetDevice(h->c.device));
+  cudaEvent_t e0, e1;
+  HSFM_CUDA(cudaEventCreate(&e0));
+  HSFM_CUDA(cudaEventCreate(&e1));
+  auto run = [&]() -> int {
+    if (!std::strcmp(kernel, "rj")) launch_rj(P, P.rows_x, P.pts_x, P.scale_p, true, false, s);
+    else if (!std::strcmp(kernel, "rj_form")) launch_rj(P, P.rows_x, P.pts_x, P.scale_p, true, true, s);
+    else if (!std::strcmp(kernel, "schur_matvec")) launch_schur_matvec(P, P.pcg_p, P.pcg_q, s);
+    else if (!std::strcmp(kernel, "backsub")) launch_backsub(P, s);
+    else if (!std::strcmp(kernel, "cam_form")) launch_cam_major(P, P.rows_x, P.pts_x, P.scale_p, 0, s);
+    else if (!std::strcmp(kernel, "cost")) launch_cost(P, P.rows_x, P.pts_x, P_COST, s);
+    else return HSFM_BA_ERR_ARG;
+    return 0;
+  };
+  // make sure the flag that silences the mat-vec is clear and a linearisation exists
+  HSFM_CUDA(cudaMemsetAsync(P.flags, 0, sizeof(int) * FLAG_SLOTS, s));
+  int rc = run();
+  if (rc) return rc;
+  HSFM_CUDA(cudaEventRecord(e0, s));
+  for (int i = 0; i < reps; ++i) run();
+  HSFM_CUDA(cudaEventRecord(e1, s));
+  HSFM_CUDA(cudaEventSynchronize(e1));
+  float t = 0.f;
+  cudaEventElapsedTime(&t, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  launch_finalize_scalars(P, s);  // drain pending reduction tasks queued by the launchers
+  *ms = (double)t / reps;
+  return 0;
+}
+
+// ---- one-shot solves on host buffers ------------------------------------------------------------
+
+int hsfm_ba_solve_packed(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
+                         int32_t n_cams, const double* K9, const double* dist, double* cam_rt, int64_t n_pts, double* pts,
+                         const hsfm_ba_options* opts, hsfm_ba_summary* summary) {
+  if (!h) return HSFM_BA_ERR_ARG;
+  if (!valid_mode(mode)) return HSFM_BA_OK;  // CTracker.cpp:692-693: nothing is added, Solve() is a no-op
+  hsfm_ba_options def;
+  if (!opts) { hsfm_ba_default_options(&def); opts = &def; }
+  int rc = hsfm_ba_problem_upload(h, mode, n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, dist, cam_rt, n_pts, pts);
+  if (rc) return rc;
+  rc = hsfm_ba_problem_solve(h, opts, summary);
+  if (rc) return rc;
+  const double t0 = now_ms();
+  rc = hsfm_ba_problem_download(h, cam_rt, pts);
+  if (summary) summary->d2h_ms = now_ms() - t0;
+  return rc;
+}
+
+int hsfm_ba_solve_ptr(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, int32_t n_cams,
+                      const double* K9, double* const* R, double* const* t, double* const* pts3d, const hsfm_ba_options* opts,
+                      hsfm_ba_summary* summary) {
+  if (!h || n_obs < 0 || n_cams < 0) return HSFM_BA_ERR_ARG;
+  if (!valid_mode(mode)) return HSFM_BA_OK;
+  if (n_obs > 0 && (!obs_xy || !cam_idx || !pts3d)) return HSFM_BA_ERR_ARG;
+  if (n_cams > 0 && (!K9 || !R || !t)) return HSFM_BA_ERR_ARG;
+  // pointer identity -> compact point ids, in order of first appearance (CSfM.cpp:331, CMap.cpp:215)
+  std::unordered_map<const double*, int32_t> ids;
+  ids.reserve((size_t)n_obs / 2 + 16);
+  std::vector<int32_t> pt_idx((size_t)n_obs);
+  std::vector<double*> uniq;
+  for (int64_t i = 0; i < n_obs; ++i) {
+    double* p = pts3d[i];
+    if (!p) return HSFM_BA_ERR_ARG;
+    auto it = ids.find(p);
+    if (it == ids.end()) {
+      it = ids.emplace(p, (int32_t)uniq.size()).first;
+      uniq.push_back(p);
+    }
+    pt_idx[(size_t)i] = it->second;
+  }
+  const int64_t n_pts = (int64_t)uniq.size();
+  std::vector<double> cam((size_t)n_cams * 6), pts((size_t)n_pts * 3);
+  for (int c = 0; c < n_cams; ++c) {
+    if (!R[c] || !t[c]) return HSFM_BA_ERR_ARG;
+    for (int k = 0; k < 3; ++k) { cam[6 * (size_t)c + k] = R[c][k]; cam[6 * (size_t)c + 3 + k] = t[c][k]; }
+  }
+  for (int64_t p = 0; p < n_pts; ++p)
+    for (int k = 0; k < 3; ++k) pts[3 * (size_t)p + k] = uniq[(size_t)p][k];
+  int rc = hsfm_ba_solve_packed(h, mode, n_obs, obs_xy, cam_idx, pt_idx.data(), n_cams, K9, nullptr, cam.data(), n_pts, pts.data(), opts, summary);
+  if (rc) return rc;  // parameters untouched on failure
+  if (mode != HSFM_BA_STRUCT_ONLY)
+    for (int c = 0; c < n_cams; ++c)
+      for (int k = 0; k < 3; ++k) { R[c][k] = cam[6 * (size_t)c + k]; t[c][k] = cam[6 * (size_t)c + 3 + k]; }
+  if (mode != HSFM_BA_POSE_ONLY)
+    for (int64_t p = 0; p < n_pts; ++p)
+      for (int k = 0; k < 3; ++k) uniq[(size_t)p][k] = pts[3 * (size_t)p + k];
+  return 0;
+}
+
+// ---- parity taps --------------------------------------------------------------------------------
+
+int hsfm_ba_eval(hsfm_ba_ctx* h, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx, int32_t n_cams,
+                 const double* K9, const double* dist, const double* cam_rt, int64_t n_pts, const double* pts, double* residuals,
+                 double* jac, double* cost) {
+  if (!h) return HSFM_BA_ERR_ARG;
+  int rc = hsfm_ba_problem_upload(h, 2, n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, dist, cam_rt, n_pts, pts);
+  if (rc) return rc;
+  Problem& P = h->c.prob;
+  cudaStream_t s = h->c.stream;
+  rc = hsfm_ba_problem_eval(h, cost);
+  if (rc) return rc;
+  if (n_obs == 0) { if (cost) *cost = 0.0; return 0; }
+  double *d_r = nullptr, *d_j = nullptr;
+  if (residuals) HSFM_CUDA(cudaMalloc(&d_r, sizeof(double) * 2 * (size_t)n_obs));
+  if (jac) HSFM_CUDA(cudaMalloc(&d_j, sizeof(double) * 18 * (size_t)n_obs));
+  launch_scatter_eval(P, d_r, d_j, s);
+  if (residuals) HSFM_CUDA(cudaMemcpyAsync(residuals, d_r, sizeof(double) * 2 * (size_t)n_obs, cudaMemcpyDeviceToHost, s));
+  if (jac) HSFM_CUDA(cudaMemcpyAsync(jac, d_j, sizeof(double) * 18 * (size_t)n_obs, cudaMemcpyDeviceToHost, s));
+  HSFM_CUDA(cudaStreamSynchronize(s));
+  if (d_r) cudaFree(d_r);
+  if (d_j) cudaFree(d_j);
+  return 0;
+}
+
+int hsfm_ba_schur(hsfm_ba_ctx* h, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx, int32_t n_cams,
+                  const double* K9, const double* dist, const double* cam_rt, int64_t n_pts, const double* pts, const hsfm_ba_options* opts,
+                  double radius, double* S_dense, double* rhs, double* Hcc, double* gc, double* Hpp, double* gp, double* scale) {
+  if (!h || !opts || !(radius > 0.0)) return HSFM_BA_ERR_ARG;
+  int rc = hsfm_ba_problem_upload(h, 2, n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, dist, cam_rt, n_pts, pts);
+  if (rc) return rc;
+  Problem& P = h->c.prob;
+  cudaStream_t s = h->c.stream;
+  const size_t n6 = 6 * (size_t)n_cams;
+  if (cudaMalloc(&P.S, sizeof(double) * std::max<size_t>(1, n6 * n6)) != cudaSuccess) { cudaGetLastError(); P.S = nullptr; return HSFM_BA_ERR_NOMEM; }
+  P.S_capacity = n6 * n6;
+  // scaling pass, linearisation, blocks
+  launch_cam_prep(P, P.cam_x, nullptr, P.rows_x, s);
+  launch_rj(P, P.rows_x, P.pts_x, nullptr, false, true, s);
+  launch_cam_major(P, P.rows_x, P.pts_x, nullptr, 0, s);
+  launch_jacobi_scale(P, opts->jacobi_scaling != 0, s);
+  launch_cam_prep(P, P.cam_x, P.scale_c, P.rows_x, s);
+  launch_rj(P, P.rows_x, P.pts_x, P.scale_p, true, true, s);
+  launch_cam_major(P, P.rows_x, P.pts_x, P.scale_p, 0, s);
+  launch_point_invert(P, radius, opts->min_lm_diagonal, opts->max_lm_diagonal, s);
+  launch_cam_diag(P, radius, opts->min_lm_diagonal, opts->max_lm_diagonal, s);
+  launch_dense_init(P, true, s);
+  launch_dense_schur(P, s);
+  launch_schur_rhs(P, true, s);
+  launch_mirror_lower(P, s);
+  launch_finalize_scalars(P, s);
+  double *d_Hcc = nullptr, *d_Hpp = nullptr;
+  if (Hcc) HSFM_CUDA(cudaMalloc(&d_Hcc, sizeof(double) * 36 * std::max(1, (int)n_cams)));
+  if (Hpp) HSFM_CUDA(cudaMalloc(&d_Hpp, sizeof(double) * 9 * std::max<size_t>(1, (size_t)n_pts)));
+  P.scal_host[31] = radius; P.scal_host[30] = opts->min_lm_diagonal; P.scal_host[29] = opts->max_lm_diagonal;
+  launch_export_blocks(P, d_Hcc, d_Hpp, s);
+  if (S_dense) HSFM_CUDA(cudaMemcpyAsync(S_dense, P.S, sizeof(double) * n6 * n6, cudaMemcpyDeviceToHost, s));
+  if (rhs) HSFM_CUDA(cudaMemcpyAsync(rhs, P.rhs, sizeof(double) * n6, cudaMemcpyDeviceToHost, s));
+  if (Hcc) HSFM_CUDA(cudaMemcpyAsync(Hcc, d_Hcc, sizeof(double) * 36 * n_cams, cudaMemcpyDeviceToHost, s));
+  if (gc) HSFM_CUDA(cudaMemcpyAsync(gc, P.gc, sizeof(double) * n6, cudaMemcpyDeviceToHost, s));
+  if (Hpp) HSFM_CUDA(cudaMemcpyAsync(Hpp, d_Hpp, sizeof(double) * 9 * (size_t)n_pts, cudaMemcpyDeviceToHost, s));
+  if (gp) HSFM_CUDA(cudaMemcpyAsync(gp, P.gp, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToHost, s));
+  if (scale) {
+    HSFM_CUDA(cudaMemcpyAsync(scale, P.scale_c, sizeof(double) * n6, cudaMemcpyDeviceToHost, s));
+    HSFM_CUDA(cudaMemcpyAsync(scale + n6, P.scale_p, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToHost, s));
+  }
+  HSFM_CUDA(cudaStreamSynchronize(s));
+  if (d_Hcc) cudaFree(d_Hcc);
+  if (d_Hpp) cudaFree(d_Hpp);
+  return 0;
+}
+
+}  // extern "C"

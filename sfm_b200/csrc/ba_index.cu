@@ -1,0 +1,242 @@
+// ba_index.cu — upload + one-time index build of a resident problem (the packed
+// arrays CSfM::bundleAdjustment assembles at CSfM.cpp:311-341 arrive camera-major; the solver
+// wants them point-major in tiles plus a camera-major copy).  Sorting is a plain library
+// operation done once per problem: CUB radix sort (stable, so equal keys keep input order and
+// every later floating-point sum has a fixed order).
+#include <cub/cub.cuh>
+
+#include <algorithm>
+#include <chrono>
+
+#include "ba_internal.h"
+
+namespace hsfm {
+
+void Problem::release() {
+  for (void* p : allocs) cudaFree(p);
+  allocs.clear();
+  if (scal_host) cudaFreeHost(scal_host);
+  if (flags_host) cudaFreeHost(flags_host);
+  scal_host = nullptr;
+  flags_host = nullptr;
+  S = nullptr;
+  S_capacity = 0;
+  *this = Problem();
+}
+
+namespace {
+
+template <typename T>
+int dev_alloc(Problem& P, T** out, size_t count) {
+  void* p = nullptr;
+  if (count == 0) count = 1;
+  cudaError_t e = cudaMalloc(&p, count * sizeof(T));
+  if (e != cudaSuccess) return HSFM_BA_ERR_NOMEM;
+  P.allocs.push_back(p);
+  *out = reinterpret_cast<T*>(p);
+  return 0;
+}
+#define ALLOC(ptr, count)                         \
+  do {                                            \
+    int rc__ = dev_alloc(P, &(ptr), (count));     \
+    if (rc__) return rc__;                        \
+  } while (0)
+
+__global__ void iota_kernel(int n, int* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = i;
+}
+__global__ void gather_obs_kernel(int n, const int* __restrict__ order, const double2* __restrict__ obs_in, const int* __restrict__ cam_in,
+                                  double2* __restrict__ obs, int* __restrict__ cam) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int o = order[i];
+  obs[i] = obs_in[o];
+  cam[i] = cam_in[o];
+}
+__global__ void gather_cs_kernel(int n, const int* __restrict__ pos, const double2* __restrict__ obs, const int* __restrict__ pt,
+                                 double2* __restrict__ obs_cs, int* __restrict__ pt_cs) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int j = pos[i];
+  obs_cs[i] = obs[j];
+  pt_cs[i] = pt[j];
+}
+// start[k] = first index i with keys[i] >= k   (keys sorted ascending), k = 0..n_keys
+__global__ void lower_bound_kernel(int n, const int* __restrict__ keys, int n_keys, int* __restrict__ start) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > n_keys) return;
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (keys[mid] < k) lo = mid + 1; else hi = mid;
+  }
+  start[k] = lo;
+}
+__global__ void diff_kernel(int n, const int* __restrict__ start, int* __restrict__ cnt) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) cnt[k] = start[k + 1] - start[k];
+}
+
+inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+}  // namespace
+
+int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
+                  int32_t n_cams, const double* K9, const double* dist, const double* cam_rt, int64_t n_pts64, const double* pts,
+                  Comm& comm, cudaStream_t s, double* setup_ms, double* h2d_ms) {
+  P.release();
+  if (n_obs64 >= (int64_t)1 << 31 || n_pts64 >= (int64_t)1 << 30) return HSFM_BA_ERR_UNSUPPORTED;
+  const int n = (int)n_obs64, n_pts = (int)n_pts64;
+  P.mode = mode; P.n_obs = n; P.n_cams = n_cams; P.n_pts = n_pts;
+
+  // ---- host-side validation of indices (the reference indexes unchecked: CTracker.cpp:676-690) ----
+  for (int i = 0; i < n; ++i)
+    if (cam_idx[i] < 0 || cam_idx[i] >= n_cams || pt_idx[i] < 0 || pt_idx[i] >= n_pts) return HSFM_BA_ERR_ARG;
+
+  const double t_h2d0 = now_ms();
+  double2* obs_in; int *cam_in, *pt_in;
+  ALLOC(obs_in, n); ALLOC(cam_in, n); ALLOC(pt_in, n);
+  ALLOC(P.K9, 9 * (size_t)n_cams); ALLOC(P.dist, 2 * (size_t)n_cams);
+  ALLOC(P.cam_x, 6 * (size_t)n_cams); ALLOC(P.pts_x, 3 * (size_t)n_pts);
+  ALLOC(P.cam_x0, 6 * (size_t)n_cams); ALLOC(P.pts_x0, 3 * (size_t)n_pts);
+  HSFM_CUDA(cudaMemcpyAsync(obs_in, obs_xy, sizeof(double) * 2 * n, cudaMemcpyHostToDevice, s));
+  HSFM_CUDA(cudaMemcpyAsync(cam_in, cam_idx, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, s));
+  HSFM_CUDA(cudaMemcpyAsync(pt_in, pt_idx, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, s));
+  HSFM_CUDA(cudaMemcpyAsync(P.K9, K9, sizeof(double) * 9 * n_cams, cudaMemcpyHostToDevice, s));
+  if (dist) HSFM_CUDA(cudaMemcpyAsync(P.dist, dist, sizeof(double) * 2 * n_cams, cudaMemcpyHostToDevice, s));
+  else HSFM_CUDA(cudaMemsetAsync(P.dist, 0, sizeof(double) * 2 * std::max(1, n_cams), s));
+  HSFM_CUDA(cudaMemcpyAsync(P.cam_x0, cam_rt, sizeof(double) * 6 * n_cams, cudaMemcpyHostToDevice, s));
+  HSFM_CUDA(cudaMemcpyAsync(P.pts_x0, pts, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyHostToDevice, s));
+  HSFM_CUDA(cudaMemcpyAsync(P.cam_x, P.cam_x0, sizeof(double) * 6 * n_cams, cudaMemcpyDeviceToDevice, s));
+  HSFM_CUDA(cudaMemcpyAsync(P.pts_x, P.pts_x0, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToDevice, s));
+  HSFM_CUDA(cudaStreamSynchronize(s));
+  const double t_setup0 = now_ms();
+  if (h2d_ms) *h2d_ms = t_setup0 - t_h2d0;
+
+  // ---- static arrays ----
+  double2 *obs, *obs_cs; int *cam, *pt, *pt_cs, *pt_start, *cam_start, *iota, *pos_cs, *cam_sorted;
+  ALLOC(obs, n); ALLOC(cam, n); ALLOC(pt, n); ALLOC(obs_cs, n); ALLOC(pt_cs, n);
+  ALLOC(pt_start, (size_t)n_pts + 1); ALLOC(cam_start, (size_t)n_cams + 1);
+  ALLOC(iota, n); ALLOC(P.order_pm, n); ALLOC(pos_cs, n); ALLOC(cam_sorted, n);
+  if (n > 0) {
+    iota_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, iota);
+    // point-major: stable sort by point id
+    size_t tmp_bytes = 0, tmp2 = 0;
+    int pbits = 1; while ((1ll << pbits) < std::max(2, n_pts)) ++pbits;
+    int cbits = 1; while ((1ll << cbits) < std::max(2, (int)n_cams)) ++cbits;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, pt_in, pt, iota, P.order_pm, n, 0, pbits, s);
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp2, cam, cam_sorted, iota, pos_cs, n, 0, cbits, s);
+    tmp_bytes = std::max(tmp_bytes, tmp2);
+    void* tmp = nullptr;
+    HSFM_CUDA(cudaMalloc(&tmp, tmp_bytes));
+    cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, pt_in, pt, iota, P.order_pm, n, 0, pbits, s);
+    gather_obs_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, P.order_pm, obs_in, cam_in, obs, cam);
+    // camera-major: stable sort of point-major positions by camera
+    cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, cam, cam_sorted, iota, pos_cs, n, 0, cbits, s);
+    gather_cs_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, pos_cs, obs, pt, obs_cs, pt_cs);
+    lower_bound_kernel<<<cdiv(n_pts + 1, 256), 256, 0, s>>>(n, pt, n_pts, pt_start);
+    lower_bound_kernel<<<cdiv(n_cams + 1, 256), 256, 0, s>>>(n, cam_sorted, n_cams, cam_start);
+    HSFM_CUDA(cudaStreamSynchronize(s));
+    cudaFree(tmp);
+  } else {
+    HSFM_CUDA(cudaMemsetAsync(pt_start, 0, sizeof(int) * ((size_t)n_pts + 1), s));
+    HSFM_CUDA(cudaMemsetAsync(cam_start, 0, sizeof(int) * ((size_t)n_cams + 1), s));
+  }
+
+  // ---- tiles: greedy packing of whole points into <= TILE observations (host, O(n_pts)) ----
+  std::vector<int> h_pt_start((size_t)n_pts + 1), h_cam_start((size_t)n_cams + 1);
+  HSFM_CUDA(cudaMemcpyAsync(h_pt_start.data(), pt_start, sizeof(int) * ((size_t)n_pts + 1), cudaMemcpyDeviceToHost, s));
+  HSFM_CUDA(cudaMemcpyAsync(h_cam_start.data(), cam_start, sizeof(int) * ((size_t)n_cams + 1), cudaMemcpyDeviceToHost, s));
+  HSFM_CUDA(cudaStreamSynchronize(s));
+  std::vector<int> tiles;
+  tiles.reserve((size_t)n / (TILE - 32) + 2);
+  int max_track = 0;
+  {
+    int tile_b = 0;
+    tiles.push_back(0);
+    for (int p = 0; p < n_pts; ++p) {
+      const int b = h_pt_start[p], e = h_pt_start[p + 1];
+      max_track = std::max(max_track, e - b);
+      if (e - tile_b > TILE) {  // point p does not fit: close the tile before it
+        if (b > tile_b) { tiles.push_back(b); tile_b = b; }
+      }
+    }
+    if (n > tile_b) tiles.push_back(n);
+    if (tiles.size() == 1) tiles.clear();
+  }
+  P.max_track = max_track;
+  if (max_track > MAX_TRACK) return HSFM_BA_ERR_UNSUPPORTED;
+  P.n_tiles = tiles.empty() ? 0 : (int)tiles.size() - 1;
+  int* tile_start;
+  ALLOC(tile_start, tiles.size() + 1);
+  if (!tiles.empty()) HSFM_CUDA(cudaMemcpyAsync(tile_start, tiles.data(), sizeof(int) * tiles.size(), cudaMemcpyHostToDevice, s));
+
+  // ---- camera-major warp chunks ----
+  std::vector<int> ch_cam, ch_b, ch_e, cam_ch_start((size_t)n_cams + 1, 0);
+  for (int c = 0; c < n_cams; ++c) {
+    cam_ch_start[c] = (int)ch_cam.size();
+    for (int b = h_cam_start[c]; b < h_cam_start[c + 1]; b += CHUNK) {
+      ch_cam.push_back(c); ch_b.push_back(b); ch_e.push_back(std::min(b + CHUNK, h_cam_start[c + 1]));
+    }
+  }
+  cam_ch_start[n_cams] = (int)ch_cam.size();
+  P.n_chunks = (int)ch_cam.size();
+  int *d_ch_cam, *d_ch_b, *d_ch_e, *d_cam_ch_start;
+  ALLOC(d_ch_cam, ch_cam.size()); ALLOC(d_ch_b, ch_cam.size()); ALLOC(d_ch_e, ch_cam.size()); ALLOC(d_cam_ch_start, (size_t)n_cams + 1);
+  if (P.n_chunks) {
+    HSFM_CUDA(cudaMemcpyAsync(d_ch_cam, ch_cam.data(), sizeof(int) * ch_cam.size(), cudaMemcpyHostToDevice, s));
+    HSFM_CUDA(cudaMemcpyAsync(d_ch_b, ch_b.data(), sizeof(int) * ch_cam.size(), cudaMemcpyHostToDevice, s));
+    HSFM_CUDA(cudaMemcpyAsync(d_ch_e, ch_e.data(), sizeof(int) * ch_cam.size(), cudaMemcpyHostToDevice, s));
+  }
+  HSFM_CUDA(cudaMemcpyAsync(d_cam_ch_start, cam_ch_start.data(), sizeof(int) * ((size_t)n_cams + 1), cudaMemcpyHostToDevice, s));
+
+  // ---- observation counts per camera over ALL ranks (cameras without observations are not
+  //      parameter blocks of the reference problem: CTracker.cpp:676-696 adds blocks per residual) ----
+  ALLOC(P.cam_nobs, (size_t)n_cams);
+  diff_kernel<<<cdiv(std::max(1, (int)n_cams), 256), 256, 0, s>>>(n_cams, cam_start, P.cam_nobs);
+  if (comm.n_ranks > 1) {
+    int rc = comm.allreduce_sum_i32(P.cam_nobs, (size_t)n_cams, s);
+    if (rc) return rc;
+  }
+
+  // ---- linearisation + solver state ----
+  double2 *r, *Jc, *Jp;
+  ALLOC(r, n); ALLOC(Jc, 6 * (size_t)n); ALLOC(Jp, 3 * (size_t)n);
+  ALLOC(P.cam_c, 6 * (size_t)n_cams); ALLOC(P.pts_c, 3 * (size_t)n_pts);
+  ALLOC(P.rows_x, n_cams); ALLOC(P.rows_c, n_cams);
+  ALLOC(P.scale_c, 6 * (size_t)n_cams); ALLOC(P.scale_p, 3 * (size_t)n_pts);
+  ALLOC(P.Hpp, 6 * (size_t)n_pts); ALLOC(P.gp, 3 * (size_t)n_pts); ALLOC(P.Hpp_inv, 6 * (size_t)n_pts); ALLOC(P.zp, 3 * (size_t)n_pts);
+  ALLOC(P.Hcc, 21 * (size_t)n_cams); ALLOC(P.gc, 6 * (size_t)n_cams); ALLOC(P.E, 21 * (size_t)n_cams);
+  ALLOC(P.chunk_part, 27 * (size_t)std::max(1, P.n_chunks));
+  ALLOC(P.Dc2, 6 * (size_t)n_cams); ALLOC(P.Minv, 36 * (size_t)n_cams);
+  ALLOC(P.rhs, 6 * (size_t)n_cams); ALLOC(P.yc, 12 * (size_t)n_cams); ALLOC(P.yp, 3 * (size_t)n_pts);
+  ALLOC(P.pcg_x, 6 * (size_t)n_cams); ALLOC(P.pcg_r, 6 * (size_t)n_cams); ALLOC(P.pcg_z, 6 * (size_t)n_cams);
+  ALLOC(P.pcg_p, 6 * (size_t)n_cams); ALLOC(P.pcg_q, 6 * (size_t)n_cams);
+  P.part_stride = std::max({P.n_tiles, cdiv(6 * n_cams, 256), cdiv(3 * n_pts, 256), 1});
+  ALLOC(P.part, (size_t)PART_SLOTS * P.part_stride);
+  ALLOC(P.scal, SCAL_SLOTS); ALLOC(P.flags, FLAG_SLOTS);
+  HSFM_CUDA(cudaMallocHost(&P.scal_host, sizeof(double) * SCAL_SLOTS));
+  HSFM_CUDA(cudaMallocHost(&P.flags_host, sizeof(int) * FLAG_SLOTS));
+  HSFM_CUDA(cudaMemsetAsync(P.scal, 0, sizeof(double) * SCAL_SLOTS, s));
+  HSFM_CUDA(cudaMemsetAsync(P.flags, 0, sizeof(int) * FLAG_SLOTS, s));
+  HSFM_CUDA(cudaMemsetAsync(P.part, 0, sizeof(double) * (size_t)PART_SLOTS * P.part_stride, s));
+  // blocks of points / cameras without observations are never written by the kernels: keep them zero
+  HSFM_CUDA(cudaMemsetAsync(P.Hpp, 0, sizeof(double) * 6 * std::max<size_t>(1, n_pts), s));
+  HSFM_CUDA(cudaMemsetAsync(P.gp, 0, sizeof(double) * 3 * std::max<size_t>(1, n_pts), s));
+  HSFM_CUDA(cudaMemsetAsync(P.yp, 0, sizeof(double) * 3 * std::max<size_t>(1, n_pts), s));
+  HSFM_CUDA(cudaMemsetAsync(P.yc, 0, sizeof(double) * 12 * std::max<size_t>(1, n_cams), s));
+  HSFM_CUDA(cudaMemcpyAsync(P.pts_c, P.pts_x, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToDevice, s));
+
+  Dev& d = P.d;
+  d.n_obs = n; d.n_cams = n_cams; d.n_pts = n_pts; d.n_tiles = P.n_tiles; d.n_chunks = P.n_chunks;
+  d.obs = obs; d.cam = cam; d.pt = pt; d.pt_start = pt_start; d.tile_start = tile_start;
+  d.obs_cs = obs_cs; d.pt_cs = pt_cs; d.chunk_cam = d_ch_cam; d.chunk_b = d_ch_b; d.chunk_e = d_ch_e; d.cam_chunk_start = d_cam_ch_start;
+  d.r = r; d.Jc = Jc; d.Jp = Jp;
+  HSFM_CUDA(cudaStreamSynchronize(s));
+  if (setup_ms) *setup_ms = now_ms() - t_setup0;
+  return 0;
+}
+
+}  // namespace hsfm

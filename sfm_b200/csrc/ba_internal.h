@@ -1,0 +1,154 @@
+// ba_internal.h — internal declarations shared by the translation units of libhsfm_ba.so.
+// Device-resident problem state, kernel launch wrappers, the LM driver.  Not installed.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/hsfm_ba.h"
+#include "ba_math.cuh"
+
+namespace hsfm {
+
+constexpr int TILE = 256;        // observations per point-major tile == threads per CTA
+constexpr int CHUNK = 256;       // observations per camera-major warp chunk
+constexpr int MAX_TRACK = TILE;  // a point's observations must fit one tile (checked at upload)
+
+#define HSFM_CUDA(call)                                         \
+  do {                                                          \
+    cudaError_t e__ = (call);                                   \
+    if (e__ != cudaSuccess) return 1000 + (int)e__;             \
+  } while (0)
+
+// Plain device pointers of one resident problem (passed to kernels by value).
+struct Dev {
+  int n_obs, n_cams, n_pts, n_tiles, n_chunks;
+  // static, point-major order (sorted by point; ties keep input order)
+  const double2* obs;    // [n_obs] observed pixel
+  const int* cam;        // [n_obs]
+  const int* pt;         // [n_obs]
+  const int* pt_start;   // [n_pts+1] CSR over point-major observations
+  const int* tile_start; // [n_tiles+1] first observation of each tile (tiles hold whole points)
+  // static, camera-major order
+  const double2* obs_cs; // [n_obs]
+  const int* pt_cs;      // [n_obs]
+  const int* chunk_cam;  // [n_chunks]
+  const int* chunk_b;    // [n_chunks]
+  const int* chunk_e;    // [n_chunks]
+  const int* cam_chunk_start;  // [n_cams+1]
+  // linearisation, point-major SoA planes of double2 = (d u, d v)
+  double2* r;            // [n_obs]
+  double2* Jc;           // [6][n_obs]
+  double2* Jp;           // [3][n_obs]
+};
+
+// Everything the solver keeps on the device for one problem.
+struct Problem {
+  int mode = 2;
+  int n_obs = 0, n_cams = 0, n_pts = 0, n_tiles = 0, n_chunks = 0;
+  int max_track = 0;
+  Dev d{};
+  // owned allocations (freed in release())
+  std::vector<void*> allocs;
+  // input order → point-major position (for the eval tap) and static copies
+  int* order_pm = nullptr;  // [n_obs] input index of the j-th point-major observation
+  double* K9 = nullptr;     // [n_cams][9]
+  double* dist = nullptr;   // [n_cams][2]
+  // parameters
+  double *cam_x = nullptr, *pts_x = nullptr;        // current x   [n_cams][6], [n_pts][3]
+  double *cam_c = nullptr, *pts_c = nullptr;        // candidate
+  double *cam_x0 = nullptr, *pts_x0 = nullptr;      // uploaded initial values (problem_reset)
+  CamRow *rows_x = nullptr, *rows_c = nullptr;      // prepared camera tables for x / candidate
+  double *scale_c = nullptr, *scale_p = nullptr;    // Jacobi scaling [6 n_cams], [3 n_pts]
+  int *cam_nobs = nullptr, *pt_nobs_mask = nullptr; // global observation count per camera (all ranks)
+  // normal-equation blocks
+  double *Hpp = nullptr, *gp = nullptr, *Hpp_inv = nullptr, *zp = nullptr;  // [n_pts][6],[3],[6],[3]
+  double *Hcc = nullptr, *gc = nullptr;             // [n_cams][21] upper-tri row-major, [n_cams][6]
+  double *chunk_part = nullptr;                     // [n_chunks][27]
+  double *Dc2 = nullptr;                            // [6 n_cams] squared LM diagonal of the camera block
+  double *Minv = nullptr;                           // [n_cams][36] block-Jacobi preconditioner / pose-only inverse
+  double *E = nullptr;                              // [n_cams][21] sum_i Jc^T Jp Hpp^-1 Jp^T Jc
+  double *rhs = nullptr, *yc = nullptr, *yp = nullptr;
+  double *pcg_x = nullptr, *pcg_r = nullptr, *pcg_z = nullptr, *pcg_p = nullptr, *pcg_q = nullptr;
+  double *S = nullptr;                              // dense reduced camera matrix (lazily allocated)
+  size_t S_capacity = 0;
+  // scalar plumbing
+  double *part = nullptr;    // [PART_SLOTS][part_stride] per-block partial sums
+  int part_stride = 0;
+  double *scal = nullptr;    // [32] reduced scalars (device)
+  double *scal_host = nullptr;  // pinned mirror
+  int *flags = nullptr;      // [8] device flags: 0 = not-PD / invalid, 1 = pcg done, 2 = pcg iterations
+  int *flags_host = nullptr; // pinned mirror
+  int64_t launches = 0;
+  void release();
+};
+
+enum PartSlot { P_COST = 0, P_MCC, P_DN_P, P_XN_P, P_DN_C, P_XN_C, P_GMAX_C, P_GMAX_P, PART_SLOTS };
+// slots 0..4 are per-rank partial sums (all-reduced with SUM under a communicator), S_GMAX_P with MAX;
+// the camera-side slots are computed from replicated data and are identical on every rank.
+enum ScalSlot { S_COST = 0, S_MCC, S_DN_P, S_XN_P, S_CAND_COST, S_GMAX_P, S_DN_C, S_XN_C, S_GMAX_C, S_PCG_RHO0, S_PCG_RHO, SCAL_SLOTS = 32 };
+enum FlagSlot { F_INVALID = 0, F_PCG_DONE = 1, F_PCG_ITERS = 2, F_CHOL_FAIL = 3, FLAG_SLOTS = 8 };
+
+// ---- communicator (NCCL, loaded at run time; ba_comm.cu) ----
+struct Comm {
+  void* handle = nullptr;  // ncclComm_t
+  int rank = 0, n_ranks = 1;
+  int allreduce_sum(double* buf, size_t count, cudaStream_t s);
+  int allreduce_max(double* buf, size_t count, cudaStream_t s);
+  int allreduce_sum_i32(int* buf, size_t count, cudaStream_t s);
+  void destroy();
+};
+int comm_unique_id(void* out128);
+int comm_init(Comm& c, const void* id128, int rank, int n_ranks);
+
+// ---- index build (ba_index.cu) ----
+int build_problem(Problem& P, int mode, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
+                  int32_t n_cams, const double* K9, const double* dist, const double* cam_rt, int64_t n_pts, const double* pts,
+                  Comm& comm, cudaStream_t s, double* setup_ms, double* h2d_ms);
+
+// ---- kernel launchers (ba_kernels.cu); every launcher bumps P.launches ----
+void launch_cam_prep(Problem& P, const double* cam, const double* scale_c /*null = 1*/, CamRow* rows, cudaStream_t s);
+// residual + Jacobian (+ point blocks Hpp,gp when form) ; scale_p null = 1
+void launch_rj(Problem& P, const CamRow* rows, const double* pts, const double* scale_p, bool write_j, bool form, cudaStream_t s);
+void launch_cost(Problem& P, const CamRow* rows, const double* pts, int part_slot, cudaStream_t s);
+// camera-major passes: mode 0 → Hcc,gc ; mode 1 → E (needs Hpp_inv)
+void launch_cam_major(Problem& P, const CamRow* rows, const double* pts, const double* scale_p, int what, cudaStream_t s);
+void launch_jacobi_scale(Problem& P, bool enabled, cudaStream_t s);  // from Hcc / Hpp diagonals (unscaled pass)
+void launch_point_invert(Problem& P, double radius, double min_diag, double max_diag, cudaStream_t s);
+void launch_cam_diag(Problem& P, double radius, double min_diag, double max_diag, cudaStream_t s);  // Dc2
+void launch_precond_invert(Problem& P, bool with_E, cudaStream_t s);  // Minv = (Hcc + Dc2 - E)^-1
+void launch_schur_rhs(Problem& P, bool preload_gc, cudaStream_t s);  // rhs = [gc] - sum Jc^T Jp zp
+void launch_schur_matvec(Problem& P, const double* pvec, double* q, cudaStream_t s);  // q += (Jc^T (I - Jp Hpp^-1 Jp^T) Jc) p ; honours F_PCG_DONE
+void launch_backsub(Problem& P, cudaStream_t s);        // yp, candidate points, model-cost-change and norm partials
+void launch_cam_step(Problem& P, cudaStream_t s);       // candidate cameras, norm partials
+void launch_block_solve_cams(Problem& P, cudaStream_t s);  // pose-only: yc = Minv gc
+void launch_grad_norm(Problem& P, cudaStream_t s);      // max |g/scale| partials
+void launch_finalize_scalars(Problem& P, cudaStream_t s);  // partials -> scal[]
+void launch_pcg_init(Problem& P, cudaStream_t s);
+void launch_pcg_step(Problem& P, double tol, int max_it, cudaStream_t s);
+void launch_dense_init(Problem& P, bool with_diag, cudaStream_t s);  // S = [blockdiag(Hcc + Dc2)]
+void launch_dense_schur(Problem& P, cudaStream_t s);    // S -= sum_p W Hpp^-1 W^T (lower block triangle)
+void launch_scatter_eval(Problem& P, double* r_out, double* jac_out, cudaStream_t s);  // back to input order, Ceres layout
+void launch_export_blocks(Problem& P, double* Hcc36, double* Hpp9, cudaStream_t s);  // parity tap (adds LM diagonal)
+void launch_mirror_lower(Problem& P, cudaStream_t s);   // S upper <- lower (parity tap)
+
+// ---- dense Cholesky (ba_chol.cu) ----
+// In-place lower Cholesky of row-major n×n S (lower triangle read/written); *fail_flag set to
+// non-zero on a non-positive pivot.  Then solve S y = b in place in b.
+void launch_cholesky(double* S, int n, int* fail_flag, cudaStream_t s, int64_t* launches);
+void launch_chol_solve(const double* L, int n, double* b, cudaStream_t s, int64_t* launches);
+
+// ---- LM driver (ba_solver.cu) ----
+struct Ctx {
+  int device = 0;
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;
+  Comm comm;
+  Problem prob;
+  bool has_problem = false;
+};
+int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary);
+
+}  // namespace hsfm

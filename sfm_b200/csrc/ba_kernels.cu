@@ -1,0 +1,971 @@
+// ba_kernels.cu — sm_100a kernels of the bundle-adjustment hot path.
+//
+// Data layout: observations are kept twice, both static after upload:
+//   * point-major (sorted by point), cut into TILES of <= 256 observations that contain whole
+//     points only.  One CTA = one tile, one thread = one observation.  All point-keyed sums
+//     (Hpp, g_p, W^T y, back-substitution) are warp-shuffle segmented scans inside the tile,
+//     stitched across warps through shared memory — deterministic, no atomics.
+//   * camera-major (sorted by camera), cut into warp CHUNKS of <= 256 observations of ONE
+//     camera.  Camera-keyed sums that are needed once per linearisation (Hcc, g_c, the
+//     block-Jacobi diagonal) are recomputed here from 20 B/observation + a point gather
+//     instead of being scattered with 27 atomics per observation.
+// The linearisation (r, Jc, Jp) is materialised point-major as SoA planes of double2 = (du,dv)
+// so every load/store of the streaming passes is a fully coalesced 16-byte access.
+#include <cooperative_groups.h>
+
+#include "ba_internal.h"
+
+namespace hsfm {
+
+namespace {
+
+constexpr unsigned FULL = 0xffffffffu;
+
+__device__ __forceinline__ CamRow load_row(const CamRow* rows, int c) {
+  CamRow C;
+  const double2* src = reinterpret_cast<const double2*>(rows + c);
+  double2* dst = reinterpret_cast<double2*>(&C);
+#pragma unroll
+  for (int q = 0; q < 12; ++q) dst[q] = __ldg(src + q);
+  return C;
+}
+
+__device__ __forceinline__ constexpr int tri6(int a, int b) { return a * 6 - (a * (a - 1)) / 2 + (b - a); }  // a <= b
+
+// Sum over the CTA; result valid on thread 0.  sm must hold 8 doubles... (256 threads).
+__device__ __forceinline__ double block_sum_256(double v, double* sm) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(FULL, v, d);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) sm[warp] = v;
+  __syncthreads();
+  double t = 0.0;
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += sm[w];
+  }
+  __syncthreads();
+  return t;
+}
+
+// Per-thread view of a point-major tile.
+struct TileThread {
+  int i;      // observation index (point-major), valid iff i < tile_e
+  int tile_b, tile_e;
+  int p;      // point id
+  int seg_b, seg_e;  // observation range of the point
+  bool valid;
+};
+
+__device__ __forceinline__ TileThread tile_thread(const Dev& d) {
+  TileThread t;
+  t.tile_b = __ldg(d.tile_start + blockIdx.x);
+  t.tile_e = __ldg(d.tile_start + blockIdx.x + 1);
+  t.i = t.tile_b + (int)threadIdx.x;
+  t.valid = t.i < t.tile_e;
+  t.p = t.valid ? __ldg(d.pt + t.i) : 0;
+  t.seg_b = t.valid ? __ldg(d.pt_start + t.p) : 0;
+  t.seg_e = t.valid ? __ldg(d.pt_start + t.p + 1) : 0;
+  return t;
+}
+
+// Replace v[] (this observation's contribution; zeros on invalid threads) by the sum over all
+// observations of the thread's point.  In-warp inclusive segmented scan by shuffles, warp-local
+// total fetched from the segment's last lane, cross-warp pieces stitched through shared memory
+// in a fixed order (deterministic).  sm: 2*8*K doubles.  Must be called by all 256 threads.
+template <int K>
+__device__ __forceinline__ void tile_segment_total(double (&v)[K], const TileThread& t, double* sm) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int warp_base = t.tile_b + warp * 32;
+  const int first_lane = t.valid ? max(t.seg_b - warp_base, 0) : lane;
+  const int last_lane = t.valid ? min(t.seg_e - 1 - warp_base, 31) : lane;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const double up = __shfl_up_sync(FULL, v[k], d);
+      if (lane - d >= first_lane) v[k] += up;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < K; ++k) v[k] = __shfl_sync(FULL, v[k], last_lane);
+  const bool before = t.valid && (t.seg_b < warp_base);
+  const bool after = t.valid && (t.seg_e > warp_base + 32);
+  const bool crosses = before || after;
+  if (__syncthreads_or(crosses)) {
+    double* smF = sm;          // [8][K] piece of a segment that started in an earlier warp
+    double* smL = sm + 8 * K;  // [8][K] piece of a segment that starts here and continues
+    if (lane == 0 && before) {
+#pragma unroll
+      for (int k = 0; k < K; ++k) smF[warp * K + k] = v[k];
+    }
+    if (lane == 31 && after && !before) {
+#pragma unroll
+      for (int k = 0; k < K; ++k) smL[warp * K + k] = v[k];
+    }
+    __syncthreads();
+    if (crosses) {
+      const int w_head = (t.seg_b - t.tile_b) >> 5;
+      const int w_last = (t.seg_e - 1 - t.tile_b) >> 5;
+#pragma unroll
+      for (int k = 0; k < K; ++k) {
+        double s = smL[w_head * K + k];
+        for (int w = w_head + 1; w <= w_last; ++w) s += smF[w * K + k];
+        v[k] = s;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+__global__ void cam_prep_kernel(int n_cams, const double* __restrict__ cam, const double* __restrict__ K9,
+                                const double* __restrict__ dist, const double* __restrict__ scale_c, CamRow* __restrict__ rows) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n_cams) return;
+  CamRow C;
+  cam_prepare(cam + 6 * c, K9 + 9 * c, dist ? dist + 2 * c : nullptr, scale_c ? scale_c + 6 * c : nullptr, C);
+  rows[c] = C;
+}
+
+// Kernel RJ: residual + Jacobian per observation (a1), fused with the point-keyed part of the
+// normal equations (a7: Hpp = sum Jp^T Jp, g_p = sum Jp^T r) and the cost partial (a6).
+// Algorithmic bytes / observation: 24 in (obs 16, cam 4, pt 4) + 160 out (r 16, Jc 96, Jp 48).
+template <bool WRITE_J, bool FORM>
+__global__ void __launch_bounds__(TILE) rj_kernel(Dev d, const CamRow* __restrict__ rows, const double* __restrict__ pts,
+                                                   const double* __restrict__ scale_p, double* __restrict__ Hpp,
+                                                   double* __restrict__ gp, double* __restrict__ cost_part) {
+  __shared__ double sm[2 * 8 * 9];
+  const TileThread t = tile_thread(d);
+  double r0 = 0.0, r1 = 0.0;
+  double jc[12], jp[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) jp[k] = 0.0;
+  if (t.valid) {
+    const double2 o = __ldg(d.obs + t.i);
+    const int c = __ldg(d.cam + t.i);
+    const CamRow C = load_row(rows, c);
+    const double X0 = __ldg(pts + 3 * (size_t)t.p), X1 = __ldg(pts + 3 * (size_t)t.p + 1), X2 = __ldg(pts + 3 * (size_t)t.p + 2);
+    double sp[3] = {1.0, 1.0, 1.0};
+    if (scale_p) {
+      sp[0] = __ldg(scale_p + 3 * (size_t)t.p); sp[1] = __ldg(scale_p + 3 * (size_t)t.p + 1); sp[2] = __ldg(scale_p + 3 * (size_t)t.p + 2);
+    }
+    reproject_rj(C, X0, X1, X2, o.x, o.y, sp, r0, r1, jc, jp);
+    if (WRITE_J) {
+      const size_t n = (size_t)d.n_obs;
+      d.r[t.i] = make_double2(r0, r1);
+#pragma unroll
+      for (int k = 0; k < 6; ++k) d.Jc[k * n + t.i] = make_double2(jc[k], jc[6 + k]);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) d.Jp[k * n + t.i] = make_double2(jp[k], jp[3 + k]);
+    }
+  }
+  const double cs = block_sum_256(r0 * r0 + r1 * r1, sm);
+  if (threadIdx.x == 0) cost_part[blockIdx.x] = cs;
+  if (FORM) {
+    double v[9];
+    v[0] = jp[0] * jp[0] + jp[3] * jp[3];
+    v[1] = jp[0] * jp[1] + jp[3] * jp[4];
+    v[2] = jp[0] * jp[2] + jp[3] * jp[5];
+    v[3] = jp[1] * jp[1] + jp[4] * jp[4];
+    v[4] = jp[1] * jp[2] + jp[4] * jp[5];
+    v[5] = jp[2] * jp[2] + jp[5] * jp[5];
+    v[6] = jp[0] * r0 + jp[3] * r1;
+    v[7] = jp[1] * r0 + jp[4] * r1;
+    v[8] = jp[2] * r0 + jp[5] * r1;
+    tile_segment_total<9>(v, t, sm);
+    if (t.valid && t.i == t.seg_b) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) Hpp[6 * (size_t)t.p + k] = v[k];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) gp[3 * (size_t)t.p + k] = v[6 + k];
+    }
+  }
+}
+
+// Candidate cost: residual only (a9), 24 B/observation.
+__global__ void __launch_bounds__(TILE) cost_kernel(Dev d, const CamRow* __restrict__ rows, const double* __restrict__ pts,
+                                                     double* __restrict__ cost_part) {
+  __shared__ double sm[8];
+  const int tile_b = __ldg(d.tile_start + blockIdx.x), tile_e = __ldg(d.tile_start + blockIdx.x + 1);
+  const int i = tile_b + (int)threadIdx.x;
+  double e = 0.0;
+  if (i < tile_e) {
+    const double2 o = __ldg(d.obs + i);
+    const int c = __ldg(d.cam + i);
+    const int p = __ldg(d.pt + i);
+    const CamRow C = load_row(rows, c);
+    double r0, r1;
+    reproject_r(C, __ldg(pts + 3 * (size_t)p), __ldg(pts + 3 * (size_t)p + 1), __ldg(pts + 3 * (size_t)p + 2), o.x, o.y, r0, r1);
+    e = r0 * r0 + r1 * r1;
+  }
+  const double cs = block_sum_256(e, sm);
+  if (threadIdx.x == 0) cost_part[blockIdx.x] = cs;
+}
+
+// Camera-major pass: one warp per chunk of <= 256 observations of one camera; recomputes the
+// (scaled) Jacobian from 20 B/observation + a point gather and reduces camera-keyed sums.
+//   WHAT == 0: 21 upper-triangle entries of Jc^T Jc and the 6 of Jc^T r          (a7: Hcc, g_c)
+//   WHAT == 1: 21 entries of Jc^T (Jp Hpp^-1 Jp^T) Jc  (diagonal blocks of W Hpp^-1 W^T)
+template <int WHAT>
+__global__ void __launch_bounds__(256) cam_major_kernel(Dev d, const CamRow* __restrict__ rows, const double* __restrict__ pts,
+                                                        const double* __restrict__ scale_p, const double* __restrict__ Hpp_inv,
+                                                        double* __restrict__ chunk_part) {
+  constexpr int NV = (WHAT == 0) ? 27 : 21;
+  const int lane = threadIdx.x & 31;
+  const int wc = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (wc >= d.n_chunks) return;
+  const int c = __ldg(d.chunk_cam + wc);
+  const int b = __ldg(d.chunk_b + wc), e = __ldg(d.chunk_e + wc);
+  const CamRow C = load_row(rows, c);
+  double acc[NV];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) acc[k] = 0.0;
+  for (int j = b + lane; j < e; j += 32) {
+    const double2 o = __ldg(d.obs_cs + j);
+    const int p = __ldg(d.pt_cs + j);
+    const double X0 = __ldg(pts + 3 * (size_t)p), X1 = __ldg(pts + 3 * (size_t)p + 1), X2 = __ldg(pts + 3 * (size_t)p + 2);
+    double sp[3] = {1.0, 1.0, 1.0};
+    if (scale_p) {
+      sp[0] = __ldg(scale_p + 3 * (size_t)p); sp[1] = __ldg(scale_p + 3 * (size_t)p + 1); sp[2] = __ldg(scale_p + 3 * (size_t)p + 2);
+    }
+    double r0, r1, jc[12], jp[6];
+    reproject_rj(C, X0, X1, X2, o.x, o.y, sp, r0, r1, jc, jp);
+    if (WHAT == 0) {
+#pragma unroll
+      for (int a = 0; a < 6; ++a) {
+#pragma unroll
+        for (int bb = a; bb < 6; ++bb) acc[tri6(a, bb)] += jc[a] * jc[bb] + jc[6 + a] * jc[6 + bb];
+        acc[21 + a] += jc[a] * r0 + jc[6 + a] * r1;
+      }
+    } else {
+      double Hi[6];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) Hi[k] = __ldg(Hpp_inv + 6 * (size_t)p + k);
+      // M = Jp Hi Jp^T (2x2 symmetric)
+      double a0, a1, a2, b0, b1, b2;
+      sym3_mul(Hi, jp[0], jp[1], jp[2], a0, a1, a2);
+      sym3_mul(Hi, jp[3], jp[4], jp[5], b0, b1, b2);
+      const double m00 = jp[0] * a0 + jp[1] * a1 + jp[2] * a2;
+      const double m01 = jp[0] * b0 + jp[1] * b1 + jp[2] * b2;
+      const double m11 = jp[3] * b0 + jp[4] * b1 + jp[5] * b2;
+#pragma unroll
+      for (int a = 0; a < 6; ++a) {
+        const double ta = m00 * jc[a] + m01 * jc[6 + a];  // (M Jc)[0][a]
+        const double tb = m01 * jc[a] + m11 * jc[6 + a];  // (M Jc)[1][a]
+#pragma unroll
+        for (int bb = a; bb < 6; ++bb) acc[tri6(a, bb)] += jc[bb] * ta + jc[6 + bb] * tb;
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    double v = acc[k];
+#pragma unroll
+    for (int dd = 16; dd > 0; dd >>= 1) v += __shfl_xor_sync(FULL, v, dd);
+    acc[k] = v;
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; ++k) chunk_part[(size_t)wc * 27 + k] = acc[k];
+  }
+}
+
+// Fold the chunk partials of each camera in chunk order (deterministic).
+__global__ void cam_reduce_kernel(int n_cams, int nv, const int* __restrict__ cam_chunk_start, const double* __restrict__ chunk_part,
+                                  double* __restrict__ out21, double* __restrict__ out6) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n_cams * nv) return;
+  const int c = idx / nv, k = idx % nv;
+  double s = 0.0;
+  for (int w = cam_chunk_start[c]; w < cam_chunk_start[c + 1]; ++w) s += chunk_part[(size_t)w * 27 + k];
+  if (k < 21) out21[(size_t)c * 21 + k] = s;
+  else out6[(size_t)c * 6 + (k - 21)] = s;
+}
+
+__global__ void jacobi_scale_kernel(int n_cams, int n_pts, const double* __restrict__ Hcc, const double* __restrict__ Hpp,
+                                    double* __restrict__ scale_c, double* __restrict__ scale_p, int enabled) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nc6 = 6 * n_cams;
+  if (idx < nc6) {
+    const int c = idx / 6, a = idx % 6;
+    scale_c[idx] = enabled ? 1.0 / (1.0 + sqrt(Hcc[(size_t)c * 21 + tri6(a, a)])) : 1.0;
+  } else if (idx < nc6 + 3 * n_pts) {
+    const int j = idx - nc6;
+    const int p = j / 3, a = j % 3;
+    const int diag = (a == 0) ? 0 : (a == 1 ? 3 : 5);
+    scale_p[j] = enabled ? 1.0 / (1.0 + sqrt(Hpp[(size_t)p * 6 + diag])) : 1.0;
+  }
+}
+
+// Per attempt: Hpp_inv = (Hpp + D_p^2)^-1 with D = sqrt(clamp(diag)/radius) (a7), z_p = Hpp_inv g_p.
+__global__ void point_invert_kernel(int n_pts, const double* __restrict__ Hpp, const double* __restrict__ gp, double radius,
+                                    double min_diag, double max_diag, double* __restrict__ Hpp_inv, double* __restrict__ zp,
+                                    int* __restrict__ flags) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_pts) return;
+  double H[6], Hi[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) H[k] = Hpp[6 * (size_t)p + k];
+  const int dg[3] = {0, 3, 5};
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    const double D = sqrt(fmin(fmax(H[dg[a]], min_diag), max_diag) / radius);
+    H[dg[a]] += D * D;
+  }
+  if (!inv3_spd(H, Hi)) {
+    atomicOr(flags + F_INVALID, 1);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) Hi[k] = 0.0;
+  }
+#pragma unroll
+  for (int k = 0; k < 6; ++k) Hpp_inv[6 * (size_t)p + k] = Hi[k];
+  double z0, z1, z2;
+  sym3_mul(Hi, gp[3 * (size_t)p], gp[3 * (size_t)p + 1], gp[3 * (size_t)p + 2], z0, z1, z2);
+  zp[3 * (size_t)p] = z0; zp[3 * (size_t)p + 1] = z1; zp[3 * (size_t)p + 2] = z2;
+}
+
+__global__ void cam_diag_kernel(int n_cams, const double* __restrict__ Hcc, double radius, double min_diag, double max_diag,
+                                double* __restrict__ Dc2) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= 6 * n_cams) return;
+  const int c = idx / 6, a = idx % 6;
+  const double D = sqrt(fmin(fmax(Hcc[(size_t)c * 21 + tri6(a, a)], min_diag), max_diag) / radius);
+  Dc2[idx] = D * D;
+}
+
+// Minv[c] = (Hcc + Dc2 - E)^-1 : block-Jacobi preconditioner (diagonal blocks of S), or with
+// with_E == 0 the pose-only normal matrix inverse.
+__global__ void precond_invert_kernel(int n_cams, const double* __restrict__ Hcc, const double* __restrict__ Dc2,
+                                      const double* __restrict__ E, int with_E, double* __restrict__ Minv, int* __restrict__ flags) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n_cams) return;
+  double A[36];
+#pragma unroll
+  for (int a = 0; a < 6; ++a)
+#pragma unroll
+    for (int b = a; b < 6; ++b) {
+      double v = Hcc[(size_t)c * 21 + tri6(a, b)];
+      if (with_E) v -= E[(size_t)c * 21 + tri6(a, b)];
+      if (a == b) v += Dc2[6 * c + a];
+      A[a * 6 + b] = v;
+      A[b * 6 + a] = v;
+    }
+  if (!inv6_spd(A)) {
+    atomicOr(flags + F_INVALID, 2);
+#pragma unroll
+    for (int k = 0; k < 36; ++k) A[k] = 0.0;
+  }
+#pragma unroll
+  for (int k = 0; k < 36; ++k) Minv[(size_t)c * 36 + k] = A[k];
+}
+
+// Streaming pass over the stored linearisation, point-major tiles.
+//   MODE 0 (RHS)    : rhs[c] += Jc^T (-Jp z_p)                      (a7: g_c - W Hpp^-1 g_p; rhs preloaded with g_c)
+//   MODE 1 (MATVEC) : q[c]   += Jc^T (I - Jp Hpp^-1 Jp^T) Jc p      (implicit S p without the D_c^2 p term)
+//   MODE 2 (BACKSUB): y_p = z_p - Hpp^-1 W^T y_c ; candidate point ; model cost change ; norms   (a8, a9)
+// Algorithmic bytes / observation: Jc 96 + Jp 48 + cam 4 + pt 4 (+ r 16 in MODE 2).
+template <int MODE>
+__global__ void __launch_bounds__(TILE) schur_pass_kernel(Dev d, const double* __restrict__ Hpp_inv, const double* __restrict__ zp,
+                                                          const double* __restrict__ vec_in /* p or y_c */, double* __restrict__ vec_out,
+                                                          const double* __restrict__ pts_x, const double* __restrict__ scale_p,
+                                                          double* __restrict__ yp, double* __restrict__ pts_c,
+                                                          double* __restrict__ part, int part_stride, const int* __restrict__ flags,
+                                                          int cams_free, int pts_free) {
+  __shared__ double sm[2 * 8 * 3 + 8];
+  if (MODE == 1) {
+    if (flags[F_PCG_DONE]) return;
+  }
+  const TileThread t = tile_thread(d);
+  const size_t n = (size_t)d.n_obs;
+  double jc[12], jp[6];
+  int c = 0;
+  if (t.valid) {
+    c = __ldg(d.cam + t.i);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      const double2 v = d.Jc[k * n + t.i];
+      jc[k] = v.x; jc[6 + k] = v.y;
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const double2 v = d.Jp[k * n + t.i];
+      jp[k] = v.x; jp[3 + k] = v.y;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < 12; ++k) jc[k] = 0.0;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) jp[k] = 0.0;
+  }
+  if (MODE == 0) {
+    if (t.valid) {
+      const double z0 = __ldg(zp + 3 * (size_t)t.p), z1 = __ldg(zp + 3 * (size_t)t.p + 1), z2 = __ldg(zp + 3 * (size_t)t.p + 2);
+      const double y0 = -(jp[0] * z0 + jp[1] * z1 + jp[2] * z2);
+      const double y1 = -(jp[3] * z0 + jp[4] * z1 + jp[5] * z2);
+#pragma unroll
+      for (int k = 0; k < 6; ++k) atomicAdd(vec_out + 6 * (size_t)c + k, jc[k] * y0 + jc[6 + k] * y1);
+    }
+    return;
+  }
+  // u = Jc * vec_in[c]
+  double u0 = 0.0, u1 = 0.0;
+  if (t.valid && (MODE == 1 || cams_free)) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      const double pk = __ldg(vec_in + 6 * (size_t)c + k);
+      u0 += jc[k] * pk;
+      u1 += jc[6 + k] * pk;
+    }
+  }
+  double v[3];
+  v[0] = jp[0] * u0 + jp[3] * u1;
+  v[1] = jp[1] * u0 + jp[4] * u1;
+  v[2] = jp[2] * u0 + jp[5] * u1;
+  tile_segment_total<3>(v, t, sm);
+  double Hi[6];
+  if (t.valid) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) Hi[k] = __ldg(Hpp_inv + 6 * (size_t)t.p + k);
+  } else {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) Hi[k] = 0.0;
+  }
+  double w0, w1, w2;
+  sym3_mul(Hi, v[0], v[1], v[2], w0, w1, w2);  // Hpp^-1 W^T (.)
+  if (MODE == 1) {
+    if (t.valid) {
+      const double y0 = u0 - (jp[0] * w0 + jp[1] * w1 + jp[2] * w2);
+      const double y1 = u1 - (jp[3] * w0 + jp[4] * w1 + jp[5] * w2);
+#pragma unroll
+      for (int k = 0; k < 6; ++k) atomicAdd(vec_out + 6 * (size_t)c + k, jc[k] * y0 + jc[6 + k] * y1);
+    }
+    return;
+  }
+  // MODE 2
+  double mcc = 0.0, dn = 0.0, xn = 0.0;
+  if (t.valid) {
+    double y0 = 0.0, y1 = 0.0, y2 = 0.0;  // y_p
+    if (pts_free) {
+      y0 = __ldg(zp + 3 * (size_t)t.p) - w0;
+      y1 = __ldg(zp + 3 * (size_t)t.p + 1) - w1;
+      y2 = __ldg(zp + 3 * (size_t)t.p + 2) - w2;
+    }
+    // step = -y ; m = J step
+    const double m0 = -(u0 + jp[0] * y0 + jp[1] * y1 + jp[2] * y2);
+    const double m1 = -(u1 + jp[3] * y0 + jp[4] * y1 + jp[5] * y2);
+    const double2 r = d.r[t.i];
+    mcc = -(m0 * (r.x + m0 / 2.0) + m1 * (r.y + m1 / 2.0));
+    if (t.i == t.seg_b) {
+      const size_t q = 3 * (size_t)t.p;
+      if (pts_free) {
+        yp[q] = y0; yp[q + 1] = y1; yp[q + 2] = y2;
+        const double x0 = pts_x[q], x1 = pts_x[q + 1], x2 = pts_x[q + 2];
+        const double c0 = x0 + (-y0) * scale_p[q], c1 = x1 + (-y1) * scale_p[q + 1], c2 = x2 + (-y2) * scale_p[q + 2];
+        pts_c[q] = c0; pts_c[q + 1] = c1; pts_c[q + 2] = c2;
+        const double e0 = x0 - c0, e1 = x1 - c1, e2 = x2 - c2;
+        dn = e0 * e0 + e1 * e1 + e2 * e2;
+        xn = x0 * x0 + x1 * x1 + x2 * x2;
+      }
+    }
+  }
+  double* smr = sm + 48;
+  const double s0 = block_sum_256(mcc, smr);
+  const double s1 = block_sum_256(dn, smr);
+  const double s2 = block_sum_256(xn, smr);
+  if (threadIdx.x == 0) {
+    part[P_MCC * (size_t)part_stride + blockIdx.x] = s0;
+    part[P_DN_P * (size_t)part_stride + blockIdx.x] = s1;
+    part[P_XN_P * (size_t)part_stride + blockIdx.x] = s2;
+  }
+}
+
+// Candidate cameras: cand = x + (-y_c) * scale ; |delta|^2, |x|^2 partials over cameras that have observations.
+__global__ void __launch_bounds__(256) cam_step_kernel(int n6, const double* __restrict__ x, const double* __restrict__ yc,
+                                                       const double* __restrict__ scale_c, const int* __restrict__ cam_nobs,
+                                                       double* __restrict__ cand, double* __restrict__ part, int part_stride,
+                                                       int cams_free, int* __restrict__ flags) {
+  __shared__ double sm[8];
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  double dn = 0.0, xn = 0.0;
+  if (k < n6) {
+    const double xv = x[k];
+    double cv = xv;
+    if (cams_free && cam_nobs[k / 6] > 0) {
+      const double y = yc[k];
+      if (!isfinite(y)) atomicOr(flags + F_INVALID, 4);
+      cv = xv + (-y) * scale_c[k];
+      const double e = xv - cv;
+      dn = e * e;
+      xn = xv * xv;
+    }
+    cand[k] = cv;
+  }
+  const double s0 = block_sum_256(dn, sm);
+  const double s1 = block_sum_256(xn, sm);
+  if (threadIdx.x == 0) {
+    part[P_DN_C * (size_t)part_stride + blockIdx.x] = s0;
+    part[P_XN_C * (size_t)part_stride + blockIdx.x] = s1;
+  }
+}
+
+// |x|^2 of the point block over points that have observations (used at linearisation).
+__global__ void __launch_bounds__(256) block_solve_cams_kernel(int n_cams, const double* __restrict__ Minv,
+                                                               const double* __restrict__ gc, double* __restrict__ yc) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= 6 * n_cams) return;
+  const int c = k / 6, a = k % 6;
+  double s = 0.0;
+#pragma unroll
+  for (int b = 0; b < 6; ++b) s += Minv[(size_t)c * 36 + a * 6 + b] * gc[6 * c + b];
+  yc[k] = s;
+}
+
+// max_k |g_k / scale_k| partials (gradient of the unscaled problem, a6/a9).
+__global__ void __launch_bounds__(256) grad_norm_kernel(int n, const double* __restrict__ g, const double* __restrict__ scale,
+                                                        double* __restrict__ part_out) {
+  __shared__ double sm[8];
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  double v = 0.0;
+  if (k < n) v = fabs(g[k] / scale[k]);
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v = fmax(v, __shfl_down_sync(FULL, v, d));
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double m = 0.0;
+    for (int w = 0; w < 8; ++w) m = fmax(m, sm[w]);
+    part_out[blockIdx.x] = m;
+  }
+}
+
+struct RedTasks {
+  const double* in[8];
+  double* out[8];
+  int n[8];
+  int op[8];  // 0 sum, 1 max, 2 sum then *0.5
+};
+__global__ void __launch_bounds__(1024) reduce_tasks_kernel(RedTasks T) {
+  __shared__ double sm[32];
+  const int task = blockIdx.x;
+  const double* in = T.in[task];
+  const int n = T.n[task], op = T.op[task];
+  double v = 0.0;
+  if (op == 1) {
+    for (int k = threadIdx.x; k < n; k += 1024) v = fmax(v, in[k]);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v = fmax(v, __shfl_down_sync(FULL, v, d));
+  } else {
+    for (int k = threadIdx.x; k < n; k += 1024) v += in[k];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(FULL, v, d);
+  }
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+    for (int w = 0; w < 32; ++w) s = (op == 1) ? fmax(s, sm[w]) : s + sm[w];
+    if (op == 2) s *= 0.5;
+    *T.out[task] = s;
+  }
+}
+
+// ---- block-Jacobi PCG on the reduced camera system, vectors of 6 n_cams, one CTA -------------
+__device__ __forceinline__ double block_sum_1024(double v, double* sm) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(FULL, v, d);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double s = 0.0;
+  if (threadIdx.x < 32) {
+    s = sm[threadIdx.x];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(FULL, s, d);
+  }
+  if (threadIdx.x == 0) sm[32] = s;
+  __syncthreads();
+  s = sm[32];
+  __syncthreads();
+  return s;
+}
+
+__global__ void __launch_bounds__(1024) pcg_init_kernel(int n, const double* __restrict__ rhs, const double* __restrict__ Minv,
+                                                        double* x, double* r, double* z, double* p, double* q, double* scal, int* flags) {
+  __shared__ double sm[33];
+  double loc = 0.0;
+  for (int k = threadIdx.x; k < n; k += 1024) {
+    const int c = k / 6, a = k % 6;
+    double s = 0.0;
+#pragma unroll
+    for (int b = 0; b < 6; ++b) s += Minv[(size_t)c * 36 + a * 6 + b] * rhs[6 * c + b];
+    x[k] = 0.0; r[k] = rhs[k]; z[k] = s; p[k] = s; q[k] = 0.0;
+    loc += rhs[k] * s;
+  }
+  const double rho = block_sum_1024(loc, sm);
+  if (threadIdx.x == 0) {
+    scal[S_PCG_RHO0] = rho;
+    scal[S_PCG_RHO] = rho;
+    flags[F_PCG_ITERS] = 0;
+    flags[F_PCG_DONE] = (rho > 0.0 && isfinite(rho)) ? 0 : 1;
+  }
+}
+
+__global__ void __launch_bounds__(1024) pcg_step_kernel(int n, const double* __restrict__ Minv, const double* __restrict__ Dc2,
+                                                        double* x, double* r, double* z, double* p, double* q, double* scal, int* flags,
+                                                        double tol2, int max_it) {
+  __shared__ double sm[33];
+  if (flags[F_PCG_DONE]) return;
+  const double rho = scal[S_PCG_RHO], rho0 = scal[S_PCG_RHO0];
+  double loc = 0.0;
+  for (int k = threadIdx.x; k < n; k += 1024) {
+    const double pk = p[k];
+    const double qk = q[k] + Dc2[k] * pk;
+    q[k] = qk;
+    loc += pk * qk;
+  }
+  const double pq = block_sum_1024(loc, sm);
+  if (!(pq > 0.0) || !isfinite(pq)) {
+    if (threadIdx.x == 0) flags[F_PCG_DONE] = 2;
+    return;
+  }
+  const double alpha = rho / pq;
+  for (int k = threadIdx.x; k < n; k += 1024) {
+    x[k] += alpha * p[k];
+    r[k] -= alpha * q[k];
+  }
+  __syncthreads();
+  loc = 0.0;
+  for (int k = threadIdx.x; k < n; k += 1024) {
+    const int c = k / 6, a = k % 6;
+    double s = 0.0;
+#pragma unroll
+    for (int b = 0; b < 6; ++b) s += Minv[(size_t)c * 36 + a * 6 + b] * r[6 * c + b];
+    z[k] = s;
+    loc += r[k] * s;
+  }
+  const double rho_new = block_sum_1024(loc, sm);
+  const int it = flags[F_PCG_ITERS] + 1;
+  __syncthreads();
+  const bool done = (rho_new <= tol2 * rho0) || (it >= max_it) || !isfinite(rho_new);
+  const double beta = rho_new / rho;
+  for (int k = threadIdx.x; k < n; k += 1024) {
+    p[k] = z[k] + beta * p[k];
+    q[k] = 0.0;
+  }
+  if (threadIdx.x == 0) {
+    flags[F_PCG_ITERS] = it;
+    scal[S_PCG_RHO] = rho_new;
+    if (done) flags[F_PCG_DONE] = 1;
+  }
+}
+
+// ---- explicit dense S (DENSE_SCHUR, a7/a8) ---------------------------------------------------
+__global__ void dense_init_kernel(int n_cams, const double* __restrict__ Hcc, const double* __restrict__ Dc2, double* __restrict__ S) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n_cams * 36) return;
+  const int c = idx / 36, a = (idx % 36) / 6, b = idx % 6;
+  const int lo = min(a, b), hi = max(a, b);
+  double v = Hcc[(size_t)c * 21 + tri6(lo, hi)];
+  if (a == b) v += Dc2[6 * c + a];
+  const size_t n = 6 * (size_t)n_cams;
+  S[(6 * (size_t)c + a) * n + 6 * (size_t)c + b] = v;
+}
+
+// S[ci,cj] -= W_i Hpp^-1 W_j^T for every ordered pair (i,j) of observations of a point with
+// cam(i) >= cam(j): lower block triangle.  One thread per observation i, W of the tile staged in
+// shared memory so the inner loop over j reads it from there.
+__global__ void __launch_bounds__(TILE) dense_schur_kernel(Dev d, const double* __restrict__ Hpp_inv, double* __restrict__ S) {
+  __shared__ double sW[TILE][19];
+  __shared__ int sCam[TILE];
+  const TileThread t = tile_thread(d);
+  const size_t n = (size_t)d.n_obs;
+  double W[18];
+  int ci = -1;
+  if (t.valid) {
+    ci = __ldg(d.cam + t.i);
+    double jc[12], jp[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      const double2 v = d.Jc[k * n + t.i];
+      jc[k] = v.x; jc[6 + k] = v.y;
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const double2 v = d.Jp[k * n + t.i];
+      jp[k] = v.x; jp[3 + k] = v.y;
+    }
+#pragma unroll
+    for (int a = 0; a < 6; ++a)
+#pragma unroll
+      for (int b = 0; b < 3; ++b) W[a * 3 + b] = jc[a] * jp[b] + jc[6 + a] * jp[3 + b];
+#pragma unroll
+    for (int k = 0; k < 18; ++k) sW[threadIdx.x][k] = W[k];
+  }
+  sCam[threadIdx.x] = ci;
+  __syncthreads();
+  if (!t.valid) return;
+  double Hi[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) Hi[k] = __ldg(Hpp_inv + 6 * (size_t)t.p + k);
+  double A[18];  // W_i Hpp^-1
+#pragma unroll
+  for (int a = 0; a < 6; ++a) sym3_mul(Hi, W[a * 3], W[a * 3 + 1], W[a * 3 + 2], A[a * 3], A[a * 3 + 1], A[a * 3 + 2]);
+  const size_t ld = 6 * (size_t)d.n_cams;
+  for (int j = t.seg_b; j < t.seg_e; ++j) {
+    const int lj = j - t.tile_b;
+    const int cj = sCam[lj];
+    if (cj > ci) continue;
+    double* dst = S + (6 * (size_t)ci) * ld + 6 * (size_t)cj;
+#pragma unroll
+    for (int a = 0; a < 6; ++a)
+#pragma unroll
+      for (int b = 0; b < 6; ++b) {
+        const double v = A[a * 3] * sW[lj][b * 3] + A[a * 3 + 1] * sW[lj][b * 3 + 1] + A[a * 3 + 2] * sW[lj][b * 3 + 2];
+        atomicAdd(dst + a * ld + b, -v);
+      }
+  }
+}
+
+__global__ void mirror_lower_kernel(int n, double* __restrict__ S) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = blockIdx.y;
+  if (j < n && j > i) S[(size_t)i * n + j] = S[(size_t)j * n + i];
+}
+
+// ---- parity taps -----------------------------------------------------------------------------
+__global__ void scatter_eval_kernel(Dev d, const int* __restrict__ order_pm, double* __restrict__ r_out, double* __restrict__ jac_out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= d.n_obs) return;
+  const size_t n = (size_t)d.n_obs;
+  const size_t o = (size_t)order_pm[i];
+  if (r_out) {
+    const double2 r = d.r[i];
+    r_out[2 * o] = r.x; r_out[2 * o + 1] = r.y;
+  }
+  if (jac_out) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      const double2 v = d.Jc[k * n + i];
+      jac_out[18 * o + k] = v.x; jac_out[18 * o + 9 + k] = v.y;
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const double2 v = d.Jp[k * n + i];
+      jac_out[18 * o + 6 + k] = v.x; jac_out[18 * o + 15 + k] = v.y;
+    }
+  }
+}
+
+__global__ void export_blocks_kernel(int n_cams, int n_pts, const double* __restrict__ Hcc, const double* __restrict__ Dc2,
+                                     const double* __restrict__ Hpp, double radius, double min_diag, double max_diag,
+                                     double* __restrict__ Hcc36, double* __restrict__ Hpp9) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (Hcc36 && idx < n_cams * 36) {
+    const int c = idx / 36, a = (idx % 36) / 6, b = idx % 6;
+    double v = Hcc[(size_t)c * 21 + tri6(min(a, b), max(a, b))];
+    if (a == b) v += Dc2[6 * c + a];
+    Hcc36[idx] = v;
+  }
+  if (Hpp9 && idx < n_pts * 9) {
+    const int p = idx / 9, a = (idx % 9) / 3, b = idx % 3;
+    const int lo = min(a, b), hi = max(a, b);
+    const int t3 = lo * 3 - (lo * (lo - 1)) / 2 + (hi - lo);
+    double v = Hpp[(size_t)p * 6 + t3];
+    if (a == b) {
+      const double D = sqrt(fmin(fmax(v, min_diag), max_diag) / radius);
+      v += D * D;
+    }
+    Hpp9[idx] = v;
+  }
+}
+
+inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+}  // namespace
+
+// ==========================================================================================
+// launchers
+// ==========================================================================================
+struct PendingTask { const double* in; int n; int scal_slot; int op; };
+static thread_local std::vector<PendingTask> g_pending;  // per calling thread; flushed by launch_finalize_scalars
+
+static void add_task(Problem& P, int part_slot, int n, int scal_slot, int op) {
+  g_pending.push_back({P.part + (size_t)part_slot * P.part_stride, n, scal_slot, op});
+}
+
+void launch_cam_prep(Problem& P, const double* cam, const double* scale_c, CamRow* rows, cudaStream_t s) {
+  cam_prep_kernel<<<cdiv(P.n_cams, 128), 128, 0, s>>>(P.n_cams, cam, P.K9, P.dist, scale_c, rows);
+  P.launches++;
+}
+
+void launch_rj(Problem& P, const CamRow* rows, const double* pts, const double* scale_p, bool write_j, bool form, cudaStream_t s) {
+  if (P.n_tiles == 0) return;
+  double* cp = P.part + (size_t)P_COST * P.part_stride;
+  if (write_j && form) rj_kernel<true, true><<<P.n_tiles, TILE, 0, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp);
+  else if (write_j) rj_kernel<true, false><<<P.n_tiles, TILE, 0, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp);
+  else if (form) rj_kernel<false, true><<<P.n_tiles, TILE, 0, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp);
+  else rj_kernel<false, false><<<P.n_tiles, TILE, 0, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp);
+  P.launches++;
+  add_task(P, P_COST, P.n_tiles, S_COST, 2);
+}
+
+void launch_cost(Problem& P, const CamRow* rows, const double* pts, int part_slot, cudaStream_t s) {
+  if (P.n_tiles == 0) return;
+  cost_kernel<<<P.n_tiles, TILE, 0, s>>>(P.d, rows, pts, P.part + (size_t)part_slot * P.part_stride);
+  P.launches++;
+  add_task(P, part_slot, P.n_tiles, S_CAND_COST, 2);
+}
+
+void launch_cam_major(Problem& P, const CamRow* rows, const double* pts, const double* scale_p, int what, cudaStream_t s) {
+  if (P.n_chunks > 0) {
+    if (what == 0) cam_major_kernel<0><<<cdiv(P.n_chunks, 8), 256, 0, s>>>(P.d, rows, pts, scale_p, P.Hpp_inv, P.chunk_part);
+    else cam_major_kernel<1><<<cdiv(P.n_chunks, 8), 256, 0, s>>>(P.d, rows, pts, scale_p, P.Hpp_inv, P.chunk_part);
+    P.launches++;
+  }
+  const int nv = what == 0 ? 27 : 21;
+  cam_reduce_kernel<<<cdiv(P.n_cams * nv, 256), 256, 0, s>>>(P.n_cams, nv, P.d.cam_chunk_start, P.chunk_part, what == 0 ? P.Hcc : P.E, P.gc);
+  P.launches++;
+}
+
+void launch_jacobi_scale(Problem& P, bool enabled, cudaStream_t s) {
+  const int n = 6 * P.n_cams + 3 * P.n_pts;
+  jacobi_scale_kernel<<<cdiv(n, 256), 256, 0, s>>>(P.n_cams, P.n_pts, P.Hcc, P.Hpp, P.scale_c, P.scale_p, enabled ? 1 : 0);
+  P.launches++;
+}
+
+void launch_point_invert(Problem& P, double radius, double min_diag, double max_diag, cudaStream_t s) {
+  if (P.n_pts == 0) return;
+  point_invert_kernel<<<cdiv(P.n_pts, 256), 256, 0, s>>>(P.n_pts, P.Hpp, P.gp, radius, min_diag, max_diag, P.Hpp_inv, P.zp, P.flags);
+  P.launches++;
+}
+
+void launch_cam_diag(Problem& P, double radius, double min_diag, double max_diag, cudaStream_t s) {
+  cam_diag_kernel<<<cdiv(6 * P.n_cams, 256), 256, 0, s>>>(P.n_cams, P.Hcc, radius, min_diag, max_diag, P.Dc2);
+  P.launches++;
+}
+
+void launch_precond_invert(Problem& P, bool with_E, cudaStream_t s) {
+  precond_invert_kernel<<<cdiv(P.n_cams, 64), 64, 0, s>>>(P.n_cams, P.Hcc, P.Dc2, P.E, with_E ? 1 : 0, P.Minv, P.flags);
+  P.launches++;
+}
+
+void launch_schur_rhs(Problem& P, bool preload_gc, cudaStream_t s) {
+  if (preload_gc) cudaMemcpyAsync(P.rhs, P.gc, sizeof(double) * 6 * P.n_cams, cudaMemcpyDeviceToDevice, s);
+  else cudaMemsetAsync(P.rhs, 0, sizeof(double) * 6 * P.n_cams, s);
+  if (P.n_tiles == 0) return;
+  schur_pass_kernel<0><<<P.n_tiles, TILE, 0, s>>>(P.d, P.Hpp_inv, P.zp, nullptr, P.rhs, nullptr, nullptr, nullptr, nullptr, P.part,
+                                                  P.part_stride, P.flags, 1, 1);
+  P.launches++;
+}
+
+void launch_schur_matvec(Problem& P, const double* pvec, double* q, cudaStream_t s) {
+  if (P.n_tiles == 0) return;
+  schur_pass_kernel<1><<<P.n_tiles, TILE, 0, s>>>(P.d, P.Hpp_inv, P.zp, pvec, q, nullptr, nullptr, nullptr, nullptr, P.part,
+                                                  P.part_stride, P.flags, 1, 1);
+  P.launches++;
+}
+
+void launch_backsub(Problem& P, cudaStream_t s) {
+  if (P.n_tiles == 0) return;
+  const int cams_free = P.mode != 0, pts_free = P.mode != 1;
+  schur_pass_kernel<2><<<P.n_tiles, TILE, 0, s>>>(P.d, P.Hpp_inv, P.zp, P.yc, nullptr, P.pts_x, P.scale_p, P.yp, P.pts_c, P.part,
+                                                  P.part_stride, P.flags, cams_free, pts_free);
+  P.launches++;
+  add_task(P, P_MCC, P.n_tiles, S_MCC, 0);
+  add_task(P, P_DN_P, P.n_tiles, S_DN_P, 0);
+  add_task(P, P_XN_P, P.n_tiles, S_XN_P, 0);
+}
+
+void launch_cam_step(Problem& P, cudaStream_t s) {
+  const int n6 = 6 * P.n_cams, g = cdiv(n6, 256);
+  cam_step_kernel<<<g, 256, 0, s>>>(n6, P.cam_x, P.yc, P.scale_c, P.cam_nobs, P.cam_c, P.part, P.part_stride, P.mode != 0 ? 1 : 0, P.flags);
+  P.launches++;
+  add_task(P, P_DN_C, g, S_DN_C, 0);
+  add_task(P, P_XN_C, g, S_XN_C, 0);
+}
+
+void launch_block_solve_cams(Problem& P, cudaStream_t s) {
+  block_solve_cams_kernel<<<cdiv(6 * P.n_cams, 256), 256, 0, s>>>(P.n_cams, P.Minv, P.gc, P.yc);
+  P.launches++;
+}
+
+void launch_grad_norm(Problem& P, cudaStream_t s) {
+  if (P.mode != 0) {
+    const int n = 6 * P.n_cams, g = cdiv(n, 256);
+    grad_norm_kernel<<<g, 256, 0, s>>>(n, P.gc, P.scale_c, P.part + (size_t)P_GMAX_C * P.part_stride);
+    P.launches++;
+    add_task(P, P_GMAX_C, g, S_GMAX_C, 1);
+  }
+  if (P.mode != 1 && P.n_pts > 0) {
+    const int n = 3 * P.n_pts, g = cdiv(n, 256);
+    grad_norm_kernel<<<g, 256, 0, s>>>(n, P.gp, P.scale_p, P.part + (size_t)P_GMAX_P * P.part_stride);
+    P.launches++;
+    add_task(P, P_GMAX_P, g, S_GMAX_P, 1);
+  }
+}
+
+void launch_finalize_scalars(Problem& P, cudaStream_t s) {
+  size_t k = 0;
+  while (k < g_pending.size()) {
+    RedTasks T;
+    int cnt = 0;
+    for (; cnt < 8 && k < g_pending.size(); ++cnt, ++k) {
+      T.in[cnt] = g_pending[k].in;
+      T.n[cnt] = g_pending[k].n;
+      T.out[cnt] = P.scal + g_pending[k].scal_slot;
+      T.op[cnt] = g_pending[k].op;
+    }
+    reduce_tasks_kernel<<<cnt, 1024, 0, s>>>(T);
+    P.launches++;
+  }
+  g_pending.clear();
+}
+
+void launch_pcg_init(Problem& P, cudaStream_t s) {
+  pcg_init_kernel<<<1, 1024, 0, s>>>(6 * P.n_cams, P.rhs, P.Minv, P.pcg_x, P.pcg_r, P.pcg_z, P.pcg_p, P.pcg_q, P.scal, P.flags);
+  P.launches++;
+}
+
+void launch_pcg_step(Problem& P, double tol, int max_it, cudaStream_t s) {
+  pcg_step_kernel<<<1, 1024, 0, s>>>(6 * P.n_cams, P.Minv, P.Dc2, P.pcg_x, P.pcg_r, P.pcg_z, P.pcg_p, P.pcg_q, P.scal, P.flags, tol * tol, max_it);
+  P.launches++;
+}
+
+void launch_dense_init(Problem& P, bool with_diag, cudaStream_t s) {
+  const size_t n = 6 * (size_t)P.n_cams;
+  cudaMemsetAsync(P.S, 0, sizeof(double) * n * n, s);
+  if (!with_diag) return;
+  dense_init_kernel<<<cdiv(P.n_cams * 36, 256), 256, 0, s>>>(P.n_cams, P.Hcc, P.Dc2, P.S);
+  P.launches++;
+}
+
+void launch_dense_schur(Problem& P, cudaStream_t s) {
+  if (P.n_tiles == 0) return;
+  dense_schur_kernel<<<P.n_tiles, TILE, 0, s>>>(P.d, P.Hpp_inv, P.S);
+  P.launches++;
+}
+
+void launch_mirror_lower(Problem& P, cudaStream_t s) {
+  const int n = 6 * P.n_cams;
+  if (n == 0) return;
+  dim3 g(cdiv(n, 256), n);
+  mirror_lower_kernel<<<g, 256, 0, s>>>(n, P.S);
+  P.launches++;
+}
+
+void launch_scatter_eval(Problem& P, double* r_out, double* jac_out, cudaStream_t s) {
+  if (P.n_obs == 0) return;
+  scatter_eval_kernel<<<cdiv(P.n_obs, 256), 256, 0, s>>>(P.d, P.order_pm, r_out, jac_out);
+  P.launches++;
+}
+
+void launch_export_blocks(Problem& P, double* Hcc36, double* Hpp9, cudaStream_t s) {
+  // uses the radius baked into Dc2 for cameras; points recompute from the diagonal — caller passes radius via P.scal_host[31]
+  const int n = max(P.n_cams * 36, P.n_pts * 9);
+  if (n == 0) return;
+  export_blocks_kernel<<<cdiv(n, 256), 256, 0, s>>>(P.n_cams, P.n_pts, P.Hcc, P.Dc2, P.Hpp, P.scal_host[31], P.scal_host[30], P.scal_host[29],
+                                                    Hcc36, Hpp9);
+  P.launches++;
+}
+
+}  // namespace hsfm

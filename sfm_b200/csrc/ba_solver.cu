@@ -1,0 +1,284 @@
+// ba_solver.cu — Levenberg–Marquardt trust-region driver with Ceres' semantics (SURVEY.md
+// Appendix A.3; replaces ceres::Solve at CTracker.cpp:700-701 with the options of
+// CTracker.cpp:571-577).  All arithmetic runs in the kernels of ba_kernels.cu / ba_chol.cu; the
+// host only sequences launches and reads back a 256-byte scalar block once per trust-region
+// attempt to take the accept/reject decision.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+#include "ba_internal.h"
+
+namespace hsfm {
+namespace {
+
+struct Driver {
+  Ctx& ctx;
+  Problem& P;
+  cudaStream_t s;
+  const hsfm_ba_options& o;
+  bool cams_free, pts_free;
+  bool dense;
+  int rc = 0;
+
+  Driver(Ctx& c, const hsfm_ba_options& opt)
+      : ctx(c), P(c.prob), s(c.stream), o(opt), cams_free(c.prob.mode != 0), pts_free(c.prob.mode != 1), dense(false) {}
+
+  bool multi() const { return ctx.comm.n_ranks > 1; }
+  void chk(int r) { if (r && !rc) rc = r; }
+
+  int read_back() {
+    HSFM_CUDA(cudaMemcpyAsync(P.scal_host, P.scal, sizeof(double) * 16, cudaMemcpyDeviceToHost, s));
+    HSFM_CUDA(cudaMemcpyAsync(P.flags_host, P.flags, sizeof(int) * FLAG_SLOTS, cudaMemcpyDeviceToHost, s));
+    HSFM_CUDA(cudaStreamSynchronize(s));
+    return 0;
+  }
+
+  // Jacobi column scaling from the unscaled Jacobian at the initial point (A.3 "iter 0").
+  void compute_scaling() {
+    launch_cam_prep(P, P.cam_x, nullptr, P.rows_x, s);
+    launch_rj(P, P.rows_x, P.pts_x, nullptr, /*write_j=*/false, /*form=*/true, s);
+    launch_cam_major(P, P.rows_x, P.pts_x, nullptr, 0, s);
+    if (multi()) chk(ctx.comm.allreduce_sum(P.Hcc, 21 * (size_t)P.n_cams, s));
+    launch_jacobi_scale(P, o.jacobi_scaling != 0, s);
+  }
+
+  // r, J (scaled), cost, point blocks, camera blocks, gradient norm at the current x.
+  void linearize() {
+    launch_cam_prep(P, P.cam_x, P.scale_c, P.rows_x, s);
+    launch_rj(P, P.rows_x, P.pts_x, P.scale_p, true, true, s);
+    launch_cam_major(P, P.rows_x, P.pts_x, P.scale_p, 0, s);
+    if (multi()) {
+      chk(ctx.comm.allreduce_sum(P.Hcc, 21 * (size_t)P.n_cams, s));
+      chk(ctx.comm.allreduce_sum(P.gc, 6 * (size_t)P.n_cams, s));
+    }
+    launch_grad_norm(P, s);
+    launch_finalize_scalars(P, s);
+    if (multi()) {
+      chk(ctx.comm.allreduce_sum(P.scal + S_COST, 1, s));
+      chk(ctx.comm.allreduce_max(P.scal + S_GMAX_P, 1, s));
+    }
+  }
+
+  // One linear solve + candidate evaluation.  Leaves scalars/flags on the host mirrors.
+  int attempt(double radius, int* linear_its) {
+    *linear_its = 0;
+    HSFM_CUDA(cudaMemsetAsync(P.flags, 0, sizeof(int) * FLAG_SLOTS, s));
+    if (pts_free) launch_point_invert(P, radius, o.min_lm_diagonal, o.max_lm_diagonal, s);
+    if (cams_free) launch_cam_diag(P, radius, o.min_lm_diagonal, o.max_lm_diagonal, s);
+    const int n6 = 6 * P.n_cams;
+    if (P.mode == 2) {
+      const bool lead = ctx.comm.rank == 0;
+      if (dense) {
+        launch_dense_init(P, lead, s);
+        launch_dense_schur(P, s);
+        launch_schur_rhs(P, lead, s);
+        if (multi()) {
+          chk(ctx.comm.allreduce_sum(P.S, (size_t)n6 * n6, s));
+          chk(ctx.comm.allreduce_sum(P.rhs, n6, s));
+        }
+        launch_cholesky(P.S, n6, P.flags + F_CHOL_FAIL, s, &P.launches);
+        HSFM_CUDA(cudaMemcpyAsync(P.yc, P.rhs, sizeof(double) * n6, cudaMemcpyDeviceToDevice, s));
+        launch_chol_solve(P.S, n6, P.yc, s, &P.launches);
+      } else {
+        launch_cam_major(P, P.rows_x, P.pts_x, P.scale_p, 1, s);
+        if (multi()) chk(ctx.comm.allreduce_sum(P.E, 21 * (size_t)P.n_cams, s));
+        launch_precond_invert(P, true, s);
+        launch_schur_rhs(P, lead, s);
+        if (multi()) chk(ctx.comm.allreduce_sum(P.rhs, n6, s));
+        launch_pcg_init(P, s);
+        const int batch = 8;
+        int issued = 0;
+        while (issued < o.pcg_max_iterations) {
+          for (int b = 0; b < batch && issued < o.pcg_max_iterations; ++b, ++issued) {
+            launch_schur_matvec(P, P.pcg_p, P.pcg_q, s);
+            if (multi()) chk(ctx.comm.allreduce_sum(P.pcg_q, n6, s));
+            launch_pcg_step(P, o.pcg_tolerance, o.pcg_max_iterations, s);
+          }
+          HSFM_CUDA(cudaMemcpyAsync(P.flags_host, P.flags, sizeof(int) * FLAG_SLOTS, cudaMemcpyDeviceToHost, s));
+          HSFM_CUDA(cudaStreamSynchronize(s));
+          if (P.flags_host[F_PCG_DONE]) break;
+        }
+        *linear_its = P.flags_host[F_PCG_ITERS];
+        HSFM_CUDA(cudaMemcpyAsync(P.yc, P.pcg_x, sizeof(double) * n6, cudaMemcpyDeviceToDevice, s));
+      }
+    } else if (P.mode == 1) {
+      launch_precond_invert(P, false, s);
+      launch_block_solve_cams(P, s);
+    }
+    launch_cam_step(P, s);
+    launch_cam_prep(P, P.cam_c, P.scale_c, P.rows_c, s);
+    launch_backsub(P, s);
+    launch_cost(P, P.rows_c, P.pts_c, P_COST, s);
+    launch_finalize_scalars(P, s);
+    if (multi()) chk(ctx.comm.allreduce_sum(P.scal + S_MCC, 4, s));
+    if (rc) return rc;
+    return read_back();
+  }
+};
+
+}  // namespace
+
+int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
+  Problem& P = ctx.prob;
+  cudaStream_t s = ctx.stream;
+  hsfm_ba_summary local;
+  std::memset(&local, 0, sizeof(local));
+  hsfm_ba_iteration* trace = summary ? summary->trace : nullptr;
+  const int trace_cap = summary ? summary->trace_capacity : 0;
+  hsfm_ba_summary& S = summary ? *summary : local;
+  const double keep_setup = S.setup_ms, keep_h2d = S.h2d_ms;
+  std::memset(&S, 0, sizeof(S));
+  S.trace = trace; S.trace_capacity = trace_cap; S.setup_ms = keep_setup; S.h2d_ms = keep_h2d;
+  S.n_ranks = ctx.comm.n_ranks;
+  int trace_n = 0;
+  auto push = [&](const hsfm_ba_iteration& it) { if (trace && trace_n < trace_cap) trace[trace_n] = it; ++trace_n; };
+  const int64_t launches0 = P.launches;
+
+  Driver D(ctx, o);
+  const int n6 = 6 * P.n_cams;
+  if (P.mode == 2) {
+    if (o.linear_solver == HSFM_BA_LINEAR_DENSE_SCHUR) D.dense = true;
+    else if (o.linear_solver == HSFM_BA_LINEAR_PCG) D.dense = false;
+    else D.dense = P.n_cams <= o.dense_max_cams;
+    if (D.dense) {
+      const size_t need = (size_t)n6 * n6;
+      if (P.S_capacity < need) {
+        if (P.S) cudaFree(P.S);
+        P.S = nullptr; P.S_capacity = 0;
+        if (cudaMalloc(&P.S, sizeof(double) * std::max<size_t>(need, 1)) != cudaSuccess) {
+          cudaGetLastError();
+          if (o.linear_solver == HSFM_BA_LINEAR_DENSE_SCHUR) return HSFM_BA_ERR_NOMEM;
+          D.dense = false;
+        } else {
+          P.S_capacity = need;
+        }
+      }
+    }
+  }
+  S.linear_solver_used = (P.mode == 2 && !D.dense) ? HSFM_BA_LINEAR_PCG : HSFM_BA_LINEAR_DENSE_SCHUR;
+
+  cudaEvent_t ev0, ev1;
+  HSFM_CUDA(cudaEventCreate(&ev0));
+  HSFM_CUDA(cudaEventCreate(&ev1));
+  HSFM_CUDA(cudaEventRecord(ev0, s));
+
+  D.compute_scaling();
+  D.linearize();
+  if (D.rc) return D.rc;
+  { int r = D.read_back(); if (r) return r; }
+  auto gmax_of = [&]() {
+    double g = 0.0;
+    if (D.cams_free) g = std::max(g, P.scal_host[S_GMAX_C]);
+    if (D.pts_free) g = std::max(g, P.scal_host[S_GMAX_P]);
+    return g;
+  };
+  double x_cost = P.scal_host[S_COST];
+  double gmax = gmax_of();
+  S.initial_cost = x_cost;
+  double radius = o.initial_trust_region_radius, decrease_factor = 2.0;
+  int invalid_run = 0, num_success = 0, total_lin = 0, iter = 0;
+  int term = HSFM_BA_NO_CONVERGENCE;
+  {
+    hsfm_ba_iteration it0;
+    std::memset(&it0, 0, sizeof(it0));
+    it0.cost = x_cost; it0.gradient_max_norm = gmax; it0.trust_region_radius = radius; it0.step_is_valid = 1; it0.step_is_successful = 1;
+    push(it0);
+  }
+  if (!std::isfinite(x_cost)) {
+    term = HSFM_BA_FAILURE;
+  } else if (gmax <= o.gradient_tolerance || P.n_obs == 0) {
+    term = HSFM_BA_CONVERGENCE;
+  } else {
+    while (true) {
+      if (iter >= o.max_num_iterations) { term = HSFM_BA_NO_CONVERGENCE; break; }
+      ++iter;
+      hsfm_ba_iteration its;
+      std::memset(&its, 0, sizeof(its));
+      int lin = 0;
+      { int r = D.attempt(radius, &lin); if (r) return r; }
+      total_lin += lin;
+      its.linear_iterations = lin;
+      const double mcc = P.scal_host[S_MCC];
+      const double cand_cost_raw = P.scal_host[S_CAND_COST];
+      const double dn2 = (D.cams_free ? P.scal_host[S_DN_C] : 0.0) + (D.pts_free ? P.scal_host[S_DN_P] : 0.0);
+      const double xn2 = (D.cams_free ? P.scal_host[S_XN_C] : 0.0) + (D.pts_free ? P.scal_host[S_XN_P] : 0.0);
+      const bool bad = P.flags_host[F_INVALID] != 0 || P.flags_host[F_CHOL_FAIL] != 0 || !std::isfinite(mcc) || !(mcc > 0.0) ||
+                       !std::isfinite(dn2);
+      its.model_cost_change = mcc;
+      if (bad) {
+        ++invalid_run;
+        its.step_is_valid = 0; its.cost = x_cost; its.gradient_max_norm = gmax;
+        radius /= decrease_factor; decrease_factor *= 2.0;
+        its.trust_region_radius = radius;
+        push(its);
+        if (o.verbose) std::fprintf(stderr, "[hsfm_ba] it %3d INVALID step (flags %d chol %d mcc %.3e) radius -> %.3e\n", iter,
+                                    P.flags_host[F_INVALID], P.flags_host[F_CHOL_FAIL], mcc, radius);
+        if (invalid_run >= o.max_consecutive_invalid_steps) { term = HSFM_BA_FAILURE; break; }
+        if (radius <= o.min_trust_region_radius) { term = HSFM_BA_CONVERGENCE; break; }
+        continue;
+      }
+      invalid_run = 0;
+      its.step_is_valid = 1;
+      double cand_cost = cand_cost_raw;
+      if (!std::isfinite(cand_cost)) cand_cost = 1.7976931348623157e308;
+      const double x_norm = std::sqrt(xn2);
+      its.step_norm = std::sqrt(dn2);
+      its.cost_change = x_cost - cand_cost;
+      its.cost = x_cost; its.gradient_max_norm = gmax; its.trust_region_radius = radius;
+      if (its.step_norm <= o.parameter_tolerance * (x_norm + o.parameter_tolerance)) { term = HSFM_BA_CONVERGENCE; push(its); break; }
+      if (std::fabs(its.cost_change) <= o.function_tolerance * x_cost) { term = HSFM_BA_CONVERGENCE; push(its); break; }
+      const double rho = its.cost_change / mcc;
+      its.relative_decrease = rho;
+      if (rho > o.min_relative_decrease) {
+        std::swap(P.cam_x, P.cam_c);
+        std::swap(P.pts_x, P.pts_c);
+        D.linearize();
+        if (D.rc) return D.rc;
+        { int r = D.read_back(); if (r) return r; }
+        x_cost = P.scal_host[S_COST];
+        gmax = gmax_of();
+        ++num_success;
+        its.step_is_successful = 1;
+        radius = radius / std::max(1.0 / 3.0, 1.0 - std::pow(2.0 * rho - 1.0, 3));
+        radius = std::min(o.max_trust_region_radius, radius);
+        decrease_factor = 2.0;
+        its.cost = x_cost; its.gradient_max_norm = gmax; its.trust_region_radius = radius;
+        push(its);
+        if (o.verbose)
+          std::fprintf(stderr, "[hsfm_ba] it %3d cost %.9e dcost %.3e |g| %.3e |step| %.3e rho %.3e radius %.3e lin %d\n", iter, its.cost,
+                       its.cost_change, its.gradient_max_norm, its.step_norm, rho, radius, lin);
+        if (gmax <= o.gradient_tolerance) { term = HSFM_BA_CONVERGENCE; break; }
+      } else {
+        radius /= decrease_factor; decrease_factor *= 2.0;
+        its.trust_region_radius = radius;
+        push(its);
+        if (o.verbose)
+          std::fprintf(stderr, "[hsfm_ba] it %3d REJECTED cost %.9e cand %.9e rho %.3e radius -> %.3e lin %d\n", iter, x_cost, cand_cost, rho,
+                       radius, lin);
+        if (radius <= o.min_trust_region_radius) { term = HSFM_BA_CONVERGENCE; break; }
+      }
+    }
+  }
+  HSFM_CUDA(cudaEventRecord(ev1, s));
+  HSFM_CUDA(cudaEventSynchronize(ev1));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, ev0, ev1);
+  cudaEventDestroy(ev0);
+  cudaEventDestroy(ev1);
+  S.solve_ms = ms;
+  S.final_cost = x_cost;
+  int64_t n_obs_total = P.n_obs;
+  S.rms_px = 0.0;  // filled by the caller when the global observation count is known
+  (void)n_obs_total;
+  S.num_iterations = iter;
+  S.num_successful_steps = num_success;
+  S.termination_type = term;
+  S.total_linear_iterations = total_lin;
+  S.gpu_launches = P.launches - launches0;
+  S.trace_count = std::min(trace_n, trace_cap);
+  return 0;
+}
+
+}  // namespace hsfm

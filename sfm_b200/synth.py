@@ -193,32 +193,40 @@ def make_path(n_cams: int, n_pts: int, n_obs: int, seed: int, *, skew: float = 0
     mean_track = n_obs / n_pts
     max_track = min(max_track, n_cams)
     n_gen = int(n_pts * 1.15) + 64
-    p_geo = 1.0 / max(mean_track * 1.06 - 1.0, 1.0 + 1e-9)
-    L = np.minimum(1 + rng.geometric(min(p_geo, 1.0), n_gen), max_track).astype(np.int64)
-    centre_cam = rng.integers(0, n_cams, n_gen)
-    # point in the centre camera's frame, then to world
-    depth = rng.uniform(6.0, 14.0, n_gen)
-    xc = np.stack([rng.uniform(-0.25, 0.25, n_gen) * depth, rng.uniform(-0.25, 0.25, n_gen) * depth, depth], axis=1)
-    pts_all = np.einsum("nij,nj->ni", Rc2w[centre_cam], xc) + C[centre_cam]
-
-    cam_l, pt_l = [], []
-    for ell in np.unique(L):
-        sel = np.nonzero(L == ell)[0]
-        win = min(3 * int(ell), n_cams)
-        keys = rng.random((sel.size, win))
-        offs = np.argsort(keys, axis=1)[:, : int(ell)] - win // 2
-        cams = (centre_cam[sel, None] + offs) % n_cams
-        cam_l.append(cams.reshape(-1))
-        pt_l.append(np.repeat(sel, int(ell)))
-    cam_idx = np.concatenate(cam_l)
-    pt_idx = np.concatenate(pt_l)
-    uv, z = project(cam_true, K, pts_all, cam_idx, pt_idx, dist)
-    ok = (z > 0.1) & (uv[:, 0] >= 0) & (uv[:, 0] < WIDTH) & (uv[:, 1] >= 0) & (uv[:, 1] < HEIGHT)
-    cam_idx, pt_idx = cam_idx[ok], pt_idx[ok]
-    cnt = np.bincount(pt_idx, minlength=n_gen)
-    good = np.nonzero(cnt >= 2)[0]
-    if good.size < n_pts:
-        raise RuntimeError(f"generator produced only {good.size} valid points, need {n_pts}")
+    factor = 1.06
+    for _attempt in range(8):
+        p_geo = 1.0 / max(mean_track * factor - 1.0, 1.0 + 1e-9)
+        L = np.minimum(1 + rng.geometric(min(p_geo, 1.0), n_gen), max_track).astype(np.int64)
+        centre_cam = rng.integers(0, n_cams, n_gen)
+        # point in the centre camera's frame, then to world
+        depth = rng.uniform(6.0, 14.0, n_gen)
+        xc = np.stack([rng.uniform(-0.25, 0.25, n_gen) * depth, rng.uniform(-0.25, 0.25, n_gen) * depth, depth], axis=1)
+        pts_all = np.einsum("nij,nj->ni", Rc2w[centre_cam], xc) + C[centre_cam]
+        cam_l, pt_l = [], []
+        for ell in np.unique(L):
+            sel = np.nonzero(L == ell)[0]
+            win = min(3 * int(ell), n_cams)
+            keys = rng.random((sel.size, win))
+            offs = np.argsort(keys, axis=1)[:, : int(ell)] - win // 2
+            cams = (centre_cam[sel, None] + offs) % n_cams
+            cam_l.append(cams.reshape(-1))
+            pt_l.append(np.repeat(sel, int(ell)))
+        cam_idx = np.concatenate(cam_l)
+        pt_idx = np.concatenate(pt_l)
+        uv, z = project(cam_true, K, pts_all, cam_idx, pt_idx, dist)
+        ok = (z > 0.1) & (uv[:, 0] >= 0) & (uv[:, 0] < WIDTH) & (uv[:, 1] >= 0) & (uv[:, 1] < HEIGHT)
+        cam_idx, pt_idx = cam_idx[ok], pt_idx[ok]
+        cnt = np.bincount(pt_idx, minlength=n_gen)
+        good = np.nonzero(cnt >= 2)[0]
+        got = int(cnt[good[:n_pts]].sum()) if good.size >= n_pts else 0
+        if good.size >= n_pts and got >= n_obs:
+            break
+        if good.size < n_pts:
+            n_gen = int(n_gen * 1.3)
+        else:
+            factor *= max(1.04, 1.03 * n_obs / max(got, 1))
+    else:
+        raise RuntimeError(f"generator could not reach {n_pts} points / {n_obs} observations")
     # choose n_pts points whose total is >= n_obs and as close as possible: take the first n_pts,
     # then trim single observations off tracks longer than 2 / or swap in longer tracks
     good = good[:n_pts]
