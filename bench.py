@@ -1,0 +1,291 @@
+#!/usr/bin/env python
+"""bench.py — LM bundle-adjustment throughput of the B200-native solver (BASELINE.json metric:
+"LM iters/s & residual+Jacobian obs/s at 1/2/4/8 B200 vs Ceres CPU").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--config c4] [--impl ours|reference]
+
+A *step* is one complete Levenberg–Marquardt solve of the synthetic problem from its perturbed
+initial guess with the reference's options (CTracker.cpp:571-577 = Ceres defaults), restarted
+from the same guess every step, so every step does identical work.  ``value`` = trust-region
+iterations completed per second of device time (max over ranks, inputs resident in HBM);
+``e2e`` = the same through the host-buffer C-ABI call (H2D + index build + solve + D2H inside the
+timed region).  Rank 0 prints ONE JSON line.
+
+N > 1: launched by torch.distributed.run, one rank per GPU; observations are sharded by point
+(SURVEY.md §8e), cameras replicated, NCCL all-reduces of the camera system inside the library.
+Total work is fixed as N grows => "scaling": "strong".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "lm_iterations_per_s"
+UNIT = "LM iterations/s"
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return json.load(f).get("hbm_gbs", 6650.0), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled during the timed region (B200_PROFILING.md)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.gpu)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if not self.proc:
+            return out
+        try:
+            self.proc.terminate()
+            self.proc.wait(timeout=5)
+            self.f.close()
+            rows = [l.strip().split(", ") for l in open(self.path) if l.strip()]
+            sm = [float(r[1]) for r in rows if len(r) >= 9]
+            if sm:
+                out["sm_mhz"] = float(np.median(sm))
+                out["sm_max_mhz"] = float(rows[0][2])
+                out["samples"] = len(sm)
+                names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+                for k, nm in enumerate(names):
+                    if any(r[5 + k].strip().lower().startswith("active") for r in rows if len(r) >= 9):
+                        out["reasons"].append(nm)
+        except Exception:
+            pass
+        finally:
+            try:
+                os.unlink(self.path)
+            except Exception:
+                pass
+        return out
+
+
+def run_reference(args, rank, world):
+    """Reference arm: the reference's own CPU implementation of the path.  Real Ceres cannot be
+    built here, so this is the oracle port (oracle/), all host threads, on a bounded
+    sample of the same workload: ONE trust-region iteration of the named problem per step."""
+    if rank != 0:
+        return
+    from oracle import pyoracle as po
+    from sfm_b200 import synth
+
+    prob = synth.make_config(args.config)
+    cores = os.cpu_count() or 1
+    dense_ok = prob.n_cams <= 4000
+    opts = po.default_options(num_threads=cores, max_num_iterations=1, linear_solver=1 if dense_ok else 2,
+                              pcg_tolerance=1e-10, pcg_max_iterations=1000)
+    times, its = [], 0
+    for step in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        _, _, s, _ = po.solve(prob, opts=opts)
+        dt = time.perf_counter() - t0
+        if step >= args.warmup:
+            times.append(dt)
+            its += s["num_iterations"]
+    total = sum(times)
+    value = its / total
+    sample = (f"1 LM iteration (dual-number evaluation + {'dense Schur + blocked Cholesky' if dense_ok else 'implicit-Schur block-Jacobi PCG'}"
+              f" + candidate evaluation) of {args.config} per step, {cores} OpenMP threads")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / max(1, args.steps), "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": synth.CONFIG_TITLES[args.config], "config_id": args.config, "n_cams": prob.n_cams, "n_pts": prob.n_pts,
+                   "n_obs": prob.n_obs},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "restated Ceres-1.12 semantics (oracle/), not Ceres itself: the reference cannot be compiled in this image",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--config", default="c4", choices=["c1", "c2", "c3", "c4", "c5"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--linear", default="auto", choices=["auto", "dense", "pcg"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    from sfm_b200 import api, synth
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the solver has no CPU path")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    prob = synth.make_config(args.config)
+    n_obs_total, n_cams, n_pts_total = prob.n_obs, prob.n_cams, prob.n_pts
+    full = prob
+    if world > 1:
+        prob = synth.shard_by_point(full, world)[rank][0]
+
+    ctx = api.Context(local_rank)
+    stream = torch.cuda.current_stream()
+    ctx.set_stream(stream.cuda_stream)
+    if world > 1:
+        uid = [api.Context.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.comm_init(uid[0], rank, world)
+
+    linear = {"auto": api.LINEAR_AUTO, "dense": api.LINEAR_DENSE_SCHUR, "pcg": api.LINEAR_PCG}[args.linear]
+    opts = api.default_options(linear_solver=linear)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident arm -------------------------------------------------------------------
+    ctx.upload(prob)
+    summ = None
+    for _ in range(args.warmup):
+        ctx.reset()
+        summ = ctx.solve_resident(opts)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    its = launches = 0
+    e0.record(stream)
+    for _ in range(args.steps):
+        ctx.reset()
+        summ = ctx.solve_resident(opts)
+        its += summ["num_iterations"]
+        launches += summ["gpu_launches"]
+    e1.record(stream)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    value = its / (ms * 1e-3)
+
+    # ---- kernel timings / roofline (rank 0's shard; live CUDA events inside the library) ---------
+    peak, peak_src = load_peaks()
+    kernels = {}
+    for k in ["rj_form", "rj", "schur_matvec", "backsub", "cam_form", "cost"]:
+        t = ctx.time_kernel(k, 20)
+        b = ctx.algorithmic_bytes(k)
+        kernels[k] = {"ms": t, "algorithmic_bytes": b, "gbs": b / t / 1e6, "frac_of_hbm_peak": b / t / 1e6 / peak}
+    rj = kernels["rj"]
+    obs_per_s_local = prob.n_obs / (rj["ms"] * 1e-3)
+    rj_obs = torch.tensor([obs_per_s_local], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(rj_obs, op=dist.ReduceOp.SUM)
+
+    # ---- end-to-end arm: host buffers through the C ABI ----------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        pin = lambda a: torch.from_numpy(a).pin_memory().numpy()  # noqa: E731
+        hp = synth.Problem(obs=pin(prob.obs), cam_idx=pin(prob.cam_idx), pt_idx=pin(prob.pt_idx), K=pin(prob.K), cam=pin(prob.cam),
+                           pts=pin(prob.pts), cam_true=prob.cam_true, pts_true=prob.pts_true, dist=None, name=prob.name)
+        h2d = hp.obs.nbytes + hp.cam_idx.nbytes + hp.pt_idx.nbytes + hp.K.nbytes + hp.cam.nbytes + hp.pts.nbytes
+        d2h = hp.cam.nbytes + hp.pts.nbytes
+        ctx.solve_packed(hp, opts=opts)
+        barrier()
+        t0 = time.perf_counter()
+        e2e_its = 0
+        for _ in range(args.steps):
+            _, _, s2 = ctx.solve_packed(hp, opts=opts)
+            e2e_its += s2["num_iterations"]
+        barrier()
+        dt = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": e2e_its / float(dt.item()), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+               "ms_per_step": 1e3 * float(dt.item()) / args.steps}
+
+    # ---- CPU baseline (rank 0, N = 1 only): oracle port on a bounded sample ---------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import pyoracle as po
+
+        cores = os.cpu_count() or 1
+        dense_ok = n_cams <= 4000
+        oo = po.default_options(num_threads=cores, max_num_iterations=1, linear_solver=1 if dense_ok else 2)
+        t0 = time.perf_counter()
+        _, _, so, _ = po.solve(full, opts=oo)
+        dt = time.perf_counter() - t0
+        cpu = {"value": so["num_iterations"] / dt, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"1 LM iteration of {args.config} ({'dense Schur + Cholesky' if dense_ok else 'implicit-Schur PCG'}), {cores} OpenMP threads, {dt:.1f} s",
+               "eval_obs_per_s": 2 * n_obs_total / max(so["eval_seconds"], 1e-9)}
+
+    if rank == 0:
+        dom = max(("rj_form", "schur_matvec", "backsub", "cam_form"), key=lambda k: kernels[k]["ms"])
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": synth.CONFIG_TITLES[args.config], "config_id": args.config, "n_cams": n_cams, "n_pts": n_pts_total,
+                       "n_obs": n_obs_total, "parallelism": f"point-sharded x{world}", "l2": "inputs larger than L2" if n_obs_total * 184 > 126e6 else "L2-resident working set (latency-bound; no flush)",
+                       "linear_solver": {1: "dense_schur", 2: "pcg"}[summ["linear_solver_used"]], "lm_iterations_per_step": summ["num_iterations"],
+                       "final_cost": summ["final_cost"], "rms_px": summ["rms_px"], "linear_iterations_per_step": summ["total_linear_iterations"]},
+            "rj_obs_per_s": float(rj_obs.item()),
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"kernel": "rj_kernel<write_j,form>" if dom == "rj_form" else dom, "bound": "hbm", "achieved": kernels[dom]["gbs"],
+                         "peak": peak, "unit": "GB/s", "frac": kernels[dom]["gbs"] / peak, "traffic": None, "peak_source": peak_src},
+            "kernels": kernels,
+            "e2e": e2e,
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,239 @@
+"""GPU suite (-m gpu): the CUDA path, called through the C ABI of libhsfm_ba.so, against the CPU
+oracle on identical seeded inputs and against the committed golden vectors.
+
+Bars (BASELINE.json north_star): per-observation residuals and Jacobians within 1e-10 relative
+(definitions in tests/util.py), final cost / RMS within 1e-6 relative after the SAME iteration count."""
+import numpy as np
+import pytest
+
+from oracle import pyoracle as po
+from sfm_b200 import api, synth
+from tests.util import jacobian_err, kat_problem, rel, residual_err
+
+pytestmark = pytest.mark.gpu
+
+TOL_RJ = 1e-10
+TOL_COST = 1e-6
+
+
+def _with_dist(p, seed=2):
+    rng = np.random.default_rng(seed)
+    p.dist = np.ascontiguousarray(rng.normal(0, [0.05, 0.1], (p.n_cams, 2)))
+    return p
+
+
+@pytest.mark.parametrize("make", [
+    lambda: synth.make_config("c1"),
+    lambda: synth.make_config("c1", skew=0.5),
+    lambda: _with_dist(synth.make_ring(12, 500, 7, seed=31, skew=0.2)),
+    lambda: synth.make_config("c2", scale=0.1),
+    lambda: synth.make_config("c3", scale=0.05),
+], ids=["c1", "c1-skew", "ring-distortion", "c2-small", "c3-small"])
+def test_residuals_and_jacobians(ctx, make):
+    p = make()
+    r, J, cost = ctx.evaluate(p)
+    r0, J0, cost0 = po.evaluate(p)
+    assert residual_err(r, r0, p.obs) < TOL_RJ
+    assert jacobian_err(J, J0) < TOL_RJ
+    assert cost == pytest.approx(cost0, rel=1e-12)
+    # camera 0 sits at w = 0 exactly: Taylor branch of AngleAxisRotatePoint
+    m = p.cam_idx == 0
+    assert m.any() and jacobian_err(J[m], J0[m]) < TOL_RJ
+
+
+def test_golden_functor_vectors(ctx, golden_dir):
+    g = np.load(f"{golden_dir}/functor_kat.npz")
+    p = kat_problem(g)
+    r, J, _ = ctx.evaluate(p)
+    assert residual_err(r, g["r"], p.obs) < 1e-12
+    assert jacobian_err(J, g["J"]) < 1e-11  # mpmath, 50 digits
+    ns = g["K"][:, 1] == 0.0
+    assert jacobian_err(J[ns][:, :, :6], g["J_cv2"][ns]) < 1e-11  # OpenCV (no skew term there)
+
+
+def test_distortion_zero_is_bit_identical(ctx):
+    p = synth.make_ring(10, 300, 6, seed=8, skew=0.1)
+    r0, J0, c0 = ctx.evaluate(p)
+    p.dist = np.zeros((p.n_cams, 2))
+    r1, J1, c1 = ctx.evaluate(p)
+    assert np.array_equal(r0, r1) and np.array_equal(J0, J1) and c0 == c1
+
+
+def test_observation_order_does_not_matter(ctx):
+    p = synth.make_config("c3", scale=0.05)
+    r0, J0, c0 = ctx.evaluate(p)
+    perm = np.random.default_rng(0).permutation(p.n_obs)
+    q = synth.Problem(obs=np.ascontiguousarray(p.obs[perm]), cam_idx=np.ascontiguousarray(p.cam_idx[perm]),
+                      pt_idx=np.ascontiguousarray(p.pt_idx[perm]), K=p.K, cam=p.cam, pts=p.pts, cam_true=p.cam_true, pts_true=p.pts_true)
+    r1, J1, c1 = ctx.evaluate(q)
+    assert np.array_equal(r1, r0[perm]) and np.array_equal(J1, J0[perm])  # per-observation work is order independent
+    assert c1 == pytest.approx(c0, rel=1e-13)
+
+
+def test_edge_cases(ctx):
+    # empty problem
+    e = synth.make_ring(4, 10, 3, seed=1)
+    empty = synth.Problem(obs=np.zeros((0, 2)), cam_idx=np.zeros(0, np.int32), pt_idx=np.zeros(0, np.int32), K=e.K, cam=e.cam, pts=e.pts,
+                          cam_true=e.cam, pts_true=e.pts)
+    r, J, c = ctx.evaluate(empty)
+    assert r.shape == (0, 2) and c == 0.0
+    cam, pts, s = ctx.solve_packed(empty)
+    assert s["num_iterations"] == 0 and np.array_equal(cam, e.cam) and np.array_equal(pts, e.pts)
+    # ragged: points with a single observation, a camera and a point without observations, tracks crossing warps/tiles
+    rng = np.random.default_rng(5)
+    base = synth.make_ring(9, 400, 9, seed=12)
+    keep = np.ones(base.n_obs, bool)
+    keep[base.pt_idx == 7] = False          # point 7: no observations
+    keep[base.cam_idx == 3] = False         # camera 3: no observations
+    one = np.nonzero(base.pt_idx == 11)[0]
+    keep[one[1:]] = False                   # point 11: a single observation
+    q = synth.Problem(obs=np.ascontiguousarray(base.obs[keep]), cam_idx=np.ascontiguousarray(base.cam_idx[keep]),
+                      pt_idx=np.ascontiguousarray(base.pt_idx[keep]), K=base.K, cam=base.cam, pts=base.pts, cam_true=base.cam_true,
+                      pts_true=base.pts_true)
+    r, J, c = ctx.evaluate(q)
+    r0, J0, c0 = po.evaluate(q)
+    assert residual_err(r, r0, q.obs) < TOL_RJ and jacobian_err(J, J0) < TOL_RJ
+    cam, pts, s = ctx.solve_packed(q, opts=api.default_options(linear_solver=api.LINEAR_DENSE_SCHUR))
+    cam0, pts0, so, _ = po.solve(q)
+    assert s["num_iterations"] == so["num_iterations"]
+    assert s["final_cost"] == pytest.approx(so["final_cost"], rel=TOL_COST)
+    assert np.array_equal(pts[7], base.pts[7]) and np.array_equal(cam[3], base.cam[3])  # untouched blocks
+    # long tracks: every point seen by 200 cameras (segments span many warps of a tile)
+    lt = synth.make_ring(200, 40, 200, seed=13)
+    r, J, _ = ctx.evaluate(lt)
+    r0, J0, _ = po.evaluate(lt)
+    assert jacobian_err(J, J0) < TOL_RJ
+    g, o = ctx.schur(lt), po.schur(lt)
+    assert rel(g["Hpp"], o["Hpp"]) < 1e-11 and rel(g["rhs"], o["rhs"]) < 1e-9
+
+
+def test_errors_leave_parameters_untouched(ctx):
+    p = synth.make_ring(6, 50, 4, seed=2)
+    bad = p.copy()
+    bad.cam_idx = p.cam_idx.copy()
+    bad.cam_idx[5] = 99
+    with pytest.raises(api.BAError) as ei:
+        ctx.solve_packed(bad)
+    assert ei.value.code == -1
+    # a point observed more than 256 times is outside the tile layout: refused, not mis-solved
+    big = synth.make_ring(300, 4, 300, seed=3)
+    with pytest.raises(api.BAError) as ei:
+        ctx.solve_packed(big)
+    assert ei.value.code == -4
+
+
+@pytest.mark.parametrize("make", [lambda: synth.make_ring(6, 40, 4, seed=99, skew=0.3), lambda: synth.make_config("c1"),
+                                  lambda: synth.make_config("c3", scale=0.05)], ids=["kat", "c1", "c3-small"])
+def test_normal_equation_blocks(ctx, make):
+    p = make()
+    g, o = ctx.schur(p, radius=1e4), po.schur(p, radius=1e4)
+    for k, tol in [("scale", 1e-12), ("Hpp", 1e-11), ("gp", 1e-10), ("Hcc", 1e-11), ("gc", 1e-10), ("rhs", 1e-9), ("S", 1e-9)]:
+        assert rel(g[k], o[k]) < tol, k
+    assert np.array_equal(g["S"], g["S"].T)
+
+
+def test_golden_normal_equations_lapack(ctx, golden_dir):
+    g = np.load(f"{golden_dir}/normal_eq_kat.npz")
+    from tests.golden.make_golden import small_problem
+
+    p = small_problem()
+    d = ctx.schur(p, radius=float(g["radius"]))
+    assert rel(d["scale"], g["scale"]) < 1e-12 and rel(d["S"], g["S"]) < 1e-9 and rel(d["rhs"], g["rhs"]) < 1e-9
+    cam, pts, s = ctx.solve_packed(p, opts=api.default_options(max_num_iterations=1, linear_solver=api.LINEAR_DENSE_SCHUR))
+    assert s["trace"][1]["model_cost_change"] == pytest.approx(float(g["model_cost_change"]), rel=1e-8)
+
+
+@pytest.mark.parametrize("linear", [api.LINEAR_DENSE_SCHUR, api.LINEAR_PCG], ids=["dense", "pcg"])
+@pytest.mark.parametrize("make", [lambda: synth.make_config("c1"), lambda: synth.make_config("c2", scale=0.1),
+                                  lambda: synth.make_config("c3", scale=0.05), lambda: _with_dist(synth.make_ring(12, 500, 7, seed=31))],
+                         ids=["c1", "c2-small", "c3-small", "distortion"])
+def test_lm_solve_matches_oracle(ctx, make, linear):
+    p = make()
+    cam, pts, s = ctx.solve_packed(p, opts=api.default_options(linear_solver=linear, pcg_max_iterations=3000))
+    cam0, pts0, so, tro = po.solve(p, opts=po.default_options(num_threads=4))
+    assert s["num_iterations"] == so["num_iterations"] and s["num_successful_steps"] == so["num_successful_steps"]
+    assert s["termination_type"] == so["termination_type"]
+    assert s["final_cost"] == pytest.approx(so["final_cost"], rel=TOL_COST)
+    assert s["rms_px"] == pytest.approx(so["rms_px"], rel=TOL_COST)
+    for a, b in zip(s["trace"], tro):  # same trajectory, not only the same end point
+        assert a["cost"] == pytest.approx(b["cost"], rel=TOL_COST)
+        assert a["trust_region_radius"] == pytest.approx(b["trust_region_radius"], rel=1e-6)
+        assert a["step_is_successful"] == b["step_is_successful"]
+    assert np.abs(cam - cam0).max() < 1e-6 and np.abs(pts - pts0).max() < 1e-6
+    assert s["gpu_launches"] > 0 and s["linear_solver_used"] == linear
+
+
+@pytest.mark.parametrize("mode", [api.STRUCT_ONLY, api.POSE_ONLY])
+def test_struct_only_and_pose_only(ctx, mode):
+    p = synth.make_config("c1")
+    cam, pts, s = ctx.solve_packed(p, mode=mode)
+    cam0, pts0, so, _ = po.solve(p, mode=mode)
+    assert s["num_iterations"] == so["num_iterations"]
+    assert s["final_cost"] == pytest.approx(so["final_cost"], rel=TOL_COST)
+    if mode == api.STRUCT_ONLY:
+        assert np.array_equal(cam, p.cam) and np.abs(pts - pts0).max() < 1e-7
+    else:
+        assert np.array_equal(pts, p.pts) and np.abs(cam - cam0).max() < 1e-7
+
+
+def test_ctracker_pointer_interface(ctx):
+    """The reference call site: vector<double*> R, t, pts3D with pointer identity as point id
+    (CSfM.cpp:321-343).  Storage mimics CFrame::_rot/_t and CMap::_pts3D (sparse ids)."""
+    p = synth.make_config("c1")
+    frames_rot = [p.cam[c, :3].copy() for c in range(p.n_cams)]
+    frames_t = [p.cam[c, 3:].copy() for c in range(p.n_cams)]
+    store = np.full((2 * p.n_pts + 5, 3), 123.0)  # map storage with culled (unused) slots in between
+    slot = 2 * np.arange(p.n_pts) + 1
+    store[slot] = p.pts
+    pts3D = [store[slot[j]] for j in p.pt_idx]  # the SAME row view object/memory for every observation of a point
+    K = p.K.reshape(-1, 3, 3)
+    tr = api.CTracker(0)
+    ret = tr.bundleAdjustmentStructAndPose(p.obs, p.cam_idx, K, frames_rot, frames_t, pts3D, api.CTracker.STRUCT_AND_POSE)
+    assert ret is None
+    cam0, pts0, so, _ = po.solve(p)
+    assert tr.last_summary["num_iterations"] == so["num_iterations"]
+    assert tr.last_summary["final_cost"] == pytest.approx(so["final_cost"], rel=TOL_COST)
+    assert np.abs(np.array(frames_rot) - cam0[:, :3]).max() < 1e-6 and np.abs(np.array(frames_t) - cam0[:, 3:]).max() < 1e-6
+    assert np.abs(store[slot] - pts0).max() < 1e-6
+    assert np.all(store[slot - 1] == 123.0)  # culled slots untouched
+    # default branch of the switch (CTracker.cpp:692-693): nothing happens
+    before = store.copy()
+    tr.bundleAdjustmentStructAndPose(p.obs, p.cam_idx, K, frames_rot, frames_t, pts3D, 5)
+    assert np.array_equal(store, before)
+
+
+def test_resident_problem_repeatable(ctx):
+    p = synth.make_config("c2", scale=0.1)
+    ctx.upload(p)
+    c0 = ctx.eval_resident()
+    assert c0 == pytest.approx(po.evaluate(p, want_jac=False)[2], rel=1e-12)
+    a = ctx.solve_resident(api.default_options(linear_solver=api.LINEAR_DENSE_SCHUR))
+    cam_a, pts_a = ctx.download()
+    ctx.reset()
+    assert ctx.eval_resident() == c0
+    b = ctx.solve_resident(api.default_options(linear_solver=api.LINEAR_DENSE_SCHUR))
+    assert a["num_iterations"] == b["num_iterations"] and b["final_cost"] == pytest.approx(a["final_cost"], rel=1e-12)
+    assert ctx.algorithmic_bytes("rj") == 184 * p.n_obs + 88 * p.n_cams + 24 * p.n_pts
+    assert ctx.time_kernel("rj", 3) > 0
+
+
+def test_full_size_properties_c4(ctx):
+    """BASELINE configs[3] at full size (1778 cameras x 994k points x 5M observations): properties that
+    need no CPU solve — consistency of the device-resident loop with an independent evaluation,
+    shard additivity (checksum of checksums), and agreement of the two linear solvers."""
+    p = synth.make_config("c4")
+    ctx.upload(p)
+    c_init = ctx.eval_resident()
+    s = ctx.solve_resident(api.default_options(linear_solver=api.LINEAR_PCG, max_num_iterations=3, pcg_tolerance=1e-3, pcg_max_iterations=200))
+    assert s["initial_cost"] == pytest.approx(c_init, rel=1e-12)
+    assert s["final_cost"] < 1e-3 * s["initial_cost"]
+    assert ctx.eval_resident() == pytest.approx(s["final_cost"], rel=1e-12)  # the loop's cost == a fresh evaluation at x
+    cam, pts = ctx.download()
+    # shard additivity of the cost at the solution
+    shards = synth.shard_by_point(p, 3)
+    total = 0.0
+    for sh, gids in shards:
+        sh.cam, sh.pts = cam, np.ascontiguousarray(pts[gids])
+        ctx.upload(sh)
+        total += ctx.eval_resident()
+    assert total == pytest.approx(s["final_cost"], rel=1e-12)
