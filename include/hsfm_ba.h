@@ -190,6 +190,14 @@ int hsfm_ba_schur(hsfm_ba_ctx* ctx, int64_t n_obs, const double* obs_xy, const i
                   const hsfm_ba_options* opts, double radius, double* S_dense, double* rhs,
                   double* Hcc, double* gc, double* Hpp, double* gp, double* scale);
 
+/* Dense SPD solve tap: the blocked DMMA Cholesky + triangular solves that stand in for the Eigen LLT
+ * of Ceres' DENSE_SCHUR (CTracker.cpp:574), on a caller-supplied row-major n×n matrix (lower
+ * triangle read; n even, as 6*n_cams always is).  x [n] = A^-1 b; L_out (optional) [n][n] receives the
+ * lower factor.  Returns HSFM_BA_ERR_ARG with *pivot (optional) = 1-based failing column when A is
+ * not positive definite. */
+int hsfm_ba_dense_spd_solve(hsfm_ba_ctx* ctx, int32_t n, const double* A, const double* b, double* x,
+                            double* L_out, int32_t* pivot);
+
 /* ---- device-resident problem (bench / repeated solves; inputs stay in HBM) ----------------- */
 
 /* Upload + index build (sort by point, pack tiles, camera-major permutation).  Under a

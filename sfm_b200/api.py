@@ -44,6 +44,7 @@ SYMBOLS = {
     "hsfm_ba_eval": (C.c_int, [C.c_void_p, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp, _dp, _dp, _dp]),
     "hsfm_ba_schur": (C.c_int, [C.c_void_p, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp,
                                 C.POINTER(Options), C.c_double, _dp, _dp, _dp, _dp, _dp, _dp, _dp]),
+    "hsfm_ba_dense_spd_solve": (C.c_int, [C.c_void_p, C.c_int32, _dp, _dp, _dp, _dp, _ip]),
     "hsfm_ba_problem_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp]),
     "hsfm_ba_problem_reset": (C.c_int, [C.c_void_p]),
     "hsfm_ba_problem_solve": (C.c_int, [C.c_void_p, C.POINTER(Options), C.POINTER(Summary)]),
@@ -207,6 +208,20 @@ class Context:
         if rc:
             raise BAError(rc, "hsfm_ba_schur")
         return out
+
+    def dense_spd_solve(self, A, b, want_factor=False):
+        """x = A^-1 b through the library's dense Cholesky (parity tap)."""
+        A = _f64(A); b = _f64(b)
+        n = A.shape[0]
+        x = np.empty(n)
+        L = np.zeros((n, n)) if want_factor else None
+        piv = C.c_int32(0)
+        rc = self.lib.hsfm_ba_dense_spd_solve(self.h, n, _d(A), _d(b), _d(x), _d(L), C.byref(piv))
+        if rc:
+            e = BAError(rc, "hsfm_ba_dense_spd_solve")
+            e.pivot = piv.value
+            raise e
+        return (x, np.tril(L)) if want_factor else x
 
     # -- resident problem --
     def upload(self, prob, mode=STRUCT_AND_POSE):

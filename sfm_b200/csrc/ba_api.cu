@@ -315,6 +315,39 @@ int hsfm_ba_solve_ptr(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double* obs
 
 // ---- parity taps --------------------------------------------------------------------------------
 
+int hsfm_ba_dense_spd_solve(hsfm_ba_ctx* h, int32_t n, const double* A, const double* b, double* x, double* L_out, int32_t* pivot) {
+  if (!h || n <= 0 || (n & 1) || !A || !b || !x) return HSFM_BA_ERR_ARG;
+  HSFM_CUDA(cudaSetDevice(h->c.device));
+  cudaStream_t s = h->c.stream;
+  const size_t nn = (size_t)n * n;
+  double *dA = nullptr, *db = nullptr;
+  int* dflag = nullptr;
+  if (cudaMalloc(&dA, sizeof(double) * (nn + cholesky_workspace_doubles(n))) != cudaSuccess) { cudaGetLastError(); return HSFM_BA_ERR_NOMEM; }
+  if (cudaMalloc(&db, sizeof(double) * 2 * n) != cudaSuccess || cudaMalloc(&dflag, sizeof(int)) != cudaSuccess) {
+    cudaGetLastError(); cudaFree(dA); if (db) cudaFree(db); return HSFM_BA_ERR_NOMEM;
+  }
+  int rc = 0, flag = 0;
+  int64_t launches = 0;
+  auto run = [&]() -> int {
+    HSFM_CUDA(cudaMemcpyAsync(dA, A, sizeof(double) * nn, cudaMemcpyHostToDevice, s));
+    HSFM_CUDA(cudaMemcpyAsync(db, b, sizeof(double) * n, cudaMemcpyHostToDevice, s));
+    HSFM_CUDA(cudaMemsetAsync(dflag, 0, sizeof(int), s));
+    launch_cholesky(dA, n, dA + nn, dflag, s, &launches);
+    launch_chol_solve(dA, n, dA + nn, db, s, &launches);
+    HSFM_CUDA(cudaMemcpyAsync(&flag, dflag, sizeof(int), cudaMemcpyDeviceToHost, s));
+    HSFM_CUDA(cudaMemcpyAsync(x, db, sizeof(double) * n, cudaMemcpyDeviceToHost, s));
+    if (L_out) HSFM_CUDA(cudaMemcpyAsync(L_out, dA, sizeof(double) * nn, cudaMemcpyDeviceToHost, s));
+    HSFM_CUDA(cudaStreamSynchronize(s));
+    HSFM_CUDA(cudaGetLastError());
+    return 0;
+  };
+  rc = run();
+  cudaFree(dA); cudaFree(db); cudaFree(dflag);
+  if (rc) return rc;
+  if (pivot) *pivot = flag;
+  return flag ? HSFM_BA_ERR_ARG : 0;
+}
+
 int hsfm_ba_eval(hsfm_ba_ctx* h, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx, int32_t n_cams,
                  const double* K9, const double* dist, const double* cam_rt, int64_t n_pts, const double* pts, double* residuals,
                  double* jac, double* cost) {
@@ -347,8 +380,8 @@ int hsfm_ba_schur(hsfm_ba_ctx* h, int64_t n_obs, const double* obs_xy, const int
   Problem& P = h->c.prob;
   cudaStream_t s = h->c.stream;
   const size_t n6 = 6 * (size_t)n_cams;
-  if (cudaMalloc(&P.S, sizeof(double) * std::max<size_t>(1, n6 * n6)) != cudaSuccess) { cudaGetLastError(); P.S = nullptr; return HSFM_BA_ERR_NOMEM; }
-  P.S_capacity = n6 * n6;
+  if (cudaMalloc(&P.S, sizeof(double) * (std::max<size_t>(1, n6 * n6) + cholesky_workspace_doubles((int)n6))) != cudaSuccess) { cudaGetLastError(); P.S = nullptr; return HSFM_BA_ERR_NOMEM; }
+  P.S_capacity = n6 * n6 + cholesky_workspace_doubles((int)n6);
   // scaling pass, linearisation, blocks
   launch_cam_prep(P, P.cam_x, nullptr, P.rows_x, s);
   launch_rj(P, P.rows_x, P.pts_x, nullptr, false, true, s);

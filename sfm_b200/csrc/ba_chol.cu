@@ -1,238 +1,367 @@
 // ba_chol.cu — dense FP64 Cholesky + triangular solves for the reduced camera system
 // (the Eigen LLT that Ceres' DENSE_SCHUR calls, CTracker.cpp:574).
-// Right-looking blocked factorisation of the lower triangle of a row-major n×n matrix, all
-// launches enqueued back to back on one stream (no host synchronisation; a non-positive pivot
-// raises a device flag and later kernels become no-ops on NaNs that the LM driver rejects).
+//
+// Right-looking blocked factorisation of the lower triangle of a row-major n×n matrix with
+// 128-wide panels.  Per panel three launches, enqueued back to back (no host synchronisation):
+//   1. chol_diag_kernel   one CTA factors the 128×128 diagonal block with the block held in
+//                         registers (8×8 per thread, 2-D cyclic) and also forms L11^-1 by recursive
+//                         doubling, so that
+//   2. chol_gemm<TRSM>    the panel solve  L21 = A21 L11^-T  is a GEMM, and
+//   3. chol_gemm<SYRK>    the trailing update  A22 -= L21 L21^T  (lower tiles only)
+// both run on the FP64 tensor path: 128×128 CTA tiles, K staged through shared memory with
+// cp.async double buffering, mma.sync.m8n8k4.f64 (DMMA) fragments.  tcgen05 has no FP64 kind, so
+// DMMA is the tensor-core instruction this workload can use (north_star: "tensor cores only for the
+// dense Cholesky").  The stored L11^-1 blocks also turn the two triangular solves into mat-vecs.
+// A non-positive pivot raises *fail; later kernels of the same factorisation return immediately.
 #include "ba_internal.h"
 
 namespace hsfm {
 namespace {
 
-constexpr int NB = 64;
+constexpr int NB = 128;          // panel width / tile edge
+constexpr int KC = 32;           // K chunk staged per pipeline stage
+constexpr int LDS_ = KC + 4;     // padded shared-memory row stride (doubles): conflict-free DMMA fragment loads
+constexpr int DIAG_LD = NB + 1;
 
-// Factor the kb×kb diagonal block at (k0,k0) in shared memory.
-__global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, int n, int k0, int kb, int* __restrict__ fail) {
-  __shared__ double s[NB][NB + 1];
-  const int tid = threadIdx.x;
-  for (int e = tid; e < kb * kb; e += 256) {
-    const int i = e / kb, j = e % kb;
-    s[i][j] = (j <= i) ? A[(size_t)(k0 + i) * n + k0 + j] : 0.0;
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gmem_src));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+__device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+
+// ---------------------------------------------------------------------------------------------
+// 1. diagonal block: factor + inverse
+// ---------------------------------------------------------------------------------------------
+// Thread (ty,tx) of a 16×16 grid owns elements (ty+16a, tx+16b), a,b = 0..7, in registers.
+// Step j publishes column j (unscaled, including the pivot) to shared memory; one barrier per
+// step; every thread rescales by 1/sqrt(pivot) on the fly.
+__global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, int n, int k0, int kb, double* __restrict__ Linv,
+                                                         int* __restrict__ fail) {
+  extern __shared__ double dsm[];
+  double* s = dsm;                       // [NB][DIAG_LD]  L (lower, incl. diagonal) ; Linv^T (strict upper)
+  double* tmp = dsm + NB * DIAG_LD;      // [4096]
+  double* dinv = tmp + 4096;             // [NB]
+  double* col = dinv + NB;               // [2][NB]
+  if (*fail) return;
+  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+  double r[8][8];
+#pragma unroll
+  for (int a = 0; a < 8; ++a)
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+      const int i = ty + 16 * a, j = tx + 16 * b;
+      double v = (i == j) ? 1.0 : 0.0;
+      if (i < kb && j < kb) v = (j <= i) ? A[(size_t)(k0 + i) * n + k0 + j] : 0.0;
+      r[a][b] = v;
+    }
+#pragma unroll
+  for (int jb = 0; jb < 8; ++jb) {
+    for (int jj = 0; jj < 16; ++jj) {
+      const int j = jb * 16 + jj;
+      double* cj = col + (j & 1) * NB;
+      if (tx == jj) {
+#pragma unroll
+        for (int a = jb; a < 8; ++a) cj[ty + 16 * a] = r[a][jb];
+      }
+      __syncthreads();
+      const double piv = cj[j];
+      if (!(piv > 0.0) || !isfinite(piv)) {
+        if (tid == 0) atomicExch(fail, k0 + j + 1);
+        return;  // uniform
+      }
+      const double inv_d = 1.0 / sqrt(piv);
+      double lr[8], lc[8];
+#pragma unroll
+      for (int a = jb; a < 8; ++a) lr[a] = cj[ty + 16 * a] * inv_d;
+#pragma unroll
+      for (int b = jb; b < 8; ++b) lc[b] = cj[tx + 16 * b] * inv_d;
+      if (tx == jj) {
+#pragma unroll
+        for (int a = jb; a < 8; ++a)
+          if (ty + 16 * a >= j) r[a][jb] = (ty + 16 * a == j) ? piv * inv_d : lr[a];
+      }
+#pragma unroll
+      for (int a = jb; a < 8; ++a)
+#pragma unroll
+        for (int b = jb; b < 8; ++b) {
+          const int i = ty + 16 * a, c = tx + 16 * b;
+          if (c > j && i >= c) r[a][b] -= lr[a] * lc[b];
+        }
+    }
   }
+  // L to shared (lower incl. diag; strict upper zero) and to global
+#pragma unroll
+  for (int a = 0; a < 8; ++a)
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+      const int i = ty + 16 * a, j = tx + 16 * b;
+      s[i * DIAG_LD + j] = (j <= i) ? r[a][b] : 0.0;
+      if (i < kb && j <= i && j < kb) A[(size_t)(k0 + i) * n + k0 + j] = r[a][b];
+    }
   __syncthreads();
-  for (int j = 0; j < kb; ++j) {
-    const double djj = s[j][j];
-    if (!(djj > 0.0) || !isfinite(djj)) {
-      if (tid == 0) atomicExch(fail, k0 + j + 1);
-      return;  // uniform: every thread reads the same s[j][j]
+  if (tid < NB) dinv[tid] = 1.0 / s[tid * DIAG_LD + tid];
+  __syncthreads();
+  // Linv by recursive doubling: inv([[A,0],[C,B]]) = [[A^-1,0],[-B^-1 C A^-1, B^-1]].
+  // Linv(i,j), i>j is kept transposed in the strict upper triangle: s[j][i]; Linv(i,i) = dinv[i].
+  for (int h = 1; h < NB; h <<= 1) {
+    const int total = NB * h / 2;  // (NB/(2h)) blocks × h×h
+    // stage 1: T(k,j) = sum_{l in A, l>=j} L(k,l) Linv(l,j)   k in B, j in A
+    for (int e = tid; e < total; e += 256) {
+      const int blk = e / (h * h), rem = e - blk * h * h;
+      const int kk = rem / h, jj = rem - kk * h;
+      const int o = blk * 2 * h;
+      const int k = o + h + kk, j = o + jj;
+      double acc = s[k * DIAG_LD + j] * dinv[j];
+      for (int l = j + 1; l < o + h; ++l) acc += s[k * DIAG_LD + l] * s[j * DIAG_LD + l];
+      tmp[e] = acc;
     }
-    const double d = sqrt(djj);
-    const double inv = 1.0 / d;
     __syncthreads();
-    if (tid == 0) s[j][j] = d;
-    for (int i = j + 1 + tid; i < kb; i += 256) s[i][j] *= inv;
-    __syncthreads();
-    // trailing update of the lower triangle: s[i][k] -= s[i][j] s[k][j], j < k <= i
-    const int m = kb - j - 1;
-    for (int e = tid; e < m * m; e += 256) {
-      const int i = j + 1 + e / m, k = j + 1 + e % m;
-      if (k <= i) s[i][k] -= s[i][j] * s[k][j];
+    // stage 2: X(i,j) = -sum_{k in B, k<=i} Linv(i,k) T(k,j)
+    for (int e = tid; e < total; e += 256) {
+      const int blk = e / (h * h), rem = e - blk * h * h;
+      const int ii = rem / h, jj = rem - ii * h;
+      const int o = blk * 2 * h;
+      const int i = o + h + ii, j = o + jj;
+      const double* T = tmp + blk * h * h;
+      double acc = dinv[i] * T[ii * h + jj];
+      for (int kk = 0; kk < ii; ++kk) acc += s[(o + h + kk) * DIAG_LD + i] * T[kk * h + jj];
+      s[j * DIAG_LD + i] = -acc;
     }
     __syncthreads();
   }
-  for (int e = tid; e < kb * kb; e += 256) {
-    const int i = e / kb, j = e % kb;
-    if (j <= i) A[(size_t)(k0 + i) * n + k0 + j] = s[i][j];
+  for (int e = tid; e < NB * NB; e += 256) {
+    const int i = e >> 7, j = e & 127;
+    Linv[e] = (i > j) ? s[j * DIAG_LD + i] : (i == j ? dinv[i] : 0.0);
+  }
+}
+constexpr int kDiagSmem = (NB * DIAG_LD + 4096 + NB + 2 * NB) * (int)sizeof(double);
+
+// ---------------------------------------------------------------------------------------------
+// 2./3. 128×128 tile of  C = A B^T  on DMMA.  A: rows [ra, ra+128) × K columns at column offset
+// ka of matrix MA (leading dimension lda); B likewise from MB.  K = 128 in four chunks of 32,
+// double-buffered with cp.async.  8 warps as 2×4, each 64×32 = 8×4 DMMA tiles, k-step 4.
+//   MODE 0 (TRSM): A = A21 rows, B = L11^-1 (row-major 128×128)  →  C overwrites the A tile.
+//   MODE 1 (SYRK): A = L21 rows of tile bi, B = L21 rows of tile bj  →  S[bi,bj] -= C.
+// ---------------------------------------------------------------------------------------------
+struct GemmSmem {
+  double a[2][NB][LDS_];
+  double b[2][NB][LDS_];
+};
+constexpr int kGemmSmem = (int)sizeof(GemmSmem);
+
+__device__ __forceinline__ void load_tile_async(double (*dst)[LDS_], const double* __restrict__ src, int ld, int row0, int rows_valid,
+                                                int col0) {
+  // 128 rows × 32 doubles = 2048 chunks of 16 B; 256 threads × 8
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    const int e = threadIdx.x + 256 * q;
+    const int row = e >> 4, ch = e & 15;
+    double* d = &dst[row][ch * 2];
+    if (row < rows_valid) cp_async16(d, src + (size_t)(row0 + row) * ld + col0 + ch * 2);
+    else { d[0] = 0.0; d[1] = 0.0; }
   }
 }
 
-// Panel below the diagonal block: X L11^T = A21  =>  row-wise forward substitution.
-__global__ void __launch_bounds__(NB) chol_trsm_kernel(double* __restrict__ A, int n, int k0, int kb, const int* __restrict__ fail) {
-  extern __shared__ double dyn_sm[];
-  double (*sL)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(dyn_sm);
-  double (*sA)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(dyn_sm + NB * (NB + 1));
+template <int MODE>
+__global__ void __launch_bounds__(256) chol_gemm_kernel(double* __restrict__ S, int n, int k0, const double* __restrict__ Linv,
+                                                        const int* __restrict__ fail) {
+  extern __shared__ __align__(16) unsigned char gsm_raw[];
+  GemmSmem& sm = *reinterpret_cast<GemmSmem*>(gsm_raw);
   if (*fail) return;
-  const int tid = threadIdx.x;
-  const int r0 = k0 + kb + blockIdx.x * NB;
-  const int rows = min(NB, n - r0);
-  for (int e = tid; e < kb * kb; e += NB) {
-    const int i = e / kb, j = e % kb;
-    sL[i][j] = A[(size_t)(k0 + i) * n + k0 + j];
+  const int base = k0 + NB;
+  int bi, bj;
+  if (MODE == 0) {
+    bi = blockIdx.x; bj = 0;
+  } else {
+    const int t = blockIdx.x;
+    bi = (int)((sqrt(8.0 * (double)t + 1.0) - 1.0) * 0.5);
+    while ((bi + 1) * (bi + 2) / 2 <= t) ++bi;
+    while (bi * (bi + 1) / 2 > t) --bi;
+    bj = t - bi * (bi + 1) / 2;
   }
-  for (int e = tid; e < rows * kb; e += NB) {
-    const int i = e / kb, j = e % kb;
-    sA[i][j] = A[(size_t)(r0 + i) * n + k0 + j];
-  }
-  __syncthreads();
-  if (tid < rows) {
-    for (int j = 0; j < kb; ++j) {
-      double sacc = sA[tid][j];
-      for (int k = 0; k < j; ++k) sacc -= sA[tid][k] * sL[j][k];
-      sA[tid][j] = sacc / sL[j][j];
-    }
-  }
-  __syncthreads();
-  for (int e = tid; e < rows * kb; e += NB) {
-    const int i = e / kb, j = e % kb;
-    A[(size_t)(r0 + i) * n + k0 + j] = sA[i][j];
-  }
-}
-
-// Trailing update C[bi,bj] -= P[bi] P[bj]^T over lower tiles (bi >= bj) of 64×64, panel width kb.
-__global__ void __launch_bounds__(256) chol_syrk_kernel(double* __restrict__ A, int n, int k0, int kb, const int* __restrict__ fail) {
-  __shared__ double sA[32][NB + 1];  // [k][row of tile bi]
-  __shared__ double sB[32][NB + 1];  // [k][row of tile bj]
-  if (*fail) return;
-  // decode linear lower-triangular tile index
-  const int t = blockIdx.x;
-  int bi = (int)((sqrt(8.0 * (double)t + 1.0) - 1.0) * 0.5);
-  while ((bi + 1) * (bi + 2) / 2 <= t) ++bi;
-  while (bi * (bi + 1) / 2 > t) --bi;
-  const int bj = t - bi * (bi + 1) / 2;
-  const int base = k0 + kb;
   const int ri = base + bi * NB, rj = base + bj * NB;
-  const int ni = min(NB, n - ri), nj = min(NB, n - rj);
-  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-  double acc[4][4];
+  const int ni = min(NB, n - ri), nj = (MODE == 0) ? NB : min(NB, n - rj);
+  const double* Bsrc = (MODE == 0) ? Linv : S;
+  const int ldb = (MODE == 0) ? NB : n;
+  const int rb0 = (MODE == 0) ? 0 : rj;
+  const int kb0 = (MODE == 0) ? 0 : k0;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int wr = warp >> 2, wc = warp & 3;  // 2 × 4 warps
+  const int fr = lane >> 2, fk = lane & 3;
+  double acc[8][4][2];
 #pragma unroll
-  for (int a = 0; a < 4; ++a)
+  for (int a = 0; a < 8; ++a)
 #pragma unroll
-    for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
-  for (int kk = 0; kk < kb; kk += 32) {
-    const int kc = min(32, kb - kk);
-    for (int e = threadIdx.x; e < NB * 32; e += 256) {
-      const int row = e / 32, k = e % 32;
-      sA[k][row] = (row < ni && k < kc) ? A[(size_t)(ri + row) * n + k0 + kk + k] : 0.0;
-      sB[k][row] = (row < nj && k < kc) ? A[(size_t)(rj + row) * n + k0 + kk + k] : 0.0;
+    for (int b = 0; b < 4; ++b) { acc[a][b][0] = 0.0; acc[a][b][1] = 0.0; }
+
+  load_tile_async(sm.a[0], S, n, ri, ni, k0);
+  load_tile_async(sm.b[0], Bsrc, ldb, rb0, nj, kb0);
+  cp_async_commit();
+#pragma unroll 1
+  for (int ch = 0; ch < NB / KC; ++ch) {
+    const int cur = ch & 1;
+    if (ch + 1 < NB / KC) {
+      load_tile_async(sm.a[cur ^ 1], S, n, ri, ni, k0 + (ch + 1) * KC);
+      load_tile_async(sm.b[cur ^ 1], Bsrc, ldb, rb0, nj, kb0 + (ch + 1) * KC);
+      cp_async_commit();
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
     }
     __syncthreads();
-#pragma unroll 8
-    for (int k = 0; k < 32; ++k) {
-      double a[4], b[4];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) { a[q] = sA[k][ty * 4 + q]; b[q] = sB[k][tx * 4 + q]; }
+    for (int ks = 0; ks < KC / 4; ++ks) {
+      double af[8], bf[4];
 #pragma unroll
-      for (int p = 0; p < 4; ++p)
+      for (int a = 0; a < 8; ++a) af[a] = sm.a[cur][wr * 64 + a * 8 + fr][ks * 4 + fk];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) acc[p][q] += a[p] * b[q];
+      for (int b = 0; b < 4; ++b) bf[b] = sm.b[cur][wc * 32 + b * 8 + fr][ks * 4 + fk];
+#pragma unroll
+      for (int a = 0; a < 8; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
     }
     __syncthreads();
   }
+  // epilogue: lane holds C[row = fr][col = 2*fk, 2*fk+1] of each 8×8 tile
 #pragma unroll
-  for (int p = 0; p < 4; ++p) {
-    const int i = ty * 4 + p;
-    if (i >= ni) continue;
+  for (int a = 0; a < 8; ++a) {
+    const int row = wr * 64 + a * 8 + fr;
+    if (row >= ni) continue;
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int j = tx * 4 + q;
-      if (j >= nj) continue;
-      if (bi == bj && j > i) continue;
-      A[(size_t)(ri + i) * n + rj + j] -= acc[p][q];
+    for (int b = 0; b < 4; ++b) {
+      const int col = wc * 32 + b * 8 + 2 * fk;
+      if (MODE == 0) {
+        double2* dst = reinterpret_cast<double2*>(S + (size_t)(ri + row) * n + k0 + col);
+        *dst = make_double2(acc[a][b][0], acc[a][b][1]);
+      } else {
+        if (col >= nj) continue;
+        if (bi == bj && col > row + 1) continue;  // strictly above the diagonal pair: never read
+        double2* dst = reinterpret_cast<double2*>(S + (size_t)(ri + row) * n + rj + col);
+        double2 c = *dst;
+        c.x -= acc[a][b][0];
+        c.y -= acc[a][b][1];
+        *dst = c;
+      }
     }
   }
 }
 
-// Forward substitution step for block k0: every CTA solves the kb×kb diagonal system from the
-// (read-only in this launch) right-hand side, CTA 0 publishes x_k, CTA r>=1 updates 64 rows below.
-__global__ void __launch_bounds__(NB) trsv_fwd_kernel(const double* __restrict__ L, int n, int k0, int kb, double* __restrict__ b,
-                                                     double* __restrict__ x) {
-  __shared__ double sL[NB][NB + 1];
+// ---------------------------------------------------------------------------------------------
+// Triangular solves with the stored L11^-1 blocks: per panel one launch; every CTA forms
+// x_k = L11^-1 b_k (resp. L11^-T y_k) redundantly — a 128×128 mat-vec — CTA 0 publishes it and
+// CTA r >= 1 folds it into 128 rows below (resp. 128 columns to the left).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) trsv_fwd_kernel(const double* __restrict__ L, int n, int k0, int kb, const double* __restrict__ Linv,
+                                                      double* __restrict__ b, double* __restrict__ x) {
+  __shared__ double sb[NB];
   __shared__ double sx[NB];
-  const int tid = threadIdx.x;
-  for (int e = tid; e < kb * kb; e += NB) {
-    const int i = e / kb, j = e % kb;
-    sL[i][j] = L[(size_t)(k0 + i) * n + k0 + j];
-  }
-  if (tid < kb) sx[tid] = b[k0 + tid];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  sb[tid] = (tid < kb) ? b[k0 + tid] : 0.0;
   __syncthreads();
-  for (int j = 0; j < kb; ++j) {
-    if (tid == j) sx[j] = sx[j] / sL[j][j];
-    __syncthreads();
-    if (tid > j && tid < kb) sx[tid] -= sL[tid][j] * sx[j];
-    __syncthreads();
+  for (int rr = 0; rr < 32; ++rr) {
+    const int i = warp * 32 + rr;
+    const double* Li = Linv + (size_t)i * NB;
+    double acc = 0.0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) acc += Li[lane + 32 * q] * sb[lane + 32 * q];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+    if (lane == 0) sx[i] = acc;
   }
+  __syncthreads();
   if (blockIdx.x == 0) {
     if (tid < kb) x[k0 + tid] = sx[tid];
     return;
   }
-  const int row = k0 + kb + (blockIdx.x - 1) * NB + tid;
-  if (row < n) {
+  const int r0 = k0 + NB + (blockIdx.x - 1) * NB;
+  for (int rr = 0; rr < 32; ++rr) {
+    const int row = r0 + warp * 32 + rr;
+    if (row >= n) break;
     const double* Lr = L + (size_t)row * n + k0;
-    double s = 0.0;
-    for (int k = 0; k < kb; ++k) s += Lr[k] * sx[k];
-    b[row] -= s;
+    double acc = 0.0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) acc += Lr[lane + 32 * q] * sx[lane + 32 * q];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+    if (lane == 0) b[row] -= acc;
   }
 }
 
-// Backward substitution step (L^T x = y) for block k0, processed from the last block upwards.
-__global__ void __launch_bounds__(NB) trsv_bwd_kernel(const double* __restrict__ L, int n, int k0, int kb, double* __restrict__ y,
-                                                     double* __restrict__ x) {
-  __shared__ double sL[NB][NB + 1];
+__global__ void __launch_bounds__(128) trsv_bwd_kernel(const double* __restrict__ L, int n, int k0, int kb, const double* __restrict__ Linv,
+                                                      double* __restrict__ y, double* __restrict__ x) {
+  __shared__ double sy[NB];
   __shared__ double sx[NB];
   const int tid = threadIdx.x;
-  for (int e = tid; e < kb * kb; e += NB) {
-    const int i = e / kb, j = e % kb;
-    sL[i][j] = L[(size_t)(k0 + i) * n + k0 + j];
-  }
-  if (tid < kb) sx[tid] = y[k0 + tid];
+  sy[tid] = (tid < kb) ? y[k0 + tid] : 0.0;
   __syncthreads();
-  for (int j = kb - 1; j >= 0; --j) {
-    if (tid == j) sx[j] = sx[j] / sL[j][j];
-    __syncthreads();
-    if (tid < j) sx[tid] -= sL[j][tid] * sx[j];
-    __syncthreads();
+  {
+    double acc = 0.0;
+    for (int i = tid; i < NB; ++i) acc += Linv[(size_t)i * NB + tid] * sy[i];
+    sx[tid] = acc;
   }
+  __syncthreads();
   if (blockIdx.x == 0) {
     if (tid < kb) x[k0 + tid] = sx[tid];
     return;
   }
-  const int col = (blockIdx.x - 1) * NB + tid;  // rows above the block: j < k0
+  const int col = (blockIdx.x - 1) * NB + tid;
   if (col < k0) {
-    double s = 0.0;
-    for (int i = 0; i < kb; ++i) s += L[(size_t)(k0 + i) * n + col] * sx[i];
-    y[col] -= s;
+    double acc = 0.0;
+    for (int i = 0; i < kb; ++i) acc += L[(size_t)(k0 + i) * n + col] * sx[i];
+    y[col] -= acc;
   }
 }
 
 }  // namespace
 
-void launch_cholesky(double* S, int n, int* fail_flag, cudaStream_t s, int64_t* launches) {
-  constexpr int kTrsmSmem = 2 * NB * (NB + 1) * (int)sizeof(double);
+size_t cholesky_workspace_doubles(int n) { return (size_t)((n + NB - 1) / NB) * NB * NB; }
+
+void launch_cholesky(double* S, int n, double* Linv_ws, int* fail_flag, cudaStream_t s, int64_t* launches) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(chol_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTrsmSmem);
+    cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDiagSmem);
+    cudaFuncSetAttribute(chol_gemm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem);
+    cudaFuncSetAttribute(chol_gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem);
     attr_set = true;
   }
-  for (int k0 = 0; k0 < n; k0 += NB) {
+  int panel = 0;
+  for (int k0 = 0; k0 < n; k0 += NB, ++panel) {
     const int kb = min(NB, n - k0);
-    chol_diag_kernel<<<1, 256, 0, s>>>(S, n, k0, kb, fail_flag);
+    double* Linv = Linv_ws + (size_t)panel * NB * NB;
+    chol_diag_kernel<<<1, 256, kDiagSmem, s>>>(S, n, k0, kb, Linv, fail_flag);
     ++*launches;
     const int m = n - (k0 + kb);
     if (m <= 0) break;
     const int rb = (m + NB - 1) / NB;
-    chol_trsm_kernel<<<rb, NB, kTrsmSmem, s>>>(S, n, k0, kb, fail_flag);
-    chol_syrk_kernel<<<rb * (rb + 1) / 2, 256, 0, s>>>(S, n, k0, kb, fail_flag);
+    chol_gemm_kernel<0><<<rb, 256, kGemmSmem, s>>>(S, n, k0, Linv, fail_flag);
+    chol_gemm_kernel<1><<<rb * (rb + 1) / 2, 256, kGemmSmem, s>>>(S, n, k0, Linv, fail_flag);
     *launches += 2;
   }
 }
 
-// Solves S y = b with the factor from launch_cholesky; b is overwritten by the solution.
-void launch_chol_solve(const double* L, int n, double* b, cudaStream_t s, int64_t* launches) {
-  // forward: L w = b  (w written into b's storage through x == b is unsafe; use in-place carefully:
-  // x_k is published into b[k0..] by CTA 0 only after it has been read into shared memory by every
-  // CTA of the same launch?  No such guarantee — so publish into a scratch tail kept after b.)
-  // The caller provides b with room for 2n doubles: [0,n) rhs/solution, [n,2n) scratch.
-  double* x = b + n;
-  for (int k0 = 0; k0 < n; k0 += NB) {
+// Solves S y = b with the factor from launch_cholesky.  b holds 2n doubles: [0,n) right-hand side
+// in / solution out, [n,2n) scratch for the intermediate vector.
+void launch_chol_solve(const double* L, int n, const double* Linv_ws, double* b, cudaStream_t s, int64_t* launches) {
+  double* w = b + n;
+  int panel = 0;
+  for (int k0 = 0; k0 < n; k0 += NB, ++panel) {
     const int kb = min(NB, n - k0);
     const int m = n - (k0 + kb);
-    trsv_fwd_kernel<<<1 + (m + NB - 1) / NB, NB, 0, s>>>(L, n, k0, kb, b, x);
+    trsv_fwd_kernel<<<1 + (m + NB - 1) / NB, NB, 0, s>>>(L, n, k0, kb, Linv_ws + (size_t)panel * NB * NB, b, w);
     ++*launches;
   }
-  // backward: L^T y = w, w lives in x; result published back into b
-  const int last = ((n - 1) / NB) * NB;
-  for (int k0 = last; k0 >= 0; k0 -= NB) {
+  for (--panel; panel >= 0; --panel) {
+    const int k0 = panel * NB;
     const int kb = min(NB, n - k0);
-    trsv_bwd_kernel<<<1 + (k0 + NB - 1) / NB, NB, 0, s>>>(L, n, k0, kb, x, b);
+    trsv_bwd_kernel<<<1 + (k0 + NB - 1) / NB, NB, 0, s>>>(L, n, k0, kb, Linv_ws + (size_t)panel * NB * NB, w, b);
     ++*launches;
   }
 }

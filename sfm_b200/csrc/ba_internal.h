@@ -137,8 +137,9 @@ void launch_mirror_lower(Problem& P, cudaStream_t s);   // S upper <- lower (par
 // ---- dense Cholesky (ba_chol.cu) ----
 // In-place lower Cholesky of row-major n×n S (lower triangle read/written); *fail_flag set to
 // non-zero on a non-positive pivot.  Then solve S y = b in place in b.
-void launch_cholesky(double* S, int n, int* fail_flag, cudaStream_t s, int64_t* launches);
-void launch_chol_solve(const double* L, int n, double* b, cudaStream_t s, int64_t* launches);
+size_t cholesky_workspace_doubles(int n);  // room for the L11^-1 blocks, one 128×128 per panel
+void launch_cholesky(double* S, int n, double* Linv_ws, int* fail_flag, cudaStream_t s, int64_t* launches);
+void launch_chol_solve(const double* L, int n, const double* Linv_ws, double* b, cudaStream_t s, int64_t* launches);
 
 // ---- LM driver (ba_solver.cu) ----
 struct Ctx {

@@ -78,9 +78,9 @@ struct Driver {
           chk(ctx.comm.allreduce_sum(P.S, (size_t)n6 * n6, s));
           chk(ctx.comm.allreduce_sum(P.rhs, n6, s));
         }
-        launch_cholesky(P.S, n6, P.flags + F_CHOL_FAIL, s, &P.launches);
+        launch_cholesky(P.S, n6, P.S + (size_t)n6 * n6, P.flags + F_CHOL_FAIL, s, &P.launches);
         HSFM_CUDA(cudaMemcpyAsync(P.yc, P.rhs, sizeof(double) * n6, cudaMemcpyDeviceToDevice, s));
-        launch_chol_solve(P.S, n6, P.yc, s, &P.launches);
+        launch_chol_solve(P.S, n6, P.S + (size_t)n6 * n6, P.yc, s, &P.launches);
       } else {
         launch_cam_major(P, P.rows_x, P.pts_x, P.scale_p, 1, s);
         if (multi()) chk(ctx.comm.allreduce_sum(P.E, 21 * (size_t)P.n_cams, s));
@@ -143,7 +143,7 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
     else if (o.linear_solver == HSFM_BA_LINEAR_PCG) D.dense = false;
     else D.dense = P.n_cams <= o.dense_max_cams;
     if (D.dense) {
-      const size_t need = (size_t)n6 * n6;
+      const size_t need = (size_t)n6 * n6 + cholesky_workspace_doubles(n6);
       if (P.S_capacity < need) {
         if (P.S) cudaFree(P.S);
         P.S = nullptr; P.S_capacity = 0;
