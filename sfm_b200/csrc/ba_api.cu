@@ -97,6 +97,7 @@ int hsfm_ba_create(hsfm_ba_ctx** out, int device_id) {
   cudaError_t e = cudaStreamCreateWithFlags(&h->c.own_stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { delete h; return 1000 + (int)e; }
   h->c.stream = h->c.own_stream;
+  { int rc2 = h->c.chol_aux.init(); if (rc2) { cudaStreamDestroy(h->c.own_stream); delete h; return rc2; } }
   *out = h;
   return 0;
 }
@@ -108,6 +109,7 @@ void hsfm_ba_destroy(hsfm_ba_ctx* h) {
   h->c.prob.release();
   if (h->c.prob.S) { cudaFree(h->c.prob.S); h->c.prob.S = nullptr; }
   h->c.comm.destroy();
+  h->c.chol_aux.destroy();
   if (h->c.own_stream) cudaStreamDestroy(h->c.own_stream);
   delete h;
 }
@@ -332,7 +334,7 @@ int hsfm_ba_dense_spd_solve(hsfm_ba_ctx* h, int32_t n, const double* A, const do
     HSFM_CUDA(cudaMemcpyAsync(dA, A, sizeof(double) * nn, cudaMemcpyHostToDevice, s));
     HSFM_CUDA(cudaMemcpyAsync(db, b, sizeof(double) * n, cudaMemcpyHostToDevice, s));
     HSFM_CUDA(cudaMemsetAsync(dflag, 0, sizeof(int), s));
-    launch_cholesky(dA, n, dA + nn, dflag, s, &launches);
+    launch_cholesky(dA, n, dA + nn, dflag, s, &h->c.chol_aux, &launches);
     launch_chol_solve(dA, n, dA + nn, db, s, &launches);
     HSFM_CUDA(cudaMemcpyAsync(&flag, dflag, sizeof(int), cudaMemcpyDeviceToHost, s));
     HSFM_CUDA(cudaMemcpyAsync(x, db, sizeof(double) * n, cudaMemcpyDeviceToHost, s));

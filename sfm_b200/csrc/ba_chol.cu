@@ -143,24 +143,33 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
 constexpr int kDiagSmem = (NB * DIAG_LD + 4096 + NB + 2 * NB) * (int)sizeof(double);
 
 // ---------------------------------------------------------------------------------------------
-// 2./3. 128×128 tile of  C = A B^T  on DMMA.  A: rows [ra, ra+128) × K columns at column offset
-// ka of matrix MA (leading dimension lda); B likewise from MB.  K = 128 in four chunks of 32,
-// double-buffered with cp.async.  8 warps as 2×4, each 64×32 = 8×4 DMMA tiles, k-step 4.
-//   MODE 0 (TRSM): A = A21 rows, B = L11^-1 (row-major 128×128)  →  C overwrites the A tile.
-//   MODE 1 (SYRK): A = L21 rows of tile bi, B = L21 rows of tile bj  →  S[bi,bj] -= C.
+// 2./3. 128×64 tile of  C = A B^T  on DMMA.  K = 128 in four chunks of 32, double-buffered with
+// cp.async.  4 warps as 2×2, each 64×32 = 8×4 DMMA tiles (m8n8k4), so 64 FP64 accumulators per
+// lane.  110 KB of shared memory and 128 threads per CTA => two CTAs per SM, whose prologues
+// (first cp.async chunk, C prefetch) and epilogues hide behind each other's main loops.
+//   MODE 0 (TRSM): A = A21 rows, B = 64 rows of L11^-1  →  C goes to a packed scratch panel
+//                  (the two column halves of a row tile are produced by different CTAs that both
+//                  read the whole row tile, so the result cannot overwrite A21 in place);
+//                  chol_panel_copy_kernel then moves it over A21.
+//   MODE 1 (SYRK): A = L21 rows of row tile bi, B = L21 rows of 64-column block bj
+//                  →  S[bi,bj] -= C.  Accumulators start at -C (prefetched while the first chunk is
+//                  in flight), the main loop adds A B^T, the epilogue stores the negation: no
+//                  read-modify-write at the end.
 // ---------------------------------------------------------------------------------------------
+constexpr int TN = 64;  // tile columns
 struct GemmSmem {
   double a[2][NB][LDS_];
-  double b[2][NB][LDS_];
+  double b[2][TN][LDS_];
 };
 constexpr int kGemmSmem = (int)sizeof(GemmSmem);
 
+template <int ROWS>
 __device__ __forceinline__ void load_tile_async(double (*dst)[LDS_], const double* __restrict__ src, int ld, int row0, int rows_valid,
                                                 int col0) {
-  // 128 rows × 32 doubles = 2048 chunks of 16 B; 256 threads × 8
+  // ROWS rows × 32 doubles = ROWS*16 chunks of 16 B over 128 threads
 #pragma unroll
-  for (int q = 0; q < 8; ++q) {
-    const int e = threadIdx.x + 256 * q;
+  for (int q = 0; q < ROWS / 8; ++q) {
+    const int e = threadIdx.x + 128 * q;
     const int row = e >> 4, ch = e & 15;
     double* d = &dst[row][ch * 2];
     if (row < rows_valid) cp_async16(d, src + (size_t)(row0 + row) * ld + col0 + ch * 2);
@@ -168,48 +177,67 @@ __device__ __forceinline__ void load_tile_async(double (*dst)[LDS_], const doubl
   }
 }
 
+// Tile selection of a SYRK launch:
+//   col_first >= 0 : row tiles row_first.., column blocks {col_first, col_first+1}   (2 CTAs per row tile)
+//   col_first <  0 : every lower tile whose column block is >= 2 (the first 128 columns of the
+//                    trailing matrix belong to the look-ahead launch)
 template <int MODE>
-__global__ void __launch_bounds__(256) chol_gemm_kernel(double* __restrict__ S, int n, int k0, const double* __restrict__ Linv,
-                                                        const int* __restrict__ fail) {
+__global__ void __launch_bounds__(128, 2) chol_gemm_kernel(double* __restrict__ S, int n, int k0, const double* __restrict__ Linv,
+                                                           double* __restrict__ panel_out, int row_first, int col_first,
+                                                           const int* __restrict__ fail) {
   extern __shared__ __align__(16) unsigned char gsm_raw[];
   GemmSmem& sm = *reinterpret_cast<GemmSmem*>(gsm_raw);
   if (*fail) return;
   const int base = k0 + NB;
-  int bi, bj;
+  int bi, bj;  // row tile (128 rows), column block (64 columns)
   if (MODE == 0) {
-    bi = blockIdx.x; bj = 0;
+    bi = blockIdx.x >> 1; bj = blockIdx.x & 1;
+  } else if (col_first >= 0) {
+    bi = row_first + (blockIdx.x >> 1); bj = col_first + (blockIdx.x & 1);
   } else {
+    // row tile bi (>= 1) owns column blocks 2 .. 2*bi+1 → 2*bi tiles; tiles before row bi: bi*(bi-1)
     const int t = blockIdx.x;
-    bi = (int)((sqrt(8.0 * (double)t + 1.0) - 1.0) * 0.5);
-    while ((bi + 1) * (bi + 2) / 2 <= t) ++bi;
-    while (bi * (bi + 1) / 2 > t) --bi;
-    bj = t - bi * (bi + 1) / 2;
+    bi = (int)((1.0 + sqrt(1.0 + 4.0 * (double)t)) * 0.5);
+    while (bi * (bi + 1) <= t) ++bi;
+    while (bi * (bi - 1) > t) --bi;
+    bj = 2 + (t - bi * (bi - 1));
   }
-  const int ri = base + bi * NB, rj = base + bj * NB;
-  const int ni = min(NB, n - ri), nj = (MODE == 0) ? NB : min(NB, n - rj);
+  const int ri = base + bi * NB;
+  const int ni = min(NB, n - ri);
+  const int rj = (MODE == 0) ? bj * TN : base + bj * TN;  // B rows: of Linv, or of S
+  const int nj = (MODE == 0) ? TN : min(TN, n - rj);
   const double* Bsrc = (MODE == 0) ? Linv : S;
   const int ldb = (MODE == 0) ? NB : n;
-  const int rb0 = (MODE == 0) ? 0 : rj;
   const int kb0 = (MODE == 0) ? 0 : k0;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int wr = warp >> 2, wc = warp & 3;  // 2 × 4 warps
+  const int wr = warp >> 1, wc = warp & 1;  // 2 × 2 warps, 64 × 32 each
   const int fr = lane >> 2, fk = lane & 3;
+
+  load_tile_async<NB>(sm.a[0], S, n, ri, ni, k0);
+  load_tile_async<TN>(sm.b[0], Bsrc, ldb, rj, nj, kb0);
+  cp_async_commit();
+
   double acc[8][4][2];
 #pragma unroll
   for (int a = 0; a < 8; ++a)
 #pragma unroll
-    for (int b = 0; b < 4; ++b) { acc[a][b][0] = 0.0; acc[a][b][1] = 0.0; }
-
-  load_tile_async(sm.a[0], S, n, ri, ni, k0);
-  load_tile_async(sm.b[0], Bsrc, ldb, rb0, nj, kb0);
-  cp_async_commit();
+    for (int b = 0; b < 4; ++b) {
+      acc[a][b][0] = 0.0; acc[a][b][1] = 0.0;
+      if (MODE == 1) {
+        const int row = wr * 64 + a * 8 + fr, col = wc * 32 + b * 8 + 2 * fk;
+        if (row < ni && col < nj) {
+          const double2 c = *reinterpret_cast<const double2*>(S + (size_t)(ri + row) * n + rj + col);
+          acc[a][b][0] = -c.x; acc[a][b][1] = -c.y;
+        }
+      }
+    }
 #pragma unroll 1
   for (int ch = 0; ch < NB / KC; ++ch) {
     const int cur = ch & 1;
     if (ch + 1 < NB / KC) {
-      load_tile_async(sm.a[cur ^ 1], S, n, ri, ni, k0 + (ch + 1) * KC);
-      load_tile_async(sm.b[cur ^ 1], Bsrc, ldb, rb0, nj, kb0 + (ch + 1) * KC);
+      load_tile_async<NB>(sm.a[cur ^ 1], S, n, ri, ni, k0 + (ch + 1) * KC);
+      load_tile_async<TN>(sm.b[cur ^ 1], Bsrc, ldb, rj, nj, kb0 + (ch + 1) * KC);
       cp_async_commit();
       cp_async_wait<1>();
     } else {
@@ -239,42 +267,67 @@ __global__ void __launch_bounds__(256) chol_gemm_kernel(double* __restrict__ S, 
     for (int b = 0; b < 4; ++b) {
       const int col = wc * 32 + b * 8 + 2 * fk;
       if (MODE == 0) {
-        double2* dst = reinterpret_cast<double2*>(S + (size_t)(ri + row) * n + k0 + col);
+        double2* dst = reinterpret_cast<double2*>(panel_out + (size_t)(bi * NB + row) * NB + bj * TN + col);
         *dst = make_double2(acc[a][b][0], acc[a][b][1]);
       } else {
         if (col >= nj) continue;
-        if (bi == bj && col > row + 1) continue;  // strictly above the diagonal pair: never read
         double2* dst = reinterpret_cast<double2*>(S + (size_t)(ri + row) * n + rj + col);
-        double2 c = *dst;
-        c.x -= acc[a][b][0];
-        c.y -= acc[a][b][1];
-        *dst = c;
+        *dst = make_double2(-acc[a][b][0], -acc[a][b][1]);
       }
     }
   }
 }
 
+// move the packed scratch panel (m × 128) over A21
+__global__ void __launch_bounds__(256) chol_panel_copy_kernel(double* __restrict__ S, int n, int k0, int m, const double* __restrict__ panel,
+                                                               const int* __restrict__ fail) {
+  if (*fail) return;
+  const size_t e = (size_t)blockIdx.x * 256 + threadIdx.x;  // double2 index
+  if (e >= (size_t)m * (NB / 2)) return;
+  const int row = (int)(e / (NB / 2)), c2 = (int)(e % (NB / 2));
+  const double2 v = reinterpret_cast<const double2*>(panel)[e];
+  *reinterpret_cast<double2*>(S + (size_t)(k0 + NB + row) * n + k0 + 2 * c2) = v;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Triangular solves with the stored L11^-1 blocks: per panel one launch; every CTA forms
 // x_k = L11^-1 b_k (resp. L11^-T y_k) redundantly — a 128×128 mat-vec — CTA 0 publishes it and
-// CTA r >= 1 folds it into 128 rows below (resp. 128 columns to the left).
+// CTA r >= 1 folds it into 128 rows below (resp. 128 columns to the left).  Loads are issued four
+// rows (eight for the column-oriented backward pass) at a time so their latencies overlap.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) trsv_fwd_kernel(const double* __restrict__ L, int n, int k0, int kb, const double* __restrict__ Linv,
+__device__ __forceinline__ void warp_rows_dot4(const double* __restrict__ M, size_t ld, int row, int nrows, const double* __restrict__ sv,
+                                               int lane, double out[4]) {
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
+  double v[4][4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) v[r][q] = (r < nrows) ? M[(size_t)(row + r) * ld + lane + 32 * q] : 0.0;
+#pragma unroll
+  for (int r = 0; r < 4; ++r)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) acc[r] += v[r][q] * sv[lane + 32 * q];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc[r] += __shfl_xor_sync(0xffffffffu, acc[r], d);
+    out[r] = acc[r];
+  }
+}
+
+__global__ void __launch_bounds__(256) trsv_fwd_kernel(const double* __restrict__ L, int n, int k0, int kb, const double* __restrict__ Linv,
                                                       double* __restrict__ b, double* __restrict__ x) {
   __shared__ double sb[NB];
   __shared__ double sx[NB];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  sb[tid] = (tid < kb) ? b[k0 + tid] : 0.0;
+  if (tid < NB) sb[tid] = (tid < kb) ? b[k0 + tid] : 0.0;
   __syncthreads();
-  for (int rr = 0; rr < 32; ++rr) {
-    const int i = warp * 32 + rr;
-    const double* Li = Linv + (size_t)i * NB;
-    double acc = 0.0;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) acc += Li[lane + 32 * q] * sb[lane + 32 * q];
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
-    if (lane == 0) sx[i] = acc;
+#pragma unroll 1
+  for (int g = 0; g < 4; ++g) {
+    const int i = warp * 16 + g * 4;
+    double o[4];
+    warp_rows_dot4(Linv, NB, i, 4, sb, lane, o);
+    if (lane < 4) sx[i + lane] = (lane == 0) ? o[0] : (lane == 1) ? o[1] : (lane == 2) ? o[2] : o[3];
   }
   __syncthreads();
   if (blockIdx.x == 0) {
@@ -282,49 +335,94 @@ __global__ void __launch_bounds__(128) trsv_fwd_kernel(const double* __restrict_
     return;
   }
   const int r0 = k0 + NB + (blockIdx.x - 1) * NB;
-  for (int rr = 0; rr < 32; ++rr) {
-    const int row = r0 + warp * 32 + rr;
-    if (row >= n) break;
-    const double* Lr = L + (size_t)row * n + k0;
-    double acc = 0.0;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) acc += Lr[lane + 32 * q] * sx[lane + 32 * q];
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
-    if (lane == 0) b[row] -= acc;
+#pragma unroll 1
+  for (int g = 0; g < 4; ++g) {
+    const int row = r0 + warp * 16 + g * 4;
+    const int nrows = min(4, n - row);
+    if (nrows <= 0) break;
+    double o[4];
+    warp_rows_dot4(L + k0, (size_t)n, row, nrows, sx, lane, o);
+    if (lane < nrows) b[row + lane] -= (lane == 0) ? o[0] : (lane == 1) ? o[1] : (lane == 2) ? o[2] : o[3];
   }
 }
 
-__global__ void __launch_bounds__(128) trsv_bwd_kernel(const double* __restrict__ L, int n, int k0, int kb, const double* __restrict__ Linv,
+__global__ void __launch_bounds__(256) trsv_bwd_kernel(const double* __restrict__ L, int n, int k0, int kb, const double* __restrict__ Linv,
                                                       double* __restrict__ y, double* __restrict__ x) {
   __shared__ double sy[NB];
   __shared__ double sx[NB];
-  const int tid = threadIdx.x;
-  sy[tid] = (tid < kb) ? y[k0 + tid] : 0.0;
+  __shared__ double sp[NB];
+  const int tid = threadIdx.x, j = tid & (NB - 1), half = tid >> 7;
+  if (tid < NB) sy[tid] = (tid < kb) ? y[k0 + tid] : 0.0;
   __syncthreads();
   {
+    // x[j] = sum_{i >= j} Linv[i][j] y[i]; rows i split between the two halves, 8 loads in flight
     double acc = 0.0;
-    for (int i = tid; i < NB; ++i) acc += Linv[(size_t)i * NB + tid] * sy[i];
-    sx[tid] = acc;
+    const int i0 = half * 64;
+#pragma unroll 1
+    for (int ib = i0; ib < i0 + 64; ib += 8) {
+      double v[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) v[q] = (ib + q >= j) ? Linv[(size_t)(ib + q) * NB + j] : 0.0;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) acc += v[q] * sy[ib + q];
+    }
+    if (half) sp[j] = acc;
+    __syncthreads();
+    if (!half) sx[j] = acc + sp[j];
   }
   __syncthreads();
   if (blockIdx.x == 0) {
     if (tid < kb) x[k0 + tid] = sx[tid];
     return;
   }
-  const int col = (blockIdx.x - 1) * NB + tid;
+  const int col = (blockIdx.x - 1) * NB + j;
+  double acc = 0.0;
   if (col < k0) {
-    double acc = 0.0;
-    for (int i = 0; i < kb; ++i) acc += L[(size_t)(k0 + i) * n + col] * sx[i];
-    y[col] -= acc;
+    const int i0 = half * 64;
+#pragma unroll 1
+    for (int ib = i0; ib < i0 + 64; ib += 8) {
+      double v[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) v[q] = (ib + q < kb) ? L[(size_t)(k0 + ib + q) * n + col] : 0.0;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) acc += v[q] * sx[ib + q];
+    }
   }
+  if (half) sp[j] = acc;
+  __syncthreads();
+  if (!half && col < k0) y[col] -= acc + sp[j];
 }
 
 }  // namespace
 
-size_t cholesky_workspace_doubles(int n) { return (size_t)((n + NB - 1) / NB) * NB * NB; }
+size_t cholesky_workspace_doubles(int n) {
+  const size_t panels = (size_t)((n + NB - 1) / NB);
+  return panels * NB * NB /* L11^-1 blocks */ + panels * NB * NB /* packed TRSM scratch panel, m x 128 */;
+}
 
-void launch_cholesky(double* S, int n, double* Linv_ws, int* fail_flag, cudaStream_t s, int64_t* launches) {
+int CholAux::init() {
+  if (stream) return 0;
+  int lo = 0, hi = 0;
+  cudaDeviceGetStreamPriorityRange(&lo, &hi);
+  HSFM_CUDA(cudaStreamCreateWithPriority(&stream, cudaStreamNonBlocking, hi));
+  HSFM_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+  HSFM_CUDA(cudaEventCreateWithFlags(&ev_panel, cudaEventDisableTiming));
+  HSFM_CUDA(cudaEventCreateWithFlags(&ev_rest, cudaEventDisableTiming));
+  HSFM_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+  return 0;
+}
+void CholAux::destroy() {
+  if (!stream) return;
+  cudaStreamDestroy(stream);
+  cudaEventDestroy(ev_fork); cudaEventDestroy(ev_panel); cudaEventDestroy(ev_rest); cudaEventDestroy(ev_join);
+  stream = nullptr;
+}
+
+// Factorisation with one panel of look-ahead: the auxiliary (high-priority) stream runs
+//   diag(k) → trsm(k) → copy(k) → [panel k ready] → syrk of the NEXT panel's 128 columns
+// while the main stream runs the bulk of syrk(k-1); diag/trsm of panel k+1 therefore overlap the
+// trailing update of panel k instead of serialising with it.
+void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDiagSmem);
@@ -332,36 +430,60 @@ void launch_cholesky(double* S, int n, double* Linv_ws, int* fail_flag, cudaStre
     cudaFuncSetAttribute(chol_gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem);
     attr_set = true;
   }
-  int panel = 0;
-  for (int k0 = 0; k0 < n; k0 += NB, ++panel) {
+  const int panels = (n + NB - 1) / NB;
+  double* scratch = ws + (size_t)panels * NB * NB;
+  const bool la = aux && aux->stream && panels > 2;
+  cudaStream_t s2 = la ? aux->stream : s;
+  if (la) {
+    cudaEventRecord(aux->ev_fork, s);
+    cudaStreamWaitEvent(s2, aux->ev_fork, 0);
+  }
+  for (int panel = 0, k0 = 0; k0 < n; k0 += NB, ++panel) {
     const int kb = min(NB, n - k0);
-    double* Linv = Linv_ws + (size_t)panel * NB * NB;
-    chol_diag_kernel<<<1, 256, kDiagSmem, s>>>(S, n, k0, kb, Linv, fail_flag);
+    double* Linv = ws + (size_t)panel * NB * NB;
+    chol_diag_kernel<<<1, 256, kDiagSmem, s2>>>(S, n, k0, kb, Linv, fail_flag);
     ++*launches;
     const int m = n - (k0 + kb);
     if (m <= 0) break;
     const int rb = (m + NB - 1) / NB;
-    chol_gemm_kernel<0><<<rb, 256, kGemmSmem, s>>>(S, n, k0, Linv, fail_flag);
-    chol_gemm_kernel<1><<<rb * (rb + 1) / 2, 256, kGemmSmem, s>>>(S, n, k0, Linv, fail_flag);
+    chol_gemm_kernel<0><<<2 * rb, 128, kGemmSmem, s2>>>(S, n, k0, Linv, scratch, 0, 0, fail_flag);
+    chol_panel_copy_kernel<<<(int)(((size_t)m * (NB / 2) + 255) / 256), 256, 0, s2>>>(S, n, k0, m, scratch, fail_flag);
     *launches += 2;
+    if (la) {
+      cudaEventRecord(aux->ev_panel, s2);
+      if (panel > 0) cudaStreamWaitEvent(s2, aux->ev_rest, 0);  // rest(k-1) wrote the columns col(k) updates
+    }
+    // next panel's columns: column blocks 0,1 of every row tile
+    chol_gemm_kernel<1><<<2 * rb, 128, kGemmSmem, s2>>>(S, n, k0, Linv, nullptr, 0, 0, fail_flag);
+    ++*launches;
+    if (rb > 1) {
+      if (la) cudaStreamWaitEvent(s, aux->ev_panel, 0);
+      chol_gemm_kernel<1><<<rb * (rb - 1), 128, kGemmSmem, s>>>(S, n, k0, Linv, nullptr, 0, -1, fail_flag);
+      ++*launches;
+    }
+    if (la) cudaEventRecord(aux->ev_rest, s);
+  }
+  if (la) {
+    cudaEventRecord(aux->ev_join, s2);
+    cudaStreamWaitEvent(s, aux->ev_join, 0);
   }
 }
 
 // Solves S y = b with the factor from launch_cholesky.  b holds 2n doubles: [0,n) right-hand side
 // in / solution out, [n,2n) scratch for the intermediate vector.
-void launch_chol_solve(const double* L, int n, const double* Linv_ws, double* b, cudaStream_t s, int64_t* launches) {
+void launch_chol_solve(const double* L, int n, const double* ws, double* b, cudaStream_t s, int64_t* launches) {
   double* w = b + n;
   int panel = 0;
   for (int k0 = 0; k0 < n; k0 += NB, ++panel) {
     const int kb = min(NB, n - k0);
     const int m = n - (k0 + kb);
-    trsv_fwd_kernel<<<1 + (m + NB - 1) / NB, NB, 0, s>>>(L, n, k0, kb, Linv_ws + (size_t)panel * NB * NB, b, w);
+    trsv_fwd_kernel<<<1 + (m + NB - 1) / NB, 256, 0, s>>>(L, n, k0, kb, ws + (size_t)panel * NB * NB, b, w);
     ++*launches;
   }
   for (--panel; panel >= 0; --panel) {
     const int k0 = panel * NB;
     const int kb = min(NB, n - k0);
-    trsv_bwd_kernel<<<1 + (k0 + NB - 1) / NB, NB, 0, s>>>(L, n, k0, kb, Linv_ws + (size_t)panel * NB * NB, w, b);
+    trsv_bwd_kernel<<<1 + (k0 + NB - 1) / NB, 256, 0, s>>>(L, n, k0, kb, ws + (size_t)panel * NB * NB, w, b);
     ++*launches;
   }
 }

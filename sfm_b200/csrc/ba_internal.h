@@ -137,9 +137,16 @@ void launch_mirror_lower(Problem& P, cudaStream_t s);   // S upper <- lower (par
 // ---- dense Cholesky (ba_chol.cu) ----
 // In-place lower Cholesky of row-major n×n S (lower triangle read/written); *fail_flag set to
 // non-zero on a non-positive pivot.  Then solve S y = b in place in b.
-size_t cholesky_workspace_doubles(int n);  // room for the L11^-1 blocks, one 128×128 per panel
-void launch_cholesky(double* S, int n, double* Linv_ws, int* fail_flag, cudaStream_t s, int64_t* launches);
-void launch_chol_solve(const double* L, int n, const double* Linv_ws, double* b, cudaStream_t s, int64_t* launches);
+// auxiliary high-priority stream + events for the panel look-ahead of the factorisation
+struct CholAux {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_panel = nullptr, ev_rest = nullptr, ev_join = nullptr;
+  int init();
+  void destroy();
+};
+size_t cholesky_workspace_doubles(int n);  // L11^-1 blocks (one 128×128 per panel) + packed TRSM scratch panel
+void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches);
+void launch_chol_solve(const double* L, int n, const double* ws, double* b, cudaStream_t s, int64_t* launches);
 
 // ---- LM driver (ba_solver.cu) ----
 struct Ctx {
@@ -147,6 +154,7 @@ struct Ctx {
   cudaStream_t own_stream = nullptr;
   cudaStream_t stream = nullptr;
   Comm comm;
+  CholAux chol_aux;
   Problem prob;
   bool has_problem = false;
 };

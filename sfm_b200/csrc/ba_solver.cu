@@ -78,7 +78,7 @@ struct Driver {
           chk(ctx.comm.allreduce_sum(P.S, (size_t)n6 * n6, s));
           chk(ctx.comm.allreduce_sum(P.rhs, n6, s));
         }
-        launch_cholesky(P.S, n6, P.S + (size_t)n6 * n6, P.flags + F_CHOL_FAIL, s, &P.launches);
+        launch_cholesky(P.S, n6, P.S + (size_t)n6 * n6, P.flags + F_CHOL_FAIL, s, &ctx.chol_aux, &P.launches);
         HSFM_CUDA(cudaMemcpyAsync(P.yc, P.rhs, sizeof(double) * n6, cudaMemcpyDeviceToDevice, s));
         launch_chol_solve(P.S, n6, P.S + (size_t)n6 * n6, P.yc, s, &P.launches);
       } else {
