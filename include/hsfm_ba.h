@@ -63,7 +63,7 @@ typedef struct hsfm_ba_options {
   int32_t max_consecutive_invalid_steps; /* 5    */
   int32_t jacobi_scaling;                /* 1    */
   int32_t linear_solver;                 /* HSFM_BA_LINEAR_AUTO */
-  int32_t dense_max_cams;                /* 512: largest camera count solved by dense Cholesky under AUTO */
+  int32_t dense_max_cams;                /* 2048: largest camera count solved by dense Cholesky under AUTO */
   int32_t pcg_max_iterations;            /* 1000 */
   int32_t verbose;                       /* 0; 1 prints a Ceres-like progress table to stderr */
   int32_t reserved0;
@@ -197,6 +197,13 @@ int hsfm_ba_schur(hsfm_ba_ctx* ctx, int64_t n_obs, const double* obs_xy, const i
  * not positive definite. */
 int hsfm_ba_dense_spd_solve(hsfm_ba_ctx* ctx, int32_t n, const double* A, const double* b, double* x,
                             double* L_out, int32_t* pivot);
+
+/* Measurement tap for the same kernels: builds a synthetic SPD matrix of order n on the device
+ * (n even), factors it `reps` times (after one warm-up) and solves one right-hand side each time;
+ * returns the average device time of the factorisation and of the two triangular solves in ms
+ * (CUDA events on the context's stream) and the max-norm residual |A x - b| / |b| of the last solve. */
+int hsfm_ba_bench_cholesky(hsfm_ba_ctx* ctx, int32_t n, int reps, double* factor_ms, double* solve_ms,
+                           double* rel_residual);
 
 /* ---- device-resident problem (bench / repeated solves; inputs stay in HBM) ----------------- */
 

@@ -45,6 +45,7 @@ SYMBOLS = {
     "hsfm_ba_schur": (C.c_int, [C.c_void_p, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp,
                                 C.POINTER(Options), C.c_double, _dp, _dp, _dp, _dp, _dp, _dp, _dp]),
     "hsfm_ba_dense_spd_solve": (C.c_int, [C.c_void_p, C.c_int32, _dp, _dp, _dp, _dp, _ip]),
+    "hsfm_ba_bench_cholesky": (C.c_int, [C.c_void_p, C.c_int32, C.c_int, _dp, _dp, _dp]),
     "hsfm_ba_problem_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp]),
     "hsfm_ba_problem_reset": (C.c_int, [C.c_void_p]),
     "hsfm_ba_problem_solve": (C.c_int, [C.c_void_p, C.POINTER(Options), C.POINTER(Summary)]),
@@ -222,6 +223,14 @@ class Context:
             e.pivot = piv.value
             raise e
         return (x, np.tril(L)) if want_factor else x
+
+    def bench_cholesky(self, n: int, reps: int = 3):
+        """(factor ms, solve ms, relative residual) of the dense Cholesky on a synthetic SPD matrix of order n."""
+        f, s, r = C.c_double(), C.c_double(), C.c_double()
+        rc = self.lib.hsfm_ba_bench_cholesky(self.h, n, reps, C.byref(f), C.byref(s), C.byref(r))
+        if rc:
+            raise BAError(rc, "hsfm_ba_bench_cholesky")
+        return f.value, s.value, r.value
 
     # -- resident problem --
     def upload(self, prob, mode=STRUCT_AND_POSE):

@@ -70,7 +70,7 @@ void hsfm_ba_default_options(hsfm_ba_options* o) {
   o->max_consecutive_invalid_steps = 5;
   o->jacobi_scaling = 1;
   o->linear_solver = HSFM_BA_LINEAR_AUTO;
-  o->dense_max_cams = 512;
+  o->dense_max_cams = 2048;
   o->pcg_max_iterations = 1000;
   o->verbose = 0;
   o->initial_trust_region_radius = 1e4;
@@ -348,6 +348,60 @@ int hsfm_ba_dense_spd_solve(hsfm_ba_ctx* h, int32_t n, const double* A, const do
   if (rc) return rc;
   if (pivot) *pivot = flag;
   return flag ? HSFM_BA_ERR_ARG : 0;
+}
+
+int hsfm_ba_bench_cholesky(hsfm_ba_ctx* h, int32_t n, int reps, double* factor_ms, double* solve_ms, double* rel_residual) {
+  if (!h || n <= 0 || (n & 1) || reps <= 0) return HSFM_BA_ERR_ARG;
+  HSFM_CUDA(cudaSetDevice(h->c.device));
+  cudaStream_t s = h->c.stream;
+  const size_t nn = (size_t)n * n;
+  double *dA = nullptr, *db = nullptr, *derr = nullptr;
+  int* dflag = nullptr;
+  if (cudaMalloc(&dA, sizeof(double) * (nn + cholesky_workspace_doubles(n))) != cudaSuccess) { cudaGetLastError(); return HSFM_BA_ERR_NOMEM; }
+  if (cudaMalloc(&db, sizeof(double) * 3 * n) != cudaSuccess || cudaMalloc(&dflag, sizeof(int)) != cudaSuccess ||
+      cudaMalloc(&derr, sizeof(double)) != cudaSuccess) {
+    cudaGetLastError(); cudaFree(dA); if (db) cudaFree(db); if (dflag) cudaFree(dflag); return HSFM_BA_ERR_NOMEM;
+  }
+  cudaEvent_t e0, e1, e2;
+  cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
+  int64_t launches = 0;
+  float tf = 0.f, ts = 0.f;
+  int flag = 0;
+  double err = 0.0;
+  auto run = [&]() -> int {
+    for (int it = 0; it <= reps; ++it) {
+      launch_spd_fill(dA, n, it == 0 ? db + 2 * n : nullptr, s);
+      HSFM_CUDA(cudaMemcpyAsync(db, db + 2 * n, sizeof(double) * n, cudaMemcpyDeviceToDevice, s));
+      HSFM_CUDA(cudaMemsetAsync(dflag, 0, sizeof(int), s));
+      HSFM_CUDA(cudaEventRecord(e0, s));
+      launch_cholesky(dA, n, dA + nn, dflag, s, &h->c.chol_aux, &launches);
+      HSFM_CUDA(cudaEventRecord(e1, s));
+      launch_chol_solve(dA, n, dA + nn, db, s, &launches);
+      HSFM_CUDA(cudaEventRecord(e2, s));
+      HSFM_CUDA(cudaEventSynchronize(e2));
+      if (it > 0) {
+        float a = 0.f, b = 0.f;
+        cudaEventElapsedTime(&a, e0, e1);
+        cudaEventElapsedTime(&b, e1, e2);
+        tf += a; ts += b;
+      }
+    }
+    launch_spd_err(n, db, derr, s);
+    HSFM_CUDA(cudaMemcpyAsync(&flag, dflag, sizeof(int), cudaMemcpyDeviceToHost, s));
+    HSFM_CUDA(cudaMemcpyAsync(&err, derr, sizeof(double), cudaMemcpyDeviceToHost, s));
+    HSFM_CUDA(cudaStreamSynchronize(s));
+    HSFM_CUDA(cudaGetLastError());
+    return 0;
+  };
+  const int rc = run();
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
+  cudaFree(dA); cudaFree(db); cudaFree(dflag); cudaFree(derr);
+  if (rc) return rc;
+  if (flag) return HSFM_BA_ERR_STATE;
+  if (factor_ms) *factor_ms = tf / reps;
+  if (solve_ms) *solve_ms = ts / reps;
+  if (rel_residual) *rel_residual = err;
+  return 0;
 }
 
 int hsfm_ba_eval(hsfm_ba_ctx* h, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx, int32_t n_cams,

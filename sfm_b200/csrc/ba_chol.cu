@@ -152,8 +152,8 @@ constexpr int kDiagSmem = (NB * DIAG_LD + 4096 + NB + 2 * NB) * (int)sizeof(doub
 //                  read the whole row tile, so the result cannot overwrite A21 in place);
 //                  chol_panel_copy_kernel then moves it over A21.
 //   MODE 1 (SYRK): A = L21 rows of row tile bi, B = L21 rows of 64-column block bj
-//                  →  S[bi,bj] -= C.  Accumulators start at -C (prefetched while the first chunk is
-//                  in flight), the main loop adds A B^T, the epilogue stores the negation: no
+//                  →  S[bi,bj] -= C.  Accumulators start at C (prefetched while the first chunk is
+//                  in flight), the main loop feeds negated A fragments, the epilogue stores: no
 //                  read-modify-write at the end.
 // ---------------------------------------------------------------------------------------------
 constexpr int TN = 64;  // tile columns
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(128, 2) chol_gemm_kernel(double* __restrict__ 
                                                            const int* __restrict__ fail) {
   extern __shared__ __align__(16) unsigned char gsm_raw[];
   GemmSmem& sm = *reinterpret_cast<GemmSmem*>(gsm_raw);
-  if (*fail) return;
+  const int failed = *fail;  // consumed after the prologue loads are in flight
   const int base = k0 + NB;
   int bi, bj;  // row tile (128 rows), column block (64 columns)
   if (MODE == 0) {
@@ -197,7 +197,7 @@ __global__ void __launch_bounds__(128, 2) chol_gemm_kernel(double* __restrict__ 
   } else {
     // row tile bi (>= 1) owns column blocks 2 .. 2*bi+1 → 2*bi tiles; tiles before row bi: bi*(bi-1)
     const int t = blockIdx.x;
-    bi = (int)((1.0 + sqrt(1.0 + 4.0 * (double)t)) * 0.5);
+    bi = (int)((1.0f + sqrtf(1.0f + 4.0f * (float)t)) * 0.5f);
     while (bi * (bi + 1) <= t) ++bi;
     while (bi * (bi - 1) > t) --bi;
     bj = 2 + (t - bi * (bi - 1));
@@ -218,6 +218,9 @@ __global__ void __launch_bounds__(128, 2) chol_gemm_kernel(double* __restrict__ 
   load_tile_async<TN>(sm.b[0], Bsrc, ldb, rj, nj, kb0);
   cp_async_commit();
 
+  // Accumulators start at C itself (SYRK); the main loop feeds NEGATED A fragments, so the result is
+  // C - A B^T with no arithmetic between the 32 independent 16-byte loads (they all stay in flight
+  // together; a negation here made ptxas serialise them through one temporary).
   double acc[8][4][2];
 #pragma unroll
   for (int a = 0; a < 8; ++a)
@@ -227,11 +230,12 @@ __global__ void __launch_bounds__(128, 2) chol_gemm_kernel(double* __restrict__ 
       if (MODE == 1) {
         const int row = wr * 64 + a * 8 + fr, col = wc * 32 + b * 8 + 2 * fk;
         if (row < ni && col < nj) {
-          const double2 c = *reinterpret_cast<const double2*>(S + (size_t)(ri + row) * n + rj + col);
-          acc[a][b][0] = -c.x; acc[a][b][1] = -c.y;
+          const double2 c = __ldcs(reinterpret_cast<const double2*>(S + (size_t)(ri + row) * n + rj + col));
+          acc[a][b][0] = c.x; acc[a][b][1] = c.y;
         }
       }
     }
+  if (failed) { cp_async_wait<0>(); return; }
 #pragma unroll 1
   for (int ch = 0; ch < NB / KC; ++ch) {
     const int cur = ch & 1;
@@ -248,7 +252,10 @@ __global__ void __launch_bounds__(128, 2) chol_gemm_kernel(double* __restrict__ 
     for (int ks = 0; ks < KC / 4; ++ks) {
       double af[8], bf[4];
 #pragma unroll
-      for (int a = 0; a < 8; ++a) af[a] = sm.a[cur][wr * 64 + a * 8 + fr][ks * 4 + fk];
+      for (int a = 0; a < 8; ++a) {
+        const double v = sm.a[cur][wr * 64 + a * 8 + fr][ks * 4 + fk];
+        af[a] = (MODE == 1) ? -v : v;
+      }
 #pragma unroll
       for (int b = 0; b < 4; ++b) bf[b] = sm.b[cur][wc * 32 + b * 8 + fr][ks * 4 + fk];
 #pragma unroll
@@ -272,7 +279,7 @@ __global__ void __launch_bounds__(128, 2) chol_gemm_kernel(double* __restrict__ 
       } else {
         if (col >= nj) continue;
         double2* dst = reinterpret_cast<double2*>(S + (size_t)(ri + row) * n + rj + col);
-        *dst = make_double2(-acc[a][b][0], -acc[a][b][1]);
+        *dst = make_double2(acc[a][b][0], acc[a][b][1]);
       }
     }
   }
@@ -393,7 +400,39 @@ __global__ void __launch_bounds__(256) trsv_bwd_kernel(const double* __restrict_
   if (!half && col < k0) y[col] -= acc + sp[j];
 }
 
+// synthetic SPD test matrix A_ij = 1/(1+|i-j|) + 2 delta_ij (Polya: convex decreasing kernel), b = A 1
+__global__ void spd_fill_kernel(double* __restrict__ A, int n) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (j < n) A[(size_t)i * n + j] = 1.0 / (1.0 + fabs((double)(i - j))) + (i == j ? 2.0 : 0.0);
+}
+__global__ void spd_rowsum_kernel(int n, double* __restrict__ b) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double s = 2.0;
+  for (int j = 0; j < n; ++j) s += 1.0 / (1.0 + fabs((double)(i - j)));
+  b[i] = s;
+}
+__global__ void spd_err_kernel(int n, const double* __restrict__ x, double* __restrict__ err) {
+  __shared__ double sm[256];
+  double m = 0.0;
+  for (int i = threadIdx.x; i < n; i += 256) m = fmax(m, fabs(x[i] - 1.0));
+  sm[threadIdx.x] = m;
+  __syncthreads();
+  for (int d = 128; d > 0; d >>= 1) {
+    if ((int)threadIdx.x < d) sm[threadIdx.x] = fmax(sm[threadIdx.x], sm[threadIdx.x + d]);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *err = sm[0];
+}
+
 }  // namespace
+
+void launch_spd_fill(double* A, int n, double* b, cudaStream_t s) {
+  dim3 g((n + 255) / 256, n);
+  spd_fill_kernel<<<g, 256, 0, s>>>(A, n);
+  if (b) spd_rowsum_kernel<<<(n + 127) / 128, 128, 0, s>>>(n, b);
+}
+void launch_spd_err(int n, const double* x, double* err, cudaStream_t s) { spd_err_kernel<<<1, 256, 0, s>>>(n, x, err); }
 
 size_t cholesky_workspace_doubles(int n) {
   const size_t panels = (size_t)((n + NB - 1) / NB);
