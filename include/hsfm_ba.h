@@ -115,6 +115,13 @@ typedef struct hsfm_ba_summary {
   hsfm_ba_iteration* trace;
   int32_t trace_capacity;
   int32_t trace_count;
+  /* device time of the solve by phase (CUDA events on the solve stream), milliseconds:
+   * [0] linearise (residual+Jacobian, point and camera blocks, gradient norm)
+   * [1] reduced-system formation (point inverses, explicit S or block-Jacobi blocks, reduced rhs)
+   * [2] dense Cholesky factorisation      [3] triangular solves or PCG iterations
+   * [4] step, back-substitution, model cost change, candidate cost
+   * [5] scalar read-back + host decision   [6],[7] reserved */
+  double phase_ms[8];
 } hsfm_ba_summary;
 
 typedef struct hsfm_ba_ctx hsfm_ba_ctx;

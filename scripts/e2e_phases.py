@@ -18,5 +18,6 @@ for rep in range(4):
     _, _, s = ctx.solve_packed(hp, opts=opts)
     dt = (time.perf_counter() - t0) * 1e3
     print(f"{cfg} rep {rep}: wall {dt:.1f} ms | h2d {s['h2d_ms']:.1f} setup {s['setup_ms']:.1f} solve {s['solve_ms']:.1f} d2h {s['d2h_ms']:.1f} | "
-          f"its {s['num_iterations']} lin {s['total_linear_iterations']} launches {s['gpu_launches']} cost {s['final_cost']:.6f}")
+          f"its {s['num_iterations']} lin {s['total_linear_iterations']} launches {s['gpu_launches']} cost {s['final_cost']:.6f} | "
+          f"phases lin/form/factor/solve/step/sync = " + "/".join(f"{v:.1f}" for v in s["phase_ms"][:6]))
 ctx.close()

@@ -64,6 +64,7 @@ class Summary(C.Structure):
         ("trace", C.POINTER(Iteration)),
         ("trace_capacity", C.c_int32),
         ("trace_count", C.c_int32),
+        ("phase_ms", C.c_double * 8),
     ]
 
 

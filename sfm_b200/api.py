@@ -117,7 +117,8 @@ class _SummaryBox:
         self.s.trace_capacity = trace_capacity
 
     def as_dict(self):
-        d = {f: getattr(self.s, f) for f, _ in self.s._fields_ if f != "trace"}
+        d = {f: getattr(self.s, f) for f, _ in self.s._fields_ if f not in ("trace", "phase_ms")}
+        d["phase_ms"] = [float(v) for v in self.s.phase_ms]
         d["trace"] = [self.trace_buf[i].as_dict() for i in range(self.s.trace_count)]
         return d
 

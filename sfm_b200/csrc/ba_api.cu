@@ -110,6 +110,7 @@ void hsfm_ba_destroy(hsfm_ba_ctx* h) {
   if (h->c.prob.S) { cudaFree(h->c.prob.S); h->c.prob.S = nullptr; }
   h->c.comm.destroy();
   h->c.chol_aux.destroy();
+  for (cudaEvent_t e : h->c.phase_events) cudaEventDestroy(e);
   if (h->c.own_stream) cudaStreamDestroy(h->c.own_stream);
   delete h;
 }
@@ -201,7 +202,10 @@ int hsfm_ba_problem_download(hsfm_ba_ctx* h, double* cam_rt, double* pts) {
   Problem& P = h->c.prob;
   HSFM_CUDA(cudaSetDevice(h->c.device));
   if (cam_rt) HSFM_CUDA(cudaMemcpyAsync(cam_rt, P.cam_x, sizeof(double) * 6 * P.n_cams, cudaMemcpyDeviceToHost, h->c.stream));
-  if (pts) HSFM_CUDA(cudaMemcpyAsync(pts, P.pts_x, sizeof(double) * 3 * (size_t)P.n_pts, cudaMemcpyDeviceToHost, h->c.stream));
+  if (pts) {
+    launch_rows_to_caller(P, 3, P.pts_x, P.pts_io, h->c.stream);
+    HSFM_CUDA(cudaMemcpyAsync(pts, P.pts_io, sizeof(double) * 3 * (size_t)P.n_pts, cudaMemcpyDeviceToHost, h->c.stream));
+  }
   HSFM_CUDA(cudaStreamSynchronize(h->c.stream));
   return 0;
 }
@@ -453,24 +457,35 @@ int hsfm_ba_schur(hsfm_ba_ctx* h, int64_t n_obs, const double* obs_xy, const int
   launch_schur_rhs(P, true, s);
   launch_mirror_lower(P, s);
   launch_finalize_scalars(P, s);
-  double *d_Hcc = nullptr, *d_Hpp = nullptr;
+  double *d_Hcc = nullptr, *d_Hpp = nullptr, *d_tmp = nullptr;  // point rows go back in the caller's point order
   if (Hcc) HSFM_CUDA(cudaMalloc(&d_Hcc, sizeof(double) * 36 * std::max(1, (int)n_cams)));
   if (Hpp) HSFM_CUDA(cudaMalloc(&d_Hpp, sizeof(double) * 9 * std::max<size_t>(1, (size_t)n_pts)));
+  HSFM_CUDA(cudaMalloc(&d_tmp, sizeof(double) * 9 * std::max<size_t>(1, (size_t)n_pts)));
   P.scal_host[31] = radius; P.scal_host[30] = opts->min_lm_diagonal; P.scal_host[29] = opts->max_lm_diagonal;
   launch_export_blocks(P, d_Hcc, d_Hpp, s);
   if (S_dense) HSFM_CUDA(cudaMemcpyAsync(S_dense, P.S, sizeof(double) * n6 * n6, cudaMemcpyDeviceToHost, s));
   if (rhs) HSFM_CUDA(cudaMemcpyAsync(rhs, P.rhs, sizeof(double) * n6, cudaMemcpyDeviceToHost, s));
   if (Hcc) HSFM_CUDA(cudaMemcpyAsync(Hcc, d_Hcc, sizeof(double) * 36 * n_cams, cudaMemcpyDeviceToHost, s));
   if (gc) HSFM_CUDA(cudaMemcpyAsync(gc, P.gc, sizeof(double) * n6, cudaMemcpyDeviceToHost, s));
-  if (Hpp) HSFM_CUDA(cudaMemcpyAsync(Hpp, d_Hpp, sizeof(double) * 9 * (size_t)n_pts, cudaMemcpyDeviceToHost, s));
-  if (gp) HSFM_CUDA(cudaMemcpyAsync(gp, P.gp, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToHost, s));
+  if (Hpp) {
+    launch_rows_to_caller(P, 9, d_Hpp, d_tmp, s);
+    HSFM_CUDA(cudaMemcpyAsync(Hpp, d_tmp, sizeof(double) * 9 * (size_t)n_pts, cudaMemcpyDeviceToHost, s));
+    HSFM_CUDA(cudaStreamSynchronize(s));
+  }
+  if (gp) {
+    launch_rows_to_caller(P, 3, P.gp, d_tmp, s);
+    HSFM_CUDA(cudaMemcpyAsync(gp, d_tmp, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToHost, s));
+    HSFM_CUDA(cudaStreamSynchronize(s));
+  }
   if (scale) {
     HSFM_CUDA(cudaMemcpyAsync(scale, P.scale_c, sizeof(double) * n6, cudaMemcpyDeviceToHost, s));
-    HSFM_CUDA(cudaMemcpyAsync(scale + n6, P.scale_p, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToHost, s));
+    launch_rows_to_caller(P, 3, P.scale_p, d_tmp, s);
+    HSFM_CUDA(cudaMemcpyAsync(scale + n6, d_tmp, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToHost, s));
   }
   HSFM_CUDA(cudaStreamSynchronize(s));
   if (d_Hcc) cudaFree(d_Hcc);
   if (d_Hpp) cudaFree(d_Hpp);
+  cudaFree(d_tmp);
   return 0;
 }
 

@@ -73,15 +73,51 @@ __global__ void lower_bound_kernel(int n, const int* __restrict__ keys, int n_ke
   }
   start[k] = lo;
 }
+// ---- point renumbering: internal id = rank of (smallest observing camera, caller id) ----
+__global__ void fill_int_kernel(int n, int v, int* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = v;
+}
+__global__ void min_cam_kernel(int n, const int* __restrict__ pt, const int* __restrict__ cam, int* __restrict__ min_cam) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) atomicMin(min_cam + pt[i], cam[i]);
+}
+__global__ void invert_perm_kernel(int n, const int* __restrict__ old_of_new, int* __restrict__ new_of_old) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) new_of_old[old_of_new[k]] = k;
+}
+__global__ void gather_int_kernel(int n, const int* __restrict__ idx, const int* __restrict__ table, int* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = table[idx[i]];
+}
+// dst[k][0..w) = src[row_of[k]][0..w)
+__global__ void gather_rows_kernel(int n, int w, const int* __restrict__ row_of, const double* __restrict__ src, double* __restrict__ dst) {
+  const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= (size_t)n * w) return;
+  const int k = (int)(e / w), c = (int)(e % w);
+  dst[e] = src[(size_t)row_of[k] * w + c];
+}
 __global__ void diff_kernel(int n, const int* __restrict__ start, int* __restrict__ cnt) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k < n) cnt[k] = start[k + 1] - start[k];
 }
 
 inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+inline int cdivz(size_t a, int b) { return (int)((a + b - 1) / b); }
 double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
 }  // namespace
+
+void launch_rows_to_internal(Problem& P, int w, const double* caller_order, double* internal_order, cudaStream_t s) {
+  if (P.n_pts == 0) return;
+  gather_rows_kernel<<<cdivz((size_t)P.n_pts * w, 256), 256, 0, s>>>(P.n_pts, w, P.pt_old_of_new, caller_order, internal_order);
+  P.launches++;
+}
+void launch_rows_to_caller(Problem& P, int w, const double* internal_order, double* caller_order, cudaStream_t s) {
+  if (P.n_pts == 0) return;
+  gather_rows_kernel<<<cdivz((size_t)P.n_pts * w, 256), 256, 0, s>>>(P.n_pts, w, P.pt_new_of_old, internal_order, caller_order);
+  P.launches++;
+}
 
 int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
                   int32_t n_cams, const double* K9, const double* dist, const double* cam_rt, int64_t n_pts64, const double* pts,
@@ -100,7 +136,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   ALLOC(obs_in, n); ALLOC(cam_in, n); ALLOC(pt_in, n);
   ALLOC(P.K9, 9 * (size_t)n_cams); ALLOC(P.dist, 2 * (size_t)n_cams);
   ALLOC(P.cam_x, 6 * (size_t)n_cams); ALLOC(P.pts_x, 3 * (size_t)n_pts);
-  ALLOC(P.cam_x0, 6 * (size_t)n_cams); ALLOC(P.pts_x0, 3 * (size_t)n_pts);
+  ALLOC(P.cam_x0, 6 * (size_t)n_cams); ALLOC(P.pts_x0, 3 * (size_t)n_pts); ALLOC(P.pts_io, 3 * (size_t)n_pts);
   HSFM_CUDA(cudaMemcpyAsync(obs_in, obs_xy, sizeof(double) * 2 * n, cudaMemcpyHostToDevice, s));
   HSFM_CUDA(cudaMemcpyAsync(cam_in, cam_idx, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, s));
   HSFM_CUDA(cudaMemcpyAsync(pt_in, pt_idx, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, s));
@@ -108,42 +144,58 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   if (dist) HSFM_CUDA(cudaMemcpyAsync(P.dist, dist, sizeof(double) * 2 * n_cams, cudaMemcpyHostToDevice, s));
   else HSFM_CUDA(cudaMemsetAsync(P.dist, 0, sizeof(double) * 2 * std::max(1, n_cams), s));
   HSFM_CUDA(cudaMemcpyAsync(P.cam_x0, cam_rt, sizeof(double) * 6 * n_cams, cudaMemcpyHostToDevice, s));
-  HSFM_CUDA(cudaMemcpyAsync(P.pts_x0, pts, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyHostToDevice, s));
+  HSFM_CUDA(cudaMemcpyAsync(P.pts_io, pts, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyHostToDevice, s));
   HSFM_CUDA(cudaMemcpyAsync(P.cam_x, P.cam_x0, sizeof(double) * 6 * n_cams, cudaMemcpyDeviceToDevice, s));
-  HSFM_CUDA(cudaMemcpyAsync(P.pts_x, P.pts_x0, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToDevice, s));
   HSFM_CUDA(cudaStreamSynchronize(s));
   const double t_setup0 = now_ms();
   if (h2d_ms) *h2d_ms = t_setup0 - t_h2d0;
 
   // ---- static arrays ----
-  double2 *obs, *obs_cs; int *cam, *pt, *pt_cs, *pt_start, *cam_start, *iota, *pos_cs, *cam_sorted;
+  double2 *obs, *obs_cs; int *cam, *pt, *pt_cs, *pt_start, *cam_start, *iota, *pos_cs, *cam_sorted, *order1, *key2, *min_cam, *min_cam_sorted;
   ALLOC(obs, n); ALLOC(cam, n); ALLOC(pt, n); ALLOC(obs_cs, n); ALLOC(pt_cs, n);
   ALLOC(pt_start, (size_t)n_pts + 1); ALLOC(cam_start, (size_t)n_cams + 1);
-  ALLOC(iota, n); ALLOC(P.order_pm, n); ALLOC(pos_cs, n); ALLOC(cam_sorted, n);
+  const int n_iota = std::max(n, n_pts);
+  ALLOC(iota, n_iota); ALLOC(P.order_pm, n); ALLOC(pos_cs, n); ALLOC(cam_sorted, n); ALLOC(order1, n); ALLOC(key2, n);
+  ALLOC(min_cam, n_pts); ALLOC(min_cam_sorted, n_pts); ALLOC(P.pt_old_of_new, n_pts); ALLOC(P.pt_new_of_old, n_pts);
+  if (n_iota > 0) iota_kernel<<<cdiv(n_iota, 256), 256, 0, s>>>(n_iota, iota);
+  int pbits = 1; while ((1ll << pbits) < std::max(2, n_pts)) ++pbits;
+  int cbits = 1; while ((1ll << cbits) < std::max(2, (int)n_cams) + 1) ++cbits;
+  size_t tmp_bytes = 0, tmp2 = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, pt_in, pt, iota, P.order_pm, std::max(n, 1), 0, pbits, s);
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp2, cam, cam_sorted, iota, pos_cs, std::max({n, n_pts, 1}), 0, cbits, s);
+  tmp_bytes = std::max(tmp_bytes, tmp2);
+  void* tmp = nullptr;
+  HSFM_CUDA(cudaMalloc(&tmp, tmp_bytes));
+  // Internal point ids: points ordered by their smallest observing camera (ties: caller id).  Points that
+  // share cameras become neighbours, so a tile's camera rows, the camera-vector atomics of the mat-vec
+  // and above all the 6x6 blocks of S that dense_schur updates stay within a small, L2-resident window.
+  if (n_pts > 0) {
+    fill_int_kernel<<<cdiv(n_pts, 256), 256, 0, s>>>(n_pts, n_cams, min_cam);  // no observation: sorted last
+    if (n > 0) min_cam_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, pt_in, cam_in, min_cam);
+    cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, min_cam, min_cam_sorted, iota, P.pt_old_of_new, n_pts, 0, cbits, s);
+    invert_perm_kernel<<<cdiv(n_pts, 256), 256, 0, s>>>(n_pts, P.pt_old_of_new, P.pt_new_of_old);
+    gather_rows_kernel<<<cdivz((size_t)n_pts * 3, 256), 256, 0, s>>>(n_pts, 3, P.pt_old_of_new, P.pts_io, P.pts_x0);
+  }
+  HSFM_CUDA(cudaMemcpyAsync(P.pts_x, P.pts_x0, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToDevice, s));
   if (n > 0) {
-    iota_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, iota);
-    // point-major: stable sort by point id
-    size_t tmp_bytes = 0, tmp2 = 0;
-    int pbits = 1; while ((1ll << pbits) < std::max(2, n_pts)) ++pbits;
-    int cbits = 1; while ((1ll << cbits) < std::max(2, (int)n_cams)) ++cbits;
-    cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, pt_in, pt, iota, P.order_pm, n, 0, pbits, s);
-    cub::DeviceRadixSort::SortPairs(nullptr, tmp2, cam, cam_sorted, iota, pos_cs, n, 0, cbits, s);
-    tmp_bytes = std::max(tmp_bytes, tmp2);
-    void* tmp = nullptr;
-    HSFM_CUDA(cudaMalloc(&tmp, tmp_bytes));
-    cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, pt_in, pt, iota, P.order_pm, n, 0, pbits, s);
+    // point-major with cameras ascending inside a point: stable sort by camera, then stable sort by
+    // internal point id (ties keep input order, so every later floating-point sum has a fixed order)
+    cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, cam_in, cam_sorted, iota, order1, n, 0, cbits, s);
+    gather_int_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, order1, pt_in, key2);
+    gather_int_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, key2, P.pt_new_of_old, pos_cs /*scratch*/);
+    cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, pos_cs, pt, order1, P.order_pm, n, 0, pbits, s);
     gather_obs_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, P.order_pm, obs_in, cam_in, obs, cam);
     // camera-major: stable sort of point-major positions by camera
     cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, cam, cam_sorted, iota, pos_cs, n, 0, cbits, s);
     gather_cs_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, pos_cs, obs, pt, obs_cs, pt_cs);
     lower_bound_kernel<<<cdiv(n_pts + 1, 256), 256, 0, s>>>(n, pt, n_pts, pt_start);
     lower_bound_kernel<<<cdiv(n_cams + 1, 256), 256, 0, s>>>(n, cam_sorted, n_cams, cam_start);
-    HSFM_CUDA(cudaStreamSynchronize(s));
-    cudaFree(tmp);
   } else {
     HSFM_CUDA(cudaMemsetAsync(pt_start, 0, sizeof(int) * ((size_t)n_pts + 1), s));
     HSFM_CUDA(cudaMemsetAsync(cam_start, 0, sizeof(int) * ((size_t)n_cams + 1), s));
   }
+  HSFM_CUDA(cudaStreamSynchronize(s));
+  cudaFree(tmp);
 
   // ---- tiles: greedy packing of whole points into <= TILE observations (host, O(n_pts)) ----
   std::vector<int> h_pt_start((size_t)n_pts + 1), h_cam_start((size_t)n_cams + 1);

@@ -54,6 +54,9 @@ struct Problem {
   std::vector<void*> allocs;
   // input order → point-major position (for the eval tap) and static copies
   int* order_pm = nullptr;  // [n_obs] input index of the j-th point-major observation
+  int* pt_old_of_new = nullptr;  // [n_pts] caller's point id of internal point k (internal order: by smallest observing camera)
+  int* pt_new_of_old = nullptr;  // [n_pts] inverse
+  double* pts_io = nullptr;      // [n_pts][3] staging in the caller's point order (upload / download / taps)
   double* K9 = nullptr;     // [n_cams][9]
   double* dist = nullptr;   // [n_cams][2]
   // parameters
@@ -108,6 +111,10 @@ int build_problem(Problem& P, int mode, int64_t n_obs, const double* obs_xy, con
                   int32_t n_cams, const double* K9, const double* dist, const double* cam_rt, int64_t n_pts, const double* pts,
                   Comm& comm, cudaStream_t s, double* setup_ms, double* h2d_ms);
 
+// point-indexed rows between the caller's point order and the internal one (ba_index.cu)
+void launch_rows_to_internal(Problem& P, int w, const double* caller_order, double* internal_order, cudaStream_t s);
+void launch_rows_to_caller(Problem& P, int w, const double* internal_order, double* caller_order, cudaStream_t s);
+
 // ---- kernel launchers (ba_kernels.cu); every launcher bumps P.launches ----
 void launch_cam_prep(Problem& P, const double* cam, const double* scale_c /*null = 1*/, CamRow* rows, cudaStream_t s);
 // residual + Jacobian (+ point blocks Hpp,gp when form) ; scale_p null = 1
@@ -160,6 +167,7 @@ struct Ctx {
   CholAux chol_aux;
   Problem prob;
   bool has_problem = false;
+  std::vector<cudaEvent_t> phase_events;  // pool reused across solves (phase timing of lm_solve)
 };
 int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary);
 

@@ -671,19 +671,26 @@ __global__ void dense_init_kernel(int n_cams, const double* __restrict__ Hcc, co
   S[(6 * (size_t)c + a) * n + 6 * (size_t)c + b] = v;
 }
 
-// S[ci,cj] -= W_i Hpp^-1 W_j^T for every ordered pair (i,j) of observations of a point with
-// cam(i) >= cam(j): lower block triangle.  One thread per observation i, W of the tile staged in
-// shared memory so the inner loop over j reads it from there.
+// S[ci,cj] -= W_i Hpp^-1 W_j^T for every pair (i,j) of observations of a point with cam(i) >= cam(j):
+// lower block triangle (a7).  Phase 1: one thread per observation stages W_i = Jc_i^T Jp_i (6x3) and
+// A_i = W_i Hpp^-1 in shared memory.  Phase 2: the tile's pairs are numbered by a prefix sum and dealt to
+// the warps eight at a time; consecutive lanes take consecutive block elements, so every RED instruction carries whole
+// 6-double rows of a 6x6 block (48 contiguous bytes) instead of 32 unrelated addresses — measured 2.2-2.8x
+// the FP64 atomic rate of the one-thread-per-block scatter (scripts/micro/fp64_peaks.cu).  Observations of a
+// point are stored with ascending camera (ba_index.cu), so pair (i,j), j <= i, lands in the lower triangle.
+constexpr int kDenseSchurSmem = TILE * 36 * (int)sizeof(double) + (3 * TILE + 8) * (int)sizeof(int);
 __global__ void __launch_bounds__(TILE) dense_schur_kernel(Dev d, const double* __restrict__ Hpp_inv, double* __restrict__ S) {
-  __shared__ double sW[TILE][19];
-  __shared__ int sCam[TILE];
+  extern __shared__ __align__(16) unsigned char ds_raw[];
+  double (*sA)[18] = reinterpret_cast<double (*)[18]>(ds_raw);
+  double (*sW)[18] = reinterpret_cast<double (*)[18]>(ds_raw + TILE * 18 * sizeof(double));
+  int* sCam = reinterpret_cast<int*>(ds_raw + TILE * 36 * sizeof(double));
+  int* sOff = sCam + TILE;      // exclusive pair offsets per observation
+  int* sSeg = sOff + TILE;      // tile-local index of the first observation of the point
+  int* sWarpTot = sSeg + TILE;  // [8]
   const TileThread t = tile_thread(d);
   const size_t n = (size_t)d.n_obs;
-  double W[18];
-  int ci = -1;
   if (t.valid) {
-    ci = __ldg(d.cam + t.i);
-    double jc[12], jp[6];
+    double jc[12], jp[6], W[18], Hi[6];
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
       const double2 v = d.Jc[k * n + t.i];
@@ -695,34 +702,74 @@ __global__ void __launch_bounds__(TILE) dense_schur_kernel(Dev d, const double* 
       jp[k] = v.x; jp[3 + k] = v.y;
     }
 #pragma unroll
-    for (int a = 0; a < 6; ++a)
+    for (int k = 0; k < 6; ++k) Hi[k] = __ldg(Hpp_inv + 6 * (size_t)t.p + k);
+#pragma unroll
+    for (int a = 0; a < 6; ++a) {
 #pragma unroll
       for (int b = 0; b < 3; ++b) W[a * 3 + b] = jc[a] * jp[b] + jc[6 + a] * jp[3 + b];
-#pragma unroll
-    for (int k = 0; k < 18; ++k) sW[threadIdx.x][k] = W[k];
+      double a0, a1, a2;
+      sym3_mul(Hi, W[a * 3], W[a * 3 + 1], W[a * 3 + 2], a0, a1, a2);
+      sA[threadIdx.x][a * 3] = a0; sA[threadIdx.x][a * 3 + 1] = a1; sA[threadIdx.x][a * 3 + 2] = a2;
+      sW[threadIdx.x][a * 3] = W[a * 3]; sW[threadIdx.x][a * 3 + 1] = W[a * 3 + 1]; sW[threadIdx.x][a * 3 + 2] = W[a * 3 + 2];
+    }
+    sCam[threadIdx.x] = __ldg(d.cam + t.i);
   }
-  sCam[threadIdx.x] = ci;
+  // pairs owned by observation i: (i, j) for j = segment start .. i  →  exclusive scan over the tile
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cnt = t.valid ? (t.i - t.seg_b + 1) : 0;
+  int incl = cnt;
+#pragma unroll
+  for (int dd = 1; dd < 32; dd <<= 1) {
+    const int up = __shfl_up_sync(FULL, incl, dd);
+    if (lane >= dd) incl += up;
+  }
+  if (lane == 31) sWarpTot[warp] = incl;
+  sSeg[threadIdx.x] = t.valid ? (t.seg_b - t.tile_b) : 0;
   __syncthreads();
-  if (!t.valid) return;
-  double Hi[6];
+  int warp_off = 0, total_pairs = 0;
 #pragma unroll
-  for (int k = 0; k < 6; ++k) Hi[k] = __ldg(Hpp_inv + 6 * (size_t)t.p + k);
-  double A[18];  // W_i Hpp^-1
-#pragma unroll
-  for (int a = 0; a < 6; ++a) sym3_mul(Hi, W[a * 3], W[a * 3 + 1], W[a * 3 + 2], A[a * 3], A[a * 3 + 1], A[a * 3 + 2]);
+  for (int w = 0; w < TILE / 32; ++w) {
+    const int v = sWarpTot[w];
+    if (w < warp) warp_off += v;
+    total_pairs += v;
+  }
+  sOff[threadIdx.x] = warp_off + incl - cnt;
+  __syncthreads();
   const size_t ld = 6 * (size_t)d.n_cams;
-  for (int j = t.seg_b; j < t.seg_e; ++j) {
-    const int lj = j - t.tile_b;
-    const int cj = sCam[lj];
-    if (cj > ci) continue;
-    double* dst = S + (6 * (size_t)ci) * ld + 6 * (size_t)cj;
+  // every warp takes 8 pairs (288 block elements = 9 full warp passes) at a time, round-robin over the tile:
+  // the work of a long track is spread over all warps
+  for (int base = warp * 8; base < total_pairs; base += (TILE / 32) * 8) {
+    int packed = -1;
+    {
+      const int q = base + (lane & 7);
+      if (q < total_pairs) {
+        int lo = 0, hi = TILE - 1;  // largest i with sOff[i] <= q (ties: the last such i owns pairs)
 #pragma unroll
-    for (int a = 0; a < 6; ++a)
-#pragma unroll
-      for (int b = 0; b < 6; ++b) {
-        const double v = A[a * 3] * sW[lj][b * 3] + A[a * 3 + 1] * sW[lj][b * 3 + 1] + A[a * 3 + 2] * sW[lj][b * 3 + 2];
-        atomicAdd(dst + a * ld + b, -v);
+        for (int it = 0; it < 8; ++it) {
+          const int mid = (lo + hi + 1) >> 1;
+          if (sOff[mid] <= q) lo = mid; else hi = mid - 1;
+        }
+        const int i = lo, j = sSeg[i] + (q - sOff[i]);
+        packed = (i << 16) | j;
       }
+    }
+#pragma unroll
+    for (int pass = 0; pass < 9; ++pass) {
+      const int g = pass * 32 + lane;
+      const int pl = g / 36, e = g - pl * 36;
+      const int ij = __shfl_sync(FULL, packed, pl);
+      if (ij < 0) continue;
+      const int i = ij >> 16, j = ij & 0xffff;
+      const int a = e / 6, b = e - a * 6;
+      const double* Ai = sA[i];
+      const double* Wj = sW[j];
+      double v = Ai[a * 3] * Wj[b * 3] + Ai[a * 3 + 1] * Wj[b * 3 + 1] + Ai[a * 3 + 2] * Wj[b * 3 + 2];
+      const int ci = sCam[i], cj = sCam[j];
+      if (ci == cj && i != j)  // a camera listed twice in a track: the block is diagonal, it needs M + M^T
+        v += Ai[b * 3] * Wj[a * 3] + Ai[b * 3 + 1] * Wj[a * 3 + 1] + Ai[b * 3 + 2] * Wj[a * 3 + 2];
+      double* dst = (ci >= cj) ? S + (6 * (size_t)ci + a) * ld + 6 * (size_t)cj + b : S + (6 * (size_t)cj + b) * ld + 6 * (size_t)ci + a;
+      atomicAdd(dst, -v);
+    }
   }
 }
 
@@ -941,7 +988,12 @@ void launch_dense_init(Problem& P, bool with_diag, cudaStream_t s) {
 
 void launch_dense_schur(Problem& P, cudaStream_t s) {
   if (P.n_tiles == 0) return;
-  dense_schur_kernel<<<P.n_tiles, TILE, 0, s>>>(P.d, P.Hpp_inv, P.S);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(dense_schur_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDenseSchurSmem);
+    attr_set = true;
+  }
+  dense_schur_kernel<<<P.n_tiles, TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S);
   P.launches++;
 }
 

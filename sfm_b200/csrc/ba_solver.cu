@@ -25,10 +25,30 @@ struct Driver {
   Driver(Ctx& c, const hsfm_ba_options& opt)
       : ctx(c), P(c.prob), s(c.stream), o(opt), cams_free(c.prob.mode != 0), pts_free(c.prob.mode != 1), dense(false) {}
 
+  // phase timing: mark(p) says "phase p starts here"; elapsed times between consecutive marks are
+  // summed per phase after the solve.
+  std::vector<int> marks;
+  void mark(int phase) {
+    if (marks.size() >= ctx.phase_events.size()) {
+      cudaEvent_t e;
+      if (cudaEventCreate(&e) != cudaSuccess) return;
+      ctx.phase_events.push_back(e);
+    }
+    cudaEventRecord(ctx.phase_events[marks.size()], s);
+    marks.push_back(phase);
+  }
+  void collect(double* phase_ms) {
+    for (size_t k = 0; k + 1 < marks.size(); ++k) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, ctx.phase_events[k], ctx.phase_events[k + 1]) == cudaSuccess) phase_ms[marks[k]] += ms;
+    }
+  }
+
   bool multi() const { return ctx.comm.n_ranks > 1; }
   void chk(int r) { if (r && !rc) rc = r; }
 
   int read_back() {
+    mark(5);
     HSFM_CUDA(cudaMemcpyAsync(P.scal_host, P.scal, sizeof(double) * 16, cudaMemcpyDeviceToHost, s));
     HSFM_CUDA(cudaMemcpyAsync(P.flags_host, P.flags, sizeof(int) * FLAG_SLOTS, cudaMemcpyDeviceToHost, s));
     HSFM_CUDA(cudaStreamSynchronize(s));
@@ -37,6 +57,7 @@ struct Driver {
 
   // Jacobi column scaling from the unscaled Jacobian at the initial point (A.3 "iter 0").
   void compute_scaling() {
+    mark(0);
     launch_cam_prep(P, P.cam_x, nullptr, P.rows_x, s);
     launch_rj(P, P.rows_x, P.pts_x, nullptr, /*write_j=*/false, /*form=*/true, s);
     launch_cam_major(P, P.rows_x, P.pts_x, nullptr, 0, s);
@@ -46,6 +67,7 @@ struct Driver {
 
   // r, J (scaled), cost, point blocks, camera blocks, gradient norm at the current x.
   void linearize() {
+    mark(0);
     launch_cam_prep(P, P.cam_x, P.scale_c, P.rows_x, s);
     launch_rj(P, P.rows_x, P.pts_x, P.scale_p, true, true, s);
     launch_cam_major(P, P.rows_x, P.pts_x, P.scale_p, 0, s);
@@ -64,6 +86,7 @@ struct Driver {
   // One linear solve + candidate evaluation.  Leaves scalars/flags on the host mirrors.
   int attempt(double radius, int* linear_its) {
     *linear_its = 0;
+    mark(1);
     HSFM_CUDA(cudaMemsetAsync(P.flags, 0, sizeof(int) * FLAG_SLOTS, s));
     if (pts_free) launch_point_invert(P, radius, o.min_lm_diagonal, o.max_lm_diagonal, s);
     if (cams_free) launch_cam_diag(P, radius, o.min_lm_diagonal, o.max_lm_diagonal, s);
@@ -78,7 +101,9 @@ struct Driver {
           chk(ctx.comm.allreduce_sum(P.S, (size_t)n6 * n6, s));
           chk(ctx.comm.allreduce_sum(P.rhs, n6, s));
         }
+        mark(2);
         launch_cholesky(P.S, n6, P.S + (size_t)n6 * n6, P.flags + F_CHOL_FAIL, s, &ctx.chol_aux, &P.launches);
+        mark(3);
         HSFM_CUDA(cudaMemcpyAsync(P.yc, P.rhs, sizeof(double) * n6, cudaMemcpyDeviceToDevice, s));
         launch_chol_solve(P.S, n6, P.S + (size_t)n6 * n6, P.yc, s, &P.launches);
       } else {
@@ -87,6 +112,7 @@ struct Driver {
         launch_precond_invert(P, true, s);
         launch_schur_rhs(P, lead, s);
         if (multi()) chk(ctx.comm.allreduce_sum(P.rhs, n6, s));
+        mark(3);
         launch_pcg_init(P, s);
         const int batch = 8;
         int issued = 0;
@@ -107,6 +133,7 @@ struct Driver {
       launch_precond_invert(P, false, s);
       launch_block_solve_cams(P, s);
     }
+    mark(4);
     launch_cam_step(P, s);
     launch_cam_prep(P, P.cam_c, P.scale_c, P.rows_c, s);
     launch_backsub(P, s);
@@ -261,8 +288,10 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
       }
     }
   }
+  D.mark(7);
   HSFM_CUDA(cudaEventRecord(ev1, s));
   HSFM_CUDA(cudaEventSynchronize(ev1));
+  D.collect(S.phase_ms);
   float ms = 0.f;
   cudaEventElapsedTime(&ms, ev0, ev1);
   cudaEventDestroy(ev0);
