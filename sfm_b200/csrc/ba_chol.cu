@@ -21,7 +21,6 @@ namespace {
 constexpr int NB = 128;          // panel width / tile edge
 constexpr int KC = 32;           // K chunk staged per pipeline stage
 constexpr int LDS_ = KC + 4;     // padded shared-memory row stride (doubles): conflict-free DMMA fragment loads
-constexpr int DIAG_LD = NB + 1;
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
   const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
@@ -36,111 +35,222 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
 }
 
 // ---------------------------------------------------------------------------------------------
-// 1. diagonal block: factor + inverse
+// 1. diagonal block: factor + inverse, one CTA, blocked 4 x 32
 // ---------------------------------------------------------------------------------------------
-// Thread (ty,tx) of a 16×16 grid owns elements (ty+16a, tx+16b), a,b = 0..7, in registers.
-// Step j publishes column j (unscaled, including the pivot) to shared memory; one barrier per
-// step; every thread rescales by 1/sqrt(pivot) on the fly.
-__global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, int n, int k0, int kb, double* __restrict__ Linv,
-                                                         int* __restrict__ fail) {
-  extern __shared__ double dsm[];
-  double* s = dsm;                       // [NB][DIAG_LD]  L (lower, incl. diagonal) ; Linv^T (strict upper)
-  double* tmp = dsm + NB * DIAG_LD;      // [4096]
-  double* dinv = tmp + 4096;             // [NB]
-  double* col = dinv + NB;               // [2][NB]
-  if (*fail) return;
-  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
-  double r[8][8];
+// The 128x128 block lives in shared memory as its ten lower 32x32 sub-blocks (row stride 36 doubles:
+// DMMA fragment loads in either orientation are bank-conflict free).  Per sub-block column kb:
+//   warp 0 factors the 32x32 diagonal sub-block in registers (one row per lane, shuffles, no barrier),
+//   one thread per row solves the sub-panel below it by substitution,
+//   all eight warps apply the trailing update with DMMA tiles.
+// L11^-1 then follows by block forward substitution: four warps invert the diagonal sub-blocks in
+// registers, three levels of DMMA block products fill the sub-diagonals.  ~128 barrier-separated column
+// steps of the previous version become ~20 phases.
+constexpr int SB = 32;             // sub-block edge
+constexpr int LB = SB + 4;         // sub-block row stride in shared memory (doubles)
+constexpr int SBLK = SB * LB;      // doubles per stored sub-block
+__device__ __forceinline__ constexpr int blk_id(int bi, int bj) { return bi * (bi + 1) / 2 + bj; }  // bj <= bi
+
+// One 8x8 tile of A(32xK=32 block, rows m) * B over the full K = 32.  B_KN: B is stored [k][n], else [n][k].
+template <bool B_KN>
+__device__ __forceinline__ void tile_mma32(double& c0, double& c1, const double* __restrict__ A, const double* __restrict__ B, int ti, int tj,
+                                           int lane) {
+  const int fr = lane >> 2, fk = lane & 3;
 #pragma unroll
-  for (int a = 0; a < 8; ++a)
-#pragma unroll
-    for (int b = 0; b < 8; ++b) {
-      const int i = ty + 16 * a, j = tx + 16 * b;
-      double v = (i == j) ? 1.0 : 0.0;
-      if (i < kb && j < kb) v = (j <= i) ? A[(size_t)(k0 + i) * n + k0 + j] : 0.0;
-      r[a][b] = v;
-    }
-#pragma unroll
-  for (int jb = 0; jb < 8; ++jb) {
-    for (int jj = 0; jj < 16; ++jj) {
-      const int j = jb * 16 + jj;
-      double* cj = col + (j & 1) * NB;
-      if (tx == jj) {
-#pragma unroll
-        for (int a = jb; a < 8; ++a) cj[ty + 16 * a] = r[a][jb];
-      }
-      __syncthreads();
-      const double piv = cj[j];
-      if (!(piv > 0.0) || !isfinite(piv)) {
-        if (tid == 0) atomicExch(fail, k0 + j + 1);
-        return;  // uniform
-      }
-      const double inv_d = 1.0 / sqrt(piv);
-      double lr[8], lc[8];
-#pragma unroll
-      for (int a = jb; a < 8; ++a) lr[a] = cj[ty + 16 * a] * inv_d;
-#pragma unroll
-      for (int b = jb; b < 8; ++b) lc[b] = cj[tx + 16 * b] * inv_d;
-      if (tx == jj) {
-#pragma unroll
-        for (int a = jb; a < 8; ++a)
-          if (ty + 16 * a >= j) r[a][jb] = (ty + 16 * a == j) ? piv * inv_d : lr[a];
-      }
-#pragma unroll
-      for (int a = jb; a < 8; ++a)
-#pragma unroll
-        for (int b = jb; b < 8; ++b) {
-          const int i = ty + 16 * a, c = tx + 16 * b;
-          if (c > j && i >= c) r[a][b] -= lr[a] * lc[b];
-        }
-    }
-  }
-  // L to shared (lower incl. diag; strict upper zero) and to global
-#pragma unroll
-  for (int a = 0; a < 8; ++a)
-#pragma unroll
-    for (int b = 0; b < 8; ++b) {
-      const int i = ty + 16 * a, j = tx + 16 * b;
-      s[i * DIAG_LD + j] = (j <= i) ? r[a][b] : 0.0;
-      if (i < kb && j <= i && j < kb) A[(size_t)(k0 + i) * n + k0 + j] = r[a][b];
-    }
-  __syncthreads();
-  if (tid < NB) dinv[tid] = 1.0 / s[tid * DIAG_LD + tid];
-  __syncthreads();
-  // Linv by recursive doubling: inv([[A,0],[C,B]]) = [[A^-1,0],[-B^-1 C A^-1, B^-1]].
-  // Linv(i,j), i>j is kept transposed in the strict upper triangle: s[j][i]; Linv(i,i) = dinv[i].
-  for (int h = 1; h < NB; h <<= 1) {
-    const int total = NB * h / 2;  // (NB/(2h)) blocks × h×h
-    // stage 1: T(k,j) = sum_{l in A, l>=j} L(k,l) Linv(l,j)   k in B, j in A
-    for (int e = tid; e < total; e += 256) {
-      const int blk = e / (h * h), rem = e - blk * h * h;
-      const int kk = rem / h, jj = rem - kk * h;
-      const int o = blk * 2 * h;
-      const int k = o + h + kk, j = o + jj;
-      double acc = s[k * DIAG_LD + j] * dinv[j];
-      for (int l = j + 1; l < o + h; ++l) acc += s[k * DIAG_LD + l] * s[j * DIAG_LD + l];
-      tmp[e] = acc;
-    }
-    __syncthreads();
-    // stage 2: X(i,j) = -sum_{k in B, k<=i} Linv(i,k) T(k,j)
-    for (int e = tid; e < total; e += 256) {
-      const int blk = e / (h * h), rem = e - blk * h * h;
-      const int ii = rem / h, jj = rem - ii * h;
-      const int o = blk * 2 * h;
-      const int i = o + h + ii, j = o + jj;
-      const double* T = tmp + blk * h * h;
-      double acc = dinv[i] * T[ii * h + jj];
-      for (int kk = 0; kk < ii; ++kk) acc += s[(o + h + kk) * DIAG_LD + i] * T[kk * h + jj];
-      s[j * DIAG_LD + i] = -acc;
-    }
-    __syncthreads();
-  }
-  for (int e = tid; e < NB * NB; e += 256) {
-    const int i = e >> 7, j = e & 127;
-    Linv[e] = (i > j) ? s[j * DIAG_LD + i] : (i == j ? dinv[i] : 0.0);
+  for (int ks = 0; ks < SB / 4; ++ks) {
+    const double a = A[(ti * 8 + fr) * LB + ks * 4 + fk];
+    const double b = B_KN ? B[(ks * 4 + fk) * LB + tj * 8 + fr] : B[(tj * 8 + fr) * LB + ks * 4 + fk];
+    dmma884(c0, c1, a, b);
   }
 }
-constexpr int kDiagSmem = (NB * DIAG_LD + 4096 + NB + 2 * NB) * (int)sizeof(double);
+
+// Cholesky of a 32x32 sub-block by one warp.  Lane r keeps the not-yet-eliminated part of row r in a
+// register window that shifts left by one column per step, so the step body is the same ~100
+// instructions for every column (a fully unrolled triangle would be ~6000 instructions executed once —
+// instruction-fetch bound).  The pivot column is broadcast through `col` (64 doubles of shared memory,
+// written twice so that col[j+c] needs no wrap).  D (row stride LB) receives L (strict upper zeroed),
+// dinv[r] = 1/L[r][r].  Returns 0 or the 1-based failing column.
+__device__ __forceinline__ int warp_chol32(double* __restrict__ D, double* __restrict__ col, double* __restrict__ dinv, int lane) {
+  double a[SB];
+#pragma unroll
+  for (int c = 0; c < SB; ++c) a[c] = D[lane * LB + c];
+  int bad = 0;
+#pragma unroll 1
+  for (int j = 0; j < SB; ++j) {
+    col[lane] = a[0];
+    col[lane + SB] = a[0];
+    __syncwarp();
+    const double d = col[j];
+    if (!(d > 0.0) || !isfinite(d)) { bad = j + 1; break; }  // uniform
+    const double inv = rsqrt(d);
+    const double u = a[0] * (inv * inv);
+    double l = a[0] * inv;
+    if (lane == j) { l = d * inv; dinv[j] = inv; }
+    D[lane * LB + j] = (lane >= j) ? l : 0.0;
+#pragma unroll
+    for (int c = 1; c < SB; ++c) a[c - 1] = fma(-u, col[j + c], a[c]);  // columns past 31 hold don't-care values
+    __syncwarp();
+  }
+  return bad;
+}
+
+// Inverse of the lower-triangular 32x32 sub-block D by one warp, written to X (both row stride LB).
+// Row k of the inverse is final at step k; lane k publishes it in X and the lanes below eliminate it.
+__device__ __forceinline__ void warp_trinv32(const double* __restrict__ D, double my_dinv, double* __restrict__ X, int lane) {
+  double x[SB];
+#pragma unroll
+  for (int c = 0; c < SB; ++c) x[c] = (c == lane) ? 1.0 : 0.0;
+#pragma unroll 1
+  for (int k = 0; k < SB; ++k) {
+    if (lane == k) {
+#pragma unroll
+      for (int c = 0; c < SB; c += 2)
+        *reinterpret_cast<double2*>(X + k * LB + c) = make_double2(x[c] * my_dinv, x[c + 1] * my_dinv);
+    }
+    __syncwarp();
+    if (lane > k) {
+      const double lrk = D[lane * LB + k];
+#pragma unroll
+      for (int c = 0; c < SB; c += 2) {
+        const double2 xk = *reinterpret_cast<const double2*>(X + k * LB + c);
+        x[c] = fma(-lrk, xk.x, x[c]);
+        x[c + 1] = fma(-lrk, xk.y, x[c + 1]);
+      }
+    }
+  }
+}
+
+constexpr int kDiagSmem = (20 * SBLK + 3 * SBLK + NB) * (int)sizeof(double) + 16;
+
+__global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, int n, int k0, int kb, double* __restrict__ Linv,
+                                                         int* __restrict__ fail) {
+  extern __shared__ __align__(16) double dsm[];
+  double* sL = dsm;                 // [10][32][LB] lower sub-blocks of the matrix, then of L
+  double* sX = sL + 10 * SBLK;      // [10][32][LB] lower sub-blocks of L^-1
+  double* sT = sX + 10 * SBLK;      // [3][32][LB]  block-product temporaries
+  double* sDinv = sT + 3 * SBLK;    // [128] 1 / L[i][i]
+  int* sBad = reinterpret_cast<int*>(sDinv + NB);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int failed = *fail;
+  if (tid == 0) *sBad = 0;
+  // load the lower sub-blocks (identity beyond kb; strict upper of the diagonal sub-blocks zero)
+  for (int e = tid; e < 10 * SB * (SB / 2); e += 256) {
+    const int blk = e / (SB * (SB / 2)), rem = e - blk * (SB * (SB / 2));
+    const int r = rem / (SB / 2), c = (rem - r * (SB / 2)) * 2;
+    int bi = 0;
+    while (blk_id(bi + 1, 0) <= blk) ++bi;
+    const int bj = blk - blk_id(bi, 0);
+    const int i = bi * SB + r, j = bj * SB + c;
+    double2 v = make_double2(0.0, 0.0);
+    if (i < kb && j + 1 < kb) v = *reinterpret_cast<const double2*>(A + (size_t)(k0 + i) * n + k0 + j);
+    else if (i < kb && j < kb) v.x = A[(size_t)(k0 + i) * n + k0 + j];
+    if (j > i) v.x = 0.0;
+    if (j + 1 > i) v.y = 0.0;
+    if (i >= kb) { v.x = (i == j) ? 1.0 : 0.0; v.y = (i == j + 1) ? 1.0 : 0.0; }
+    *reinterpret_cast<double2*>(sL + blk * SBLK + r * LB + c) = v;
+  }
+  __syncthreads();
+  if (failed) return;
+#pragma unroll 1
+  for (int kq = 0; kq < 4; ++kq) {
+    // (a) diagonal sub-block, warp 0
+    if (warp == 0) {
+      const int bad = warp_chol32(sL + blk_id(kq, kq) * SBLK, sT, sDinv + kq * SB, lane);
+      if (bad && lane == 0) { *sBad = 1; atomicExch(fail, k0 + kq * SB + bad); }
+    }
+    __syncthreads();
+    if (*sBad) return;
+    if (kq == 3) break;
+    // (b) sub-panel: rows below, X D^T = P by substitution, one thread per row
+    {
+      const int rows = (3 - kq) * SB;
+      if (tid < rows) {
+        const int bi = kq + 1 + tid / SB, r = tid % SB;
+        double* P = sL + blk_id(bi, kq) * SBLK + r * LB;
+        const double* D = sL + blk_id(kq, kq) * SBLK;
+        double x[SB];
+#pragma unroll
+        for (int c = 0; c < SB; ++c) x[c] = P[c];
+#pragma unroll
+        for (int c = 0; c < SB; ++c) {
+          double s0 = x[c], s1 = 0.0;
+#pragma unroll
+          for (int k = 0; k + 1 < c; k += 2) {
+            s0 = fma(-x[k], D[c * LB + k], s0);
+            s1 = fma(-x[k + 1], D[c * LB + k + 1], s1);
+          }
+          if (c & 1) s0 = fma(-x[c - 1], D[c * LB + c - 1], s0);
+          x[c] = (s0 + s1) * sDinv[kq * SB + c];
+        }
+#pragma unroll
+        for (int c = 0; c < SB; ++c) P[c] = x[c];
+      }
+    }
+    __syncthreads();
+    // (c) trailing update: L(bi,bj) -= L(bi,kq) L(bj,kq)^T for kq < bj <= bi, 16 tiles of 8x8 per sub-block
+    {
+      const int m = 3 - kq, ntiles = m * (m + 1) / 2 * 16;
+      for (int t = warp; t < ntiles; t += 8) {
+        const int b = t >> 4, tile = t & 15;
+        int di = 0;
+        while ((di + 1) * (di + 2) / 2 <= b) ++di;
+        const int dj = b - di * (di + 1) / 2;
+        const int bi = kq + 1 + di, bj = kq + 1 + dj;
+        const int ti = tile >> 2, tj = tile & 3;
+        double c0 = 0.0, c1 = 0.0;
+        tile_mma32<false>(c0, c1, sL + blk_id(bi, kq) * SBLK, sL + blk_id(bj, kq) * SBLK, ti, tj, lane);
+        double2* dst = reinterpret_cast<double2*>(sL + blk_id(bi, bj) * SBLK + (ti * 8 + (lane >> 2)) * LB + tj * 8 + 2 * (lane & 3));
+        double2 v = *dst;
+        v.x -= c0; v.y -= c1;
+        *dst = v;
+      }
+    }
+    __syncthreads();
+  }
+  // ---- L^-1 ----
+  // diagonal sub-blocks: warps 0..3, in registers
+  if (warp < 4) {
+    warp_trinv32(sL + blk_id(warp, warp) * SBLK, sDinv[warp * SB + lane], sX + blk_id(warp, warp) * SBLK, lane);
+  }
+  __syncthreads();
+  // sub-diagonal d: X(i,j) = -X(i,i) * sum_{k=j}^{i-1} L(i,k) X(k,j),  j = i - d
+#pragma unroll 1
+  for (int d = 1; d < 4; ++d) {
+    const int nb = 4 - d;  // sub-blocks on this sub-diagonal
+    for (int t = warp; t < nb * 16; t += 8) {
+      const int b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
+      const int i = d + b, j = b;
+      double c0 = 0.0, c1 = 0.0;
+      for (int k = j; k < i; ++k) tile_mma32<true>(c0, c1, sL + blk_id(i, k) * SBLK, sX + blk_id(k, j) * SBLK, ti, tj, lane);
+      *reinterpret_cast<double2*>(sT + b * SBLK + (ti * 8 + (lane >> 2)) * LB + tj * 8 + 2 * (lane & 3)) = make_double2(c0, c1);
+    }
+    __syncthreads();
+    for (int t = warp; t < nb * 16; t += 8) {
+      const int b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
+      const int i = d + b, j = b;
+      double c0 = 0.0, c1 = 0.0;
+      tile_mma32<true>(c0, c1, sX + blk_id(i, i) * SBLK, sT + b * SBLK, ti, tj, lane);
+      *reinterpret_cast<double2*>(sX + blk_id(i, j) * SBLK + (ti * 8 + (lane >> 2)) * LB + tj * 8 + 2 * (lane & 3)) = make_double2(-c0, -c1);
+    }
+    __syncthreads();
+  }
+  // ---- write back: L over the lower triangle of A, L^-1 as a full 128x128 row-major block ----
+  for (int e = tid; e < NB * (NB / 2); e += 256) {
+    const int i = e / (NB / 2), j = (e - i * (NB / 2)) * 2;
+    const int bi = i / SB, bj = j / SB;
+    double2 lv = make_double2(0.0, 0.0), xv = make_double2(0.0, 0.0);
+    if (bj <= bi) {
+      const int off = blk_id(bi, bj) * SBLK + (i % SB) * LB + (j % SB);
+      lv = *reinterpret_cast<const double2*>(sL + off);
+      xv = *reinterpret_cast<const double2*>(sX + off);
+    }
+    reinterpret_cast<double2*>(Linv)[e] = xv;  // sub-blocks hold zeros above the diagonal already
+    if (i < kb && j <= i) {
+      double* dst = A + (size_t)(k0 + i) * n + k0 + j;
+      if (j + 1 <= i && j + 1 < kb) *reinterpret_cast<double2*>(dst) = lv;
+      else dst[0] = lv.x;
+    }
+  }
+}
 
 // ---------------------------------------------------------------------------------------------
 // 2./3. 128×64 tile of  C = A B^T  on DMMA.  K = 128 in four chunks of 32, double-buffered with
