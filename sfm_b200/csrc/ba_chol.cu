@@ -13,6 +13,9 @@
 // DMMA is the tensor-core instruction this workload can use (north_star: "tensor cores only for the
 // dense Cholesky").  The stored L11^-1 blocks also turn the two triangular solves into mat-vecs.
 // A non-positive pivot raises *fail; later kernels of the same factorisation return immediately.
+#include <cstdio>
+#include <cstdlib>
+
 #include "ba_internal.h"
 
 namespace hsfm {
@@ -119,6 +122,13 @@ __device__ __forceinline__ void warp_trinv32(const double* __restrict__ D, doubl
   }
 }
 
+#ifdef HSFM_DIAG_TIMING
+__device__ long long g_diag_clk[32];
+#define DIAG_TICK(k) do { if (threadIdx.x == 0) g_diag_clk[k] = clock64(); } while (0)
+#else
+#define DIAG_TICK(k) do { } while (0)
+#endif
+
 constexpr int kDiagSmem = (20 * SBLK + 3 * SBLK + NB) * (int)sizeof(double) + 16;
 
 __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, int n, int k0, int kb, double* __restrict__ Linv,
@@ -132,6 +142,7 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int failed = *fail;
   if (tid == 0) *sBad = 0;
+  DIAG_TICK(0);
   // load the lower sub-blocks (identity beyond kb; strict upper of the diagonal sub-blocks zero)
   for (int e = tid; e < 10 * SB * (SB / 2); e += 256) {
     const int blk = e / (SB * (SB / 2)), rem = e - blk * (SB * (SB / 2));
@@ -150,6 +161,7 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
   }
   __syncthreads();
   if (failed) return;
+  DIAG_TICK(1);
 #pragma unroll 1
   for (int kq = 0; kq < 4; ++kq) {
     // (a) diagonal sub-block, warp 0
@@ -159,6 +171,7 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
     }
     __syncthreads();
     if (*sBad) return;
+    DIAG_TICK(2 + 3 * kq);
     if (kq == 3) break;
     // (b) sub-panel: rows below, X D^T = P by substitution, one thread per row
     {
@@ -186,6 +199,7 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
       }
     }
     __syncthreads();
+    DIAG_TICK(3 + 3 * kq);
     // (c) trailing update: L(bi,bj) -= L(bi,kq) L(bj,kq)^T for kq < bj <= bi, 16 tiles of 8x8 per sub-block
     {
       const int m = 3 - kq, ntiles = m * (m + 1) / 2 * 16;
@@ -205,6 +219,7 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
       }
     }
     __syncthreads();
+    DIAG_TICK(4 + 3 * kq);
   }
   // ---- L^-1 ----
   // diagonal sub-blocks: warps 0..3, in registers
@@ -212,6 +227,7 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
     warp_trinv32(sL + blk_id(warp, warp) * SBLK, sDinv[warp * SB + lane], sX + blk_id(warp, warp) * SBLK, lane);
   }
   __syncthreads();
+  DIAG_TICK(12);
   // sub-diagonal d: X(i,j) = -X(i,i) * sum_{k=j}^{i-1} L(i,k) X(k,j),  j = i - d
 #pragma unroll 1
   for (int d = 1; d < 4; ++d) {
@@ -232,6 +248,7 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
       *reinterpret_cast<double2*>(sX + blk_id(i, j) * SBLK + (ti * 8 + (lane >> 2)) * LB + tj * 8 + 2 * (lane & 3)) = make_double2(-c0, -c1);
     }
     __syncthreads();
+    DIAG_TICK(12 + d);
   }
   // ---- write back: L over the lower triangle of A, L^-1 as a full 128x128 row-major block ----
   for (int e = tid; e < NB * (NB / 2); e += 256) {
@@ -250,21 +267,23 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
       else dst[0] = lv.x;
     }
   }
+  __syncthreads();
+  DIAG_TICK(16);
 }
 
 // ---------------------------------------------------------------------------------------------
-// 2./3. 128×64 tile of  C = A B^T  on DMMA.  K = 128 in four chunks of 32, double-buffered with
-// cp.async.  4 warps as 2×2, each 64×32 = 8×4 DMMA tiles (m8n8k4), so 64 FP64 accumulators per
-// lane.  110 KB of shared memory and 128 threads per CTA => two CTAs per SM, whose prologues
-// (first cp.async chunk, C prefetch) and epilogues hide behind each other's main loops.
-//   MODE 0 (TRSM): A = A21 rows, B = 64 rows of L11^-1  →  C goes to a packed scratch panel
-//                  (the two column halves of a row tile are produced by different CTAs that both
-//                  read the whole row tile, so the result cannot overwrite A21 in place);
-//                  chol_panel_copy_kernel then moves it over A21.
-//   MODE 1 (SYRK): A = L21 rows of row tile bi, B = L21 rows of 64-column block bj
-//                  →  S[bi,bj] -= C.  Accumulators start at C (prefetched while the first chunk is
-//                  in flight), the main loop feeds negated A fragments, the epilogue stores: no
-//                  read-modify-write at the end.
+// 3. Trailing update  S[bi,bj] -= L21[bi] L21[bj]^T  on DMMA: 128×64 output tiles, K = 128 (the panel) in four
+// chunks of 32 staged through shared memory.  PERSISTENT: the grid is (at most) two CTAs per SM and every CTA
+// walks tiles t = blockIdx.x, blockIdx.x + gridDim.x, …; the two-stage cp.async ring runs straight across
+// tile boundaries (the first chunk of the next tile streams in while the last chunk of this one is in the
+// tensor pipe) and the next tile's C is pulled into L2 a whole tile ahead, so the only exposed latency per
+// tile is one L2 round trip for the accumulator preload.  4 warps as 2×2, each 64×32 = 8×4 DMMA tiles
+// (m8n8k4): 64 FP64 accumulators per lane that START at C; the loop feeds NEGATED A fragments (free operand
+// modifier), so the epilogue is a plain store — no read-modify-write, no arithmetic between the 32
+// independent accumulator loads (they stay in flight together).
+// Tile sets (64-wide column blocks cb, 128-row tiles bi, relative to the trailing matrix):
+//   col_first >= 0 : row tiles row_first.., column blocks {col_first, col_first+1}   (2 tiles per row tile)
+//   col_first <  0 : bulk — column blocks c0 = -col_first (even, >= 2) and beyond, lower tiles only
 // ---------------------------------------------------------------------------------------------
 constexpr int TN = 64;  // tile columns
 struct GemmSmem {
@@ -287,123 +306,240 @@ __device__ __forceinline__ void load_tile_async(double (*dst)[LDS_], const doubl
   }
 }
 
-// Tile selection of a SYRK launch:
-//   col_first >= 0 : row tiles row_first.., column blocks {col_first, col_first+1}   (2 CTAs per row tile)
-//   col_first <  0 : every lower tile whose column block is >= 2 (the first 128 columns of the
-//                    trailing matrix belong to the look-ahead launch)
-template <int MODE>
-__global__ void __launch_bounds__(128, 2) chol_gemm_kernel(double* __restrict__ S, int n, int k0, const double* __restrict__ Linv,
-                                                           double* __restrict__ panel_out, int row_first, int col_first,
-                                                           const int* __restrict__ fail) {
+struct SyrkTile { int ri, ni, rj, nj; };
+__device__ __forceinline__ SyrkTile syrk_tile(int t, int n, int base, int row_first, int col_first) {
+  int bi, bj;
+  if (col_first >= 0) {
+    bi = row_first + (t >> 1); bj = col_first + (t & 1);
+  } else {
+    // with h = c0/2 - 1, row tile bi = q + h (q >= 1) owns column blocks c0 .. 2*bi+1 → 2q tiles; before row q: q(q-1)
+    const int c0 = -col_first, h = c0 / 2 - 1;
+    int q = (int)((1.0f + sqrtf(1.0f + 4.0f * (float)t)) * 0.5f);
+    while (q * (q + 1) <= t) ++q;
+    while (q * (q - 1) > t) --q;
+    bi = q + h;
+    bj = c0 + (t - q * (q - 1));
+  }
+  SyrkTile T;
+  T.ri = base + bi * NB; T.ni = min(NB, n - T.ri);
+  T.rj = base + bj * TN; T.nj = min(TN, n - T.rj);
+  return T;
+}
+
+__global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ S, int n, int k0, int row_first, int col_first, int n_tiles,
+                                                           int stagger, const int* __restrict__ fail) {
   extern __shared__ __align__(16) unsigned char gsm_raw[];
   GemmSmem& sm = *reinterpret_cast<GemmSmem*>(gsm_raw);
-  const int failed = *fail;  // consumed after the prologue loads are in flight
+  int t = blockIdx.x;
+  if (t >= n_tiles) return;
+  const int failed = *fail;
   const int base = k0 + NB;
-  int bi, bj;  // row tile (128 rows), column block (64 columns)
-  if (MODE == 0) {
-    bi = blockIdx.x >> 1; bj = blockIdx.x & 1;
-  } else if (col_first >= 0) {
-    bi = row_first + (blockIdx.x >> 1); bj = col_first + (blockIdx.x & 1);
-  } else {
-    // row tile bi (>= 1) owns column blocks 2 .. 2*bi+1 → 2*bi tiles; tiles before row bi: bi*(bi-1)
-    const int t = blockIdx.x;
-    bi = (int)((1.0f + sqrtf(1.0f + 4.0f * (float)t)) * 0.5f);
-    while (bi * (bi + 1) <= t) ++bi;
-    while (bi * (bi - 1) > t) --bi;
-    bj = 2 + (t - bi * (bi - 1));
-  }
-  const int ri = base + bi * NB;
-  const int ni = min(NB, n - ri);
-  const int rj = (MODE == 0) ? bj * TN : base + bj * TN;  // B rows: of Linv, or of S
-  const int nj = (MODE == 0) ? TN : min(TN, n - rj);
-  const double* Bsrc = (MODE == 0) ? Linv : S;
-  const int ldb = (MODE == 0) ? NB : n;
-  const int kb0 = (MODE == 0) ? 0 : k0;
-
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int wr = warp >> 1, wc = warp & 1;  // 2 × 2 warps, 64 × 32 each
   const int fr = lane >> 2, fk = lane & 3;
 
-  load_tile_async<NB>(sm.a[0], S, n, ri, ni, k0);
-  load_tile_async<TN>(sm.b[0], Bsrc, ldb, rj, nj, kb0);
+  // All CTAs of a launch start together; left alone, the two CTAs of an SM (and the whole GPU) stay in
+  // phase — everyone loads C at once, then everyone shares the DMMA pipe at half speed.  Delaying the second
+  // half of the grid by half a tile time puts the co-resident CTAs in anti-phase (a stable state: one streams
+  // its C tile while the other owns the tensor pipe), which also spreads the HBM traffic evenly in time.
+  if (stagger && n_tiles > 2 * (int)gridDim.x && blockIdx.x >= gridDim.x / 2) {
+    const long long t0 = clock64();
+    while (clock64() - t0 < 16000) { }
+  }
+  SyrkTile cur = syrk_tile(t, n, base, row_first, col_first);
+  load_tile_async<NB>(sm.a[0], S, n, cur.ri, cur.ni, k0);
+  load_tile_async<TN>(sm.b[0], S, n, cur.rj, cur.nj, k0);
   cp_async_commit();
-
-  // Accumulators start at C itself (SYRK); the main loop feeds NEGATED A fragments, so the result is
-  // C - A B^T with no arithmetic between the 32 independent 16-byte loads (they all stay in flight
-  // together; a negation here made ptxas serialise them through one temporary).
-  double acc[8][4][2];
-#pragma unroll
-  for (int a = 0; a < 8; ++a)
-#pragma unroll
-    for (int b = 0; b < 4; ++b) {
-      acc[a][b][0] = 0.0; acc[a][b][1] = 0.0;
-      if (MODE == 1) {
-        const int row = wr * 64 + a * 8 + fr, col = wc * 32 + b * 8 + 2 * fk;
-        if (row < ni && col < nj) {
-          const double2 c = __ldcs(reinterpret_cast<const double2*>(S + (size_t)(ri + row) * n + rj + col));
-          acc[a][b][0] = c.x; acc[a][b][1] = c.y;
-        }
-      }
-    }
   if (failed) { cp_async_wait<0>(); return; }
+  int stage = 0;
 #pragma unroll 1
-  for (int ch = 0; ch < NB / KC; ++ch) {
-    const int cur = ch & 1;
-    if (ch + 1 < NB / KC) {
-      load_tile_async<NB>(sm.a[cur ^ 1], S, n, ri, ni, k0 + (ch + 1) * KC);
-      load_tile_async<TN>(sm.b[cur ^ 1], Bsrc, ldb, rj, nj, kb0 + (ch + 1) * KC);
-      cp_async_commit();
-      cp_async_wait<1>();
-    } else {
-      cp_async_wait<0>();
-    }
-    __syncthreads();
-#pragma unroll
-    for (int ks = 0; ks < KC / 4; ++ks) {
-      double af[8], bf[4];
-#pragma unroll
-      for (int a = 0; a < 8; ++a) {
-        const double v = sm.a[cur][wr * 64 + a * 8 + fr][ks * 4 + fk];
-        af[a] = (MODE == 1) ? -v : v;
-      }
-#pragma unroll
-      for (int b = 0; b < 4; ++b) bf[b] = sm.b[cur][wc * 32 + b * 8 + fr][ks * 4 + fk];
+  for (; t < n_tiles; t += gridDim.x) {
+    const int t_next = t + gridDim.x;
+    const bool has_next = t_next < n_tiles;
+    SyrkTile nxt = cur;
+    if (has_next) nxt = syrk_tile(t_next, n, base, row_first, col_first);
+    // C → accumulators.  Full tiles take an unpredicated path: one row pointer per 8-row group, the four
+    // column tiles at immediate offsets, every load straight into its accumulator pair — nothing recycles a
+    // register, so all 32 loads are in flight at once.
+    double acc[8][4][2];
+    double* const crow = S + (size_t)(cur.ri + wr * 64 + fr) * n + cur.rj + wc * 32 + 2 * fk;
+    const size_t rstep = 8 * (size_t)n;
+    const bool full = (cur.ni == NB) && (cur.nj == TN);
+#ifdef HSFM_SYRK_NOLOAD
+    if (full) {
 #pragma unroll
       for (int a = 0; a < 8; ++a)
 #pragma unroll
-        for (int b = 0; b < 4; ++b) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+        for (int b = 0; b < 4; ++b) { acc[a][b][0] = 0.0; acc[a][b][1] = 0.0; }
+    } else
+#endif
+    if (full) {
+#pragma unroll
+      for (int a = 0; a < 8; ++a) {
+        const double2* p = reinterpret_cast<const double2*>(crow + a * rstep);
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const double2 c = __ldcs(p + b * 4);
+          acc[a][b][0] = c.x; acc[a][b][1] = c.y;
+        }
+      }
+    } else {
+#pragma unroll
+      for (int a = 0; a < 8; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          acc[a][b][0] = 0.0; acc[a][b][1] = 0.0;
+          const int row = wr * 64 + a * 8 + fr, col = wc * 32 + b * 8 + 2 * fk;
+          if (row < cur.ni && col < cur.nj) {
+            const double2 c = __ldcs(reinterpret_cast<const double2*>(crow + a * rstep) + b * 4);
+            acc[a][b][0] = c.x; acc[a][b][1] = c.y;
+          }
+        }
     }
-    __syncthreads();
-  }
-  // epilogue: lane holds C[row = fr][col = 2*fk, 2*fk+1] of each 8×8 tile
+    if (has_next) {
+      // next tile's C → L2: 128 rows × 512 B = 4 lines per row, one line per thread per pass
 #pragma unroll
-  for (int a = 0; a < 8; ++a) {
-    const int row = wr * 64 + a * 8 + fr;
-    if (row >= ni) continue;
-#pragma unroll
-    for (int b = 0; b < 4; ++b) {
-      const int col = wc * 32 + b * 8 + 2 * fk;
-      if (MODE == 0) {
-        double2* dst = reinterpret_cast<double2*>(panel_out + (size_t)(bi * NB + row) * NB + bj * TN + col);
-        *dst = make_double2(acc[a][b][0], acc[a][b][1]);
-      } else {
-        if (col >= nj) continue;
-        double2* dst = reinterpret_cast<double2*>(S + (size_t)(ri + row) * n + rj + col);
-        *dst = make_double2(acc[a][b][0], acc[a][b][1]);
+      for (int q = 0; q < 4; ++q) {
+        const int e = threadIdx.x + 128 * q;
+        const int row = e >> 2, seg = e & 3;
+        if (row < nxt.ni && seg * 16 < nxt.nj)
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(S + (size_t)(nxt.ri + row) * n + nxt.rj + seg * 16));
       }
     }
+#pragma unroll 1
+    for (int ch = 0; ch < NB / KC; ++ch) {
+      if (ch + 1 < NB / KC) {
+        load_tile_async<NB>(sm.a[stage ^ 1], S, n, cur.ri, cur.ni, k0 + (ch + 1) * KC);
+        load_tile_async<TN>(sm.b[stage ^ 1], S, n, cur.rj, cur.nj, k0 + (ch + 1) * KC);
+      } else if (has_next) {
+        load_tile_async<NB>(sm.a[stage ^ 1], S, n, nxt.ri, nxt.ni, k0);
+        load_tile_async<TN>(sm.b[stage ^ 1], S, n, nxt.rj, nxt.nj, k0);
+      }
+      cp_async_commit();
+      cp_async_wait<1>();
+      __syncthreads();
+#pragma unroll
+      for (int ks = 0; ks < KC / 4; ++ks) {
+        double af[8], bf[4];
+#pragma unroll
+        for (int a = 0; a < 8; ++a) af[a] = -sm.a[stage][wr * 64 + a * 8 + fr][ks * 4 + fk];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) bf[b] = sm.b[stage][wc * 32 + b * 8 + fr][ks * 4 + fk];
+#pragma unroll
+        for (int a = 0; a < 8; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+      }
+      __syncthreads();
+      stage ^= 1;
+    }
+    // epilogue: lane holds C[row = fr][col = 2*fk, 2*fk+1] of each 8×8 tile
+#ifdef HSFM_SYRK_NOSTORE
+    if (full) {
+      if (acc[0][0][0] == 1.2345e300) crow[0] = 1.0;
+    } else
+#endif
+    if (full) {
+#pragma unroll
+      for (int a = 0; a < 8; ++a) {
+        double2* p = reinterpret_cast<double2*>(crow + a * rstep);
+#pragma unroll
+        for (int b = 0; b < 4; ++b) p[b * 4] = make_double2(acc[a][b][0], acc[a][b][1]);
+      }
+    } else {
+#pragma unroll
+      for (int a = 0; a < 8; ++a) {
+        const int row = wr * 64 + a * 8 + fr;
+        if (row >= cur.ni) continue;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const int col = wc * 32 + b * 8 + 2 * fk;
+          if (col >= cur.nj) continue;
+          reinterpret_cast<double2*>(crow + a * rstep)[b * 4] = make_double2(acc[a][b][0], acc[a][b][1]);
+        }
+      }
+    }
+    cur = nxt;
   }
+  cp_async_wait<0>();
 }
 
-// move the packed scratch panel (m × 128) over A21
-__global__ void __launch_bounds__(256) chol_panel_copy_kernel(double* __restrict__ S, int n, int k0, int m, const double* __restrict__ panel,
-                                                               const int* __restrict__ fail) {
-  if (*fail) return;
-  const size_t e = (size_t)blockIdx.x * 256 + threadIdx.x;  // double2 index
-  if (e >= (size_t)m * (NB / 2)) return;
-  const int row = (int)(e / (NB / 2)), c2 = (int)(e % (NB / 2));
-  const double2 v = reinterpret_cast<const double2*>(panel)[e];
-  *reinterpret_cast<double2*>(S + (size_t)(k0 + NB + row) * n + k0 + 2 * c2) = v;
+// Panel solve  L21 = A21 L11^-T  as a product with the stored inverse, IN PLACE: every CTA owns a strip of
+// rows (all 128 columns), stages the strip in shared memory and writes the result over it.  The B fragments
+// (rows of L11^-1, 128 KB shared by every CTA, L2-resident) are read straight from global memory four k-steps
+// ahead of their use, so the kernel needs only the strip in shared memory (<= 93 KB) and fits on an SM next
+// to a resident trailing-update CTA.  Only k <= column contributes (L11^-1 is lower triangular); warp w takes
+// the 8-column tiles w and 15-w, which together need the same 34 k-steps for every warp.
+constexpr int TS_LD = NB + 4;
+constexpr int TS_MAXROWS = 88;
+__global__ void __launch_bounds__(256) chol_trsm_strip_kernel(double* __restrict__ S, int n, int k0, const double* __restrict__ Linv,
+                                                               int rows_per, const int* __restrict__ fail) {
+  extern __shared__ __align__(16) double tsm[];
+  double (*sA)[TS_LD] = reinterpret_cast<double (*)[TS_LD]>(tsm);
+  const int failed = *fail;
+  const int r0 = k0 + NB + blockIdx.x * rows_per;
+  const int nr = min(rows_per, n - r0);
+  const int tid = threadIdx.x;
+  for (int e = tid; e < rows_per * (NB / 2); e += 256) {
+    const int row = e >> 6, c2 = (e & 63) * 2;
+    if (row < nr) cp_async16(&sA[row][c2], S + (size_t)(r0 + row) * n + k0 + c2);
+    else { sA[row][c2] = 0.0; sA[row][c2 + 1] = 0.0; }
+  }
+  cp_async_commit();
+  const int warp = tid >> 5, lane = tid & 31, fr = lane >> 2, fk = lane & 3;
+  const int RT = rows_per >> 3;
+  const int ct_lo = warp, ct_hi = 15 - warp;
+  const int ks_hi = 2 * (ct_hi + 1), ks_lo = 2 * (ct_lo + 1);  // k-steps (of 4) each column tile needs
+  const double* __restrict__ Bhi = Linv + (ct_hi * 8 + fr) * NB + fk;
+  const double* __restrict__ Blo = Linv + (ct_lo * 8 + fr) * NB + fk;
+  double bh[4], bl[4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    bh[u] = (u < ks_hi) ? __ldg(Bhi + 4 * u) : 0.0;
+    bl[u] = (u < ks_lo) ? __ldg(Blo + 4 * u) : 0.0;
+  }
+  cp_async_wait<0>();
+  __syncthreads();
+  if (failed || nr <= 0) return;
+  double acc[TS_MAXROWS / 8][2][2];
+#pragma unroll
+  for (int rt = 0; rt < TS_MAXROWS / 8; ++rt) { acc[rt][0][0] = acc[rt][0][1] = acc[rt][1][0] = acc[rt][1][1] = 0.0; }
+#pragma unroll 1
+  for (int ks0 = 0; ks0 < ks_hi; ks0 += 4) {
+    double nh[4], nl[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {  // next group of B fragments, in flight while this group is multiplied
+      const int ks = ks0 + 4 + u;
+      nh[u] = (ks < ks_hi) ? __ldg(Bhi + 4 * ks) : 0.0;
+      nl[u] = (ks < ks_lo) ? __ldg(Blo + 4 * ks) : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int ks = ks0 + u;
+      if (ks < ks_hi) {
+        const bool lo = ks < ks_lo;
+#pragma unroll
+        for (int rt = 0; rt < TS_MAXROWS / 8; ++rt) {
+          if (rt < RT) {
+            const double a = sA[rt * 8 + fr][ks * 4 + fk];
+            dmma884(acc[rt][1][0], acc[rt][1][1], a, bh[u]);
+            if (lo) dmma884(acc[rt][0][0], acc[rt][0][1], a, bl[u]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { bh[u] = nh[u]; bl[u] = nl[u]; }
+  }
+#pragma unroll
+  for (int rt = 0; rt < TS_MAXROWS / 8; ++rt) {
+    const int row = rt * 8 + fr;
+    if (rt < RT && row < nr) {
+      double* dst = S + (size_t)(r0 + row) * n + k0 + 2 * fk;
+      *reinterpret_cast<double2*>(dst + ct_lo * 8) = make_double2(acc[rt][0][0], acc[rt][0][1]);
+      *reinterpret_cast<double2*>(dst + ct_hi * 8) = make_double2(acc[rt][1][0], acc[rt][1][1]);
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -542,11 +678,21 @@ void launch_spd_fill(double* A, int n, double* b, cudaStream_t s) {
   spd_fill_kernel<<<g, 256, 0, s>>>(A, n);
   if (b) spd_rowsum_kernel<<<(n + 127) / 128, 128, 0, s>>>(n, b);
 }
-void launch_spd_err(int n, const double* x, double* err, cudaStream_t s) { spd_err_kernel<<<1, 256, 0, s>>>(n, x, err); }
+void launch_spd_err(int n, const double* x, double* err, cudaStream_t s) {
+  spd_err_kernel<<<1, 256, 0, s>>>(n, x, err);
+#ifdef HSFM_DIAG_TIMING
+  long long h[32];
+  cudaStreamSynchronize(s);
+  cudaMemcpyFromSymbol(h, g_diag_clk, sizeof(h));
+  const char* nm[17] = {"", "load", "fac0", "sub0", "upd0", "fac1", "sub1", "upd1", "fac2", "sub2", "upd2", "fac3", "trinv", "inv1", "inv2", "inv3", "store"};
+  for (int k = 1; k <= 16; ++k) std::fprintf(stderr, "%s %lld  ", nm[k], h[k] - h[k - 1]);
+  std::fprintf(stderr, "total %lld clk\n", h[16] - h[0]);
+#endif
+}
 
 size_t cholesky_workspace_doubles(int n) {
   const size_t panels = (size_t)((n + NB - 1) / NB);
-  return panels * NB * NB /* L11^-1 blocks */ + panels * NB * NB /* packed TRSM scratch panel, m x 128 */;
+  return panels * NB * NB;  // one L11^-1 block per panel
 }
 
 int CholAux::init() {
@@ -567,20 +713,35 @@ void CholAux::destroy() {
   stream = nullptr;
 }
 
-// Factorisation with one panel of look-ahead: the auxiliary (high-priority) stream runs
-//   diag(k) → trsm(k) → copy(k) → [panel k ready] → syrk of the NEXT panel's 128 columns
-// while the main stream runs the bulk of syrk(k-1); diag/trsm of panel k+1 therefore overlap the
-// trailing update of panel k instead of serialising with it.
+// Factorisation with two panels of look-ahead.  Relative to panel k (trailing matrix starts at k0+128,
+// 64-wide column blocks cb): cb 0,1 are panel k+1's columns, cb 2,3 panel k+2's, cb >= 4 the bulk.
+//   chain stream (high priority):  diag(k) → trsm(k) → [panel k ready] → update cb 0,1  → diag(k+1) …
+//   main stream:                   wait panel k → update cb 2,3 → [ahead k ready] → bulk update cb >= 4
+// The chain's update of cb 0,1 at step k+1 waits for "ahead k" (those are the columns cb 2,3 of step k), so
+// the bulk update of step k has the whole of chain step k+1 to finish before anything waits on it: the
+// chain (latency-bound) and the bulk (DMMA-bound) overlap and the slower of the two sets the pace.
 void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDiagSmem);
-    cudaFuncSetAttribute(chol_gemm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem);
-    cudaFuncSetAttribute(chol_gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem);
+    cudaFuncSetAttribute(chol_trsm_strip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_MAXROWS * TS_LD * (int)sizeof(double));
+    cudaFuncSetAttribute(chol_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem);
     attr_set = true;
   }
+  static int n_sm = 0;
+  if (!n_sm) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    if (n_sm <= 0) n_sm = 148;
+  }
+  static int bulk_ctas = 0;
+  if (!bulk_ctas) {
+    const char* e = getenv("HSFM_BULK_CTAS");  // experiment knob: <0 means n_sm + value
+    bulk_ctas = e ? atoi(e) : 2 * n_sm;
+    if (bulk_ctas <= 0) bulk_ctas = n_sm + bulk_ctas;
+  }
   const int panels = (n + NB - 1) / NB;
-  double* scratch = ws + (size_t)panels * NB * NB;
   const bool la = aux && aux->stream && panels > 2;
   cudaStream_t s2 = la ? aux->stream : s;
   if (la) {
@@ -595,22 +756,27 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
     const int m = n - (k0 + kb);
     if (m <= 0) break;
     const int rb = (m + NB - 1) / NB;
-    chol_gemm_kernel<0><<<2 * rb, 128, kGemmSmem, s2>>>(S, n, k0, Linv, scratch, 0, 0, fail_flag);
-    chol_panel_copy_kernel<<<(int)(((size_t)m * (NB / 2) + 255) / 256), 256, 0, s2>>>(S, n, k0, m, scratch, fail_flag);
-    *launches += 2;
+    int rows_per = ((m + n_sm - 1) / n_sm + 7) & ~7;
+    rows_per = max(8, min(TS_MAXROWS, rows_per));
+    chol_trsm_strip_kernel<<<(m + rows_per - 1) / rows_per, 256, rows_per * TS_LD * (int)sizeof(double), s2>>>(S, n, k0, Linv, rows_per,
+                                                                                                                   fail_flag);
+    ++*launches;
     if (la) {
       cudaEventRecord(aux->ev_panel, s2);
-      if (panel > 0) cudaStreamWaitEvent(s2, aux->ev_rest, 0);  // rest(k-1) wrote the columns col(k) updates
+      if (panel > 0) cudaStreamWaitEvent(s2, aux->ev_rest, 0);  // "ahead k-1": cb 2,3 of the previous step = cb 0,1 of this one
     }
-    // next panel's columns: column blocks 0,1 of every row tile
-    chol_gemm_kernel<1><<<2 * rb, 128, kGemmSmem, s2>>>(S, n, k0, Linv, nullptr, 0, 0, fail_flag);
+    chol_syrk_kernel<<<min(2 * rb, 2 * n_sm), 128, kGemmSmem, s2>>>(S, n, k0, 0, 0, 2 * rb, 0, fail_flag);
     ++*launches;
     if (rb > 1) {
       if (la) cudaStreamWaitEvent(s, aux->ev_panel, 0);
-      chol_gemm_kernel<1><<<rb * (rb - 1), 128, kGemmSmem, s>>>(S, n, k0, Linv, nullptr, 0, -1, fail_flag);
+      chol_syrk_kernel<<<min(2 * (rb - 1), 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 1, 2, 2 * (rb - 1), 0, fail_flag);
       ++*launches;
     }
     if (la) cudaEventRecord(aux->ev_rest, s);
+    if (rb > 2) {
+      chol_syrk_kernel<<<min((rb - 2) * (rb - 1), bulk_ctas), 128, kGemmSmem, s>>>(S, n, k0, 0, -4, (rb - 2) * (rb - 1), bulk_ctas > n_sm ? 1 : 0, fail_flag);
+      ++*launches;
+    }
   }
   if (la) {
     cudaEventRecord(aux->ev_join, s2);
