@@ -13,6 +13,7 @@
 // DMMA is the tensor-core instruction this workload can use (north_star: "tensor cores only for the
 // dense Cholesky").  The stored L11^-1 blocks also turn the two triangular solves into mat-vecs.
 // A non-positive pivot raises *fail; later kernels of the same factorisation return immediately.
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 
@@ -646,6 +647,140 @@ __global__ void __launch_bounds__(256) trsv_bwd_kernel(const double* __restrict_
   if (!half && col < k0) y[col] -= acc + sp[j];
 }
 
+// ---------------------------------------------------------------------------------------------
+// Both triangular solves in ONE cooperative launch.  CTA c owns the 128-row blocks c, c+G, … .
+// Forward (L y = b): the owner of block i folds L[i,k] y_k into its right-hand side as soon as block k
+// publishes y_k (flag with release/acquire at gpu scope), then applies L11^-1 of its own block and publishes.
+// Backward (L^T x = y) runs the same protocol down the columns.  Blocks only ever wait on blocks with a
+// smaller (forward) / larger (backward) index and every CTA walks its blocks in that order, so the waits
+// cannot cycle; the cooperative launch guarantees all CTAs are resident.  The dependency chain is two
+// 128x128 mat-vecs plus one flag hand-off per block instead of two kernel launches.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int ld_acquire(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release(int* p, int v) { asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+// y[r] = sum_c M[r][c] v[c] for a 128x128 block (row stride ld): thread t owns row t>>1, columns
+// (t&1)*64 .. +63 — 32 independent 16-byte loads in flight per thread, one shuffle to join the halves.
+// Rows >= nrows read as zero.  Result valid on even threads.
+__device__ __forceinline__ double block_row_dot(const double* __restrict__ M, size_t ld, int nrows, const double* __restrict__ sv, int tid) {
+  const int r = tid >> 1, h = tid & 1;
+  double2 v[32];
+  const double2* p = reinterpret_cast<const double2*>(M + (size_t)r * ld + h * 64);
+#pragma unroll
+  for (int q = 0; q < 32; ++q) v[q] = (r < nrows) ? __ldg(p + q) : make_double2(0.0, 0.0);
+  double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+  for (int q = 0; q < 32; ++q) {
+    a0 = fma(v[q].x, sv[h * 64 + 2 * q], a0);
+    a1 = fma(v[q].y, sv[h * 64 + 2 * q + 1], a1);
+  }
+  double a = a0 + a1;
+  a += __shfl_xor_sync(0xffffffffu, a, 1);
+  return a;
+}
+// x[c] = sum_r M[r][c] v[r]: thread t owns column t&127, rows (t>>7)*64 .. +63, 64 loads in flight.
+// Returns the partial sum of this thread's half.
+__device__ __forceinline__ double block_col_dot(const double* __restrict__ M, size_t ld, int nrows, int ncols, const double* __restrict__ sv, int tid,
+                                                bool lower_only) {
+  const int c = tid & (NB - 1), r0 = (tid >> 7) * 64;
+  double v[64];
+#pragma unroll
+  for (int q = 0; q < 64; ++q) {
+    const int r = r0 + q;
+    v[q] = (r < nrows && c < ncols && (!lower_only || r >= c)) ? __ldg(M + (size_t)r * ld + c) : 0.0;
+  }
+  double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+  for (int q = 0; q < 64; q += 2) {
+    a0 = fma(v[q], sv[r0 + q], a0);
+    a1 = fma(v[q + 1], sv[r0 + q + 1], a1);
+  }
+  return a0 + a1;
+}
+
+__global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict__ L, int n, const double* __restrict__ LinvAll, double* b,
+                                                        double* w, int* flag_fwd, int* flag_bwd) {
+  __shared__ double sv[NB];    // vector of the block being folded in (y_k / x_i)
+  __shared__ double sacc[NB];  // running right-hand side of the owned block
+  __shared__ double sp[NB];
+  const int tid = threadIdx.x;
+  const int P = (n + NB - 1) / NB, G = gridDim.x;
+  // ---- forward ----
+  for (int i = blockIdx.x; i < P; i += G) {
+    const int r0 = i * NB, nr = min(NB, n - r0);
+    if (tid < NB) sacc[tid] = (tid < nr) ? b[r0 + tid] : 0.0;
+    for (int e = tid; e < NB * 8; e += 256) {  // the two blocks on the dependency chain: L11^-1 and block (i, i-1)
+      const int row = e >> 3;
+      prefetch_l2(LinvAll + (size_t)i * NB * NB + row * NB + (e & 7) * 16);
+      if (i > 0 && row < nr) prefetch_l2(L + (size_t)(r0 + row) * n + (i - 1) * NB + (e & 7) * 16);
+    }
+    for (int k = 0; k < i; ++k) {
+      if (k + 2 < i) {  // pull block (i, k+2) towards L2: 128 rows x 1 KB = 8 lines per row
+        for (int e = tid; e < NB * 8; e += 256) {
+          const int row = e >> 3;
+          if (row < nr) prefetch_l2(L + (size_t)(r0 + row) * n + (k + 2) * NB + (e & 7) * 16);
+        }
+      }
+      if (tid == 0) { while (ld_acquire(flag_fwd + k) == 0) { } }
+      __syncthreads();
+      if (tid < NB) sv[tid] = __ldcg(w + k * NB + tid);
+      __syncthreads();
+      const double d = block_row_dot(L + (size_t)r0 * n + (size_t)k * NB, (size_t)n, nr, sv, tid);
+      if (!(tid & 1)) sacc[tid >> 1] -= d;
+      __syncthreads();
+    }
+    __syncthreads();
+    const double y = block_row_dot(LinvAll + (size_t)i * NB * NB, NB, NB, sacc, tid);
+    if (!(tid & 1) && (tid >> 1) < nr) w[r0 + (tid >> 1)] = y;
+    __syncthreads();
+    if (tid == 0) { __threadfence(); st_release(flag_fwd + i, 1); }
+  }
+  // ---- backward ----
+  const int j = tid & (NB - 1), half = tid >> 7;
+  for (int kk = P - 1 - (int)blockIdx.x; kk >= 0; kk -= G) {
+    const int c0 = kk * NB, kb = min(NB, n - c0);
+    for (int e = tid; e < NB * 8; e += 256) {
+      const int row = e >> 3;
+      prefetch_l2(LinvAll + (size_t)kk * NB * NB + row * NB + (e & 7) * 16);
+      if (kk + 1 < P && (kk + 1) * NB + row < n) prefetch_l2(L + (size_t)((kk + 1) * NB + row) * n + c0 + (e & 7) * 16);
+    }
+    if (tid == 0) { while (ld_acquire(flag_fwd + kk) == 0) { } }
+    __syncthreads();
+    if (tid < NB) sacc[tid] = (tid < kb) ? __ldcg(w + c0 + tid) : 0.0;
+    for (int i = P - 1; i > kk; --i) {
+      const int r0 = i * NB, nr = min(NB, n - r0);
+      if (i - 2 > kk) {
+        for (int e = tid; e < NB * 8; e += 256) {
+          const int row = e >> 3;
+          prefetch_l2(L + (size_t)((i - 2) * NB + row) * n + c0 + (e & 7) * 16);
+        }
+      }
+      if (tid == 0) { while (ld_acquire(flag_bwd + i) == 0) { } }
+      __syncthreads();
+      if (tid < NB) sv[tid] = (tid < nr) ? __ldcg(b + r0 + tid) : 0.0;
+      __syncthreads();
+      const double acc = block_col_dot(L + (size_t)r0 * n + c0, (size_t)n, nr, kb, sv, tid, false);
+      if (half) sp[j] = acc;
+      __syncthreads();
+      if (!half) sacc[j] -= acc + sp[j];
+      __syncthreads();
+    }
+    // x_k = L11^-T acc : x[j] = sum_{i >= j} Linv[i][j] acc[i]
+    __syncthreads();
+    const double acc = block_col_dot(LinvAll + (size_t)kk * NB * NB, NB, NB, NB, sacc, tid, true);
+    if (half) sp[j] = acc;
+    __syncthreads();
+    if (!half && j < kb) b[c0 + j] = acc + sp[j];
+    __syncthreads();
+    if (tid == 0) { __threadfence(); st_release(flag_bwd + kk, 1); }
+  }
+}
+
 // synthetic SPD test matrix A_ij = 1/(1+|i-j|) + 2 delta_ij (Polya: convex decreasing kernel), b = A 1
 __global__ void spd_fill_kernel(double* __restrict__ A, int n) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
@@ -692,7 +827,7 @@ void launch_spd_err(int n, const double* x, double* err, cudaStream_t s) {
 
 size_t cholesky_workspace_doubles(int n) {
   const size_t panels = (size_t)((n + NB - 1) / NB);
-  return panels * NB * NB;  // one L11^-1 block per panel
+  return panels * NB * NB + panels;  // one L11^-1 block per panel + 2 x panels int flags of the cooperative triangular solve
 }
 
 int CholAux::init() {
@@ -786,8 +921,32 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
 
 // Solves S y = b with the factor from launch_cholesky.  b holds 2n doubles: [0,n) right-hand side
 // in / solution out, [n,2n) scratch for the intermediate vector.
-void launch_chol_solve(const double* L, int n, const double* ws, double* b, cudaStream_t s, int64_t* launches) {
+void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream_t s, int64_t* launches) {
   double* w = b + n;
+  const int panels = (n + NB - 1) / NB;
+  int* flags = reinterpret_cast<int*>(ws + (size_t)panels * NB * NB);  // [2 * panels]
+  static int n_sm = 0, coop = -1;
+  if (coop < 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    if (getenv("HSFM_TRSV_LAUNCHES")) coop = 0;
+  }
+  if (coop) {
+    cudaMemsetAsync(flags, 0, sizeof(int) * 2 * panels, s);
+    const double* LinvAll = ws;
+    int* ff = flags;
+    int* fb = flags + panels;
+    int nn = n;
+    void* args[] = {(void*)&L, (void*)&nn, (void*)&LinvAll, (void*)&b, (void*)&w, (void*)&ff, (void*)&fb};
+    const int grid = std::min(panels, n_sm);
+    if (cudaLaunchCooperativeKernel((const void*)trsv_coop_kernel, dim3(grid), dim3(256), args, 0, s) == cudaSuccess) {
+      ++*launches;
+      return;
+    }
+    cudaGetLastError();  // fall through to the per-panel launches
+  }
   int panel = 0;
   for (int k0 = 0; k0 < n; k0 += NB, ++panel) {
     const int kb = min(NB, n - k0);

@@ -153,7 +153,7 @@ struct CholAux {
 };
 size_t cholesky_workspace_doubles(int n);  // L11^-1 blocks (one 128×128 per panel) + packed TRSM scratch panel
 void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches);
-void launch_chol_solve(const double* L, int n, const double* ws, double* b, cudaStream_t s, int64_t* launches);
+void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream_t s, int64_t* launches);
 
 void launch_spd_fill(double* A, int n, double* b /*null = matrix only*/, cudaStream_t s);  // bench tap: synthetic SPD matrix, b = A 1
 void launch_spd_err(int n, const double* x, double* err, cudaStream_t s);                 // max |x - 1|
