@@ -262,6 +262,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   ALLOC(P.Hpp, 6 * (size_t)n_pts); ALLOC(P.gp, 3 * (size_t)n_pts); ALLOC(P.Hpp_inv, 6 * (size_t)n_pts); ALLOC(P.zp, 3 * (size_t)n_pts);
   ALLOC(P.Hcc, 21 * (size_t)n_cams); ALLOC(P.gc, 6 * (size_t)n_cams); ALLOC(P.E, 21 * (size_t)n_cams);
   ALLOC(P.chunk_part, 27 * (size_t)std::max(1, P.n_chunks));
+  ALLOC(P.tobs, 6 * (size_t)n);
   ALLOC(P.Dc2, 6 * (size_t)n_cams); ALLOC(P.Minv, 36 * (size_t)n_cams);
   ALLOC(P.rhs, 6 * (size_t)n_cams); ALLOC(P.yc, 12 * (size_t)n_cams); ALLOC(P.yp, 3 * (size_t)n_pts);
   ALLOC(P.pcg_x, 6 * (size_t)n_cams); ALLOC(P.pcg_r, 6 * (size_t)n_cams); ALLOC(P.pcg_z, 6 * (size_t)n_cams);
@@ -284,7 +285,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   Dev& d = P.d;
   d.n_obs = n; d.n_cams = n_cams; d.n_pts = n_pts; d.n_tiles = P.n_tiles; d.n_chunks = P.n_chunks;
   d.obs = obs; d.cam = cam; d.pt = pt; d.pt_start = pt_start; d.tile_start = tile_start;
-  d.obs_cs = obs_cs; d.pt_cs = pt_cs; d.chunk_cam = d_ch_cam; d.chunk_b = d_ch_b; d.chunk_e = d_ch_e; d.cam_chunk_start = d_cam_ch_start;
+  d.obs_cs = obs_cs; d.pt_cs = pt_cs; d.pos_cs = pos_cs; d.chunk_cam = d_ch_cam; d.chunk_b = d_ch_b; d.chunk_e = d_ch_e; d.cam_chunk_start = d_cam_ch_start;
   d.r = r; d.Jc = Jc; d.Jp = Jp;
   HSFM_CUDA(cudaStreamSynchronize(s));
   if (setup_ms) *setup_ms = now_ms() - t_setup0;

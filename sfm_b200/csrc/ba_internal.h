@@ -34,6 +34,7 @@ struct Dev {
   // static, camera-major order
   const double2* obs_cs; // [n_obs]
   const int* pt_cs;      // [n_obs]
+  const int* pos_cs;     // [n_obs] point-major position of the j-th camera-major observation
   const int* chunk_cam;  // [n_chunks]
   const int* chunk_b;    // [n_chunks]
   const int* chunk_e;    // [n_chunks]
@@ -70,6 +71,7 @@ struct Problem {
   double *Hpp = nullptr, *gp = nullptr, *Hpp_inv = nullptr, *zp = nullptr;  // [n_pts][6],[3],[6],[3]
   double *Hcc = nullptr, *gc = nullptr;             // [n_cams][21] upper-tri row-major, [n_cams][6]
   double *chunk_part = nullptr;                     // [n_chunks][27]
+  double *tobs = nullptr;                           // [n_obs][6] per-observation camera-space vectors (point-major), gathered camera-major
   double *Dc2 = nullptr;                            // [6 n_cams] squared LM diagonal of the camera block
   double *Minv = nullptr;                           // [n_cams][36] block-Jacobi preconditioner / pose-only inverse
   double *E = nullptr;                              // [n_cams][21] sum_i Jc^T Jp Hpp^-1 Jp^T Jc

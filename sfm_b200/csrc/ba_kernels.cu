@@ -271,6 +271,43 @@ __global__ void __launch_bounds__(256) cam_major_kernel(Dev d, const CamRow* __r
   }
 }
 
+// Camera-major gather of the per-observation 6-vectors written point-major by schur_pass_kernel<0>:
+// one warp per chunk (<= 256 observations of one camera), 48-byte records fetched through the
+// camera-major → point-major permutation, warp-reduced into chunk_part[chunk][0..5].
+__global__ void __launch_bounds__(256) cam_gather6_kernel(Dev d, const double* __restrict__ tobs, double* __restrict__ chunk_part) {
+  const int lane = threadIdx.x & 31;
+  const int wc = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (wc >= d.n_chunks) return;
+  const int b = __ldg(d.chunk_b + wc), e = __ldg(d.chunk_e + wc);
+  double acc[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  for (int j = b + lane; j < e; j += 32) {
+    const double2* src = reinterpret_cast<const double2*>(tobs + 6 * (size_t)__ldg(d.pos_cs + j));
+    const double2 v0 = __ldg(src), v1 = __ldg(src + 1), v2 = __ldg(src + 2);
+    acc[0] += v0.x; acc[1] += v0.y; acc[2] += v1.x; acc[3] += v1.y; acc[4] += v2.x; acc[5] += v2.y;
+  }
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    double v = acc[k];
+#pragma unroll
+    for (int dd = 16; dd > 0; dd >>= 1) v += __shfl_xor_sync(FULL, v, dd);
+    acc[k] = v;
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) chunk_part[(size_t)wc * 27 + k] = acc[k];
+  }
+}
+// out[c][k] = (base ? base[c][k] : 0) - sum over the camera's chunks, in chunk order
+__global__ void cam_reduce6_sub_kernel(int n_cams, const int* __restrict__ cam_chunk_start, const double* __restrict__ chunk_part,
+                                       const double* __restrict__ base, double* __restrict__ out) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n_cams * 6) return;
+  const int c = idx / 6, k = idx % 6;
+  double s = 0.0;
+  for (int w = cam_chunk_start[c]; w < cam_chunk_start[c + 1]; ++w) s += chunk_part[(size_t)w * 27 + k];
+  out[idx] = (base ? base[idx] : 0.0) - s;
+}
+
 // Fold the chunk partials of each camera in chunk order (deterministic).
 __global__ void cam_reduce_kernel(int n_cams, int nv, const int* __restrict__ cam_chunk_start, const double* __restrict__ chunk_part,
                                   double* __restrict__ out21, double* __restrict__ out6) {
@@ -399,12 +436,16 @@ __global__ void __launch_bounds__(TILE) schur_pass_kernel(Dev d, const double* _
     for (int k = 0; k < 6; ++k) jp[k] = 0.0;
   }
   if (MODE == 0) {
+    // t_i = Jc_i^T (Jp_i z_p), stored per observation (48 B, point-major); the camera-major gather
+    // pass (cam_gather6_kernel) sums them per camera — no atomics, fixed summation order.
     if (t.valid) {
       const double z0 = __ldg(zp + 3 * (size_t)t.p), z1 = __ldg(zp + 3 * (size_t)t.p + 1), z2 = __ldg(zp + 3 * (size_t)t.p + 2);
-      const double y0 = -(jp[0] * z0 + jp[1] * z1 + jp[2] * z2);
-      const double y1 = -(jp[3] * z0 + jp[4] * z1 + jp[5] * z2);
+      const double y0 = jp[0] * z0 + jp[1] * z1 + jp[2] * z2;
+      const double y1 = jp[3] * z0 + jp[4] * z1 + jp[5] * z2;
+      double2* dst = reinterpret_cast<double2*>(vec_out + 6 * (size_t)t.i);
 #pragma unroll
-      for (int k = 0; k < 6; ++k) atomicAdd(vec_out + 6 * (size_t)c + k, jc[k] * y0 + jc[6 + k] * y1);
+      for (int k = 0; k < 3; ++k)
+        dst[k] = make_double2(jc[2 * k] * y0 + jc[6 + 2 * k] * y1, jc[2 * k + 1] * y0 + jc[7 + 2 * k] * y1);
     }
     return;
   }
@@ -897,12 +938,19 @@ void launch_precond_invert(Problem& P, bool with_E, cudaStream_t s) {
 }
 
 void launch_schur_rhs(Problem& P, bool preload_gc, cudaStream_t s) {
-  if (preload_gc) cudaMemcpyAsync(P.rhs, P.gc, sizeof(double) * 6 * P.n_cams, cudaMemcpyDeviceToDevice, s);
-  else cudaMemsetAsync(P.rhs, 0, sizeof(double) * 6 * P.n_cams, s);
-  if (P.n_tiles == 0) return;
-  schur_pass_kernel<0><<<P.n_tiles, TILE, 0, s>>>(P.d, P.Hpp_inv, P.zp, nullptr, P.rhs, nullptr, nullptr, nullptr, nullptr, P.part,
-                                                  P.part_stride, P.flags, 1, 1);
-  P.launches++;
+  if (P.n_tiles > 0) {
+    schur_pass_kernel<0><<<P.n_tiles, TILE, 0, s>>>(P.d, P.Hpp_inv, P.zp, nullptr, P.tobs, nullptr, nullptr, nullptr, nullptr, P.part,
+                                                    P.part_stride, P.flags, 1, 1);
+    P.launches++;
+  }
+  if (P.n_chunks > 0) {
+    cam_gather6_kernel<<<cdiv(P.n_chunks, 8), 256, 0, s>>>(P.d, P.tobs, P.chunk_part);
+    P.launches++;
+  }
+  if (P.n_cams > 0) {
+    cam_reduce6_sub_kernel<<<cdiv(P.n_cams * 6, 256), 256, 0, s>>>(P.n_cams, P.d.cam_chunk_start, P.chunk_part, preload_gc ? P.gc : nullptr, P.rhs);
+    P.launches++;
+  }
 }
 
 void launch_schur_matvec(Problem& P, const double* pvec, double* q, cudaStream_t s) {
