@@ -106,8 +106,7 @@ void hsfm_ba_destroy(hsfm_ba_ctx* h) {
   if (!h) return;
   cudaSetDevice(h->c.device);
   cudaStreamSynchronize(h->c.stream);
-  h->c.prob.release();
-  if (h->c.prob.S) { cudaFree(h->c.prob.S); h->c.prob.S = nullptr; }
+  h->c.prob.destroy();
   h->c.comm.destroy();
   h->c.chol_aux.destroy();
   for (cudaEvent_t e : h->c.phase_events) cudaEventDestroy(e);
@@ -145,7 +144,6 @@ int hsfm_ba_problem_upload(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double
   if (n_pts > 0 && !pts) return HSFM_BA_ERR_ARG;
   HSFM_CUDA(cudaSetDevice(h->c.device));
   h->c.has_problem = false;
-  if (h->c.prob.S) { cudaFree(h->c.prob.S); h->c.prob.S = nullptr; h->c.prob.S_capacity = 0; }
   double setup = 0, h2d = 0;
   int rc = build_problem(h->c.prob, mode, n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, dist, cam_rt, n_pts, pts, h->c.comm, h->c.stream, &setup, &h2d);
   if (rc) { h->c.prob.release(); return rc; }
@@ -440,8 +438,15 @@ int hsfm_ba_schur(hsfm_ba_ctx* h, int64_t n_obs, const double* obs_xy, const int
   Problem& P = h->c.prob;
   cudaStream_t s = h->c.stream;
   const size_t n6 = 6 * (size_t)n_cams;
-  if (cudaMalloc(&P.S, sizeof(double) * (std::max<size_t>(1, n6 * n6) + cholesky_workspace_doubles((int)n6))) != cudaSuccess) { cudaGetLastError(); P.S = nullptr; return HSFM_BA_ERR_NOMEM; }
-  P.S_capacity = n6 * n6 + cholesky_workspace_doubles((int)n6);
+  {
+    const size_t need = std::max<size_t>(1, n6 * n6) + cholesky_workspace_doubles((int)n6);
+    if (P.S_capacity < need) {
+      if (P.S) cudaFree(P.S);
+      P.S = nullptr; P.S_capacity = 0;
+      if (cudaMalloc(&P.S, sizeof(double) * need) != cudaSuccess) { cudaGetLastError(); P.S = nullptr; return HSFM_BA_ERR_NOMEM; }
+      P.S_capacity = need;
+    }
+  }
   // scaling pass, linearisation, blocks
   launch_cam_prep(P, P.cam_x, nullptr, P.rows_x, s);
   launch_rj(P, P.rows_x, P.pts_x, nullptr, false, true, s);

@@ -13,26 +13,55 @@
 namespace hsfm {
 
 void Problem::release() {
-  for (void* p : allocs) cudaFree(p);
-  allocs.clear();
+  // keep what outlives a problem: the arena, the dense matrix, the pinned scalar mirrors
+  char* a = arena; const size_t cap = arena_cap;
+  double* s_keep = S; const size_t s_cap = S_capacity;
+  double* sh = scal_host; int* fh = flags_host;
+  *this = Problem();
+  arena = a; arena_cap = cap; arena_off = 0;
+  S = s_keep; S_capacity = s_cap;
+  scal_host = sh; flags_host = fh;
+}
+
+void Problem::destroy() {
+  if (arena) cudaFree(arena);
+  if (S) cudaFree(S);
   if (scal_host) cudaFreeHost(scal_host);
   if (flags_host) cudaFreeHost(flags_host);
-  scal_host = nullptr;
-  flags_host = nullptr;
-  S = nullptr;
-  S_capacity = 0;
   *this = Problem();
+}
+
+int Problem::arena_reserve(size_t bytes) {
+  arena_off = 0;
+  if (bytes <= arena_cap) return 0;
+  if (arena) cudaFree(arena);
+  arena = nullptr; arena_cap = 0;
+  const size_t want = bytes + bytes / 4;  // head-room: the scan grows by a keyframe per call
+  if (cudaMalloc(&arena, want) != cudaSuccess) {
+    cudaGetLastError();
+    if (cudaMalloc(&arena, bytes) != cudaSuccess) { cudaGetLastError(); arena = nullptr; return HSFM_BA_ERR_NOMEM; }
+    arena_cap = bytes;
+    return 0;
+  }
+  arena_cap = want;
+  return 0;
+}
+
+void* Problem::arena_take(size_t bytes) {
+  const size_t need = (bytes + 255) & ~(size_t)255;
+  if (arena_off + need > arena_cap) return nullptr;
+  void* p = arena + arena_off;
+  arena_off += need;
+  return p;
 }
 
 namespace {
 
 template <typename T>
 int dev_alloc(Problem& P, T** out, size_t count) {
-  void* p = nullptr;
   if (count == 0) count = 1;
-  cudaError_t e = cudaMalloc(&p, count * sizeof(T));
-  if (e != cudaSuccess) return HSFM_BA_ERR_NOMEM;
-  P.allocs.push_back(p);
+  void* p = P.arena_take(count * sizeof(T));
+  if (!p) return HSFM_BA_ERR_NOMEM;
   *out = reinterpret_cast<T*>(p);
   return 0;
 }
@@ -131,6 +160,17 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   for (int i = 0; i < n; ++i)
     if (cam_idx[i] < 0 || cam_idx[i] >= n_cams || pt_idx[i] < 0 || pt_idx[i] >= n_pts) return HSFM_BA_ERR_ARG;
 
+  {
+    // upper bound of everything carved below (per observation / point / camera / tile / chunk) + sort scratch
+    const size_t no = (size_t)n, np = (size_t)n_pts, nc = (size_t)n_cams;
+    size_t sort_tmp = 0, t2 = 0;
+    int* nullk = nullptr;
+    cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp, nullk, nullk, nullk, nullk, std::max({n, n_pts, 1}), 0, 32, s);
+    t2 = sort_tmp;
+    const size_t need = 320 * no + 360 * np + 2400 * nc + 280 * (no / 128 + nc + np / 256 + 8) + 2 * t2 + ((size_t)1 << 20);
+    int rc = P.arena_reserve(need);
+    if (rc) return rc;
+  }
   const double t_h2d0 = now_ms();
   double2* obs_in; int *cam_in, *pt_in;
   ALLOC(obs_in, n); ALLOC(cam_in, n); ALLOC(pt_in, n);
@@ -164,8 +204,8 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, pt_in, pt, iota, P.order_pm, std::max(n, 1), 0, pbits, s);
   cub::DeviceRadixSort::SortPairs(nullptr, tmp2, cam, cam_sorted, iota, pos_cs, std::max({n, n_pts, 1}), 0, cbits, s);
   tmp_bytes = std::max(tmp_bytes, tmp2);
-  void* tmp = nullptr;
-  HSFM_CUDA(cudaMalloc(&tmp, tmp_bytes));
+  void* tmp = P.arena_take(tmp_bytes);
+  if (!tmp) return HSFM_BA_ERR_NOMEM;
   // Internal point ids: points ordered by their smallest observing camera (ties: caller id).  Points that
   // share cameras become neighbours, so a tile's camera rows, the camera-vector atomics of the mat-vec
   // and above all the 6x6 blocks of S that dense_schur updates stay within a small, L2-resident window.
@@ -195,7 +235,6 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     HSFM_CUDA(cudaMemsetAsync(cam_start, 0, sizeof(int) * ((size_t)n_cams + 1), s));
   }
   HSFM_CUDA(cudaStreamSynchronize(s));
-  cudaFree(tmp);
 
   // ---- tiles: greedy packing of whole points into <= TILE observations (host, O(n_pts)) ----
   std::vector<int> h_pt_start((size_t)n_pts + 1), h_cam_start((size_t)n_cams + 1);
@@ -270,8 +309,8 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   P.part_stride = std::max({P.n_tiles, cdiv(6 * n_cams, 256), cdiv(3 * n_pts, 256), 1});
   ALLOC(P.part, (size_t)PART_SLOTS * P.part_stride);
   ALLOC(P.scal, SCAL_SLOTS); ALLOC(P.flags, FLAG_SLOTS);
-  HSFM_CUDA(cudaMallocHost(&P.scal_host, sizeof(double) * SCAL_SLOTS));
-  HSFM_CUDA(cudaMallocHost(&P.flags_host, sizeof(int) * FLAG_SLOTS));
+  if (!P.scal_host) HSFM_CUDA(cudaMallocHost(&P.scal_host, sizeof(double) * SCAL_SLOTS));
+  if (!P.flags_host) HSFM_CUDA(cudaMallocHost(&P.flags_host, sizeof(int) * FLAG_SLOTS));
   HSFM_CUDA(cudaMemsetAsync(P.scal, 0, sizeof(double) * SCAL_SLOTS, s));
   HSFM_CUDA(cudaMemsetAsync(P.flags, 0, sizeof(int) * FLAG_SLOTS, s));
   HSFM_CUDA(cudaMemsetAsync(P.part, 0, sizeof(double) * (size_t)PART_SLOTS * P.part_stride, s));

@@ -51,8 +51,14 @@ struct Problem {
   int n_obs = 0, n_cams = 0, n_pts = 0, n_tiles = 0, n_chunks = 0;
   int max_track = 0;
   Dev d{};
-  // owned allocations (freed in release())
-  std::vector<void*> allocs;
+  // Device arena: ONE grow-only allocation per context that every per-problem buffer is carved from, so the
+  // per-keyframe calls of CSfM::mapping (CSfM.cpp:252-259) pay for cudaMalloc/cudaFree only when the problem
+  // outgrows the arena.  release() rewinds the arena; destroy() frees it (together with S and the pinned mirrors).
+  char* arena = nullptr;
+  size_t arena_cap = 0, arena_off = 0;
+  int arena_reserve(size_t bytes);  // grow (never shrink); invalidates previous carve-outs
+  void* arena_take(size_t bytes);   // 256-byte aligned; nullptr when exhausted
+  void destroy();
   // input order → point-major position (for the eval tap) and static copies
   int* order_pm = nullptr;  // [n_obs] input index of the j-th point-major observation
   int* pt_old_of_new = nullptr;  // [n_pts] caller's point id of internal point k (internal order: by smallest observing camera)
