@@ -274,7 +274,9 @@ __global__ void __launch_bounds__(256) cam_major_kernel(Dev d, const CamRow* __r
 // Camera-major gather of the per-observation 6-vectors written point-major by schur_pass_kernel<0>:
 // one warp per chunk (<= 256 observations of one camera), 48-byte records fetched through the
 // camera-major → point-major permutation, warp-reduced into chunk_part[chunk][0..5].
-__global__ void __launch_bounds__(256) cam_gather6_kernel(Dev d, const double* __restrict__ tobs, double* __restrict__ chunk_part) {
+__global__ void __launch_bounds__(256) cam_gather6_kernel(Dev d, const double* __restrict__ tobs, double* __restrict__ chunk_part,
+                                                          const int* __restrict__ skip_flag) {
+  if (skip_flag && *skip_flag) return;
   const int lane = threadIdx.x & 31;
   const int wc = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (wc >= d.n_chunks) return;
@@ -297,15 +299,16 @@ __global__ void __launch_bounds__(256) cam_gather6_kernel(Dev d, const double* _
     for (int k = 0; k < 6; ++k) chunk_part[(size_t)wc * 27 + k] = acc[k];
   }
 }
-// out[c][k] = (base ? base[c][k] : 0) - sum over the camera's chunks, in chunk order
-__global__ void cam_reduce6_sub_kernel(int n_cams, const int* __restrict__ cam_chunk_start, const double* __restrict__ chunk_part,
-                                       const double* __restrict__ base, double* __restrict__ out) {
+// out[c][k] = (base ? base[c][k] : 0) + sign * sum over the camera's chunks, in chunk order
+__global__ void cam_reduce6_kernel(int n_cams, const int* __restrict__ cam_chunk_start, const double* __restrict__ chunk_part,
+                                   const double* __restrict__ base, double sign, double* __restrict__ out, const int* __restrict__ skip_flag) {
+  if (skip_flag && *skip_flag) return;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n_cams * 6) return;
   const int c = idx / 6, k = idx % 6;
   double s = 0.0;
   for (int w = cam_chunk_start[c]; w < cam_chunk_start[c + 1]; ++w) s += chunk_part[(size_t)w * 27 + k];
-  out[idx] = (base ? base[idx] : 0.0) - s;
+  out[idx] = (base ? base[idx] : 0.0) + sign * s;
 }
 
 // Fold the chunk partials of each camera in chunk order (deterministic).
@@ -475,11 +478,14 @@ __global__ void __launch_bounds__(TILE) schur_pass_kernel(Dev d, const double* _
   double w0, w1, w2;
   sym3_mul(Hi, v[0], v[1], v[2], w0, w1, w2);  // Hpp^-1 W^T (.)
   if (MODE == 1) {
+    // t_i = Jc_i^T (I - Jp Hpp^-1 Jp^T)(Jc p) per observation; summed per camera by the gather pass
     if (t.valid) {
       const double y0 = u0 - (jp[0] * w0 + jp[1] * w1 + jp[2] * w2);
       const double y1 = u1 - (jp[3] * w0 + jp[4] * w1 + jp[5] * w2);
+      double2* dst = reinterpret_cast<double2*>(vec_out + 6 * (size_t)t.i);
 #pragma unroll
-      for (int k = 0; k < 6; ++k) atomicAdd(vec_out + 6 * (size_t)c + k, jc[k] * y0 + jc[6 + k] * y1);
+      for (int k = 0; k < 3; ++k)
+        dst[k] = make_double2(jc[2 * k] * y0 + jc[6 + 2 * k] * y1, jc[2 * k + 1] * y0 + jc[7 + 2 * k] * y1);
     }
     return;
   }
@@ -944,20 +950,30 @@ void launch_schur_rhs(Problem& P, bool preload_gc, cudaStream_t s) {
     P.launches++;
   }
   if (P.n_chunks > 0) {
-    cam_gather6_kernel<<<cdiv(P.n_chunks, 8), 256, 0, s>>>(P.d, P.tobs, P.chunk_part);
+    cam_gather6_kernel<<<cdiv(P.n_chunks, 8), 256, 0, s>>>(P.d, P.tobs, P.chunk_part, nullptr);
     P.launches++;
   }
   if (P.n_cams > 0) {
-    cam_reduce6_sub_kernel<<<cdiv(P.n_cams * 6, 256), 256, 0, s>>>(P.n_cams, P.d.cam_chunk_start, P.chunk_part, preload_gc ? P.gc : nullptr, P.rhs);
+    cam_reduce6_kernel<<<cdiv(P.n_cams * 6, 256), 256, 0, s>>>(P.n_cams, P.d.cam_chunk_start, P.chunk_part, preload_gc ? P.gc : nullptr, -1.0, P.rhs, nullptr);
     P.launches++;
   }
 }
 
 void launch_schur_matvec(Problem& P, const double* pvec, double* q, cudaStream_t s) {
-  if (P.n_tiles == 0) return;
-  schur_pass_kernel<1><<<P.n_tiles, TILE, 0, s>>>(P.d, P.Hpp_inv, P.zp, pvec, q, nullptr, nullptr, nullptr, nullptr, P.part,
-                                                  P.part_stride, P.flags, 1, 1);
-  P.launches++;
+  // q = (Jc^T (I - Jp Hpp^-1 Jp^T) Jc) p  (overwrites q; honours F_PCG_DONE)
+  if (P.n_tiles > 0) {
+    schur_pass_kernel<1><<<P.n_tiles, TILE, 0, s>>>(P.d, P.Hpp_inv, P.zp, pvec, P.tobs, nullptr, nullptr, nullptr, nullptr, P.part,
+                                                    P.part_stride, P.flags, 1, 1);
+    P.launches++;
+  }
+  if (P.n_chunks > 0) {
+    cam_gather6_kernel<<<cdiv(P.n_chunks, 8), 256, 0, s>>>(P.d, P.tobs, P.chunk_part, P.flags + F_PCG_DONE);
+    P.launches++;
+  }
+  if (P.n_cams > 0) {
+    cam_reduce6_kernel<<<cdiv(P.n_cams * 6, 256), 256, 0, s>>>(P.n_cams, P.d.cam_chunk_start, P.chunk_part, nullptr, 1.0, q, P.flags + F_PCG_DONE);
+    P.launches++;
+  }
 }
 
 void launch_backsub(Problem& P, cudaStream_t s) {
