@@ -31,6 +31,12 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+# FP64 tensor (DMMA m8n8k4) peak measured on this pool with scripts/micro/fp64_peaks.cu (profiles/r01_fp64_peaks.txt);
+# MEASURED_PEAKS.json carries no FP64 figure (nominal: 128 flop/clk/SM x 148 SMs x 1.965 GHz = 37.2 TFLOP/s).
+FP64_DMMA_PEAK_TFLOPS = 37.1
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures (profiles/), c4
+TRAFFIC_C4 = {"rj_form": 985.6e6, "schur_matvec": 982.2e6}
+
 METRIC = "lm_iterations_per_s"
 UNIT = "LM iterations/s"
 
@@ -224,6 +230,13 @@ def main():
     rj_obs = torch.tensor([obs_per_s_local], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(rj_obs, op=dist.ReduceOp.SUM)
+    dense = summ["linear_solver_used"] == api.LINEAR_DENSE_SCHUR
+    chol = None
+    if dense and rank == 0:
+        n6 = 6 * n_cams
+        f_ms, s_ms, res = ctx.bench_cholesky(n6, 3)
+        chol = {"n": n6, "factor_ms": f_ms, "solve_ms": s_ms, "flop": n6 ** 3 / 3.0, "tflops": n6 ** 3 / 3.0 / f_ms * 1e-9,
+                "frac_of_fp64_dmma_peak": n6 ** 3 / 3.0 / f_ms * 1e-9 / FP64_DMMA_PEAK_TFLOPS, "solve_residual": res}
 
     # ---- end-to-end arm: host buffers through the C ABI ----------------------------------------
     e2e = None
@@ -263,7 +276,19 @@ def main():
                "eval_obs_per_s": 2 * n_obs_total / max(so["eval_seconds"], 1e-9)}
 
     if rank == 0:
-        dom = max(("rj_form", "schur_matvec", "backsub", "cam_form"), key=lambda k: kernels[k]["ms"])
+        phases = dict(zip(["linearise", "reduced_system", "factor", "reduced_solve", "step_backsub_cost", "readback"], summ["phase_ms"][:6]))
+        hbm_dom = max(("rj_form", "schur_matvec", "backsub", "cam_form"), key=lambda k: kernels[k]["ms"])
+        traffic = TRAFFIC_C4.get(hbm_dom) if (args.config == "c4" and world == 1) else None
+        roof_hbm = {"kernel": "rj_kernel<write_j,form>" if hbm_dom == "rj_form" else hbm_dom, "bound": "hbm", "achieved": kernels[hbm_dom]["gbs"],
+                    "peak": peak, "unit": "GB/s", "frac": kernels[hbm_dom]["gbs"] / peak, "traffic": traffic, "peak_source": peak_src}
+        if dense and phases["factor"] >= max(phases["linearise"], phases["reduced_system"], phases["step_backsub_cost"]):
+            # the step is dominated by the dense Cholesky of the reduced camera system: FP64 tensor (DMMA) bound
+            roofline = {"kernel": "chol_syrk_kernel (dense Cholesky of S, DMMA m8n8k4)", "bound": "tensor", "achieved": chol["tflops"],
+                        "peak": FP64_DMMA_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": chol["frac_of_fp64_dmma_peak"], "traffic": None,
+                        "peak_source": "FP64 DMMA peak measured with scripts/micro/fp64_peaks.cu on this pool (MEASURED_PEAKS.json has no FP64 figure)",
+                        "share_of_step": phases["factor"] / max(sum(phases.values()), 1e-9)}
+        else:
+            roofline = roof_hbm
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
@@ -275,9 +300,11 @@ def main():
             "rj_obs_per_s": float(rj_obs.item()),
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"kernel": "rj_kernel<write_j,form>" if dom == "rj_form" else dom, "bound": "hbm", "achieved": kernels[dom]["gbs"],
-                         "peak": peak, "unit": "GB/s", "frac": kernels[dom]["gbs"] / peak, "traffic": None, "peak_source": peak_src},
+            "roofline": roofline,
+            "roofline_hbm": roof_hbm,
+            "phase_ms_per_step": phases,
             "kernels": kernels,
+            "cholesky": chol,
             "e2e": e2e,
             "cpu_baseline": cpu,
         }
