@@ -71,40 +71,47 @@ __device__ __forceinline__ void tile_mma32(double& c0, double& c1, const double*
 // register window that shifts left by one column per step, so the step body is the same ~100
 // instructions for every column (a fully unrolled triangle would be ~6000 instructions executed once —
 // instruction-fetch bound).  The pivot column is broadcast through `col` (64 doubles of shared memory,
-// written twice so that col[j+c] needs no wrap).  D (row stride LB) receives L (strict upper zeroed),
-// dinv[r] = 1/L[r][r].  Returns 0 or the 1-based failing column.
+// written twice so that col[j+c] needs no wrap).  The NEXT pivot is formed first in every step and its
+// reciprocal square root is started before the rest of the row update, so the rsqrt latency — the serial
+// chain of the whole factorisation — overlaps the 30 remaining FMAs.  D (row stride LB) receives L (strict
+// upper zeroed), dinv[r] = 1/L[r][r].  Returns 0 or the 1-based failing column.
 __device__ __forceinline__ int warp_chol32(double* __restrict__ D, double* __restrict__ col, double* __restrict__ dinv, int lane) {
   double a[SB];
 #pragma unroll
   for (int c = 0; c < SB; ++c) a[c] = D[lane * LB + c];
   int bad = 0;
+  double d = __shfl_sync(0xffffffffu, a[0], 0);
+  double inv = rsqrt(d);
 #pragma unroll 1
   for (int j = 0; j < SB; ++j) {
+    if (!(d > 0.0) || !isfinite(d)) { bad = j + 1; break; }  // uniform: d is a broadcast
     col[lane] = a[0];
     col[lane + SB] = a[0];
     __syncwarp();
-    const double d = col[j];
-    if (!(d > 0.0) || !isfinite(d)) { bad = j + 1; break; }  // uniform
-    const double inv = rsqrt(d);
     const double u = a[0] * (inv * inv);
     double l = a[0] * inv;
     if (lane == j) { l = d * inv; dinv[j] = inv; }
     D[lane * LB + j] = (lane >= j) ? l : 0.0;
+    a[0] = fma(-u, col[j + 1], a[1]);
+    d = __shfl_sync(0xffffffffu, a[0], (j + 1) & 31);
+    inv = rsqrt(d);
 #pragma unroll
-    for (int c = 1; c < SB; ++c) a[c - 1] = fma(-u, col[j + c], a[c]);  // columns past 31 hold don't-care values
+    for (int c = 2; c < SB; ++c) a[c - 1] = fma(-u, col[j + c], a[c]);  // columns past 31 hold don't-care values
     __syncwarp();
   }
   return bad;
 }
 
-// Inverse of the lower-triangular 32x32 sub-block D by one warp, written to X (both row stride LB).
-// Row k of the inverse is final at step k; lane k publishes it in X and the lanes below eliminate it.
-__device__ __forceinline__ void warp_trinv32(const double* __restrict__ D, double my_dinv, double* __restrict__ X, int lane) {
+// Inverse of the lower-triangular 32x32 sub-block D by one warp, written to X (both row stride LB; X may
+// alias D: row k of D is dead once row k of the inverse is published).  Row k of the inverse is final at
+// step k; lane k publishes it and the lanes below eliminate it.
+__device__ __forceinline__ void warp_trinv32(const double* D, double my_dinv, double* X, int lane) {
   double x[SB];
 #pragma unroll
   for (int c = 0; c < SB; ++c) x[c] = (c == lane) ? 1.0 : 0.0;
 #pragma unroll 1
   for (int k = 0; k < SB; ++k) {
+    const double lrk = (lane > k) ? D[lane * LB + k] : 0.0;  // read before row k is overwritten (only rows > k are read)
     if (lane == k) {
 #pragma unroll
       for (int c = 0; c < SB; c += 2)
@@ -112,7 +119,6 @@ __device__ __forceinline__ void warp_trinv32(const double* __restrict__ D, doubl
     }
     __syncwarp();
     if (lane > k) {
-      const double lrk = D[lane * LB + k];
 #pragma unroll
       for (int c = 0; c < SB; c += 2) {
         const double2 xk = *reinterpret_cast<const double2*>(X + k * LB + c);
@@ -130,16 +136,16 @@ __device__ long long g_diag_clk[32];
 #define DIAG_TICK(k) do { } while (0)
 #endif
 
-constexpr int kDiagSmem = (20 * SBLK + 3 * SBLK + NB) * (int)sizeof(double) + 16;
+// 10 sub-blocks + 1/diag + pivot-column scratch: 94 KB, so that (with <= 128 registers per thread) the kernel
+// fits on an SM NEXT TO a resident trailing-update CTA and never has to wait for a whole SM to drain.
+constexpr int kDiagSmem = (10 * SBLK + NB + 2 * SB) * (int)sizeof(double) + 16;
 
-__global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, int n, int k0, int kb, double* __restrict__ Linv,
-                                                         int* __restrict__ fail) {
+__global__ void __launch_bounds__(256, 2) chol_diag_kernel(double* __restrict__ A, int n, int k0, int kb, double* Linv, int* __restrict__ fail) {
   extern __shared__ __align__(16) double dsm[];
-  double* sL = dsm;                 // [10][32][LB] lower sub-blocks of the matrix, then of L
-  double* sX = sL + 10 * SBLK;      // [10][32][LB] lower sub-blocks of L^-1
-  double* sT = sX + 10 * SBLK;      // [3][32][LB]  block-product temporaries
-  double* sDinv = sT + 3 * SBLK;    // [128] 1 / L[i][i]
-  int* sBad = reinterpret_cast<int*>(sDinv + NB);
+  double* sL = dsm;                 // [10][32][LB] lower sub-blocks: the matrix, then L, then (in place) the pieces of L^-1
+  double* sDinv = sL + 10 * SBLK;   // [128] 1 / L[i][i]
+  double* sCol = sDinv + NB;        // [64] pivot-column broadcast of warp_chol32
+  int* sBad = reinterpret_cast<int*>(sCol + 2 * SB);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int failed = *fail;
   if (tid == 0) *sBad = 0;
@@ -167,12 +173,11 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
   for (int kq = 0; kq < 4; ++kq) {
     // (a) diagonal sub-block, warp 0
     if (warp == 0) {
-      const int bad = warp_chol32(sL + blk_id(kq, kq) * SBLK, sT, sDinv + kq * SB, lane);
+      const int bad = warp_chol32(sL + blk_id(kq, kq) * SBLK, sCol, sDinv + kq * SB, lane);
       if (bad && lane == 0) { *sBad = 1; atomicExch(fail, k0 + kq * SB + bad); }
     }
     __syncthreads();
     if (*sBad) return;
-    DIAG_TICK(2 + 3 * kq);
     if (kq == 3) break;
     // (b) sub-panel: rows below, X D^T = P by substitution, one thread per row
     {
@@ -200,7 +205,6 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
       }
     }
     __syncthreads();
-    DIAG_TICK(3 + 3 * kq);
     // (c) trailing update: L(bi,bj) -= L(bi,kq) L(bj,kq)^T for kq < bj <= bi, 16 tiles of 8x8 per sub-block
     {
       const int m = 3 - kq, ntiles = m * (m + 1) / 2 * 16;
@@ -220,56 +224,83 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
       }
     }
     __syncthreads();
-    DIAG_TICK(4 + 3 * kq);
   }
-  // ---- L^-1 ----
-  // diagonal sub-blocks: warps 0..3, in registers
-  if (warp < 4) {
-    warp_trinv32(sL + blk_id(warp, warp) * SBLK, sDinv[warp * SB + lane], sX + blk_id(warp, warp) * SBLK, lane);
-  }
-  __syncthreads();
-  DIAG_TICK(12);
-  // sub-diagonal d: X(i,j) = -X(i,i) * sum_{k=j}^{i-1} L(i,k) X(k,j),  j = i - d
-#pragma unroll 1
-  for (int d = 1; d < 4; ++d) {
-    const int nb = 4 - d;  // sub-blocks on this sub-diagonal
-    for (int t = warp; t < nb * 16; t += 8) {
-      const int b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
-      const int i = d + b, j = b;
-      double c0 = 0.0, c1 = 0.0;
-      for (int k = j; k < i; ++k) tile_mma32<true>(c0, c1, sL + blk_id(i, k) * SBLK, sX + blk_id(k, j) * SBLK, ti, tj, lane);
-      *reinterpret_cast<double2*>(sT + b * SBLK + (ti * 8 + (lane >> 2)) * LB + tj * 8 + 2 * (lane & 3)) = make_double2(c0, c1);
-    }
-    __syncthreads();
-    for (int t = warp; t < nb * 16; t += 8) {
-      const int b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
-      const int i = d + b, j = b;
-      double c0 = 0.0, c1 = 0.0;
-      tile_mma32<true>(c0, c1, sX + blk_id(i, i) * SBLK, sT + b * SBLK, ti, tj, lane);
-      *reinterpret_cast<double2*>(sX + blk_id(i, j) * SBLK + (ti * 8 + (lane >> 2)) * LB + tj * 8 + 2 * (lane & 3)) = make_double2(-c0, -c1);
-    }
-    __syncthreads();
-    DIAG_TICK(12 + d);
-  }
-  // ---- write back: L over the lower triangle of A, L^-1 as a full 128x128 row-major block ----
+  DIAG_TICK(2);
+  // ---- L over the lower triangle of A ----
   for (int e = tid; e < NB * (NB / 2); e += 256) {
     const int i = e / (NB / 2), j = (e - i * (NB / 2)) * 2;
     const int bi = i / SB, bj = j / SB;
-    double2 lv = make_double2(0.0, 0.0), xv = make_double2(0.0, 0.0);
-    if (bj <= bi) {
-      const int off = blk_id(bi, bj) * SBLK + (i % SB) * LB + (j % SB);
-      lv = *reinterpret_cast<const double2*>(sL + off);
-      xv = *reinterpret_cast<const double2*>(sX + off);
-    }
-    reinterpret_cast<double2*>(Linv)[e] = xv;  // sub-blocks hold zeros above the diagonal already
-    if (i < kb && j <= i) {
+    if (bj <= bi && i < kb && j <= i) {
+      const double2 lv = *reinterpret_cast<const double2*>(sL + blk_id(bi, bj) * SBLK + (i % SB) * LB + (j % SB));
       double* dst = A + (size_t)(k0 + i) * n + k0 + j;
       if (j + 1 <= i && j + 1 < kb) *reinterpret_cast<double2*>(dst) = lv;
       else dst[0] = lv.x;
     }
   }
   __syncthreads();
-  DIAG_TICK(16);
+  DIAG_TICK(3);
+  // ---- L^-1, in place ----
+  // (1) diagonal sub-blocks X(i,i) = L(i,i)^-1: warps 0..3, in registers, over L(i,i)
+  if (warp < 4) warp_trinv32(sL + blk_id(warp, warp) * SBLK, sDinv[warp * SB + lane], sL + blk_id(warp, warp) * SBLK, lane);
+  __syncthreads();
+  DIAG_TICK(4);
+  // (2) M(i,k) = X(i,i) L(i,k) over L(i,k), i > k: all 96 tiles to registers, barrier, write back
+  {
+    double m0[12], m1[12];
+#pragma unroll
+    for (int q = 0; q < 12; ++q) {
+      const int t = warp + 8 * q;
+      const int b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
+      int i = 1;
+      while (blk_id(i + 1, 0) - (i + 1) <= b) ++i;  // off-diagonal blocks before row i+1: i(i+1)/2
+      const int k = b - i * (i - 1) / 2;
+      m0[q] = 0.0; m1[q] = 0.0;
+      tile_mma32<true>(m0[q], m1[q], sL + blk_id(i, i) * SBLK, sL + blk_id(i, k) * SBLK, ti, tj, lane);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < 12; ++q) {
+      const int t = warp + 8 * q;
+      const int b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
+      int i = 1;
+      while (blk_id(i + 1, 0) - (i + 1) <= b) ++i;
+      const int k = b - i * (i - 1) / 2;
+      *reinterpret_cast<double2*>(sL + blk_id(i, k) * SBLK + (ti * 8 + (lane >> 2)) * LB + tj * 8 + 2 * (lane & 3)) = make_double2(m0[q], m1[q]);
+    }
+  }
+  __syncthreads();
+  DIAG_TICK(5);
+  // diagonal sub-blocks and the zero upper sub-blocks of the output
+  for (int e = tid; e < NB * (NB / 2); e += 256) {
+    const int i = e / (NB / 2), j = (e - i * (NB / 2)) * 2;
+    const int bi = i / SB, bj = j / SB;
+    if (bj == bi) reinterpret_cast<double2*>(Linv)[e] = *reinterpret_cast<const double2*>(sL + blk_id(bi, bi) * SBLK + (i % SB) * LB + (j % SB));
+    else if (bj > bi) reinterpret_cast<double2*>(Linv)[e] = make_double2(0.0, 0.0);
+  }
+  // (3) sub-diagonal d: X(i,j) = - sum_{k=j}^{i-1} M(i,k) X(k,j), j = i - d.  X(j,j) comes from shared memory, the
+  //     X(k,j) of earlier sub-diagonals from the output block itself (L2).
+#pragma unroll 1
+  for (int d = 1; d < 4; ++d) {
+    const int nb = 4 - d;
+    for (int t = warp; t < nb * 16; t += 8) {
+      const int b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
+      const int i = d + b, j = b;
+      const int fr = lane >> 2, fk = lane & 3;
+      double c0 = 0.0, c1 = 0.0;
+      tile_mma32<true>(c0, c1, sL + blk_id(i, j) * SBLK, sL + blk_id(j, j) * SBLK, ti, tj, lane);
+      for (int k = j + 1; k < i; ++k) {
+        double bq[SB / 4];
+#pragma unroll
+        for (int ks = 0; ks < SB / 4; ++ks) bq[ks] = __ldcg(Linv + (size_t)(k * SB + ks * 4 + fk) * NB + j * SB + tj * 8 + fr);
+        const double* Mik = sL + blk_id(i, k) * SBLK;
+#pragma unroll
+        for (int ks = 0; ks < SB / 4; ++ks) dmma884(c0, c1, Mik[(ti * 8 + fr) * LB + ks * 4 + fk], bq[ks]);
+      }
+      *reinterpret_cast<double2*>(Linv + (size_t)(i * SB + ti * 8 + fr) * NB + j * SB + tj * 8 + 2 * fk) = make_double2(-c0, -c1);
+    }
+    __syncthreads();
+  }
+  DIAG_TICK(6);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -819,9 +850,9 @@ void launch_spd_err(int n, const double* x, double* err, cudaStream_t s) {
   long long h[32];
   cudaStreamSynchronize(s);
   cudaMemcpyFromSymbol(h, g_diag_clk, sizeof(h));
-  const char* nm[17] = {"", "load", "fac0", "sub0", "upd0", "fac1", "sub1", "upd1", "fac2", "sub2", "upd2", "fac3", "trinv", "inv1", "inv2", "inv3", "store"};
-  for (int k = 1; k <= 16; ++k) std::fprintf(stderr, "%s %lld  ", nm[k], h[k] - h[k - 1]);
-  std::fprintf(stderr, "total %lld clk\n", h[16] - h[0]);
+  const char* nm[7] = {"", "load", "factor", "storeL", "trinv", "M", "levels"};
+  for (int k = 1; k <= 6; ++k) std::fprintf(stderr, "%s %lld  ", nm[k], h[k] - h[k - 1]);
+  std::fprintf(stderr, "total %lld clk\n", h[6] - h[0]);
 #endif
 }
 
@@ -874,10 +905,12 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
   if (!bulk_ctas) {
     const char* e = getenv("HSFM_BULK_CTAS");  // experiment knob: <0 means n_sm + value
     bulk_ctas = e ? atoi(e) : 2 * n_sm;
-    if (bulk_ctas <= 0) bulk_ctas = n_sm + bulk_ctas;
+    if (bulk_ctas == 0) bulk_ctas = 1 << 30;  // one tile per CTA: slots turn over every tile, chain kernels slip in
+    else if (bulk_ctas < 0) bulk_ctas = n_sm + bulk_ctas;
   }
   const int panels = (n + NB - 1) / NB;
-  const bool la = aux && aux->stream && panels > 2;
+  static const bool no_la = getenv("HSFM_NO_LOOKAHEAD") != nullptr;  // experiment knob
+  const bool la = aux && aux->stream && panels > 2 && !no_la;
   cudaStream_t s2 = la ? aux->stream : s;
   if (la) {
     cudaEventRecord(aux->ev_fork, s);
@@ -909,7 +942,7 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
     }
     if (la) cudaEventRecord(aux->ev_rest, s);
     if (rb > 2) {
-      chol_syrk_kernel<<<min((rb - 2) * (rb - 1), bulk_ctas), 128, kGemmSmem, s>>>(S, n, k0, 0, -4, (rb - 2) * (rb - 1), bulk_ctas > n_sm ? 1 : 0, fail_flag);
+      chol_syrk_kernel<<<min((rb - 2) * (rb - 1), bulk_ctas), 128, kGemmSmem, s>>>(S, n, k0, 0, -4, (rb - 2) * (rb - 1), 0, fail_flag);
       ++*launches;
     }
   }
