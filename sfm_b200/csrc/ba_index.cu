@@ -148,6 +148,34 @@ void launch_rows_to_caller(Problem& P, int w, const double* internal_order, doub
   P.launches++;
 }
 
+// One CTA per tile: the tile's distinct cameras in ascending order and the slot of every observation's
+// camera in that list.  O(TILE^2) comparisons through shared-memory broadcasts; runs once per upload.
+__global__ void __launch_bounds__(TILE) tile_cams_kernel(const int* __restrict__ tile_start, const int* __restrict__ cam,
+                                                          unsigned char* __restrict__ slot, int* __restrict__ tile_cams,
+                                                          int* __restrict__ tile_hdr, int* __restrict__ max_ncam) {
+  __shared__ int sc[TILE];
+  __shared__ int sfirst[TILE];
+  const int b = tile_start[blockIdx.x], e = tile_start[blockIdx.x + 1];
+  const int tid = threadIdx.x, i = b + tid, cnt = e - b;
+  const int c = i < e ? cam[i] : 0x7fffffff;
+  sc[tid] = c;
+  __syncthreads();
+  int first = i < e;
+  for (int j = 0; j < tid; ++j) first &= (sc[j] != c);
+  sfirst[tid] = first;
+  const int ncam = __syncthreads_count(first);
+  int rank = 0;
+  for (int j = 0; j < cnt; ++j) rank += (sfirst[j] && sc[j] < c);
+  if (i < e) {
+    slot[i] = (unsigned char)rank;
+    if (first) tile_cams[(size_t)blockIdx.x * TILE + rank] = c;
+  }
+  if (tid == 0) {
+    tile_hdr[8 * (size_t)blockIdx.x + 4] = ncam;
+    atomicMax(max_ncam, ncam);
+  }
+}
+
 int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
                   int32_t n_cams, const double* K9, const double* dist, const double* cam_rt, int64_t n_pts64, const double* pts,
                   Comm& comm, cudaStream_t s, double* setup_ms, double* h2d_ms) {
@@ -167,7 +195,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     int* nullk = nullptr;
     cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp, nullk, nullk, nullk, nullk, std::max({n, n_pts, 1}), 0, 32, s);
     t2 = sort_tmp;
-    const size_t need = 320 * no + 360 * np + 2400 * nc + 280 * (no / 128 + nc + np / 256 + 8) + 2 * t2 + ((size_t)1 << 20);
+    const size_t need = 336 * no + 360 * np + 2400 * nc + 280 * (no / 128 + nc + np / 256 + 8) + 2 * t2 + ((size_t)1 << 20);
     int rc = P.arena_reserve(need);
     if (rc) return rc;
   }
@@ -241,21 +269,23 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   HSFM_CUDA(cudaMemcpyAsync(h_pt_start.data(), pt_start, sizeof(int) * ((size_t)n_pts + 1), cudaMemcpyDeviceToHost, s));
   HSFM_CUDA(cudaMemcpyAsync(h_cam_start.data(), cam_start, sizeof(int) * ((size_t)n_cams + 1), cudaMemcpyDeviceToHost, s));
   HSFM_CUDA(cudaStreamSynchronize(s));
-  std::vector<int> tiles;
+  std::vector<int> tiles, tile_p;  // first observation / first point of every tile (+ end sentinels)
   tiles.reserve((size_t)n / (TILE - 32) + 2);
+  tile_p.reserve((size_t)n / (TILE - 32) + 2);
   int max_track = 0;
   {
-    int tile_b = 0;
-    tiles.push_back(0);
+    int tile_b = 0, p_end = 0;  // p_end: one past the last point that has observations (the others are sorted last)
+    tiles.push_back(0); tile_p.push_back(0);
     for (int p = 0; p < n_pts; ++p) {
       const int b = h_pt_start[p], e = h_pt_start[p + 1];
       max_track = std::max(max_track, e - b);
+      if (e > b) p_end = p + 1;
       if (e - tile_b > TILE) {  // point p does not fit: close the tile before it
-        if (b > tile_b) { tiles.push_back(b); tile_b = b; }
+        if (b > tile_b) { tiles.push_back(b); tile_p.push_back(p); tile_b = b; }
       }
     }
-    if (n > tile_b) tiles.push_back(n);
-    if (tiles.size() == 1) tiles.clear();
+    if (n > tile_b) { tiles.push_back(n); tile_p.push_back(p_end); }
+    if (tiles.size() == 1) { tiles.clear(); tile_p.clear(); }
   }
   P.max_track = max_track;
   if (max_track > MAX_TRACK) return HSFM_BA_ERR_UNSUPPORTED;
@@ -263,6 +293,23 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   int* tile_start;
   ALLOC(tile_start, tiles.size() + 1);
   if (!tiles.empty()) HSFM_CUDA(cudaMemcpyAsync(tile_start, tiles.data(), sizeof(int) * tiles.size(), cudaMemcpyHostToDevice, s));
+  // distinct cameras of every tile + each observation's slot in that list: the streaming kernels stage the
+  // tile's camera rows / camera vectors in shared memory once instead of gathering them per observation
+  unsigned char* slot; int *tile_cams, *tile_hdr, *d_max_ncam;
+  ALLOC(slot, n); ALLOC(tile_cams, (size_t)P.n_tiles * TILE); ALLOC(tile_hdr, 8 * (size_t)std::max(1, P.n_tiles)); ALLOC(d_max_ncam, 1);
+  P.max_tile_cams = 0;
+  if (P.n_tiles) {
+    std::vector<int> hdr(8 * (size_t)P.n_tiles, 0);
+    for (int k = 0; k < P.n_tiles; ++k) {
+      hdr[8 * (size_t)k] = tiles[k]; hdr[8 * (size_t)k + 1] = tiles[k + 1];
+      hdr[8 * (size_t)k + 2] = tile_p[k]; hdr[8 * (size_t)k + 3] = tile_p[k + 1];
+    }
+    HSFM_CUDA(cudaMemcpyAsync(tile_hdr, hdr.data(), sizeof(int) * hdr.size(), cudaMemcpyHostToDevice, s));
+    HSFM_CUDA(cudaMemsetAsync(d_max_ncam, 0, sizeof(int), s));
+    tile_cams_kernel<<<P.n_tiles, TILE, 0, s>>>(tile_start, cam, slot, tile_cams, tile_hdr, d_max_ncam);
+    HSFM_CUDA(cudaMemcpyAsync(&P.max_tile_cams, d_max_ncam, sizeof(int), cudaMemcpyDeviceToHost, s));
+    HSFM_CUDA(cudaStreamSynchronize(s));  // hdr is a local vector; max_tile_cams is needed by the launches
+  }
 
   // ---- camera-major warp chunks ----
   std::vector<int> ch_cam, ch_b, ch_e, cam_ch_start((size_t)n_cams + 1, 0);
@@ -324,6 +371,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   Dev& d = P.d;
   d.n_obs = n; d.n_cams = n_cams; d.n_pts = n_pts; d.n_tiles = P.n_tiles; d.n_chunks = P.n_chunks;
   d.obs = obs; d.cam = cam; d.pt = pt; d.pt_start = pt_start; d.tile_start = tile_start;
+  d.tile_cams = tile_cams; d.tile_hdr = reinterpret_cast<const int4*>(tile_hdr); d.slot = slot;
   d.obs_cs = obs_cs; d.pt_cs = pt_cs; d.pos_cs = pos_cs; d.chunk_cam = d_ch_cam; d.chunk_b = d_ch_b; d.chunk_e = d_ch_e; d.cam_chunk_start = d_cam_ch_start;
   d.r = r; d.Jc = Jc; d.Jp = Jp;
   HSFM_CUDA(cudaStreamSynchronize(s));

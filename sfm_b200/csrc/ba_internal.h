@@ -31,6 +31,10 @@ struct Dev {
   const int* pt;         // [n_obs]
   const int* pt_start;   // [n_pts+1] CSR over point-major observations
   const int* tile_start; // [n_tiles+1] first observation of each tile (tiles hold whole points)
+  const int4* tile_hdr;  // [n_tiles][2] {first obs, end obs, first point, end point}, {distinct cameras, 0, 0, 0}: one
+                         // 32-byte record so that a CTA learns everything about its tile in a single memory round trip
+  const int* tile_cams;  // [n_tiles][TILE] distinct cameras of each tile, ascending (first hdr.ncam entries valid)
+  const unsigned char* slot;  // [n_obs] position of the observation's camera in its tile's list
   // static, camera-major order
   const double2* obs_cs; // [n_obs]
   const int* pt_cs;      // [n_obs]
@@ -50,6 +54,7 @@ struct Problem {
   int mode = 2;
   int n_obs = 0, n_cams = 0, n_pts = 0, n_tiles = 0, n_chunks = 0;
   int max_track = 0;
+  int max_tile_cams = 0;  // largest number of distinct cameras in one tile (sizes the shared-memory row staging)
   Dev d{};
   // Device arena: ONE grow-only allocation per context that every per-problem buffer is carved from, so the
   // per-keyframe calls of CSfM::mapping (CSfM.cpp:252-259) pay for cudaMalloc/cudaFree only when the problem

@@ -3,8 +3,8 @@
 // Data layout: observations are kept twice, both static after upload:
 //   * point-major (sorted by point), cut into TILES of <= 256 observations that contain whole
 //     points only.  One CTA = one tile, one thread = one observation.  All point-keyed sums
-//     (Hpp, g_p, W^T y, back-substitution) are warp-shuffle segmented scans inside the tile,
-//     stitched across warps through shared memory — deterministic, no atomics.
+//     (Hpp, g_p, W^T y, back-substitution) are staged per observation in shared memory and added
+//     per point in observation order — deterministic, no atomics.
 //   * camera-major (sorted by camera), cut into warp CHUNKS of <= 256 observations of ONE
 //     camera.  Camera-keyed sums that are needed once per linearisation (Hcc, g_c, the
 //     block-Jacobi diagonal) are recomputed here from 20 B/observation + a point gather
@@ -29,6 +29,41 @@ __device__ __forceinline__ CamRow load_row(const CamRow* rows, int c) {
   for (int q = 0; q < 12; ++q) dst[q] = __ldg(src + q);
   return C;
 }
+
+// Everything a CTA needs to know about its tile, from one 32-byte record.
+struct TileHdr { int b, e, p_first, n_p, ncam; };
+__device__ __forceinline__ TileHdr tile_hdr(const Dev& d) {
+  const int4 h0 = __ldg(d.tile_hdr + 2 * (size_t)blockIdx.x), h1 = __ldg(d.tile_hdr + 2 * (size_t)blockIdx.x + 1);
+  TileHdr t;
+  t.b = h0.x; t.e = h0.y; t.p_first = h0.z; t.n_p = h0.w - h0.z; t.ncam = h1.x;
+  return t;
+}
+
+// Shared-memory staging of a tile's camera rows and points.  The index holds, per tile, the ascending list of its
+// distinct cameras (~40 at Venice shape, against ~18 distinct rows touched by EVERY one of the twelve 16-byte
+// gathers a warp would otherwise issue) and, per observation, the slot of its camera in that list; a tile's
+// points are the contiguous range [p_first, p_first + n_p).  All 256 threads copy rows and points with coalesced
+// loads that depend on nothing but the tile header, so the whole input of the tile is two memory round trips
+// away; the observations then read their row IN PLACE from shared memory.  Row stride 208 B: eight
+// consecutive slots fall in eight different 16-byte bank groups.
+constexpr int ROW_LD = 13;  // double2 per staged row (12 + 1 pad)
+__device__ __forceinline__ void stage_rows(const Dev& d, const TileHdr& t, const CamRow* __restrict__ rows, double2* sR) {
+  const int* list = d.tile_cams + (size_t)blockIdx.x * TILE;
+  const int m = t.ncam * 12;
+  for (int q = threadIdx.x; q < m; q += TILE) {
+    const int sl = q / 12, piece = q - sl * 12;
+    sR[sl * ROW_LD + piece] = __ldg(reinterpret_cast<const double2*>(rows + __ldg(list + sl)) + piece);
+  }
+}
+__device__ __forceinline__ void stage_points(const TileHdr& t, const double* __restrict__ src, double* sX) {
+  const double* g = src + 3 * (size_t)t.p_first;
+  for (int q = threadIdx.x; q < 3 * t.n_p; q += TILE) sX[q] = __ldg(g + q);
+}
+__device__ __forceinline__ const CamRow& staged_row(const double2* sR, int slot) {
+  return *reinterpret_cast<const CamRow*>(sR + slot * ROW_LD);
+}
+// dynamic shared memory of the kernels that stage rows (doubles): rows, then X, then whatever the kernel adds
+__host__ __device__ constexpr int rows_doubles(int row_cap) { return 2 * ROW_LD * row_cap; }
 
 __device__ __forceinline__ constexpr int tri6(int a, int b) { return a * 6 - (a * (a - 1)) / 2 + (b - a); }  // a <= b
 
@@ -69,55 +104,6 @@ __device__ __forceinline__ TileThread tile_thread(const Dev& d) {
   return t;
 }
 
-// Replace v[] (this observation's contribution; zeros on invalid threads) by the sum over all
-// observations of the thread's point.  In-warp inclusive segmented scan by shuffles, warp-local
-// total fetched from the segment's last lane, cross-warp pieces stitched through shared memory
-// in a fixed order (deterministic).  sm: 2*8*K doubles.  Must be called by all 256 threads.
-template <int K>
-__device__ __forceinline__ void tile_segment_total(double (&v)[K], const TileThread& t, double* sm) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int warp_base = t.tile_b + warp * 32;
-  const int first_lane = t.valid ? max(t.seg_b - warp_base, 0) : lane;
-  const int last_lane = t.valid ? min(t.seg_e - 1 - warp_base, 31) : lane;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-      const double up = __shfl_up_sync(FULL, v[k], d);
-      if (lane - d >= first_lane) v[k] += up;
-    }
-  }
-#pragma unroll
-  for (int k = 0; k < K; ++k) v[k] = __shfl_sync(FULL, v[k], last_lane);
-  const bool before = t.valid && (t.seg_b < warp_base);
-  const bool after = t.valid && (t.seg_e > warp_base + 32);
-  const bool crosses = before || after;
-  if (__syncthreads_or(crosses)) {
-    double* smF = sm;          // [8][K] piece of a segment that started in an earlier warp
-    double* smL = sm + 8 * K;  // [8][K] piece of a segment that starts here and continues
-    if (lane == 0 && before) {
-#pragma unroll
-      for (int k = 0; k < K; ++k) smF[warp * K + k] = v[k];
-    }
-    if (lane == 31 && after && !before) {
-#pragma unroll
-      for (int k = 0; k < K; ++k) smL[warp * K + k] = v[k];
-    }
-    __syncthreads();
-    if (crosses) {
-      const int w_head = (t.seg_b - t.tile_b) >> 5;
-      const int w_last = (t.seg_e - 1 - t.tile_b) >> 5;
-#pragma unroll
-      for (int k = 0; k < K; ++k) {
-        double s = smL[w_head * K + k];
-        for (int w = w_head + 1; w <= w_last; ++w) s += smF[w * K + k];
-        v[k] = s;
-      }
-    }
-    __syncthreads();
-  }
-}
-
 // ------------------------------------------------------------------------------------------
 __global__ void cam_prep_kernel(int n_cams, const double* __restrict__ cam, const double* __restrict__ K9,
                                 const double* __restrict__ dist, const double* __restrict__ scale_c, CamRow* __restrict__ rows) {
@@ -128,80 +114,150 @@ __global__ void cam_prep_kernel(int n_cams, const double* __restrict__ cam, cons
   rows[c] = C;
 }
 
+// Point-keyed sums of a tile through shared memory.  Every valid thread has stored its K values at
+// sv[k * SV_LD + threadIdx.x]; after the barrier one thread per (point of the tile, k) adds the L values
+// of that point in observation order (deterministic) and hands the total to out(point, k, total).
+// SV_LD = 257: the K lanes of one point fall in K distinct 8-byte banks.  The CSR bounds of the first
+// two task rounds are fetched by prefetch_point_bounds at kernel start, off the critical path.
+constexpr int SV_LD = TILE + 1;
+template <int K>
+__device__ __forceinline__ void prefetch_point_bounds(const Dev& d, const TileHdr& t, int (&bnd)[4]) {
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const int task = threadIdx.x + r * TILE;
+    bnd[2 * r] = bnd[2 * r + 1] = 0;
+    if (task < t.n_p * K) {
+      const int p = t.p_first + task / K;
+      bnd[2 * r] = __ldg(d.pt_start + p) - t.b;
+      bnd[2 * r + 1] = __ldg(d.pt_start + p + 1) - t.b;
+    }
+  }
+}
+template <int K, class Out>
+__device__ __forceinline__ void tile_point_sums(const Dev& d, const TileHdr& t, const int (&bnd)[4], const double* sv, Out&& out) {
+  const int n_task = t.n_p * K;
+#pragma unroll 1
+  for (int r = 0, task = threadIdx.x; task < n_task; task += TILE, ++r) {
+    const int pl = task / K, k = task - pl * K;
+    const int p = t.p_first + pl;
+    int b, e;
+    if (r == 0) { b = bnd[0]; e = bnd[1]; }
+    else if (r == 1) { b = bnd[2]; e = bnd[3]; }
+    else { b = __ldg(d.pt_start + p) - t.b; e = __ldg(d.pt_start + p + 1) - t.b; }
+    const double* src = sv + k * SV_LD;
+    double s0 = 0.0, s1 = 0.0;
+    int l = b;
+    for (; l + 1 < e; l += 2) { s0 += src[l]; s1 += src[l + 1]; }
+    if (l < e) s0 += src[l];
+    out(p, k, s0 + s1);
+  }
+}
+
 // Kernel RJ: residual + Jacobian per observation (a1), fused with the point-keyed part of the
 // normal equations (a7: Hpp = sum Jp^T Jp, g_p = sum Jp^T r) and the cost partial (a6).
 // Algorithmic bytes / observation: 24 in (obs 16, cam 4, pt 4) + 160 out (r 16, Jc 96, Jp 48).
+// Memory round trips on the critical path of a CTA: tile header -> {observations, slots, point ids, camera list,
+// points, scales, CSR bounds} -> camera rows.  Every Jacobian column is stored the moment it is formed and the
+// camera row is read in place from shared memory, which keeps the kernel at 64 registers = four CTAs per SM.
 template <bool WRITE_J, bool FORM>
-__global__ void __launch_bounds__(TILE) rj_kernel(Dev d, const CamRow* __restrict__ rows, const double* __restrict__ pts,
-                                                   const double* __restrict__ scale_p, double* __restrict__ Hpp,
-                                                   double* __restrict__ gp, double* __restrict__ cost_part) {
-  __shared__ double sm[2 * 8 * 9];
-  const TileThread t = tile_thread(d);
+__global__ void __launch_bounds__(TILE, 3) rj_kernel(Dev d, const CamRow* __restrict__ rows, const double* __restrict__ pts,
+                                                      const double* __restrict__ scale_p, double* __restrict__ Hpp,
+                                                      double* __restrict__ gp, double* __restrict__ cost_part, int row_cap) {
+  extern __shared__ __align__(16) double dyn[];
+  double2* sR = reinterpret_cast<double2*>(dyn);
+  double* sX = dyn + rows_doubles(row_cap);  // [n_p][3] points
+  double* sS = sX + 3 * TILE;                // [n_p][3] point column scales
+  double* sv = sS + 3 * TILE;                // [9][SV_LD] (FORM)
+  __shared__ double sm[8];
+  const TileHdr t = tile_hdr(d);
+  const int i = t.b + (int)threadIdx.x;
+  const bool valid = i < t.e;
+  double2 o = make_double2(0.0, 0.0);
+  int pl = 0, slot = 0;
+  if (valid) {
+    o = __ldg(d.obs + i);
+    slot = __ldg(d.slot + i);
+    pl = __ldg(d.pt + i) - t.p_first;
+  }
+  int bnd[4];
+  if (FORM) prefetch_point_bounds<9>(d, t, bnd);
+  stage_points(t, pts, sX);
+  if (scale_p) stage_points(t, scale_p, sS);
+  stage_rows(d, t, rows, sR);
+  __syncthreads();
   double r0 = 0.0, r1 = 0.0;
-  double jc[12], jp[6];
-#pragma unroll
-  for (int k = 0; k < 6; ++k) jp[k] = 0.0;
-  if (t.valid) {
-    const double2 o = __ldg(d.obs + t.i);
-    const int c = __ldg(d.cam + t.i);
-    const CamRow C = load_row(rows, c);
-    const double X0 = __ldg(pts + 3 * (size_t)t.p), X1 = __ldg(pts + 3 * (size_t)t.p + 1), X2 = __ldg(pts + 3 * (size_t)t.p + 2);
+  if (valid) {
+    const CamRow& C = staged_row(sR, slot);
+    const double X0 = sX[3 * pl], X1 = sX[3 * pl + 1], X2 = sX[3 * pl + 2];
     double sp[3] = {1.0, 1.0, 1.0};
-    if (scale_p) {
-      sp[0] = __ldg(scale_p + 3 * (size_t)t.p); sp[1] = __ldg(scale_p + 3 * (size_t)t.p + 1); sp[2] = __ldg(scale_p + 3 * (size_t)t.p + 2);
-    }
-    reproject_rj(C, X0, X1, X2, o.x, o.y, sp, r0, r1, jc, jp);
-    if (WRITE_J) {
-      const size_t n = (size_t)d.n_obs;
-      d.r[t.i] = make_double2(r0, r1);
-#pragma unroll
-      for (int k = 0; k < 6; ++k) d.Jc[k * n + t.i] = make_double2(jc[k], jc[6 + k]);
-#pragma unroll
-      for (int k = 0; k < 3; ++k) d.Jp[k * n + t.i] = make_double2(jp[k], jp[3 + k]);
+    if (scale_p) { sp[0] = sS[3 * pl]; sp[1] = sS[3 * pl + 1]; sp[2] = sS[3 * pl + 2]; }
+    const size_t n = (size_t)d.n_obs;
+    double jp[6];
+    reproject_lin(C, X0, X1, X2, o.x, o.y, sp, r0, r1, [&](int col, double du, double dv) {
+      if (col < 6) {
+        if (WRITE_J) d.Jc[col * n + i] = make_double2(du, dv);
+      } else {
+        if (WRITE_J) d.Jp[(col - 6) * n + i] = make_double2(du, dv);
+        jp[col - 6] = du; jp[col - 3] = dv;
+      }
+    });
+    if (WRITE_J) d.r[i] = make_double2(r0, r1);
+    if (FORM) {
+      double* v = sv + threadIdx.x;
+      v[0 * SV_LD] = jp[0] * jp[0] + jp[3] * jp[3];
+      v[1 * SV_LD] = jp[0] * jp[1] + jp[3] * jp[4];
+      v[2 * SV_LD] = jp[0] * jp[2] + jp[3] * jp[5];
+      v[3 * SV_LD] = jp[1] * jp[1] + jp[4] * jp[4];
+      v[4 * SV_LD] = jp[1] * jp[2] + jp[4] * jp[5];
+      v[5 * SV_LD] = jp[2] * jp[2] + jp[5] * jp[5];
+      v[6 * SV_LD] = jp[0] * r0 + jp[3] * r1;
+      v[7 * SV_LD] = jp[1] * r0 + jp[4] * r1;
+      v[8 * SV_LD] = jp[2] * r0 + jp[5] * r1;
     }
   }
-  const double cs = block_sum_256(r0 * r0 + r1 * r1, sm);
+  const double cs = block_sum_256(r0 * r0 + r1 * r1, sm);  // its barriers also publish sv
   if (threadIdx.x == 0) cost_part[blockIdx.x] = cs;
   if (FORM) {
-    double v[9];
-    v[0] = jp[0] * jp[0] + jp[3] * jp[3];
-    v[1] = jp[0] * jp[1] + jp[3] * jp[4];
-    v[2] = jp[0] * jp[2] + jp[3] * jp[5];
-    v[3] = jp[1] * jp[1] + jp[4] * jp[4];
-    v[4] = jp[1] * jp[2] + jp[4] * jp[5];
-    v[5] = jp[2] * jp[2] + jp[5] * jp[5];
-    v[6] = jp[0] * r0 + jp[3] * r1;
-    v[7] = jp[1] * r0 + jp[4] * r1;
-    v[8] = jp[2] * r0 + jp[5] * r1;
-    tile_segment_total<9>(v, t, sm);
-    if (t.valid && t.i == t.seg_b) {
-#pragma unroll
-      for (int k = 0; k < 6; ++k) Hpp[6 * (size_t)t.p + k] = v[k];
-#pragma unroll
-      for (int k = 0; k < 3; ++k) gp[3 * (size_t)t.p + k] = v[6 + k];
-    }
+    tile_point_sums<9>(d, t, bnd, sv, [&](int p, int k, double tot) {
+      if (k < 6) Hpp[6 * (size_t)p + k] = tot;
+      else gp[3 * (size_t)p + (k - 6)] = tot;
+    });
   }
+}
+__host__ constexpr size_t rj_smem_bytes(int row_cap, bool form) {
+  return sizeof(double) * (size_t)(rows_doubles(row_cap) + 6 * TILE + (form ? 9 * SV_LD : 0));
 }
 
 // Candidate cost: residual only (a9), 24 B/observation.
 __global__ void __launch_bounds__(TILE) cost_kernel(Dev d, const CamRow* __restrict__ rows, const double* __restrict__ pts,
-                                                     double* __restrict__ cost_part) {
+                                                     double* __restrict__ cost_part, int row_cap) {
+  extern __shared__ __align__(16) double dyn[];
+  double2* sR = reinterpret_cast<double2*>(dyn);
+  double* sX = dyn + rows_doubles(row_cap);
   __shared__ double sm[8];
-  const int tile_b = __ldg(d.tile_start + blockIdx.x), tile_e = __ldg(d.tile_start + blockIdx.x + 1);
-  const int i = tile_b + (int)threadIdx.x;
+  const TileHdr t = tile_hdr(d);
+  const int i = t.b + (int)threadIdx.x;
+  const bool valid = i < t.e;
+  double2 o = make_double2(0.0, 0.0);
+  int pl = 0, slot = 0;
+  if (valid) {
+    o = __ldg(d.obs + i);
+    slot = __ldg(d.slot + i);
+    pl = __ldg(d.pt + i) - t.p_first;
+  }
+  stage_points(t, pts, sX);
+  stage_rows(d, t, rows, sR);
+  __syncthreads();
   double e = 0.0;
-  if (i < tile_e) {
-    const double2 o = __ldg(d.obs + i);
-    const int c = __ldg(d.cam + i);
-    const int p = __ldg(d.pt + i);
-    const CamRow C = load_row(rows, c);
+  if (valid) {
     double r0, r1;
-    reproject_r(C, __ldg(pts + 3 * (size_t)p), __ldg(pts + 3 * (size_t)p + 1), __ldg(pts + 3 * (size_t)p + 2), o.x, o.y, r0, r1);
+    reproject_r(staged_row(sR, slot), sX[3 * pl], sX[3 * pl + 1], sX[3 * pl + 2], o.x, o.y, r0, r1);
     e = r0 * r0 + r1 * r1;
   }
   const double cs = block_sum_256(e, sm);
   if (threadIdx.x == 0) cost_part[blockIdx.x] = cs;
 }
+__host__ constexpr size_t cost_smem_bytes(int row_cap) { return sizeof(double) * (size_t)(rows_doubles(row_cap) + 3 * TILE); }
 
 // Camera-major pass: one warp per chunk of <= 256 observations of one camera; recomputes the
 // (scaled) Jacobian from 20 B/observation + a point gather and reduces camera-keyed sums.
@@ -406,106 +462,104 @@ __global__ void precond_invert_kernel(int n_cams, const double* __restrict__ Hcc
 //   MODE 2 (BACKSUB): y_p = z_p - Hpp^-1 W^T y_c ; candidate point ; model cost change ; norms   (a8, a9)
 // Algorithmic bytes / observation: Jc 96 + Jp 48 + cam 4 + pt 4 (+ r 16 in MODE 2).
 template <int MODE>
-__global__ void __launch_bounds__(TILE) schur_pass_kernel(Dev d, const double* __restrict__ Hpp_inv, const double* __restrict__ zp,
+__global__ void __launch_bounds__(TILE, MODE == 0 ? 8 : 4) schur_pass_kernel(Dev d, const double* __restrict__ Hpp_inv, const double* __restrict__ zp,
                                                           const double* __restrict__ vec_in /* p or y_c */, double* __restrict__ vec_out,
                                                           const double* __restrict__ pts_x, const double* __restrict__ scale_p,
                                                           double* __restrict__ yp, double* __restrict__ pts_c,
                                                           double* __restrict__ part, int part_stride, const int* __restrict__ flags,
                                                           int cams_free, int pts_free) {
-  __shared__ double sm[2 * 8 * 3 + 8];
+  __shared__ double sv[MODE == 0 ? 1 : 3 * SV_LD];  // per-observation W^T(.) pieces
+  __shared__ double sw[MODE == 0 ? 1 : 3 * TILE];   // per-point result handed back to the observations
+  __shared__ double2 sP[MODE == 0 ? 1 : 3 * TILE];  // vec_in blocks of the tile's cameras, by slot
+  __shared__ double sm[8];
   if (MODE == 1) {
     if (flags[F_PCG_DONE]) return;
   }
-  const TileThread t = tile_thread(d);
+  const TileHdr t = tile_hdr(d);
+  const int i = t.b + (int)threadIdx.x;
+  const bool valid = i < t.e;
   const size_t n = (size_t)d.n_obs;
+  const bool use_vec = MODE == 1 || (MODE == 2 && cams_free);
+  if (MODE != 0 && use_vec) {
+    const int* list = d.tile_cams + (size_t)blockIdx.x * TILE;
+    for (int q = threadIdx.x; q < 3 * t.ncam; q += TILE) {
+      const int sl = q / 3, piece = q - sl * 3;
+      sP[q] = __ldg(reinterpret_cast<const double2*>(vec_in + 6 * (size_t)__ldg(list + sl)) + piece);
+    }
+  }
   double jc[12], jp[6];
-  int c = 0;
-  if (t.valid) {
-    c = __ldg(d.cam + t.i);
+  int slot = 0, pl = 0;
+  if (valid) {
+    if (MODE != 0) slot = __ldg(d.slot + i);
+    pl = __ldg(d.pt + i) - t.p_first;
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
-      const double2 v = d.Jc[k * n + t.i];
+      const double2 v = d.Jc[k * n + i];
       jc[k] = v.x; jc[6 + k] = v.y;
     }
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-      const double2 v = d.Jp[k * n + t.i];
+      const double2 v = d.Jp[k * n + i];
       jp[k] = v.x; jp[3 + k] = v.y;
     }
-  } else {
-#pragma unroll
-    for (int k = 0; k < 12; ++k) jc[k] = 0.0;
-#pragma unroll
-    for (int k = 0; k < 6; ++k) jp[k] = 0.0;
   }
   if (MODE == 0) {
     // t_i = Jc_i^T (Jp_i z_p), stored per observation (48 B, point-major); the camera-major gather
     // pass (cam_gather6_kernel) sums them per camera — no atomics, fixed summation order.
-    if (t.valid) {
-      const double z0 = __ldg(zp + 3 * (size_t)t.p), z1 = __ldg(zp + 3 * (size_t)t.p + 1), z2 = __ldg(zp + 3 * (size_t)t.p + 2);
+    if (valid) {
+      const size_t p = (size_t)(t.p_first + pl);
+      const double z0 = __ldg(zp + 3 * p), z1 = __ldg(zp + 3 * p + 1), z2 = __ldg(zp + 3 * p + 2);
       const double y0 = jp[0] * z0 + jp[1] * z1 + jp[2] * z2;
       const double y1 = jp[3] * z0 + jp[4] * z1 + jp[5] * z2;
-      double2* dst = reinterpret_cast<double2*>(vec_out + 6 * (size_t)t.i);
+      double2* dst = reinterpret_cast<double2*>(vec_out + 6 * (size_t)i);
 #pragma unroll
       for (int k = 0; k < 3; ++k)
         dst[k] = make_double2(jc[2 * k] * y0 + jc[6 + 2 * k] * y1, jc[2 * k + 1] * y0 + jc[7 + 2 * k] * y1);
     }
     return;
   }
-  // u = Jc * vec_in[c]
+  // the per-point thread's inputs depend on the tile header only: fetch them before the barrier
+  const bool own_pt = (int)threadIdx.x < t.n_p;
+  const int pp = t.p_first + (int)threadIdx.x;
+  int sb = 0, se = 0;
+  double Hi[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  double z0 = 0.0, z1 = 0.0, z2 = 0.0;
+  if (own_pt) {
+    sb = __ldg(d.pt_start + pp) - t.b; se = __ldg(d.pt_start + pp + 1) - t.b;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) Hi[k] = __ldg(Hpp_inv + 6 * (size_t)pp + k);
+    if (MODE == 2 && pts_free) { z0 = __ldg(zp + 3 * (size_t)pp); z1 = __ldg(zp + 3 * (size_t)pp + 1); z2 = __ldg(zp + 3 * (size_t)pp + 2); }
+  }
+  __syncthreads();
+  // u = Jc * vec_in[c];  this observation's piece of W^T vec_in goes to shared memory
   double u0 = 0.0, u1 = 0.0;
-  if (t.valid && (MODE == 1 || cams_free)) {
+  if (valid) {
+    if (use_vec) {
 #pragma unroll
-    for (int k = 0; k < 6; ++k) {
-      const double pk = __ldg(vec_in + 6 * (size_t)c + k);
-      u0 += jc[k] * pk;
-      u1 += jc[6 + k] * pk;
+      for (int k = 0; k < 3; ++k) {
+        const double2 pk = sP[3 * slot + k];
+        u0 += jc[2 * k] * pk.x + jc[2 * k + 1] * pk.y;
+        u1 += jc[6 + 2 * k] * pk.x + jc[7 + 2 * k] * pk.y;
+      }
     }
+    sv[threadIdx.x] = jp[0] * u0 + jp[3] * u1;
+    sv[SV_LD + threadIdx.x] = jp[1] * u0 + jp[4] * u1;
+    sv[2 * SV_LD + threadIdx.x] = jp[2] * u0 + jp[5] * u1;
   }
-  double v[3];
-  v[0] = jp[0] * u0 + jp[3] * u1;
-  v[1] = jp[1] * u0 + jp[4] * u1;
-  v[2] = jp[2] * u0 + jp[5] * u1;
-  tile_segment_total<3>(v, t, sm);
-  double Hi[6];
-  if (t.valid) {
-#pragma unroll
-    for (int k = 0; k < 6; ++k) Hi[k] = __ldg(Hpp_inv + 6 * (size_t)t.p + k);
-  } else {
-#pragma unroll
-    for (int k = 0; k < 6; ++k) Hi[k] = 0.0;
-  }
-  double w0, w1, w2;
-  sym3_mul(Hi, v[0], v[1], v[2], w0, w1, w2);  // Hpp^-1 W^T (.)
-  if (MODE == 1) {
-    // t_i = Jc_i^T (I - Jp Hpp^-1 Jp^T)(Jc p) per observation; summed per camera by the gather pass
-    if (t.valid) {
-      const double y0 = u0 - (jp[0] * w0 + jp[1] * w1 + jp[2] * w2);
-      const double y1 = u1 - (jp[3] * w0 + jp[4] * w1 + jp[5] * w2);
-      double2* dst = reinterpret_cast<double2*>(vec_out + 6 * (size_t)t.i);
-#pragma unroll
-      for (int k = 0; k < 3; ++k)
-        dst[k] = make_double2(jc[2 * k] * y0 + jc[6 + 2 * k] * y1, jc[2 * k + 1] * y0 + jc[7 + 2 * k] * y1);
-    }
-    return;
-  }
-  // MODE 2
-  double mcc = 0.0, dn = 0.0, xn = 0.0;
-  if (t.valid) {
-    double y0 = 0.0, y1 = 0.0, y2 = 0.0;  // y_p
-    if (pts_free) {
-      y0 = __ldg(zp + 3 * (size_t)t.p) - w0;
-      y1 = __ldg(zp + 3 * (size_t)t.p + 1) - w1;
-      y2 = __ldg(zp + 3 * (size_t)t.p + 2) - w2;
-    }
-    // step = -y ; m = J step
-    const double m0 = -(u0 + jp[0] * y0 + jp[1] * y1 + jp[2] * y2);
-    const double m1 = -(u1 + jp[3] * y0 + jp[4] * y1 + jp[5] * y2);
-    const double2 r = d.r[t.i];
-    mcc = -(m0 * (r.x + m0 / 2.0) + m1 * (r.y + m1 / 2.0));
-    if (t.i == t.seg_b) {
-      const size_t q = 3 * (size_t)t.p;
-      if (pts_free) {
+  __syncthreads();
+  // one thread per point of the tile: total over the point's observations (in observation order), then the
+  // 3x3 point-block work — Hpp^-1 W^T(.) for the mat-vec; y_p, the candidate point and the norms for MODE 2
+  double dn = 0.0, xn = 0.0;
+  if (own_pt) {
+    double v0 = 0.0, v1 = 0.0, v2 = 0.0;
+    for (int l = sb; l < se; ++l) { v0 += sv[l]; v1 += sv[SV_LD + l]; v2 += sv[2 * SV_LD + l]; }
+    double w0, w1, w2;
+    sym3_mul(Hi, v0, v1, v2, w0, w1, w2);  // Hpp^-1 W^T (.)
+    if (MODE == 2) {
+      const size_t q = 3 * (size_t)pp;
+      double y0 = 0.0, y1 = 0.0, y2 = 0.0;  // y_p
+      if (pts_free && se > sb) {
+        y0 = z0 - w0; y1 = z1 - w1; y2 = z2 - w2;
         yp[q] = y0; yp[q + 1] = y1; yp[q + 2] = y2;
         const double x0 = pts_x[q], x1 = pts_x[q + 1], x2 = pts_x[q + 2];
         const double c0 = x0 + (-y0) * scale_p[q], c1 = x1 + (-y1) * scale_p[q + 1], c2 = x2 + (-y2) * scale_p[q + 2];
@@ -514,12 +568,36 @@ __global__ void __launch_bounds__(TILE) schur_pass_kernel(Dev d, const double* _
         dn = e0 * e0 + e1 * e1 + e2 * e2;
         xn = x0 * x0 + x1 * x1 + x2 * x2;
       }
+      w0 = y0; w1 = y1; w2 = y2;
     }
+    sw[3 * threadIdx.x] = w0; sw[3 * threadIdx.x + 1] = w1; sw[3 * threadIdx.x + 2] = w2;
   }
-  double* smr = sm + 48;
-  const double s0 = block_sum_256(mcc, smr);
-  const double s1 = block_sum_256(dn, smr);
-  const double s2 = block_sum_256(xn, smr);
+  __syncthreads();
+  double w0 = 0.0, w1 = 0.0, w2 = 0.0;
+  if (valid) { w0 = sw[3 * pl]; w1 = sw[3 * pl + 1]; w2 = sw[3 * pl + 2]; }
+  if (MODE == 1) {
+    // t_i = Jc_i^T (I - Jp Hpp^-1 Jp^T)(Jc p) per observation; summed per camera by the gather pass
+    if (valid) {
+      const double y0 = u0 - (jp[0] * w0 + jp[1] * w1 + jp[2] * w2);
+      const double y1 = u1 - (jp[3] * w0 + jp[4] * w1 + jp[5] * w2);
+      double2* dst = reinterpret_cast<double2*>(vec_out + 6 * (size_t)i);
+#pragma unroll
+      for (int k = 0; k < 3; ++k)
+        dst[k] = make_double2(jc[2 * k] * y0 + jc[6 + 2 * k] * y1, jc[2 * k + 1] * y0 + jc[7 + 2 * k] * y1);
+    }
+    return;
+  }
+  // MODE 2: model cost change of step = -y;  m = J step
+  double mcc = 0.0;
+  if (valid) {
+    const double m0 = -(u0 + jp[0] * w0 + jp[1] * w1 + jp[2] * w2);
+    const double m1 = -(u1 + jp[3] * w0 + jp[4] * w1 + jp[5] * w2);
+    const double2 r = d.r[i];
+    mcc = -(m0 * (r.x + m0 / 2.0) + m1 * (r.y + m1 / 2.0));
+  }
+  const double s0 = block_sum_256(mcc, sm);
+  const double s1 = block_sum_256(dn, sm);
+  const double s2 = block_sum_256(xn, sm);
   if (threadIdx.x == 0) {
     part[P_MCC * (size_t)part_stride + blockIdx.x] = s0;
     part[P_DN_P * (size_t)part_stride + blockIdx.x] = s1;
@@ -892,20 +970,36 @@ void launch_cam_prep(Problem& P, const double* cam, const double* scale_c, CamRo
   P.launches++;
 }
 
+// Largest dynamic shared memory any staging kernel can ask for (256 distinct cameras in a tile).
+constexpr int kStageSmemMax = (int)sizeof(double) * (rows_doubles(TILE) + 6 * TILE + 9 * SV_LD);
+template <class Kern>
+static void allow_stage_smem(Kern k) { cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kStageSmemMax); }
+
 void launch_rj(Problem& P, const CamRow* rows, const double* pts, const double* scale_p, bool write_j, bool form, cudaStream_t s) {
   if (P.n_tiles == 0) return;
+  static bool attr_set = false;
+  if (!attr_set) {
+    allow_stage_smem(rj_kernel<true, true>); allow_stage_smem(rj_kernel<true, false>);
+    allow_stage_smem(rj_kernel<false, true>); allow_stage_smem(rj_kernel<false, false>);
+    attr_set = true;
+  }
   double* cp = P.part + (size_t)P_COST * P.part_stride;
-  if (write_j && form) rj_kernel<true, true><<<P.n_tiles, TILE, 0, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp);
-  else if (write_j) rj_kernel<true, false><<<P.n_tiles, TILE, 0, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp);
-  else if (form) rj_kernel<false, true><<<P.n_tiles, TILE, 0, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp);
-  else rj_kernel<false, false><<<P.n_tiles, TILE, 0, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp);
+  const int cap = P.max_tile_cams;
+  const size_t sh = rj_smem_bytes(cap, form);
+  if (write_j && form) rj_kernel<true, true><<<P.n_tiles, TILE, sh, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp, cap);
+  else if (write_j) rj_kernel<true, false><<<P.n_tiles, TILE, sh, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp, cap);
+  else if (form) rj_kernel<false, true><<<P.n_tiles, TILE, sh, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp, cap);
+  else rj_kernel<false, false><<<P.n_tiles, TILE, sh, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp, cap);
   P.launches++;
   add_task(P, P_COST, P.n_tiles, S_COST, 2);
 }
 
 void launch_cost(Problem& P, const CamRow* rows, const double* pts, int part_slot, cudaStream_t s) {
   if (P.n_tiles == 0) return;
-  cost_kernel<<<P.n_tiles, TILE, 0, s>>>(P.d, rows, pts, P.part + (size_t)part_slot * P.part_stride);
+  static bool attr_set = false;
+  if (!attr_set) { allow_stage_smem(cost_kernel); attr_set = true; }
+  cost_kernel<<<P.n_tiles, TILE, cost_smem_bytes(P.max_tile_cams), s>>>(P.d, rows, pts, P.part + (size_t)part_slot * P.part_stride,
+                                                                         P.max_tile_cams);
   P.launches++;
   add_task(P, part_slot, P.n_tiles, S_CAND_COST, 2);
 }

@@ -81,60 +81,36 @@ BA_HD void reproject_r(const CamRow& C, double X0, double X1, double X2, double 
   r1 = (C.fy * yp + C.cy) - oy;
 }
 
-// Residual + Jacobian.  jc[12] = {du/dc_0..5, dv/dc_0..5} (c = w0,w1,w2,t0,t1,t2), jp[6] =
-// {du/dX_0..2, dv/dX_0..2}; camera columns are multiplied by C.sc, point columns by sp[3].
-BA_HD void reproject_rj(const CamRow& C, double X0, double X1, double X2, double ox, double oy, const double* sp,
-                        double& r0, double& r1, double* jc, double* jp) {
-  // dP[k][j] = d p_j / d param_k for the 9 parameters (w0,w1,w2,t0,t1,t2,X0,X1,X2); t columns are e_k.
-  double p0, p1, p2;
-  double dw[3][3];  // d p / d w_k
-  double R[3][3];   // d p / d X  (rotation matrix, R[j][m] = d p_j / d X_m)
+// Residual + Jacobian, column by column.  emit(col, du, dv) receives the nine Jacobian columns
+// (col 0..5 = w0,w1,w2,t0,t1,t2 scaled by C.sc; col 6..8 = X0,X1,X2 scaled by sp).
+//
+// The chain rule is grouped so that one observation costs ~230 FP64 instructions with short
+// dependency chains:
+//   * everything after the rigid transform is linear in dp = (a,b,cz): (du,dv) = M dp with one 2x3
+//     matrix M per observation (perspective divide, radial factor, intrinsics), so a column is six
+//     multiply-adds;
+//   * d p / d w_k = alpha_k X + beta_k (u x X) + gamma_k u + (s/theta) e_k x X + (tmp/theta) e_k — the
+//     products of the statement-by-statement derivative of ceres::AngleAxisRotatePoint regrouped by
+//     the vector they multiply.  The same intermediates (1-cos, u.X, ...) enter with the same values,
+//     so the ill-conditioned small-angle terms round the way the autodiff jets do.
+template <class Emit>
+BA_HD void reproject_lin(const CamRow& C, double X0, double X1, double X2, double ox, double oy, const double* sp, double& r0,
+                         double& r1, Emit&& emit) {
   const double u0 = C.u0, u1 = C.u1, u2 = C.u2;
-  if (C.ti != 0.0) {
-    const double c = C.c, s = C.s, ti = C.ti;
-    const double omc = 1.0 - c;
-    const double x0 = u1 * X2 - u2 * X1, x1 = u2 * X0 - u0 * X2, x2 = u0 * X1 - u1 * X0;
-    const double d = u0 * X0 + u1 * X1 + u2 * X2;
-    const double tmp = d * omc;
+  const bool full = C.ti != 0.0;
+  const double c = C.c, s = C.s, ti = C.ti;
+  const double omc = 1.0 - c;
+  // x = u x X (w x X on the Taylor branch), d = u.X
+  const double x0 = u1 * X2 - u2 * X1, x1 = u2 * X0 - u0 * X2, x2 = u0 * X1 - u1 * X0;
+  const double d = u0 * X0 + u1 * X1 + u2 * X2;
+  const double tmp = d * omc;
+  double p0, p1, p2;
+  if (full) {
     p0 = X0 * c + x0 * s + u0 * tmp;
     p1 = X1 * c + x1 * s + u1 * tmp;
     p2 = X2 * c + x2 * s + u2 * tmp;
-    const double uu[3] = {u0, u1, u2};
-    const double X[3] = {X0, X1, X2};
-    const double x[3] = {x0, x1, x2};
-    // e_k x X
-    const double eX[3][3] = {{0.0, -X2, X1}, {X2, 0.0, -X0}, {-X1, X0, 0.0}};
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-      const double uk = uu[k];
-      // du_j/dw_k = ti (delta_jk - u_j u_k);  d(u x X)/dw_k = ti (e_k x X - u_k x);  d(u.X)/dw_k = ti (X_k - u_k d)
-      const double dc = -s * uk, ds = c * uk;
-      const double dd = ti * (X[k] - uk * d);
-      const double dtmp = dd * omc + d * (s * uk);
-#pragma unroll
-      for (int j = 0; j < 3; ++j) {
-        const double du_j = ti * ((j == k ? 1.0 : 0.0) - uu[j] * uk);
-        const double dx_j = ti * (eX[k][j] - uk * x[j]);
-        dw[k][j] = X[j] * dc + dx_j * s + x[j] * ds + du_j * tmp + uu[j] * dtmp;
-      }
-    }
-    // R = c I + s [u]x + (1-c) u u^T
-    R[0][0] = c + omc * u0 * u0;      R[0][1] = -s * u2 + omc * u0 * u1; R[0][2] = s * u1 + omc * u0 * u2;
-    R[1][0] = s * u2 + omc * u1 * u0; R[1][1] = c + omc * u1 * u1;       R[1][2] = -s * u0 + omc * u1 * u2;
-    R[2][0] = -s * u1 + omc * u2 * u0; R[2][1] = s * u0 + omc * u2 * u1; R[2][2] = c + omc * u2 * u2;
   } else {
-    // p = X + w x X   (w stored in u)
-    p0 = X0 + (u1 * X2 - u2 * X1);
-    p1 = X1 + (u2 * X0 - u0 * X2);
-    p2 = X2 + (u0 * X1 - u1 * X0);
-    // d/dw_k = e_k x X
-    dw[0][0] = 0.0; dw[0][1] = -X2; dw[0][2] = X1;
-    dw[1][0] = X2;  dw[1][1] = 0.0; dw[1][2] = -X0;
-    dw[2][0] = -X1; dw[2][1] = X0;  dw[2][2] = 0.0;
-    // d/dX = I + [w]x
-    R[0][0] = 1.0; R[0][1] = -u2; R[0][2] = u1;
-    R[1][0] = u2;  R[1][1] = 1.0; R[1][2] = -u0;
-    R[2][0] = -u1; R[2][1] = u0;  R[2][2] = 1.0;
+    p0 = X0 + x0; p1 = X1 + x1; p2 = X2 + x2;
   }
   p0 += C.t0; p1 += C.t1; p2 += C.t2;
   const double iz = 1.0 / p2;
@@ -144,25 +120,74 @@ BA_HD void reproject_rj(const CamRow& C, double X0, double X1, double X2, double
   const double xd = xp * f, yd = yp * f;
   r0 = (C.fx * xd + C.sk * yd + C.cx) - ox;
   r1 = (C.fy * yd + C.cy) - oy;
-  const double dfdr2 = C.k1 + 2.0 * C.k2 * r2;
-  // one column: given dP = (a,b,cz) produce (du, dv)
-  auto column = [&](double a, double b, double cz, double scale, double& du, double& dv) {
-    const double dxp = (a - xp * cz) * iz;
-    const double dyp = (b - yp * cz) * iz;
-    const double dr2 = 2.0 * (xp * dxp + yp * dyp);
-    const double df = dfdr2 * dr2;
-    const double dxd = dxp * f + xp * df;
-    const double dyd = dyp * f + yp * df;
-    du = (C.fx * dxd + C.sk * dyd) * scale;
-    dv = (C.fy * dyd) * scale;
-  };
+  // M: d(xd,yd)/d(a,b,cz), then the intrinsics
+  const double g = 2.0 * (C.k1 + 2.0 * C.k2 * r2) * iz;  // d f / d(a,b,cz) = g * (xp, yp, -r2)
+  const double h = iz * f;
+  const double xg = xp * g, yg = yp * g;
+  const double q = -(g * r2 + h);
+  const double A = h + xp * xg, B = xp * yg, Cc = xp * q;
+  const double E = h + yp * yg, F = yp * q;
+  const double m00 = C.fx * A + C.sk * B, m01 = C.fx * B + C.sk * E, m02 = C.fx * Cc + C.sk * F;
+  const double m10 = C.fy * B, m11 = C.fy * E, m12 = C.fy * F;
+  // translation columns: dp = e_k
+  emit(3, m00 * C.sc[3], m10 * C.sc[3]);
+  emit(4, m01 * C.sc[4], m11 * C.sc[4]);
+  emit(5, m02 * C.sc[5], m12 * C.sc[5]);
+  if (full) {
+    // point columns: dp = R e_m,  R = c I + s [u]x + (1-c) u u^T
+    const double o0 = omc * u0, o1 = omc * u1, o2 = omc * u2;
+    const double su0 = s * u0, su1 = s * u1, su2 = s * u2;
+    {
+      const double a = c + o0 * u0, b = su2 + o1 * u0, cz = o2 * u0 - su1;
+      emit(6, (m00 * a + m01 * b + m02 * cz) * sp[0], (m10 * a + m11 * b + m12 * cz) * sp[0]);
+    }
+    {
+      const double a = o0 * u1 - su2, b = c + o1 * u1, cz = su0 + o2 * u1;
+      emit(7, (m00 * a + m01 * b + m02 * cz) * sp[1], (m10 * a + m11 * b + m12 * cz) * sp[1]);
+    }
+    {
+      const double a = su1 + o0 * u2, b = o1 * u2 - su0, cz = c + o2 * u2;
+      emit(8, (m00 * a + m01 * b + m02 * cz) * sp[2], (m10 * a + m11 * b + m12 * cz) * sp[2]);
+    }
+    // rotation columns
+    const double sti = s * ti, cms = c - sti, tt = ti * tmp;
+    const double X[3] = {X0, X1, X2};
+    const double uu[3] = {u0, u1, u2};
 #pragma unroll
-  for (int k = 0; k < 3; ++k) column(dw[k][0], dw[k][1], dw[k][2], C.sc[k], jc[k], jc[6 + k]);
-  column(1.0, 0.0, 0.0, C.sc[3], jc[3], jc[9]);
-  column(0.0, 1.0, 0.0, C.sc[4], jc[4], jc[10]);
-  column(0.0, 0.0, 1.0, C.sc[5], jc[5], jc[11]);
-#pragma unroll
-  for (int m = 0; m < 3; ++m) column(R[0][m], R[1][m], R[2][m], sp[m], jp[m], jp[3 + m]);
+    for (int k = 0; k < 3; ++k) {
+      const double uk = uu[k];
+      const double alpha = -s * uk, beta = uk * cms;
+      const double dd = ti * (X[k] - uk * d);
+      const double dtmp = dd * omc + d * (s * uk);
+      const double gamma = dtmp - tt * uk;
+      double a = alpha * X0 + beta * x0 + gamma * u0;
+      double b = alpha * X1 + beta * x1 + gamma * u1;
+      double cz = alpha * X2 + beta * x2 + gamma * u2;
+      // + sti * (e_k x X) + tt * e_k
+      if (k == 0) { a += tt;  b -= sti * X2; cz += sti * X1; }
+      if (k == 1) { a += sti * X2; b += tt;  cz -= sti * X0; }
+      if (k == 2) { a -= sti * X1; b += sti * X0; cz += tt; }
+      emit(k, (m00 * a + m01 * b + m02 * cz) * C.sc[k], (m10 * a + m11 * b + m12 * cz) * C.sc[k]);
+    }
+  } else {
+    // p = X + w x X:  d/dX = I + [w]x,  d/dw_k = e_k x X
+    emit(6, (m00 + m01 * u2 - m02 * u1) * sp[0], (m10 + m11 * u2 - m12 * u1) * sp[0]);
+    emit(7, (m01 - m00 * u2 + m02 * u0) * sp[1], (m11 - m10 * u2 + m12 * u0) * sp[1]);
+    emit(8, (m02 + m00 * u1 - m01 * u0) * sp[2], (m12 + m10 * u1 - m11 * u0) * sp[2]);
+    emit(0, (m02 * X1 - m01 * X2) * C.sc[0], (m12 * X1 - m11 * X2) * C.sc[0]);
+    emit(1, (m00 * X2 - m02 * X0) * C.sc[1], (m10 * X2 - m12 * X0) * C.sc[1]);
+    emit(2, (m01 * X0 - m00 * X1) * C.sc[2], (m11 * X0 - m10 * X1) * C.sc[2]);
+  }
+}
+
+// Residual + Jacobian into arrays.  jc[12] = {du/dc_0..5, dv/dc_0..5} (c = w0,w1,w2,t0,t1,t2), jp[6] =
+// {du/dX_0..2, dv/dX_0..2}; camera columns are multiplied by C.sc, point columns by sp[3].
+BA_HD void reproject_rj(const CamRow& C, double X0, double X1, double X2, double ox, double oy, const double* sp,
+                        double& r0, double& r1, double* jc, double* jp) {
+  reproject_lin(C, X0, X1, X2, ox, oy, sp, r0, r1, [&](int col, double du, double dv) {
+    if (col < 6) { jc[col] = du; jc[6 + col] = dv; }
+    else { jp[col - 6] = du; jp[col - 3] = dv; }
+  });
 }
 
 // Symmetric 3x3 stored as 6 (00,01,02,11,12,22).  SPD inverse through Cholesky (as Ceres'
