@@ -109,6 +109,7 @@ void hsfm_ba_destroy(hsfm_ba_ctx* h) {
   h->c.prob.destroy();
   h->c.comm.destroy();
   h->c.chol_aux.destroy();
+  h->c.chol_plan.destroy();
   for (cudaEvent_t e : h->c.phase_events) cudaEventDestroy(e);
   if (h->c.own_stream) cudaStreamDestroy(h->c.own_stream);
   delete h;
@@ -144,6 +145,7 @@ int hsfm_ba_problem_upload(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double
   if (n_pts > 0 && !pts) return HSFM_BA_ERR_ARG;
   HSFM_CUDA(cudaSetDevice(h->c.device));
   h->c.has_problem = false;
+  h->c.chol_plan_valid = false;
   double setup = 0, h2d = 0;
   int rc = build_problem(h->c.prob, mode, n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, dist, cam_rt, n_pts, pts, h->c.comm, h->c.stream, &setup, &h2d);
   if (rc) { h->c.prob.release(); return rc; }

@@ -339,7 +339,25 @@ __device__ __forceinline__ void load_tile_async(double (*dst)[LDS_], const doubl
 }
 
 struct SyrkTile { int ri, ni, rj, nj; };
-__device__ __forceinline__ SyrkTile syrk_tile(int t, int n, int base, int row_first, int col_first) {
+// rb_list != nullptr: envelope mode — the tiles are pairs of ACTIVE 128-row blocks (global block indices,
+// ascending).  col_first == 0: the pairs (a, 0), i.e. the column of block rb_list[0] (the next panel);
+// col_first < 0: every pair (a, b), b <= a.  Two 64-wide tiles per pair.
+__device__ __forceinline__ SyrkTile syrk_tile(int t, int n, int base, int row_first, int col_first, const int* __restrict__ rb_list) {
+  SyrkTile T;
+  if (rb_list) {
+    const int pi = t >> 1, half = t & 1;
+    int a, b;
+    if (col_first == 0) { a = pi; b = 0; }
+    else {
+      a = (int)((sqrtf(8.0f * (float)pi + 1.0f) - 1.0f) * 0.5f);
+      while ((a + 1) * (a + 2) / 2 <= pi) ++a;
+      while (a * (a + 1) / 2 > pi) --a;
+      b = pi - a * (a + 1) / 2;
+    }
+    T.ri = __ldg(rb_list + a) * NB; T.ni = min(NB, n - T.ri);
+    T.rj = __ldg(rb_list + b) * NB + half * TN; T.nj = min(TN, n - T.rj);
+    return T;
+  }
   int bi, bj;
   if (col_first >= 0) {
     bi = row_first + (t >> 1); bj = col_first + (t & 1);
@@ -352,14 +370,13 @@ __device__ __forceinline__ SyrkTile syrk_tile(int t, int n, int base, int row_fi
     bi = q + h;
     bj = c0 + (t - q * (q - 1));
   }
-  SyrkTile T;
   T.ri = base + bi * NB; T.ni = min(NB, n - T.ri);
   T.rj = base + bj * TN; T.nj = min(TN, n - T.rj);
   return T;
 }
 
 __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ S, int n, int k0, int row_first, int col_first, int n_tiles,
-                                                           int stagger, const int* __restrict__ fail) {
+                                                           int stagger, const int* __restrict__ fail, const int* __restrict__ rb_list) {
   extern __shared__ __align__(16) unsigned char gsm_raw[];
   GemmSmem& sm = *reinterpret_cast<GemmSmem*>(gsm_raw);
   int t = blockIdx.x;
@@ -378,7 +395,7 @@ __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ 
     const long long t0 = clock64();
     while (clock64() - t0 < 16000) { }
   }
-  SyrkTile cur = syrk_tile(t, n, base, row_first, col_first);
+  SyrkTile cur = syrk_tile(t, n, base, row_first, col_first, rb_list);
   load_tile_async<NB>(sm.a[0], S, n, cur.ri, cur.ni, k0);
   load_tile_async<TN>(sm.b[0], S, n, cur.rj, cur.nj, k0);
   cp_async_commit();
@@ -389,7 +406,7 @@ __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ 
     const int t_next = t + gridDim.x;
     const bool has_next = t_next < n_tiles;
     SyrkTile nxt = cur;
-    if (has_next) nxt = syrk_tile(t_next, n, base, row_first, col_first);
+    if (has_next) nxt = syrk_tile(t_next, n, base, row_first, col_first, rb_list);
     // C → accumulators.  Full tiles take an unpredicated path: one row pointer per 8-row group, the four
     // column tiles at immediate offsets, every load straight into its accumulator pair — nothing recycles a
     // register, so all 32 loads are in flight at once.
@@ -505,12 +522,20 @@ __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ 
 constexpr int TS_LD = NB + 4;
 constexpr int TS_MAXROWS = 88;
 __global__ void __launch_bounds__(256) chol_trsm_strip_kernel(double* __restrict__ S, int n, int k0, const double* __restrict__ Linv,
-                                                               int rows_per, const int* __restrict__ fail) {
+                                                               int rows_per, const int* __restrict__ fail, const int* __restrict__ rb_list,
+                                                               int strips_per_block) {
   extern __shared__ __align__(16) double tsm[];
   double (*sA)[TS_LD] = reinterpret_cast<double (*)[TS_LD]>(tsm);
   const int failed = *fail;
-  const int r0 = k0 + NB + blockIdx.x * rows_per;
-  const int nr = min(rows_per, n - r0);
+  int r0, nr;
+  if (rb_list) {  // envelope mode: strips of the active 128-row blocks only
+    const int blk = __ldg(rb_list + blockIdx.x / strips_per_block);
+    r0 = blk * NB + (blockIdx.x % strips_per_block) * rows_per;
+    nr = min(rows_per, min(n, (blk + 1) * NB) - r0);
+  } else {
+    r0 = k0 + NB + blockIdx.x * rows_per;
+    nr = min(rows_per, n - r0);
+  }
   const int tid = threadIdx.x;
   for (int e = tid; e < rows_per * (NB / 2); e += 256) {
     const int row = e >> 6, c2 = (e & 63) * 2;
@@ -735,7 +760,7 @@ __device__ __forceinline__ double block_col_dot(const double* __restrict__ M, si
 }
 
 __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict__ L, int n, const double* __restrict__ LinvAll, double* b,
-                                                        double* w, int* flag_fwd, int* flag_bwd) {
+                                                        double* w, int* flag_fwd, int* flag_bwd, const int* __restrict__ fb) {
   __shared__ double sv[NB];    // vector of the block being folded in (y_k / x_i)
   __shared__ double sacc[NB];  // running right-hand side of the owned block
   __shared__ double sp[NB];
@@ -750,7 +775,7 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
       prefetch_l2(LinvAll + (size_t)i * NB * NB + row * NB + (e & 7) * 16);
       if (i > 0 && row < nr) prefetch_l2(L + (size_t)(r0 + row) * n + (i - 1) * NB + (e & 7) * 16);
     }
-    for (int k = 0; k < i; ++k) {
+    for (int k = fb ? __ldg(fb + i) : 0; k < i; ++k) {  // blocks left of the envelope are exactly zero
       if (k + 2 < i) {  // pull block (i, k+2) towards L2: 128 rows x 1 KB = 8 lines per row
         for (int e = tid; e < NB * 8; e += 256) {
           const int row = e >> 3;
@@ -784,6 +809,7 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
     __syncthreads();
     if (tid < NB) sacc[tid] = (tid < kb) ? __ldcg(w + c0 + tid) : 0.0;
     for (int i = P - 1; i > kk; --i) {
+      if (fb && __ldg(fb + i) > kk) continue;  // block (i, kk) lies outside the envelope
       const int r0 = i * NB, nr = min(NB, n - r0);
       if (i - 2 > kk) {
         for (int e = tid; e < NB * 8; e += 256) {
@@ -886,7 +912,105 @@ void CholAux::destroy() {
 // The chain's update of cb 0,1 at step k+1 waits for "ahead k" (those are the columns cb 2,3 of step k), so
 // the bulk update of step k has the whole of chain step k+1 to finish before anything waits on it: the
 // chain (latency-bound) and the bulk (DMMA-bound) overlap and the slower of the two sets the pace.
-void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches) {
+// ---------------------------------------------------------------------------------------------
+// Envelope plan
+// ---------------------------------------------------------------------------------------------
+int CholPlan::build(int n_cams, const int* cam_first, cudaStream_t s) {
+  n = 6 * n_cams;
+  panels = (n + NB - 1) / NB;
+  use = false; fill = 1.0;
+  fb.assign((size_t)panels, 0); off.assign((size_t)panels, 0); cnt.assign((size_t)panels, 0); list.clear();
+  if (!cam_first || panels < 4) return 0;
+  for (int I = 0; I < panels; ++I) {
+    int f = I;
+    const int c_lo = (I * NB) / 6, c_hi = std::min(n_cams - 1, (std::min(n, (I + 1) * NB) - 1) / 6);
+    for (int c = c_lo; c <= c_hi; ++c) f = std::min(f, (6 * std::min(cam_first[c], c)) / NB);
+    fb[I] = f;
+  }
+  size_t env_blocks = 0;
+  for (int I = 0; I < panels; ++I) env_blocks += (size_t)(I - fb[I] + 1);
+  fill = (double)env_blocks / ((double)panels * (panels + 1) / 2);
+  for (int K = 0; K < panels; ++K) {
+    off[K] = (int)list.size();
+    for (int I = K + 1; I < panels; ++I)
+      if (fb[I] <= K) list.push_back(I);
+    cnt[K] = (int)list.size() - off[K];
+  }
+  static const bool force_dense = getenv("HSFM_CHOL_DENSE") != nullptr;  // experiment knob
+  use = fill < 0.6 && !force_dense;
+  if (!use) return 0;
+  const size_t need = (size_t)panels + list.size() + 1;
+  if (need > d_cap) {
+    if (d_fb) cudaFree(d_fb);
+    d_fb = nullptr; d_cap = 0;
+    HSFM_CUDA(cudaMalloc(&d_fb, sizeof(int) * need));
+    d_cap = need;
+  }
+  d_list = d_fb + panels;
+  HSFM_CUDA(cudaMemcpyAsync(d_fb, fb.data(), sizeof(int) * (size_t)panels, cudaMemcpyHostToDevice, s));
+  if (!list.empty()) HSFM_CUDA(cudaMemcpyAsync(d_list, list.data(), sizeof(int) * list.size(), cudaMemcpyHostToDevice, s));
+  HSFM_CUDA(cudaStreamSynchronize(s));  // the host vectors may be rebuilt by the next problem
+  return 0;
+}
+void CholPlan::destroy() {
+  if (d_fb) cudaFree(d_fb);
+  d_fb = nullptr; d_list = nullptr; d_cap = 0; use = false;
+}
+
+// Envelope factorisation: per panel K only the active row blocks R_K are solved and updated.  One panel of
+// look-ahead: the chain stream factors the diagonal block, solves the panel and updates the NEXT panel's column
+// (block K+1 against every active block); the main stream updates the other active pairs behind it.
+static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches,
+                                const CholPlan& pl, int n_sm) {
+  static const bool no_la = getenv("HSFM_NO_LOOKAHEAD") != nullptr;
+  const bool la = aux && aux->stream && !no_la;
+  cudaStream_t s2 = la ? aux->stream : s;
+  if (la) {
+    cudaEventRecord(aux->ev_fork, s);
+    cudaStreamWaitEvent(s2, aux->ev_fork, 0);
+  }
+  bool rest_pending = false;
+  for (int K = 0, k0 = 0; K < pl.panels; ++K, k0 += NB) {
+    const int kb = min(NB, n - k0);
+    double* Linv = ws + (size_t)K * NB * NB;
+    chol_diag_kernel<<<1, 256, kDiagSmem, s2>>>(S, n, k0, kb, Linv, fail_flag);
+    ++*launches;
+    const int cnt = pl.cnt[K];
+    if (cnt == 0) {  // nothing below this panel; keep the chain's "one step behind" guarantee
+      if (la && rest_pending) { cudaStreamWaitEvent(s2, aux->ev_rest, 0); rest_pending = false; }
+      continue;
+    }
+    const int* list = pl.d_list + pl.off[K];
+    int rows_per = 64;  // strips of 8..64 rows: about one CTA per SM
+    while (rows_per > 8 && cnt * (NB / rows_per) < n_sm) rows_per >>= 1;
+    const int spb = NB / rows_per;
+    chol_trsm_strip_kernel<<<cnt * spb, 256, rows_per * TS_LD * (int)sizeof(double), s2>>>(S, n, k0, Linv, rows_per, fail_flag, list, spb);
+    ++*launches;
+    const bool has_col = pl.list[(size_t)pl.off[K]] == K + 1;
+    const int rest_cnt = has_col ? cnt - 1 : cnt;
+    if (la && rest_cnt > 0) cudaEventRecord(aux->ev_panel, s2);
+    // column K+1 was last written by the main stream's update of step K-1; diag/trsm above only needed the
+    // updates up to step K-2, which the chain waited for one step ago
+    if (la && rest_pending) { cudaStreamWaitEvent(s2, aux->ev_rest, 0); rest_pending = false; }
+    if (has_col) {
+      chol_syrk_kernel<<<min(2 * cnt, 2 * n_sm), 128, kGemmSmem, s2>>>(S, n, k0, 0, 0, 2 * cnt, 0, fail_flag, list);
+      ++*launches;
+    }
+    if (rest_cnt > 0) {
+      if (la) cudaStreamWaitEvent(s, aux->ev_panel, 0);
+      const int tiles = rest_cnt * (rest_cnt + 1);
+      chol_syrk_kernel<<<min(tiles, 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 0, -1, tiles, 0, fail_flag, has_col ? list + 1 : list);
+      ++*launches;
+      if (la) { cudaEventRecord(aux->ev_rest, s); rest_pending = true; }
+    }
+  }
+  if (la) {
+    cudaEventRecord(aux->ev_join, s2);
+    cudaStreamWaitEvent(s, aux->ev_join, 0);
+  }
+}
+
+void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches, const CholPlan* plan) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDiagSmem);
@@ -908,6 +1032,10 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
     if (bulk_ctas == 0) bulk_ctas = 1 << 30;  // one tile per CTA: slots turn over every tile, chain kernels slip in
     else if (bulk_ctas < 0) bulk_ctas = n_sm + bulk_ctas;
   }
+  if (plan && plan->use && plan->n == n) {
+    launch_cholesky_env(S, n, ws, fail_flag, s, aux, launches, *plan, n_sm);
+    return;
+  }
   const int panels = (n + NB - 1) / NB;
   static const bool no_la = getenv("HSFM_NO_LOOKAHEAD") != nullptr;  // experiment knob
   const bool la = aux && aux->stream && panels > 2 && !no_la;
@@ -927,22 +1055,22 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
     int rows_per = ((m + n_sm - 1) / n_sm + 7) & ~7;
     rows_per = max(8, min(TS_MAXROWS, rows_per));
     chol_trsm_strip_kernel<<<(m + rows_per - 1) / rows_per, 256, rows_per * TS_LD * (int)sizeof(double), s2>>>(S, n, k0, Linv, rows_per,
-                                                                                                                   fail_flag);
+                                                                                                                   fail_flag, nullptr, 1);
     ++*launches;
     if (la) {
       cudaEventRecord(aux->ev_panel, s2);
       if (panel > 0) cudaStreamWaitEvent(s2, aux->ev_rest, 0);  // "ahead k-1": cb 2,3 of the previous step = cb 0,1 of this one
     }
-    chol_syrk_kernel<<<min(2 * rb, 2 * n_sm), 128, kGemmSmem, s2>>>(S, n, k0, 0, 0, 2 * rb, 0, fail_flag);
+    chol_syrk_kernel<<<min(2 * rb, 2 * n_sm), 128, kGemmSmem, s2>>>(S, n, k0, 0, 0, 2 * rb, 0, fail_flag, nullptr);
     ++*launches;
     if (rb > 1) {
       if (la) cudaStreamWaitEvent(s, aux->ev_panel, 0);
-      chol_syrk_kernel<<<min(2 * (rb - 1), 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 1, 2, 2 * (rb - 1), 0, fail_flag);
+      chol_syrk_kernel<<<min(2 * (rb - 1), 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 1, 2, 2 * (rb - 1), 0, fail_flag, nullptr);
       ++*launches;
     }
     if (la) cudaEventRecord(aux->ev_rest, s);
     if (rb > 2) {
-      chol_syrk_kernel<<<min((rb - 2) * (rb - 1), bulk_ctas), 128, kGemmSmem, s>>>(S, n, k0, 0, -4, (rb - 2) * (rb - 1), 0, fail_flag);
+      chol_syrk_kernel<<<min((rb - 2) * (rb - 1), bulk_ctas), 128, kGemmSmem, s>>>(S, n, k0, 0, -4, (rb - 2) * (rb - 1), 0, fail_flag, nullptr);
       ++*launches;
     }
   }
@@ -954,7 +1082,7 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
 
 // Solves S y = b with the factor from launch_cholesky.  b holds 2n doubles: [0,n) right-hand side
 // in / solution out, [n,2n) scratch for the intermediate vector.
-void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream_t s, int64_t* launches) {
+void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream_t s, int64_t* launches, const CholPlan* plan) {
   double* w = b + n;
   const int panels = (n + NB - 1) / NB;
   int* flags = reinterpret_cast<int*>(ws + (size_t)panels * NB * NB);  // [2 * panels]
@@ -972,7 +1100,8 @@ void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream
     int* ff = flags;
     int* fb = flags + panels;
     int nn = n;
-    void* args[] = {(void*)&L, (void*)&nn, (void*)&LinvAll, (void*)&b, (void*)&w, (void*)&ff, (void*)&fb};
+    const int* env = (plan && plan->use && plan->n == n) ? plan->d_fb : nullptr;
+    void* args[] = {(void*)&L, (void*)&nn, (void*)&LinvAll, (void*)&b, (void*)&w, (void*)&ff, (void*)&fb, (void*)&env};
     const int grid = std::min(panels, n_sm);
     if (cudaLaunchCooperativeKernel((const void*)trsv_coop_kernel, dim3(grid), dim3(256), args, 0, s) == cudaSuccess) {
       ++*launches;

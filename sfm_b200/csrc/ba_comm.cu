@@ -17,7 +17,7 @@ typedef struct { char internal[128]; } ncclUniqueId_t;
 typedef void* ncclComm_t_;
 typedef int ncclResult_t_;
 constexpr int kNcclInt32 = 2, kNcclFloat64 = 8;  // ncclDataType_t
-constexpr int kNcclSum = 0, kNcclMax = 2;        // ncclRedOp_t
+constexpr int kNcclSum = 0, kNcclMax = 2, kNcclMin = 3;  // ncclRedOp_t
 
 struct Api {
   void* lib = nullptr;
@@ -85,6 +85,11 @@ int Comm::allreduce_max(double* buf, size_t count, cudaStream_t s) {
 int Comm::allreduce_sum_i32(int* buf, size_t count, cudaStream_t s) {
   if (n_ranks <= 1 || count == 0) return 0;
   const int rc = api().AllReduce(buf, buf, count, kNcclInt32, kNcclSum, handle, s);
+  return rc ? 2000 + rc : 0;
+}
+int Comm::allreduce_min_i32(int* buf, size_t count, cudaStream_t s) {
+  if (n_ranks <= 1 || count == 0) return 0;
+  const int rc = api().AllReduce(buf, buf, count, kNcclInt32, kNcclMin, handle, s);
   return rc ? 2000 + rc : 0;
 }
 void Comm::destroy() {

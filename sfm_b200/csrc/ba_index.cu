@@ -148,6 +148,13 @@ void launch_rows_to_caller(Problem& P, int w, const double* internal_order, doub
   P.launches++;
 }
 
+// cam_first[c] = smallest camera that shares a point with camera c (initialised to c): the envelope of S.
+__global__ void cam_first_kernel(int n, const int* __restrict__ cam, const int* __restrict__ pt, const int* __restrict__ min_cam,
+                                 int* __restrict__ first) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) atomicMin(first + cam[i], min_cam[pt[i]]);
+}
+
 // One CTA per tile: the tile's distinct cameras in ascending order and the slot of every observation's
 // camera in that list.  O(TILE^2) comparisons through shared-memory broadcasts; runs once per upload.
 __global__ void __launch_bounds__(TILE) tile_cams_kernel(const int* __restrict__ tile_start, const int* __restrict__ cam,
@@ -245,6 +252,21 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     gather_rows_kernel<<<cdivz((size_t)n_pts * 3, 256), 256, 0, s>>>(n_pts, 3, P.pt_old_of_new, P.pts_io, P.pts_x0);
   }
   HSFM_CUDA(cudaMemcpyAsync(P.pts_x, P.pts_x0, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToDevice, s));
+  {
+    // envelope of the reduced camera matrix (over all ranks), kept on the host for the Cholesky plan
+    int* d_first;
+    ALLOC(d_first, n_cams);
+    P.cam_first.assign((size_t)n_cams, 0);
+    if (n_cams > 0) {
+      iota_kernel<<<cdiv(n_cams, 256), 256, 0, s>>>(n_cams, d_first);
+      if (n > 0) cam_first_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, cam_in, pt_in, min_cam, d_first);
+      if (comm.n_ranks > 1) {
+        int rc = comm.allreduce_min_i32(d_first, (size_t)n_cams, s);
+        if (rc) return rc;
+      }
+      HSFM_CUDA(cudaMemcpyAsync(P.cam_first.data(), d_first, sizeof(int) * (size_t)n_cams, cudaMemcpyDeviceToHost, s));
+    }
+  }
   if (n > 0) {
     // point-major with cameras ascending inside a point: stable sort by camera, then stable sort by
     // internal point id (ties keep input order, so every later floating-point sum has a fixed order)

@@ -55,6 +55,7 @@ struct Problem {
   int n_obs = 0, n_cams = 0, n_pts = 0, n_tiles = 0, n_chunks = 0;
   int max_track = 0;
   int max_tile_cams = 0;  // largest number of distinct cameras in one tile (sizes the shared-memory row staging)
+  std::vector<int> cam_first;  // [n_cams] smallest camera sharing a point with camera c (all ranks) — envelope of S
   Dev d{};
   // Device arena: ONE grow-only allocation per context that every per-problem buffer is carved from, so the
   // per-keyframe calls of CSfM::mapping (CSfM.cpp:252-259) pay for cudaMalloc/cudaFree only when the problem
@@ -114,6 +115,7 @@ struct Comm {
   int allreduce_sum(double* buf, size_t count, cudaStream_t s);
   int allreduce_max(double* buf, size_t count, cudaStream_t s);
   int allreduce_sum_i32(int* buf, size_t count, cudaStream_t s);
+  int allreduce_min_i32(int* buf, size_t count, cudaStream_t s);
   void destroy();
 };
 int comm_unique_id(void* out128);
@@ -164,9 +166,28 @@ struct CholAux {
   int init();
   void destroy();
 };
-size_t cholesky_workspace_doubles(int n);  // L11^-1 blocks (one 128×128 per panel) + packed TRSM scratch panel
-void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches);
-void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream_t s, int64_t* launches);
+// Block envelope of the reduced camera matrix (static per problem).  Camera c shares points with no camera
+// below cam_first[c], so row block I of S (128 rows) is exactly zero left of column block fb[I], and so is L: the
+// Cholesky factor has the envelope of the matrix.  Panel K then only has to touch the ACTIVE row blocks
+// R_K = { I > K : fb[I] <= K }.  For a scan trajectory (keyframes see points of nearby keyframes, plus a few loop
+// closures) that is a band: the factorisation of the Venice-shaped problem costs 2-3 % of the dense flops.
+struct CholPlan {
+  int n = 0, panels = 0;
+  bool use = false;            // false: treat the matrix as dense (the envelope is most of the triangle)
+  double fill = 1.0;           // envelope blocks / lower-triangle blocks
+  std::vector<int> fb;         // [panels] first column block in the envelope of row block I
+  std::vector<int> off, cnt;   // per panel K: list[off[K] .. off[K]+cnt[K]) = R_K ascending
+  std::vector<int> list;
+  int* d_fb = nullptr;         // device copy: fb, then the lists
+  int* d_list = nullptr;
+  size_t d_cap = 0;
+  int build(int n_cams, const int* cam_first, cudaStream_t s);  // cam_first on the host; nullptr = dense
+  void destroy();
+};
+size_t cholesky_workspace_doubles(int n);  // L11^-1 blocks (one 128×128 per panel) + flags of the cooperative triangular solve
+void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches,
+                     const CholPlan* plan = nullptr);
+void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream_t s, int64_t* launches, const CholPlan* plan = nullptr);
 
 void launch_spd_fill(double* A, int n, double* b /*null = matrix only*/, cudaStream_t s);  // bench tap: synthetic SPD matrix, b = A 1
 void launch_spd_err(int n, const double* x, double* err, cudaStream_t s);                 // max |x - 1|
@@ -178,6 +199,8 @@ struct Ctx {
   cudaStream_t stream = nullptr;
   Comm comm;
   CholAux chol_aux;
+  CholPlan chol_plan;     // envelope plan of the resident problem (built on first dense solve)
+  bool chol_plan_valid = false;
   Problem prob;
   bool has_problem = false;
   std::vector<cudaEvent_t> phase_events;  // pool reused across solves (phase timing of lm_solve)

@@ -102,10 +102,10 @@ struct Driver {
           chk(ctx.comm.allreduce_sum(P.rhs, n6, s));
         }
         mark(2);
-        launch_cholesky(P.S, n6, P.S + (size_t)n6 * n6, P.flags + F_CHOL_FAIL, s, &ctx.chol_aux, &P.launches);
+        launch_cholesky(P.S, n6, P.S + (size_t)n6 * n6, P.flags + F_CHOL_FAIL, s, &ctx.chol_aux, &P.launches, &ctx.chol_plan);
         mark(3);
         HSFM_CUDA(cudaMemcpyAsync(P.yc, P.rhs, sizeof(double) * n6, cudaMemcpyDeviceToDevice, s));
-        launch_chol_solve(P.S, n6, P.S + (size_t)n6 * n6, P.yc, s, &P.launches);
+        launch_chol_solve(P.S, n6, P.S + (size_t)n6 * n6, P.yc, s, &P.launches, &ctx.chol_plan);
       } else {
         launch_cam_major(P, P.rows_x, P.pts_x, P.scale_p, 1, s);
         if (multi()) chk(ctx.comm.allreduce_sum(P.E, 21 * (size_t)P.n_cams, s));
@@ -181,6 +181,11 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
         } else {
           P.S_capacity = need;
         }
+      }
+      if (D.dense && !ctx.chol_plan_valid) {  // static per problem: which 128-blocks of S (and of L) can be non-zero
+        int rc = ctx.chol_plan.build(P.n_cams, (int)P.cam_first.size() == P.n_cams ? P.cam_first.data() : nullptr, s);
+        if (rc) return rc;
+        ctx.chol_plan_valid = true;
       }
     }
   }

@@ -143,6 +143,24 @@ def test_golden_normal_equations_lapack(ctx, golden_dir):
     assert s["trace"][1]["model_cost_change"] == pytest.approx(float(g["model_cost_change"]), rel=1e-8)
 
 
+def test_tiles_with_many_distinct_cameras(ctx):
+    """Two-view tracks over 300 cameras: a 256-observation tile touches well over a hundred distinct cameras, so
+    the shared-memory staging of camera rows needs more than the 48 KB default (opt-in dynamic shared memory)."""
+    p = synth.make_ring(300, 3000, 2, seed=77, skew=0.1)
+    r, J, cost = ctx.evaluate(p)
+    r0, J0, cost0 = po.evaluate(p)
+    assert residual_err(r, r0, p.obs) < TOL_RJ and jacobian_err(J, J0) < TOL_RJ
+    assert cost == pytest.approx(cost0, rel=1e-12)
+    g, o = ctx.schur(p, radius=1e4), po.schur(p, radius=1e4)
+    for k, tol in [("Hpp", 1e-11), ("gp", 1e-10), ("Hcc", 1e-11), ("gc", 1e-10), ("rhs", 1e-9), ("S", 1e-9)]:
+        assert rel(g[k], o[k]) < tol, k
+    sd = ctx.solve_packed(p, opts=api.default_options(linear_solver=api.LINEAR_DENSE_SCHUR, max_num_iterations=3))[2]
+    sp = ctx.solve_packed(p, opts=api.default_options(linear_solver=api.LINEAR_PCG, max_num_iterations=3, pcg_max_iterations=3000))[2]
+    so = po.solve(p, opts=po.default_options(num_threads=4, max_num_iterations=3))[2]
+    assert sd["final_cost"] == pytest.approx(so["final_cost"], rel=TOL_COST)
+    assert sp["final_cost"] == pytest.approx(so["final_cost"], rel=TOL_COST)
+
+
 @pytest.mark.parametrize("linear", [api.LINEAR_DENSE_SCHUR, api.LINEAR_PCG], ids=["dense", "pcg"])
 @pytest.mark.parametrize("make", [lambda: synth.make_config("c1"), lambda: synth.make_config("c2", scale=0.1),
                                   lambda: synth.make_config("c3", scale=0.05), lambda: _with_dist(synth.make_ring(12, 500, 7, seed=31))],
