@@ -35,7 +35,9 @@ sys.path.insert(0, ROOT)
 # MEASURED_PEAKS.json carries no FP64 figure (nominal: 128 flop/clk/SM x 148 SMs x 1.965 GHz = 37.2 TFLOP/s).
 FP64_DMMA_PEAK_TFLOPS = 37.1
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures (profiles/), c4
-TRAFFIC_C4 = {"rj_form": 985.6e6, "schur_matvec": 982.2e6}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch at c4, from the ncu --set full captures summarised in
+# profiles/r01_ncu_streaming.md (rj: 163.0 + 838.9 MB; mat-vec = schur_pass<1> + cam_gather6 + cam_reduce6; ...)
+TRAFFIC_C4 = {"rj_form": 1001.9e6, "schur_matvec": 1299.8e6, "schur_rhs": 1259.0e6, "dense_schur": 902.6e6}
 
 METRIC = "lm_iterations_per_s"
 UNIT = "LM iterations/s"
@@ -221,8 +223,9 @@ def main():
     # ---- kernel timings / roofline (rank 0's shard; live CUDA events inside the library) ---------
     peak, peak_src = load_peaks()
     kernels = {}
-    for k in ["rj_form", "rj", "schur_matvec", "backsub", "cam_form", "cost"]:
-        t = ctx.time_kernel(k, 20)
+    dense = summ["linear_solver_used"] == api.LINEAR_DENSE_SCHUR
+    for k in ["rj_form", "rj", "schur_matvec", "schur_rhs", "backsub", "cam_form", "cost"] + (["dense_schur"] if dense else []):
+        t = ctx.time_kernel(k, 20 if k != "dense_schur" else 5)
         b = ctx.algorithmic_bytes(k)
         kernels[k] = {"ms": t, "algorithmic_bytes": b, "gbs": b / t / 1e6, "frac_of_hbm_peak": b / t / 1e6 / peak}
     rj = kernels["rj"]
@@ -230,7 +233,6 @@ def main():
     rj_obs = torch.tensor([obs_per_s_local], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(rj_obs, op=dist.ReduceOp.SUM)
-    dense = summ["linear_solver_used"] == api.LINEAR_DENSE_SCHUR
     chol = None
     if dense and rank == 0:
         n6 = 6 * n_cams
@@ -277,18 +279,28 @@ def main():
 
     if rank == 0:
         phases = dict(zip(["linearise", "reduced_system", "factor", "reduced_solve", "step_backsub_cost", "readback"], summ["phase_ms"][:6]))
-        hbm_dom = max(("rj_form", "schur_matvec", "backsub", "cam_form"), key=lambda k: kernels[k]["ms"])
+        # The bandwidth-bound kernels of one LM iteration (north star: residual/Jacobian and Schur kernels).  The
+        # headline roofline is the residual+Jacobian kernel; the others are listed in "kernels".
+        hbm_dom = "rj_form"
         traffic = TRAFFIC_C4.get(hbm_dom) if (args.config == "c4" and world == 1) else None
-        roof_hbm = {"kernel": "rj_kernel<write_j,form>" if hbm_dom == "rj_form" else hbm_dom, "bound": "hbm", "achieved": kernels[hbm_dom]["gbs"],
+        roof_hbm = {"kernel": "rj_kernel<write_j,form>", "bound": "hbm", "achieved": kernels[hbm_dom]["gbs"],
                     "peak": peak, "unit": "GB/s", "frac": kernels[hbm_dom]["gbs"] / peak, "traffic": traffic, "peak_source": peak_src}
-        if dense and phases["factor"] >= max(phases["linearise"], phases["reduced_system"], phases["step_backsub_cost"]):
-            # the step is dominated by the dense Cholesky of the reduced camera system: FP64 tensor (DMMA) bound
-            roofline = {"kernel": "chol_syrk_kernel (dense Cholesky of S, DMMA m8n8k4)", "bound": "tensor", "achieved": chol["tflops"],
-                        "peak": FP64_DMMA_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": chol["frac_of_fp64_dmma_peak"], "traffic": None,
-                        "peak_source": "FP64 DMMA peak measured with scripts/micro/fp64_peaks.cu on this pool (MEASURED_PEAKS.json has no FP64 figure)",
-                        "share_of_step": phases["factor"] / max(sum(phases.values()), 1e-9)}
-        else:
-            roofline = roof_hbm
+        roofline = dict(roof_hbm)
+        step_ms = max(sum(phases.values()), 1e-9)
+        its_n = max(summ["num_iterations"], 1)
+        roofline["share_of_step"] = (kernels[hbm_dom]["ms"] * its_n) / step_ms
+        roof_tensor = None
+        if chol:
+            # dense tap: the same factorisation kernels on a FULL n x n matrix (no envelope to exploit): FP64 tensor bound
+            roof_tensor = {"kernel": "chol_syrk_kernel (dense Cholesky tap, DMMA m8n8k4)", "bound": "tensor", "achieved": chol["tflops"],
+                           "peak": FP64_DMMA_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": chol["frac_of_fp64_dmma_peak"], "traffic": None,
+                           "peak_source": "FP64 DMMA peak measured with scripts/micro/fp64_peaks.cu on this pool (MEASURED_PEAKS.json has no FP64 figure)"}
+        # where the step goes: with the envelope factorisation the largest phase is the CRITICAL PATH of the
+        # per-panel diagonal-block factorisations (latency-bound, one CTA), not a throughput kernel
+        dominant = max(phases, key=lambda k: phases[k])
+        dominant_phase = {"phase": dominant, "share_of_step": phases[dominant] / step_ms,
+                          "note": "factor = envelope Cholesky of the reduced camera system: a chain of 128-column panel steps "
+                                  "(diagonal block on one CTA -> panel solve -> next-column update); latency-bound" if dominant == "factor" else ""}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
@@ -302,6 +314,8 @@ def main():
             "clocks": clocks,
             "roofline": roofline,
             "roofline_hbm": roof_hbm,
+            "roofline_tensor": roof_tensor,
+            "dominant_phase": dominant_phase,
             "phase_ms_per_step": phases,
             "kernels": kernels,
             "cholesky": chol,

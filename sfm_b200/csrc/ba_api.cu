@@ -221,6 +221,8 @@ int64_t hsfm_ba_problem_algorithmic_bytes(hsfm_ba_ctx* h, const char* kernel) {
   if (!std::strcmp(kernel, "backsub")) return 168 * N + 120 * Q + 48 * C;          // + r 16 ; Hpp^-1 48, z_p 24, y_p 24, cand 24
   if (!std::strcmp(kernel, "cam_form")) return 20 * N + 24 * Q + 88 * C + 216 * C; // obs_cs 16 + pt 4 ; point gather ; rows ; Hcc+gc out
   if (!std::strcmp(kernel, "cost")) return 24 * N + 24 * Q + 88 * C;
+  if (!std::strcmp(kernel, "schur_rhs")) return 148 * N + 24 * Q + 96 * C;         // Jc 96 + Jp 48 + pt 4 ; z_p ; g_c in, rhs out
+  if (!std::strcmp(kernel, "dense_schur")) return 152 * N + 48 * Q;                // Jc, Jp, cam, pt ; Hpp^-1 (S blocks stay in L2)
   return 0;
 }
 
@@ -239,6 +241,11 @@ int hsfm_ba_problem_time_kernel(hsfm_ba_ctx* h, const char* kernel, int reps, do
     else if (!std::strcmp(kernel, "backsub")) launch_backsub(P, s);
     else if (!std::strcmp(kernel, "cam_form")) launch_cam_major(P, P.rows_x, P.pts_x, P.scale_p, 0, s);
     else if (!std::strcmp(kernel, "cost")) launch_cost(P, P.rows_x, P.pts_x, P_COST, s);
+    else if (!std::strcmp(kernel, "schur_rhs")) launch_schur_rhs(P, true, s);
+    else if (!std::strcmp(kernel, "dense_schur")) {
+      if (!P.S) return HSFM_BA_ERR_ARG;  // needs a dense solve first (S is allocated lazily)
+      launch_dense_schur(P, s);
+    }
     else return HSFM_BA_ERR_ARG;
     return 0;
   };

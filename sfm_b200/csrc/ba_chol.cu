@@ -75,58 +75,82 @@ __device__ __forceinline__ void tile_mma32(double& c0, double& c1, const double*
 // reciprocal square root is started before the rest of the row update, so the rsqrt latency — the serial
 // chain of the whole factorisation — overlaps the 30 remaining FMAs.  D (row stride LB) receives L (strict
 // upper zeroed), dinv[r] = 1/L[r][r].  Returns 0 or the 1-based failing column.
+// 1/d and 1/sqrt(d) from the hardware seed (MUFU, ~2^-22 relative) and two Newton steps of fused multiply-adds:
+// full double precision for normal d > 0 without the special-case branches of the library routines.  The
+// factorisation checks d > 0 and finiteness itself.
+__device__ __forceinline__ double fast_rcp(double d) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+  double e = fma(-d, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-d, y, 1.0);
+  return fma(y, e, y);
+}
+__device__ __forceinline__ double fast_rsqrt(double d) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+  double e = fma(-(d * y), y, 1.0);
+  y = fma(0.5 * y, e, y);
+  e = fma(-(d * y), y, 1.0);
+  return fma(0.5 * y, e, y);
+}
+
 __device__ __forceinline__ int warp_chol32(double* __restrict__ D, double* __restrict__ col, double* __restrict__ dinv, int lane) {
   double a[SB];
 #pragma unroll
   for (int c = 0; c < SB; ++c) a[c] = D[lane * LB + c];
   int bad = 0;
+  // The serial chain of the whole factorisation is pivot -> 1/pivot -> next column -> next pivot.  Only the
+  // RECIPROCAL sits on it (seed + four dependent multiply-adds); the reciprocal square root that scales the
+  // stored column is computed beside it.
   double d = __shfl_sync(0xffffffffu, a[0], 0);
-  double inv = rsqrt(d);
+  double r = fast_rcp(d);
 #pragma unroll 1
   for (int j = 0; j < SB; ++j) {
     if (!(d > 0.0) || !isfinite(d)) { bad = j + 1; break; }  // uniform: d is a broadcast
     col[lane] = a[0];
     col[lane + SB] = a[0];
     __syncwarp();
-    const double u = a[0] * (inv * inv);
+    const double u = a[0] * r;  // A[row][j] / pivot
+    const double a0n = fma(-u, col[j + 1], a[1]);
+    const double dn = __shfl_sync(0xffffffffu, a0n, (j + 1) & 31);
+    const double rn = fast_rcp(dn);
+    const double inv = fast_rsqrt(d);
     double l = a[0] * inv;
     if (lane == j) { l = d * inv; dinv[j] = inv; }
     D[lane * LB + j] = (lane >= j) ? l : 0.0;
-    a[0] = fma(-u, col[j + 1], a[1]);
-    d = __shfl_sync(0xffffffffu, a[0], (j + 1) & 31);
-    inv = rsqrt(d);
 #pragma unroll
     for (int c = 2; c < SB; ++c) a[c - 1] = fma(-u, col[j + c], a[c]);  // columns past 31 hold don't-care values
+    a[0] = a0n;
+    d = dn;
+    r = rn;
     __syncwarp();
   }
   return bad;
 }
 
 // Inverse of the lower-triangular 32x32 sub-block D by one warp, written to X (both row stride LB; X may
-// alias D: row k of D is dead once row k of the inverse is published).  Row k of the inverse is final at
-// step k; lane k publishes it and the lanes below eliminate it.
-__device__ __forceinline__ void warp_trinv32(const double* D, double my_dinv, double* X, int lane) {
+// alias D).  Lane c solves L x = e_c for column c of the inverse by forward substitution, entirely in its own
+// registers: every lane runs the same (i, k) loop, the L[i][k] are warp-uniform shared-memory broadcasts and
+// the leading zeros of the column need no predicate (they multiply through).  No shuffles, no barriers inside
+// — a 32-step chain of independent multiply-adds instead of 32 publish/eliminate round trips.
+__device__ __forceinline__ void warp_trinv32(const double* D, const double* __restrict__ dinv, double* X, int lane) {
   double x[SB];
 #pragma unroll
-  for (int c = 0; c < SB; ++c) x[c] = (c == lane) ? 1.0 : 0.0;
-#pragma unroll 1
-  for (int k = 0; k < SB; ++k) {
-    const double lrk = (lane > k) ? D[lane * LB + k] : 0.0;  // read before row k is overwritten (only rows > k are read)
-    if (lane == k) {
+  for (int i = 0; i < SB; ++i) {
+    double s0 = (i == lane) ? 1.0 : 0.0, s1 = 0.0;
 #pragma unroll
-      for (int c = 0; c < SB; c += 2)
-        *reinterpret_cast<double2*>(X + k * LB + c) = make_double2(x[c] * my_dinv, x[c + 1] * my_dinv);
+    for (int k = 0; k + 1 < i; k += 2) {
+      const double2 l = *reinterpret_cast<const double2*>(D + i * LB + k);
+      s0 = fma(-l.x, x[k], s0);
+      s1 = fma(-l.y, x[k + 1], s1);
     }
-    __syncwarp();
-    if (lane > k) {
-#pragma unroll
-      for (int c = 0; c < SB; c += 2) {
-        const double2 xk = *reinterpret_cast<const double2*>(X + k * LB + c);
-        x[c] = fma(-lrk, xk.x, x[c]);
-        x[c + 1] = fma(-lrk, xk.y, x[c + 1]);
-      }
-    }
+    if (i & 1) s0 = fma(-D[i * LB + i - 1], x[i - 1], s0);
+    x[i] = (s0 + s1) * dinv[i];
   }
+  __syncwarp();  // every lane has read all of D before anyone overwrites it
+#pragma unroll
+  for (int i = 0; i < SB; ++i) X[i * LB + lane] = x[i];
 }
 
 #ifdef HSFM_DIAG_TIMING
@@ -241,7 +265,7 @@ __global__ void __launch_bounds__(256, 2) chol_diag_kernel(double* __restrict__ 
   DIAG_TICK(3);
   // ---- L^-1, in place ----
   // (1) diagonal sub-blocks X(i,i) = L(i,i)^-1: warps 0..3, in registers, over L(i,i)
-  if (warp < 4) warp_trinv32(sL + blk_id(warp, warp) * SBLK, sDinv[warp * SB + lane], sL + blk_id(warp, warp) * SBLK, lane);
+  if (warp < 4) warp_trinv32(sL + blk_id(warp, warp) * SBLK, sDinv + warp * SB, sL + blk_id(warp, warp) * SBLK, lane);
   __syncthreads();
   DIAG_TICK(4);
   // (2) M(i,k) = X(i,i) L(i,k) over L(i,k), i > k: all 96 tiles to registers, barrier, write back
@@ -549,44 +573,70 @@ __global__ void __launch_bounds__(256) chol_trsm_strip_kernel(double* __restrict
   const int ks_hi = 2 * (ct_hi + 1), ks_lo = 2 * (ct_lo + 1);  // k-steps (of 4) each column tile needs
   const double* __restrict__ Bhi = Linv + (ct_hi * 8 + fr) * NB + fk;
   const double* __restrict__ Blo = Linv + (ct_lo * 8 + fr) * NB + fk;
-  double bh[4], bl[4];
-#pragma unroll
-  for (int u = 0; u < 4; ++u) {
-    bh[u] = (u < ks_hi) ? __ldg(Bhi + 4 * u) : 0.0;
-    bl[u] = (u < ks_lo) ? __ldg(Blo + 4 * u) : 0.0;
-  }
-  cp_async_wait<0>();
-  __syncthreads();
-  if (failed || nr <= 0) return;
   double acc[TS_MAXROWS / 8][2][2];
 #pragma unroll
   for (int rt = 0; rt < TS_MAXROWS / 8; ++rt) { acc[rt][0][0] = acc[rt][0][1] = acc[rt][1][0] = acc[rt][1][1] = 0.0; }
-#pragma unroll 1
-  for (int ks0 = 0; ks0 < ks_hi; ks0 += 4) {
-    double nh[4], nl[4];
+  if (rows_per <= 16) {
+    // Latency path (envelope factorisation: few rows per CTA, the kernel sits on the critical path): all 34
+    // B fragments of the warp's two column tiles are fetched in ONE round trip, before the strip lands.
+    double bh[32], bl[16];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {  // next group of B fragments, in flight while this group is multiplied
-      const int ks = ks0 + 4 + u;
-      nh[u] = (ks < ks_hi) ? __ldg(Bhi + 4 * ks) : 0.0;
-      nl[u] = (ks < ks_lo) ? __ldg(Blo + 4 * ks) : 0.0;
-    }
+    for (int u = 0; u < 32; ++u) bh[u] = (u < ks_hi) ? __ldg(Bhi + 4 * u) : 0.0;
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int ks = ks0 + u;
-      if (ks < ks_hi) {
-        const bool lo = ks < ks_lo;
+    for (int u = 0; u < 16; ++u) bl[u] = (u < ks_lo) ? __ldg(Blo + 4 * u) : 0.0;
+    cp_async_wait<0>();
+    __syncthreads();
+    if (failed || nr <= 0) return;
 #pragma unroll
-        for (int rt = 0; rt < TS_MAXROWS / 8; ++rt) {
+    for (int u = 0; u < 32; ++u) {
+      if (u < ks_hi) {
+#pragma unroll
+        for (int rt = 0; rt < 2; ++rt) {
           if (rt < RT) {
-            const double a = sA[rt * 8 + fr][ks * 4 + fk];
+            const double a = sA[rt * 8 + fr][u * 4 + fk];
             dmma884(acc[rt][1][0], acc[rt][1][1], a, bh[u]);
-            if (lo) dmma884(acc[rt][0][0], acc[rt][0][1], a, bl[u]);
+            if (u < 16 && u < ks_lo) dmma884(acc[rt][0][0], acc[rt][0][1], a, bl[u < 16 ? u : 0]);
           }
         }
       }
     }
+  } else {
+    double bh[4], bl[4];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) { bh[u] = nh[u]; bl[u] = nl[u]; }
+    for (int u = 0; u < 4; ++u) {
+      bh[u] = (u < ks_hi) ? __ldg(Bhi + 4 * u) : 0.0;
+      bl[u] = (u < ks_lo) ? __ldg(Blo + 4 * u) : 0.0;
+    }
+    cp_async_wait<0>();
+    __syncthreads();
+    if (failed || nr <= 0) return;
+#pragma unroll 1
+    for (int ks0 = 0; ks0 < ks_hi; ks0 += 4) {
+      double nh[4], nl[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {  // next group of B fragments, in flight while this group is multiplied
+        const int ks = ks0 + 4 + u;
+        nh[u] = (ks < ks_hi) ? __ldg(Bhi + 4 * ks) : 0.0;
+        nl[u] = (ks < ks_lo) ? __ldg(Blo + 4 * ks) : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int ks = ks0 + u;
+        if (ks < ks_hi) {
+          const bool lo = ks < ks_lo;
+#pragma unroll
+          for (int rt = 0; rt < TS_MAXROWS / 8; ++rt) {
+            if (rt < RT) {
+              const double a = sA[rt * 8 + fr][ks * 4 + fk];
+              dmma884(acc[rt][1][0], acc[rt][1][1], a, bh[u]);
+              if (lo) dmma884(acc[rt][0][0], acc[rt][0][1], a, bl[u]);
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { bh[u] = nh[u]; bl[u] = nl[u]; }
+    }
   }
 #pragma unroll
   for (int rt = 0; rt < TS_MAXROWS / 8; ++rt) {

@@ -148,11 +148,18 @@ void launch_rows_to_caller(Problem& P, int w, const double* internal_order, doub
   P.launches++;
 }
 
-// cam_first[c] = smallest camera that shares a point with camera c (initialised to c): the envelope of S.
-__global__ void cam_first_kernel(int n, const int* __restrict__ cam, const int* __restrict__ pt, const int* __restrict__ min_cam,
-                                 int* __restrict__ first) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) atomicMin(first + cam[i], min_cam[pt[i]]);
+// cam_first[c] = smallest camera that shares a point with camera c: the envelope of S.  Internal point ids
+// are ordered by their smallest observing camera, so it is min_cam_sorted[smallest internal point id among
+// the camera's observations]; one warp per camera over the camera-major list, no atomics.
+__global__ void cam_first_kernel(int n_cams, const int* __restrict__ cam_start, const int* __restrict__ pt_cs,
+                                 const int* __restrict__ min_cam_sorted, int* __restrict__ first) {
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (c >= n_cams) return;
+  int m = 0x7fffffff;
+  for (int j = cam_start[c] + lane; j < cam_start[c + 1]; j += 32) m = min(m, pt_cs[j]);
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) m = min(m, __shfl_xor_sync(0xffffffffu, m, d));
+  if (lane == 0) first[c] = (m == 0x7fffffff) ? c : min(c, min_cam_sorted[m]);
 }
 
 // One CTA per tile: the tile's distinct cameras in ascending order and the slot of every observation's
@@ -252,21 +259,6 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     gather_rows_kernel<<<cdivz((size_t)n_pts * 3, 256), 256, 0, s>>>(n_pts, 3, P.pt_old_of_new, P.pts_io, P.pts_x0);
   }
   HSFM_CUDA(cudaMemcpyAsync(P.pts_x, P.pts_x0, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToDevice, s));
-  {
-    // envelope of the reduced camera matrix (over all ranks), kept on the host for the Cholesky plan
-    int* d_first;
-    ALLOC(d_first, n_cams);
-    P.cam_first.assign((size_t)n_cams, 0);
-    if (n_cams > 0) {
-      iota_kernel<<<cdiv(n_cams, 256), 256, 0, s>>>(n_cams, d_first);
-      if (n > 0) cam_first_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, cam_in, pt_in, min_cam, d_first);
-      if (comm.n_ranks > 1) {
-        int rc = comm.allreduce_min_i32(d_first, (size_t)n_cams, s);
-        if (rc) return rc;
-      }
-      HSFM_CUDA(cudaMemcpyAsync(P.cam_first.data(), d_first, sizeof(int) * (size_t)n_cams, cudaMemcpyDeviceToHost, s));
-    }
-  }
   if (n > 0) {
     // point-major with cameras ascending inside a point: stable sort by camera, then stable sort by
     // internal point id (ties keep input order, so every later floating-point sum has a fixed order)
@@ -283,6 +275,20 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   } else {
     HSFM_CUDA(cudaMemsetAsync(pt_start, 0, sizeof(int) * ((size_t)n_pts + 1), s));
     HSFM_CUDA(cudaMemsetAsync(cam_start, 0, sizeof(int) * ((size_t)n_cams + 1), s));
+  }
+  {
+    // envelope of the reduced camera matrix (over all ranks), kept on the host for the Cholesky plan
+    int* d_first;
+    ALLOC(d_first, n_cams);
+    P.cam_first.assign((size_t)n_cams, 0);
+    if (n_cams > 0) {
+      cam_first_kernel<<<cdiv(n_cams * 32, 256), 256, 0, s>>>(n_cams, cam_start, pt_cs, min_cam_sorted, d_first);
+      if (comm.n_ranks > 1) {
+        int rc = comm.allreduce_min_i32(d_first, (size_t)n_cams, s);
+        if (rc) return rc;
+      }
+      HSFM_CUDA(cudaMemcpyAsync(P.cam_first.data(), d_first, sizeof(int) * (size_t)n_cams, cudaMemcpyDeviceToHost, s));
+    }
   }
   HSFM_CUDA(cudaStreamSynchronize(s));
 
