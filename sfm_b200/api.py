@@ -21,7 +21,7 @@ from ._cdefs import (CONVERGENCE, FAILURE, LINEAR_AUTO, LINEAR_DENSE_SCHUR, LINE
                      STRUCT_AND_POSE, STRUCT_ONLY, Iteration, Options, Summary)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhsfm_ba.so")
+LIB_PATH = os.environ.get("HSFM_BA_LIB", os.path.join(_HERE, "libhsfm_ba.so"))  # override: instrumented experiment builds
 
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int32)

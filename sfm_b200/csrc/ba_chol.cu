@@ -160,6 +160,86 @@ __device__ long long g_diag_clk[32];
 #define DIAG_TICK(k) do { } while (0)
 #endif
 
+// Trailing update of step KQ inside the diagonal block: the warp's T = 12 / 6 / 2 tiles share one k loop.
+template <int KQ>
+__device__ __forceinline__ void diag_trailing(double* sL, int warp, int lane) {
+  constexpr int M = 3 - KQ, T = M * (M + 1) / 2 * 16 / 8;
+  const int fr = lane >> 2, fk = lane & 3;
+  double c0[T], c1[T];
+  const double* pa[T];
+  const double* pb[T];
+  double2* pd[T];
+#pragma unroll
+  for (int q = 0; q < T; ++q) {
+    const int t = warp + 8 * q, b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
+    const int di = b < 1 ? 0 : b < 3 ? 1 : 2, dj = b - di * (di + 1) / 2;
+    const int bi = KQ + 1 + di, bj = KQ + 1 + dj;
+    pa[q] = sL + blk_id(bi, KQ) * SBLK + (ti * 8 + fr) * LB + fk;
+    pb[q] = sL + blk_id(bj, KQ) * SBLK + (tj * 8 + fr) * LB + fk;
+    pd[q] = reinterpret_cast<double2*>(sL + blk_id(bi, bj) * SBLK + (ti * 8 + fr) * LB + tj * 8 + 2 * fk);
+    c0[q] = 0.0; c1[q] = 0.0;
+  }
+#pragma unroll
+  for (int ks = 0; ks < SB / 4; ++ks) {
+#pragma unroll
+    for (int q = 0; q < T; ++q) dmma884(c0[q], c1[q], pa[q][ks * 4], pb[q][ks * 4]);
+  }
+#pragma unroll
+  for (int q = 0; q < T; ++q) {
+    double2 v = *pd[q];
+    v.x -= c0[q]; v.y -= c1[q];
+    *pd[q] = v;
+  }
+}
+
+// Sub-diagonal D of the inverse: X(i,j) = - sum_{k=j}^{i-1} M(i,k) X(k,j), j = i - D.  X(j,j) comes from shared
+// memory, the X(k,j) of earlier sub-diagonals from the output block itself (L2).  The warp's T = 6 / 4 / 2
+// tiles advance together; the global fragments of a product are all fetched before its multiply-adds.
+template <int D>
+__device__ __forceinline__ void inv_level(const double* sL, double* Linv, int warp, int lane) {
+  constexpr int T = 2 * (4 - D);
+  const int fr = lane >> 2, fk = lane & 3;
+  double c0[T], c1[T];
+#pragma unroll
+  for (int q = 0; q < T; ++q) { c0[q] = 0.0; c1[q] = 0.0; }
+#pragma unroll
+  for (int ks = 0; ks < SB / 4; ++ks) {
+#pragma unroll
+    for (int q = 0; q < T; ++q) {
+      const int t = warp + 8 * q, b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
+      const int i = D + b, j = b;
+      dmma884(c0[q], c1[q], sL[blk_id(i, j) * SBLK + (ti * 8 + fr) * LB + ks * 4 + fk],
+              sL[blk_id(j, j) * SBLK + (ks * 4 + fk) * LB + tj * 8 + fr]);
+    }
+  }
+#pragma unroll
+  for (int kk = 1; kk < D; ++kk) {
+    double bq[T][SB / 4];
+#pragma unroll
+    for (int q = 0; q < T; ++q) {
+      const int t = warp + 8 * q, b = t >> 4, tile = t & 15, tj = tile & 3;
+      const int j = b, k = j + kk;
+#pragma unroll
+      for (int ks = 0; ks < SB / 4; ++ks) bq[q][ks] = __ldcg(Linv + (size_t)(k * SB + ks * 4 + fk) * NB + j * SB + tj * 8 + fr);
+    }
+#pragma unroll
+    for (int ks = 0; ks < SB / 4; ++ks) {
+#pragma unroll
+      for (int q = 0; q < T; ++q) {
+        const int t = warp + 8 * q, b = t >> 4, tile = t & 15, ti = tile >> 2;
+        const int i = D + b, k = b + kk;
+        dmma884(c0[q], c1[q], sL[blk_id(i, k) * SBLK + (ti * 8 + fr) * LB + ks * 4 + fk], bq[q][ks]);
+      }
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < T; ++q) {
+    const int t = warp + 8 * q, b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
+    const int i = D + b, j = b;
+    *reinterpret_cast<double2*>(Linv + (size_t)(i * SB + ti * 8 + fr) * NB + j * SB + tj * 8 + 2 * fk) = make_double2(-c0[q], -c1[q]);
+  }
+}
+
 // 10 sub-blocks + 1/diag + pivot-column scratch: 94 KB, so that (with <= 128 registers per thread) the kernel
 // fits on an SM NEXT TO a resident trailing-update CTA and never has to wait for a whole SM to drain.
 constexpr int kDiagSmem = (10 * SBLK + NB + 2 * SB) * (int)sizeof(double) + 16;
@@ -174,21 +254,33 @@ __global__ void __launch_bounds__(256, 2) chol_diag_kernel(double* __restrict__ 
   const int failed = *fail;
   if (tid == 0) *sBad = 0;
   DIAG_TICK(0);
-  // load the lower sub-blocks (identity beyond kb; strict upper of the diagonal sub-blocks zero)
-  for (int e = tid; e < 10 * SB * (SB / 2); e += 256) {
-    const int blk = e / (SB * (SB / 2)), rem = e - blk * (SB * (SB / 2));
-    const int r = rem / (SB / 2), c = (rem - r * (SB / 2)) * 2;
-    int bi = 0;
-    while (blk_id(bi + 1, 0) <= blk) ++bi;
-    const int bj = blk - blk_id(bi, 0);
-    const int i = bi * SB + r, j = bj * SB + c;
-    double2 v = make_double2(0.0, 0.0);
-    if (i < kb && j + 1 < kb) v = *reinterpret_cast<const double2*>(A + (size_t)(k0 + i) * n + k0 + j);
-    else if (i < kb && j < kb) v.x = A[(size_t)(k0 + i) * n + k0 + j];
-    if (j > i) v.x = 0.0;
-    if (j + 1 > i) v.y = 0.0;
-    if (i >= kb) { v.x = (i == j) ? 1.0 : 0.0; v.y = (i == j + 1) ? 1.0 : 0.0; }
-    *reinterpret_cast<double2*>(sL + blk * SBLK + r * LB + c) = v;
+  // load the lower sub-blocks (identity beyond kb; strict upper of the diagonal sub-blocks zero).  Element
+  // e = tid + 256 it lies in sub-block it >> 1: the block decode is a compile-time constant of the unrolled
+  // loop and the twenty 16-byte loads of a thread are all in flight before the first store.
+  {
+    double2 v[20];
+#pragma unroll
+    for (int it = 0; it < 20; ++it) {
+      const int blk = it >> 1, rem = tid + 256 * (it & 1);
+      const int bi = blk < 1 ? 0 : blk < 3 ? 1 : blk < 6 ? 2 : 3, bj = blk - blk_id(bi, 0);
+      const int r = rem / (SB / 2), c = (rem - r * (SB / 2)) * 2;
+      const int i = bi * SB + r, j = bj * SB + c;
+      v[it] = make_double2(0.0, 0.0);
+      if (i < kb && j + 1 < kb) v[it] = *reinterpret_cast<const double2*>(A + (size_t)(k0 + i) * n + k0 + j);
+      else if (i < kb && j < kb) v[it].x = A[(size_t)(k0 + i) * n + k0 + j];
+    }
+#pragma unroll
+    for (int it = 0; it < 20; ++it) {
+      const int blk = it >> 1, rem = tid + 256 * (it & 1);
+      const int bi = blk < 1 ? 0 : blk < 3 ? 1 : blk < 6 ? 2 : 3, bj = blk - blk_id(bi, 0);
+      const int r = rem / (SB / 2), c = (rem - r * (SB / 2)) * 2;
+      const int i = bi * SB + r, j = bj * SB + c;
+      double2 w = v[it];
+      if (j > i) w.x = 0.0;
+      if (j + 1 > i) w.y = 0.0;
+      if (i >= kb) { w.x = (i == j) ? 1.0 : 0.0; w.y = (i == j + 1) ? 1.0 : 0.0; }
+      *reinterpret_cast<double2*>(sL + blk * SBLK + r * LB + c) = w;
+    }
   }
   __syncthreads();
   if (failed) return;
@@ -229,24 +321,11 @@ __global__ void __launch_bounds__(256, 2) chol_diag_kernel(double* __restrict__ 
       }
     }
     __syncthreads();
-    // (c) trailing update: L(bi,bj) -= L(bi,kq) L(bj,kq)^T for kq < bj <= bi, 16 tiles of 8x8 per sub-block
-    {
-      const int m = 3 - kq, ntiles = m * (m + 1) / 2 * 16;
-      for (int t = warp; t < ntiles; t += 8) {
-        const int b = t >> 4, tile = t & 15;
-        int di = 0;
-        while ((di + 1) * (di + 2) / 2 <= b) ++di;
-        const int dj = b - di * (di + 1) / 2;
-        const int bi = kq + 1 + di, bj = kq + 1 + dj;
-        const int ti = tile >> 2, tj = tile & 3;
-        double c0 = 0.0, c1 = 0.0;
-        tile_mma32<false>(c0, c1, sL + blk_id(bi, kq) * SBLK, sL + blk_id(bj, kq) * SBLK, ti, tj, lane);
-        double2* dst = reinterpret_cast<double2*>(sL + blk_id(bi, bj) * SBLK + (ti * 8 + (lane >> 2)) * LB + tj * 8 + 2 * (lane & 3));
-        double2 v = *dst;
-        v.x -= c0; v.y -= c1;
-        *dst = v;
-      }
-    }
+    // (c) trailing update: L(bi,bj) -= L(bi,kq) L(bj,kq)^T for kq < bj <= bi, 16 tiles of 8x8 per sub-block;
+    //     a warp's tiles (12, 6 or 2) advance together through the eight k-steps, so their DMMA chains overlap
+    if (kq == 0) diag_trailing<0>(sL, warp, lane);
+    else if (kq == 1) diag_trailing<1>(sL, warp, lane);
+    else diag_trailing<2>(sL, warp, lane);
     __syncthreads();
   }
   DIAG_TICK(2);
@@ -303,27 +382,11 @@ __global__ void __launch_bounds__(256, 2) chol_diag_kernel(double* __restrict__ 
   }
   // (3) sub-diagonal d: X(i,j) = - sum_{k=j}^{i-1} M(i,k) X(k,j), j = i - d.  X(j,j) comes from shared memory, the
   //     X(k,j) of earlier sub-diagonals from the output block itself (L2).
-#pragma unroll 1
-  for (int d = 1; d < 4; ++d) {
-    const int nb = 4 - d;
-    for (int t = warp; t < nb * 16; t += 8) {
-      const int b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
-      const int i = d + b, j = b;
-      const int fr = lane >> 2, fk = lane & 3;
-      double c0 = 0.0, c1 = 0.0;
-      tile_mma32<true>(c0, c1, sL + blk_id(i, j) * SBLK, sL + blk_id(j, j) * SBLK, ti, tj, lane);
-      for (int k = j + 1; k < i; ++k) {
-        double bq[SB / 4];
-#pragma unroll
-        for (int ks = 0; ks < SB / 4; ++ks) bq[ks] = __ldcg(Linv + (size_t)(k * SB + ks * 4 + fk) * NB + j * SB + tj * 8 + fr);
-        const double* Mik = sL + blk_id(i, k) * SBLK;
-#pragma unroll
-        for (int ks = 0; ks < SB / 4; ++ks) dmma884(c0, c1, Mik[(ti * 8 + fr) * LB + ks * 4 + fk], bq[ks]);
-      }
-      *reinterpret_cast<double2*>(Linv + (size_t)(i * SB + ti * 8 + fr) * NB + j * SB + tj * 8 + 2 * fk) = make_double2(-c0, -c1);
-    }
-    __syncthreads();
-  }
+  inv_level<1>(sL, Linv, warp, lane);
+  __syncthreads();
+  inv_level<2>(sL, Linv, warp, lane);
+  __syncthreads();
+  inv_level<3>(sL, Linv, warp, lane);
   DIAG_TICK(6);
 }
 
