@@ -600,6 +600,70 @@ __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ 
   cp_async_wait<0>();
 }
 
+// Latency variant of the trailing update for the envelope factorisation's critical path: the update of the
+// NEXT panel's column (128 columns of block rb_list[0]) against every active row block.  One 128x64 tile per
+// CTA would put 8.4 us of DMMA issue on a single SM; here a CTA takes a 64x64 tile (four warps of 32x32), the
+// whole K = 128 of both operands arrives in shared memory with ONE cp.async burst, and 4 x cnt CTAs spread over
+// the GPU: ~2 us of tensor work per SM.
+constexpr int LT = 64;             // tile edge
+constexpr int LT_LD = NB + 4;      // operand row stride in shared memory (doubles)
+constexpr int kSyrkLatSmem = 2 * LT * LT_LD * (int)sizeof(double);
+__global__ void __launch_bounds__(128) chol_syrk_col_kernel(double* __restrict__ S, int n, int k0, const int* __restrict__ rb_list,
+                                                            const int* __restrict__ fail) {
+  extern __shared__ __align__(16) double lsm[];
+  double (*sA)[LT_LD] = reinterpret_cast<double (*)[LT_LD]>(lsm);
+  double (*sB)[LT_LD] = reinterpret_cast<double (*)[LT_LD]>(lsm + LT * LT_LD);
+  const int a = blockIdx.x >> 2, rh = (blockIdx.x >> 1) & 1, ch = blockIdx.x & 1;
+  if (a == 0 && ch > rh) return;  // strictly upper part of the diagonal block
+  const int ri = __ldg(rb_list + a) * NB + rh * LT, rj = __ldg(rb_list) * NB + ch * LT;
+  const int ni = min(LT, n - ri), nj = min(LT, n - rj);
+  if (ni <= 0 || nj <= 0 || *fail) return;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, fr = lane >> 2, fk = lane & 3;
+  for (int e = tid; e < LT * (NB / 2); e += 128) {
+    const int row = e >> 6, c2 = (e & 63) * 2;
+    if (row < ni) cp_async16(&sA[row][c2], S + (size_t)(ri + row) * n + k0 + c2);
+    else { sA[row][c2] = 0.0; sA[row][c2 + 1] = 0.0; }
+    if (row < nj) cp_async16(&sB[row][c2], S + (size_t)(rj + row) * n + k0 + c2);
+    else { sB[row][c2] = 0.0; sB[row][c2 + 1] = 0.0; }
+  }
+  cp_async_commit();
+  const int wr = warp >> 1, wc = warp & 1;  // 2 x 2 warps of 32 x 32
+  double acc[4][4][2];
+  double* const crow = S + (size_t)(ri + wr * 32 + fr) * n + rj + wc * 32 + 2 * fk;
+#pragma unroll
+  for (int p = 0; p < 4; ++p)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      acc[p][q][0] = 0.0; acc[p][q][1] = 0.0;
+      const int row = wr * 32 + p * 8 + fr, col = wc * 32 + q * 8 + 2 * fk;
+      if (row < ni && col < nj) {
+        const double2 c = *reinterpret_cast<const double2*>(crow + (size_t)p * 8 * n + q * 8);
+        acc[p][q][0] = c.x; acc[p][q][1] = c.y;
+      }
+    }
+  cp_async_wait<0>();
+  __syncthreads();
+#pragma unroll 4
+  for (int ks = 0; ks < NB / 4; ++ks) {
+    double af[4], bf[4];
+#pragma unroll
+    for (int p = 0; p < 4; ++p) af[p] = -sA[wr * 32 + p * 8 + fr][ks * 4 + fk];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) bf[q] = sB[wc * 32 + q * 8 + fr][ks * 4 + fk];
+#pragma unroll
+    for (int p = 0; p < 4; ++p)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) dmma884(acc[p][q][0], acc[p][q][1], af[p], bf[q]);
+  }
+#pragma unroll
+  for (int p = 0; p < 4; ++p)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int row = wr * 32 + p * 8 + fr, col = wc * 32 + q * 8 + 2 * fk;
+      if (row < ni && col < nj) *reinterpret_cast<double2*>(crow + (size_t)p * 8 * n + q * 8) = make_double2(acc[p][q][0], acc[p][q][1]);
+    }
+}
+
 // Panel solve  L21 = A21 L11^-T  as a product with the stored inverse, IN PLACE: every CTA owns a strip of
 // rows (all 128 columns), stages the strip in shared memory and writes the result over it.  The B fragments
 // (rows of L11^-1, 128 KB shared by every CTA, L2-resident) are read straight from global memory four k-steps
@@ -1106,7 +1170,7 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
     // updates up to step K-2, which the chain waited for one step ago
     if (la && rest_pending) { cudaStreamWaitEvent(s2, aux->ev_rest, 0); rest_pending = false; }
     if (has_col) {
-      chol_syrk_kernel<<<min(2 * cnt, 2 * n_sm), 128, kGemmSmem, s2>>>(S, n, k0, 0, 0, 2 * cnt, 0, fail_flag, list);
+      chol_syrk_col_kernel<<<4 * cnt, 128, kSyrkLatSmem, s2>>>(S, n, k0, list, fail_flag);
       ++*launches;
     }
     if (rest_cnt > 0) {
@@ -1129,6 +1193,7 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
     cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDiagSmem);
     cudaFuncSetAttribute(chol_trsm_strip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_MAXROWS * TS_LD * (int)sizeof(double));
     cudaFuncSetAttribute(chol_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem);
+    cudaFuncSetAttribute(chol_syrk_col_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrkLatSmem);
     attr_set = true;
   }
   static int n_sm = 0;
