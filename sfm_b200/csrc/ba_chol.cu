@@ -897,47 +897,62 @@ __device__ __forceinline__ int ld_acquire(const int* p) {
 __device__ __forceinline__ void st_release(int* p, int v) { asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
-// y[r] = sum_c M[r][c] v[c] for a 128x128 block (row stride ld): thread t owns row t>>1, columns
-// (t&1)*64 .. +63 — 32 independent 16-byte loads in flight per thread, one shuffle to join the halves.
-// Rows >= nrows read as zero.  Result valid on even threads.
-__device__ __forceinline__ double block_row_dot(const double* __restrict__ M, size_t ld, int nrows, const double* __restrict__ sv, int tid) {
+// Block mat-vec pieces of the triangular solves, split into "fetch the matrix block into registers" and "multiply
+// with the vector", so that the fetch is issued BEFORE the CTA waits for the flag of the vector's producer: when
+// the flag arrives only the vector load and a short multiply-add tree are left on the critical path.
+// Row form: thread t owns row t>>1, columns (t&1)*64 .. +63 (32 x 16-byte loads).  Rows >= nrows read as zero.
+struct RowFrag { double2 v[32]; };
+__device__ __forceinline__ void row_fetch(RowFrag& f, const double* __restrict__ M, size_t ld, int nrows, int tid) {
   const int r = tid >> 1, h = tid & 1;
-  double2 v[32];
   const double2* p = reinterpret_cast<const double2*>(M + (size_t)r * ld + h * 64);
 #pragma unroll
-  for (int q = 0; q < 32; ++q) v[q] = (r < nrows) ? __ldg(p + q) : make_double2(0.0, 0.0);
-  double a0 = 0.0, a1 = 0.0;
+  for (int q = 0; q < 32; ++q) f.v[q] = (r < nrows) ? __ldg(p + q) : make_double2(0.0, 0.0);
+}
+__device__ __forceinline__ double row_dot(const RowFrag& f, const double* __restrict__ sv, int tid) {  // valid on even threads
+  const int h = tid & 1;
+  double a[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
 #pragma unroll
   for (int q = 0; q < 32; ++q) {
-    a0 = fma(v[q].x, sv[h * 64 + 2 * q], a0);
-    a1 = fma(v[q].y, sv[h * 64 + 2 * q + 1], a1);
+    a[(2 * q) & 7] = fma(f.v[q].x, sv[h * 64 + 2 * q], a[(2 * q) & 7]);
+    a[(2 * q + 1) & 7] = fma(f.v[q].y, sv[h * 64 + 2 * q + 1], a[(2 * q + 1) & 7]);
   }
-  double a = a0 + a1;
-  a += __shfl_xor_sync(0xffffffffu, a, 1);
-  return a;
+  double s = ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
+  s += __shfl_xor_sync(0xffffffffu, s, 1);
+  return s;
 }
-// x[c] = sum_r M[r][c] v[r]: thread t owns column t&127, rows (t>>7)*64 .. +63, 64 loads in flight.
-// Returns the partial sum of this thread's half.
-__device__ __forceinline__ double block_col_dot(const double* __restrict__ M, size_t ld, int nrows, int ncols, const double* __restrict__ sv, int tid,
-                                                bool lower_only) {
+// Column form: thread t owns column t&127, rows (t>>7)*64 .. +63.
+struct ColFrag { double v[64]; };
+__device__ __forceinline__ void col_fetch(ColFrag& f, const double* __restrict__ M, size_t ld, int nrows, int ncols, int tid) {
   const int c = tid & (NB - 1), r0 = (tid >> 7) * 64;
-  double v[64];
 #pragma unroll
   for (int q = 0; q < 64; ++q) {
     const int r = r0 + q;
-    v[q] = (r < nrows && c < ncols && (!lower_only || r >= c)) ? __ldg(M + (size_t)r * ld + c) : 0.0;
+    f.v[q] = (r < nrows && c < ncols) ? __ldg(M + (size_t)r * ld + c) : 0.0;
   }
-  double a0 = 0.0, a1 = 0.0;
+}
+__device__ __forceinline__ double col_dot(const ColFrag& f, const double* __restrict__ sv, int tid) {  // partial sum of this half
+  const int r0 = (tid >> 7) * 64;
+  double a[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
 #pragma unroll
-  for (int q = 0; q < 64; q += 2) {
-    a0 = fma(v[q], sv[r0 + q], a0);
-    a1 = fma(v[q + 1], sv[r0 + q + 1], a1);
+  for (int q = 0; q < 64; ++q) a[q & 7] = fma(f.v[q], sv[r0 + q], a[q & 7]);
+  return ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
+}
+
+// L11^-1 block in shared memory (row stride 130 doubles: the 16 rows a warp reads together fall in distinct
+// 16-byte bank groups), fetched with cp.async while the off-diagonal blocks are folded in.
+constexpr int TI_LD = NB + 2;
+constexpr int kTrsvSmem = NB * TI_LD * (int)sizeof(double);
+__device__ __forceinline__ void inv_stage(double* sInv, const double* __restrict__ Linv, int tid) {
+  for (int e = tid; e < NB * (NB / 2); e += 256) {
+    const int row = e >> 6, c2 = (e & 63) * 2;
+    cp_async16(sInv + row * TI_LD + c2, Linv + row * NB + c2);
   }
-  return a0 + a1;
+  cp_async_commit();
 }
 
 __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict__ L, int n, const double* __restrict__ LinvAll, double* b,
                                                         double* w, int* flag_fwd, int* flag_bwd, const int* __restrict__ fb) {
+  extern __shared__ __align__(16) double sInv[];  // [128][TI_LD]
   __shared__ double sv[NB];    // vector of the block being folded in (y_k / x_i)
   __shared__ double sacc[NB];  // running right-hand side of the owned block
   __shared__ double sp[NB];
@@ -946,30 +961,36 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
   // ---- forward ----
   for (int i = blockIdx.x; i < P; i += G) {
     const int r0 = i * NB, nr = min(NB, n - r0);
+    __syncthreads();
+    inv_stage(sInv, LinvAll + (size_t)i * NB * NB, tid);
     if (tid < NB) sacc[tid] = (tid < nr) ? b[r0 + tid] : 0.0;
-    for (int e = tid; e < NB * 8; e += 256) {  // the two blocks on the dependency chain: L11^-1 and block (i, i-1)
-      const int row = e >> 3;
-      prefetch_l2(LinvAll + (size_t)i * NB * NB + row * NB + (e & 7) * 16);
-      if (i > 0 && row < nr) prefetch_l2(L + (size_t)(r0 + row) * n + (i - 1) * NB + (e & 7) * 16);
-    }
     for (int k = fb ? __ldg(fb + i) : 0; k < i; ++k) {  // blocks left of the envelope are exactly zero
-      if (k + 2 < i) {  // pull block (i, k+2) towards L2: 128 rows x 1 KB = 8 lines per row
-        for (int e = tid; e < NB * 8; e += 256) {
-          const int row = e >> 3;
-          if (row < nr) prefetch_l2(L + (size_t)(r0 + row) * n + (k + 2) * NB + (e & 7) * 16);
-        }
-      }
+      RowFrag f;
+      row_fetch(f, L + (size_t)r0 * n + (size_t)k * NB, (size_t)n, nr, tid);
       if (tid == 0) { while (ld_acquire(flag_fwd + k) == 0) { } }
       __syncthreads();
       if (tid < NB) sv[tid] = __ldcg(w + k * NB + tid);
       __syncthreads();
-      const double d = block_row_dot(L + (size_t)r0 * n + (size_t)k * NB, (size_t)n, nr, sv, tid);
+      const double d = row_dot(f, sv, tid);
       if (!(tid & 1)) sacc[tid >> 1] -= d;
-      __syncthreads();
     }
+    cp_async_wait<0>();
     __syncthreads();
-    const double y = block_row_dot(LinvAll + (size_t)i * NB * NB, NB, NB, sacc, tid);
-    if (!(tid & 1) && (tid >> 1) < nr) w[r0 + (tid >> 1)] = y;
+    {
+      // y = L11^-1 acc from shared memory: thread t owns row t>>1, half t&1
+      const int r = tid >> 1, h = tid & 1;
+      const double* row = sInv + r * TI_LD + h * 64;
+      double a[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+      for (int q = 0; q < 32; ++q) {
+        const double2 m = *reinterpret_cast<const double2*>(row + 2 * q);
+        a[(2 * q) & 3] = fma(m.x, sacc[h * 64 + 2 * q], a[(2 * q) & 3]);
+        a[(2 * q + 1) & 3] = fma(m.y, sacc[h * 64 + 2 * q + 1], a[(2 * q + 1) & 3]);
+      }
+      double y = (a[0] + a[1]) + (a[2] + a[3]);
+      y += __shfl_xor_sync(0xffffffffu, y, 1);
+      if (!h && r < nr) w[r0 + r] = y;
+    }
     __syncthreads();
     if (tid == 0) { __threadfence(); st_release(flag_fwd + i, 1); }
   }
@@ -977,39 +998,42 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
   const int j = tid & (NB - 1), half = tid >> 7;
   for (int kk = P - 1 - (int)blockIdx.x; kk >= 0; kk -= G) {
     const int c0 = kk * NB, kb = min(NB, n - c0);
-    for (int e = tid; e < NB * 8; e += 256) {
-      const int row = e >> 3;
-      prefetch_l2(LinvAll + (size_t)kk * NB * NB + row * NB + (e & 7) * 16);
-      if (kk + 1 < P && (kk + 1) * NB + row < n) prefetch_l2(L + (size_t)((kk + 1) * NB + row) * n + c0 + (e & 7) * 16);
-    }
+    __syncthreads();
+    inv_stage(sInv, LinvAll + (size_t)kk * NB * NB, tid);
     if (tid == 0) { while (ld_acquire(flag_fwd + kk) == 0) { } }
     __syncthreads();
     if (tid < NB) sacc[tid] = (tid < kb) ? __ldcg(w + c0 + tid) : 0.0;
     for (int i = P - 1; i > kk; --i) {
       if (fb && __ldg(fb + i) > kk) continue;  // block (i, kk) lies outside the envelope
       const int r0 = i * NB, nr = min(NB, n - r0);
-      if (i - 2 > kk) {
-        for (int e = tid; e < NB * 8; e += 256) {
-          const int row = e >> 3;
-          prefetch_l2(L + (size_t)((i - 2) * NB + row) * n + c0 + (e & 7) * 16);
-        }
-      }
+      ColFrag f;
+      col_fetch(f, L + (size_t)r0 * n + c0, (size_t)n, nr, kb, tid);
       if (tid == 0) { while (ld_acquire(flag_bwd + i) == 0) { } }
       __syncthreads();
       if (tid < NB) sv[tid] = (tid < nr) ? __ldcg(b + r0 + tid) : 0.0;
       __syncthreads();
-      const double acc = block_col_dot(L + (size_t)r0 * n + c0, (size_t)n, nr, kb, sv, tid, false);
+      const double acc = col_dot(f, sv, tid);
       if (half) sp[j] = acc;
       __syncthreads();
       if (!half) sacc[j] -= acc + sp[j];
-      __syncthreads();
     }
-    // x_k = L11^-T acc : x[j] = sum_{i >= j} Linv[i][j] acc[i]
+    cp_async_wait<0>();
     __syncthreads();
-    const double acc = block_col_dot(LinvAll + (size_t)kk * NB * NB, NB, NB, NB, sacc, tid, true);
-    if (half) sp[j] = acc;
-    __syncthreads();
-    if (!half && j < kb) b[c0 + j] = acc + sp[j];
+    {
+      // x_k = L11^-T acc : x[j] = sum_{i >= j} Linv[i][j] acc[i]  (column j of the staged block, this half's rows)
+      const int r0h = half * 64;
+      double a[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+      for (int q = 0; q < 64; ++q) {
+        const int r = r0h + q;
+        const double m = (r >= j) ? sInv[r * TI_LD + j] : 0.0;
+        a[q & 3] = fma(m, sacc[r], a[q & 3]);
+      }
+      const double acc = (a[0] + a[1]) + (a[2] + a[3]);
+      if (half) sp[j] = acc;
+      __syncthreads();
+      if (!half && j < kb) b[c0 + j] = acc + sp[j];
+    }
     __syncthreads();
     if (tid == 0) { __threadfence(); st_release(flag_bwd + kk, 1); }
   }
@@ -1281,7 +1305,9 @@ void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream
     const int* env = (plan && plan->use && plan->n == n) ? plan->d_fb : nullptr;
     void* args[] = {(void*)&L, (void*)&nn, (void*)&LinvAll, (void*)&b, (void*)&w, (void*)&ff, (void*)&fb, (void*)&env};
     const int grid = std::min(panels, n_sm);
-    if (cudaLaunchCooperativeKernel((const void*)trsv_coop_kernel, dim3(grid), dim3(256), args, 0, s) == cudaSuccess) {
+    static bool attr_set = false;
+    if (!attr_set) { cudaFuncSetAttribute(trsv_coop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTrsvSmem); attr_set = true; }
+    if (cudaLaunchCooperativeKernel((const void*)trsv_coop_kernel, dim3(grid), dim3(256), args, kTrsvSmem, s) == cudaSuccess) {
       ++*launches;
       return;
     }
