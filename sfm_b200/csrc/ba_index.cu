@@ -16,16 +16,19 @@ void Problem::release() {
   // keep what outlives a problem: the arena, the dense matrix, the pinned scalar mirrors
   char* a = arena; const size_t cap = arena_cap;
   double* s_keep = S; const size_t s_cap = S_capacity;
+  unsigned* pl_keep = pair_list; const size_t pl_cap = pair_capacity;
   double* sh = scal_host; int* fh = flags_host;
   *this = Problem();
   arena = a; arena_cap = cap; arena_off = 0;
   S = s_keep; S_capacity = s_cap;
+  pair_list = pl_keep; pair_capacity = pl_cap;
   scal_host = sh; flags_host = fh;
 }
 
 void Problem::destroy() {
   if (arena) cudaFree(arena);
   if (S) cudaFree(S);
+  if (pair_list) cudaFree(pair_list);
   if (scal_host) cudaFreeHost(scal_host);
   if (flags_host) cudaFreeHost(flags_host);
   *this = Problem();
@@ -323,6 +326,28 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   if (!tiles.empty()) HSFM_CUDA(cudaMemcpyAsync(tile_start, tiles.data(), sizeof(int) * tiles.size(), cudaMemcpyHostToDevice, s));
   // distinct cameras of every tile + each observation's slot in that list: the streaming kernels stage the
   // tile's camera rows / camera vectors in shared memory once instead of gathering them per observation
+  // per-tile offsets into the (lazily built) sorted pair lists of dense_schur: sum over the tile's points of L(L+1)/2
+  int* pair_off = nullptr;
+  {
+    std::vector<int> po((size_t)P.n_tiles + 1, 0);
+    long long acc = 0;
+    for (int k = 0; k < P.n_tiles; ++k) {
+      po[k] = (int)acc;
+      for (int p = tile_p[k]; p < tile_p[k + 1]; ++p) {
+        const long long L = h_pt_start[p + 1] - h_pt_start[p];
+        acc += L * (L + 1) / 2;
+      }
+      if (acc >= (1ll << 31)) break;
+    }
+    P.total_pairs = acc;
+    P.pairs_ready = false;
+    if (acc < (1ll << 31) && P.n_tiles > 0) {
+      po[P.n_tiles] = (int)acc;
+      ALLOC(pair_off, (size_t)P.n_tiles + 1);
+      HSFM_CUDA(cudaMemcpyAsync(pair_off, po.data(), sizeof(int) * po.size(), cudaMemcpyHostToDevice, s));
+      HSFM_CUDA(cudaStreamSynchronize(s));
+    }
+  }
   unsigned char* slot; int *tile_cams, *tile_hdr, *d_max_ncam;
   ALLOC(slot, n); ALLOC(tile_cams, (size_t)P.n_tiles * TILE); ALLOC(tile_hdr, 8 * (size_t)std::max(1, P.n_tiles)); ALLOC(d_max_ncam, 1);
   P.max_tile_cams = 0;
@@ -400,6 +425,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   d.n_obs = n; d.n_cams = n_cams; d.n_pts = n_pts; d.n_tiles = P.n_tiles; d.n_chunks = P.n_chunks;
   d.obs = obs; d.cam = cam; d.pt = pt; d.pt_start = pt_start; d.tile_start = tile_start;
   d.tile_cams = tile_cams; d.tile_hdr = reinterpret_cast<const int4*>(tile_hdr); d.slot = slot;
+  d.pair_off = pair_off; d.pair_list = nullptr;
   d.obs_cs = obs_cs; d.pt_cs = pt_cs; d.pos_cs = pos_cs; d.chunk_cam = d_ch_cam; d.chunk_b = d_ch_b; d.chunk_e = d_ch_e; d.cam_chunk_start = d_cam_ch_start;
   d.r = r; d.Jc = Jc; d.Jp = Jp;
   HSFM_CUDA(cudaStreamSynchronize(s));

@@ -35,6 +35,9 @@ struct Dev {
                          // 32-byte record so that a CTA learns everything about its tile in a single memory round trip
   const int* tile_cams;  // [n_tiles][TILE] distinct cameras of each tile, ascending (first hdr.ncam entries valid)
   const unsigned char* slot;  // [n_obs] position of the observation's camera in its tile's list
+  const int* pair_off;        // [n_tiles+1] first entry of each tile in pair_list (null: more than 2^31 pairs)
+  const unsigned* pair_list;  // per tile: the (i,j) observation pairs of its points SORTED by destination block of S,
+                              // (slot_i << 24 | slot_j << 16 | i << 8 | j); built lazily by the first dense solve
   // static, camera-major order
   const double2* obs_cs; // [n_obs]
   const int* pt_cs;      // [n_obs]
@@ -91,6 +94,10 @@ struct Problem {
   double *pcg_x = nullptr, *pcg_r = nullptr, *pcg_z = nullptr, *pcg_p = nullptr, *pcg_q = nullptr;
   double *S = nullptr;                              // dense reduced camera matrix (lazily allocated)
   size_t S_capacity = 0;
+  unsigned* pair_list = nullptr;                    // sorted pair lists of dense_schur (lazily built, persists like S)
+  size_t pair_capacity = 0;
+  long long total_pairs = 0;
+  bool pairs_ready = false;
   // scalar plumbing
   double *part = nullptr;    // [PART_SLOTS][part_stride] per-block partial sums
   int part_stride = 0;

@@ -21,6 +21,11 @@ namespace {
 
 constexpr unsigned FULL = 0xffffffffu;
 
+// D(8x8) += A(8x4) * B(4x8), FP64 tensor core.  Lane l holds A[l>>2][l&3], B[l&3][l>>2], D[l>>2][2(l&3) .. +1].
+__device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+
 __device__ __forceinline__ CamRow load_row(const CamRow* rows, int c) {
   CamRow C;
   const double2* src = reinterpret_cast<const double2*>(rows + c);
@@ -803,7 +808,8 @@ __global__ void dense_init_kernel(int n_cams, const double* __restrict__ Hcc, co
 // 6-double rows of a 6x6 block (48 contiguous bytes) instead of 32 unrelated addresses — measured 2.2-2.8x
 // the FP64 atomic rate of the one-thread-per-block scatter (scripts/micro/fp64_peaks.cu).  Observations of a
 // point are stored with ascending camera (ba_index.cu), so pair (i,j), j <= i, lands in the lower triangle.
-constexpr int kDenseSchurSmem = TILE * 36 * (int)sizeof(double) + (3 * TILE + 8) * (int)sizeof(int);
+constexpr int kDenseSchurSmem = TILE * 36 * (int)sizeof(double) + (3 * TILE + 8) * (int)sizeof(int) + 8 * 8 * 36 * (int)sizeof(double) + 8 * 8 * (int)sizeof(long long);
+template <bool SORTED>
 __global__ void __launch_bounds__(TILE) dense_schur_kernel(Dev d, const double* __restrict__ Hpp_inv, double* __restrict__ S) {
   extern __shared__ __align__(16) unsigned char ds_raw[];
   double (*sA)[18] = reinterpret_cast<double (*)[18]>(ds_raw);
@@ -839,30 +845,113 @@ __global__ void __launch_bounds__(TILE) dense_schur_kernel(Dev d, const double* 
     }
     sCam[threadIdx.x] = __ldg(d.cam + t.i);
   }
-  // pairs owned by observation i: (i, j) for j = segment start .. i  →  exclusive scan over the tile
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int cnt = t.valid ? (t.i - t.seg_b + 1) : 0;
-  int incl = cnt;
+  int total_pairs = 0;
+  if (!SORTED) {
+    // pairs owned by observation i: (i, j) for j = segment start .. i  →  exclusive scan over the tile
+    const int cnt = t.valid ? (t.i - t.seg_b + 1) : 0;
+    int incl = cnt;
 #pragma unroll
-  for (int dd = 1; dd < 32; dd <<= 1) {
-    const int up = __shfl_up_sync(FULL, incl, dd);
-    if (lane >= dd) incl += up;
-  }
-  if (lane == 31) sWarpTot[warp] = incl;
-  sSeg[threadIdx.x] = t.valid ? (t.seg_b - t.tile_b) : 0;
-  __syncthreads();
-  int warp_off = 0, total_pairs = 0;
+    for (int dd = 1; dd < 32; dd <<= 1) {
+      const int up = __shfl_up_sync(FULL, incl, dd);
+      if (lane >= dd) incl += up;
+    }
+    if (lane == 31) sWarpTot[warp] = incl;
+    sSeg[threadIdx.x] = t.valid ? (t.seg_b - t.tile_b) : 0;
+    __syncthreads();
+    int warp_off = 0;
 #pragma unroll
-  for (int w = 0; w < TILE / 32; ++w) {
-    const int v = sWarpTot[w];
-    if (w < warp) warp_off += v;
-    total_pairs += v;
+    for (int w = 0; w < TILE / 32; ++w) {
+      const int v = sWarpTot[w];
+      if (w < warp) warp_off += v;
+      total_pairs += v;
+    }
+    sOff[threadIdx.x] = warp_off + incl - cnt;
   }
-  sOff[threadIdx.x] = warp_off + incl - cnt;
   __syncthreads();
   const size_t ld = 6 * (size_t)d.n_cams;
-  // every warp takes 8 pairs (288 block elements = 9 full warp passes) at a time, round-robin over the tile:
-  // the work of a long track is spread over all warps
+  // Each 6x6 block A_i W_j^T is ONE FP64 tensor-core instruction (mma m8n8k4: rows = the six camera parameters
+  // of i, columns = those of j, k = the three point coordinates; two LDS.64 per lane instead of six per
+  // element).  The accumulator fragments go through a warp-private 8 x 36 staging buffer so that the reduction
+  // into S keeps its efficient shape: nine full-warp passes in which consecutive lanes take consecutive block
+  // elements (whole 48-byte rows per RED instruction).
+  double* sC = reinterpret_cast<double*>(sWarpTot + 8) + warp * (8 * 36);                    // [8][36] per warp
+  long long* sBase = reinterpret_cast<long long*>(reinterpret_cast<double*>(sWarpTot + 8) + 8 * 8 * 36) + warp * 8;  // [8] per warp
+  const int fr = lane >> 2, fk = lane & 3;
+  const bool frag_ok = fr < 6 && fk < 3;
+  // which pair and which element of its block this lane reduces in each of the nine passes: lane constants
+  int pass_pl[9];
+  size_t pass_off[9], pass_offT[9];
+#pragma unroll
+  for (int pass = 0; pass < 9; ++pass) {
+    const int g = pass * 32 + lane, pl = g / 36, e = g - pl * 36, a = e / 6, b = e - a * 6;
+    pass_pl[pass] = pl;
+    pass_off[pass] = (size_t)a * ld + b;
+    pass_offT[pass] = (size_t)b * ld + a;
+  }
+  // element (a, b) of the staged block goes to S[6 ci + a][6 cj + b] (ci < cj cannot happen with cameras ascending
+  // inside a point, but then the transposed element is addressed)
+  auto block_base = [&](int i, int j) -> long long {
+    const int ci = sCam[i], cj = sCam[j];
+    return (ci >= cj) ? (long long)((6 * (size_t)ci) * ld + 6 * (size_t)cj) : -1 - (long long)((6 * (size_t)cj) * ld + 6 * (size_t)ci);
+  };
+  auto reduce_staged = [&](int cnt) {
+    __syncwarp();
+#pragma unroll
+    for (int pass = 0; pass < 9; ++pass) {
+      if (pass_pl[pass] < cnt) {
+        const long long bs = sBase[pass_pl[pass]];
+        double* dst = (bs >= 0) ? S + bs + pass_off[pass] : S + (-1 - bs) + pass_offT[pass];
+        atomicAdd(dst, -sC[pass * 32 + lane]);
+      }
+    }
+    __syncwarp();
+  };
+  if (SORTED) {
+    // The tile's pairs come from the static list SORTED BY DESTINATION BLOCK (ba_index / tile_pairs_kernel): a
+    // warp walks a contiguous piece of the list and keeps accumulating into the same tensor-core fragment while
+    // the destination stays the same, so the ~2.1 pairs per distinct block of a tile cost one reduction, not 2.1.
+    const int p_off = __ldg(d.pair_off + blockIdx.x);
+    const int n_pairs = __ldg(d.pair_off + blockIdx.x + 1) - p_off;
+    const unsigned* __restrict__ list = d.pair_list + p_off;
+    const int chunk = (n_pairs + 7) >> 3;
+    const int beg = warp * chunk, end = min(n_pairs, beg + chunk);
+    int nbuf = 0, li = 0, lj = 0;
+    unsigned cur = 0x10000u;  // no destination yet
+    double c0 = 0.0, c1 = 0.0;
+    auto flush = [&]() {
+      if (frag_ok) *reinterpret_cast<double2*>(sC + nbuf * 36 + fr * 6 + 2 * fk) = make_double2(c0, c1);
+      if (lane == 0) sBase[nbuf] = block_base(li, lj);
+      if (++nbuf == 8) { reduce_staged(8); nbuf = 0; }
+    };
+    for (int base = beg; base < end; base += 32) {
+      const unsigned key = (base + lane < end) ? __ldg(list + base + lane) : 0xffffffffu;
+      const int cnt = min(32, end - base);
+#pragma unroll 4
+      for (int pl = 0; pl < cnt; ++pl) {
+        const unsigned k = __shfl_sync(FULL, key, pl);
+        const unsigned dest = k >> 16;
+        const int i = (k >> 8) & 0xff, j = k & 0xff;
+        const double a_frag = frag_ok ? sA[i][fr * 3 + fk] : 0.0;
+        const double b_frag = frag_ok ? sW[j][fr * 3 + fk] : 0.0;
+        if (dest != cur) {  // warp-uniform
+          if (cur != 0x10000u) flush();
+          cur = dest; c0 = 0.0; c1 = 0.0;
+        }
+        li = i; lj = j;
+        dmma884(c0, c1, a_frag, b_frag);
+        if (i != j && (dest >> 8) == (dest & 0xff)) {  // a camera listed twice in a track: diagonal block, M + M^T
+          const double at = frag_ok ? sW[j][fr * 3 + fk] : 0.0, bt = frag_ok ? sA[i][fr * 3 + fk] : 0.0;
+          dmma884(c0, c1, at, bt);
+        }
+      }
+    }
+    if (cur != 0x10000u) flush();
+    if (nbuf) reduce_staged(nbuf);
+    return;
+  }
+  // Unsorted fallback (no pair list): every warp takes 8 pairs (288 block elements) at a time, round-robin over the
+  // tile, so the work of a long track is spread over all warps.
   for (int base = warp * 8; base < total_pairs; base += (TILE / 32) * 8) {
     int packed = -1;
     {
@@ -876,26 +965,101 @@ __global__ void __launch_bounds__(TILE) dense_schur_kernel(Dev d, const double* 
         }
         const int i = lo, j = sSeg[i] + (q - sOff[i]);
         packed = (i << 16) | j;
+        if (lane < 8) sBase[lane] = block_base(i, j);
       }
     }
+    const int cnt = min(8, total_pairs - base);
+    // all eight pairs in flight: operand loads first, then the tensor-core products, then the staging stores
+    double af[8], bf[8];
+    bool dup[8];
 #pragma unroll
-    for (int pass = 0; pass < 9; ++pass) {
-      const int g = pass * 32 + lane;
-      const int pl = g / 36, e = g - pl * 36;
+    for (int pl = 0; pl < 8; ++pl) {
       const int ij = __shfl_sync(FULL, packed, pl);
-      if (ij < 0) continue;
-      const int i = ij >> 16, j = ij & 0xffff;
-      const int a = e / 6, b = e - a * 6;
-      const double* Ai = sA[i];
-      const double* Wj = sW[j];
-      double v = Ai[a * 3] * Wj[b * 3] + Ai[a * 3 + 1] * Wj[b * 3 + 1] + Ai[a * 3 + 2] * Wj[b * 3 + 2];
-      const int ci = sCam[i], cj = sCam[j];
-      if (ci == cj && i != j)  // a camera listed twice in a track: the block is diagonal, it needs M + M^T
-        v += Ai[b * 3] * Wj[a * 3] + Ai[b * 3 + 1] * Wj[a * 3 + 1] + Ai[b * 3 + 2] * Wj[a * 3 + 2];
-      double* dst = (ci >= cj) ? S + (6 * (size_t)ci + a) * ld + 6 * (size_t)cj + b : S + (6 * (size_t)cj + b) * ld + 6 * (size_t)ci + a;
-      atomicAdd(dst, -v);
+      const int i = (ij >> 16) & 0xff, j = ij & 0xff;  // packed = -1 past the end: any valid row, result unused
+      af[pl] = frag_ok ? sA[i][fr * 3 + fk] : 0.0;
+      bf[pl] = frag_ok ? sW[j][fr * 3 + fk] : 0.0;
+      dup[pl] = ij >= 0 && i != j && sCam[i] == sCam[j];
+    }
+#pragma unroll
+    for (int pl = 0; pl < 8; ++pl) {
+      double c0 = 0.0, c1 = 0.0;
+      dmma884(c0, c1, af[pl], bf[pl]);  // (A_i W_j^T)[fr][2 fk], [2 fk + 1]
+      if (dup[pl]) {                     // a camera listed twice in a track: the block is diagonal, it needs M + M^T
+        const int ij = __shfl_sync(FULL, packed, pl);
+        const int i = ij >> 16, j = ij & 0xffff;
+        double at = 0.0, bt = 0.0;
+        if (frag_ok) { at = sW[j][fr * 3 + fk]; bt = sA[i][fr * 3 + fk]; }
+        dmma884(c0, c1, at, bt);
+      }
+      if (frag_ok) *reinterpret_cast<double2*>(sC + pl * 36 + fr * 6 + 2 * fk) = make_double2(c0, c1);
+    }
+    reduce_staged(cnt);
+  }
+}
+
+// Static pair lists of dense_schur (one CTA per tile, once per problem): every (i, j) pair of observations of one
+// point, j <= i, keyed by its destination block (slot of camera i, slot of camera j) and sorted by that key with
+// a bitonic network in shared memory.  Tiles with more pairs than the network holds keep generation order (the
+// consumer only loses the merging of equal destinations there).
+constexpr int PAIR_SORT_CAP = 4096;
+__global__ void __launch_bounds__(TILE) tile_pairs_kernel(Dev d, unsigned* __restrict__ list) {
+  __shared__ unsigned sk[PAIR_SORT_CAP];
+  __shared__ int sOff[TILE], sSeg[TILE], sWarpTot[TILE / 32];
+  __shared__ unsigned char sSlot[TILE];
+  const TileThread t = tile_thread(d);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cnt = t.valid ? (t.i - t.seg_b + 1) : 0;
+  int incl = cnt;
+#pragma unroll
+  for (int dd = 1; dd < 32; dd <<= 1) {
+    const int up = __shfl_up_sync(FULL, incl, dd);
+    if (lane >= dd) incl += up;
+  }
+  if (lane == 31) sWarpTot[warp] = incl;
+  sSeg[threadIdx.x] = t.valid ? (t.seg_b - t.tile_b) : 0;
+  sSlot[threadIdx.x] = t.valid ? d.slot[t.i] : 0;
+  __syncthreads();
+  int warp_off = 0;
+#pragma unroll
+  for (int w = 0; w < TILE / 32; ++w)
+    if (w < warp) warp_off += sWarpTot[w];
+  sOff[threadIdx.x] = warp_off + incl - cnt;
+  __syncthreads();
+  const int p_off = d.pair_off[blockIdx.x];
+  const int total = d.pair_off[blockIdx.x + 1] - p_off;
+  const bool sorted = total <= PAIR_SORT_CAP;
+  int npow = 2;
+  while (npow < total) npow <<= 1;
+  for (int q = threadIdx.x; q < (sorted ? npow : total); q += TILE) {
+    unsigned key = 0xffffffffu;
+    if (q < total) {
+      int lo = 0, hi = TILE - 1;  // largest i with sOff[i] <= q
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (sOff[mid] <= q) lo = mid; else hi = mid - 1;
+      }
+      const int i = lo, j = sSeg[i] + (q - sOff[i]);
+      key = ((unsigned)sSlot[i] << 24) | ((unsigned)sSlot[j] << 16) | ((unsigned)i << 8) | (unsigned)j;
+    }
+    if (sorted) sk[q] = key; else list[p_off + q] = key;
+  }
+  if (!sorted) return;
+  __syncthreads();
+  for (int k = 2; k <= npow; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int e = threadIdx.x; e < npow; e += TILE) {
+        const int partner = e ^ j;
+        if (partner > e) {
+          const unsigned x = sk[e], y = sk[partner];
+          const bool up = (e & k) == 0;
+          if ((x > y) == up) { sk[e] = y; sk[partner] = x; }
+        }
+      }
+      __syncthreads();
     }
   }
+  for (int q = threadIdx.x; q < total; q += TILE) list[p_off + q] = sk[q];
 }
 
 __global__ void mirror_lower_kernel(int n, double* __restrict__ S) {
@@ -1148,10 +1312,29 @@ void launch_dense_schur(Problem& P, cudaStream_t s) {
   if (P.n_tiles == 0) return;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(dense_schur_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDenseSchurSmem);
+    cudaFuncSetAttribute(dense_schur_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDenseSchurSmem);
+    cudaFuncSetAttribute(dense_schur_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDenseSchurSmem);
     attr_set = true;
   }
-  dense_schur_kernel<<<P.n_tiles, TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S);
+  static const bool no_sort = getenv("HSFM_SCHUR_UNSORTED") != nullptr;  // experiment knob
+  if (!P.pairs_ready && P.d.pair_off && !no_sort) {
+    // first dense solve of this problem: build the destination-sorted pair lists (static, like the rest of the index)
+    const size_t need = (size_t)std::max<long long>(P.total_pairs, 1);
+    if (P.pair_capacity < need) {
+      if (P.pair_list) cudaFree(P.pair_list);
+      P.pair_list = nullptr; P.pair_capacity = 0;
+      if (cudaMalloc(&P.pair_list, sizeof(unsigned) * need) == cudaSuccess) P.pair_capacity = need;
+      else cudaGetLastError();
+    }
+    if (P.pair_list) {
+      tile_pairs_kernel<<<P.n_tiles, TILE, 0, s>>>(P.d, P.pair_list);
+      P.launches++;
+      P.d.pair_list = P.pair_list;
+      P.pairs_ready = true;
+    }
+  }
+  if (P.pairs_ready) dense_schur_kernel<true><<<P.n_tiles, TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S);
+  else dense_schur_kernel<false><<<P.n_tiles, TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S);
   P.launches++;
 }
 
