@@ -248,15 +248,19 @@ def main():
                            pts=pin(prob.pts), cam_true=prob.cam_true, pts_true=prob.pts_true, dist=None, name=prob.name)
         h2d = hp.obs.nbytes + hp.cam_idx.nbytes + hp.pt_idx.nbytes + hp.K.nbytes + hp.cam.nbytes + hp.pts.nbytes
         d2h = hp.cam.nbytes + hp.pts.nbytes
-        ctx.solve_packed(hp, opts=opts)
-        barrier()
-        t0 = time.perf_counter()
-        e2e_its = 0
+        cam0, pts0 = prob.cam.copy(), prob.pts.copy()
+        ctx.solve_packed(hp, opts=opts, inplace=True)
+        e2e_its, e2e_s = 0, 0.0
         for _ in range(args.steps):
-            _, _, s2 = ctx.solve_packed(hp, opts=opts)
+            np.copyto(hp.cam, cam0); np.copyto(hp.pts, pts0)  # restore the initial guess in the caller's (pinned) storage: not timed
+            barrier()
+            t0 = time.perf_counter()
+            _, _, s2 = ctx.solve_packed(hp, opts=opts, inplace=True)  # H2D + index build + solve + D2H, in place like the reference
+            torch.cuda.synchronize()
+            e2e_s += time.perf_counter() - t0
             e2e_its += s2["num_iterations"]
         barrier()
-        dt = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
+        dt = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": e2e_its / float(dt.item()), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),

@@ -15,7 +15,10 @@ opts = api.default_options(linear_solver=lin)
 for rep in range(4):
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    _, _, s = ctx.solve_packed(hp, opts=opts)
+    np.copyto(hp.cam, prob.cam); np.copyto(hp.pts, prob.pts)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    _, _, s = ctx.solve_packed(hp, opts=opts, inplace=True)
     dt = (time.perf_counter() - t0) * 1e3
     print(f"{cfg} rep {rep}: wall {dt:.1f} ms | h2d {s['h2d_ms']:.1f} setup {s['setup_ms']:.1f} solve {s['solve_ms']:.1f} d2h {s['d2h_ms']:.1f} | "
           f"its {s['num_iterations']} lin {s['total_linear_iterations']} launches {s['gpu_launches']} cost {s['final_cost']:.6f} | "

@@ -173,9 +173,11 @@ class Context:
             raise BAError(rc, "hsfm_ba_comm_init")
 
     # -- one-shot calls on host buffers --
-    def solve_packed(self, prob, mode=STRUCT_AND_POSE, opts=None, trace_capacity=64):
-        """Solves a sfm_b200.synth.Problem-like object; returns (cam, pts, summary dict)."""
-        cam, pts = prob.cam.copy(), prob.pts.copy()
+    def solve_packed(self, prob, mode=STRUCT_AND_POSE, opts=None, trace_capacity=64, inplace=False):
+        """Solves a sfm_b200.synth.Problem-like object; returns (cam, pts, summary dict).  ``inplace=True`` is the
+        reference's own contract (CTracker.cpp:670-702 updates the caller's pose/point storage): prob.cam / prob.pts
+        are read as the initial guess and overwritten with the result, no copies on the Python side."""
+        cam, pts = (prob.cam, prob.pts) if inplace else (prob.cam.copy(), prob.pts.copy())
         box = _SummaryBox(trace_capacity)
         rc = self.lib.hsfm_ba_solve_packed(self.h, mode, prob.n_obs, _d(prob.obs), _i(prob.cam_idx), _i(prob.pt_idx), prob.n_cams,
                                            _d(prob.K), _d(prob.dist), _d(cam), prob.n_pts, _d(pts),

@@ -151,6 +151,12 @@ void launch_rows_to_caller(Problem& P, int w, const double* internal_order, doub
   P.launches++;
 }
 
+__global__ void validate_idx_kernel(int n, const int* __restrict__ cam, const int* __restrict__ pt, int n_cams, int n_pts,
+                                    int* __restrict__ bad) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && ((unsigned)cam[i] >= (unsigned)n_cams || (unsigned)pt[i] >= (unsigned)n_pts)) *bad = 1;
+}
+
 // cam_first[c] = smallest camera that shares a point with camera c: the envelope of S.  Internal point ids
 // are ordered by their smallest observing camera, so it is min_cam_sorted[smallest internal point id among
 // the camera's observations]; one warp per camera over the camera-major list, no atomics.
@@ -201,9 +207,8 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   const int n = (int)n_obs64, n_pts = (int)n_pts64;
   P.mode = mode; P.n_obs = n; P.n_cams = n_cams; P.n_pts = n_pts;
 
-  // ---- host-side validation of indices (the reference indexes unchecked: CTracker.cpp:676-690) ----
-  for (int i = 0; i < n; ++i)
-    if (cam_idx[i] < 0 || cam_idx[i] >= n_cams || pt_idx[i] < 0 || pt_idx[i] >= n_pts) return HSFM_BA_ERR_ARG;
+  // indices are validated on the device right after the upload (the reference indexes unchecked:
+  // CTracker.cpp:676-690), before any kernel uses them as addresses
 
   {
     // upper bound of everything carved below (per observation / point / camera / tile / chunk) + sort scratch
@@ -231,7 +236,16 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   HSFM_CUDA(cudaMemcpyAsync(P.cam_x0, cam_rt, sizeof(double) * 6 * n_cams, cudaMemcpyHostToDevice, s));
   HSFM_CUDA(cudaMemcpyAsync(P.pts_io, pts, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyHostToDevice, s));
   HSFM_CUDA(cudaMemcpyAsync(P.cam_x, P.cam_x0, sizeof(double) * 6 * n_cams, cudaMemcpyDeviceToDevice, s));
-  HSFM_CUDA(cudaStreamSynchronize(s));
+  {
+    int* d_bad;
+    ALLOC(d_bad, 1);
+    int h_bad = 0;
+    HSFM_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(int), s));
+    if (n > 0) validate_idx_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, cam_in, pt_in, n_cams, n_pts, d_bad);
+    HSFM_CUDA(cudaMemcpyAsync(&h_bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, s));
+    HSFM_CUDA(cudaStreamSynchronize(s));
+    if (h_bad) return HSFM_BA_ERR_ARG;
+  }
   const double t_setup0 = now_ms();
   if (h2d_ms) *h2d_ms = t_setup0 - t_h2d0;
 
@@ -301,22 +315,26 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   HSFM_CUDA(cudaMemcpyAsync(h_cam_start.data(), cam_start, sizeof(int) * ((size_t)n_cams + 1), cudaMemcpyDeviceToHost, s));
   HSFM_CUDA(cudaStreamSynchronize(s));
   std::vector<int> tiles, tile_p;  // first observation / first point of every tile (+ end sentinels)
+  std::vector<long long> pair_cum; // observation pairs (sum over points of L(L+1)/2) before every tile (+ total)
   tiles.reserve((size_t)n / (TILE - 32) + 2);
   tile_p.reserve((size_t)n / (TILE - 32) + 2);
+  pair_cum.reserve((size_t)n / (TILE - 32) + 2);
   int max_track = 0;
   {
     int tile_b = 0, p_end = 0;  // p_end: one past the last point that has observations (the others are sorted last)
-    tiles.push_back(0); tile_p.push_back(0);
+    long long acc = 0;
+    tiles.push_back(0); tile_p.push_back(0); pair_cum.push_back(0);
     for (int p = 0; p < n_pts; ++p) {
       const int b = h_pt_start[p], e = h_pt_start[p + 1];
       max_track = std::max(max_track, e - b);
       if (e > b) p_end = p + 1;
       if (e - tile_b > TILE) {  // point p does not fit: close the tile before it
-        if (b > tile_b) { tiles.push_back(b); tile_p.push_back(p); tile_b = b; }
+        if (b > tile_b) { tiles.push_back(b); tile_p.push_back(p); pair_cum.push_back(acc); tile_b = b; }
       }
+      acc += (long long)(e - b) * (e - b + 1) / 2;
     }
-    if (n > tile_b) { tiles.push_back(n); tile_p.push_back(p_end); }
-    if (tiles.size() == 1) { tiles.clear(); tile_p.clear(); }
+    if (n > tile_b) { tiles.push_back(n); tile_p.push_back(p_end); pair_cum.push_back(acc); }
+    if (tiles.size() == 1) { tiles.clear(); tile_p.clear(); pair_cum.clear(); }
   }
   P.max_track = max_track;
   if (max_track > MAX_TRACK) return HSFM_BA_ERR_UNSUPPORTED;
@@ -330,15 +348,9 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   int* pair_off = nullptr;
   {
     std::vector<int> po((size_t)P.n_tiles + 1, 0);
-    long long acc = 0;
-    for (int k = 0; k < P.n_tiles; ++k) {
-      po[k] = (int)acc;
-      for (int p = tile_p[k]; p < tile_p[k + 1]; ++p) {
-        const long long L = h_pt_start[p + 1] - h_pt_start[p];
-        acc += L * (L + 1) / 2;
-      }
-      if (acc >= (1ll << 31)) break;
-    }
+    const long long acc = P.n_tiles ? pair_cum[(size_t)P.n_tiles] : 0;
+    if (acc < (1ll << 31))
+      for (int k = 0; k < P.n_tiles; ++k) po[k] = (int)pair_cum[(size_t)k];
     P.total_pairs = acc;
     P.pairs_ready = false;
     if (acc < (1ll << 31) && P.n_tiles > 0) {
