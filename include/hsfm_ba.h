@@ -66,7 +66,8 @@ typedef struct hsfm_ba_options {
   int32_t dense_max_cams;                /* 2048: largest camera count solved by dense Cholesky under AUTO */
   int32_t pcg_max_iterations;            /* 1000 */
   int32_t verbose;                       /* 0; 1 prints a Ceres-like progress table to stderr */
-  int32_t reserved0;
+  int32_t dense_flags;                   /* 0; bit 0: factor S as a full dense matrix (ignore its envelope), bit 1: form S
+                                            from unsorted observation pairs.  Same result either way; for tests and benches */
   double initial_trust_region_radius;    /* 1e4  */
   double max_trust_region_radius;        /* 1e16 */
   double min_trust_region_radius;        /* 1e-32*/

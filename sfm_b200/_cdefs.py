@@ -12,7 +12,7 @@ class Options(C.Structure):
         ("dense_max_cams", C.c_int32),
         ("pcg_max_iterations", C.c_int32),
         ("verbose", C.c_int32),
-        ("reserved0", C.c_int32),  # oracle: num_threads
+        ("dense_flags", C.c_int32),  # same slot as the oracle's num_threads
         ("initial_trust_region_radius", C.c_double),
         ("max_trust_region_radius", C.c_double),
         ("min_trust_region_radius", C.c_double),

@@ -73,6 +73,7 @@ void hsfm_ba_default_options(hsfm_ba_options* o) {
   o->dense_max_cams = 2048;
   o->pcg_max_iterations = 1000;
   o->verbose = 0;
+  o->dense_flags = 0;
   o->initial_trust_region_radius = 1e4;
   o->max_trust_region_radius = 1e16;
   o->min_trust_region_radius = 1e-32;

@@ -1182,8 +1182,8 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
       continue;
     }
     const int* list = pl.d_list + pl.off[K];
-    int rows_per = 64;  // strips of 8..64 rows: about one CTA per SM
-    while (rows_per > 8 && cnt * (NB / rows_per) < n_sm) rows_per >>= 1;
+    int rows_per = 64;  // strips of 8..64 rows: as many CTAs as fit in ONE wave (the kernel runs one CTA per SM)
+    while (rows_per > 8 && cnt * (NB / (rows_per >> 1)) <= n_sm) rows_per >>= 1;
     const int spb = NB / rows_per;
     chol_trsm_strip_kernel<<<cnt * spb, 256, rows_per * TS_LD * (int)sizeof(double), s2>>>(S, n, k0, Linv, rows_per, fail_flag, list, spb);
     ++*launches;

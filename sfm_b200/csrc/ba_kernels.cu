@@ -1308,7 +1308,7 @@ void launch_dense_init(Problem& P, bool with_diag, cudaStream_t s) {
   P.launches++;
 }
 
-void launch_dense_schur(Problem& P, cudaStream_t s) {
+void launch_dense_schur(Problem& P, cudaStream_t s, bool sorted_pairs) {
   if (P.n_tiles == 0) return;
   static bool attr_set = false;
   if (!attr_set) {
@@ -1317,7 +1317,7 @@ void launch_dense_schur(Problem& P, cudaStream_t s) {
     attr_set = true;
   }
   static const bool no_sort = getenv("HSFM_SCHUR_UNSORTED") != nullptr;  // experiment knob
-  if (!P.pairs_ready && P.d.pair_off && !no_sort) {
+  if (!P.pairs_ready && P.d.pair_off && !no_sort && sorted_pairs) {
     // first dense solve of this problem: build the destination-sorted pair lists (static, like the rest of the index)
     const size_t need = (size_t)std::max<long long>(P.total_pairs, 1);
     if (P.pair_capacity < need) {
@@ -1333,7 +1333,7 @@ void launch_dense_schur(Problem& P, cudaStream_t s) {
       P.pairs_ready = true;
     }
   }
-  if (P.pairs_ready) dense_schur_kernel<true><<<P.n_tiles, TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S);
+  if (P.pairs_ready && sorted_pairs) dense_schur_kernel<true><<<P.n_tiles, TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S);
   else dense_schur_kernel<false><<<P.n_tiles, TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S);
   P.launches++;
 }

@@ -95,17 +95,17 @@ struct Driver {
       const bool lead = ctx.comm.rank == 0;
       if (dense) {
         launch_dense_init(P, lead, s);
-        launch_dense_schur(P, s);
+        launch_dense_schur(P, s, !(o.dense_flags & 2));
         launch_schur_rhs(P, lead, s);
         if (multi()) {
           chk(ctx.comm.allreduce_sum(P.S, (size_t)n6 * n6, s));
           chk(ctx.comm.allreduce_sum(P.rhs, n6, s));
         }
         mark(2);
-        launch_cholesky(P.S, n6, P.S + (size_t)n6 * n6, P.flags + F_CHOL_FAIL, s, &ctx.chol_aux, &P.launches, &ctx.chol_plan);
+        launch_cholesky(P.S, n6, P.S + (size_t)n6 * n6, P.flags + F_CHOL_FAIL, s, &ctx.chol_aux, &P.launches, (o.dense_flags & 1) ? nullptr : &ctx.chol_plan);
         mark(3);
         HSFM_CUDA(cudaMemcpyAsync(P.yc, P.rhs, sizeof(double) * n6, cudaMemcpyDeviceToDevice, s));
-        launch_chol_solve(P.S, n6, P.S + (size_t)n6 * n6, P.yc, s, &P.launches, &ctx.chol_plan);
+        launch_chol_solve(P.S, n6, P.S + (size_t)n6 * n6, P.yc, s, &P.launches, (o.dense_flags & 1) ? nullptr : &ctx.chol_plan);
       } else {
         launch_cam_major(P, P.rows_x, P.pts_x, P.scale_p, 1, s);
         if (multi()) chk(ctx.comm.allreduce_sum(P.E, 21 * (size_t)P.n_cams, s));

@@ -143,6 +143,47 @@ def test_golden_normal_equations_lapack(ctx, golden_dir):
     assert s["trace"][1]["model_cost_change"] == pytest.approx(float(g["model_cost_change"]), rel=1e-8)
 
 
+def _trajectory(n_cams=420, window=12, n_pts=6000, seed=5, closure=True):
+    """Scan trajectory: every point is seen by cameras of a short window of consecutive keyframes; a loop closure
+    ties the last keyframes to the first.  The reduced camera matrix is a band plus a few long rows — the case the
+    envelope factorisation exists for (n = 2520: 20 panels of 128)."""
+    p = synth.make_ring(n_cams, n_pts, 4, seed=seed, skew=0.05)
+    rng = np.random.default_rng(seed)
+    start = rng.integers(0, n_cams - window, n_pts)
+    offs = np.sort(np.argsort(rng.random((n_pts, window)), axis=1)[:, :4], axis=1)  # four distinct keyframes of the window
+    cams = start[:, None] + offs
+    if closure:
+        k = n_pts // 50
+        cams[:k] = (n_cams - window) + offs[:k]
+        cams[:k, 0] = rng.integers(0, 4, k)  # ... and one of the first keyframes
+    cam_idx = cams.reshape(-1).astype(np.int32)
+    pt_idx = np.repeat(np.arange(n_pts, dtype=np.int32), 4)
+    obs = synth.project(p.cam_true, p.K, p.pts_true, cam_idx, pt_idx)[0] + rng.normal(0.0, 0.5, (cam_idx.size, 2))
+    return synth.Problem(obs=np.ascontiguousarray(obs), cam_idx=cam_idx, pt_idx=pt_idx, K=p.K, cam=p.cam, pts=p.pts,
+                         cam_true=p.cam_true, pts_true=p.pts_true, name="trajectory")
+
+
+@pytest.mark.parametrize("closure", [False, True], ids=["band", "band+loop-closure"])
+def test_envelope_factorisation_equals_dense(ctx, closure):
+    """The envelope Cholesky skips only blocks that are exactly zero: same iterates as the full dense factorisation
+    of the same matrix (dense_flags bit 0), and as the unsorted formation of S (bit 1)."""
+    p = _trajectory(closure=closure)
+    runs = {}
+    for name, flags in [("envelope", 0), ("dense", 1), ("unsorted", 2)]:
+        o = api.default_options(linear_solver=api.LINEAR_DENSE_SCHUR, max_num_iterations=6)
+        o.dense_flags = flags
+        runs[name] = ctx.solve_packed(p, opts=o)
+    ce, pe, se = runs["envelope"]
+    for other in ("dense", "unsorted"):
+        co, po_, so = runs[other]
+        assert se["num_iterations"] == so["num_iterations"] and se["num_successful_steps"] == so["num_successful_steps"]
+        assert se["final_cost"] == pytest.approx(so["final_cost"], rel=1e-10)
+        assert np.abs(ce - co).max() < 1e-8 and np.abs(pe - po_).max() < 1e-8
+    assert se["final_cost"] < 0.05 * se["initial_cost"]
+    so = po.solve(p, opts=po.default_options(num_threads=4, max_num_iterations=6))[2]
+    assert se["final_cost"] == pytest.approx(so["final_cost"], rel=TOL_COST)
+
+
 def test_tiles_with_many_distinct_cameras(ctx):
     """Two-view tracks over 300 cameras: a 256-observation tile touches well over a hundred distinct cameras, so
     the shared-memory staging of camera rows needs more than the 48 KB default (opt-in dynamic shared memory)."""
