@@ -1148,12 +1148,42 @@ int CholPlan::build(int n_cams, const int* cam_first, cudaStream_t s) {
     d_cap = need;
   }
   d_list = d_fb + panels;
+  blk_off.assign((size_t)panels + 1, 0);
+  for (int I = 0; I < panels; ++I) {
+    const long long rows = std::min(NB, n - I * NB), width = (long long)NB * (I + 1 - fb[I]);
+    blk_off[I + 1] = blk_off[I] + rows * width;
+  }
+  if ((size_t)panels + 1 > d_blk_cap) {
+    if (d_blk_off) cudaFree(d_blk_off);
+    d_blk_off = nullptr; d_blk_cap = 0;
+    HSFM_CUDA(cudaMalloc(&d_blk_off, sizeof(long long) * ((size_t)panels + 1)));
+    d_blk_cap = (size_t)panels + 1;
+  }
+  HSFM_CUDA(cudaMemcpyAsync(d_blk_off, blk_off.data(), sizeof(long long) * blk_off.size(), cudaMemcpyHostToDevice, s));
   HSFM_CUDA(cudaMemcpyAsync(d_fb, fb.data(), sizeof(int) * (size_t)panels, cudaMemcpyHostToDevice, s));
   if (!list.empty()) HSFM_CUDA(cudaMemcpyAsync(d_list, list.data(), sizeof(int) * list.size(), cudaMemcpyHostToDevice, s));
   HSFM_CUDA(cudaStreamSynchronize(s));  // the host vectors may be rebuilt by the next problem
   return 0;
 }
+// One CTA per matrix row: the row's envelope segment <-> its place in the packed buffer (16-byte accesses).
+__global__ void __launch_bounds__(256) envelope_pack_kernel(double* __restrict__ S, int n, const int* __restrict__ fb,
+                                                            const long long* __restrict__ blk_off, double* __restrict__ packed, int to_packed) {
+  const int r = blockIdx.x, I = r / NB;
+  const int c0 = __ldg(fb + I) * NB, width = NB * (I + 1) - c0;
+  double2* row = reinterpret_cast<double2*>(S + (size_t)r * n + c0);
+  double2* pk = reinterpret_cast<double2*>(packed + __ldg(blk_off + I) + (long long)(r - I * NB) * width);
+  const int valid = min(width, n - c0);  // the last block's columns past n do not exist (n is even: 6 per camera)
+  for (int e = threadIdx.x; e < valid / 2; e += 256) {
+    if (to_packed) pk[e] = row[e]; else row[e] = pk[e];
+  }
+}
+void launch_envelope_pack(const CholPlan& pl, double* S, double* packed, bool to_packed, cudaStream_t s) {
+  envelope_pack_kernel<<<pl.n, 256, 0, s>>>(S, pl.n, pl.d_fb, pl.d_blk_off, packed, to_packed ? 1 : 0);
+}
+
 void CholPlan::destroy() {
+  if (d_blk_off) cudaFree(d_blk_off);
+  d_blk_off = nullptr; d_blk_cap = 0;
   if (d_fb) cudaFree(d_fb);
   d_fb = nullptr; d_list = nullptr; d_cap = 0; use = false;
 }

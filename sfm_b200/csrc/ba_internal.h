@@ -188,6 +188,12 @@ struct CholPlan {
   int* d_fb = nullptr;         // device copy: fb, then the lists
   int* d_list = nullptr;
   size_t d_cap = 0;
+  // packed envelope (multi-GPU: only these entries of S are summed across ranks): row r of block I occupies
+  // packed[blk_off[I] + (r - 128 I) * width(I)) .. + width(I)), width(I) = 128 (I + 1 - fb[I]) columns from 128 fb[I]
+  std::vector<long long> blk_off;  // [panels + 1]
+  long long* d_blk_off = nullptr;
+  size_t d_blk_cap = 0;
+  long long packed_doubles() const { return blk_off.empty() ? 0 : blk_off.back(); }
   int build(int n_cams, const int* cam_first, cudaStream_t s);  // cam_first on the host; nullptr = dense
   void destroy();
 };
@@ -196,6 +202,8 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
                      const CholPlan* plan = nullptr);
 void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream_t s, int64_t* launches, const CholPlan* plan = nullptr);
 
+// S envelope <-> packed buffer (to_packed: gather; else scatter)
+void launch_envelope_pack(const CholPlan& pl, double* S, double* packed, bool to_packed, cudaStream_t s);
 void launch_spd_fill(double* A, int n, double* b /*null = matrix only*/, cudaStream_t s);  // bench tap: synthetic SPD matrix, b = A 1
 void launch_spd_err(int n, const double* x, double* err, cudaStream_t s);                 // max |x - 1|
 

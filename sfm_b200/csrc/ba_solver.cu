@@ -98,7 +98,19 @@ struct Driver {
         launch_dense_schur(P, s, !(o.dense_flags & 2));
         launch_schur_rhs(P, lead, s);
         if (multi()) {
-          chk(ctx.comm.allreduce_sum(P.S, (size_t)n6 * n6, s));
+          const CholPlan& pl = ctx.chol_plan;
+          if (pl.use && pl.n == n6 && !(o.dense_flags & 1) && (size_t)pl.packed_doubles() <= 6 * (size_t)P.n_obs) {
+            // only the envelope of S can be non-zero on any rank: sum that (packed into the per-observation
+            // staging buffer of the Schur passes, idle between the right-hand side and the next mat-vec) instead
+            // of the whole n x n matrix
+            double* packed = P.tobs;
+            launch_envelope_pack(pl, P.S, packed, true, s);
+            chk(ctx.comm.allreduce_sum(packed, (size_t)pl.packed_doubles(), s));
+            launch_envelope_pack(pl, P.S, packed, false, s);
+            P.launches += 2;
+          } else {
+            chk(ctx.comm.allreduce_sum(P.S, (size_t)n6 * n6, s));
+          }
           chk(ctx.comm.allreduce_sum(P.rhs, n6, s));
         }
         mark(2);
