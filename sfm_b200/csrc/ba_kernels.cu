@@ -158,79 +158,188 @@ __device__ __forceinline__ void tile_point_sums(const Dev& d, const TileHdr& t, 
   }
 }
 
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
 // Kernel RJ: residual + Jacobian per observation (a1), fused with the point-keyed part of the
 // normal equations (a7: Hpp = sum Jp^T Jp, g_p = sum Jp^T r) and the cost partial (a6).
 // Algorithmic bytes / observation: 24 in (obs 16, cam 4, pt 4) + 160 out (r 16, Jc 96, Jp 48).
-// Memory round trips on the critical path of a CTA: tile header -> {observations, slots, point ids, camera list,
-// points, scales, CSR bounds} -> camera rows.  Every Jacobian column is stored the moment it is formed and the
-// camera row is read in place from shared memory, which keeps the kernel at 64 registers = four CTAs per SM.
+//
+// PERSISTENT and double-buffered: two CTAs per SM walk the tiles.  Everything a tile needs is brought into shared
+// memory by cp.async one tile ahead — camera rows, points, scales, observations, point ids, slots, CSR bounds —
+// and the header + camera list ("meta") two tiles ahead, because the row copies of tile t+1 take their source
+// addresses from it.  The three dependent memory round trips of a tile (header -> lists -> rows) are never
+// waited for after the first tile, and being asynchronous copies the prefetches cannot be scheduled late by
+// the compiler the way register prefetches are.  Every Jacobian column is stored the moment it is formed; the
+// camera row is read in place from shared memory.  One barrier per tile (+ one before the point sums).
+struct RjStage {          // byte offsets inside one stage, all 16-byte aligned
+  int rows, X, S, obs, pt, slotw, bnd, bytes;
+};
+__host__ __device__ constexpr RjStage rj_stage(int row_cap) {
+  RjStage g{};
+  g.rows = 0;
+  g.X = g.rows + 16 * ROW_LD * row_cap;
+  g.S = g.X + 24 * TILE;
+  g.obs = g.S + 24 * TILE;
+  g.pt = g.obs + 16 * TILE;
+  g.slotw = g.pt + 4 * TILE;
+  g.bnd = g.slotw + 4 * TILE;      // [2 rounds][TILE][2] ints
+  g.bytes = g.bnd + 16 * TILE;
+  return g;
+}
+constexpr int RJ_META_BYTES = 32 + 4 * TILE;  // header + camera list
+__host__ constexpr size_t rj_smem_bytes(int row_cap, bool form) {
+  return 2 * (size_t)rj_stage(row_cap).bytes + 3 * RJ_META_BYTES + (form ? sizeof(double) * 9 * SV_LD : 0);
+}
 template <bool WRITE_J, bool FORM>
-__global__ void __launch_bounds__(TILE, 3) rj_kernel(Dev d, const CamRow* __restrict__ rows, const double* __restrict__ pts,
+__global__ void __launch_bounds__(TILE, 2) rj_kernel(Dev d, const CamRow* __restrict__ rows, const double* __restrict__ pts,
                                                       const double* __restrict__ scale_p, double* __restrict__ Hpp,
                                                       double* __restrict__ gp, double* __restrict__ cost_part, int row_cap) {
-  extern __shared__ __align__(16) double dyn[];
-  double2* sR = reinterpret_cast<double2*>(dyn);
-  double* sX = dyn + rows_doubles(row_cap);  // [n_p][3] points
-  double* sS = sX + 3 * TILE;                // [n_p][3] point column scales
-  double* sv = sS + 3 * TILE;                // [9][SV_LD] (FORM)
+  extern __shared__ __align__(16) unsigned char dynb[];
+  const RjStage L = rj_stage(row_cap);
+  unsigned char* meta0 = dynb + 2 * L.bytes;
+  double* sv = reinterpret_cast<double*>(meta0 + 3 * RJ_META_BYTES);  // [9][SV_LD] (FORM)
   __shared__ double sm[8];
-  const TileHdr t = tile_hdr(d);
-  const int i = t.b + (int)threadIdx.x;
-  const bool valid = i < t.e;
-  double2 o = make_double2(0.0, 0.0);
-  int pl = 0, slot = 0;
-  if (valid) {
-    o = __ldg(d.obs + i);
-    slot = __ldg(d.slot + i);
-    pl = __ldg(d.pt + i) - t.p_first;
-  }
-  int bnd[4];
-  if (FORM) prefetch_point_bounds<9>(d, t, bnd);
-  stage_points(t, pts, sX);
-  if (scale_p) stage_points(t, scale_p, sS);
-  stage_rows(d, t, rows, sR);
-  __syncthreads();
-  double r0 = 0.0, r1 = 0.0;
-  if (valid) {
-    const CamRow& C = staged_row(sR, slot);
-    const double X0 = sX[3 * pl], X1 = sX[3 * pl + 1], X2 = sX[3 * pl + 2];
-    double sp[3] = {1.0, 1.0, 1.0};
-    if (scale_p) { sp[0] = sS[3 * pl]; sp[1] = sS[3 * pl + 1]; sp[2] = sS[3 * pl + 2]; }
-    const size_t n = (size_t)d.n_obs;
-    double jp[6];
-    reproject_lin(C, X0, X1, X2, o.x, o.y, sp, r0, r1, [&](int col, double du, double dv) {
-      if (col < 6) {
-        if (WRITE_J) d.Jc[col * n + i] = make_double2(du, dv);
-      } else {
-        if (WRITE_J) d.Jp[(col - 6) * n + i] = make_double2(du, dv);
-        jp[col - 6] = du; jp[col - 3] = dv;
+  const int tid = threadIdx.x;
+  const int rounds = (row_cap * 12 + TILE - 1) / TILE;
+
+  // three meta slots: tile t computes from slot t % 3 while t+1's is read for its copies and t+2's is being written
+  auto meta_hdr = [&](int seq) { return reinterpret_cast<const int*>(meta0 + (seq % 3) * RJ_META_BYTES); };
+  auto meta_list = [&](int seq) { return reinterpret_cast<const int*>(meta0 + (seq % 3) * RJ_META_BYTES + 32); };
+  // header (two 16-byte pieces) + the 64 16-byte pieces of the camera list of one tile
+  auto issue_meta = [&](int seq, int tile) {
+    unsigned char* m = meta0 + (seq % 3) * RJ_META_BYTES;
+    if (tid < 2) cp_async16(m + 16 * tid, d.tile_hdr + 2 * (size_t)tile + tid);
+    else if (tid < 2 + TILE / 4) cp_async16(m + 32 + 16 * (tid - 2), d.tile_cams + (size_t)tile * TILE + 4 * (tid - 2));
+  };
+  // all inputs of the tile whose meta is in slot seq -> stage seq & 1
+  auto issue_stage = [&](int seq) {
+    const int* h = meta_hdr(seq);
+    const int* lst = meta_list(seq);
+    const int tb = h[0], te = h[1], p_first = h[2], n_p = h[3] - h[2], ncam = h[4];
+    unsigned char* st = dynb + (seq & 1) * L.bytes;
+    double2* sR = reinterpret_cast<double2*>(st + L.rows);
+    for (int r = 0; r < rounds; ++r) {
+      const int q = tid + r * TILE;
+      if (q < ncam * 12) {
+        const int sl = q / 12, piece = q - sl * 12;
+        cp_async16(sR + sl * ROW_LD + piece, reinterpret_cast<const double2*>(rows + lst[sl]) + piece);
       }
-    });
-    if (WRITE_J) d.r[i] = make_double2(r0, r1);
-    if (FORM) {
-      double* v = sv + threadIdx.x;
-      v[0 * SV_LD] = jp[0] * jp[0] + jp[3] * jp[3];
-      v[1 * SV_LD] = jp[0] * jp[1] + jp[3] * jp[4];
-      v[2 * SV_LD] = jp[0] * jp[2] + jp[3] * jp[5];
-      v[3 * SV_LD] = jp[1] * jp[1] + jp[4] * jp[4];
-      v[4 * SV_LD] = jp[1] * jp[2] + jp[4] * jp[5];
-      v[5 * SV_LD] = jp[2] * jp[2] + jp[5] * jp[5];
-      v[6 * SV_LD] = jp[0] * r0 + jp[3] * r1;
-      v[7 * SV_LD] = jp[1] * r0 + jp[4] * r1;
-      v[8 * SV_LD] = jp[2] * r0 + jp[5] * r1;
     }
+    double* sX = reinterpret_cast<double*>(st + L.X);
+    double* sS = reinterpret_cast<double*>(st + L.S);
+    for (int q = tid; q < 3 * n_p; q += TILE) {
+      cp_async8(sX + q, pts + 3 * (size_t)p_first + q);
+      if (scale_p) cp_async8(sS + q, scale_p + 3 * (size_t)p_first + q);
+    }
+    const int i = tb + tid;
+    if (i < te) {
+      cp_async16(st + L.obs + 16 * tid, d.obs + i);
+      cp_async4(st + L.pt + 4 * tid, d.pt + i);
+      cp_async4(st + L.slotw + 4 * tid, d.slot + (i & ~3));  // the aligned word that holds this observation's slot byte
+    }
+    if (FORM) {
+      int* sb = reinterpret_cast<int*>(st + L.bnd);
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int task = tid + r * TILE;
+        if (task < n_p * 9) {  // {start, end} of the task's point
+          cp_async4(sb + 2 * task, d.pt_start + p_first + task / 9);
+          cp_async4(sb + 2 * task + 1, d.pt_start + p_first + task / 9 + 1);
+        }
+      }
+    }
+  };
+
+  const int tile0 = blockIdx.x;
+  if (tile0 >= d.n_tiles) return;
+  // prologue: meta of the first two tiles, then the first stage
+  issue_meta(0, tile0);
+  if (tile0 + (int)gridDim.x < d.n_tiles) issue_meta(1, tile0 + gridDim.x);
+  cp_async_commit();
+  cp_async_wait<0>();
+  __syncthreads();
+  issue_stage(0);
+  cp_async_commit();
+  double cost_acc = 0.0;  // this thread's share of the cost over all tiles of the CTA
+  for (int seq = 0, tile = tile0; tile < d.n_tiles; ++seq, tile += gridDim.x) {
+    cp_async_wait<0>();  // this tile's stage (and the next tile's meta) have landed ...
+    __syncthreads();     // ... for everyone, and everyone has left the previous tile: its stage, meta slot and sv are free
+    const int* h = meta_hdr(seq);
+    TileHdr t;
+    t.b = h[0]; t.e = h[1]; t.p_first = h[2]; t.n_p = h[3] - h[2]; t.ncam = h[4];
+    const int nxt = tile + gridDim.x, nn = nxt + gridDim.x;
+    if (nxt < d.n_tiles) issue_stage(seq + 1);
+    if (nn < d.n_tiles) issue_meta(seq + 2, nn);
+    cp_async_commit();
+
+    const unsigned char* st = dynb + (seq & 1) * L.bytes;
+    const double2* sR = reinterpret_cast<const double2*>(st + L.rows);
+    const double* sX = reinterpret_cast<const double*>(st + L.X);
+    const double* sS = reinterpret_cast<const double*>(st + L.S);
+    const int i = t.b + tid;
+    if (i < t.e) {
+      const double2 o = *reinterpret_cast<const double2*>(st + L.obs + 16 * tid);
+      const int slot = (int)((*reinterpret_cast<const unsigned*>(st + L.slotw + 4 * tid) >> (8 * (i & 3))) & 0xffu);
+      const int pl = *reinterpret_cast<const int*>(st + L.pt + 4 * tid) - t.p_first;
+      const CamRow& C = staged_row(sR, slot);
+      const double X0 = sX[3 * pl], X1 = sX[3 * pl + 1], X2 = sX[3 * pl + 2];
+      double sp[3] = {1.0, 1.0, 1.0};
+      if (scale_p) { sp[0] = sS[3 * pl]; sp[1] = sS[3 * pl + 1]; sp[2] = sS[3 * pl + 2]; }
+      const size_t n = (size_t)d.n_obs;
+      double r0, r1, jp[6];
+      reproject_lin(C, X0, X1, X2, o.x, o.y, sp, r0, r1, [&](int col, double du, double dv) {
+        if (col < 6) {
+          if (WRITE_J) d.Jc[col * n + i] = make_double2(du, dv);
+        } else {
+          if (WRITE_J) d.Jp[(col - 6) * n + i] = make_double2(du, dv);
+          jp[col - 6] = du; jp[col - 3] = dv;
+        }
+      });
+      if (WRITE_J) d.r[i] = make_double2(r0, r1);
+      cost_acc += r0 * r0 + r1 * r1;
+      if (FORM) {
+        double* v = sv + tid;
+        v[0 * SV_LD] = jp[0] * jp[0] + jp[3] * jp[3];
+        v[1 * SV_LD] = jp[0] * jp[1] + jp[3] * jp[4];
+        v[2 * SV_LD] = jp[0] * jp[2] + jp[3] * jp[5];
+        v[3 * SV_LD] = jp[1] * jp[1] + jp[4] * jp[4];
+        v[4 * SV_LD] = jp[1] * jp[2] + jp[4] * jp[5];
+        v[5 * SV_LD] = jp[2] * jp[2] + jp[5] * jp[5];
+        v[6 * SV_LD] = jp[0] * r0 + jp[3] * r1;
+        v[7 * SV_LD] = jp[1] * r0 + jp[4] * r1;
+        v[8 * SV_LD] = jp[2] * r0 + jp[5] * r1;
+      }
+    }
+    if (FORM) {
+      __syncthreads();
+      const int* sb = reinterpret_cast<const int*>(st + L.bnd);
+      int bnd[4] = {0, 0, 0, 0};
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int task = tid + r * TILE;
+        if (task < t.n_p * 9) { bnd[2 * r] = sb[2 * task] - t.b; bnd[2 * r + 1] = sb[2 * task + 1] - t.b; }
+      }
+      tile_point_sums<9>(d, t, bnd, sv, [&](int p, int k, double tot) {
+        if (k < 6) Hpp[6 * (size_t)p + k] = tot;
+        else gp[3 * (size_t)p + (k - 6)] = tot;
+      });
+    }
+    if (tid == 0 && tile != tile0) cost_part[tile] = 0.0;  // the CTA's cost goes to the slot of its first tile
   }
-  const double cs = block_sum_256(r0 * r0 + r1 * r1, sm);  // its barriers also publish sv
-  if (threadIdx.x == 0) cost_part[blockIdx.x] = cs;
-  if (FORM) {
-    tile_point_sums<9>(d, t, bnd, sv, [&](int p, int k, double tot) {
-      if (k < 6) Hpp[6 * (size_t)p + k] = tot;
-      else gp[3 * (size_t)p + (k - 6)] = tot;
-    });
-  }
-}
-__host__ constexpr size_t rj_smem_bytes(int row_cap, bool form) {
-  return sizeof(double) * (size_t)(rows_doubles(row_cap) + 6 * TILE + (form ? 9 * SV_LD : 0));
+  cp_async_wait<0>();
+  const double cs = block_sum_256(cost_acc, sm);
+  if (tid == 0) cost_part[tile0] = cs;
 }
 
 // Candidate cost: residual only (a9), 24 B/observation.
@@ -1135,7 +1244,7 @@ void launch_cam_prep(Problem& P, const double* cam, const double* scale_c, CamRo
 }
 
 // Largest dynamic shared memory any staging kernel can ask for (256 distinct cameras in a tile).
-constexpr int kStageSmemMax = (int)sizeof(double) * (rows_doubles(TILE) + 6 * TILE + 9 * SV_LD);
+constexpr int kStageSmemMax = 2 * rj_stage(TILE).bytes + 3 * RJ_META_BYTES + (int)sizeof(double) * 9 * SV_LD;
 template <class Kern>
 static void allow_stage_smem(Kern k) { cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kStageSmemMax); }
 
@@ -1150,10 +1259,18 @@ void launch_rj(Problem& P, const CamRow* rows, const double* pts, const double* 
   double* cp = P.part + (size_t)P_COST * P.part_stride;
   const int cap = P.max_tile_cams;
   const size_t sh = rj_smem_bytes(cap, form);
-  if (write_j && form) rj_kernel<true, true><<<P.n_tiles, TILE, sh, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp, cap);
-  else if (write_j) rj_kernel<true, false><<<P.n_tiles, TILE, sh, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp, cap);
-  else if (form) rj_kernel<false, true><<<P.n_tiles, TILE, sh, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp, cap);
-  else rj_kernel<false, false><<<P.n_tiles, TILE, sh, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp, cap);
+  static int n_sm = 0;
+  if (!n_sm) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    if (n_sm <= 0) n_sm = 148;
+  }
+  const int grid = std::min(P.n_tiles, 2 * n_sm);  // persistent: two CTAs per SM walk the tiles
+  if (write_j && form) rj_kernel<true, true><<<grid, TILE, sh, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp, cap);
+  else if (write_j) rj_kernel<true, false><<<grid, TILE, sh, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp, cap);
+  else if (form) rj_kernel<false, true><<<grid, TILE, sh, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp, cap);
+  else rj_kernel<false, false><<<grid, TILE, sh, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp, cap);
   P.launches++;
   add_task(P, P_COST, P.n_tiles, S_COST, 2);
 }
