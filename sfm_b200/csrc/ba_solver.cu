@@ -94,7 +94,7 @@ struct Driver {
     if (P.mode == 2) {
       const bool lead = ctx.comm.rank == 0;
       if (dense) {
-        launch_dense_init(P, lead, s);
+        launch_dense_init(P, lead, s, (o.dense_flags & 1) ? nullptr : &ctx.chol_plan);
         launch_dense_schur(P, s, !(o.dense_flags & 2));
         launch_schur_rhs(P, lead, s);
         if (multi()) {
