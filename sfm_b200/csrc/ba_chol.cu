@@ -1100,6 +1100,7 @@ int CholAux::init() {
   return 0;
 }
 void CholAux::destroy() {
+  if (graph) { cudaGraphExecDestroy(graph); graph = nullptr; }
   if (!stream) return;
   cudaStreamDestroy(stream);
   cudaEventDestroy(ev_fork); cudaEventDestroy(ev_panel); cudaEventDestroy(ev_rest); cudaEventDestroy(ev_join);
@@ -1117,6 +1118,7 @@ void CholAux::destroy() {
 // Envelope plan
 // ---------------------------------------------------------------------------------------------
 int CholPlan::build(int n_cams, const int* cam_first, cudaStream_t s) {
+  ++version;
   n = 6 * n_cams;
   panels = (n + NB - 1) / NB;
   use = false; fill = 1.0;
@@ -1265,6 +1267,34 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
     else if (bulk_ctas < 0) bulk_ctas = n_sm + bulk_ctas;
   }
   if (plan && plan->use && plan->n == n) {
+    // The launch sequence (4-5 kernels and 3 event operations per panel, two streams) is static per problem:
+    // capture it once and replay it as a CUDA graph — no host launch cost, tighter kernel-to-kernel hand-over.
+    static const bool no_graph = getenv("HSFM_NO_GRAPH") != nullptr;  // experiment knob
+    if (aux && aux->stream && !no_graph) {
+      const bool valid = aux->graph && aux->g_S == S && aux->g_ws == ws && aux->g_fail == fail_flag && aux->g_stream == (const void*)s &&
+                         aux->g_n == n && aux->g_version == plan->version;
+      if (!valid) {
+        if (aux->graph) { cudaGraphExecDestroy(aux->graph); aux->graph = nullptr; }
+        cudaGraph_t g = nullptr;
+        int64_t counted = 0;
+        if (cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+          launch_cholesky_env(S, n, ws, fail_flag, s, aux, &counted, *plan, n_sm);
+          if (cudaStreamEndCapture(s, &g) == cudaSuccess && g && cudaGraphInstantiate(&aux->graph, g, 0) == cudaSuccess) {
+            aux->g_S = S; aux->g_ws = ws; aux->g_fail = fail_flag; aux->g_stream = (const void*)s; aux->g_n = n;
+            aux->g_version = plan->version; aux->g_launches = counted;
+          } else {
+            aux->graph = nullptr;
+          }
+          if (g) cudaGraphDestroy(g);
+        }
+        cudaGetLastError();
+      }
+      if (aux->graph && cudaGraphLaunch(aux->graph, s) == cudaSuccess) {
+        *launches += aux->g_launches;
+        return;
+      }
+      cudaGetLastError();
+    }
     launch_cholesky_env(S, n, ws, fail_flag, s, aux, launches, *plan, n_sm);
     return;
   }

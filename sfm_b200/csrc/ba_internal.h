@@ -171,6 +171,11 @@ void launch_mirror_lower(Problem& P, cudaStream_t s);   // S upper <- lower (par
 struct CholAux {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_panel = nullptr, ev_rest = nullptr, ev_join = nullptr;
+  // captured launch sequence of the envelope factorisation (static per problem: same S, workspace and plan)
+  cudaGraphExec_t graph = nullptr;
+  const void* g_S = nullptr; const void* g_ws = nullptr; const void* g_fail = nullptr; const void* g_stream = nullptr;
+  int g_n = 0, g_version = -1;
+  int64_t g_launches = 0;
   int init();
   void destroy();
 };
@@ -181,6 +186,7 @@ struct CholAux {
 // closures) that is a band: the factorisation of the Venice-shaped problem costs 2-3 % of the dense flops.
 struct CholPlan {
   int n = 0, panels = 0;
+  int version = 0;             // bumped by every build(): invalidates captured launch graphs
   bool use = false;            // false: treat the matrix as dense (the envelope is most of the triangle)
   double fill = 1.0;           // envelope blocks / lower-triangle blocks
   std::vector<int> fb;         // [panels] first column block in the envelope of row block I
