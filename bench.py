@@ -36,8 +36,8 @@ sys.path.insert(0, ROOT)
 FP64_DMMA_PEAK_TFLOPS = 37.1
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures (profiles/), c4
 # dram__bytes_read.sum + dram__bytes_write.sum per launch at c4, from the ncu --set full captures summarised in
-# profiles/r01_ncu_streaming.md (rj: 163.0 + 838.9 MB; mat-vec = schur_pass<1> + cam_gather6 + cam_reduce6; ...)
-TRAFFIC_C4 = {"rj_form": 1001.9e6, "schur_matvec": 1299.8e6, "schur_rhs": 1259.0e6, "dense_schur": 902.6e6}
+# profiles/r01_ncu_streaming.md (rj: 178.1 + 814.4 MB; mat-vec = schur_pass<1> + cam_gather6 + cam_reduce6; ...)
+TRAFFIC_C4 = {"rj_form": 992.5e6, "schur_matvec": 1299.8e6, "schur_rhs": 1259.0e6, "dense_schur": 902.6e6}
 
 METRIC = "lm_iterations_per_s"
 UNIT = "LM iterations/s"
