@@ -52,7 +52,8 @@ extern "C" {
 #define HSFM_BA_FAILURE 2
 
 /* linear solver for the reduced camera system */
-#define HSFM_BA_LINEAR_AUTO 0        /* dense Cholesky when n_cams <= dense_max_cams, else PCG       */
+#define HSFM_BA_LINEAR_AUTO 0        /* Cholesky when n_cams <= dense_max_cams, or up to 16x that when the reduced camera
+                                        matrix is a narrow envelope (< 15 % of the triangle) and fits in memory; else PCG */
 #define HSFM_BA_LINEAR_DENSE_SCHUR 1 /* what the reference selects, CTracker.cpp:574                 */
 #define HSFM_BA_LINEAR_PCG 2         /* implicit Schur complement, block-Jacobi preconditioned CG    */
 

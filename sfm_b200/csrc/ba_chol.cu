@@ -1085,7 +1085,7 @@ void launch_spd_err(int n, const double* x, double* err, cudaStream_t s) {
 
 size_t cholesky_workspace_doubles(int n) {
   const size_t panels = (size_t)((n + NB - 1) / NB);
-  return panels * NB * NB + panels;  // one L11^-1 block per panel + 2 x panels int flags of the cooperative triangular solve
+  return (panels * NB * NB + panels + 1) & ~(size_t)1;  // one L11^-1 block per panel + 2 x panels int flags of the cooperative triangular solve (even: what follows stays 16-byte aligned)
 }
 
 int CholAux::init() {

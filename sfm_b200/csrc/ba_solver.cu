@@ -99,11 +99,10 @@ struct Driver {
         launch_schur_rhs(P, lead, s);
         if (multi()) {
           const CholPlan& pl = ctx.chol_plan;
-          if (pl.use && pl.n == n6 && !(o.dense_flags & 1) && (size_t)pl.packed_doubles() <= 6 * (size_t)P.n_obs) {
-            // only the envelope of S can be non-zero on any rank: sum that (packed into the per-observation
-            // staging buffer of the Schur passes, idle between the right-hand side and the next mat-vec) instead
-            // of the whole n x n matrix
-            double* packed = P.tobs;
+          if (pl.use && pl.n == n6 && !(o.dense_flags & 1)) {
+            // only the envelope of S can be non-zero on any rank: sum that (packed behind the factorisation's
+            // workspace) instead of the whole n x n matrix
+            double* packed = P.S + (size_t)n6 * n6 + cholesky_workspace_doubles(n6);
             launch_envelope_pack(pl, P.S, packed, true, s);
             chk(ctx.comm.allreduce_sum(packed, (size_t)pl.packed_doubles(), s));
             launch_envelope_pack(pl, P.S, packed, false, s);
@@ -178,11 +177,38 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
   Driver D(ctx, o);
   const int n6 = 6 * P.n_cams;
   if (P.mode == 2) {
+    auto ensure_plan = [&]() -> int {  // static per problem: which 128-blocks of S (and of L) can be non-zero
+      if (ctx.chol_plan_valid) return 0;
+      int rc = ctx.chol_plan.build(P.n_cams, (int)P.cam_first.size() == P.n_cams ? P.cam_first.data() : nullptr, s);
+      if (rc) return rc;
+      ctx.chol_plan_valid = true;
+      return 0;
+    };
     if (o.linear_solver == HSFM_BA_LINEAR_DENSE_SCHUR) D.dense = true;
     else if (o.linear_solver == HSFM_BA_LINEAR_PCG) D.dense = false;
-    else D.dense = P.n_cams <= o.dense_max_cams;
+    else {
+      D.dense = P.n_cams <= o.dense_max_cams;
+      if (!D.dense && P.n_cams <= 16 * (int64_t)o.dense_max_cams) {
+        // Beyond dense_max_cams a dense factorisation is hopeless — unless S is a narrow envelope (a scan trajectory):
+        // then the envelope factorisation costs a latency chain of n/128 panel steps, far less than the hundreds
+        // of implicit-Schur mat-vecs PCG needs per LM iteration.  S is still stored as a full n x n array (only the
+        // envelope is ever touched), so it must fit next to the problem.
+        int rc = ensure_plan();
+        if (rc) return rc;
+        size_t free_b = 0, total_b = 0;
+        cudaMemGetInfo(&free_b, &total_b);
+        const size_t need_b = sizeof(double) * ((size_t)n6 * n6 + cholesky_workspace_doubles(n6) + (size_t)ctx.chol_plan.packed_doubles()) +
+                              sizeof(unsigned) * (size_t)std::max<long long>(P.total_pairs, 0);
+        const size_t have_b = free_b + sizeof(double) * P.S_capacity;
+        if (ctx.chol_plan.use && ctx.chol_plan.fill < 0.15 && have_b > need_b + ((size_t)4 << 30)) D.dense = true;
+      }
+    }
     if (D.dense) {
-      const size_t need = (size_t)n6 * n6 + cholesky_workspace_doubles(n6);
+      int rc = ensure_plan();
+      if (rc) return rc;
+      // workspace after S: L11^-1 blocks + flags, then (multi-GPU) the packed envelope for the all-reduce
+      const size_t packed = (ctx.comm.n_ranks > 1 && ctx.chol_plan.use) ? (size_t)ctx.chol_plan.packed_doubles() : 0;
+      const size_t need = (size_t)n6 * n6 + cholesky_workspace_doubles(n6) + packed;
       if (P.S_capacity < need) {
         if (P.S) cudaFree(P.S);
         P.S = nullptr; P.S_capacity = 0;
@@ -193,11 +219,6 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
         } else {
           P.S_capacity = need;
         }
-      }
-      if (D.dense && !ctx.chol_plan_valid) {  // static per problem: which 128-blocks of S (and of L) can be non-zero
-        int rc = ctx.chol_plan.build(P.n_cams, (int)P.cam_first.size() == P.n_cams ? P.cam_first.data() : nullptr, s);
-        if (rc) return rc;
-        ctx.chol_plan_valid = true;
       }
     }
   }

@@ -184,6 +184,21 @@ def test_envelope_factorisation_equals_dense(ctx, closure):
     assert se["final_cost"] == pytest.approx(so["final_cost"], rel=TOL_COST)
 
 
+def test_auto_uses_the_envelope_beyond_dense_max_cams(ctx):
+    """AUTO: more cameras than dense_max_cams still get the (envelope) Cholesky when the reduced camera matrix is a
+    narrow band; a camera graph without that structure falls back to PCG.  Both agree with the PCG solution."""
+    p = _trajectory(n_cams=840, n_pts=9000, closure=True)
+    o = api.default_options(max_num_iterations=5)
+    o.dense_max_cams = 100
+    sa = ctx.solve_packed(p, opts=o)[2]
+    assert sa["linear_solver_used"] == api.LINEAR_DENSE_SCHUR
+    sp = ctx.solve_packed(p, opts=api.default_options(max_num_iterations=5, linear_solver=api.LINEAR_PCG, pcg_max_iterations=3000))[2]
+    assert sa["final_cost"] == pytest.approx(sp["final_cost"], rel=TOL_COST)
+    q = synth.make_ring(300, 3000, 2, seed=77, skew=0.1)  # two-view tracks over random camera pairs: S is full
+    sq = ctx.solve_packed(q, opts=o)[2]
+    assert sq["linear_solver_used"] == api.LINEAR_PCG
+
+
 def test_tiles_with_many_distinct_cameras(ctx):
     """Two-view tracks over 300 cameras: a 256-observation tile touches well over a hundred distinct cameras, so
     the shared-memory staging of camera rows needs more than the 48 KB default (opt-in dynamic shared memory)."""
