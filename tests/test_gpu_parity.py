@@ -187,9 +187,9 @@ def test_envelope_factorisation_equals_dense(ctx, closure):
 def test_auto_uses_the_envelope_beyond_dense_max_cams(ctx):
     """AUTO: more cameras than dense_max_cams still get the (envelope) Cholesky when the reduced camera matrix is a
     narrow band; a camera graph without that structure falls back to PCG.  Both agree with the PCG solution."""
-    p = _trajectory(n_cams=840, n_pts=9000, closure=True)
+    p = _trajectory(n_cams=1680, n_pts=16000, closure=True)  # 79 panels; the envelope holds ~10 % of the triangle
     o = api.default_options(max_num_iterations=5)
-    o.dense_max_cams = 100
+    o.dense_max_cams = 200
     sa = ctx.solve_packed(p, opts=o)[2]
     assert sa["linear_solver_used"] == api.LINEAR_DENSE_SCHUR
     sp = ctx.solve_packed(p, opts=api.default_options(max_num_iterations=5, linear_solver=api.LINEAR_PCG, pcg_max_iterations=3000))[2]
