@@ -609,11 +609,11 @@ constexpr int LT = 64;             // tile edge
 constexpr int LT_LD = NB + 4;      // operand row stride in shared memory (doubles)
 constexpr int kSyrkLatSmem = 2 * LT * LT_LD * (int)sizeof(double);
 __global__ void __launch_bounds__(128) chol_syrk_col_kernel(double* __restrict__ S, int n, int k0, const int* __restrict__ rb_list,
-                                                            const int* __restrict__ fail) {
+                                                            const int* __restrict__ fail, int a0) {
   extern __shared__ __align__(16) double lsm[];
   double (*sA)[LT_LD] = reinterpret_cast<double (*)[LT_LD]>(lsm);
   double (*sB)[LT_LD] = reinterpret_cast<double (*)[LT_LD]>(lsm + LT * LT_LD);
-  const int a = blockIdx.x >> 2, rh = (blockIdx.x >> 1) & 1, ch = blockIdx.x & 1;
+  const int a = a0 + (blockIdx.x >> 2), rh = (blockIdx.x >> 1) & 1, ch = blockIdx.x & 1;
   if (a == 0 && ch > rh) return;  // strictly upper part of the diagonal block
   const int ri = __ldg(rb_list + a) * NB + rh * LT, rj = __ldg(rb_list) * NB + ch * LT;
   const int ni = min(LT, n - ri), nj = min(LT, n - rj);
@@ -1097,13 +1097,14 @@ int CholAux::init() {
   HSFM_CUDA(cudaEventCreateWithFlags(&ev_panel, cudaEventDisableTiming));
   HSFM_CUDA(cudaEventCreateWithFlags(&ev_rest, cudaEventDisableTiming));
   HSFM_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+  HSFM_CUDA(cudaEventCreateWithFlags(&ev_next, cudaEventDisableTiming));
   return 0;
 }
 void CholAux::destroy() {
   if (graph) { cudaGraphExecDestroy(graph); graph = nullptr; }
   if (!stream) return;
   cudaStreamDestroy(stream);
-  cudaEventDestroy(ev_fork); cudaEventDestroy(ev_panel); cudaEventDestroy(ev_rest); cudaEventDestroy(ev_join);
+  cudaEventDestroy(ev_fork); cudaEventDestroy(ev_panel); cudaEventDestroy(ev_rest); cudaEventDestroy(ev_join); cudaEventDestroy(ev_next);
   stream = nullptr;
 }
 
@@ -1190,9 +1191,12 @@ void CholPlan::destroy() {
   d_fb = nullptr; d_list = nullptr; d_cap = 0; use = false;
 }
 
-// Envelope factorisation: per panel K only the active row blocks R_K are solved and updated.  One panel of
-// look-ahead: the chain stream factors the diagonal block, solves the panel and updates the NEXT panel's column
-// (block K+1 against every active block); the main stream updates the other active pairs behind it.
+// Envelope factorisation: per panel K only the active row blocks R_K are solved and updated.  The critical path is
+// kept as short as the data dependence allows:
+//   chain stream:  diag(K) -> solve ONLY row block K+1 of the panel -> update ONLY the diagonal tile (K+1,K+1) -> diag(K+1)
+//   main stream:   after diag(K): solve the other active row blocks; after the chain's solve: the rest of column
+//                  K+1; then every other active pair.  All of it has one whole diagonal-block factorisation to finish
+//                  before the chain needs it (tile (K+2,K+1) at the next step).
 static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches,
                                 const CholPlan& pl, int n_sm) {
   static const bool no_la = getenv("HSFM_NO_LOOKAHEAD") != nullptr;
@@ -1202,6 +1206,13 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
     cudaEventRecord(aux->ev_fork, s);
     cudaStreamWaitEvent(s2, aux->ev_fork, 0);
   }
+  auto trsm = [&](cudaStream_t st, int k0, double* Linv, const int* list, int cnt) {
+    int rows_per = 64;  // strips of 8..64 rows: as many CTAs as fit in ONE wave (the kernel runs one CTA per SM)
+    while (rows_per > 8 && cnt * (NB / (rows_per >> 1)) <= n_sm) rows_per >>= 1;
+    const int spb = NB / rows_per;
+    chol_trsm_strip_kernel<<<cnt * spb, 256, rows_per * TS_LD * (int)sizeof(double), st>>>(S, n, k0, Linv, rows_per, fail_flag, list, spb);
+    ++*launches;
+  };
   bool rest_pending = false;
   for (int K = 0, k0 = 0; K < pl.panels; ++K, k0 += NB) {
     const int kb = min(NB, n - k0);
@@ -1209,30 +1220,30 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
     chol_diag_kernel<<<1, 256, kDiagSmem, s2>>>(S, n, k0, kb, Linv, fail_flag);
     ++*launches;
     const int cnt = pl.cnt[K];
-    if (cnt == 0) {  // nothing below this panel; keep the chain's "one step behind" guarantee
-      if (la && rest_pending) { cudaStreamWaitEvent(s2, aux->ev_rest, 0); rest_pending = false; }
-      continue;
-    }
-    const int* list = pl.d_list + pl.off[K];
-    int rows_per = 64;  // strips of 8..64 rows: as many CTAs as fit in ONE wave (the kernel runs one CTA per SM)
-    while (rows_per > 8 && cnt * (NB / (rows_per >> 1)) <= n_sm) rows_per >>= 1;
-    const int spb = NB / rows_per;
-    chol_trsm_strip_kernel<<<cnt * spb, 256, rows_per * TS_LD * (int)sizeof(double), s2>>>(S, n, k0, Linv, rows_per, fail_flag, list, spb);
-    ++*launches;
-    const bool has_col = pl.list[(size_t)pl.off[K]] == K + 1;
-    const int rest_cnt = has_col ? cnt - 1 : cnt;
-    if (la && rest_cnt > 0) cudaEventRecord(aux->ev_panel, s2);
-    // column K+1 was last written by the main stream's update of step K-1; diag/trsm above only needed the
-    // updates up to step K-2, which the chain waited for one step ago
+    // everything the main stream did one step ago must be complete before the chain touches column K+1 / block K+1
     if (la && rest_pending) { cudaStreamWaitEvent(s2, aux->ev_rest, 0); rest_pending = false; }
+    if (cnt == 0) continue;
+    const int* list = pl.d_list + pl.off[K];
+    const bool has_col = pl.list[(size_t)pl.off[K]] == K + 1;
+    if (la) cudaEventRecord(aux->ev_panel, s2);  // diag(K) done
     if (has_col) {
-      chol_syrk_col_kernel<<<4 * cnt, 128, kSyrkLatSmem, s2>>>(S, n, k0, list, fail_flag);
+      trsm(s2, k0, Linv, list, 1);               // L(K+1, K)
+      if (la && cnt > 1) cudaEventRecord(aux->ev_next, s2);
+      chol_syrk_col_kernel<<<4, 128, kSyrkLatSmem, s2>>>(S, n, k0, list, fail_flag, 0);  // tile (K+1, K+1)
       ++*launches;
     }
+    const int rest_cnt = has_col ? cnt - 1 : cnt;
     if (rest_cnt > 0) {
+      const int* rl = has_col ? list + 1 : list;
       if (la) cudaStreamWaitEvent(s, aux->ev_panel, 0);
+      trsm(s, k0, Linv, rl, rest_cnt);
+      if (has_col) {
+        if (la) cudaStreamWaitEvent(s, aux->ev_next, 0);
+        chol_syrk_col_kernel<<<4 * rest_cnt, 128, kSyrkLatSmem, s>>>(S, n, k0, list, fail_flag, 1);  // tiles (I, K+1), I > K+1
+        ++*launches;
+      }
       const int tiles = rest_cnt * (rest_cnt + 1);
-      chol_syrk_kernel<<<min(tiles, 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 0, -1, tiles, 0, fail_flag, has_col ? list + 1 : list);
+      chol_syrk_kernel<<<min(tiles, 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 0, -1, tiles, 0, fail_flag, rl);
       ++*launches;
       if (la) { cudaEventRecord(aux->ev_rest, s); rest_pending = true; }
     }

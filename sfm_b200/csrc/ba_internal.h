@@ -170,7 +170,7 @@ void launch_mirror_lower(Problem& P, cudaStream_t s);   // S upper <- lower (par
 // auxiliary high-priority stream + events for the panel look-ahead of the factorisation
 struct CholAux {
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_panel = nullptr, ev_rest = nullptr, ev_join = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_panel = nullptr, ev_rest = nullptr, ev_join = nullptr, ev_next = nullptr;
   // captured launch sequence of the envelope factorisation (static per problem: same S, workspace and plan)
   cudaGraphExec_t graph = nullptr;
   const void* g_S = nullptr; const void* g_ws = nullptr; const void* g_fail = nullptr; const void* g_stream = nullptr;
