@@ -3,9 +3,9 @@
 //
 // Right-looking blocked factorisation of the lower triangle of a row-major n×n matrix with
 // 128-wide panels.  Per panel three launches, enqueued back to back (no host synchronisation):
-//   1. chol_diag_kernel   one CTA factors the 128×128 diagonal block with the block held in
-//                         registers (8×8 per thread, 2-D cyclic) and also forms L11^-1 by recursive
-//                         doubling, so that
+//   1. chol_diag_kernel   one CTA factors the 128×128 diagonal block in shared memory (4 x 32 sub-blocks:
+//                         one warp runs the pivot chain, six work in its shadow) and also forms L11^-1,
+//                         so that
 //   2. chol_gemm<TRSM>    the panel solve  L21 = A21 L11^-T  is a GEMM, and
 //   3. chol_gemm<SYRK>    the trailing update  A22 -= L21 L21^T  (lower tiles only)
 // both run on the FP64 tensor path: 128×128 CTA tiles, K staged through shared memory with
@@ -42,39 +42,21 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
 // 1. diagonal block: factor + inverse, one CTA, blocked 4 x 32
 // ---------------------------------------------------------------------------------------------
 // The 128x128 block lives in shared memory as its ten lower 32x32 sub-blocks (row stride 36 doubles:
-// DMMA fragment loads in either orientation are bank-conflict free).  Per sub-block column kb:
-//   warp 0 factors the 32x32 diagonal sub-block in registers (one row per lane, shuffles, no barrier),
-//   one thread per row solves the sub-panel below it by substitution,
-//   all eight warps apply the trailing update with DMMA tiles.
-// L11^-1 then follows by block forward substitution: four warps invert the diagonal sub-blocks in
-// registers, three levels of DMMA block products fill the sub-diagonals.  ~128 barrier-separated column
-// steps of the previous version become ~20 phases.
+// DMMA fragment loads in either orientation are bank-conflict free).  The kernel is a latency chain —
+// 128 dependent pivots — so the work is split by whether it is ON that chain:
+//   chain  (per sub-block column kq): warp 0 runs the 32 pivots of sub-block (kq,kq) (warp_chol32);
+//          all warps scale it to L and put it out (diag_scale_out); warp 0 inverts it in place on DMMA
+//          (warp_trinv32_dmma); all warps form L(kq+1,kq) as a product with that inverse and update
+//          sub-block (kq+1,kq+1) alone (diag_chain_step) — the next pivots can start;
+//   shadow (warps 1,2,3,5,6,7 while warp 0 runs the pivots of kq+1; warp 4 shares warp 0's scheduler and
+//          idles): the rest of the sub-panel, the rest of the trailing update, L out to global, and the
+//          rows of L11^-1 that are already determined (diag_shadow).
+// After the fourth sub-block only the last row of L11^-1 remains (three 32^3 products).
 constexpr int SB = 32;             // sub-block edge
 constexpr int LB = SB + 4;         // sub-block row stride in shared memory (doubles)
 constexpr int SBLK = SB * LB;      // doubles per stored sub-block
 __device__ __forceinline__ constexpr int blk_id(int bi, int bj) { return bi * (bi + 1) / 2 + bj; }  // bj <= bi
 
-// One 8x8 tile of A(32xK=32 block, rows m) * B over the full K = 32.  B_KN: B is stored [k][n], else [n][k].
-template <bool B_KN>
-__device__ __forceinline__ void tile_mma32(double& c0, double& c1, const double* __restrict__ A, const double* __restrict__ B, int ti, int tj,
-                                           int lane) {
-  const int fr = lane >> 2, fk = lane & 3;
-#pragma unroll
-  for (int ks = 0; ks < SB / 4; ++ks) {
-    const double a = A[(ti * 8 + fr) * LB + ks * 4 + fk];
-    const double b = B_KN ? B[(ks * 4 + fk) * LB + tj * 8 + fr] : B[(tj * 8 + fr) * LB + ks * 4 + fk];
-    dmma884(c0, c1, a, b);
-  }
-}
-
-// Cholesky of a 32x32 sub-block by one warp.  Lane r keeps the not-yet-eliminated part of row r in a
-// register window that shifts left by one column per step, so the step body is the same ~100
-// instructions for every column (a fully unrolled triangle would be ~6000 instructions executed once —
-// instruction-fetch bound).  The pivot column is broadcast through `col` (64 doubles of shared memory,
-// written twice so that col[j+c] needs no wrap).  The NEXT pivot is formed first in every step and its
-// reciprocal square root is started before the rest of the row update, so the rsqrt latency — the serial
-// chain of the whole factorisation — overlaps the 30 remaining FMAs.  D (row stride LB) receives L (strict
-// upper zeroed), dinv[r] = 1/L[r][r].  Returns 0 or the 1-based failing column.
 // 1/d and 1/sqrt(d) from the hardware seed (MUFU, ~2^-22 relative) and two Newton steps of fused multiply-adds:
 // full double precision for normal d > 0 without the special-case branches of the library routines.  The
 // factorisation checks d > 0 and finiteness itself.
@@ -95,161 +77,449 @@ __device__ __forceinline__ double fast_rsqrt(double d) {
   return fma(0.5 * y, e, y);
 }
 
-__device__ __forceinline__ int warp_chol32(double* __restrict__ D, double* __restrict__ col, double* __restrict__ dinv, int lane) {
+#ifdef HSFM_DIAG_TIMING
+__device__ long long g_diag_clk[40];
+__device__ long long g_step_clk[40];
+__device__ unsigned g_mask[40];
+__device__ unsigned g_mask2[40];
+#define DIAG_TICK(k) do { const unsigned am_ = __activemask(); if (threadIdx.x == 0) { g_diag_clk[k] = clock64(); g_mask2[k] = am_; } __syncwarp(); } while (0)
+#ifdef HSFM_STEP_TIMING
+#define STEP_TICK(k) do { const unsigned am_ = __activemask(); if (threadIdx.x == 0) { g_step_clk[k] = clock64(); g_mask[k] = am_; } __syncwarp(); } while (0)
+#else
+#define STEP_TICK(k) do { } while (0)
+#endif
+#else
+#define DIAG_TICK(k) do { } while (0)
+#define STEP_TICK(k) do { } while (0)
+#endif
+
+// 1/d with the second Newton correction taken as e*e (1 - d*y1 = e^2 exactly): three dependent multiply-adds
+// after the seed instead of four; <= 2 ulp.
+__device__ __forceinline__ double fast_rcp3(double d) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+  const double e = fma(-d, y, 1.0);
+  const double y1 = fma(y, e, y);
+  const double e2 = e * e;
+  return fma(y1, e2, y1);
+}
+
+// One pivot step of warp_chol32.  PAR = j & 1 (fixes which history entries are 16-byte pairs), W = live window
+// width: columns c < W are updated, a[c-1] = a[c] - u h[c].
+template <int PAR, int W>
+__device__ __forceinline__ void chol32_step(double (&a)[SB], double* __restrict__ hist, int j, int lane, double& r, double& sq, double& g, int& bad) {
+  STEP_TICK(j);
+  const double* hs = hist + j * SB + j;  // hs[c] = A(j)[j+c][j]
+  const double dn = fma(-sq, r, g);      // pivot j+1 (don't-care at j = 31): the serial chain
+  const double rn = fast_rcp3(dn);
+  const double nu = -(a[0] * r);
+  if (PAR == 0) {
+    a[0] = fma(nu, hs[1], a[1]);
+#pragma unroll
+    for (int c = 2; c + 1 < W; c += 2) {
+      const double2 h2 = *reinterpret_cast<const double2*>(hs + c);
+      a[c - 1] = fma(nu, h2.x, a[c]);
+      a[c] = fma(nu, h2.y, a[c + 1]);
+    }
+  } else {
+#pragma unroll
+    for (int c = 1; c + 1 < W; c += 2) {
+      const double2 h2 = *reinterpret_cast<const double2*>(hs + c);
+      a[c - 1] = fma(nu, h2.x, a[c]);
+      a[c] = fma(nu, h2.y, a[c + 1]);
+    }
+    a[W - 2] = fma(nu, hs[W - 1], a[W - 1]);
+  }
+  hist[(j + 1) * SB + lane] = a[0];
+  const double hq = __shfl_sync(0xffffffffu, a[0], (j + 2) & 31), gq = __shfl_sync(0xffffffffu, a[1], (j + 2) & 31);
+  sq = hq * hq;
+  g = gq;
+  if (j + 1 < SB && !bad && !(dn > 0.0 && dn < 1e300)) bad = j + 2;
+  r = rn;
+  __syncwarp();
+}
+
+// Cholesky of a 32x32 sub-block by one warp, lane r = row r in a register window that shifts left one column
+// per step.  The serial chain of the whole factorisation is pivot -> 1/pivot -> next pivot; everything else is
+// kept off it:
+//   * step j publishes the lanes' next column entries A(j+1)[.][j+1] to slot j+1 of a history buffer (the
+//     sub-block's own shared memory: its rows are in registers); the next-but-one pivot's two ingredients come
+//     by shuffle from the lane that owns them, so the next pivot is d(j+1) = g - h*h*r with h*h ready before r;
+//   * the reciprocal square roots that scale L are taken once, after the loop, 32 in parallel;
+//   * the window narrows every eight steps (32, 24, 16, 8 columns), history entries are read as 16-byte pairs.
+// D (row stride LB) receives L (strict upper zeroed), dinv[r] = 1/L[r][r].  Returns 0 or the 1-based failing column.
+__device__ __noinline__ int warp_chol32(double* __restrict__ D, double* __restrict__ dinv, int lane) {
+  STEP_TICK(34);
   double a[SB];
 #pragma unroll
-  for (int c = 0; c < SB; ++c) a[c] = D[lane * LB + c];
-  int bad = 0;
-  // The serial chain of the whole factorisation is pivot -> 1/pivot -> next column -> next pivot.  Only the
-  // RECIPROCAL sits on it (seed + four dependent multiply-adds); the reciprocal square root that scales the
-  // stored column is computed beside it.
-  double d = __shfl_sync(0xffffffffu, a[0], 0);
-  double r = fast_rcp(d);
-#pragma unroll 1
-  for (int j = 0; j < SB; ++j) {
-    if (!(d > 0.0) || !isfinite(d)) { bad = j + 1; break; }  // uniform: d is a broadcast
-    col[lane] = a[0];
-    col[lane + SB] = a[0];
-    __syncwarp();
-    const double u = a[0] * r;  // A[row][j] / pivot
-    const double a0n = fma(-u, col[j + 1], a[1]);
-    const double dn = __shfl_sync(0xffffffffu, a0n, (j + 1) & 31);
-    const double rn = fast_rcp(dn);
-    const double inv = fast_rsqrt(d);
-    double l = a[0] * inv;
-    if (lane == j) { l = d * inv; dinv[j] = inv; }
-    D[lane * LB + j] = (lane >= j) ? l : 0.0;
-#pragma unroll
-    for (int c = 2; c < SB; ++c) a[c - 1] = fma(-u, col[j + c], a[c]);  // columns past 31 hold don't-care values
-    a[0] = a0n;
-    d = dn;
-    r = rn;
-    __syncwarp();
+  for (int c = 0; c < SB; c += 2) {
+    const double2 v = *reinterpret_cast<const double2*>(D + lane * LB + c);
+    a[c] = v.x; a[c + 1] = v.y;
   }
+  __syncwarp();
+  double* hist = D;  // slot j, entry i: A(j)[i][j]  (unscaled column j of L); 33 slots of 32 fit in 32 x LB
+  hist[lane] = a[0];
+  const double d = __shfl_sync(0xffffffffu, a[0], 0);
+  int bad = (d > 0.0 && d < 1e300) ? 0 : 1;
+  double r = fast_rcp(d);
+  const double h1 = __shfl_sync(0xffffffffu, a[0], 1);
+  double sq = h1 * h1, g = __shfl_sync(0xffffffffu, a[1], 1);
+  __syncwarp();
+#pragma unroll 1
+  for (int j = 0; j < 8; j += 2) { chol32_step<0, 32>(a, hist, j, lane, r, sq, g, bad); chol32_step<1, 32>(a, hist, j + 1, lane, r, sq, g, bad); }
+#pragma unroll 1
+  for (int j = 8; j < 16; j += 2) { chol32_step<0, 24>(a, hist, j, lane, r, sq, g, bad); chol32_step<1, 24>(a, hist, j + 1, lane, r, sq, g, bad); }
+#pragma unroll 1
+  for (int j = 16; j < 24; j += 2) { chol32_step<0, 16>(a, hist, j, lane, r, sq, g, bad); chol32_step<1, 16>(a, hist, j + 1, lane, r, sq, g, bad); }
+#pragma unroll 1
+  for (int j = 24; j < 32; j += 2) { chol32_step<0, 8>(a, hist, j, lane, r, sq, g, bad); chol32_step<1, 8>(a, hist, j + 1, lane, r, sq, g, bad); }
+  STEP_TICK(32);
   return bad;
 }
 
-// Inverse of the lower-triangular 32x32 sub-block D by one warp, written to X (both row stride LB; X may
-// alias D).  Lane c solves L x = e_c for column c of the inverse by forward substitution, entirely in its own
-// registers: every lane runs the same (i, k) loop, the L[i][k] are warp-uniform shared-memory broadcasts and
-// the leading zeros of the column need no predicate (they multiply through).  No shuffles, no barriers inside
-// — a 32-step chain of independent multiply-adds instead of 32 publish/eliminate round trips.
-__device__ __forceinline__ void warp_trinv32(const double* D, const double* __restrict__ dinv, double* X, int lane) {
-  double x[SB];
+// After warp_chol32: all eight warps turn the pivot-column history (slot j, entry i = A(j)[i][j], in the sub-block's
+// own storage) into L[i][j] = A(j)[i][j] / sqrt(A(j)[j][j]) in place (row stride LB, strict upper zeroed),
+// dinv[j] = 1/L[j][j], and put the lower triangle out to global memory.  Thread = (row lane, four columns warp*4..).
+__device__ __forceinline__ void diag_scale_out(double* __restrict__ D, double* __restrict__ dinv, double* __restrict__ gdst, int n, int rows_valid) {
+  const int lane = threadIdx.x & 31, c4 = (threadIdx.x >> 5) * 4;
+  double l[4], iv[4];
 #pragma unroll
-  for (int i = 0; i < SB; ++i) {
-    double s0 = (i == lane) ? 1.0 : 0.0, s1 = 0.0;
-#pragma unroll
-    for (int k = 0; k + 1 < i; k += 2) {
-      const double2 l = *reinterpret_cast<const double2*>(D + i * LB + k);
-      s0 = fma(-l.x, x[k], s0);
-      s1 = fma(-l.y, x[k + 1], s1);
-    }
-    if (i & 1) s0 = fma(-D[i * LB + i - 1], x[i - 1], s0);
-    x[i] = (s0 + s1) * dinv[i];
+  for (int q = 0; q < 4; ++q) {
+    const int j = c4 + q;
+    iv[q] = fast_rsqrt(D[j * SB + j]);
+    l[q] = (lane >= j) ? D[j * SB + lane] * iv[q] : 0.0;
   }
-  __syncwarp();  // every lane has read all of D before anyone overwrites it
+  __syncthreads();
+  *reinterpret_cast<double2*>(D + lane * LB + c4) = make_double2(l[0], l[1]);
+  *reinterpret_cast<double2*>(D + lane * LB + c4 + 2) = make_double2(l[2], l[3]);
 #pragma unroll
-  for (int i = 0; i < SB; ++i) X[i * LB + lane] = x[i];
+  for (int q = 0; q < 4; ++q)
+    if (lane == c4 + q) dinv[lane] = iv[q];
+  if (lane < rows_valid) {
+    double* dst = gdst + (size_t)lane * n + c4;
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+      const int c = c4 + 2 * p;
+      if (c + 1 <= lane) *reinterpret_cast<double2*>(dst + 2 * p) = make_double2(l[2 * p], l[2 * p + 1]);
+      else if (c == lane) dst[2 * p] = l[2 * p];
+    }
+  }
+  __syncthreads();
 }
 
-#ifdef HSFM_DIAG_TIMING
-__device__ long long g_diag_clk[32];
-#define DIAG_TICK(k) do { if (threadIdx.x == 0) g_diag_clk[k] = clock64(); } while (0)
-#else
-#define DIAG_TICK(k) do { } while (0)
-#endif
+// In-place inverse of the lower-triangular 32x32 sub-block D (row stride LB, strict upper zero) by one warp, by
+// recursive doubling on DMMA: the four 8x8 diagonal blocks by substitution in registers (lane = block*8 + column),
+// then X21 = -X22 (L21 X11) at block size 8 and 16.  ~1/5 of the latency of a 32-step substitution.  scr: 320 doubles.
+__device__ __noinline__ void warp_trinv32_dmma(double* D, const double* __restrict__ dinv, double* scr, int lane) {
+  const int fr = lane >> 2, fk = lane & 3;
+  {
+    const int b = lane >> 3, c = lane & 7;
+    const double* Lb = D + (b * 8) * LB + b * 8;
+    double x[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      double s = (i == c) ? 1.0 : 0.0;
+#pragma unroll
+      for (int k = 0; k < i; ++k) s = fma(-Lb[i * LB + k], x[k], s);
+      x[i] = s * dinv[b * 8 + i];
+    }
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 8; ++i) D[(b * 8 + i) * LB + b * 8 + c] = x[i];
+    __syncwarp();
+  }
+  // block size 8: pairs (0,1) and (2,3)
+  {
+    double t0[2] = {0.0, 0.0}, t1[2] = {0.0, 0.0};
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+      const double* L21 = D + (16 * p + 8) * LB + 16 * p;
+      const double* X11 = D + (16 * p) * LB + 16 * p;
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks) dmma884(t0[p], t1[p], L21[fr * LB + ks * 4 + fk], X11[(ks * 4 + fk) * LB + fr]);
+    }
+#pragma unroll
+    for (int p = 0; p < 2; ++p) *reinterpret_cast<double2*>(scr + p * 96 + fr * 12 + 2 * fk) = make_double2(t0[p], t1[p]);
+    __syncwarp();
+    double x0[2] = {0.0, 0.0}, x1[2] = {0.0, 0.0};
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+      const double* X22 = D + (16 * p + 8) * LB + 16 * p + 8;
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks) dmma884(x0[p], x1[p], X22[fr * LB + ks * 4 + fk], scr[p * 96 + (ks * 4 + fk) * 12 + fr]);
+    }
+#pragma unroll
+    for (int p = 0; p < 2; ++p)
+      *reinterpret_cast<double2*>(D + (16 * p + 8 + fr) * LB + 16 * p + 2 * fk) = make_double2(-x0[p], -x1[p]);
+    __syncwarp();
+  }
+  // block size 16
+  {
+    double t0[4], t1[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { t0[q] = 0.0; t1[q] = 0.0; }
+    const double* L21 = D + 16 * LB;
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int ti = q >> 1, tj = q & 1;
+        dmma884(t0[q], t1[q], L21[(ti * 8 + fr) * LB + ks * 4 + fk], D[(ks * 4 + fk) * LB + tj * 8 + fr]);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int ti = q >> 1, tj = q & 1;
+      *reinterpret_cast<double2*>(scr + (ti * 8 + fr) * 20 + tj * 8 + 2 * fk) = make_double2(t0[q], t1[q]);
+    }
+    __syncwarp();
+    double x0[4], x1[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { x0[q] = 0.0; x1[q] = 0.0; }
+    const double* X22 = D + 16 * LB + 16;
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int ti = q >> 1, tj = q & 1;
+        dmma884(x0[q], x1[q], X22[(ti * 8 + fr) * LB + ks * 4 + fk], scr[(ks * 4 + fk) * 20 + tj * 8 + fr]);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int ti = q >> 1, tj = q & 1;
+      *reinterpret_cast<double2*>(D + (16 + ti * 8 + fr) * LB + tj * 8 + 2 * fk) = make_double2(-x0[q], -x1[q]);
+    }
+    __syncwarp();
+  }
+}
 
-// Trailing update of step KQ inside the diagonal block: the warp's T = 12 / 6 / 2 tiles share one k loop.
+// Barrier of the six "shadow" warps (1,2,3,5,6,7) that work beside the factoring warp 0; warp 4 shares warp 0's
+// scheduler and stays idle.
+__device__ __forceinline__ void shadow_sync() { asm volatile("bar.sync 1, 192;" ::: "memory"); }
+
+// One 8x8 output tile of the 32x32 block product A * B over K = 32, accumulated into (c0, c1).  A is [m][k];
+// B is [k][n] when B_KN, else [n][k] (i.e. the product is A * B^T).
+template <bool B_KN>
+__device__ __forceinline__ void tile_acc32(double& c0, double& c1, const double* __restrict__ A, const double* __restrict__ B, int ti, int tj,
+                                           int fr, int fk) {
+#pragma unroll
+  for (int ks = 0; ks < SB / 4; ++ks) {
+    const double a = A[(ti * 8 + fr) * LB + ks * 4 + fk];
+    const double b = B_KN ? B[(ks * 4 + fk) * LB + tj * 8 + fr] : B[(tj * 8 + fr) * LB + ks * 4 + fk];
+    dmma884(c0, c1, a, b);
+  }
+}
+
+// Work of step KQ that is NOT on the chain, done by warps 1..7 while warp 0 factors sub-block KQ+1:
+//   (a) the trailing update of every sub-block but (KQ+1,KQ+1),   (b) L(.,KQ) below the diagonal -> global,
+//   (c1) row KQ of the inverse  X(KQ,j) = -X(KQ,KQ) Y(KQ,j),     (d) that row -> global,
+//   (c2) Y(KQ+1,j) = sum_{k=j..KQ} L(KQ+1,k) X(k,j) over L(KQ+1,j)   (the part of row KQ+1 that needs no X(KQ+1,KQ+1)).
 template <int KQ>
-__device__ __forceinline__ void diag_trailing(double* sL, int warp, int lane) {
-  constexpr int M = 3 - KQ, T = M * (M + 1) / 2 * 16 / 8;
-  const int fr = lane >> 2, fk = lane & 3;
-  double c0[T], c1[T];
-  const double* pa[T];
-  const double* pb[T];
-  double2* pd[T];
-#pragma unroll
-  for (int q = 0; q < T; ++q) {
-    const int t = warp + 8 * q, b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
-    const int di = b < 1 ? 0 : b < 3 ? 1 : 2, dj = b - di * (di + 1) / 2;
-    const int bi = KQ + 1 + di, bj = KQ + 1 + dj;
-    pa[q] = sL + blk_id(bi, KQ) * SBLK + (ti * 8 + fr) * LB + fk;
-    pb[q] = sL + blk_id(bj, KQ) * SBLK + (tj * 8 + fr) * LB + fk;
-    pd[q] = reinterpret_cast<double2*>(sL + blk_id(bi, bj) * SBLK + (ti * 8 + fr) * LB + tj * 8 + 2 * fk);
-    c0[q] = 0.0; c1[q] = 0.0;
-  }
-#pragma unroll
-  for (int ks = 0; ks < SB / 4; ++ks) {
-#pragma unroll
-    for (int q = 0; q < T; ++q) dmma884(c0[q], c1[q], pa[q][ks * 4], pb[q][ks * 4]);
-  }
-#pragma unroll
-  for (int q = 0; q < T; ++q) {
-    double2 v = *pd[q];
-    v.x -= c0[q]; v.y -= c1[q];
-    *pd[q] = v;
-  }
-}
-
-// Sub-diagonal D of the inverse: X(i,j) = - sum_{k=j}^{i-1} M(i,k) X(k,j), j = i - D.  X(j,j) comes from shared
-// memory, the X(k,j) of earlier sub-diagonals from the output block itself (L2).  The warp's T = 6 / 4 / 2
-// tiles advance together; the global fragments of a product are all fetched before its multiply-adds.
-template <int D>
-__device__ __forceinline__ void inv_level(const double* sL, double* Linv, int warp, int lane) {
-  constexpr int T = 2 * (4 - D);
-  const int fr = lane >> 2, fk = lane & 3;
-  double c0[T], c1[T];
-#pragma unroll
-  for (int q = 0; q < T; ++q) { c0[q] = 0.0; c1[q] = 0.0; }
-#pragma unroll
-  for (int ks = 0; ks < SB / 4; ++ks) {
+__device__ __forceinline__ void diag_shadow(double* sL, double* __restrict__ A, int n, int k0, int kb, double* __restrict__ Linv, int tid7) {
+  const int w7 = tid7 >> 5, lane = tid7 & 31, fr = lane >> 2, fk = lane & 3;
+  // (a0) the rows of the sub-panel below sub-block (KQ+1,KQ): L(bi,KQ) = P(bi,KQ) X(KQ,KQ)^T, bi >= KQ+2
+  if constexpr (KQ < 2) {
+    constexpr int NT = (2 - KQ) * 16, T = (NT + 5) / 6;
+    double c0[T], c1[T];
+    const double* X = sL + blk_id(KQ, KQ) * SBLK;
 #pragma unroll
     for (int q = 0; q < T; ++q) {
-      const int t = warp + 8 * q, b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
-      const int i = D + b, j = b;
-      dmma884(c0[q], c1[q], sL[blk_id(i, j) * SBLK + (ti * 8 + fr) * LB + ks * 4 + fk],
-              sL[blk_id(j, j) * SBLK + (ks * 4 + fk) * LB + tj * 8 + fr]);
+      const int t = w7 + 6 * q;
+      c0[q] = 0.0; c1[q] = 0.0;
+      if (t < NT) {
+        const int bi = KQ + 2 + (t >> 4), tile = t & 15;
+        tile_acc32<false>(c0[q], c1[q], sL + blk_id(bi, KQ) * SBLK, X, tile >> 2, tile & 3, fr, fk);
+      }
     }
-  }
-#pragma unroll
-  for (int kk = 1; kk < D; ++kk) {
-    double bq[T][SB / 4];
+    shadow_sync();
 #pragma unroll
     for (int q = 0; q < T; ++q) {
-      const int t = warp + 8 * q, b = t >> 4, tile = t & 15, tj = tile & 3;
-      const int j = b, k = j + kk;
-#pragma unroll
-      for (int ks = 0; ks < SB / 4; ++ks) bq[q][ks] = __ldcg(Linv + (size_t)(k * SB + ks * 4 + fk) * NB + j * SB + tj * 8 + fr);
+      const int t = w7 + 6 * q;
+      if (t < NT) {
+        const int bi = KQ + 2 + (t >> 4), tile = t & 15, ti = tile >> 2, tj = tile & 3;
+        *reinterpret_cast<double2*>(sL + blk_id(bi, KQ) * SBLK + (ti * 8 + fr) * LB + tj * 8 + 2 * fk) = make_double2(c0[q], c1[q]);
+      }
     }
+    shadow_sync();
+  }
+  // (a)
+  {
+    constexpr int NBLK = KQ == 0 ? 5 : KQ == 1 ? 2 : 0;
+    constexpr int BI[5] = {KQ == 0 ? 2 : 3, KQ == 0 ? 2 : 3, 3, 3, 3};
+    constexpr int BJ[5] = {KQ == 0 ? 1 : 2, KQ == 0 ? 2 : 3, 1, 2, 3};
+    constexpr int T = (NBLK * 16 + 5) / 6;
 #pragma unroll
-    for (int ks = 0; ks < SB / 4; ++ks) {
+    for (int q = 0; q < T; ++q) {
+      const int t = w7 + 6 * q;
+      if (t < NBLK * 16) {
+        const int b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
+        int bi = BI[0], bj = BJ[0];
 #pragma unroll
-      for (int q = 0; q < T; ++q) {
-        const int t = warp + 8 * q, b = t >> 4, tile = t & 15, ti = tile >> 2;
-        const int i = D + b, k = b + kk;
-        dmma884(c0[q], c1[q], sL[blk_id(i, k) * SBLK + (ti * 8 + fr) * LB + ks * 4 + fk], bq[q][ks]);
+        for (int z = 1; z < 5; ++z)
+          if (b == z) { bi = BI[z]; bj = BJ[z]; }
+        double c0 = 0.0, c1 = 0.0;
+        tile_acc32<false>(c0, c1, sL + blk_id(bi, KQ) * SBLK, sL + blk_id(bj, KQ) * SBLK, ti, tj, fr, fk);
+        double2* pd = reinterpret_cast<double2*>(sL + blk_id(bi, bj) * SBLK + (ti * 8 + fr) * LB + tj * 8 + 2 * fk);
+        double2 v = *pd;
+        v.x -= c0; v.y -= c1;
+        *pd = v;
       }
     }
   }
+  // (b)
+  {
+    constexpr int NE = (3 - KQ) * SB * (SB / 2);
+    for (int e = tid7; e < NE; e += 192) {
+      const int blk = e / (SB * SB / 2), rem = e - blk * (SB * SB / 2), r = rem >> 4, c = (rem & 15) * 2;
+      const int i = (KQ + 1 + blk) * SB + r;
+      if (i < kb)
+        *reinterpret_cast<double2*>(A + (size_t)(k0 + i) * n + k0 + KQ * SB + c) =
+            *reinterpret_cast<const double2*>(sL + blk_id(KQ + 1 + blk, KQ) * SBLK + r * LB + c);
+    }
+  }
+  shadow_sync();
+  // (c1)
+  if constexpr (KQ >= 1) {
+    constexpr int T = (KQ * 16 + 5) / 6;
+    double c0[T], c1[T];
 #pragma unroll
-  for (int q = 0; q < T; ++q) {
-    const int t = warp + 8 * q, b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
-    const int i = D + b, j = b;
-    *reinterpret_cast<double2*>(Linv + (size_t)(i * SB + ti * 8 + fr) * NB + j * SB + tj * 8 + 2 * fk) = make_double2(-c0[q], -c1[q]);
+    for (int q = 0; q < T; ++q) {
+      const int t = w7 + 6 * q;
+      c0[q] = 0.0; c1[q] = 0.0;
+      if (t < KQ * 16) {
+        const int j = t >> 4, tile = t & 15;
+        tile_acc32<true>(c0[q], c1[q], sL + blk_id(KQ, KQ) * SBLK, sL + blk_id(KQ, j) * SBLK, tile >> 2, tile & 3, fr, fk);
+      }
+    }
+    shadow_sync();
+#pragma unroll
+    for (int q = 0; q < T; ++q) {
+      const int t = w7 + 6 * q;
+      if (t < KQ * 16) {
+        const int j = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
+        *reinterpret_cast<double2*>(sL + blk_id(KQ, j) * SBLK + (ti * 8 + fr) * LB + tj * 8 + 2 * fk) = make_double2(-c0[q], -c1[q]);
+      }
+    }
+    shadow_sync();
+  }
+  // (d)
+  for (int e = tid7; e < SB * (NB / 2); e += 192) {
+    const int r = e >> 6, cc = (e & 63) * 2, bj = cc >> 5;
+    double2 v = make_double2(0.0, 0.0);
+    if (bj <= KQ) v = *reinterpret_cast<const double2*>(sL + blk_id(KQ, bj) * SBLK + r * LB + (cc & 31));
+    *reinterpret_cast<double2*>(Linv + (size_t)(KQ * SB + r) * NB + cc) = v;
+  }
+  // (c2)
+  {
+    constexpr int T = ((KQ + 1) * 16 + 5) / 6;
+    double c0[T], c1[T];
+#pragma unroll
+    for (int q = 0; q < T; ++q) {
+      const int t = w7 + 6 * q;
+      c0[q] = 0.0; c1[q] = 0.0;
+      if (t < (KQ + 1) * 16) {
+        const int j = t >> 4, tile = t & 15;
+#pragma unroll
+        for (int k = 0; k <= KQ; ++k)
+          if (k >= j) tile_acc32<true>(c0[q], c1[q], sL + blk_id(KQ + 1, k) * SBLK, sL + blk_id(k, j) * SBLK, tile >> 2, tile & 3, fr, fk);
+      }
+    }
+    shadow_sync();
+#pragma unroll
+    for (int q = 0; q < T; ++q) {
+      const int t = w7 + 6 * q;
+      if (t < (KQ + 1) * 16) {
+        const int j = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
+        *reinterpret_cast<double2*>(sL + blk_id(KQ + 1, j) * SBLK + (ti * 8 + fr) * LB + tj * 8 + 2 * fk) = make_double2(c0[q], c1[q]);
+      }
+    }
   }
 }
 
-// 10 sub-blocks + 1/diag + pivot-column scratch: 94 KB, so that (with <= 128 registers per thread) the kernel
+// The part of step KQ that IS on the chain, all eight warps: sub-block (KQ+1,KQ) of the panel as a product with the
+// inverse, L(KQ+1,KQ) = P(KQ+1,KQ) X(KQ,KQ)^T, then the trailing update of sub-block (KQ+1,KQ+1) alone.
+template <int KQ>
+__device__ __forceinline__ void diag_chain_step(double* sL, int warp, int lane) {
+  const int fr = lane >> 2, fk = lane & 3, tj = warp & 3, ti0 = warp >> 2;
+  {
+    double c0[2] = {0.0, 0.0}, c1[2] = {0.0, 0.0};
+    const double* X = sL + blk_id(KQ, KQ) * SBLK;
+    double* P = sL + blk_id(KQ + 1, KQ) * SBLK;
+#pragma unroll
+    for (int ks = 0; ks < SB / 4; ++ks) {
+      if (ks < 2 * tj + 2) {  // X is lower triangular: X[n][k] = 0 for k > n
+        const double b = X[(tj * 8 + fr) * LB + ks * 4 + fk];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) dmma884(c0[q], c1[q], P[((ti0 + 2 * q) * 8 + fr) * LB + ks * 4 + fk], b);
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < 2; ++q) *reinterpret_cast<double2*>(P + ((ti0 + 2 * q) * 8 + fr) * LB + tj * 8 + 2 * fk) = make_double2(c0[q], c1[q]);
+    __syncthreads();
+  }
+  {
+    const double* P = sL + blk_id(KQ + 1, KQ) * SBLK;
+    double c0[2] = {0.0, 0.0}, c1[2] = {0.0, 0.0};
+#pragma unroll
+    for (int ks = 0; ks < SB / 4; ++ks) {
+      const double b = P[(tj * 8 + fr) * LB + ks * 4 + fk];
+#pragma unroll
+      for (int q = 0; q < 2; ++q) dmma884(c0[q], c1[q], P[((ti0 + 2 * q) * 8 + fr) * LB + ks * 4 + fk], b);
+    }
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      double2* pd = reinterpret_cast<double2*>(sL + blk_id(KQ + 1, KQ + 1) * SBLK + ((ti0 + 2 * q) * 8 + fr) * LB + tj * 8 + 2 * fk);
+      double2 v = *pd;
+      v.x -= c0[q]; v.y -= c1[q];
+      *pd = v;
+    }
+    __syncthreads();
+  }
+}
+
+// Step KQ of the diagonal block.  Returns true when a pivot failed (uniform over the CTA).
+template <int KQ>
+__device__ __forceinline__ bool diag_phase(double* sL, double* sDinv, double* sScr, int* sBad, double* __restrict__ A, int n, int k0,
+                                           int kb, double* __restrict__ Linv, int* __restrict__ fail) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double* D = sL + blk_id(KQ, KQ) * SBLK;
+  if (warp == 0) {
+    // the chain: factor the diagonal sub-block
+    const int bad = warp_chol32(D, sDinv + KQ * SB, lane);
+    if (bad && lane == 0) { *sBad = 1; atomicExch(fail, k0 + KQ * SB + bad); }
+  } else if (KQ > 0 && warp != 4) {
+    diag_shadow<(KQ > 0 ? KQ - 1 : 0)>(sL, A, n, k0, kb, Linv, warp < 4 ? tid - 32 : tid - 64);
+#ifdef HSFM_DIAG_TIMING
+    if (tid == 32) g_diag_clk[24 + KQ] = clock64();
+    __syncwarp();
+#endif
+  }
+  __syncthreads();
+  DIAG_TICK(20 + KQ);
+  if (*sBad) return true;
+  diag_scale_out(D, sDinv + KQ * SB, A + (size_t)(k0 + KQ * SB) * n + k0 + KQ * SB, n, kb - KQ * SB);
+  if (warp == 0) warp_trinv32_dmma(D, sDinv + KQ * SB, sScr, lane);
+  __syncthreads();
+  DIAG_TICK(8 + 3 * KQ);
+  if (KQ < 3) {
+    diag_chain_step<(KQ < 3 ? KQ : 0)>(sL, warp, lane);
+    DIAG_TICK(10 + 3 * KQ);
+  }
+  return false;
+}
+
+// 10 sub-blocks + 1/diag + inverse scratch: 95 KB, so that (with <= 128 registers per thread) the kernel
 // fits on an SM NEXT TO a resident trailing-update CTA and never has to wait for a whole SM to drain.
-constexpr int kDiagSmem = (10 * SBLK + NB + 2 * SB) * (int)sizeof(double) + 16;
+constexpr int kDiagSmem = (10 * SBLK + NB + 320) * (int)sizeof(double) + 16;
 
 __global__ void __launch_bounds__(256, 2) chol_diag_kernel(double* __restrict__ A, int n, int k0, int kb, double* Linv, int* __restrict__ fail) {
   extern __shared__ __align__(16) double dsm[];
   double* sL = dsm;                 // [10][32][LB] lower sub-blocks: the matrix, then L, then (in place) the pieces of L^-1
   double* sDinv = sL + 10 * SBLK;   // [128] 1 / L[i][i]
-  double* sCol = sDinv + NB;        // [64] pivot-column broadcast of warp_chol32
-  int* sBad = reinterpret_cast<int*>(sCol + 2 * SB);
+  double* sScr = sDinv + NB;        // [320] scratch of warp_trinv32_dmma
+  int* sBad = reinterpret_cast<int*>(sScr + 320);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int failed = *fail;
   if (tid == 0) *sBad = 0;
@@ -285,108 +555,29 @@ __global__ void __launch_bounds__(256, 2) chol_diag_kernel(double* __restrict__ 
   __syncthreads();
   if (failed) return;
   DIAG_TICK(1);
-#pragma unroll 1
-  for (int kq = 0; kq < 4; ++kq) {
-    // (a) diagonal sub-block, warp 0
-    if (warp == 0) {
-      const int bad = warp_chol32(sL + blk_id(kq, kq) * SBLK, sCol, sDinv + kq * SB, lane);
-      if (bad && lane == 0) { *sBad = 1; atomicExch(fail, k0 + kq * SB + bad); }
-    }
-    __syncthreads();
-    if (*sBad) return;
-    if (kq == 3) break;
-    // (b) sub-panel: rows below, X D^T = P by substitution, one thread per row
-    {
-      const int rows = (3 - kq) * SB;
-      if (tid < rows) {
-        const int bi = kq + 1 + tid / SB, r = tid % SB;
-        double* P = sL + blk_id(bi, kq) * SBLK + r * LB;
-        const double* D = sL + blk_id(kq, kq) * SBLK;
-        double x[SB];
-#pragma unroll
-        for (int c = 0; c < SB; ++c) x[c] = P[c];
-#pragma unroll
-        for (int c = 0; c < SB; ++c) {
-          double s0 = x[c], s1 = 0.0;
-#pragma unroll
-          for (int k = 0; k + 1 < c; k += 2) {
-            s0 = fma(-x[k], D[c * LB + k], s0);
-            s1 = fma(-x[k + 1], D[c * LB + k + 1], s1);
-          }
-          if (c & 1) s0 = fma(-x[c - 1], D[c * LB + c - 1], s0);
-          x[c] = (s0 + s1) * sDinv[kq * SB + c];
-        }
-#pragma unroll
-        for (int c = 0; c < SB; ++c) P[c] = x[c];
-      }
-    }
-    __syncthreads();
-    // (c) trailing update: L(bi,bj) -= L(bi,kq) L(bj,kq)^T for kq < bj <= bi, 16 tiles of 8x8 per sub-block;
-    //     a warp's tiles (12, 6 or 2) advance together through the eight k-steps, so their DMMA chains overlap
-    if (kq == 0) diag_trailing<0>(sL, warp, lane);
-    else if (kq == 1) diag_trailing<1>(sL, warp, lane);
-    else diag_trailing<2>(sL, warp, lane);
-    __syncthreads();
-  }
-  DIAG_TICK(2);
-  // ---- L over the lower triangle of A ----
-  for (int e = tid; e < NB * (NB / 2); e += 256) {
-    const int i = e / (NB / 2), j = (e - i * (NB / 2)) * 2;
-    const int bi = i / SB, bj = j / SB;
-    if (bj <= bi && i < kb && j <= i) {
-      const double2 lv = *reinterpret_cast<const double2*>(sL + blk_id(bi, bj) * SBLK + (i % SB) * LB + (j % SB));
-      double* dst = A + (size_t)(k0 + i) * n + k0 + j;
-      if (j + 1 <= i && j + 1 < kb) *reinterpret_cast<double2*>(dst) = lv;
-      else dst[0] = lv.x;
-    }
-  }
-  __syncthreads();
-  DIAG_TICK(3);
-  // ---- L^-1, in place ----
-  // (1) diagonal sub-blocks X(i,i) = L(i,i)^-1: warps 0..3, in registers, over L(i,i)
-  if (warp < 4) warp_trinv32(sL + blk_id(warp, warp) * SBLK, sDinv + warp * SB, sL + blk_id(warp, warp) * SBLK, lane);
-  __syncthreads();
-  DIAG_TICK(4);
-  // (2) M(i,k) = X(i,i) L(i,k) over L(i,k), i > k: all 96 tiles to registers, barrier, write back
+  if (diag_phase<0>(sL, sDinv, sScr, sBad, A, n, k0, kb, Linv, fail)) return;
+  if (diag_phase<1>(sL, sDinv, sScr, sBad, A, n, k0, kb, Linv, fail)) return;
+  if (diag_phase<2>(sL, sDinv, sScr, sBad, A, n, k0, kb, Linv, fail)) return;
+  if (diag_phase<3>(sL, sDinv, sScr, sBad, A, n, k0, kb, Linv, fail)) return;
+  // ---- last row of the inverse: X(3,3) and X(3,j) = -X(3,3) Y(3,j), straight to global ----
   {
-    double m0[12], m1[12];
+    const int fr = lane >> 2, fk = lane & 3;
+    const double* X33 = sL + blk_id(3, 3) * SBLK;
 #pragma unroll
-    for (int q = 0; q < 12; ++q) {
-      const int t = warp + 8 * q;
-      const int b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
-      int i = 1;
-      while (blk_id(i + 1, 0) - (i + 1) <= b) ++i;  // off-diagonal blocks before row i+1: i(i+1)/2
-      const int k = b - i * (i - 1) / 2;
-      m0[q] = 0.0; m1[q] = 0.0;
-      tile_mma32<true>(m0[q], m1[q], sL + blk_id(i, i) * SBLK, sL + blk_id(i, k) * SBLK, ti, tj, lane);
+    for (int q = 0; q < 6; ++q) {
+      const int t = warp + 8 * q, j = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
+      double c0 = 0.0, c1 = 0.0;
+      const double* Y = sL + blk_id(3, j) * SBLK;
+#pragma unroll
+      for (int ks = 0; ks < SB / 4; ++ks)
+        if (ks < 2 * ti + 2) dmma884(c0, c1, X33[(ti * 8 + fr) * LB + ks * 4 + fk], Y[(ks * 4 + fk) * LB + tj * 8 + fr]);
+      *reinterpret_cast<double2*>(Linv + (size_t)(3 * SB + ti * 8 + fr) * NB + j * SB + tj * 8 + 2 * fk) = make_double2(-c0, -c1);
     }
-    __syncthreads();
-#pragma unroll
-    for (int q = 0; q < 12; ++q) {
-      const int t = warp + 8 * q;
-      const int b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
-      int i = 1;
-      while (blk_id(i + 1, 0) - (i + 1) <= b) ++i;
-      const int k = b - i * (i - 1) / 2;
-      *reinterpret_cast<double2*>(sL + blk_id(i, k) * SBLK + (ti * 8 + (lane >> 2)) * LB + tj * 8 + 2 * (lane & 3)) = make_double2(m0[q], m1[q]);
+    for (int e = tid; e < SB * (SB / 2); e += 256) {
+      const int r = e >> 4, c = (e & 15) * 2;
+      *reinterpret_cast<double2*>(Linv + (size_t)(3 * SB + r) * NB + 3 * SB + c) = *reinterpret_cast<const double2*>(X33 + r * LB + c);
     }
   }
-  __syncthreads();
-  DIAG_TICK(5);
-  // diagonal sub-blocks and the zero upper sub-blocks of the output
-  for (int e = tid; e < NB * (NB / 2); e += 256) {
-    const int i = e / (NB / 2), j = (e - i * (NB / 2)) * 2;
-    const int bi = i / SB, bj = j / SB;
-    if (bj == bi) reinterpret_cast<double2*>(Linv)[e] = *reinterpret_cast<const double2*>(sL + blk_id(bi, bi) * SBLK + (i % SB) * LB + (j % SB));
-    else if (bj > bi) reinterpret_cast<double2*>(Linv)[e] = make_double2(0.0, 0.0);
-  }
-  // (3) sub-diagonal d: X(i,j) = - sum_{k=j}^{i-1} M(i,k) X(k,j), j = i - d.  X(j,j) comes from shared memory, the
-  //     X(k,j) of earlier sub-diagonals from the output block itself (L2).
-  inv_level<1>(sL, Linv, warp, lane);
-  __syncthreads();
-  inv_level<2>(sL, Linv, warp, lane);
-  __syncthreads();
-  inv_level<3>(sL, Linv, warp, lane);
   DIAG_TICK(6);
 }
 
