@@ -45,6 +45,7 @@ int main() {
   }
   std::printf("\n     tail %lld total %lld clk\n", c[6] - c[17], c[6] - c[0]);
   for (int kq = 1; kq < 4; ++kq) std::printf("kq%d: factor done +%lld (scale+inv +%lld), shadow done +%lld (from phase start)\n", kq, c[20 + kq] - c[10 + 3 * (kq - 1)], c[8 + 3 * kq] - c[20 + kq], c[24 + kq] - c[10 + 3 * (kq - 1)]);
+  std::printf("shadow<0>: a0 %lld a %lld b %lld c1 %lld d %lld c2 %lld (start +%lld after phase start)\n", c[29]-c[28], c[30]-c[29], c[31]-c[30], c[32]-c[31], c[33]-c[32], c[34]-c[33], c[28]-c[10]);
 #ifdef HSFM_STEP_TIMING
   long long sc[40];
   cudaMemcpyFromSymbol(sc, g_step_clk, sizeof(sc));

@@ -83,6 +83,7 @@ __device__ long long g_step_clk[40];
 __device__ unsigned g_mask[40];
 __device__ unsigned g_mask2[40];
 #define DIAG_TICK(k) do { const unsigned am_ = __activemask(); if (threadIdx.x == 0) { g_diag_clk[k] = clock64(); g_mask2[k] = am_; } __syncwarp(); } while (0)
+#define SHADOW_TICK(k) do { if (KQ == 0) { if (tid6 == 0) g_diag_clk[k] = clock64(); __syncwarp(); } } while (0)
 #ifdef HSFM_STEP_TIMING
 #define STEP_TICK(k) do { const unsigned am_ = __activemask(); if (threadIdx.x == 0) { g_step_clk[k] = clock64(); g_mask[k] = am_; } __syncwarp(); } while (0)
 #else
@@ -91,6 +92,7 @@ __device__ unsigned g_mask2[40];
 #else
 #define DIAG_TICK(k) do { } while (0)
 #define STEP_TICK(k) do { } while (0)
+#define SHADOW_TICK(k) do { } while (0)
 #endif
 
 // 1/d with the second Newton correction taken as e*e (1 - d*y1 = e^2 exactly): three dependent multiply-adds
@@ -302,75 +304,105 @@ __device__ __forceinline__ void shadow_sync() { asm volatile("bar.sync 1, 192;" 
 // B is [k][n] when B_KN, else [n][k] (i.e. the product is A * B^T).
 template <bool B_KN>
 __device__ __forceinline__ void tile_acc32(double& c0, double& c1, const double* __restrict__ A, const double* __restrict__ B, int ti, int tj,
-                                           int fr, int fk) {
+                                           int fr, int fk, int ks_lo = 0, int ks_hi = SB / 4) {
 #pragma unroll
   for (int ks = 0; ks < SB / 4; ++ks) {
-    const double a = A[(ti * 8 + fr) * LB + ks * 4 + fk];
-    const double b = B_KN ? B[(ks * 4 + fk) * LB + tj * 8 + fr] : B[(tj * 8 + fr) * LB + ks * 4 + fk];
-    dmma884(c0, c1, a, b);
+    if (ks >= ks_lo && ks < ks_hi) {  // warp-uniform: triangular operands skip their zero k-steps
+      const double a = A[(ti * 8 + fr) * LB + ks * 4 + fk];
+      const double b = B_KN ? B[(ks * 4 + fk) * LB + tj * 8 + fr] : B[(tj * 8 + fr) * LB + ks * 4 + fk];
+      dmma884(c0, c1, a, b);
+    }
   }
 }
 
-// Work of step KQ that is NOT on the chain, done by warps 1..7 while warp 0 factors sub-block KQ+1:
-//   (a) the trailing update of every sub-block but (KQ+1,KQ+1),   (b) L(.,KQ) below the diagonal -> global,
-//   (c1) row KQ of the inverse  X(KQ,j) = -X(KQ,KQ) Y(KQ,j),     (d) that row -> global,
+// T output tiles of a warp advance together through the eight k-steps of a 32^3 block product, so that their DMMA
+// dependency chains overlap.  oa/ob: offsets (doubles, from sL) of the lane's A and B fragment at k-step 0; a tile
+// takes k-steps lo <= ks < hi only (triangular operands skip their zero k-steps; hi = 0 switches a tile off).
+template <int T, bool B_KN>
+__device__ __forceinline__ void tiles_mma(double (&c0)[T], double (&c1)[T], const double* __restrict__ sL, const int (&oa)[T], const int (&ob)[T],
+                                          const int (&lo)[T], const int (&hi)[T]) {
+#pragma unroll
+  for (int ks = 0; ks < SB / 4; ++ks) {
+#pragma unroll
+    for (int q = 0; q < T; ++q)
+      if (ks >= lo[q] && ks < hi[q]) dmma884(c0[q], c1[q], sL[oa[q] + ks * 4], sL[ob[q] + (B_KN ? ks * 4 * LB : ks * 4)]);
+  }
+}
+__device__ __forceinline__ int frag_a(int blk, int ti, int fr, int fk) { return blk * SBLK + (ti * 8 + fr) * LB + fk; }       // A [m][k]
+__device__ __forceinline__ int frag_bt(int blk, int tj, int fr, int fk) { return blk * SBLK + (tj * 8 + fr) * LB + fk; }      // B as [n][k]
+__device__ __forceinline__ int frag_bn(int blk, int tj, int fr, int fk) { return blk * SBLK + fk * LB + tj * 8 + fr; }        // B as [k][n]
+__device__ __forceinline__ int frag_c(int blk, int ti, int tj, int fr, int fk) { return blk * SBLK + (ti * 8 + fr) * LB + tj * 8 + 2 * fk; }
+
+// Work of step KQ that is NOT on the chain, done by warps 1,2,3,5,6,7 while warp 0 runs the pivots of sub-block KQ+1:
+//   (a0) the sub-panel rows below sub-block (KQ+1,KQ),           (a) the trailing update of every sub-block but (KQ+1,KQ+1),
+//   (b) L(.,KQ) below the diagonal -> global,                     (c1) row KQ of the inverse  X(KQ,j) = -X(KQ,KQ) Y(KQ,j),
+//   (d) that row -> global,
 //   (c2) Y(KQ+1,j) = sum_{k=j..KQ} L(KQ+1,k) X(k,j) over L(KQ+1,j)   (the part of row KQ+1 that needs no X(KQ+1,KQ+1)).
 template <int KQ>
-__device__ __forceinline__ void diag_shadow(double* sL, double* __restrict__ A, int n, int k0, int kb, double* __restrict__ Linv, int tid7) {
-  const int w7 = tid7 >> 5, lane = tid7 & 31, fr = lane >> 2, fk = lane & 3;
-  // (a0) the rows of the sub-panel below sub-block (KQ+1,KQ): L(bi,KQ) = P(bi,KQ) X(KQ,KQ)^T, bi >= KQ+2
+__device__ __forceinline__ void diag_shadow(double* sL, double* __restrict__ A, int n, int k0, int kb, double* __restrict__ Linv, int tid6) {
+  const int w6 = tid6 >> 5, lane = tid6 & 31, fr = lane >> 2, fk = lane & 3;
+  SHADOW_TICK(28);
+  // (a0) L(bi,KQ) = P(bi,KQ) X(KQ,KQ)^T, bi >= KQ+2
   if constexpr (KQ < 2) {
     constexpr int NT = (2 - KQ) * 16, T = (NT + 5) / 6;
     double c0[T], c1[T];
-    const double* X = sL + blk_id(KQ, KQ) * SBLK;
+    int oa[T], ob[T], oc[T], lo[T], hi[T];
 #pragma unroll
     for (int q = 0; q < T; ++q) {
-      const int t = w7 + 6 * q;
+      const int t = w6 + 6 * q, bi = KQ + 2 + (t >> 4), ti = (t >> 2) & 3, tj = t & 3;
       c0[q] = 0.0; c1[q] = 0.0;
-      if (t < NT) {
-        const int bi = KQ + 2 + (t >> 4), tile = t & 15;
-        tile_acc32<false>(c0[q], c1[q], sL + blk_id(bi, KQ) * SBLK, X, tile >> 2, tile & 3, fr, fk);
-      }
+      oa[q] = frag_a(blk_id(bi, KQ), ti, fr, fk);
+      ob[q] = frag_bt(blk_id(KQ, KQ), tj, fr, fk);
+      oc[q] = frag_c(blk_id(bi, KQ), ti, tj, fr, fk);
+      lo[q] = 0; hi[q] = t < NT ? 2 * tj + 2 : 0;  // X is lower triangular: X[n][k] = 0 for k > n
     }
+    tiles_mma<T, false>(c0, c1, sL, oa, ob, lo, hi);
     shadow_sync();
 #pragma unroll
-    for (int q = 0; q < T; ++q) {
-      const int t = w7 + 6 * q;
-      if (t < NT) {
-        const int bi = KQ + 2 + (t >> 4), tile = t & 15, ti = tile >> 2, tj = tile & 3;
-        *reinterpret_cast<double2*>(sL + blk_id(bi, KQ) * SBLK + (ti * 8 + fr) * LB + tj * 8 + 2 * fk) = make_double2(c0[q], c1[q]);
-      }
-    }
+    for (int q = 0; q < T; ++q)
+      if (hi[q]) *reinterpret_cast<double2*>(sL + oc[q]) = make_double2(c0[q], c1[q]);
     shadow_sync();
   }
-  // (a)
-  {
-    constexpr int NBLK = KQ == 0 ? 5 : KQ == 1 ? 2 : 0;
+  SHADOW_TICK(29);
+  // (a) L(bi,bj) -= L(bi,KQ) L(bj,KQ)^T, in two halves (registers)
+  if constexpr (KQ < 2) {
+    constexpr int NBLK = KQ == 0 ? 5 : 2;
     constexpr int BI[5] = {KQ == 0 ? 2 : 3, KQ == 0 ? 2 : 3, 3, 3, 3};
     constexpr int BJ[5] = {KQ == 0 ? 1 : 2, KQ == 0 ? 2 : 3, 1, 2, 3};
-    constexpr int T = (NBLK * 16 + 5) / 6;
+    constexpr int T = (NBLK * 16 + 11) / 12;
 #pragma unroll
-    for (int q = 0; q < T; ++q) {
-      const int t = w7 + 6 * q;
-      if (t < NBLK * 16) {
-        const int b = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
+    for (int half = 0; half < 2; ++half) {
+      double c0[T], c1[T];
+      int oa[T], ob[T], oc[T], lo[T], hi[T];
+#pragma unroll
+      for (int q = 0; q < T; ++q) {
+        const int t = w6 + 6 * (half * T + q), b = t >> 4, ti = (t >> 2) & 3, tj = t & 3;
         int bi = BI[0], bj = BJ[0];
 #pragma unroll
         for (int z = 1; z < 5; ++z)
           if (b == z) { bi = BI[z]; bj = BJ[z]; }
-        double c0 = 0.0, c1 = 0.0;
-        tile_acc32<false>(c0, c1, sL + blk_id(bi, KQ) * SBLK, sL + blk_id(bj, KQ) * SBLK, ti, tj, fr, fk);
-        double2* pd = reinterpret_cast<double2*>(sL + blk_id(bi, bj) * SBLK + (ti * 8 + fr) * LB + tj * 8 + 2 * fk);
-        double2 v = *pd;
-        v.x -= c0; v.y -= c1;
-        *pd = v;
+        c0[q] = 0.0; c1[q] = 0.0;
+        oa[q] = frag_a(blk_id(bi, KQ), ti, fr, fk);
+        ob[q] = frag_bt(blk_id(bj, KQ), tj, fr, fk);
+        oc[q] = frag_c(blk_id(bi, bj), ti, tj, fr, fk);
+        lo[q] = 0; hi[q] = (t < NBLK * 16 && (bi != bj || ti >= tj)) ? SB / 4 : 0;  // strict upper of a diagonal sub-block: never read
       }
+      tiles_mma<T, false>(c0, c1, sL, oa, ob, lo, hi);
+#pragma unroll
+      for (int q = 0; q < T; ++q)
+        if (hi[q]) {
+          double2* pd = reinterpret_cast<double2*>(sL + oc[q]);
+          double2 v = *pd;
+          v.x -= c0[q]; v.y -= c1[q];
+          *pd = v;
+        }
     }
   }
+  SHADOW_TICK(30);
   // (b)
   {
     constexpr int NE = (3 - KQ) * SB * (SB / 2);
-    for (int e = tid7; e < NE; e += 192) {
+    for (int e = tid6; e < NE; e += 192) {
       const int blk = e / (SB * SB / 2), rem = e - blk * (SB * SB / 2), r = rem >> 4, c = (rem & 15) * 2;
       const int i = (KQ + 1 + blk) * SB + r;
       if (i < kb)
@@ -379,62 +411,64 @@ __device__ __forceinline__ void diag_shadow(double* sL, double* __restrict__ A, 
     }
   }
   shadow_sync();
-  // (c1)
+  SHADOW_TICK(31);
+  // (c1) X(KQ,j) = -X(KQ,KQ) Y(KQ,j), j < KQ
   if constexpr (KQ >= 1) {
-    constexpr int T = (KQ * 16 + 5) / 6;
+    constexpr int NT = KQ * 16, T = (NT + 5) / 6;
     double c0[T], c1[T];
+    int oa[T], ob[T], oc[T], lo[T], hi[T];
 #pragma unroll
     for (int q = 0; q < T; ++q) {
-      const int t = w7 + 6 * q;
+      const int t = w6 + 6 * q, j = t >> 4, ti = (t >> 2) & 3, tj = t & 3;
       c0[q] = 0.0; c1[q] = 0.0;
-      if (t < KQ * 16) {
-        const int j = t >> 4, tile = t & 15;
-        tile_acc32<true>(c0[q], c1[q], sL + blk_id(KQ, KQ) * SBLK, sL + blk_id(KQ, j) * SBLK, tile >> 2, tile & 3, fr, fk);
-      }
+      oa[q] = frag_a(blk_id(KQ, KQ), ti, fr, fk);
+      ob[q] = frag_bn(blk_id(KQ, j < KQ ? j : 0), tj, fr, fk);
+      oc[q] = frag_c(blk_id(KQ, j < KQ ? j : 0), ti, tj, fr, fk);
+      lo[q] = 0; hi[q] = t < NT ? 2 * ti + 2 : 0;  // X(KQ,KQ)[m][k] = 0 for k > m
     }
+    tiles_mma<T, true>(c0, c1, sL, oa, ob, lo, hi);
     shadow_sync();
 #pragma unroll
-    for (int q = 0; q < T; ++q) {
-      const int t = w7 + 6 * q;
-      if (t < KQ * 16) {
-        const int j = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
-        *reinterpret_cast<double2*>(sL + blk_id(KQ, j) * SBLK + (ti * 8 + fr) * LB + tj * 8 + 2 * fk) = make_double2(-c0[q], -c1[q]);
-      }
-    }
+    for (int q = 0; q < T; ++q)
+      if (hi[q]) *reinterpret_cast<double2*>(sL + oc[q]) = make_double2(-c0[q], -c1[q]);
     shadow_sync();
   }
+  SHADOW_TICK(32);
   // (d)
-  for (int e = tid7; e < SB * (NB / 2); e += 192) {
+  for (int e = tid6; e < SB * (NB / 2); e += 192) {
     const int r = e >> 6, cc = (e & 63) * 2, bj = cc >> 5;
     double2 v = make_double2(0.0, 0.0);
     if (bj <= KQ) v = *reinterpret_cast<const double2*>(sL + blk_id(KQ, bj) * SBLK + r * LB + (cc & 31));
     *reinterpret_cast<double2*>(Linv + (size_t)(KQ * SB + r) * NB + cc) = v;
   }
-  // (c2)
+  SHADOW_TICK(33);
+  // (c2) Y(KQ+1,j) = sum_{k=j..KQ} L(KQ+1,k) X(k,j), j <= KQ
   {
-    constexpr int T = ((KQ + 1) * 16 + 5) / 6;
+    constexpr int NT = (KQ + 1) * 16, T = (NT + 5) / 6;
     double c0[T], c1[T];
+    int oc[T];
 #pragma unroll
-    for (int q = 0; q < T; ++q) {
-      const int t = w7 + 6 * q;
-      c0[q] = 0.0; c1[q] = 0.0;
-      if (t < (KQ + 1) * 16) {
-        const int j = t >> 4, tile = t & 15;
+    for (int q = 0; q < T; ++q) { c0[q] = 0.0; c1[q] = 0.0; }
 #pragma unroll
-        for (int k = 0; k <= KQ; ++k)
-          if (k >= j) tile_acc32<true>(c0[q], c1[q], sL + blk_id(KQ + 1, k) * SBLK, sL + blk_id(k, j) * SBLK, tile >> 2, tile & 3, fr, fk);
+    for (int k = 0; k <= KQ; ++k) {
+      int oa[T], ob[T], lo[T], hi[T];
+#pragma unroll
+      for (int q = 0; q < T; ++q) {
+        const int t = w6 + 6 * q, j = t >> 4, ti = (t >> 2) & 3, tj = t & 3, jj = j <= k ? j : k;
+        oa[q] = frag_a(blk_id(KQ + 1, k), ti, fr, fk);
+        ob[q] = frag_bn(blk_id(k, jj), tj, fr, fk);
+        oc[q] = frag_c(blk_id(KQ + 1, j <= KQ ? j : 0), ti, tj, fr, fk);
+        lo[q] = k == j ? 2 * tj : 0;  // X(j,j)[k][n] = 0 for k < n
+        hi[q] = (t < NT && k >= j) ? SB / 4 : 0;
       }
+      tiles_mma<T, true>(c0, c1, sL, oa, ob, lo, hi);
     }
     shadow_sync();
 #pragma unroll
-    for (int q = 0; q < T; ++q) {
-      const int t = w7 + 6 * q;
-      if (t < (KQ + 1) * 16) {
-        const int j = t >> 4, tile = t & 15, ti = tile >> 2, tj = tile & 3;
-        *reinterpret_cast<double2*>(sL + blk_id(KQ + 1, j) * SBLK + (ti * 8 + fr) * LB + tj * 8 + 2 * fk) = make_double2(c0[q], c1[q]);
-      }
-    }
+    for (int q = 0; q < T; ++q)
+      if (w6 + 6 * q < NT) *reinterpret_cast<double2*>(sL + oc[q]) = make_double2(c0[q], c1[q]);
   }
+  SHADOW_TICK(34);
 }
 
 // The part of step KQ that IS on the chain, all eight warps: sub-block (KQ+1,KQ) of the panel as a product with the
