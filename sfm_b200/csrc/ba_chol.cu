@@ -830,15 +830,17 @@ __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ 
 // CTA would put 8.4 us of DMMA issue on a single SM; here a CTA takes a 64x64 tile (four warps of 32x32), the
 // whole K = 128 of both operands arrives in shared memory with ONE cp.async burst, and 4 x cnt CTAs spread over
 // the GPU: ~2 us of tensor work per SM.
-constexpr int LT = 64;             // tile edge
+constexpr int LT_MAX = 64;         // largest tile edge (LT = 64: throughput; LT = 32: the chain's diagonal tile on 10 SMs)
 constexpr int LT_LD = NB + 4;      // operand row stride in shared memory (doubles)
-constexpr int kSyrkLatSmem = 2 * LT * LT_LD * (int)sizeof(double);
+constexpr int kSyrkLatSmem = 2 * LT_MAX * LT_LD * (int)sizeof(double);
+template <int LT>
 __global__ void __launch_bounds__(128) chol_syrk_col_kernel(double* __restrict__ S, int n, int k0, const int* __restrict__ rb_list,
                                                             const int* __restrict__ fail, int a0) {
   extern __shared__ __align__(16) double lsm[];
   double (*sA)[LT_LD] = reinterpret_cast<double (*)[LT_LD]>(lsm);
   double (*sB)[LT_LD] = reinterpret_cast<double (*)[LT_LD]>(lsm + LT * LT_LD);
-  const int a = a0 + (blockIdx.x >> 2), rh = (blockIdx.x >> 1) & 1, ch = blockIdx.x & 1;
+  constexpr int PER = NB / LT, H = LT / 2, NT = H / 8;  // tiles per block edge, warp tile edge, 8x8 tiles per warp edge
+  const int a = a0 + blockIdx.x / (PER * PER), rh = (blockIdx.x / PER) % PER, ch = blockIdx.x % PER;
   if (a == 0 && ch > rh) return;  // strictly upper part of the diagonal block
   const int ri = __ldg(rb_list + a) * NB + rh * LT, rj = __ldg(rb_list) * NB + ch * LT;
   const int ni = min(LT, n - ri), nj = min(LT, n - rj);
@@ -852,15 +854,15 @@ __global__ void __launch_bounds__(128) chol_syrk_col_kernel(double* __restrict__
     else { sB[row][c2] = 0.0; sB[row][c2 + 1] = 0.0; }
   }
   cp_async_commit();
-  const int wr = warp >> 1, wc = warp & 1;  // 2 x 2 warps of 32 x 32
-  double acc[4][4][2];
-  double* const crow = S + (size_t)(ri + wr * 32 + fr) * n + rj + wc * 32 + 2 * fk;
+  const int wr = warp >> 1, wc = warp & 1;  // 2 x 2 warps of H x H
+  double acc[NT][NT][2];
+  double* const crow = S + (size_t)(ri + wr * H + fr) * n + rj + wc * H + 2 * fk;
 #pragma unroll
-  for (int p = 0; p < 4; ++p)
+  for (int p = 0; p < NT; ++p)
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
+    for (int q = 0; q < NT; ++q) {
       acc[p][q][0] = 0.0; acc[p][q][1] = 0.0;
-      const int row = wr * 32 + p * 8 + fr, col = wc * 32 + q * 8 + 2 * fk;
+      const int row = wr * H + p * 8 + fr, col = wc * H + q * 8 + 2 * fk;
       if (row < ni && col < nj) {
         const double2 c = *reinterpret_cast<const double2*>(crow + (size_t)p * 8 * n + q * 8);
         acc[p][q][0] = c.x; acc[p][q][1] = c.y;
@@ -870,21 +872,21 @@ __global__ void __launch_bounds__(128) chol_syrk_col_kernel(double* __restrict__
   __syncthreads();
 #pragma unroll 4
   for (int ks = 0; ks < NB / 4; ++ks) {
-    double af[4], bf[4];
+    double af[NT], bf[NT];
 #pragma unroll
-    for (int p = 0; p < 4; ++p) af[p] = -sA[wr * 32 + p * 8 + fr][ks * 4 + fk];
+    for (int p = 0; p < NT; ++p) af[p] = -sA[wr * H + p * 8 + fr][ks * 4 + fk];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) bf[q] = sB[wc * 32 + q * 8 + fr][ks * 4 + fk];
+    for (int q = 0; q < NT; ++q) bf[q] = sB[wc * H + q * 8 + fr][ks * 4 + fk];
 #pragma unroll
-    for (int p = 0; p < 4; ++p)
+    for (int p = 0; p < NT; ++p)
 #pragma unroll
-      for (int q = 0; q < 4; ++q) dmma884(acc[p][q][0], acc[p][q][1], af[p], bf[q]);
+      for (int q = 0; q < NT; ++q) dmma884(acc[p][q][0], acc[p][q][1], af[p], bf[q]);
   }
 #pragma unroll
-  for (int p = 0; p < 4; ++p)
+  for (int p = 0; p < NT; ++p)
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int row = wr * 32 + p * 8 + fr, col = wc * 32 + q * 8 + 2 * fk;
+    for (int q = 0; q < NT; ++q) {
+      const int row = wr * H + p * 8 + fr, col = wc * H + q * 8 + 2 * fk;
       if (row < ni && col < nj) *reinterpret_cast<double2*>(crow + (size_t)p * 8 * n + q * 8) = make_double2(acc[p][q][0], acc[p][q][1]);
     }
 }
@@ -1454,7 +1456,7 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
     if (has_col) {
       trsm(s2, k0, Linv, list, 1);               // L(K+1, K)
       if (la && cnt > 1) cudaEventRecord(aux->ev_next, s2);
-      chol_syrk_col_kernel<<<4, 128, kSyrkLatSmem, s2>>>(S, n, k0, list, fail_flag, 0);  // tile (K+1, K+1)
+      chol_syrk_col_kernel<32><<<16, 128, kSyrkLatSmem / 2, s2>>>(S, n, k0, list, fail_flag, 0);  // tile (K+1, K+1): 10 active CTAs of 32 x 32
       ++*launches;
     }
     const int rest_cnt = has_col ? cnt - 1 : cnt;
@@ -1464,7 +1466,7 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
       trsm(s, k0, Linv, rl, rest_cnt);
       if (has_col) {
         if (la) cudaStreamWaitEvent(s, aux->ev_next, 0);
-        chol_syrk_col_kernel<<<4 * rest_cnt, 128, kSyrkLatSmem, s>>>(S, n, k0, list, fail_flag, 1);  // tiles (I, K+1), I > K+1
+        chol_syrk_col_kernel<64><<<4 * rest_cnt, 128, kSyrkLatSmem, s>>>(S, n, k0, list, fail_flag, 1);  // tiles (I, K+1), I > K+1
         ++*launches;
       }
       const int tiles = rest_cnt * (rest_cnt + 1);
@@ -1485,7 +1487,8 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
     cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDiagSmem);
     cudaFuncSetAttribute(chol_trsm_strip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_MAXROWS * TS_LD * (int)sizeof(double));
     cudaFuncSetAttribute(chol_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem);
-    cudaFuncSetAttribute(chol_syrk_col_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrkLatSmem);
+    cudaFuncSetAttribute(chol_syrk_col_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrkLatSmem);
+    cudaFuncSetAttribute(chol_syrk_col_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrkLatSmem / 2);
     attr_set = true;
   }
   static int n_sm = 0;
