@@ -179,34 +179,37 @@ __device__ __noinline__ int warp_chol32(double* __restrict__ D, double* __restri
   return bad;
 }
 
-// After warp_chol32: all eight warps turn the pivot-column history (slot j, entry i = A(j)[i][j], in the sub-block's
+// Barrier of the two chain warps (0 and 4).
+__device__ __forceinline__ void chain_sync() { asm volatile("bar.sync 2, 64;" ::: "memory"); }
+
+// After warp_chol32: warps 0 and 4 turn the pivot-column history (slot j, entry i = A(j)[i][j], in the sub-block's
 // own storage) into L[i][j] = A(j)[i][j] / sqrt(A(j)[j][j]) in place (row stride LB, strict upper zeroed),
-// dinv[j] = 1/L[j][j], and put the lower triangle out to global memory.  Thread = (row lane, four columns warp*4..).
-__device__ __forceinline__ void diag_scale_out(double* __restrict__ D, double* __restrict__ dinv, double* __restrict__ gdst, int n, int rows_valid) {
-  const int lane = threadIdx.x & 31, c4 = (threadIdx.x >> 5) * 4;
-  double l[4], iv[4];
+// dinv[j] = 1/L[j][j], and put the lower triangle out to global memory.  Thread = (row lane, sixteen columns).
+__device__ __forceinline__ void diag_scale_out(double* __restrict__ D, double* __restrict__ dinv, double* __restrict__ gdst, int n, int rows_valid,
+                                               int warp, int lane) {
+  const int c16 = warp ? 16 : 0;
+  if (warp == 0) dinv[lane] = fast_rsqrt(D[lane * SB + lane]);
+  chain_sync();
+  double l[16];
 #pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    const int j = c4 + q;
-    iv[q] = fast_rsqrt(D[j * SB + j]);
-    l[q] = (lane >= j) ? D[j * SB + lane] * iv[q] : 0.0;
+  for (int q = 0; q < 16; q += 2) {
+    const double2 iv = *reinterpret_cast<const double2*>(dinv + c16 + q);
+    const int j = c16 + q;
+    l[q] = (lane >= j) ? D[j * SB + lane] * iv.x : 0.0;
+    l[q + 1] = (lane >= j + 1) ? D[(j + 1) * SB + lane] * iv.y : 0.0;
   }
-  __syncthreads();
-  *reinterpret_cast<double2*>(D + lane * LB + c4) = make_double2(l[0], l[1]);
-  *reinterpret_cast<double2*>(D + lane * LB + c4 + 2) = make_double2(l[2], l[3]);
+  chain_sync();
+  double* dst = gdst + (size_t)lane * n + c16;
 #pragma unroll
-  for (int q = 0; q < 4; ++q)
-    if (lane == c4 + q) dinv[lane] = iv[q];
-  if (lane < rows_valid) {
-    double* dst = gdst + (size_t)lane * n + c4;
-#pragma unroll
-    for (int p = 0; p < 2; ++p) {
-      const int c = c4 + 2 * p;
-      if (c + 1 <= lane) *reinterpret_cast<double2*>(dst + 2 * p) = make_double2(l[2 * p], l[2 * p + 1]);
-      else if (c == lane) dst[2 * p] = l[2 * p];
+  for (int q = 0; q < 16; q += 2) {
+    *reinterpret_cast<double2*>(D + lane * LB + c16 + q) = make_double2(l[q], l[q + 1]);
+    const int c = c16 + q;
+    if (lane < rows_valid) {
+      if (c + 1 <= lane) *reinterpret_cast<double2*>(dst + q) = make_double2(l[q], l[q + 1]);
+      else if (c == lane) dst[q] = l[q];
     }
   }
-  __syncthreads();
+  chain_sync();
 }
 
 // In-place inverse of the lower-triangular 32x32 sub-block D (row stride LB, strict upper zero) by one warp, by
@@ -519,11 +522,18 @@ __device__ __forceinline__ bool diag_phase(double* sL, double* sDinv, double* sS
                                            int kb, double* __restrict__ Linv, int* __restrict__ fail) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   double* D = sL + blk_id(KQ, KQ) * SBLK;
-  if (warp == 0) {
-    // the chain: factor the diagonal sub-block
-    const int bad = warp_chol32(D, sDinv + KQ * SB, lane);
-    if (bad && lane == 0) { *sBad = 1; atomicExch(fail, k0 + KQ * SB + bad); }
-  } else if (KQ > 0 && warp != 4) {
+  if ((warp & 3) == 0) {
+    // the chain: warp 0 runs the pivots (warp 4, on the same scheduler, waits), both scale and put L out, warp 0 inverts
+    if (warp == 0) {
+      const int bad = warp_chol32(D, sDinv + KQ * SB, lane);
+      if (bad && lane == 0) { *sBad = 1; atomicExch(fail, k0 + KQ * SB + bad); }
+    }
+    chain_sync();
+    if (!*sBad) {
+      diag_scale_out(D, sDinv + KQ * SB, A + (size_t)(k0 + KQ * SB) * n + k0 + KQ * SB, n, kb - KQ * SB, warp, lane);
+      if (warp == 0) warp_trinv32_dmma(D, sDinv + KQ * SB, sScr, lane);
+    }
+  } else if (KQ > 0) {
     diag_shadow<(KQ > 0 ? KQ - 1 : 0)>(sL, A, n, k0, kb, Linv, warp < 4 ? tid - 32 : tid - 64);
 #ifdef HSFM_DIAG_TIMING
     if (tid == 32) g_diag_clk[24 + KQ] = clock64();
@@ -531,11 +541,7 @@ __device__ __forceinline__ bool diag_phase(double* sL, double* sDinv, double* sS
 #endif
   }
   __syncthreads();
-  DIAG_TICK(20 + KQ);
   if (*sBad) return true;
-  diag_scale_out(D, sDinv + KQ * SB, A + (size_t)(k0 + KQ * SB) * n + k0 + KQ * SB, n, kb - KQ * SB);
-  if (warp == 0) warp_trinv32_dmma(D, sDinv + KQ * SB, sScr, lane);
-  __syncthreads();
   DIAG_TICK(8 + 3 * KQ);
   if (KQ < 3) {
     diag_chain_step<(KQ < 3 ? KQ : 0)>(sL, warp, lane);
