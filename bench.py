@@ -159,6 +159,8 @@ def main():
         run_reference(args, rank, world)
         return
 
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+        os.environ["NCCL_DEBUG"] = "WARN"  # NCCL's version banner goes to stdout: keep stdout to the one JSON line
     import torch
     import torch.distributed as dist
 
