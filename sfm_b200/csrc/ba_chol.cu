@@ -659,7 +659,7 @@ __device__ __forceinline__ void load_tile_async(double (*dst)[LDS_], const doubl
 struct SyrkTile { int ri, ni, rj, nj; };
 // rb_list != nullptr: envelope mode — the tiles are pairs of ACTIVE 128-row blocks (global block indices,
 // ascending).  col_first == 0: the pairs (a, 0), i.e. the column of block rb_list[0] (the next panel);
-// col_first < 0: every pair (a, b), b <= a.  Two 64-wide tiles per pair.
+// col_first == -1: every pair (a, b), b <= a; col_first == -2: all of them but (0, 0).  Two 64-wide tiles per pair.
 __device__ __forceinline__ SyrkTile syrk_tile(int t, int n, int base, int row_first, int col_first, const int* __restrict__ rb_list) {
   SyrkTile T;
   if (rb_list) {
@@ -667,10 +667,11 @@ __device__ __forceinline__ SyrkTile syrk_tile(int t, int n, int base, int row_fi
     int a, b;
     if (col_first == 0) { a = pi; b = 0; }
     else {
-      a = (int)((sqrtf(8.0f * (float)pi + 1.0f) - 1.0f) * 0.5f);
-      while ((a + 1) * (a + 2) / 2 <= pi) ++a;
-      while (a * (a + 1) / 2 > pi) --a;
-      b = pi - a * (a + 1) / 2;
+      const int pp = pi + (col_first == -2 ? 1 : 0);  // -2: every pair but (0, 0), which the chain stream updates
+      a = (int)((sqrtf(8.0f * (float)pp + 1.0f) - 1.0f) * 0.5f);
+      while ((a + 1) * (a + 2) / 2 <= pp) ++a;
+      while (a * (a + 1) / 2 > pp) --a;
+      b = pp - a * (a + 1) / 2;
     }
     T.ri = __ldg(rb_list + a) * NB; T.ni = min(NB, n - T.ri);
     T.rj = __ldg(rb_list + b) * NB + half * TN; T.nj = min(TN, n - T.rj);
@@ -1471,12 +1472,14 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
       if (la) cudaStreamWaitEvent(s, aux->ev_panel, 0);
       trsm(s, k0, Linv, rl, rest_cnt);
       if (has_col) {
+        // one update launch for column K+1 below its diagonal tile and every other active pair
         if (la) cudaStreamWaitEvent(s, aux->ev_next, 0);
-        chol_syrk_col_kernel<64><<<4 * rest_cnt, 128, kSyrkLatSmem, s>>>(S, n, k0, list, fail_flag, 1);  // tiles (I, K+1), I > K+1
-        ++*launches;
+        const int tiles = cnt * (cnt + 1) - 2;
+        chol_syrk_kernel<<<min(tiles, 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 0, -2, tiles, 0, fail_flag, list);
+      } else {
+        const int tiles = rest_cnt * (rest_cnt + 1);
+        chol_syrk_kernel<<<min(tiles, 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 0, -1, tiles, 0, fail_flag, rl);
       }
-      const int tiles = rest_cnt * (rest_cnt + 1);
-      chol_syrk_kernel<<<min(tiles, 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 0, -1, tiles, 0, fail_flag, rl);
       ++*launches;
       if (la) { cudaEventRecord(aux->ev_rest, s); rest_pending = true; }
     }
