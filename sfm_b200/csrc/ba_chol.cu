@@ -34,6 +34,14 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
 
+// Programmatic dependent launch (the chain kernels of the envelope factorisation): a kernel lets its successor in
+// the stream be launched at once and waits for its predecessor's results itself, so the hand-over from kernel to
+// kernel costs no launch latency.  Both are no-ops in a launch without the attribute.
+__device__ __forceinline__ void pdl_enter() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
@@ -550,6 +558,10 @@ __device__ __forceinline__ bool diag_phase(double* sL, double* sDinv, double* sS
   return false;
 }
 
+#ifdef HSFM_CHAIN_TIMING
+__device__ unsigned long long g_chain_ts[4096];  // [2 * panel] start, [2 * panel + 1] end of the diagonal-block kernel (globaltimer, ns)
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#endif
 // 10 sub-blocks + 1/diag + inverse scratch: 95 KB, so that (with <= 128 registers per thread) the kernel
 // fits on an SM NEXT TO a resident trailing-update CTA and never has to wait for a whole SM to drain.
 constexpr int kDiagSmem = (10 * SBLK + NB + 320) * (int)sizeof(double) + 16;
@@ -561,8 +573,12 @@ __global__ void __launch_bounds__(256, 2) chol_diag_kernel(double* __restrict__ 
   double* sScr = sDinv + NB;        // [320] scratch of warp_trinv32_dmma
   int* sBad = reinterpret_cast<int*>(sScr + 320);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  pdl_enter();
   const int failed = *fail;
   if (tid == 0) *sBad = 0;
+#ifdef HSFM_CHAIN_TIMING
+  if (tid == 0) g_chain_ts[2 * ((k0 / NB) & 2047)] = gtime();
+#endif
   DIAG_TICK(0);
   // load the lower sub-blocks (identity beyond kb; strict upper of the diagonal sub-blocks zero).  Element
   // e = tid + 256 it lies in sub-block it >> 1: the block decode is a compile-time constant of the unrolled
@@ -619,6 +635,10 @@ __global__ void __launch_bounds__(256, 2) chol_diag_kernel(double* __restrict__ 
     }
   }
   DIAG_TICK(6);
+#ifdef HSFM_CHAIN_TIMING
+  __syncthreads();
+  if (tid == 0) g_chain_ts[2 * ((k0 / NB) & 2047) + 1] = gtime();
+#endif
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -843,6 +863,7 @@ constexpr int kSyrkLatSmem = 2 * LT_MAX * LT_LD * (int)sizeof(double);
 template <int LT>
 __global__ void __launch_bounds__(128) chol_syrk_col_kernel(double* __restrict__ S, int n, int k0, const int* __restrict__ rb_list,
                                                             const int* __restrict__ fail, int a0) {
+  pdl_enter();
   extern __shared__ __align__(16) double lsm[];
   double (*sA)[LT_LD] = reinterpret_cast<double (*)[LT_LD]>(lsm);
   double (*sB)[LT_LD] = reinterpret_cast<double (*)[LT_LD]>(lsm + LT * LT_LD);
@@ -911,6 +932,7 @@ __global__ void __launch_bounds__(256) chol_trsm_strip_kernel(double* __restrict
                                                                int strips_per_block) {
   extern __shared__ __align__(16) double tsm[];
   double (*sA)[TS_LD] = reinterpret_cast<double (*)[TS_LD]>(tsm);
+  pdl_enter();
   const int failed = *fail;
   int r0, nr;
   if (rb_list) {  // envelope mode: strips of the active 128-row blocks only
@@ -1317,6 +1339,11 @@ void launch_spd_err(int n, const double* x, double* err, cudaStream_t s) {
 #endif
 }
 
+#ifdef HSFM_CHAIN_TIMING
+extern "C" int hsfm_ba_debug_chain_ts(unsigned long long* out, int n) {
+  return (int)cudaMemcpyFromSymbol(out, g_chain_ts, sizeof(unsigned long long) * (size_t)n);
+}
+#endif
 size_t cholesky_workspace_doubles(int n) {
   const size_t panels = (size_t)((n + NB - 1) / NB);
   return (panels * NB * NB + panels + 1) & ~(size_t)1;  // one L11^-1 block per panel + 2 x panels int flags of the cooperative triangular solve (even: what follows stays 16-byte aligned)
@@ -1447,11 +1474,25 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
     chol_trsm_strip_kernel<<<cnt * spb, 256, rows_per * TS_LD * (int)sizeof(double), st>>>(S, n, k0, Linv, rows_per, fail_flag, list, spb);
     ++*launches;
   };
+  // chain-stream launches carry the programmatic-serialisation attribute (see pdl_enter)
+  static const bool no_pdl = getenv("HSFM_NO_PDL") != nullptr;  // experiment knob
+  cudaLaunchAttribute pdl_attr[1];
+  pdl_attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  pdl_attr[0].val.programmaticStreamSerializationAllowed = 1;
+  auto chain_cfg = [&](int grid, int block, size_t smem) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = smem; cfg.stream = s2;
+    cfg.attrs = pdl_attr; cfg.numAttrs = (la && !no_pdl) ? 1 : 0;
+    return cfg;
+  };
   bool rest_pending = false;
   for (int K = 0, k0 = 0; K < pl.panels; ++K, k0 += NB) {
     const int kb = min(NB, n - k0);
     double* Linv = ws + (size_t)K * NB * NB;
-    chol_diag_kernel<<<1, 256, kDiagSmem, s2>>>(S, n, k0, kb, Linv, fail_flag);
+    {
+      cudaLaunchConfig_t cfg = chain_cfg(1, 256, kDiagSmem);
+      cudaLaunchKernelEx(&cfg, chol_diag_kernel, S, n, k0, kb, Linv, fail_flag);
+    }
     ++*launches;
     const int cnt = pl.cnt[K];
     // everything the main stream did one step ago must be complete before the chain touches column K+1 / block K+1
@@ -1461,10 +1502,17 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
     const bool has_col = pl.list[(size_t)pl.off[K]] == K + 1;
     if (la) cudaEventRecord(aux->ev_panel, s2);  // diag(K) done
     if (has_col) {
-      trsm(s2, k0, Linv, list, 1);               // L(K+1, K)
+      {  // L(K+1, K): 16 strips of 8 rows
+        cudaLaunchConfig_t cfg = chain_cfg(NB / 8, 256, 8 * TS_LD * sizeof(double));
+        cudaLaunchKernelEx(&cfg, chol_trsm_strip_kernel, S, n, k0, (const double*)Linv, 8, (const int*)fail_flag, list, NB / 8);
+        ++*launches;
+      }
       if (la && cnt > 1) cudaEventRecord(aux->ev_next, s2);
-      chol_syrk_col_kernel<32><<<16, 128, kSyrkLatSmem / 2, s2>>>(S, n, k0, list, fail_flag, 0);  // tile (K+1, K+1): 10 active CTAs of 32 x 32
-      ++*launches;
+      {  // tile (K+1, K+1): 10 active CTAs of 32 x 32
+        cudaLaunchConfig_t cfg = chain_cfg(16, 128, kSyrkLatSmem / 2);
+        cudaLaunchKernelEx(&cfg, chol_syrk_col_kernel<32>, S, n, k0, list, (const int*)fail_flag, 0);
+        ++*launches;
+      }
     }
     const int rest_cnt = has_col ? cnt - 1 : cnt;
     if (rest_cnt > 0) {
