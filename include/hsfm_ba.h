@@ -232,6 +232,12 @@ int hsfm_ba_problem_solve(hsfm_ba_ctx* ctx, const hsfm_ba_options* opts, hsfm_ba
 int hsfm_ba_problem_eval(hsfm_ba_ctx* ctx, double* cost);
 /* Copy the current parameters back. */
 int hsfm_ba_problem_download(hsfm_ba_ctx* ctx, double* cam_rt, double* pts);
+/* Per-keyframe reprojection statistics at the current parameters: for camera c over its
+ * observations, rms_px[c] = sqrt(mean d^2) and max_px[c] = sqrt(max d^2), d = reprojection distance in pixels —
+ * the two numbers CSfM::bundleAdjustment hands to CKeyFrame::updateFrameErrorStatistics in the block the reference
+ * keeps commented out (CSfM.cpp:350-382; TODO at CSfM.cpp:24-27).  Either array ([n_cams]) may be NULL; cameras
+ * without observations get 0.  With several ranks every rank receives the statistics over all shards. */
+int hsfm_ba_problem_frame_stats(hsfm_ba_ctx* ctx, double* rms_px, double* max_px);
 /* Algorithmic byte counts of one launch of the named kernel on the resident problem
  * ("rj", "schur_matvec", "cam_form", "backsub"); 0 if unknown.  DESIGN.md derives them. */
 int64_t hsfm_ba_problem_algorithmic_bytes(hsfm_ba_ctx* ctx, const char* kernel);

@@ -111,6 +111,26 @@ def evaluate(prob, cam=None, pts=None, want_jac=True, threads=1):
     return r, J, cost.value
 
 
+def frame_error_stats(prob, cam=None, pts=None):
+    """Per-keyframe reprojection statistics as the reference computes them in the block it keeps commented out
+    (CSfM.cpp:350-382): walking the observations frame by frame, dist = squared pixel distance between the
+    reprojected point and the observation (CSfM.cpp:376), meanDist /= count (:381), and the two numbers handed
+    to updateFrameErrorStatistics are sqrt(meanDist), sqrt(maxDist) (:382).  Plain loop over the oracle's
+    residuals (r = projected - observed, CTracker.cpp:601-602)."""
+    r, _, _ = evaluate(prob, cam, pts, want_jac=False)
+    mean = np.zeros(prob.n_cams)
+    mx = np.zeros(prob.n_cams)
+    count = np.zeros(prob.n_cams, dtype=np.int64)
+    for i in range(prob.n_obs):
+        c = int(prob.cam_idx[i])
+        dist = r[i, 0] * r[i, 0] + r[i, 1] * r[i, 1]
+        mx[c] = dist if dist > mx[c] else mx[c]
+        mean[c] += dist
+        count[c] += 1
+    mean = np.where(count > 0, mean / np.maximum(count, 1), 0.0)
+    return np.sqrt(mean), np.sqrt(mx)
+
+
 def schur(prob, radius=1e4, opts=None, cam=None, pts=None):
     cam = prob.cam if cam is None else cam
     pts = prob.pts if pts is None else pts

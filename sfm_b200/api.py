@@ -50,6 +50,7 @@ SYMBOLS = {
     "hsfm_ba_problem_reset": (C.c_int, [C.c_void_p]),
     "hsfm_ba_problem_solve": (C.c_int, [C.c_void_p, C.POINTER(Options), C.POINTER(Summary)]),
     "hsfm_ba_problem_eval": (C.c_int, [C.c_void_p, _dp]),
+    "hsfm_ba_problem_frame_stats": (C.c_int, [C.c_void_p, _dp, _dp]),
     "hsfm_ba_problem_download": (C.c_int, [C.c_void_p, _dp, _dp]),
     "hsfm_ba_problem_algorithmic_bytes": (C.c_int64, [C.c_void_p, C.c_char_p]),
     "hsfm_ba_problem_time_kernel": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, _dp]),
@@ -262,6 +263,16 @@ class Context:
         if rc:
             raise BAError(rc, "hsfm_ba_problem_eval")
         return cost.value if want_cost else None
+
+    def frame_stats(self):
+        """Per-camera (rms, max) reprojection distance in pixels at the current parameters
+        (the statistics of CSfM.cpp:350-382)."""
+        n = self._keep.n_cams
+        rms, mx = np.empty(n), np.empty(n)
+        rc = self.lib.hsfm_ba_problem_frame_stats(self.h, _d(rms), _d(mx))
+        if rc:
+            raise BAError(rc, "hsfm_ba_problem_frame_stats")
+        return rms, mx
 
     def download(self):
         p = self._keep

@@ -198,6 +198,34 @@ int hsfm_ba_problem_eval(hsfm_ba_ctx* h, double* cost) {
   return 0;
 }
 
+int hsfm_ba_problem_frame_stats(hsfm_ba_ctx* h, double* rms_px, double* max_px) {
+  if (!h || !h->c.has_problem) return HSFM_BA_ERR_STATE;
+  if (!rms_px && !max_px) return HSFM_BA_ERR_ARG;
+  Problem& P = h->c.prob;
+  cudaStream_t s = h->c.stream;
+  HSFM_CUDA(cudaSetDevice(h->c.device));
+  const size_t nc = (size_t)P.n_cams;
+  if (nc == 0) return 0;
+  launch_cam_prep(P, P.cam_x, nullptr, P.rows_x, s);
+  double* out3 = P.rhs;  // 6 n_cams doubles of per-solve scratch: [sum d^2 | count | max d^2]
+  launch_frame_stats(P, P.rows_x, P.pts_x, out3, s);
+  if (h->c.comm.n_ranks > 1) {  // observations are sharded by point: a camera's observations live on every rank
+    int rc = h->c.comm.allreduce_sum(out3, 2 * nc, s);
+    if (rc) return rc;
+    rc = h->c.comm.allreduce_max(out3 + 2 * nc, nc, s);
+    if (rc) return rc;
+  }
+  std::vector<double> host(3 * nc);
+  HSFM_CUDA(cudaMemcpyAsync(host.data(), out3, sizeof(double) * 3 * nc, cudaMemcpyDeviceToHost, s));
+  HSFM_CUDA(cudaStreamSynchronize(s));
+  for (size_t c = 0; c < nc; ++c) {
+    const double cnt = host[nc + c];
+    if (rms_px) rms_px[c] = cnt > 0.0 ? std::sqrt(host[c] / cnt) : 0.0;
+    if (max_px) max_px[c] = std::sqrt(host[2 * nc + c]);
+  }
+  return 0;
+}
+
 int hsfm_ba_problem_download(hsfm_ba_ctx* h, double* cam_rt, double* pts) {
   if (!h || !h->c.has_problem) return HSFM_BA_ERR_STATE;
   Problem& P = h->c.prob;

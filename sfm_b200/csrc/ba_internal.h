@@ -155,6 +155,7 @@ void launch_cam_step(Problem& P, cudaStream_t s);       // candidate cameras, no
 void launch_block_solve_cams(Problem& P, cudaStream_t s);  // pose-only: yc = Minv gc
 void launch_grad_norm(Problem& P, cudaStream_t s);      // max |g/scale| partials
 void launch_finalize_scalars(Problem& P, cudaStream_t s);  // partials -> scal[]
+void launch_frame_stats(Problem& P, const CamRow* rows, const double* pts, double* out3 /*[3 n_cams]: sum d^2, count, max d^2*/, cudaStream_t s);
 void launch_pcg_init(Problem& P, cudaStream_t s);
 void launch_pcg_step(Problem& P, double tol, int max_it, cudaStream_t s);
 struct CholPlan;

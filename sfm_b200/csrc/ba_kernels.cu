@@ -441,6 +441,53 @@ __global__ void __launch_bounds__(256) cam_major_kernel(Dev d, const CamRow* __r
   }
 }
 
+// Per-keyframe reprojection statistics after the adjustment (the block the reference keeps
+// commented out at CSfM.cpp:350-382 and asks for in its TODOs, CSfM.cpp:24-27): for every camera the sum and the
+// maximum of the squared reprojection distance over its observations.  Camera-major, one warp per chunk.
+__global__ void __launch_bounds__(256) frame_stats_kernel(Dev d, const CamRow* __restrict__ rows, const double* __restrict__ pts,
+                                                          double* __restrict__ chunk_part) {
+  const int lane = threadIdx.x & 31;
+  const int wc = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (wc >= d.n_chunks) return;
+  const int c = __ldg(d.chunk_cam + wc);
+  const int b = __ldg(d.chunk_b + wc), e = __ldg(d.chunk_e + wc);
+  const CamRow C = load_row(rows, c);
+  const double sp[3] = {1.0, 1.0, 1.0};
+  double sum = 0.0, mx = 0.0;
+  for (int j = b + lane; j < e; j += 32) {
+    const double2 o = __ldg(d.obs_cs + j);
+    const int p = __ldg(d.pt_cs + j);
+    double r0, r1, jc[12], jp[6];
+    reproject_rj(C, __ldg(pts + 3 * (size_t)p), __ldg(pts + 3 * (size_t)p + 1), __ldg(pts + 3 * (size_t)p + 2), o.x, o.y, sp, r0, r1, jc, jp);
+    const double d2 = r0 * r0 + r1 * r1;
+    sum += d2;
+    mx = fmax(mx, d2);
+  }
+#pragma unroll
+  for (int dd = 16; dd > 0; dd >>= 1) {
+    sum += __shfl_xor_sync(FULL, sum, dd);
+    mx = fmax(mx, __shfl_xor_sync(FULL, mx, dd));
+  }
+  if (lane == 0) {
+    chunk_part[(size_t)wc * 27] = sum;
+    chunk_part[(size_t)wc * 27 + 1] = mx;
+    chunk_part[(size_t)wc * 27 + 2] = (double)(e - b);
+  }
+}
+// out[c] = sum, out[n_cams + c] = observation count, out[2 n_cams + c] = max of the squared distances of camera c
+__global__ void frame_stats_reduce_kernel(int n_cams, const int* __restrict__ cam_chunk_start, const double* __restrict__ chunk_part,
+                                          double* __restrict__ out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n_cams) return;
+  double sum = 0.0, mx = 0.0, cnt = 0.0;
+  for (int w = cam_chunk_start[c]; w < cam_chunk_start[c + 1]; ++w) {
+    sum += chunk_part[(size_t)w * 27];
+    mx = fmax(mx, chunk_part[(size_t)w * 27 + 1]);
+    cnt += chunk_part[(size_t)w * 27 + 2];
+  }
+  out[c] = sum; out[n_cams + c] = cnt; out[2 * n_cams + c] = mx;
+}
+
 // Camera-major gather of the per-observation 6-vectors written point-major by schur_pass_kernel<0>:
 // one warp per chunk (<= 256 observations of one camera), 48-byte records fetched through the
 // camera-major → point-major permutation, warp-reduced into chunk_part[chunk][0..5].
@@ -1436,6 +1483,16 @@ void launch_dense_init(Problem& P, bool with_diag, cudaStream_t s, const CholPla
   }
   if (!with_diag) return;
   dense_init_kernel<<<cdiv(P.n_cams * 36, 256), 256, 0, s>>>(P.n_cams, P.Hcc, P.Dc2, P.S);
+  P.launches++;
+}
+
+void launch_frame_stats(Problem& P, const CamRow* rows, const double* pts, double* out3, cudaStream_t s) {
+  if (P.n_cams == 0) return;
+  if (P.n_chunks > 0) {
+    frame_stats_kernel<<<cdiv(P.n_chunks, 8), 256, 0, s>>>(P.d, rows, pts, P.chunk_part);
+    P.launches++;
+  }
+  frame_stats_reduce_kernel<<<cdiv(P.n_cams, 256), 256, 0, s>>>(P.n_cams, P.d.cam_chunk_start, P.chunk_part, out3);
   P.launches++;
 }
 

@@ -291,6 +291,32 @@ def test_resident_problem_repeatable(ctx):
     assert ctx.time_kernel("rj", 3) > 0
 
 
+def test_frame_error_statistics(ctx):
+    """per-keyframe (rms, max) reprojection distance, before and after the adjustment, against
+    the loop of CSfM.cpp:350-382 over the oracle's residuals.  1e-10 relative to the pixel scale (residuals cancel)."""
+    p = synth.make_ring(14, 400, 9, seed=11, name="stats")
+    ctx.upload(p)
+    rms, mx = ctx.frame_stats()
+    rms0, mx0 = po.frame_error_stats(p)
+    assert np.abs(rms - rms0).max() <= 1e-10 * max(1.0, rms0.max()) and np.abs(mx - mx0).max() <= 1e-10 * max(1.0, mx0.max())
+    ctx.solve_resident(api.default_options(linear_solver=api.LINEAR_DENSE_SCHUR))
+    cam, pts = ctx.download()
+    rms, mx = ctx.frame_stats()
+    rms1, mx1 = po.frame_error_stats(p, cam, pts)
+    assert np.abs(rms - rms1).max() <= 1e-9 and np.abs(mx - mx1).max() <= 1e-9
+    assert rms.max() < rms0.min()  # the adjustment brought every keyframe down
+    # a camera without observations reports 0
+    import dataclasses
+    keep = p.cam_idx != 3
+    q = dataclasses.replace(p, obs=np.ascontiguousarray(p.obs[keep]), cam_idx=np.ascontiguousarray(p.cam_idx[keep]),
+                            pt_idx=np.ascontiguousarray(p.pt_idx[keep]), name="nocam3")
+    ctx.upload(q)
+    rms, mx = ctx.frame_stats()
+    assert rms[3] == 0.0 and mx[3] == 0.0 and (rms[np.arange(p.n_cams) != 3] > 0).all()
+    rms2, mx2 = po.frame_error_stats(q)
+    assert np.abs(rms - rms2).max() <= 1e-10 * rms2.max() and np.abs(mx - mx2).max() <= 1e-10 * mx2.max()
+
+
 def test_full_size_properties_c4(ctx):
     """BASELINE configs[3] at full size (1778 cameras x 994k points x 5M observations): properties that
     need no CPU solve — consistency of the device-resident loop with an independent evaluation,

@@ -110,3 +110,14 @@ def test_distortion_extension_reduces_to_reference_at_zero():
     p.dist = np.zeros((p.n_cams, 2))
     r1, J1, c1 = po.evaluate(p)
     assert np.array_equal(r0, r1) and np.array_equal(J0, J1) and c0 == c1
+
+
+def test_frame_error_statistics_loop_equals_grouped_numpy():
+    """The restated loop of CSfM.cpp:350-382 against a vectorised grouping of the same residuals."""
+    p = synth.make_ring(9, 120, 5, seed=3, name="stats")
+    rms, mx = po.frame_error_stats(p)
+    r, _, _ = po.evaluate(p, want_jac=False)
+    d2 = (r * r).sum(axis=1)
+    for c in range(p.n_cams):
+        sel = d2[p.cam_idx == c]
+        assert rms[c] == pytest.approx(np.sqrt(sel.mean()), rel=1e-13) and mx[c] == pytest.approx(np.sqrt(sel.max()), rel=1e-15)
