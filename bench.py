@@ -136,10 +136,32 @@ def run_reference(args, rank, world):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "restated Ceres-1.12 semantics (oracle/), not Ceres itself: the reference cannot be compiled in this image",
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
+
+
+_JSON_FD = None
+
+
+def _claim_stdout():
+    """Everything any library writes to file descriptor 1 (NCCL's version banner, for one) goes to stderr from here
+    on; the one JSON line is written to the real stdout by _emit."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def _emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
 
 
 def main():
+    _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
@@ -159,8 +181,6 @@ def main():
         run_reference(args, rank, world)
         return
 
-    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-        os.environ["NCCL_DEBUG"] = "WARN"  # NCCL's version banner goes to stdout: keep stdout to the one JSON line
     import torch
     import torch.distributed as dist
 
@@ -328,7 +348,7 @@ def main():
             "e2e": e2e,
             "cpu_baseline": cpu,
         }
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if world > 1:
         dist.destroy_process_group()
     ctx.close()
