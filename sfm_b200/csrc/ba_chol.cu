@@ -42,6 +42,18 @@ __device__ __forceinline__ void pdl_enter() {
   asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
+// Global loads for the latency-bound chain kernels (volatile: kept where they are written by the front end).
+__device__ __forceinline__ double ld_now(const double* p) {
+  double v;
+  asm volatile("ld.global.nc.f64 %0, [%1];" : "=d"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ double2 ld_now2(const double* p) {
+  double2 v;
+  asm volatile("ld.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
+  return v;
+}
+
 __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
@@ -874,14 +886,28 @@ __global__ void __launch_bounds__(128) chol_syrk_col_kernel(double* __restrict__
   const int ni = min(LT, n - ri), nj = min(LT, n - rj);
   if (ni <= 0 || nj <= 0 || *fail) return;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, fr = lane >> 2, fk = lane & 3;
-  for (int e = tid; e < LT * (NB / 2); e += 128) {
-    const int row = e >> 6, c2 = (e & 63) * 2;
-    if (row < ni) cp_async16(&sA[row][c2], S + (size_t)(ri + row) * n + k0 + c2);
-    else { sA[row][c2] = 0.0; sA[row][c2 + 1] = 0.0; }
-    if (row < nj) cp_async16(&sB[row][c2], S + (size_t)(rj + row) * n + k0 + c2);
-    else { sB[row][c2] = 0.0; sB[row][c2 + 1] = 0.0; }
+  // LT == 32 (the chain's tile): operands by plain loads, issued together with the accumulator preload — one memory
+  // round trip (ptxas puts a cp.async wait ahead of the other loads).  LT == 64: cp.async.
+  constexpr int NLD = LT == 32 ? LT * (NB / 2) / 128 : 1;
+  double2 opa[NLD], opb[NLD];
+  if (LT == 32) {
+#pragma unroll
+    for (int it = 0; it < NLD; ++it) {
+      const int e = tid + 128 * it, row = e >> 6, c2 = (e & 63) * 2;
+      opa[it] = make_double2(0.0, 0.0); opb[it] = make_double2(0.0, 0.0);
+      if (row < ni) opa[it] = ld_now2(S + (size_t)(ri + row) * n + k0 + c2);
+      if (row < nj) opb[it] = ld_now2(S + (size_t)(rj + row) * n + k0 + c2);
+    }
+  } else {
+    for (int e = tid; e < LT * (NB / 2); e += 128) {
+      const int row = e >> 6, c2 = (e & 63) * 2;
+      if (row < ni) cp_async16(&sA[row][c2], S + (size_t)(ri + row) * n + k0 + c2);
+      else { sA[row][c2] = 0.0; sA[row][c2 + 1] = 0.0; }
+      if (row < nj) cp_async16(&sB[row][c2], S + (size_t)(rj + row) * n + k0 + c2);
+      else { sB[row][c2] = 0.0; sB[row][c2 + 1] = 0.0; }
+    }
+    cp_async_commit();
   }
-  cp_async_commit();
   const int wr = warp >> 1, wc = warp & 1;  // 2 x 2 warps of H x H
   double acc[NT][NT][2];
   double* const crow = S + (size_t)(ri + wr * H + fr) * n + rj + wc * H + 2 * fk;
@@ -892,12 +918,26 @@ __global__ void __launch_bounds__(128) chol_syrk_col_kernel(double* __restrict__
       acc[p][q][0] = 0.0; acc[p][q][1] = 0.0;
       const int row = wr * H + p * 8 + fr, col = wc * H + q * 8 + 2 * fk;
       if (row < ni && col < nj) {
-        const double2 c = *reinterpret_cast<const double2*>(crow + (size_t)p * 8 * n + q * 8);
+        const double2 c = ld_now2(crow + (size_t)p * 8 * n + q * 8);
         acc[p][q][0] = c.x; acc[p][q][1] = c.y;
       }
     }
-  cp_async_wait<0>();
-  __syncthreads();
+  int nonfinite = 0;  // ties the accumulator preload to the barrier (see chol_trsm_strip_kernel)
+#pragma unroll
+  for (int p = 0; p < NT; ++p)
+#pragma unroll
+    for (int q = 0; q < NT; ++q) nonfinite |= ((__double2hiint(acc[p][q][0]) | __double2hiint(acc[p][q][1])) & 0x7ff00000) == 0x7ff00000;
+  if (LT == 32) {
+#pragma unroll
+    for (int it = 0; it < NLD; ++it) {
+      const int e = tid + 128 * it, row = e >> 6, c2 = (e & 63) * 2;
+      *reinterpret_cast<double2*>(&sA[row][c2]) = opa[it];
+      *reinterpret_cast<double2*>(&sB[row][c2]) = opb[it];
+    }
+  } else {
+    cp_async_wait<0>();
+  }
+  if (__syncthreads_or(nonfinite)) return;
 #pragma unroll 4
   for (int ks = 0; ks < NB / 4; ++ks) {
     double af[NT], bf[NT];
@@ -944,12 +984,24 @@ __global__ void __launch_bounds__(256) chol_trsm_strip_kernel(double* __restrict
     nr = min(rows_per, n - r0);
   }
   const int tid = threadIdx.x;
-  for (int e = tid; e < rows_per * (NB / 2); e += 256) {
-    const int row = e >> 6, c2 = (e & 63) * 2;
-    if (row < nr) cp_async16(&sA[row][c2], S + (size_t)(r0 + row) * n + k0 + c2);
-    else { sA[row][c2] = 0.0; sA[row][c2 + 1] = 0.0; }
+  // Latency path (<= 16 rows): the strip comes by plain loads into registers, issued together with the B fragments
+  // below — ONE memory round trip.  (With cp.async ptxas puts the wait for the copies ahead of the fragment loads.)
+  double2 strip[4];
+  if (rows_per <= 16) {
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const int e = tid + 256 * it, row = e >> 6, c2 = (e & 63) * 2;
+      strip[it] = make_double2(0.0, 0.0);
+      if (e < rows_per * (NB / 2) && row < nr) strip[it] = ld_now2(S + (size_t)(r0 + row) * n + k0 + c2);
+    }
+  } else {
+    for (int e = tid; e < rows_per * (NB / 2); e += 256) {
+      const int row = e >> 6, c2 = (e & 63) * 2;
+      if (row < nr) cp_async16(&sA[row][c2], S + (size_t)(r0 + row) * n + k0 + c2);
+      else { sA[row][c2] = 0.0; sA[row][c2 + 1] = 0.0; }
+    }
+    cp_async_commit();
   }
-  cp_async_commit();
   const int warp = tid >> 5, lane = tid & 31, fr = lane >> 2, fk = lane & 3;
   const int RT = rows_per >> 3;
   const int ct_lo = warp, ct_hi = 15 - warp;
@@ -964,12 +1016,24 @@ __global__ void __launch_bounds__(256) chol_trsm_strip_kernel(double* __restrict
     // B fragments of the warp's two column tiles are fetched in ONE round trip, before the strip lands.
     double bh[32], bl[16];
 #pragma unroll
-    for (int u = 0; u < 32; ++u) bh[u] = (u < ks_hi) ? __ldg(Bhi + 4 * u) : 0.0;
+    for (int u = 0; u < 32; ++u) bh[u] = (u < ks_hi) ? ld_now(Bhi + 4 * u) : 0.0;
 #pragma unroll
-    for (int u = 0; u < 16; ++u) bl[u] = (u < ks_lo) ? __ldg(Blo + 4 * u) : 0.0;
-    cp_async_wait<0>();
-    __syncthreads();
-    if (failed || nr <= 0) return;
+    for (int u = 0; u < 16; ++u) bl[u] = (u < ks_lo) ? ld_now(Blo + 4 * u) : 0.0;
+    // The barrier's predicate depends on every fragment (a NaN/Inf check that is worth having anyway), so ptxas cannot
+    // sink these loads below it into the multiply loop — which it otherwise does, and which costs a second memory
+    // round trip (2.3 us per panel of the chain, measured with scripts/chain_timing.py).
+    int nonfinite = 0;
+#pragma unroll
+    for (int u = 0; u < 32; ++u) nonfinite |= (__double2hiint(bh[u]) & 0x7ff00000) == 0x7ff00000;
+#pragma unroll
+    for (int u = 0; u < 16; ++u) nonfinite |= (__double2hiint(bl[u]) & 0x7ff00000) == 0x7ff00000;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const int e = tid + 256 * it, row = e >> 6, c2 = (e & 63) * 2;
+      if (e < rows_per * (NB / 2)) *reinterpret_cast<double2*>(&sA[row][c2]) = strip[it];
+    }
+    nonfinite = __syncthreads_or(nonfinite);
+    if (failed || nr <= 0 || nonfinite) return;
 #pragma unroll
     for (int u = 0; u < 32; ++u) {
       if (u < ks_hi) {
