@@ -965,8 +965,10 @@ __global__ void dense_init_kernel(int n_cams, const double* __restrict__ Hcc, co
 // the FP64 atomic rate of the one-thread-per-block scatter (scripts/micro/fp64_peaks.cu).  Observations of a
 // point are stored with ascending camera (ba_index.cu), so pair (i,j), j <= i, lands in the lower triangle.
 constexpr int kDenseSchurSmem = TILE * 36 * (int)sizeof(double) + (3 * TILE + 8) * (int)sizeof(int) + 8 * 8 * 36 * (int)sizeof(double) + 8 * 8 * (int)sizeof(long long);
+// The sorted path runs 16 warps on a tile (512 threads; the first 256 stage the tile's observations), each with four
+// staging slots: twice the warps per SM at the same shared-memory footprint — the pair loop is latency-bound.
 template <bool SORTED>
-__global__ void __launch_bounds__(TILE) dense_schur_kernel(Dev d, const double* __restrict__ Hpp_inv, double* __restrict__ S) {
+__global__ void __launch_bounds__(SORTED ? 2 * TILE : TILE, 2) dense_schur_kernel(Dev d, const double* __restrict__ Hpp_inv, double* __restrict__ S) {
   extern __shared__ __align__(16) unsigned char ds_raw[];
   double (*sA)[18] = reinterpret_cast<double (*)[18]>(ds_raw);
   double (*sW)[18] = reinterpret_cast<double (*)[18]>(ds_raw + TILE * 18 * sizeof(double));
@@ -1031,15 +1033,16 @@ __global__ void __launch_bounds__(TILE) dense_schur_kernel(Dev d, const double* 
   // element).  The accumulator fragments go through a warp-private 8 x 36 staging buffer so that the reduction
   // into S keeps its efficient shape: nine full-warp passes in which consecutive lanes take consecutive block
   // elements (whole 48-byte rows per RED instruction).
-  double* sC = reinterpret_cast<double*>(sWarpTot + 8) + warp * (8 * 36);                    // [8][36] per warp
-  long long* sBase = reinterpret_cast<long long*>(reinterpret_cast<double*>(sWarpTot + 8) + 8 * 8 * 36) + warp * 8;  // [8] per warp
+  constexpr int SLOTS = SORTED ? 4 : 8, NW = SORTED ? 2 * TILE / 32 : TILE / 32, NPASS = (SLOTS * 36 + 31) / 32;
+  double* sC = reinterpret_cast<double*>(sWarpTot + 8) + warp * (SLOTS * 36);                // [SLOTS][36] per warp
+  long long* sBase = reinterpret_cast<long long*>(reinterpret_cast<double*>(sWarpTot + 8) + 8 * 8 * 36) + warp * SLOTS;  // [SLOTS] per warp
   const int fr = lane >> 2, fk = lane & 3;
   const bool frag_ok = fr < 6 && fk < 3;
   // which pair and which element of its block this lane reduces in each of the nine passes: lane constants
-  int pass_pl[9];
-  size_t pass_off[9], pass_offT[9];
+  int pass_pl[NPASS];
+  size_t pass_off[NPASS], pass_offT[NPASS];
 #pragma unroll
-  for (int pass = 0; pass < 9; ++pass) {
+  for (int pass = 0; pass < NPASS; ++pass) {
     const int g = pass * 32 + lane, pl = g / 36, e = g - pl * 36, a = e / 6, b = e - a * 6;
     pass_pl[pass] = pl;
     pass_off[pass] = (size_t)a * ld + b;
@@ -1054,7 +1057,7 @@ __global__ void __launch_bounds__(TILE) dense_schur_kernel(Dev d, const double* 
   auto reduce_staged = [&](int cnt) {
     __syncwarp();
 #pragma unroll
-    for (int pass = 0; pass < 9; ++pass) {
+    for (int pass = 0; pass < NPASS; ++pass) {
       if (pass_pl[pass] < cnt) {
         const long long bs = sBase[pass_pl[pass]];
         double* dst = (bs >= 0) ? S + bs + pass_off[pass] : S + (-1 - bs) + pass_offT[pass];
@@ -1070,7 +1073,7 @@ __global__ void __launch_bounds__(TILE) dense_schur_kernel(Dev d, const double* 
     const int p_off = __ldg(d.pair_off + blockIdx.x);
     const int n_pairs = __ldg(d.pair_off + blockIdx.x + 1) - p_off;
     const unsigned* __restrict__ list = d.pair_list + p_off;
-    const int chunk = (n_pairs + 7) >> 3;
+    const int chunk = (n_pairs + NW - 1) / NW;
     const int beg = warp * chunk, end = min(n_pairs, beg + chunk);
     int nbuf = 0, li = 0, lj = 0;
     unsigned cur = 0x10000u;  // no destination yet
@@ -1078,7 +1081,7 @@ __global__ void __launch_bounds__(TILE) dense_schur_kernel(Dev d, const double* 
     auto flush = [&]() {
       if (frag_ok) *reinterpret_cast<double2*>(sC + nbuf * 36 + fr * 6 + 2 * fk) = make_double2(c0, c1);
       if (lane == 0) sBase[nbuf] = block_base(li, lj);
-      if (++nbuf == 8) { reduce_staged(8); nbuf = 0; }
+      if (++nbuf == SLOTS) { reduce_staged(SLOTS); nbuf = 0; }
     };
     for (int base = beg; base < end; base += 32) {
       const unsigned key = (base + lane < end) ? __ldg(list + base + lane) : 0xffffffffu;
@@ -1521,7 +1524,7 @@ void launch_dense_schur(Problem& P, cudaStream_t s, bool sorted_pairs) {
       P.pairs_ready = true;
     }
   }
-  if (P.pairs_ready && sorted_pairs) dense_schur_kernel<true><<<P.n_tiles, TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S);
+  if (P.pairs_ready && sorted_pairs) dense_schur_kernel<true><<<P.n_tiles, 2 * TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S);
   else dense_schur_kernel<false><<<P.n_tiles, TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S);
   P.launches++;
 }
