@@ -48,3 +48,15 @@ def test_not_positive_definite_is_reported(ctx):
     assert ei.value.code == -1 and 1 <= ei.value.pivot <= 151
     with pytest.raises(api.BAError):
         ctx.dense_spd_solve(np.eye(3), np.ones(3))  # odd n is outside the contract (6*n_cams is even)
+
+
+@pytest.mark.parametrize("where", [(3, 3), (140, 7), (399, 399)])
+def test_non_finite_input_is_reported_not_propagated(ctx, where):
+    """NaN anywhere in the lower triangle fails a pivot test (NaN > 0 is false) or the finiteness test of the panel
+    operands; the call returns an error instead of a factor full of NaN."""
+    A = spd(400, 9)
+    A[where] = np.nan
+    A[where[::-1]] = np.nan
+    with pytest.raises(api.BAError) as ei:
+        ctx.dense_spd_solve(A, np.ones(400))
+    assert ei.value.code == -1
