@@ -1078,10 +1078,36 @@ __global__ void __launch_bounds__(SORTED ? 2 * TILE : TILE, 2) dense_schur_kerne
     int nbuf = 0, li = 0, lj = 0;
     unsigned cur = 0x10000u;  // no destination yet
     double c0 = 0.0, c1 = 0.0;
+    // The pair loop is instruction-issue-bound (ncu: 64 % issue-active, no dominant stall), so the hand-over of a
+    // finished block is kept short: the base offset is one 32x32->64-bit multiply-add computed by every lane (no
+    // divergent single-lane section), offsets inside a block are 32-bit lane constants, and the staged reduction
+    // assumes ci >= cj — what the index guarantees (cameras ascend inside a point); a block with ci < cj would go
+    // out transposed, element by element, straight from the fragment registers.
+    const unsigned ld32 = (unsigned)ld;
+    unsigned off32[NPASS];
+#pragma unroll
+    for (int pass = 0; pass < NPASS; ++pass) off32[pass] = (unsigned)pass_off[pass];
+    unsigned long long* sBaseU = reinterpret_cast<unsigned long long*>(sBase);
+    auto reduce_sorted = [&](int cnt) {
+      __syncwarp();
+#pragma unroll
+      for (int pass = 0; pass < NPASS; ++pass) {
+        if (pass_pl[pass] < cnt) atomicAdd(S + (sBaseU[pass_pl[pass]] + off32[pass]), -sC[pass * 32 + lane]);
+      }
+      __syncwarp();
+    };
     auto flush = [&]() {
-      if (frag_ok) *reinterpret_cast<double2*>(sC + nbuf * 36 + fr * 6 + 2 * fk) = make_double2(c0, c1);
-      if (lane == 0) sBase[nbuf] = block_base(li, lj);
-      if (++nbuf == SLOTS) { reduce_staged(SLOTS); nbuf = 0; }
+      const unsigned ci = (unsigned)sCam[li], cj = (unsigned)sCam[lj];
+      if (ci >= cj) {  // warp-uniform
+        if (frag_ok) *reinterpret_cast<double2*>(sC + nbuf * 36 + fr * 6 + 2 * fk) = make_double2(c0, c1);
+        const unsigned long long bs = (unsigned long long)(6u * ci) * ld32 + 6u * cj;
+        if (lane == 0) sBaseU[nbuf] = bs;
+        if (++nbuf == SLOTS) { reduce_sorted(SLOTS); nbuf = 0; }
+      } else if (frag_ok) {
+        double* dst = S + (size_t)(6u * cj + 2 * fk) * ld + 6u * ci + fr;
+        atomicAdd(dst, -c0);
+        atomicAdd(dst + ld, -c1);
+      }
     };
     for (int base = beg; base < end; base += 32) {
       const unsigned key = (base + lane < end) ? __ldg(list + base + lane) : 0xffffffffu;
@@ -1106,7 +1132,7 @@ __global__ void __launch_bounds__(SORTED ? 2 * TILE : TILE, 2) dense_schur_kerne
       }
     }
     if (cur != 0x10000u) flush();
-    if (nbuf) reduce_staged(nbuf);
+    if (nbuf) reduce_sorted(nbuf);
     return;
   }
   // Unsorted fallback (no pair list): every warp takes 8 pairs (288 block elements) at a time, round-robin over the
