@@ -43,6 +43,7 @@ __device__ __forceinline__ void pdl_enter() {
 }
 
 // Global loads for the latency-bound chain kernels (volatile: kept where they are written by the front end).
+__device__ __forceinline__ int is_nonfinite(double v) { return (__double2hiint(v) & 0x7ff00000) == 0x7ff00000; }  // Inf or NaN
 __device__ __forceinline__ double ld_now(const double* p) {
   double v;
   asm volatile("ld.global.nc.f64 %0, [%1];" : "=d"(v) : "l"(p));
@@ -926,7 +927,7 @@ __global__ void __launch_bounds__(128) chol_syrk_col_kernel(double* __restrict__
 #pragma unroll
   for (int p = 0; p < NT; ++p)
 #pragma unroll
-    for (int q = 0; q < NT; ++q) nonfinite |= ((__double2hiint(acc[p][q][0]) | __double2hiint(acc[p][q][1])) & 0x7ff00000) == 0x7ff00000;
+    for (int q = 0; q < NT; ++q) nonfinite |= is_nonfinite(acc[p][q][0]) | is_nonfinite(acc[p][q][1]);
   if (LT == 32) {
 #pragma unroll
     for (int it = 0; it < NLD; ++it) {
@@ -965,6 +966,120 @@ __global__ void __launch_bounds__(128) chol_syrk_col_kernel(double* __restrict__
 // ahead of their use, so the kernel needs only the strip in shared memory (<= 93 KB) and fits on an SM next
 // to a resident trailing-update CTA.  Only k <= column contributes (L11^-1 is lower triangular); warp w takes
 // the 8-column tiles w and 15-w, which together need the same 34 k-steps for every warp.
+// ---------------------------------------------------------------------------------------------
+// Chain kernel of the envelope factorisation: the next diagonal tile straight from the UNSOLVED panel block.
+//   S(K+1,K+1) -= L21 L21^T   with   L21 = A21 Linv^T   is   S(K+1,K+1) -= ((A21 Linv^T) Linv) A21^T,
+// and in that form every 8-row strip of the tile needs only its own rows of A21 (plus all of A21 and Linv as
+// read-only operands): 16 independent CTAs, ONE kernel and one memory round trip between two diagonal-block kernels
+// instead of panel solve -> hand-over -> tile update.  A21 is only read here; the panel solve that overwrites it with
+// L21 runs afterwards on the main stream together with the other rows of the panel.
+// Per CTA (strip r, 8 rows): Linv and A21 arrive by coalesced 16-byte loads (registers -> shared memory, the A21
+// copy takes over Linv's buffer once Linv is no longer needed); Z = A_r Linv^T, T = Z Linv (both triangular: half
+// the k-steps), D = T A21^T over the column tiles at or left of the strip's diagonal.  DMMA m8n8k4 throughout.
+constexpr int CT_LD = NB + 4;
+constexpr int kChainTileSmem = (NB + 3 * 8) * CT_LD * (int)sizeof(double);
+__global__ void __launch_bounds__(256, 1) chol_chain_tile_kernel(double* __restrict__ S, int n, int k0, const double* __restrict__ Linv,
+                                                                 const int* __restrict__ rb_list, const int* __restrict__ fail) {
+  extern __shared__ __align__(16) double csm[];
+  double (*sM)[CT_LD] = reinterpret_cast<double (*)[CT_LD]>(csm);                      // [128] Linv, later A21
+  double (*sA)[CT_LD] = reinterpret_cast<double (*)[CT_LD]>(csm + NB * CT_LD);          // [8] strip of A21
+  double (*sZ)[CT_LD] = reinterpret_cast<double (*)[CT_LD]>(csm + (NB + 8) * CT_LD);    // [8] Z
+  double (*sT)[CT_LD] = reinterpret_cast<double (*)[CT_LD]>(csm + (NB + 16) * CT_LD);   // [8] T
+  pdl_enter();
+  const int failed = *fail;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, fr = lane >> 2, fk = lane & 3;
+  const int blk = __ldg(rb_list);
+  const int b0 = blk * NB, nb = min(NB, n - b0);  // first row and number of valid rows of block K+1
+  const int strip = blockIdx.x, r0 = b0 + strip * 8;
+  if (strip * 8 >= nb) return;
+  // ---- every operand in one round trip ----
+  double2 li[32], am[32], cpre[2];
+#pragma unroll
+  for (int it = 0; it < 32; ++it) {
+    const int e = tid + 256 * it, row = e >> 6, c2 = (e & 63) * 2;
+    li[it] = make_double2(0.0, 0.0);
+    if (c2 <= row) li[it] = ld_now2(Linv + (size_t)row * NB + c2);  // lower triangular: the rest is zero
+    am[it] = make_double2(0.0, 0.0);
+    if (row < nb && row < 8 * (strip + 1)) am[it] = ld_now2(S + (size_t)(b0 + row) * n + k0 + c2);  // rows of the column tiles this strip updates
+  }
+  double2 st2[2];
+#pragma unroll
+  for (int it = 0; it < 2; ++it) {
+    const int e = tid + 256 * it, row = e >> 6, c2 = (e & 63) * 2;
+    st2[it] = make_double2(0.0, 0.0);
+    if (strip * 8 + row < nb) st2[it] = ld_now2(S + (size_t)(r0 + row) * n + k0 + c2);
+  }
+  const int ct_lo = warp, ct_hi = 15 - warp;
+  const bool row_ok = strip * 8 + fr < nb;
+  double* const crow = S + (size_t)(r0 + fr) * n + b0 + 2 * fk;
+  cpre[0] = make_double2(0.0, 0.0); cpre[1] = make_double2(0.0, 0.0);
+  if (row_ok && ct_lo <= strip && b0 + ct_lo * 8 + 2 * fk + 1 < n) cpre[0] = ld_now2(crow + ct_lo * 8);
+  if (row_ok && ct_hi <= strip && b0 + ct_hi * 8 + 2 * fk + 1 < n) cpre[1] = ld_now2(crow + ct_hi * 8);
+  int nonfinite = 0;
+#pragma unroll
+  for (int it = 0; it < 32; ++it)
+    nonfinite |= is_nonfinite(li[it].x) | is_nonfinite(li[it].y) | is_nonfinite(am[it].x) | is_nonfinite(am[it].y);
+  nonfinite |= is_nonfinite(cpre[0].x) | is_nonfinite(cpre[0].y) | is_nonfinite(cpre[1].x) | is_nonfinite(cpre[1].y);
+#pragma unroll
+  for (int it = 0; it < 32; ++it) {
+    const int e = tid + 256 * it, row = e >> 6, c2 = (e & 63) * 2;
+    *reinterpret_cast<double2*>(&sM[row][c2]) = li[it];
+  }
+#pragma unroll
+  for (int it = 0; it < 2; ++it) {
+    const int e = tid + 256 * it, row = e >> 6, c2 = (e & 63) * 2;
+    *reinterpret_cast<double2*>(&sA[row][c2]) = st2[it];
+  }
+  nonfinite = __syncthreads_or(nonfinite);
+  if (failed || nonfinite) return;
+  // ---- Z = A_r Linv^T : Z[r][c] = sum_{k <= c} A[r][k] Linv[c][k] ----
+  double z[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+  for (int u = 0; u < 32; ++u) {
+    if (u < 2 * (ct_hi + 1)) {
+      const double a = sA[fr][u * 4 + fk];
+      dmma884(z[1][0], z[1][1], a, sM[ct_hi * 8 + fr][u * 4 + fk]);
+      if (u < 2 * (ct_lo + 1)) dmma884(z[0][0], z[0][1], a, sM[ct_lo * 8 + fr][u * 4 + fk]);
+    }
+  }
+  *reinterpret_cast<double2*>(&sZ[fr][ct_lo * 8 + 2 * fk]) = make_double2(z[0][0], z[0][1]);
+  *reinterpret_cast<double2*>(&sZ[fr][ct_hi * 8 + 2 * fk]) = make_double2(z[1][0], z[1][1]);
+  __syncthreads();
+  // ---- T = Z Linv : T[r][c] = sum_{k >= c} Z[r][k] Linv[k][c] ----
+  double t[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+  for (int u = 0; u < 32; ++u) {
+    if (u >= 2 * ct_lo) {
+      const double a = sZ[fr][u * 4 + fk];
+      dmma884(t[0][0], t[0][1], a, sM[u * 4 + fk][ct_lo * 8 + fr]);
+      if (u >= 2 * ct_hi) dmma884(t[1][0], t[1][1], a, sM[u * 4 + fk][ct_hi * 8 + fr]);
+    }
+  }
+  __syncthreads();  // everybody is done with Linv in sM
+  *reinterpret_cast<double2*>(&sT[fr][ct_lo * 8 + 2 * fk]) = make_double2(t[0][0], t[0][1]);
+  *reinterpret_cast<double2*>(&sT[fr][ct_hi * 8 + 2 * fk]) = make_double2(t[1][0], t[1][1]);
+#pragma unroll
+  for (int it = 0; it < 32; ++it) {
+    const int e = tid + 256 * it, row = e >> 6, c2 = (e & 63) * 2;
+    *reinterpret_cast<double2*>(&sM[row][c2]) = am[it];
+  }
+  __syncthreads();
+  // ---- tile rows of the strip: C[r][c] -= sum_k T[r][k] A21[c][k], column tiles at or left of the diagonal ----
+  const bool do_lo = ct_lo <= strip, do_hi = ct_hi <= strip;
+  if (!do_lo && !do_hi) return;
+  double c[2][2] = {{cpre[0].x, cpre[0].y}, {cpre[1].x, cpre[1].y}};
+#pragma unroll 8
+  for (int u = 0; u < 32; ++u) {
+    const double a = -sT[fr][u * 4 + fk];
+    if (do_lo) dmma884(c[0][0], c[0][1], a, sM[ct_lo * 8 + fr][u * 4 + fk]);
+    if (do_hi) dmma884(c[1][0], c[1][1], a, sM[ct_hi * 8 + fr][u * 4 + fk]);
+  }
+  if (row_ok) {
+    if (do_lo && b0 + ct_lo * 8 + 2 * fk + 1 < n) *reinterpret_cast<double2*>(crow + ct_lo * 8) = make_double2(c[0][0], c[0][1]);
+    if (do_hi && b0 + ct_hi * 8 + 2 * fk + 1 < n) *reinterpret_cast<double2*>(crow + ct_hi * 8) = make_double2(c[1][0], c[1][1]);
+  }
+}
+
 constexpr int TS_LD = NB + 4;
 constexpr int TS_MAXROWS = 88;
 __global__ void __launch_bounds__(256) chol_trsm_strip_kernel(double* __restrict__ S, int n, int k0, const double* __restrict__ Linv,
@@ -1024,9 +1139,9 @@ __global__ void __launch_bounds__(256) chol_trsm_strip_kernel(double* __restrict
     // round trip (2.3 us per panel of the chain, measured with scripts/chain_timing.py).
     int nonfinite = 0;
 #pragma unroll
-    for (int u = 0; u < 32; ++u) nonfinite |= (__double2hiint(bh[u]) & 0x7ff00000) == 0x7ff00000;
+    for (int u = 0; u < 32; ++u) nonfinite |= is_nonfinite(bh[u]);
 #pragma unroll
-    for (int u = 0; u < 16; ++u) nonfinite |= (__double2hiint(bl[u]) & 0x7ff00000) == 0x7ff00000;
+    for (int u = 0; u < 16; ++u) nonfinite |= is_nonfinite(bl[u]);
 #pragma unroll
     for (int it = 0; it < 4; ++it) {
       const int e = tid + 256 * it, row = e >> 6, c2 = (e & 63) * 2;
@@ -1565,6 +1680,24 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
     const int* list = pl.d_list + pl.off[K];
     const bool has_col = pl.list[(size_t)pl.off[K]] == K + 1;
     if (la) cudaEventRecord(aux->ev_panel, s2);  // diag(K) done
+    static const bool split_chain = getenv("HSFM_CHAIN_SPLIT") != nullptr;  // experiment knob: panel solve + tile update as two kernels
+    if (has_col && !split_chain) {
+      // tile (K+1, K+1) straight from the unsolved block A(K+1, K): one kernel between two diagonal blocks
+      cudaLaunchConfig_t cfg = chain_cfg(NB / 8, 256, kChainTileSmem);
+      cudaLaunchKernelEx(&cfg, chol_chain_tile_kernel, S, n, k0, (const double*)Linv, list, (const int*)fail_flag);
+      ++*launches;
+      if (la) cudaEventRecord(aux->ev_next, s2);  // A(K+1, K) has been read: the main stream may overwrite it with L(K+1, K)
+      if (la) cudaStreamWaitEvent(s, aux->ev_panel, 0);
+      if (la) cudaStreamWaitEvent(s, aux->ev_next, 0);
+      trsm(s, k0, Linv, list, cnt);
+      const int tiles = cnt * (cnt + 1) - 2;
+      if (tiles > 0) {
+        chol_syrk_kernel<<<min(tiles, 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 0, -2, tiles, 0, fail_flag, list);
+        ++*launches;
+      }
+      if (la) { cudaEventRecord(aux->ev_rest, s); rest_pending = true; }
+      continue;
+    }
     if (has_col) {
       {  // L(K+1, K): 16 strips of 8 rows
         cudaLaunchConfig_t cfg = chain_cfg(NB / 8, 256, 8 * TS_LD * sizeof(double));
@@ -1610,6 +1743,7 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
     cudaFuncSetAttribute(chol_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem);
     cudaFuncSetAttribute(chol_syrk_col_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrkLatSmem);
     cudaFuncSetAttribute(chol_syrk_col_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrkLatSmem / 2);
+    cudaFuncSetAttribute(chol_chain_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kChainTileSmem);
     attr_set = true;
   }
   static int n_sm = 0;
