@@ -1427,7 +1427,7 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
       if (!h && r < nr) w[r0 + r] = y;
     }
     __syncthreads();
-    if (tid == 0) { __threadfence(); st_release(flag_fwd + i, 1); }
+    if (tid == 0) st_release(flag_fwd + i, 1);  // release after the barrier: cumulative over the CTA's writes of w (no separate fence: it costs a second MEMBAR and an L1 invalidate per step of the chain)
   }
   // ---- backward ----
   const int j = tid & (NB - 1), half = tid >> 7;
@@ -1470,7 +1470,7 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
       if (!half && j < kb) b[c0 + j] = acc + sp[j];
     }
     __syncthreads();
-    if (tid == 0) { __threadfence(); st_release(flag_bwd + kk, 1); }
+    if (tid == 0) st_release(flag_bwd + kk, 1);
   }
 }
 
