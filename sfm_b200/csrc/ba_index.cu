@@ -18,11 +18,13 @@ void Problem::release() {
   double* s_keep = S; const size_t s_cap = S_capacity;
   unsigned* pl_keep = pair_list; const size_t pl_cap = pair_capacity;
   double* sh = scal_host; int* fh = flags_host;
+  int* ih = idx_host; const size_t ih_cap = idx_host_cap;
   *this = Problem();
   arena = a; arena_cap = cap; arena_off = 0;
   S = s_keep; S_capacity = s_cap;
   pair_list = pl_keep; pair_capacity = pl_cap;
   scal_host = sh; flags_host = fh;
+  idx_host = ih; idx_host_cap = ih_cap;
 }
 
 void Problem::destroy() {
@@ -31,6 +33,7 @@ void Problem::destroy() {
   if (pair_list) cudaFree(pair_list);
   if (scal_host) cudaFreeHost(scal_host);
   if (flags_host) cudaFreeHost(flags_host);
+  if (idx_host) cudaFreeHost(idx_host);
   *this = Problem();
 }
 
@@ -310,8 +313,17 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   HSFM_CUDA(cudaStreamSynchronize(s));
 
   // ---- tiles: greedy packing of whole points into <= TILE observations (host, O(n_pts)) ----
-  std::vector<int> h_pt_start((size_t)n_pts + 1), h_cam_start((size_t)n_cams + 1);
-  HSFM_CUDA(cudaMemcpyAsync(h_pt_start.data(), pt_start, sizeof(int) * ((size_t)n_pts + 1), cudaMemcpyDeviceToHost, s));
+  // the point offsets come back through a pinned, grow-only staging buffer (a pageable 4 MB copy per call costs ~1 ms)
+  if (P.idx_host_cap < (size_t)n_pts + 1) {
+    if (P.idx_host) cudaFreeHost(P.idx_host);
+    P.idx_host = nullptr; P.idx_host_cap = 0;
+    const size_t want = ((size_t)n_pts + 1) * 5 / 4 + 1024;
+    HSFM_CUDA(cudaMallocHost(&P.idx_host, sizeof(int) * want));
+    P.idx_host_cap = want;
+  }
+  int* const h_pt_start = P.idx_host;
+  std::vector<int> h_cam_start((size_t)n_cams + 1);
+  HSFM_CUDA(cudaMemcpyAsync(h_pt_start, pt_start, sizeof(int) * ((size_t)n_pts + 1), cudaMemcpyDeviceToHost, s));
   HSFM_CUDA(cudaMemcpyAsync(h_cam_start.data(), cam_start, sizeof(int) * ((size_t)n_cams + 1), cudaMemcpyDeviceToHost, s));
   HSFM_CUDA(cudaStreamSynchronize(s));
   std::vector<int> tiles, tile_p;  // first observation / first point of every tile (+ end sentinels)

@@ -105,6 +105,8 @@ struct Problem {
   double *scal_host = nullptr;  // pinned mirror
   int *flags = nullptr;      // [8] device flags: 0 = not-PD / invalid, 1 = pcg done, 2 = pcg iterations
   int *flags_host = nullptr; // pinned mirror
+  int *idx_host = nullptr;   // pinned staging of the index build (point CSR offsets), grow-only
+  size_t idx_host_cap = 0;
   int64_t launches = 0;
   void release();
 };
