@@ -998,6 +998,7 @@ __global__ void __launch_bounds__(SORTED ? 2 * TILE : TILE, 2) dense_schur_kerne
       for (int b = 0; b < 3; ++b) W[a * 3 + b] = jc[a] * jp[b] + jc[6 + a] * jp[3 + b];
       double a0, a1, a2;
       sym3_mul(Hi, W[a * 3], W[a * 3 + 1], W[a * 3 + 2], a0, a1, a2);
+      if (SORTED) { a0 = -a0; a1 = -a1; a2 = -a2; }  // the sorted path accumulates -A W^T: what is added to S
       sA[threadIdx.x][a * 3] = a0; sA[threadIdx.x][a * 3 + 1] = a1; sA[threadIdx.x][a * 3 + 2] = a2;
       sW[threadIdx.x][a * 3] = W[a * 3]; sW[threadIdx.x][a * 3 + 1] = W[a * 3 + 1]; sW[threadIdx.x][a * 3 + 2] = W[a * 3 + 2];
     }
@@ -1077,6 +1078,7 @@ __global__ void __launch_bounds__(SORTED ? 2 * TILE : TILE, 2) dense_schur_kerne
     const int beg = warp * chunk, end = min(n_pairs, beg + chunk);
     int nbuf = 0, li = 0, lj = 0;
     unsigned cur = 0x10000u;  // no destination yet
+    bool diag_dest = false;
     double c0 = 0.0, c1 = 0.0;
     // The pair loop is instruction-issue-bound (ncu: 64 % issue-active, no dominant stall), so the hand-over of a
     // finished block is kept short: the base offset is one 32x32->64-bit multiply-add computed by every lane (no
@@ -1092,7 +1094,7 @@ __global__ void __launch_bounds__(SORTED ? 2 * TILE : TILE, 2) dense_schur_kerne
       __syncwarp();
 #pragma unroll
       for (int pass = 0; pass < NPASS; ++pass) {
-        if (pass_pl[pass] < cnt) atomicAdd(S + (sBaseU[pass_pl[pass]] + off32[pass]), -sC[pass * 32 + lane]);
+        if (pass_pl[pass] < cnt) atomicAdd(S + (sBaseU[pass_pl[pass]] + off32[pass]), sC[pass * 32 + lane]);
       }
       __syncwarp();
     };
@@ -1105,8 +1107,8 @@ __global__ void __launch_bounds__(SORTED ? 2 * TILE : TILE, 2) dense_schur_kerne
         if (++nbuf == SLOTS) { reduce_sorted(SLOTS); nbuf = 0; }
       } else if (frag_ok) {
         double* dst = S + (size_t)(6u * cj + 2 * fk) * ld + 6u * ci + fr;
-        atomicAdd(dst, -c0);
-        atomicAdd(dst + ld, -c1);
+        atomicAdd(dst, c0);
+        atomicAdd(dst + ld, c1);
       }
     };
     for (int base = beg; base < end; base += 32) {
@@ -1122,10 +1124,11 @@ __global__ void __launch_bounds__(SORTED ? 2 * TILE : TILE, 2) dense_schur_kerne
         if (dest != cur) {  // warp-uniform
           if (cur != 0x10000u) flush();
           cur = dest; c0 = 0.0; c1 = 0.0;
+          diag_dest = (dest >> 8) == (dest & 0xff);
         }
         li = i; lj = j;
         dmma884(c0, c1, a_frag, b_frag);
-        if (i != j && (dest >> 8) == (dest & 0xff)) {  // a camera listed twice in a track: diagonal block, M + M^T
+        if (diag_dest && i != j) {  // a camera listed twice in a track: diagonal block, M + M^T
           const double at = frag_ok ? sW[j][fr * 3 + fk] : 0.0, bt = frag_ok ? sA[i][fr * 3 + fk] : 0.0;
           dmma884(c0, c1, at, bt);
         }
