@@ -17,7 +17,7 @@ int main() {
   cudaMemcpy(S, h.data(), sizeof(double) * n * n, cudaMemcpyHostToDevice);
   cudaMemcpy(Linv, li.data(), sizeof(double) * NB * NB, cudaMemcpyHostToDevice);
   cudaFuncSetAttribute(chol_chain_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kChainTileSmem);
-  chol_chain_tile_kernel<<<16, 256, kChainTileSmem>>>(S, n, k0, Linv, list, fail);
+  chol_chain_tile_kernel<<<32, 256, kChainTileSmem>>>(S, n, k0, Linv, list, fail);
   std::vector<double> out((size_t)n * n);
   cudaMemcpy(out.data(), S, sizeof(double) * n * n, cudaMemcpyDeviceToHost);
   std::printf("launch: %s\n", cudaGetErrorString(cudaGetLastError()));

@@ -970,7 +970,7 @@ __global__ void __launch_bounds__(128) chol_syrk_col_kernel(double* __restrict__
 // Chain kernel of the envelope factorisation: the next diagonal tile straight from the UNSOLVED panel block.
 //   S(K+1,K+1) -= L21 L21^T   with   L21 = A21 Linv^T   is   S(K+1,K+1) -= ((A21 Linv^T) Linv) A21^T,
 // and in that form every 8-row strip of the tile needs only its own rows of A21 (plus all of A21 and Linv as
-// read-only operands): 16 independent CTAs, ONE kernel and one memory round trip between two diagonal-block kernels
+// read-only operands): independent CTAs (two per strip, one per half of the block's columns), ONE kernel and one memory round trip between two diagonal-block kernels
 // instead of panel solve -> hand-over -> tile update.  A21 is only read here; the panel solve that overwrites it with
 // L21 runs afterwards on the main stream together with the other rows of the panel.
 // Per CTA (strip r, 8 rows): Linv and A21 arrive by coalesced 16-byte loads (registers -> shared memory, the A21
@@ -990,17 +990,23 @@ __global__ void __launch_bounds__(256, 1) chol_chain_tile_kernel(double* __restr
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, fr = lane >> 2, fk = lane & 3;
   const int blk = __ldg(rb_list);
   const int b0 = blk * NB, nb = min(NB, n - b0);  // first row and number of valid rows of block K+1
-  const int strip = blockIdx.x, r0 = b0 + strip * 8;
-  if (strip * 8 >= nb) return;
+  // two CTAs per strip: each forms Z and T (cheap) and updates the column tiles of its half of the block, so it
+  // needs only 64 rows of A21
+  const int strip = blockIdx.x >> 1, half = blockIdx.x & 1, r0 = b0 + strip * 8;
+  if (strip * 8 >= nb || (half && strip < 8)) return;
   // ---- every operand in one round trip ----
-  double2 li[32], am[32], cpre[2];
+  double2 li[32], am[16], cpre;
 #pragma unroll
   for (int it = 0; it < 32; ++it) {
     const int e = tid + 256 * it, row = e >> 6, c2 = (e & 63) * 2;
     li[it] = make_double2(0.0, 0.0);
     if (c2 <= row) li[it] = ld_now2(Linv + (size_t)row * NB + c2);  // lower triangular: the rest is zero
+  }
+#pragma unroll
+  for (int it = 0; it < 16; ++it) {
+    const int e = tid + 256 * it, row = half * 64 + (e >> 6), c2 = (e & 63) * 2;
     am[it] = make_double2(0.0, 0.0);
-    if (row < nb && row < 8 * (strip + 1)) am[it] = ld_now2(S + (size_t)(b0 + row) * n + k0 + c2);  // rows of the column tiles this strip updates
+    if (row < nb && row < 8 * (strip + 1)) am[it] = ld_now2(S + (size_t)(b0 + row) * n + k0 + c2);  // rows of the column tiles this CTA updates
   }
   double2 st2[2];
 #pragma unroll
@@ -1012,14 +1018,16 @@ __global__ void __launch_bounds__(256, 1) chol_chain_tile_kernel(double* __restr
   const int ct_lo = warp, ct_hi = 15 - warp;
   const bool row_ok = strip * 8 + fr < nb;
   double* const crow = S + (size_t)(r0 + fr) * n + b0 + 2 * fk;
-  cpre[0] = make_double2(0.0, 0.0); cpre[1] = make_double2(0.0, 0.0);
-  if (row_ok && ct_lo <= strip && b0 + ct_lo * 8 + 2 * fk + 1 < n) cpre[0] = ld_now2(crow + ct_lo * 8);
-  if (row_ok && ct_hi <= strip && b0 + ct_hi * 8 + 2 * fk + 1 < n) cpre[1] = ld_now2(crow + ct_hi * 8);
+  const int ct3 = half * 8 + warp;  // the column tile this warp updates in the last product
+  const bool do3 = ct3 <= strip;
+  cpre = make_double2(0.0, 0.0);
+  if (row_ok && do3 && b0 + ct3 * 8 + 2 * fk + 1 < n) cpre = ld_now2(crow + ct3 * 8);
   int nonfinite = 0;
 #pragma unroll
-  for (int it = 0; it < 32; ++it)
-    nonfinite |= is_nonfinite(li[it].x) | is_nonfinite(li[it].y) | is_nonfinite(am[it].x) | is_nonfinite(am[it].y);
-  nonfinite |= is_nonfinite(cpre[0].x) | is_nonfinite(cpre[0].y) | is_nonfinite(cpre[1].x) | is_nonfinite(cpre[1].y);
+  for (int it = 0; it < 32; ++it) nonfinite |= is_nonfinite(li[it].x) | is_nonfinite(li[it].y);
+#pragma unroll
+  for (int it = 0; it < 16; ++it) nonfinite |= is_nonfinite(am[it].x) | is_nonfinite(am[it].y);
+  nonfinite |= is_nonfinite(cpre.x) | is_nonfinite(cpre.y);
 #pragma unroll
   for (int it = 0; it < 32; ++it) {
     const int e = tid + 256 * it, row = e >> 6, c2 = (e & 63) * 2;
@@ -1059,26 +1067,19 @@ __global__ void __launch_bounds__(256, 1) chol_chain_tile_kernel(double* __restr
   *reinterpret_cast<double2*>(&sT[fr][ct_lo * 8 + 2 * fk]) = make_double2(t[0][0], t[0][1]);
   *reinterpret_cast<double2*>(&sT[fr][ct_hi * 8 + 2 * fk]) = make_double2(t[1][0], t[1][1]);
 #pragma unroll
-  for (int it = 0; it < 32; ++it) {
-    const int e = tid + 256 * it, row = e >> 6, c2 = (e & 63) * 2;
+  for (int it = 0; it < 16; ++it) {
+    const int e = tid + 256 * it, row = half * 64 + (e >> 6), c2 = (e & 63) * 2;
     *reinterpret_cast<double2*>(&sM[row][c2]) = am[it];
   }
   __syncthreads();
   // ---- tile rows of the strip: C[r][c] -= sum_k T[r][k] A21[c][k], column tiles at or left of the diagonal ----
-  const bool do_lo = ct_lo <= strip, do_hi = ct_hi <= strip;
-  if (!do_lo && !do_hi) return;
-  double c[2][2] = {{cpre[0].x, cpre[0].y}, {cpre[1].x, cpre[1].y}};
+  if (!do3) return;
+  double c0 = cpre.x, c1 = cpre.y;
 #pragma unroll 8
-  for (int u = 0; u < 32; ++u) {
-    const double a = -sT[fr][u * 4 + fk];
-    if (do_lo) dmma884(c[0][0], c[0][1], a, sM[ct_lo * 8 + fr][u * 4 + fk]);
-    if (do_hi) dmma884(c[1][0], c[1][1], a, sM[ct_hi * 8 + fr][u * 4 + fk]);
-  }
-  if (row_ok) {
-    if (do_lo && b0 + ct_lo * 8 + 2 * fk + 1 < n) *reinterpret_cast<double2*>(crow + ct_lo * 8) = make_double2(c[0][0], c[0][1]);
-    if (do_hi && b0 + ct_hi * 8 + 2 * fk + 1 < n) *reinterpret_cast<double2*>(crow + ct_hi * 8) = make_double2(c[1][0], c[1][1]);
-  }
+  for (int u = 0; u < 32; ++u) dmma884(c0, c1, -sT[fr][u * 4 + fk], sM[ct3 * 8 + fr][u * 4 + fk]);
+  if (row_ok && b0 + ct3 * 8 + 2 * fk + 1 < n) *reinterpret_cast<double2*>(crow + ct3 * 8) = make_double2(c0, c1);
 }
+
 
 constexpr int TS_LD = NB + 4;
 constexpr int TS_MAXROWS = 88;
@@ -1683,7 +1684,7 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
     static const bool split_chain = getenv("HSFM_CHAIN_SPLIT") != nullptr;  // experiment knob: panel solve + tile update as two kernels
     if (has_col && !split_chain) {
       // tile (K+1, K+1) straight from the unsolved block A(K+1, K): one kernel between two diagonal blocks
-      cudaLaunchConfig_t cfg = chain_cfg(NB / 8, 256, kChainTileSmem);
+      cudaLaunchConfig_t cfg = chain_cfg(2 * (NB / 8), 256, kChainTileSmem);
       cudaLaunchKernelEx(&cfg, chol_chain_tile_kernel, S, n, k0, (const double*)Linv, list, (const int*)fail_flag);
       ++*launches;
       if (la) cudaEventRecord(aux->ev_next, s2);  // A(K+1, K) has been read: the main stream may overwrite it with L(K+1, K)
