@@ -1031,7 +1031,7 @@ __global__ void __launch_bounds__(256, 1) chol_chain_tile_kernel(double* __restr
 #pragma unroll
   for (int it = 0; it < 32; ++it) {
     const int e = tid + 256 * it, row = e >> 6, c2 = (e & 63) * 2;
-    *reinterpret_cast<double2*>(&sM[row][c2]) = li[it];
+    if (c2 < 8 * ((row >> 3) + 1)) *reinterpret_cast<double2*>(&sM[row][c2]) = li[it];  // nothing right of the diagonal 8x8 tile is ever read
   }
 #pragma unroll
   for (int it = 0; it < 2; ++it) {
