@@ -5,6 +5,7 @@
 // Build: g++ -O2 -ffp-contract=off -fopenmp (no -ffast-math, no FMA contraction: the dual-number
 // evaluation must round like a plain IEEE build of the reference would).
 #include "ba_oracle.h"
+#include "ba_oracle_jet.h"
 
 #include <algorithm>
 #include <chrono>
@@ -19,69 +20,7 @@
 
 namespace {
 
-// ------------------------------------------------------------------------------------------
-// Dual numbers with ceres::Jet<double,N> rules (Ceres 1.12 include/ceres/jet.h, published
-// upstream; not in /root/reference).  Value a, infinitesimal part v[N].
-// ------------------------------------------------------------------------------------------
-template <int N>
-struct Jet {
-  double a;
-  double v[N];
-  Jet() : a(0.0) { for (int i = 0; i < N; ++i) v[i] = 0.0; }
-  explicit Jet(double s) : a(s) { for (int i = 0; i < N; ++i) v[i] = 0.0; }
-  Jet(double s, int k) : a(s) { for (int i = 0; i < N; ++i) v[i] = 0.0; v[k] = 1.0; }
-};
-template <int N> inline Jet<N> operator+(const Jet<N>& f, const Jet<N>& g) {
-  Jet<N> h; h.a = f.a + g.a; for (int i = 0; i < N; ++i) h.v[i] = f.v[i] + g.v[i]; return h; }
-template <int N> inline Jet<N> operator-(const Jet<N>& f, const Jet<N>& g) {
-  Jet<N> h; h.a = f.a - g.a; for (int i = 0; i < N; ++i) h.v[i] = f.v[i] - g.v[i]; return h; }
-template <int N> inline Jet<N> operator*(const Jet<N>& f, const Jet<N>& g) {
-  Jet<N> h; h.a = f.a * g.a; for (int i = 0; i < N; ++i) h.v[i] = f.a * g.v[i] + f.v[i] * g.a; return h; }
-template <int N> inline Jet<N> operator/(const Jet<N>& f, const Jet<N>& g) {
-  // ceres: g_a_inverse = 1/g.a; f_a_by_g_a = f.a * g_a_inverse; (f.v - f_a_by_g_a * g.v) * g_a_inverse
-  const double gi = 1.0 / g.a; const double q = f.a * gi;
-  Jet<N> h; h.a = q; for (int i = 0; i < N; ++i) h.v[i] = (f.v[i] - q * g.v[i]) * gi; return h; }
-template <int N> inline Jet<N> operator/(double s, const Jet<N>& g) {
-  const double m = -s / (g.a * g.a);
-  Jet<N> h; h.a = s / g.a; for (int i = 0; i < N; ++i) h.v[i] = g.v[i] * m; return h; }
-template <int N> inline Jet<N> operator+=(Jet<N>& f, const Jet<N>& g) { f = f + g; return f; }
-template <int N> inline bool operator>(const Jet<N>& f, const Jet<N>& g) { return f.a > g.a; }
-template <int N> inline Jet<N> sqrt(const Jet<N>& f) {
-  const double t = std::sqrt(f.a); const double two_a_inverse = 1.0 / (2.0 * t);
-  Jet<N> h; h.a = t; for (int i = 0; i < N; ++i) h.v[i] = f.v[i] * two_a_inverse; return h; }
-template <int N> inline Jet<N> cos(const Jet<N>& f) {
-  const double ms = -std::sin(f.a);
-  Jet<N> h; h.a = std::cos(f.a); for (int i = 0; i < N; ++i) h.v[i] = ms * f.v[i]; return h; }
-template <int N> inline Jet<N> sin(const Jet<N>& f) {
-  const double c = std::cos(f.a);
-  Jet<N> h; h.a = std::sin(f.a); for (int i = 0; i < N; ++i) h.v[i] = c * f.v[i]; return h; }
-inline double sqrt(double x) { return std::sqrt(x); }
-inline double cos(double x) { return std::cos(x); }
-inline double sin(double x) { return std::sin(x); }
-
-// ceres::AngleAxisRotatePoint (Ceres 1.12 include/ceres/rotation.h).
-template <typename T>
-inline void AngleAxisRotatePoint(const T angle_axis[3], const T pt[3], T result[3]) {
-  const T theta2 = angle_axis[0] * angle_axis[0] + angle_axis[1] * angle_axis[1] + angle_axis[2] * angle_axis[2];
-  if (theta2 > T(std::numeric_limits<double>::epsilon())) {
-    const T theta = sqrt(theta2);
-    const T costheta = cos(theta);
-    const T sintheta = sin(theta);
-    const T theta_inverse = 1.0 / theta;
-    const T w[3] = {angle_axis[0] * theta_inverse, angle_axis[1] * theta_inverse, angle_axis[2] * theta_inverse};
-    const T w_cross_pt[3] = {w[1] * pt[2] - w[2] * pt[1], w[2] * pt[0] - w[0] * pt[2], w[0] * pt[1] - w[1] * pt[0]};
-    const T tmp = (w[0] * pt[0] + w[1] * pt[1] + w[2] * pt[2]) * (T(1.0) - costheta);
-    result[0] = pt[0] * costheta + w_cross_pt[0] * sintheta + w[0] * tmp;
-    result[1] = pt[1] * costheta + w_cross_pt[1] * sintheta + w[1] * tmp;
-    result[2] = pt[2] * costheta + w_cross_pt[2] * sintheta + w[2] * tmp;
-  } else {
-    const T w_cross_pt[3] = {angle_axis[1] * pt[2] - angle_axis[2] * pt[1], angle_axis[2] * pt[0] - angle_axis[0] * pt[2],
-                             angle_axis[0] * pt[1] - angle_axis[1] * pt[0]};
-    result[0] = pt[0] + w_cross_pt[0];
-    result[1] = pt[1] + w_cross_pt[1];
-    result[2] = pt[2] + w_cross_pt[2];
-  }
-}
+using namespace ba_oracle;
 
 // The reference functor body, CTracker.cpp:585-604 (identical in :615-636 and :647-668 apart
 // from which arguments are constants).  k = Matx33d::val row-major; k[0],k[1],k[2],k[4],k[5] used.
@@ -122,10 +61,23 @@ struct Problem {
   const double* K9 = nullptr;
   const double* dist = nullptr;
   int threads = 1;
+  // constant parameter blocks: what ceres::Problem::SetParameterBlockConstant does to a camera
+  // (both its R and t blocks) or a point — the block keeps its value and is not a column of the Jacobian
+  const uint8_t* cam_fixed = nullptr;  // [n_cams] or null
+  const uint8_t* pt_fixed = nullptr;   // [n_pts] or null
+  // residual + Jacobian evaluation through a caller-supplied callback instead of the built-in restatement of the
+  // functor: oracle/_ref plugs the reference's OWN functor text in here (oracle/make_ref.py)
+  ba_oracle_eval_fn eval_fn = nullptr;
+  void* eval_user = nullptr;
+  bool cam_is_fixed(int64_t c) const { return cam_fixed && cam_fixed[c]; }
+  bool pt_is_fixed(int64_t p) const { return pt_fixed && pt_fixed[p]; }
   // CSR by point
   std::vector<int64_t> pt_start;
   std::vector<int64_t> pt_obs;
+  std::vector<uint8_t> cam_used;  // parameter blocks exist only for cameras / points some residual references (CTracker.cpp:676-696)
   void build_index() {
+    cam_used.assign((size_t)n_cams, 0);
+    for (int64_t i = 0; i < n_obs; ++i) cam_used[cam_idx[i]] = 1;
     pt_start.assign(n_pts + 1, 0);
     for (int64_t i = 0; i < n_obs; ++i) pt_start[pt_idx[i] + 1]++;
     for (int64_t p = 0; p < n_pts; ++p) pt_start[p + 1] += pt_start[p];
@@ -138,22 +90,41 @@ struct Problem {
 };
 
 int validate(int64_t n_obs, const double* obs, const int32_t* cam_idx, const int32_t* pt_idx, int32_t n_cams,
-             const double* K9, const double* cam_rt, int64_t n_pts, const double* pts) {
+             const double* K9, const double* cam_rt, int64_t n_pts, const double* pts, bool external_eval = false) {
   if (n_obs < 0 || n_cams < 0 || n_pts < 0) return -1;
-  if (n_obs > 0 && (!obs || !cam_idx || !pt_idx || !K9 || !cam_rt || !pts)) return -1;
+  if (n_obs > 0 && (!cam_idx || !pt_idx || !cam_rt || !pts)) return -1;
+  if (n_obs > 0 && !external_eval && (!obs || !K9)) return -1;
   for (int64_t i = 0; i < n_obs; ++i)
     if (cam_idx[i] < 0 || cam_idx[i] >= n_cams || pt_idx[i] < 0 || pt_idx[i] >= n_pts) return -1;
   return 0;
 }
 
 // r, J (unscaled) — Jc [n_obs][12] = rows (du/d[R t], dv/d[R t]); Jp [n_obs][6] = rows (du/dX, dv/dX).
-double evaluate(const Problem& P, const double* cam, const double* pts, double* r, double* Jc, double* Jp) {
-  double cost = 0.0;
+// A residual whose parameter blocks are ALL constant is not part of the reduced program (Ceres removes it and
+// carries its cost as Summary::fixed_cost): it adds nothing to the returned cost; *fixed_cost (optional) receives
+// 1/2 sum of those.  Jacobian columns of constant blocks are zeroed (they do not exist in the reduced program).
+double evaluate(const Problem& P, const double* cam, const double* pts, double* r, double* Jc, double* Jp, double* fixed_cost = nullptr) {
+  double cost = 0.0, fcost = 0.0;
   const bool want_j = (Jc != nullptr);
-#pragma omp parallel for schedule(static) reduction(+ : cost) num_threads(P.threads)
+  if (P.eval_fn) {
+    std::vector<double> rtmp;
+    if (!r) { rtmp.resize((size_t)P.n_obs * 2); r = rtmp.data(); }
+    if (P.eval_fn(P.eval_user, cam, pts, r, Jc, Jp)) return std::numeric_limits<double>::quiet_NaN();
+    for (int64_t i = 0; i < P.n_obs; ++i) {
+      const bool cf = !P.cams_free() || P.cam_is_fixed(P.cam_idx[i]), pf = !P.pts_free() || P.pt_is_fixed(P.pt_idx[i]);
+      const double e = r[2 * i] * r[2 * i] + r[2 * i + 1] * r[2 * i + 1];
+      if (cf && pf) fcost += e; else cost += e;
+      if (want_j && P.cam_is_fixed(P.cam_idx[i])) for (int j = 0; j < 12; ++j) Jc[12 * i + j] = 0.0;
+      if (want_j && P.pt_is_fixed(P.pt_idx[i])) for (int j = 0; j < 6; ++j) Jp[6 * i + j] = 0.0;
+    }
+    if (fixed_cost) *fixed_cost = 0.5 * fcost;
+    return 0.5 * cost;
+  }
+#pragma omp parallel for schedule(static) reduction(+ : cost, fcost) num_threads(P.threads)
   for (int64_t i = 0; i < P.n_obs; ++i) {
     const int c = P.cam_idx[i];
     const int64_t p = P.pt_idx[i];
+    const bool both_fixed = (!P.cams_free() || P.cam_is_fixed(c)) && (!P.pts_free() || P.pt_is_fixed(p)) && (P.cam_fixed || P.pt_fixed);
     const double* k = P.K9 + 9 * (int64_t)c;
     const double* d = P.dist ? P.dist + 2 * (int64_t)c : nullptr;
     if (want_j) {
@@ -167,18 +138,22 @@ double evaluate(const Problem& P, const double* cam, const double* pts, double* 
       reprojection(R, t, X, k, d, P.obs[2 * i], P.obs[2 * i + 1], res);
       r[2 * i] = res[0].a;
       r[2 * i + 1] = res[1].a;
+      const bool cfx = P.cam_is_fixed(c), pfx = P.pt_is_fixed(p);
       for (int row = 0; row < 2; ++row) {
-        for (int j = 0; j < 6; ++j) Jc[12 * i + 6 * row + j] = res[row].v[j];
-        for (int j = 0; j < 3; ++j) Jp[6 * i + 3 * row + j] = res[row].v[6 + j];
+        for (int j = 0; j < 6; ++j) Jc[12 * i + 6 * row + j] = cfx ? 0.0 : res[row].v[j];
+        for (int j = 0; j < 3; ++j) Jp[6 * i + 3 * row + j] = pfx ? 0.0 : res[row].v[6 + j];
       }
-      cost += res[0].a * res[0].a + res[1].a * res[1].a;
+      const double e = res[0].a * res[0].a + res[1].a * res[1].a;
+      if (both_fixed) fcost += e; else cost += e;
     } else {
       double res[2];
       reprojection<double>(cam + 6 * c, cam + 6 * c + 3, pts + 3 * p, k, d, P.obs[2 * i], P.obs[2 * i + 1], res);
       if (r) { r[2 * i] = res[0]; r[2 * i + 1] = res[1]; }
-      cost += res[0] * res[0] + res[1] * res[1];
+      const double e = res[0] * res[0] + res[1] * res[1];
+      if (both_fixed) fcost += e; else cost += e;
     }
   }
+  if (fixed_cost) *fixed_cost = 0.5 * fcost;
   return 0.5 * cost;
 }
 
@@ -657,14 +632,23 @@ int ba_oracle_schur(int64_t n_obs, const double* obs_xy, const int32_t* cam_idx,
 int ba_oracle_solve(int mode, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
                     int32_t n_cams, const double* K9, const double* dist, double* cam_rt, int64_t n_pts, double* pts,
                     const ba_oracle_options* opts, ba_oracle_summary* summary) {
+  return ba_oracle_solve_ex(mode, n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, dist, cam_rt, n_pts, pts, nullptr, nullptr, opts, summary,
+                            nullptr, nullptr);
+}
+
+int ba_oracle_solve_ex(int mode, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
+                       int32_t n_cams, const double* K9, const double* dist, double* cam_rt, int64_t n_pts, double* pts,
+                       const uint8_t* cam_fixed, const uint8_t* pt_fixed, const ba_oracle_options* opts,
+                       ba_oracle_summary* summary, ba_oracle_eval_fn eval_fn, void* eval_user) {
   if (!opts) return -1;
   if (mode < 0 || mode > 2) return 0;  // CTracker.cpp:692-693: nothing is added, nothing happens
-  if (validate(n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, cam_rt, n_pts, pts)) return -1;
+  if (validate(n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, cam_rt, n_pts, pts, eval_fn != nullptr)) return -1;
   const ba_oracle_options& o = *opts;
   const double t_begin = now_s();
   Problem P;
   P.mode = mode; P.n_obs = n_obs; P.n_pts = n_pts; P.n_cams = n_cams; P.obs = obs_xy; P.cam_idx = cam_idx;
   P.pt_idx = pt_idx; P.K9 = K9; P.dist = dist; P.threads = std::max(1, (int)o.num_threads);
+  P.cam_fixed = cam_fixed; P.pt_fixed = pt_fixed; P.eval_fn = eval_fn; P.eval_user = eval_user;
   P.build_index();
 
   const int64_t nc6 = 6 * (int64_t)n_cams, np3 = 3 * n_pts;
@@ -685,10 +669,10 @@ int ba_oracle_solve(int mode, int64_t n_obs, const double* obs_xy, const int32_t
   auto push_trace = [&](const ba_oracle_iteration& it) { if (trace && trace_n < trace_cap) trace[trace_n] = it; ++trace_n; };
 
   bool have_scale = false;
-  double x_cost = 0.0, gmax = 0.0, x_norm = 0.0;
+  double x_cost = 0.0, gmax = 0.0, x_norm = 0.0, fixed_cost = 0.0;
   auto linearize = [&]() {
     const double t0 = now_s();
-    x_cost = evaluate(P, xc.data(), xp.data(), r.data(), Jc.data(), Jp.data());
+    x_cost = evaluate(P, xc.data(), xp.data(), r.data(), Jc.data(), Jp.data(), &fixed_cost);
     // gradient from the UNscaled Jacobian
     std::vector<double> Hc_, gc_, Hp_, gp_;
     if (!have_scale) {
@@ -701,8 +685,9 @@ int ba_oracle_solve(int mode, int64_t n_obs, const double* obs_xy, const int32_t
     if (P.cams_free()) for (int64_t k = 0; k < nc6; ++k) gmax = std::max(gmax, std::fabs(gc[k] / sc[k]));
     if (P.pts_free()) for (int64_t k = 0; k < np3; ++k) gmax = std::max(gmax, std::fabs(gp[k] / sp[k]));
     double s = 0.0;
-    if (P.cams_free()) for (int64_t k = 0; k < nc6; ++k) s += xc[k] * xc[k];
-    if (P.pts_free()) for (int64_t k = 0; k < np3; ++k) s += xp[k] * xp[k];
+    // |x| over the parameter blocks of the reduced program: referenced by a residual and not constant
+    if (P.cams_free()) for (int64_t k = 0; k < nc6; ++k) if (P.cam_used[k / 6] && !P.cam_is_fixed(k / 6)) s += xc[k] * xc[k];
+    if (P.pts_free()) for (int64_t k = 0; k < np3; ++k) if (P.pt_start[k / 3 + 1] > P.pt_start[k / 3] && !P.pt_is_fixed(k / 3)) s += xp[k] * xp[k];
     x_norm = std::sqrt(s);
     eval_s += now_s() - t0;
   };
@@ -797,7 +782,7 @@ int ba_oracle_solve(int mode, int64_t n_obs, const double* obs_xy, const int32_t
         its.trust_region_radius = radius;
         push_trace(its);
         if (invalid_run >= o.max_consecutive_invalid_steps) { term = 2; break; }
-        if (radius <= o.min_trust_region_radius) { term = 0; break; }
+        if (radius < o.min_trust_region_radius) { term = 0; break; }
         continue;
       }
       invalid_run = 0;
@@ -833,7 +818,7 @@ int ba_oracle_solve(int mode, int64_t n_obs, const double* obs_xy, const int32_t
         radius = radius / decrease_factor; decrease_factor *= 2.0; reuse_diag = true;
         its.trust_region_radius = radius;
         push_trace(its);
-        if (radius <= o.min_trust_region_radius) { term = 0; break; }
+        if (radius < o.min_trust_region_radius) { term = 0; break; }
       }
       if (o.verbose)
         std::fprintf(stderr, "[oracle] it %3d cost %.9e dcost %.3e |g| %.3e |step| %.3e rho %.3e radius %.3e lin %d\n", iter, its.cost,
@@ -842,8 +827,11 @@ int ba_oracle_solve(int mode, int64_t n_obs, const double* obs_xy, const int32_t
 
   std::memcpy(cam_rt, xc.data(), sizeof(double) * nc6);
   std::memcpy(pts, xp.data(), sizeof(double) * np3);
-  S.final_cost = x_cost;
-  S.rms_px = n_obs > 0 ? std::sqrt(2.0 * x_cost / (double)n_obs) : 0.0;
+  // ceres::Solver::Summary: initial/final cost = the reduced program's cost + fixed_cost (residuals whose blocks are all constant)
+  S.initial_cost += fixed_cost;
+  S.final_cost = x_cost + fixed_cost;
+  S.fixed_cost = fixed_cost;
+  S.rms_px = n_obs > 0 ? std::sqrt(2.0 * S.final_cost / (double)n_obs) : 0.0;
   S.num_iterations = iter;
   S.num_successful_steps = num_success;
   S.termination_type = term;

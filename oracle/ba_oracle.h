@@ -52,6 +52,7 @@ typedef struct ba_oracle_summary {
   double total_seconds;
   ba_oracle_iteration* trace;
   int32_t trace_capacity, trace_count;
+  double fixed_cost;     /* 1/2 sum r^2 over residuals whose parameter blocks are all constant (Ceres Summary::fixed_cost) */
 } ba_oracle_summary;
 
 void ba_oracle_default_options(ba_oracle_options* o);
@@ -74,6 +75,23 @@ int ba_oracle_solve(int mode, int64_t n_obs, const double* obs_xy, const int32_t
                     const int32_t* pt_idx, int32_t n_cams, const double* K9, const double* dist,
                     double* cam_rt, int64_t n_pts, double* pts, const ba_oracle_options* opts,
                     ba_oracle_summary* summary);
+
+/* Residual + Jacobian callback for ba_oracle_solve_ex: fills r [n_obs][2] and, when Jc != NULL, the UNSCALED
+ * Jc [n_obs][12] = rows (du/d[R t], dv/d[R t]) and Jp [n_obs][6] = rows (du/dX, dv/dX) at (cam [n_cams][6], pts [n_pts][3]);
+ * returns non-zero on failure.  oracle/_ref supplies one that calls the reference's own functors. */
+typedef int (*ba_oracle_eval_fn)(void* user, const double* cam, const double* pts, double* r, double* Jc, double* Jp);
+
+/* ba_oracle_solve with
+ *   cam_fixed [n_cams] / pt_fixed [n_pts] (NULL = none): parameter blocks held constant, as
+ *     ceres::Problem::SetParameterBlockConstant would (gauge fixing / windowed BA, SURVEY.md 8f row 2;
+ *     reference intent CMap.cpp:80-112,317-330, CSfM.cpp:123,254);
+ *   eval_fn (NULL = the built-in restatement of CTracker.cpp:585-604): external residual/Jacobian evaluation;
+ *     obs_xy / K9 / dist are then unused and may be NULL. */
+int ba_oracle_solve_ex(int mode, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx,
+                       const int32_t* pt_idx, int32_t n_cams, const double* K9, const double* dist,
+                       double* cam_rt, int64_t n_pts, double* pts, const uint8_t* cam_fixed,
+                       const uint8_t* pt_fixed, const ba_oracle_options* opts,
+                       ba_oracle_summary* summary, ba_oracle_eval_fn eval_fn, void* eval_user);
 
 /* In-place lower Cholesky of a dense row-major n×n SPD matrix (blocked, OpenMP); returns 0 or
  * the 1-based index of the first non-positive pivot.  Exposed for the Cholesky KATs. */

@@ -43,21 +43,37 @@ class OSummary(C.Structure):
         ("linear_solver_used", C.c_int32), ("total_linear_iterations", C.c_int32), ("n_threads", C.c_int32),
         ("eval_seconds", C.c_double), ("linear_seconds", C.c_double), ("total_seconds", C.c_double),
         ("trace", C.POINTER(OIteration)), ("trace_capacity", C.c_int32), ("trace_count", C.c_int32),
+        ("fixed_cost", C.c_double),
     ]
 
 
 def build(force: bool = False) -> str:
     if force or not os.path.exists(_SO) or any(
         os.path.getmtime(os.path.join(_HERE, f)) > os.path.getmtime(_SO)
-        for f in ("ba_oracle.cpp", "ba_oracle_chol.cpp", "ba_oracle.h", "Makefile")
+        for f in ("ba_oracle.cpp", "ba_oracle_chol.cpp", "ba_oracle.h", "ba_oracle_jet.h", "Makefile")
     ):
         subprocess.run(["make", "-C", _HERE], check=True, capture_output=True)
     return _SO
 
 
+def build_ref(force: bool = False):
+    """oracle/_ref/libba_ref.so: the reference's own functor + problem-assembly text (CTracker.h:64-67,98-151,
+    CTracker.cpp:571-702) compiled from where it lies under /root/reference against the stand-in headers
+    (oracle/make_ref.py).  Returns None when neither the reference tree nor a prebuilt file is present."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("_make_ref", os.path.join(_HERE, "make_ref.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m.build(force=force)
+
+
 _lib = None
+_ref = None
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int32)
+_bp = C.POINTER(C.c_uint8)
+_EVAL_FN = C.c_void_p
 
 
 def lib():
@@ -73,13 +89,36 @@ def lib():
         _lib.ba_oracle_solve.restype = C.c_int
         _lib.ba_oracle_solve.argtypes = [C.c_int, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp,
                                          C.POINTER(OOptions), C.POINTER(OSummary)]
+        _lib.ba_oracle_solve_ex.restype = C.c_int
+        _lib.ba_oracle_solve_ex.argtypes = [C.c_int, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp, _bp, _bp,
+                                            C.POINTER(OOptions), C.POINTER(OSummary), _EVAL_FN, C.c_void_p]
         _lib.ba_oracle_cholesky.restype = C.c_int
         _lib.ba_oracle_cholesky.argtypes = [_dp, C.c_int64, C.c_int]
     return _lib
 
 
+def ref_lib():
+    """libba_ref.so or None (reference tree absent and nothing prebuilt)."""
+    global _ref
+    if _ref is None:
+        so = build_ref()
+        if so is None or not os.path.exists(so):
+            return None
+        _ref = C.CDLL(so)
+        _ref.ba_ref_eval.restype = C.c_int
+        _ref.ba_ref_eval.argtypes = [C.c_int, C.c_int64, _dp, _dp, _dp, _dp, _dp, _dp, _dp]
+        _ref.ba_ref_solve.restype = C.c_int
+        _ref.ba_ref_solve.argtypes = [C.c_int, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, C.c_int64, _dp, C.POINTER(OOptions),
+                                      C.POINTER(OSummary)]
+    return _ref
+
+
 def _d(a):
     return None if a is None else a.ctypes.data_as(_dp)
+
+
+def _b(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.uint8).ctypes.data_as(_bp)
 
 
 def _i(a):
@@ -146,19 +185,56 @@ def schur(prob, radius=1e4, opts=None, cam=None, pts=None):
     return out
 
 
-def solve(prob, mode=2, opts=None, trace_capacity=64):
-    """In-place Ceres-semantics LM on copies; returns (cam, pts, summary dict, trace list)."""
+def solve(prob, mode=2, opts=None, trace_capacity=64, cam_fixed=None, pt_fixed=None):
+    """In-place Ceres-semantics LM on copies; returns (cam, pts, summary dict, trace list).  cam_fixed / pt_fixed:
+    optional boolean masks of parameter blocks held constant (ceres::Problem::SetParameterBlockConstant)."""
     opts = opts or default_options()
     cam, pts = prob.cam.copy(), prob.pts.copy()
     trace = (OIteration * trace_capacity)()
     s = OSummary()
     s.trace = C.cast(trace, C.POINTER(OIteration))
     s.trace_capacity = trace_capacity
-    rc = lib().ba_oracle_solve(mode, prob.n_obs, _d(prob.obs), _i(prob.cam_idx), _i(prob.pt_idx), prob.n_cams, _d(prob.K),
-                               _d(prob.dist), _d(cam), prob.n_pts, _d(pts), C.byref(opts), C.byref(s))
+    cf = None if cam_fixed is None else np.ascontiguousarray(cam_fixed, dtype=np.uint8)
+    pf = None if pt_fixed is None else np.ascontiguousarray(pt_fixed, dtype=np.uint8)
+    rc = lib().ba_oracle_solve_ex(mode, prob.n_obs, _d(prob.obs), _i(prob.cam_idx), _i(prob.pt_idx), prob.n_cams, _d(prob.K),
+                                  _d(prob.dist), _d(cam), prob.n_pts, _d(pts), _b(cf), _b(pf), C.byref(opts), C.byref(s), None, None)
     if rc:
         raise RuntimeError(f"ba_oracle_solve -> {rc}")
     summ = {f: getattr(s, f) for f, _ in s._fields_ if f != "trace"}
+    return cam, pts, summ, [trace[i].as_dict() for i in range(s.trace_count)]
+
+
+def ref_evaluate(which, obs, K9, R, t, X, want_jac=True):
+    """One observation per row through the REFERENCE's own functor text (oracle/_ref): which = 2
+    BAStructAndPoseFunctor (CTracker.cpp:585-604), 1 BAPoseFunctor (:615-636), 0 BAStructFunctor (:647-668).
+    Returns (r [n,2], J [n,2,9]); Jacobian columns of the functor's constant arguments are zero."""
+    n = len(obs)
+    a = [np.ascontiguousarray(v, dtype=np.float64) for v in (obs, K9, R, t, X)]
+    r = np.empty((n, 2))
+    J = np.zeros((n, 2, 9)) if want_jac else None
+    rc = ref_lib().ba_ref_eval(which, n, *[_d(v) for v in a], _d(r), _d(J))
+    if rc:
+        raise RuntimeError(f"ba_ref_eval -> {rc}")
+    return r, J
+
+
+def ref_solve(prob, mode=2, opts=None, trace_capacity=64):
+    """The reference call itself: CTracker::bundleAdjustmentStructAndPose (CTracker.cpp:670-702, verbatim in oracle/_ref)
+    on arguments laid out as CSfM.cpp:311-341 builds them; the stand-in ceres::Solve runs the oracle's trust-region loop
+    over the reference's own cost functions.  Returns (cam, pts, summary dict, trace list); summary["n_parameter_blocks"]
+    = the parameter blocks found by pointer identity."""
+    opts = opts or default_options()
+    cam, pts = prob.cam.copy(), prob.pts.copy()
+    trace = (OIteration * trace_capacity)()
+    s = OSummary()
+    s.trace = C.cast(trace, C.POINTER(OIteration))
+    s.trace_capacity = trace_capacity
+    rc = ref_lib().ba_ref_solve(mode, prob.n_obs, _d(prob.obs), _i(prob.cam_idx), _i(prob.pt_idx), prob.n_cams, _d(prob.K), _d(cam),
+                                prob.n_pts, _d(pts), C.byref(opts), C.byref(s))
+    if rc:
+        raise RuntimeError(f"ba_ref_solve -> {rc}")
+    summ = {f: getattr(s, f) for f, _ in s._fields_ if f != "trace"}
+    summ["n_parameter_blocks"] = summ.pop("total_linear_iterations")
     return cam, pts, summ, [trace[i].as_dict() for i in range(s.trace_count)]
 
 

@@ -99,6 +99,8 @@ int hsfm_ba_create(hsfm_ba_ctx** out, int device_id) {
   if (e != cudaSuccess) { delete h; return 1000 + (int)e; }
   h->c.stream = h->c.own_stream;
   { int rc2 = h->c.chol_aux.init(); if (rc2) { cudaStreamDestroy(h->c.own_stream); delete h; return rc2; } }
+  { int rc2 = init_kernel_attributes(); if (rc2) { h->c.chol_aux.destroy(); cudaStreamDestroy(h->c.own_stream); delete h; return rc2; } }
+  h->c.prob.n_sm = h->c.chol_aux.n_sm;
   *out = h;
   return 0;
 }
@@ -375,7 +377,7 @@ int hsfm_ba_dense_spd_solve(hsfm_ba_ctx* h, int32_t n, const double* A, const do
     HSFM_CUDA(cudaMemcpyAsync(db, b, sizeof(double) * n, cudaMemcpyHostToDevice, s));
     HSFM_CUDA(cudaMemsetAsync(dflag, 0, sizeof(int), s));
     launch_cholesky(dA, n, dA + nn, dflag, s, &h->c.chol_aux, &launches);
-    launch_chol_solve(dA, n, dA + nn, db, s, &launches);
+    launch_chol_solve(dA, n, dA + nn, db, s, &launches, &h->c.chol_aux);
     HSFM_CUDA(cudaMemcpyAsync(&flag, dflag, sizeof(int), cudaMemcpyDeviceToHost, s));
     HSFM_CUDA(cudaMemcpyAsync(x, db, sizeof(double) * n, cudaMemcpyDeviceToHost, s));
     if (L_out) HSFM_CUDA(cudaMemcpyAsync(L_out, dA, sizeof(double) * nn, cudaMemcpyDeviceToHost, s));
@@ -416,7 +418,7 @@ int hsfm_ba_bench_cholesky(hsfm_ba_ctx* h, int32_t n, int reps, double* factor_m
       HSFM_CUDA(cudaEventRecord(e0, s));
       launch_cholesky(dA, n, dA + nn, dflag, s, &h->c.chol_aux, &launches);
       HSFM_CUDA(cudaEventRecord(e1, s));
-      launch_chol_solve(dA, n, dA + nn, db, s, &launches);
+      launch_chol_solve(dA, n, dA + nn, db, s, &launches, &h->c.chol_aux);
       HSFM_CUDA(cudaEventRecord(e2, s));
       HSFM_CUDA(cudaEventSynchronize(e2));
       if (it > 0) {

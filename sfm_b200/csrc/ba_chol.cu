@@ -1531,6 +1531,20 @@ size_t cholesky_workspace_doubles(int n) {
 
 int CholAux::init() {
   if (stream) return 0;
+  // per device (function attributes and the SM count belong to the device of the owning context)
+  int dev = 0;
+  HSFM_CUDA(cudaGetDevice(&dev));
+  cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+  if (n_sm <= 0) n_sm = 148;
+  cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+  if (getenv("HSFM_TRSV_LAUNCHES")) coop = 0;
+  HSFM_CUDA(cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDiagSmem));
+  HSFM_CUDA(cudaFuncSetAttribute(chol_trsm_strip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_MAXROWS * TS_LD * (int)sizeof(double)));
+  HSFM_CUDA(cudaFuncSetAttribute(chol_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+  HSFM_CUDA(cudaFuncSetAttribute(chol_syrk_col_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrkLatSmem));
+  HSFM_CUDA(cudaFuncSetAttribute(chol_syrk_col_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrkLatSmem / 2));
+  HSFM_CUDA(cudaFuncSetAttribute(chol_chain_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kChainTileSmem));
+  HSFM_CUDA(cudaFuncSetAttribute(trsv_coop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTrsvSmem));
   int lo = 0, hi = 0;
   cudaDeviceGetStreamPriorityRange(&lo, &hi);
   HSFM_CUDA(cudaStreamCreateWithPriority(&stream, cudaStreamNonBlocking, hi));
@@ -1737,23 +1751,7 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
 }
 
 void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches, const CholPlan* plan) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDiagSmem);
-    cudaFuncSetAttribute(chol_trsm_strip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_MAXROWS * TS_LD * (int)sizeof(double));
-    cudaFuncSetAttribute(chol_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem);
-    cudaFuncSetAttribute(chol_syrk_col_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrkLatSmem);
-    cudaFuncSetAttribute(chol_syrk_col_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrkLatSmem / 2);
-    cudaFuncSetAttribute(chol_chain_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kChainTileSmem);
-    attr_set = true;
-  }
-  static int n_sm = 0;
-  if (!n_sm) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-    if (n_sm <= 0) n_sm = 148;
-  }
+  const int n_sm = (aux && aux->n_sm > 0) ? aux->n_sm : 148;
   static int bulk_ctas = 0;
   if (!bulk_ctas) {
     const char* e = getenv("HSFM_BULK_CTAS");  // experiment knob: <0 means n_sm + value
@@ -1839,18 +1837,12 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
 
 // Solves S y = b with the factor from launch_cholesky.  b holds 2n doubles: [0,n) right-hand side
 // in / solution out, [n,2n) scratch for the intermediate vector.
-void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream_t s, int64_t* launches, const CholPlan* plan) {
+void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream_t s, int64_t* launches, const CholAux* aux, const CholPlan* plan) {
   double* w = b + n;
   const int panels = (n + NB - 1) / NB;
   int* flags = reinterpret_cast<int*>(ws + (size_t)panels * NB * NB);  // [2 * panels]
-  static int n_sm = 0, coop = -1;
-  if (coop < 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
-    if (getenv("HSFM_TRSV_LAUNCHES")) coop = 0;
-  }
+  const int n_sm = (aux && aux->n_sm > 0) ? aux->n_sm : 148;
+  const int coop = aux ? aux->coop : 0;
   if (coop) {
     cudaMemsetAsync(flags, 0, sizeof(int) * 2 * panels, s);
     const double* LinvAll = ws;
@@ -1860,8 +1852,6 @@ void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream
     const int* env = (plan && plan->use && plan->n == n) ? plan->d_fb : nullptr;
     void* args[] = {(void*)&L, (void*)&nn, (void*)&LinvAll, (void*)&b, (void*)&w, (void*)&ff, (void*)&fb, (void*)&env};
     const int grid = std::min(panels, n_sm);
-    static bool attr_set = false;
-    if (!attr_set) { cudaFuncSetAttribute(trsv_coop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTrsvSmem); attr_set = true; }
     if (cudaLaunchCooperativeKernel((const void*)trsv_coop_kernel, dim3(grid), dim3(256), args, kTrsvSmem, s) == cudaSuccess) {
       ++*launches;
       return;

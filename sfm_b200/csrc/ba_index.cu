@@ -19,7 +19,9 @@ void Problem::release() {
   unsigned* pl_keep = pair_list; const size_t pl_cap = pair_capacity;
   double* sh = scal_host; int* fh = flags_host;
   int* ih = idx_host; const size_t ih_cap = idx_host_cap;
+  const int sm = n_sm;
   *this = Problem();
+  n_sm = sm;
   arena = a; arena_cap = cap; arena_off = 0;
   S = s_keep; S_capacity = s_cap;
   pair_list = pl_keep; pair_capacity = pl_cap;

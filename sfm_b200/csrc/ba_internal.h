@@ -57,6 +57,7 @@ struct Problem {
   int mode = 2;
   int n_obs = 0, n_cams = 0, n_pts = 0, n_tiles = 0, n_chunks = 0;
   int max_track = 0;
+  int n_sm = 148;         // SM count of the context's device (set by hsfm_ba_create; survives release())
   int max_tile_cams = 0;  // largest number of distinct cameras in one tile (sizes the shared-memory row staging)
   std::vector<int> cam_first;  // [n_cams] smallest camera sharing a point with camera c (all ranks) — envelope of S
   Dev d{};
@@ -140,6 +141,7 @@ void launch_rows_to_internal(Problem& P, int w, const double* caller_order, doub
 void launch_rows_to_caller(Problem& P, int w, const double* internal_order, double* caller_order, cudaStream_t s);
 
 // ---- kernel launchers (ba_kernels.cu); every launcher bumps P.launches ----
+int init_kernel_attributes();  // per-device dynamic shared-memory opt-ins (call with the context's device current)
 void launch_cam_prep(Problem& P, const double* cam, const double* scale_c /*null = 1*/, CamRow* rows, cudaStream_t s);
 // residual + Jacobian (+ point blocks Hpp,gp when form) ; scale_p null = 1
 void launch_rj(Problem& P, const CamRow* rows, const double* pts, const double* scale_p, bool write_j, bool form, cudaStream_t s);
@@ -179,7 +181,8 @@ struct CholAux {
   const void* g_S = nullptr; const void* g_ws = nullptr; const void* g_fail = nullptr; const void* g_stream = nullptr;
   int g_n = 0, g_version = -1;
   int64_t g_launches = 0;
-  int init();
+  int n_sm = 0, coop = 0;  // of the context's device
+  int init();              // also opts the factorisation kernels into their dynamic shared memory ON THE CURRENT DEVICE
   void destroy();
 };
 // Block envelope of the reduced camera matrix (static per problem).  Camera c shares points with no camera
@@ -210,7 +213,8 @@ struct CholPlan {
 size_t cholesky_workspace_doubles(int n);  // L11^-1 blocks (one 128×128 per panel) + flags of the cooperative triangular solve
 void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches,
                      const CholPlan* plan = nullptr);
-void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream_t s, int64_t* launches, const CholPlan* plan = nullptr);
+void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream_t s, int64_t* launches, const CholAux* aux,
+                       const CholPlan* plan = nullptr);
 
 // S envelope <-> packed buffer (to_packed: gather; else scatter)
 void launch_envelope_pack(const CholPlan& pl, double* S, double* packed, bool to_packed, cudaStream_t s);

@@ -1327,25 +1327,24 @@ constexpr int kStageSmemMax = 2 * rj_stage(TILE).bytes + 3 * RJ_META_BYTES + (in
 template <class Kern>
 static void allow_stage_smem(Kern k) { cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kStageSmemMax); }
 
+// Dynamic shared-memory opt-ins of this translation unit.  Function attributes are PER DEVICE: called by
+// hsfm_ba_create for the context's device (after cudaSetDevice), not once per process.
+int init_kernel_attributes() {
+  allow_stage_smem(rj_kernel<true, true>); allow_stage_smem(rj_kernel<true, false>);
+  allow_stage_smem(rj_kernel<false, true>); allow_stage_smem(rj_kernel<false, false>);
+  allow_stage_smem(cost_kernel);
+  cudaFuncSetAttribute(dense_schur_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDenseSchurSmem);
+  cudaFuncSetAttribute(dense_schur_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDenseSchurSmem);
+  const cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : 1000 + (int)e;
+}
+
 void launch_rj(Problem& P, const CamRow* rows, const double* pts, const double* scale_p, bool write_j, bool form, cudaStream_t s) {
   if (P.n_tiles == 0) return;
-  static bool attr_set = false;
-  if (!attr_set) {
-    allow_stage_smem(rj_kernel<true, true>); allow_stage_smem(rj_kernel<true, false>);
-    allow_stage_smem(rj_kernel<false, true>); allow_stage_smem(rj_kernel<false, false>);
-    attr_set = true;
-  }
   double* cp = P.part + (size_t)P_COST * P.part_stride;
   const int cap = P.max_tile_cams;
   const size_t sh = rj_smem_bytes(cap, form);
-  static int n_sm = 0;
-  if (!n_sm) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-    if (n_sm <= 0) n_sm = 148;
-  }
-  const int grid = std::min(P.n_tiles, 2 * n_sm);  // persistent: two CTAs per SM walk the tiles
+  const int grid = std::min(P.n_tiles, 2 * P.n_sm);  // persistent: two CTAs per SM walk the tiles
   if (write_j && form) rj_kernel<true, true><<<grid, TILE, sh, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp, cap);
   else if (write_j) rj_kernel<true, false><<<grid, TILE, sh, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp, cap);
   else if (form) rj_kernel<false, true><<<grid, TILE, sh, s>>>(P.d, rows, pts, scale_p, P.Hpp, P.gp, cp, cap);
@@ -1356,8 +1355,6 @@ void launch_rj(Problem& P, const CamRow* rows, const double* pts, const double* 
 
 void launch_cost(Problem& P, const CamRow* rows, const double* pts, int part_slot, cudaStream_t s) {
   if (P.n_tiles == 0) return;
-  static bool attr_set = false;
-  if (!attr_set) { allow_stage_smem(cost_kernel); attr_set = true; }
   cost_kernel<<<P.n_tiles, TILE, cost_smem_bytes(P.max_tile_cams), s>>>(P.d, rows, pts, P.part + (size_t)part_slot * P.part_stride,
                                                                          P.max_tile_cams);
   P.launches++;
@@ -1530,12 +1527,6 @@ void launch_frame_stats(Problem& P, const CamRow* rows, const double* pts, doubl
 
 void launch_dense_schur(Problem& P, cudaStream_t s, bool sorted_pairs) {
   if (P.n_tiles == 0) return;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(dense_schur_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDenseSchurSmem);
-    cudaFuncSetAttribute(dense_schur_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDenseSchurSmem);
-    attr_set = true;
-  }
   static const bool no_sort = getenv("HSFM_SCHUR_UNSORTED") != nullptr;  // experiment knob
   if (!P.pairs_ready && P.d.pair_off && !no_sort && sorted_pairs) {
     // first dense solve of this problem: build the destination-sorted pair lists (static, like the rest of the index)

@@ -52,6 +52,7 @@ struct Driver {
     HSFM_CUDA(cudaMemcpyAsync(P.scal_host, P.scal, sizeof(double) * 16, cudaMemcpyDeviceToHost, s));
     HSFM_CUDA(cudaMemcpyAsync(P.flags_host, P.flags, sizeof(int) * FLAG_SLOTS, cudaMemcpyDeviceToHost, s));
     HSFM_CUDA(cudaStreamSynchronize(s));
+    HSFM_CUDA(cudaGetLastError());  // launch-configuration errors are not sticky: without this a failed launch would go unnoticed
     return 0;
   }
 
@@ -116,7 +117,7 @@ struct Driver {
         launch_cholesky(P.S, n6, P.S + (size_t)n6 * n6, P.flags + F_CHOL_FAIL, s, &ctx.chol_aux, &P.launches, (o.dense_flags & 1) ? nullptr : &ctx.chol_plan);
         mark(3);
         HSFM_CUDA(cudaMemcpyAsync(P.yc, P.rhs, sizeof(double) * n6, cudaMemcpyDeviceToDevice, s));
-        launch_chol_solve(P.S, n6, P.S + (size_t)n6 * n6, P.yc, s, &P.launches, (o.dense_flags & 1) ? nullptr : &ctx.chol_plan);
+        launch_chol_solve(P.S, n6, P.S + (size_t)n6 * n6, P.yc, s, &P.launches, &ctx.chol_aux, (o.dense_flags & 1) ? nullptr : &ctx.chol_plan);
       } else {
         launch_cam_major(P, P.rows_x, P.pts_x, P.scale_p, 1, s);
         if (multi()) chk(ctx.comm.allreduce_sum(P.E, 21 * (size_t)P.n_cams, s));
@@ -281,7 +282,7 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
         if (o.verbose) std::fprintf(stderr, "[hsfm_ba] it %3d INVALID step (flags %d chol %d mcc %.3e) radius -> %.3e\n", iter,
                                     P.flags_host[F_INVALID], P.flags_host[F_CHOL_FAIL], mcc, radius);
         if (invalid_run >= o.max_consecutive_invalid_steps) { term = HSFM_BA_FAILURE; break; }
-        if (radius <= o.min_trust_region_radius) { term = HSFM_BA_CONVERGENCE; break; }
+        if (radius < o.min_trust_region_radius) { term = HSFM_BA_CONVERGENCE; break; }
         continue;
       }
       invalid_run = 0;
@@ -322,7 +323,7 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
         if (o.verbose)
           std::fprintf(stderr, "[hsfm_ba] it %3d REJECTED cost %.9e cand %.9e rho %.3e radius -> %.3e lin %d\n", iter, x_cost, cand_cost, rho,
                        radius, lin);
-        if (radius <= o.min_trust_region_radius) { term = HSFM_BA_CONVERGENCE; break; }
+        if (radius < o.min_trust_region_radius) { term = HSFM_BA_CONVERGENCE; break; }
       }
     }
   }

@@ -121,3 +121,56 @@ def test_frame_error_statistics_loop_equals_grouped_numpy():
     for c in range(p.n_cams):
         sel = d2[p.cam_idx == c]
         assert rms[c] == pytest.approx(np.sqrt(sel.mean()), rel=1e-13) and mx[c] == pytest.approx(np.sqrt(sel.max()), rel=1e-15)
+
+
+def _scipy_cost_with_fixed(p, cam_fixed, pt_fixed):
+    """Converged cost of the same problem with the masked blocks held constant, from an independent optimiser
+    (scipy trust-region-reflective over the FREE parameters only, numpy projection)."""
+    from scipy.optimize import least_squares
+
+    cf, pf = np.asarray(cam_fixed, bool), np.asarray(pt_fixed, bool)
+    nc, npf = int((~cf).sum()), int((~pf).sum())
+
+    def unpack(x):
+        cam, pts = p.cam.copy(), p.pts.copy()
+        cam[~cf] = x[:6 * nc].reshape(nc, 6)
+        pts[~pf] = x[6 * nc:].reshape(npf, 3)
+        return cam, pts
+
+    def fun(x):
+        cam, pts = unpack(x)
+        uv, _ = synth.project(cam, p.K, pts, p.cam_idx, p.pt_idx)
+        return (uv - p.obs).ravel()
+
+    x0 = np.concatenate([p.cam[~cf].ravel(), p.pts[~pf].ravel()])
+    sol = least_squares(fun, x0, method="trf", xtol=1e-14, ftol=1e-14, gtol=1e-12, max_nfev=300)
+    return 0.5 * float((sol.fun ** 2).sum())
+
+
+def test_constant_blocks_gauge_and_window():
+    """parameter blocks held constant.  Fixed blocks keep their value bit for bit; the free ones
+    converge to the optimum an independent optimiser finds for the reduced problem; an all-constant residual
+    contributes only Summary::fixed_cost."""
+    p = synth.make_ring(8, 90, 5, seed=21, name="gauge")
+    tight = po.default_options(function_tolerance=1e-14, parameter_tolerance=1e-14, max_num_iterations=200)
+    cf = np.zeros(p.n_cams, np.uint8); cf[0] = 1            # gauge: oldest keyframe fixed
+    pf = np.zeros(p.n_pts, np.uint8)
+    cam, pts, s, _ = po.solve(p, opts=tight, cam_fixed=cf)
+    assert np.array_equal(cam[0], p.cam[0]) and not np.array_equal(cam[1:], p.cam[1:])
+    assert s["final_cost"] == pytest.approx(_scipy_cost_with_fixed(p, cf, pf), rel=1e-6)
+    assert s["fixed_cost"] == 0.0
+    # window: only the last three keyframes and the points they see are free
+    cf[:] = 1; cf[-3:] = 0
+    seen = np.zeros(p.n_pts, bool); seen[p.pt_idx[np.isin(p.cam_idx, np.nonzero(cf == 0)[0])]] = True
+    pf = (~seen).astype(np.uint8)
+    cam, pts, s, _ = po.solve(p, opts=tight, cam_fixed=cf, pt_fixed=pf)
+    assert np.array_equal(cam[cf == 1], p.cam[cf == 1]) and np.array_equal(pts[pf == 1], p.pts[pf == 1])
+    assert s["final_cost"] == pytest.approx(_scipy_cost_with_fixed(p, cf, pf), rel=1e-6)
+    # residuals between a fixed camera and a fixed point are not part of the reduced program
+    r, _, _ = po.evaluate(p, want_jac=False)
+    both = (cf[p.cam_idx] == 1) & (pf[p.pt_idx] == 1)
+    assert s["fixed_cost"] == pytest.approx(0.5 * float((r[both] ** 2).sum()), rel=1e-12)
+    # no mask == null mask == the unmasked entry point
+    a = po.solve(p, opts=po.default_options())
+    b = po.solve(p, opts=po.default_options(), cam_fixed=np.zeros(p.n_cams, np.uint8), pt_fixed=np.zeros(p.n_pts, np.uint8))
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and a[3] == b[3]
