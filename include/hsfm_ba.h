@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define HSFM_BA_ABI_VERSION 1
+#define HSFM_BA_ABI_VERSION 2
 
 /* enum BA_TYPE, CTracker.h:67.  Any other value: the reference adds no residual block
  * (CTracker.cpp:692-693) and Solve() returns immediately; we return 0 and touch nothing. */
@@ -124,6 +124,13 @@ typedef struct hsfm_ba_summary {
    * [4] step, back-substitution, model cost change, candidate cost
    * [5] scalar read-back + host decision   [6],[7] reserved */
   double phase_ms[8];
+  /* ---- ABI version 2 ---- */
+  double fixed_cost;            /* 1/2 sum r^2 of residuals whose parameter blocks are all constant (ceres Summary::fixed_cost);
+                                   included in initial_cost / final_cost, not in the per-iteration costs */
+  int32_t chol_panels;          /* 128-column panels of the reduced camera system (0: no Cholesky in this solve) */
+  int32_t chol_critical_panels; /* panels on the serial chain of the factorisation: = chol_panels with one chain, fewer with two */
+  int32_t cameras_reordered;    /* 1: the problem is held in the library's two-ended camera order (hsfm_ba_set_ordering) */
+  int32_t reserved1;
 } hsfm_ba_summary;
 
 typedef struct hsfm_ba_ctx hsfm_ba_ctx;
@@ -141,6 +148,21 @@ void hsfm_ba_default_options(hsfm_ba_options* opts);
 /* Run all subsequent work of this context on an externally owned cudaStream_t (passed as
  * void*), e.g. a harness' timing stream.  NULL restores the context's own stream. */
 int hsfm_ba_set_stream(hsfm_ba_ctx* ctx, void* cuda_stream);
+
+/* Internal camera order of subsequently uploaded problems.  0 (default): chosen by the library — a banded camera
+ * graph (a scan trajectory) is numbered from both ends towards the middle, so that the Cholesky of the reduced camera
+ * system runs as two concurrent panel chains; results are returned in the caller's order either way.  1: keep the
+ * caller's order (one chain).  The solution is the same up to rounding. */
+int hsfm_ba_set_ordering(hsfm_ba_ctx* ctx, int ordering);
+
+/* Host-only tap (no device needed): the camera order, the 128-row block structure of the Cholesky factor and the
+ * panel-chain schedule the library derives from an envelope cam_first[c] = smallest camera sharing a point with
+ * camera c (caller order).  natural != 0: keep the caller's order.  new_of_old [n_cams] (optional) internal position
+ * of every camera; info [8] = {panels, first panel of the second chain or -1, first common panel or -1, structured
+ * factorisation used (0/1), reordered (0/1), first camera of the second chain, 0, 0}; fill (optional) = structural
+ * blocks / triangle blocks; structure (optional) [panels][panels] bytes, lower triangle, 1 = block of L may be non-zero. */
+int hsfm_ba_debug_structure(int32_t n_cams, const int32_t* cam_first, int32_t natural, int32_t* new_of_old, int32_t* info,
+                            double* fill, uint8_t* structure);
 
 /* Multi-GPU (one process per GPU, observations sharded by point, cameras replicated).
  * unique_id: the 128-byte ncclUniqueId produced by hsfm_ba_comm_unique_id() on rank 0 and

@@ -65,6 +65,11 @@ class Summary(C.Structure):
         ("trace_capacity", C.c_int32),
         ("trace_count", C.c_int32),
         ("phase_ms", C.c_double * 8),
+        ("fixed_cost", C.c_double),
+        ("chol_panels", C.c_int32),
+        ("chol_critical_panels", C.c_int32),
+        ("cameras_reordered", C.c_int32),
+        ("reserved1", C.c_int32),
     ]
 
 

@@ -35,6 +35,8 @@ SYMBOLS = {
     "hsfm_ba_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
     "hsfm_ba_destroy": (None, [C.c_void_p]),
     "hsfm_ba_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "hsfm_ba_set_ordering": (C.c_int, [C.c_void_p, C.c_int]),
+    "hsfm_ba_debug_structure": (C.c_int, [C.c_int32, _ip, C.c_int32, _ip, _ip, _dp, C.POINTER(C.c_uint8)]),
     "hsfm_ba_comm_unique_id": (C.c_int, [C.c_void_p]),
     "hsfm_ba_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "hsfm_ba_solve_ptr": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, _dp, _ip, C.c_int32, _dp, _pp, _pp, _pp,
@@ -124,6 +126,24 @@ class _SummaryBox:
         return d
 
 
+def debug_structure(cam_first, natural=False):
+    """Host-only: camera order, block structure of the Cholesky factor and chain schedule for an envelope
+    (hsfm_ba_debug_structure).  Returns a dict."""
+    first = np.ascontiguousarray(cam_first, dtype=np.int32)
+    n = first.shape[0]
+    perm = np.empty(n, dtype=np.int32)
+    info = np.zeros(8, dtype=np.int32)
+    fill = C.c_double()
+    panels = (6 * n + 127) // 128
+    st = np.zeros((panels, panels), dtype=np.uint8)
+    rc = load_library().hsfm_ba_debug_structure(n, _i(first), int(bool(natural)), _i(perm), _i(info), C.byref(fill),
+                                                st.ctypes.data_as(C.POINTER(C.c_uint8)))
+    if rc:
+        raise BAError(rc, "hsfm_ba_debug_structure")
+    return dict(new_of_old=perm, panels=int(info[0]), split_a=int(info[1]), split_t0=int(info[2]), structured=bool(info[3]),
+                reordered=bool(info[4]), split_cams=int(info[5]), fill=fill.value, structure=st)
+
+
 class Context:
     """One hsfm_ba_ctx (one GPU)."""
 
@@ -158,6 +178,12 @@ class Context:
         rc = self.lib.hsfm_ba_set_stream(self.h, C.c_void_p(cuda_stream_ptr or 0))
         if rc:
             raise BAError(rc, "hsfm_ba_set_stream")
+
+    def set_ordering(self, ordering: int):
+        """0 = library-chosen internal camera order (default), 1 = keep the caller's order."""
+        rc = self.lib.hsfm_ba_set_ordering(self.h, ordering)
+        if rc:
+            raise BAError(rc, "hsfm_ba_set_ordering")
 
     @staticmethod
     def comm_unique_id() -> bytes:

@@ -10,7 +10,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libhsfm_ba.so")
-SOURCES = ["ba_kernels.cu", "ba_chol.cu", "ba_index.cu", "ba_comm.cu", "ba_solver.cu", "ba_api.cu"]
+SOURCES = ["ba_kernels.cu", "ba_chol.cu", "ba_index.cu", "ba_comm.cu", "ba_solver.cu", "ba_api.cu", "ba_order.cpp"]
 HEADERS = ["ba_internal.h", "ba_math.cuh", os.path.join("..", "..", "include", "hsfm_ba.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
@@ -35,8 +35,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
     procs = []
     for src in SOURCES:
-        obj = os.path.join(HERE, "build", src.replace(".cu", ".o"))
-        cmd = [NVCC, *FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        obj = os.path.join(HERE, "build", os.path.splitext(src)[0] + ".o")
+        cmd = [NVCC, *FLAGS, *(["-x", "cu"] if src.endswith(".cpp") else []), "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas")
             cmd.insert(2, "-v")

@@ -125,6 +125,40 @@ int hsfm_ba_set_stream(hsfm_ba_ctx* h, void* cuda_stream) {
   return 0;
 }
 
+int hsfm_ba_set_ordering(hsfm_ba_ctx* h, int ordering) {
+  if (!h || ordering < 0 || ordering > 1) return HSFM_BA_ERR_ARG;
+  h->c.ordering = ordering;
+  return 0;
+}
+
+int hsfm_ba_debug_structure(int32_t n_cams, const int32_t* cam_first, int32_t natural, int32_t* new_of_old, int32_t* info, double* fill,
+                            uint8_t* structure) {
+  if (n_cams <= 0 || !cam_first || !info) return HSFM_BA_ERR_ARG;
+  for (int c = 0; c < n_cams; ++c)
+    if (cam_first[c] < 0 || cam_first[c] > c) return HSFM_BA_ERR_ARG;
+  std::vector<int> perm;
+  int split_cams = -1;
+  const bool re = !natural && choose_camera_order(n_cams, cam_first, perm, &split_cams);
+  if (!re) { perm.clear(); split_cams = -1; }
+  if (new_of_old)
+    for (int c = 0; c < n_cams; ++c) new_of_old[c] = re ? perm[(size_t)c] : c;
+  std::vector<uint8_t> pattern;
+  int panels = 0;
+  block_pattern_from_envelope(n_cams, cam_first, re ? perm.data() : nullptr, pattern, &panels);
+  CholPlan pl;
+  pl.compute(n_cams, pattern.data(), panels, split_cams > 0 ? (6 * split_cams) / 128 : -1);
+  info[0] = panels; info[1] = pl.split_a; info[2] = pl.split_t0; info[3] = pl.use ? 1 : 0; info[4] = re ? 1 : 0; info[5] = split_cams;
+  info[6] = info[7] = 0;
+  if (fill) *fill = pl.fill;
+  if (structure) {
+    std::memset(structure, 0, (size_t)panels * panels);
+    if (!pl.row_list.empty())
+      for (int I = 0; I < panels; ++I)
+        for (int q = pl.row_off[(size_t)I]; q < pl.row_off[(size_t)I + 1]; ++q) structure[(size_t)I * panels + pl.row_list[(size_t)q]] = 1;
+  }
+  return 0;
+}
+
 int hsfm_ba_comm_unique_id(void* unique_id_128) {
   if (!unique_id_128) return HSFM_BA_ERR_ARG;
   return comm_unique_id(unique_id_128);
@@ -150,7 +184,8 @@ int hsfm_ba_problem_upload(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double
   h->c.has_problem = false;
   h->c.chol_plan_valid = false;
   double setup = 0, h2d = 0;
-  int rc = build_problem(h->c.prob, mode, n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, dist, cam_rt, n_pts, pts, h->c.comm, h->c.stream, &setup, &h2d);
+  const bool natural = h->c.ordering == 1 || h->c.tap_upload;
+  int rc = build_problem(h->c.prob, mode, n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, dist, cam_rt, n_pts, pts, h->c.comm, h->c.stream, &setup, &h2d, natural);
   if (rc) { h->c.prob.release(); return rc; }
   launch_jacobi_scale(h->c.prob, false, h->c.stream);  // scale = 1 until a solve computes it
   h->c.prob.scal_host[20] = setup;
@@ -221,9 +256,10 @@ int hsfm_ba_problem_frame_stats(hsfm_ba_ctx* h, double* rms_px, double* max_px) 
   HSFM_CUDA(cudaMemcpyAsync(host.data(), out3, sizeof(double) * 3 * nc, cudaMemcpyDeviceToHost, s));
   HSFM_CUDA(cudaStreamSynchronize(s));
   for (size_t c = 0; c < nc; ++c) {
-    const double cnt = host[nc + c];
-    if (rms_px) rms_px[c] = cnt > 0.0 ? std::sqrt(host[c] / cnt) : 0.0;
-    if (max_px) max_px[c] = std::sqrt(host[2 * nc + c]);
+    const size_t k = P.h_cam_new_of_old.empty() ? c : (size_t)P.h_cam_new_of_old[c];  // internal row of the caller's camera c
+    const double cnt = host[nc + k];
+    if (rms_px) rms_px[c] = cnt > 0.0 ? std::sqrt(host[k] / cnt) : 0.0;
+    if (max_px) max_px[c] = std::sqrt(host[2 * nc + k]);
   }
   return 0;
 }
@@ -232,7 +268,12 @@ int hsfm_ba_problem_download(hsfm_ba_ctx* h, double* cam_rt, double* pts) {
   if (!h || !h->c.has_problem) return HSFM_BA_ERR_STATE;
   Problem& P = h->c.prob;
   HSFM_CUDA(cudaSetDevice(h->c.device));
-  if (cam_rt) HSFM_CUDA(cudaMemcpyAsync(cam_rt, P.cam_x, sizeof(double) * 6 * P.n_cams, cudaMemcpyDeviceToHost, h->c.stream));
+  if (cam_rt && P.cam_new_of_old) {
+    launch_cam_rows_to_caller(P, 6, P.cam_x, P.cam_io, h->c.stream);
+    HSFM_CUDA(cudaMemcpyAsync(cam_rt, P.cam_io, sizeof(double) * 6 * P.n_cams, cudaMemcpyDeviceToHost, h->c.stream));
+  } else if (cam_rt) {
+    HSFM_CUDA(cudaMemcpyAsync(cam_rt, P.cam_x, sizeof(double) * 6 * P.n_cams, cudaMemcpyDeviceToHost, h->c.stream));
+  }
   if (pts) {
     launch_rows_to_caller(P, 3, P.pts_x, P.pts_io, h->c.stream);
     HSFM_CUDA(cudaMemcpyAsync(pts, P.pts_io, sizeof(double) * 3 * (size_t)P.n_pts, cudaMemcpyDeviceToHost, h->c.stream));
@@ -450,7 +491,9 @@ int hsfm_ba_eval(hsfm_ba_ctx* h, int64_t n_obs, const double* obs_xy, const int3
                  const double* K9, const double* dist, const double* cam_rt, int64_t n_pts, const double* pts, double* residuals,
                  double* jac, double* cost) {
   if (!h) return HSFM_BA_ERR_ARG;
+  h->c.tap_upload = true;  // parity taps report per-camera quantities: keep the caller's camera order
   int rc = hsfm_ba_problem_upload(h, 2, n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, dist, cam_rt, n_pts, pts);
+  h->c.tap_upload = false;
   if (rc) return rc;
   Problem& P = h->c.prob;
   cudaStream_t s = h->c.stream;
@@ -473,7 +516,9 @@ int hsfm_ba_schur(hsfm_ba_ctx* h, int64_t n_obs, const double* obs_xy, const int
                   const double* K9, const double* dist, const double* cam_rt, int64_t n_pts, const double* pts, const hsfm_ba_options* opts,
                   double radius, double* S_dense, double* rhs, double* Hcc, double* gc, double* Hpp, double* gp, double* scale) {
   if (!h || !opts || !(radius > 0.0)) return HSFM_BA_ERR_ARG;
+  h->c.tap_upload = true;
   int rc = hsfm_ba_problem_upload(h, 2, n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, dist, cam_rt, n_pts, pts);
+  h->c.tap_upload = false;
   if (rc) return rc;
   Problem& P = h->c.prob;
   cudaStream_t s = h->c.stream;

@@ -690,22 +690,19 @@ __device__ __forceinline__ void load_tile_async(double (*dst)[LDS_], const doubl
 }
 
 struct SyrkTile { int ri, ni, rj, nj; };
-// rb_list != nullptr: envelope mode — the tiles are pairs of ACTIVE 128-row blocks (global block indices,
-// ascending).  col_first == 0: the pairs (a, 0), i.e. the column of block rb_list[0] (the next panel);
-// col_first == -1: every pair (a, b), b <= a; col_first == -2: all of them but (0, 0).  Two 64-wide tiles per pair.
-__device__ __forceinline__ SyrkTile syrk_tile(int t, int n, int base, int row_first, int col_first, const int* __restrict__ rb_list) {
+// rb_list != nullptr: structured mode — the tiles are pairs (a, b), b <= a, of the panel's ACTIVE 128-row blocks
+// rb_list[0 .. cnt) (global block indices, ascending), two 64-wide tiles per pair, enumerated column by column:
+// column b holds the rows a = b .. cnt-1.  A launch with fewer tiles than all pairs covers the first block columns
+// only (the two-chain schedule defers the others); col_first == -2 skips pair (0, 0), which the chain stream
+// updates itself.
+__device__ __forceinline__ SyrkTile syrk_tile(int t, int n, int base, int row_first, int col_first, const int* __restrict__ rb_list, int cnt) {
   SyrkTile T;
   if (rb_list) {
-    const int pi = t >> 1, half = t & 1;
-    int a, b;
-    if (col_first == 0) { a = pi; b = 0; }
-    else {
-      const int pp = pi + (col_first == -2 ? 1 : 0);  // -2: every pair but (0, 0), which the chain stream updates
-      a = (int)((sqrtf(8.0f * (float)pp + 1.0f) - 1.0f) * 0.5f);
-      while ((a + 1) * (a + 2) / 2 <= pp) ++a;
-      while (a * (a + 1) / 2 > pp) --a;
-      b = pp - a * (a + 1) / 2;
-    }
+    const int half = t & 1;
+    int pp = (t >> 1) + (col_first == -2 ? 1 : 0);
+    int b = 0, rem = cnt;
+    while (pp >= rem) { pp -= rem; --rem; ++b; }
+    const int a = b + pp;
     T.ri = __ldg(rb_list + a) * NB; T.ni = min(NB, n - T.ri);
     T.rj = __ldg(rb_list + b) * NB + half * TN; T.nj = min(TN, n - T.rj);
     return T;
@@ -728,7 +725,8 @@ __device__ __forceinline__ SyrkTile syrk_tile(int t, int n, int base, int row_fi
 }
 
 __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ S, int n, int k0, int row_first, int col_first, int n_tiles,
-                                                           int stagger, const int* __restrict__ fail, const int* __restrict__ rb_list) {
+                                                           int stagger, const int* __restrict__ fail, const int* __restrict__ rb_list, int rb_cnt,
+                                                           double* __restrict__ Cside, int ldc_side, int side_blk0) {
   extern __shared__ __align__(16) unsigned char gsm_raw[];
   GemmSmem& sm = *reinterpret_cast<GemmSmem*>(gsm_raw);
   int t = blockIdx.x;
@@ -747,7 +745,7 @@ __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ 
     const long long t0 = clock64();
     while (clock64() - t0 < 16000) { }
   }
-  SyrkTile cur = syrk_tile(t, n, base, row_first, col_first, rb_list);
+  SyrkTile cur = syrk_tile(t, n, base, row_first, col_first, rb_list, rb_cnt);
   load_tile_async<NB>(sm.a[0], S, n, cur.ri, cur.ni, k0);
   load_tile_async<TN>(sm.b[0], S, n, cur.rj, cur.nj, k0);
   cp_async_commit();
@@ -758,13 +756,17 @@ __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ 
     const int t_next = t + gridDim.x;
     const bool has_next = t_next < n_tiles;
     SyrkTile nxt = cur;
-    if (has_next) nxt = syrk_tile(t_next, n, base, row_first, col_first, rb_list);
+    if (has_next) nxt = syrk_tile(t_next, n, base, row_first, col_first, rb_list, rb_cnt);
     // C → accumulators.  Full tiles take an unpredicated path: one row pointer per 8-row group, the four
     // column tiles at immediate offsets, every load straight into its accumulator pair — nothing recycles a
     // register, so all 32 loads are in flight at once.
     double acc[8][4][2];
-    double* const crow = S + (size_t)(cur.ri + wr * 64 + fr) * n + cur.rj + wc * 32 + 2 * fk;
-    const size_t rstep = 8 * (size_t)n;
+    // the output tile: in place in S, or (Cside) in the side matrix whose block (0, 0) is block (side_blk0, side_blk0) of S
+    double* const cbase = Cside ? Cside : S;
+    const size_t ldc = Cside ? (size_t)ldc_side : (size_t)n;
+    const int coff = Cside ? side_blk0 * NB : 0;
+    double* const crow = cbase + (size_t)(cur.ri - coff + wr * 64 + fr) * ldc + (cur.rj - coff) + wc * 32 + 2 * fk;
+    const size_t rstep = 8 * ldc;
     const bool full = (cur.ni == NB) && (cur.nj == TN);
 #ifdef HSFM_SYRK_NOLOAD
     if (full) {
@@ -804,7 +806,7 @@ __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ 
         const int e = threadIdx.x + 128 * q;
         const int row = e >> 2, seg = e & 3;
         if (row < nxt.ni && seg * 16 < nxt.nj)
-          asm volatile("prefetch.global.L2 [%0];" ::"l"(S + (size_t)(nxt.ri + row) * n + nxt.rj + seg * 16));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(cbase + (size_t)(nxt.ri - coff + row) * ldc + (nxt.rj - coff) + seg * 16));
       }
     }
 #pragma unroll 1
@@ -1386,8 +1388,12 @@ __device__ __forceinline__ void inv_stage(double* sInv, const double* __restrict
   cp_async_commit();
 }
 
+// Structure (optional, all null = dense): row_off/row_list = the column blocks of every row block (ascending, the
+// diagonal block last), col_off/col_cnt/col_list = the row blocks below the diagonal of every column block.
 __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict__ L, int n, const double* __restrict__ LinvAll, double* b,
-                                                        double* w, int* flag_fwd, int* flag_bwd, const int* __restrict__ fb) {
+                                                        double* w, int* flag_fwd, int* flag_bwd, const int* __restrict__ row_off,
+                                                        const int* __restrict__ row_list, const int* __restrict__ col_off,
+                                                        const int* __restrict__ col_cnt, const int* __restrict__ col_list) {
   extern __shared__ __align__(16) double sInv[];  // [128][TI_LD]
   __shared__ double sv[NB];    // vector of the block being folded in (y_k / x_i)
   __shared__ double sacc[NB];  // running right-hand side of the owned block
@@ -1400,7 +1406,9 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
     __syncthreads();
     inv_stage(sInv, LinvAll + (size_t)i * NB * NB, tid);
     if (tid < NB) sacc[tid] = (tid < nr) ? b[r0 + tid] : 0.0;
-    for (int k = fb ? __ldg(fb + i) : 0; k < i; ++k) {  // blocks left of the envelope are exactly zero
+    const int q_end = row_off ? __ldg(row_off + i + 1) - 1 : i;  // structural blocks only: the others are exactly zero
+    for (int q = row_off ? __ldg(row_off + i) : 0; q < q_end; ++q) {
+      const int k = row_off ? __ldg(row_list + q) : q;
       RowFrag f;
       row_fetch(f, L + (size_t)r0 * n + (size_t)k * NB, (size_t)n, nr, tid);
       if (tid == 0) { while (ld_acquire(flag_fwd + k) == 0) { } }
@@ -1439,8 +1447,9 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
     if (tid == 0) { while (ld_acquire(flag_fwd + kk) == 0) { } }
     __syncthreads();
     if (tid < NB) sacc[tid] = (tid < kb) ? __ldcg(w + c0 + tid) : 0.0;
-    for (int i = P - 1; i > kk; --i) {
-      if (fb && __ldg(fb + i) > kk) continue;  // block (i, kk) lies outside the envelope
+    const int c_beg = col_off ? __ldg(col_off + kk) : 0, c_cnt = col_off ? __ldg(col_cnt + kk) : P - 1 - kk;
+    for (int q = c_cnt - 1; q >= 0; --q) {  // structural blocks of column kk, bottom up
+      const int i = col_off ? __ldg(col_list + c_beg + q) : kk + 1 + q;
       const int r0 = i * NB, nr = min(NB, n - r0);
       ColFrag f;
       col_fetch(f, L + (size_t)r0 * n + c0, (size_t)n, nr, kb, tid);
@@ -1553,6 +1562,13 @@ int CholAux::init() {
   HSFM_CUDA(cudaEventCreateWithFlags(&ev_rest, cudaEventDisableTiming));
   HSFM_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
   HSFM_CUDA(cudaEventCreateWithFlags(&ev_next, cudaEventDisableTiming));
+  HSFM_CUDA(cudaEventCreateWithFlags(&ev_doneA, cudaEventDisableTiming));
+  HSFM_CUDA(cudaStreamCreateWithPriority(&chainB.chain, cudaStreamNonBlocking, hi));
+  HSFM_CUDA(cudaStreamCreateWithPriority(&chainB.bulk, cudaStreamNonBlocking, lo));
+  HSFM_CUDA(cudaEventCreateWithFlags(&chainB.ev_panel, cudaEventDisableTiming));
+  HSFM_CUDA(cudaEventCreateWithFlags(&chainB.ev_next, cudaEventDisableTiming));
+  HSFM_CUDA(cudaEventCreateWithFlags(&chainB.ev_rest, cudaEventDisableTiming));
+  HSFM_CUDA(cudaEventCreateWithFlags(&chainB.ev_done, cudaEventDisableTiming));
   return 0;
 }
 void CholAux::destroy() {
@@ -1560,6 +1576,15 @@ void CholAux::destroy() {
   if (!stream) return;
   cudaStreamDestroy(stream);
   cudaEventDestroy(ev_fork); cudaEventDestroy(ev_panel); cudaEventDestroy(ev_rest); cudaEventDestroy(ev_join); cudaEventDestroy(ev_next);
+  if (ev_doneA) cudaEventDestroy(ev_doneA);
+  if (chainB.chain) cudaStreamDestroy(chainB.chain);
+  if (chainB.bulk) cudaStreamDestroy(chainB.bulk);
+  if (chainB.ev_panel) cudaEventDestroy(chainB.ev_panel);
+  if (chainB.ev_next) cudaEventDestroy(chainB.ev_next);
+  if (chainB.ev_rest) cudaEventDestroy(chainB.ev_rest);
+  if (chainB.ev_done) cudaEventDestroy(chainB.ev_done);
+  chainB = CholChain();
+  ev_doneA = nullptr;
   stream = nullptr;
 }
 
@@ -1573,44 +1598,77 @@ void CholAux::destroy() {
 // ---------------------------------------------------------------------------------------------
 // Envelope plan
 // ---------------------------------------------------------------------------------------------
-int CholPlan::build(int n_cams, const int* cam_first, cudaStream_t s) {
-  ++version;
-  n = 6 * n_cams;
-  panels = (n + NB - 1) / NB;
-  use = false; fill = 1.0;
-  fb.assign((size_t)panels, 0); off.assign((size_t)panels, 0); cnt.assign((size_t)panels, 0); list.clear();
-  if (!cam_first || panels < 4) return 0;
-  for (int I = 0; I < panels; ++I) {
-    int f = I;
-    const int c_lo = (I * NB) / 6, c_hi = std::min(n_cams - 1, (std::min(n, (I + 1) * NB) - 1) / 6);
-    for (int c = c_lo; c <= c_hi; ++c) f = std::min(f, (6 * std::min(cam_first[c], c)) / NB);
-    fb[I] = f;
+// Host part of build(): structure lists and schedule.  Returns false when the plan already holds this structure.
+bool CholPlan::compute(int n_cams, const uint8_t* pattern, int P, int split_hint) {
+  const int n_new = 6 * n_cams, panels_new = (n_new + NB - 1) / NB;
+  {
+    // same structure as the plan already holds (the per-keyframe calls of a scan mostly re-solve an unchanged camera
+    // graph, and bench restarts the same problem): keep plan, device lists, version — and the captured launch graph
+    std::vector<uint8_t> k;
+    if (pattern && P == panels_new) k.assign(pattern, pattern + (size_t)P * P);
+    k.push_back((uint8_t)(split_hint & 0xff)); k.push_back((uint8_t)((split_hint >> 8) & 0xff));
+    if (n == n_new && version > 0 && k == key) return false;
+    key.swap(k);
   }
-  size_t env_blocks = 0;
-  for (int I = 0; I < panels; ++I) env_blocks += (size_t)(I - fb[I] + 1);
-  fill = (double)env_blocks / ((double)panels * (panels + 1) / 2);
-  for (int K = 0; K < panels; ++K) {
+  ++version;
+  n = n_new;
+  panels = panels_new;
+  use = false; fill = 1.0; split_a = split_t0 = -1;
+  off.assign((size_t)panels, 0); cnt.assign((size_t)panels, 0); list.clear();
+  row_off.assign((size_t)panels + 1, 0); row_list.clear();
+  blk_off.clear();
+  if (!pattern || P != panels || panels < 4) return true;
+  std::vector<uint8_t> st(pattern, pattern + (size_t)P * P);
+  symbolic_block_factor(P, st);
+  for (int K = 0; K < P; ++K) {
     off[K] = (int)list.size();
-    for (int I = K + 1; I < panels; ++I)
-      if (fb[I] <= K) list.push_back(I);
+    for (int I = K + 1; I < P; ++I)
+      if (st[(size_t)I * P + K]) list.push_back(I);
     cnt[K] = (int)list.size() - off[K];
   }
+  for (int I = 0; I < P; ++I) {
+    row_off[I] = (int)row_list.size();
+    for (int J = 0; J < I; ++J)
+      if (st[(size_t)I * P + J]) row_list.push_back(J);
+    row_list.push_back(I);
+  }
+  row_off[P] = (int)row_list.size();
+  fill = (double)row_list.size() / ((double)P * (P + 1) / 2);
   static const bool force_dense = getenv("HSFM_CHOL_DENSE") != nullptr;  // experiment knob
   use = fill < 0.6 && !force_dense;
-  if (!use) return 0;
-  const size_t need = (size_t)panels + list.size() + 1;
-  if (need > d_cap) {
-    if (d_fb) cudaFree(d_fb);
-    d_fb = nullptr; d_cap = 0;
-    HSFM_CUDA(cudaMalloc(&d_fb, sizeof(int) * need));
-    d_cap = need;
+  if (!use) return true;
+  // two-chain schedule: chain 0 = [0, a), chain 1 = [a, t0) with t0 the first panel >= a that chain 0 updates
+  if (split_hint > 0 && split_hint < P) {
+    int t0 = P;
+    for (int K = 0; K < split_hint; ++K)
+      for (int q = 0; q < cnt[K]; ++q)
+        if (list[(size_t)off[K] + q] >= split_hint) { t0 = std::min(t0, list[(size_t)off[K] + q]); break; }
+    // worth it only if the second chain has a real share of the panels to itself
+    static const bool one_chain = getenv("HSFM_ONE_CHAIN") != nullptr;  // experiment knob
+    if (!one_chain && t0 - split_hint >= 4 && t0 - split_hint >= split_hint / 4) { split_a = split_hint; split_t0 = t0; }
   }
-  d_list = d_fb + panels;
   blk_off.assign((size_t)panels + 1, 0);
   for (int I = 0; I < panels; ++I) {
-    const long long rows = std::min(NB, n - I * NB), width = (long long)NB * (I + 1 - fb[I]);
+    const long long rows = std::min(NB, n - I * NB), width = (long long)NB * (row_off[I + 1] - row_off[I]);
     blk_off[I + 1] = blk_off[I] + rows * width;
   }
+  return true;
+}
+
+int CholPlan::build(int n_cams, const uint8_t* pattern, int P, int split_hint, cudaStream_t s) {
+  if (!compute(n_cams, pattern, P, split_hint) || !use) return 0;
+  const size_t need = list.size() + row_off.size() + row_list.size() + 2 * (size_t)panels + 1;
+  if (need > d_cap) {
+    if (d_ints) cudaFree(d_ints);
+    d_ints = nullptr; d_cap = 0;
+    HSFM_CUDA(cudaMalloc(&d_ints, sizeof(int) * need));
+    d_cap = need;
+  }
+  d_list = d_ints;
+  d_row_off = d_list + list.size();
+  d_row_list = d_row_off + row_off.size();
+  d_col_off = d_row_list + row_list.size();
+  d_col_cnt = d_col_off + panels;
   if ((size_t)panels + 1 > d_blk_cap) {
     if (d_blk_off) cudaFree(d_blk_off);
     d_blk_off = nullptr; d_blk_cap = 0;
@@ -1618,54 +1676,75 @@ int CholPlan::build(int n_cams, const int* cam_first, cudaStream_t s) {
     d_blk_cap = (size_t)panels + 1;
   }
   HSFM_CUDA(cudaMemcpyAsync(d_blk_off, blk_off.data(), sizeof(long long) * blk_off.size(), cudaMemcpyHostToDevice, s));
-  HSFM_CUDA(cudaMemcpyAsync(d_fb, fb.data(), sizeof(int) * (size_t)panels, cudaMemcpyHostToDevice, s));
   if (!list.empty()) HSFM_CUDA(cudaMemcpyAsync(d_list, list.data(), sizeof(int) * list.size(), cudaMemcpyHostToDevice, s));
+  HSFM_CUDA(cudaMemcpyAsync(d_row_off, row_off.data(), sizeof(int) * row_off.size(), cudaMemcpyHostToDevice, s));
+  HSFM_CUDA(cudaMemcpyAsync(d_row_list, row_list.data(), sizeof(int) * row_list.size(), cudaMemcpyHostToDevice, s));
+  HSFM_CUDA(cudaMemcpyAsync(d_col_off, off.data(), sizeof(int) * (size_t)panels, cudaMemcpyHostToDevice, s));
+  HSFM_CUDA(cudaMemcpyAsync(d_col_cnt, cnt.data(), sizeof(int) * (size_t)panels, cudaMemcpyHostToDevice, s));
   HSFM_CUDA(cudaStreamSynchronize(s));  // the host vectors may be rebuilt by the next problem
   return 0;
 }
-// One CTA per matrix row: the row's envelope segment <-> its place in the packed buffer (16-byte accesses).
-__global__ void __launch_bounds__(256) envelope_pack_kernel(double* __restrict__ S, int n, const int* __restrict__ fb,
-                                                            const long long* __restrict__ blk_off, double* __restrict__ packed, int to_packed) {
+// One CTA per matrix row: the row's structural blocks <-> their place in the packed buffer (16-byte accesses), or
+// (mode 2) zeroed in place.
+__global__ void __launch_bounds__(256) structure_rows_kernel(double* __restrict__ S, int n, const int* __restrict__ row_off,
+                                                             const int* __restrict__ row_list, const long long* __restrict__ blk_off,
+                                                             double* __restrict__ packed, int mode) {
   const int r = blockIdx.x, I = r / NB;
-  const int c0 = __ldg(fb + I) * NB, width = NB * (I + 1) - c0;
-  double2* row = reinterpret_cast<double2*>(S + (size_t)r * n + c0);
-  double2* pk = reinterpret_cast<double2*>(packed + __ldg(blk_off + I) + (long long)(r - I * NB) * width);
-  const int valid = min(width, n - c0);  // the last block's columns past n do not exist (n is even: 6 per camera)
-  for (int e = threadIdx.x; e < valid / 2; e += 256) {
-    if (to_packed) pk[e] = row[e]; else row[e] = pk[e];
+  const int q0 = __ldg(row_off + I), nb = __ldg(row_off + I + 1) - q0;
+  double2* pk = mode == 2 ? nullptr : reinterpret_cast<double2*>(packed + __ldg(blk_off + I) + (long long)(r - I * NB) * (NB * nb));
+  for (int e = threadIdx.x; e < nb * (NB / 2); e += 256) {
+    const int q = e / (NB / 2), c2 = (e - q * (NB / 2)) * 2;
+    const int col = __ldg(row_list + q0 + q) * NB + c2;
+    if (col >= n) continue;  // the last block's columns past n do not exist (n is even: 6 per camera)
+    double2* cell = reinterpret_cast<double2*>(S + (size_t)r * n + col);
+    if (mode == 2) *cell = make_double2(0.0, 0.0);
+    else if (mode == 1) pk[e] = *cell;
+    else *cell = pk[e];
   }
 }
 void launch_envelope_pack(const CholPlan& pl, double* S, double* packed, bool to_packed, cudaStream_t s) {
-  envelope_pack_kernel<<<pl.n, 256, 0, s>>>(S, pl.n, pl.d_fb, pl.d_blk_off, packed, to_packed ? 1 : 0);
+  structure_rows_kernel<<<pl.n, 256, 0, s>>>(S, pl.n, pl.d_row_off, pl.d_row_list, pl.d_blk_off, packed, to_packed ? 1 : 0);
+}
+void launch_structure_zero(const CholPlan& pl, double* S, cudaStream_t s) {
+  structure_rows_kernel<<<pl.n, 256, 0, s>>>(S, pl.n, pl.d_row_off, pl.d_row_list, nullptr, nullptr, 2);
 }
 
 void CholPlan::destroy() {
   if (d_blk_off) cudaFree(d_blk_off);
   d_blk_off = nullptr; d_blk_cap = 0;
-  if (d_fb) cudaFree(d_fb);
-  d_fb = nullptr; d_list = nullptr; d_cap = 0; use = false;
+  if (d_ints) cudaFree(d_ints);
+  d_ints = nullptr; d_list = d_row_off = d_row_list = d_col_off = d_col_cnt = nullptr; d_cap = 0; use = false; key.clear(); version = 0;
 }
 
-// Envelope factorisation: per panel K only the active row blocks R_K are solved and updated.  The critical path is
+// Structured factorisation: per panel K only the active row blocks R_K are solved and updated.  The critical path is
 // kept as short as the data dependence allows:
-//   chain stream:  diag(K) -> solve ONLY row block K+1 of the panel -> update ONLY the diagonal tile (K+1,K+1) -> diag(K+1)
-//   main stream:   after diag(K): solve the other active row blocks; after the chain's solve: the rest of column
-//                  K+1; then every other active pair.  All of it has one whole diagonal-block factorisation to finish
-//                  before the chain needs it (tile (K+2,K+1) at the next step).
-static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches,
-                                const CholPlan& pl, int n_sm) {
-  static const bool no_la = getenv("HSFM_NO_LOOKAHEAD") != nullptr;
-  const bool la = aux && aux->stream && !no_la;
-  cudaStream_t s2 = la ? aux->stream : s;
-  if (la) {
-    cudaEventRecord(aux->ev_fork, s);
-    cudaStreamWaitEvent(s2, aux->ev_fork, 0);
-  }
+//   chain stream:  diag(K) -> tile (K+1,K+1) straight from the unsolved block A(K+1,K) -> diag(K+1)
+//   bulk stream:   after diag(K) and once the chain has read A(K+1,K): panel solve of all active row blocks, then every
+//                  active pair but (K+1,K+1).  All of it has one whole diagonal-block factorisation to finish before
+//                  the chain needs it (tile (K+2,K+1) at the next step).
+// run_chain() enqueues the panels [K_begin, K_end) of ONE chain on a (chain, bulk) stream pair.  own_end < panels:
+// trailing updates whose COLUMN block is >= own_end (R_K is ascending, so the pairs among its last entries) do not go
+// into S but into the side matrix Ctail (order (panels - own_end) * 128, zero at the start): see launch_cholesky_struct.
+struct ChainStreams {
+  cudaStream_t chain, bulk;
+  cudaEvent_t ev_panel, ev_next, ev_rest;
+  bool la;  // chain and bulk are different streams
+};
+static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainStreams& cs, int64_t* launches, const CholPlan& pl, int n_sm,
+                      int K_begin, int K_end, int own_end, double* Ctail, cudaEvent_t start_ev) {
+  const bool la = cs.la;
+  cudaStream_t s = cs.bulk, s2 = cs.chain;
+  const int ldt = (pl.panels - own_end) * NB;
   auto trsm = [&](cudaStream_t st, int k0, double* Linv, const int* list, int cnt) {
     int rows_per = 64;  // strips of 8..64 rows: as many CTAs as fit in ONE wave (the kernel runs one CTA per SM)
     while (rows_per > 8 && cnt * (NB / (rows_per >> 1)) <= n_sm) rows_per >>= 1;
     const int spb = NB / rows_per;
     chol_trsm_strip_kernel<<<cnt * spb, 256, rows_per * TS_LD * (int)sizeof(double), st>>>(S, n, k0, Linv, rows_per, fail_flag, list, spb);
+    ++*launches;
+  };
+  auto syrk = [&](int k0, int col_first, int tiles, const int* list, int cnt, double* C, int ldc, int blk0) {
+    if (tiles <= 0) return;
+    chol_syrk_kernel<<<min(tiles, 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 0, col_first, tiles, 0, fail_flag, list, cnt, C, ldc, blk0);
     ++*launches;
   };
   // chain-stream launches carry the programmatic-serialisation attribute (see pdl_enter)
@@ -1680,7 +1759,8 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
     return cfg;
   };
   bool rest_pending = false;
-  for (int K = 0, k0 = 0; K < pl.panels; ++K, k0 += NB) {
+  if (la && start_ev) cudaStreamWaitEvent(s2, start_ev, 0);
+  for (int K = K_begin, k0 = K_begin * NB; K < K_end; ++K, k0 += NB) {
     const int kb = min(NB, n - k0);
     double* Linv = ws + (size_t)K * NB * NB;
     {
@@ -1689,28 +1769,30 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
     }
     ++*launches;
     const int cnt = pl.cnt[K];
-    // everything the main stream did one step ago must be complete before the chain touches column K+1 / block K+1
-    if (la && rest_pending) { cudaStreamWaitEvent(s2, aux->ev_rest, 0); rest_pending = false; }
+    // everything the bulk stream did one step ago must be complete before the chain touches column K+1 / block K+1
+    if (la && rest_pending) { cudaStreamWaitEvent(s2, cs.ev_rest, 0); rest_pending = false; }
     if (cnt == 0) continue;
+    const int* hl = pl.list.data() + pl.off[K];
     const int* list = pl.d_list + pl.off[K];
-    const bool has_col = pl.list[(size_t)pl.off[K]] == K + 1;
-    if (la) cudaEventRecord(aux->ev_panel, s2);  // diag(K) done
+    int n_own = cnt;  // active rows whose block column is updated in S here
+    if (own_end < pl.panels) { n_own = 0; while (n_own < cnt && hl[n_own] < own_end) ++n_own; }
+    const int ct = cnt - n_own;
+    const bool has_col = hl[0] == K + 1 && n_own > 0;
+    if (la) cudaEventRecord(cs.ev_panel, s2);  // diag(K) done
+    const int pairs_own = n_own * cnt - n_own * (n_own - 1) / 2;  // pairs (a, b), b < n_own, a = b .. cnt-1
     static const bool split_chain = getenv("HSFM_CHAIN_SPLIT") != nullptr;  // experiment knob: panel solve + tile update as two kernels
     if (has_col && !split_chain) {
       // tile (K+1, K+1) straight from the unsolved block A(K+1, K): one kernel between two diagonal blocks
       cudaLaunchConfig_t cfg = chain_cfg(2 * (NB / 8), 256, kChainTileSmem);
       cudaLaunchKernelEx(&cfg, chol_chain_tile_kernel, S, n, k0, (const double*)Linv, list, (const int*)fail_flag);
       ++*launches;
-      if (la) cudaEventRecord(aux->ev_next, s2);  // A(K+1, K) has been read: the main stream may overwrite it with L(K+1, K)
-      if (la) cudaStreamWaitEvent(s, aux->ev_panel, 0);
-      if (la) cudaStreamWaitEvent(s, aux->ev_next, 0);
+      if (la) cudaEventRecord(cs.ev_next, s2);  // A(K+1, K) has been read: the bulk stream may overwrite it with L(K+1, K)
+      if (la) cudaStreamWaitEvent(s, cs.ev_panel, 0);
+      if (la) cudaStreamWaitEvent(s, cs.ev_next, 0);
       trsm(s, k0, Linv, list, cnt);
-      const int tiles = cnt * (cnt + 1) - 2;
-      if (tiles > 0) {
-        chol_syrk_kernel<<<min(tiles, 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 0, -2, tiles, 0, fail_flag, list);
-        ++*launches;
-      }
-      if (la) { cudaEventRecord(aux->ev_rest, s); rest_pending = true; }
+      syrk(k0, -2, 2 * (pairs_own - 1), list, cnt, nullptr, 0, 0);
+      if (ct > 0) syrk(k0, -1, ct * (ct + 1), list + n_own, ct, Ctail, ldt, own_end);
+      if (la) { cudaEventRecord(cs.ev_rest, s); rest_pending = true; }
       continue;
     }
     if (has_col) {
@@ -1719,7 +1801,7 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
         cudaLaunchKernelEx(&cfg, chol_trsm_strip_kernel, S, n, k0, (const double*)Linv, 8, (const int*)fail_flag, list, NB / 8);
         ++*launches;
       }
-      if (la && cnt > 1) cudaEventRecord(aux->ev_next, s2);
+      if (la && cnt > 1) cudaEventRecord(cs.ev_next, s2);
       {  // tile (K+1, K+1): 10 active CTAs of 32 x 32
         cudaLaunchConfig_t cfg = chain_cfg(16, 128, kSyrkLatSmem / 2);
         cudaLaunchKernelEx(&cfg, chol_syrk_col_kernel<32>, S, n, k0, list, (const int*)fail_flag, 0);
@@ -1729,23 +1811,79 @@ static void launch_cholesky_env(double* S, int n, double* ws, int* fail_flag, cu
     const int rest_cnt = has_col ? cnt - 1 : cnt;
     if (rest_cnt > 0) {
       const int* rl = has_col ? list + 1 : list;
-      if (la) cudaStreamWaitEvent(s, aux->ev_panel, 0);
+      if (la) cudaStreamWaitEvent(s, cs.ev_panel, 0);
       trsm(s, k0, Linv, rl, rest_cnt);
       if (has_col) {
         // one update launch for column K+1 below its diagonal tile and every other active pair
-        if (la) cudaStreamWaitEvent(s, aux->ev_next, 0);
-        const int tiles = cnt * (cnt + 1) - 2;
-        chol_syrk_kernel<<<min(tiles, 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 0, -2, tiles, 0, fail_flag, list);
+        if (la) cudaStreamWaitEvent(s, cs.ev_next, 0);
+        syrk(k0, -2, 2 * (pairs_own - 1), list, cnt, nullptr, 0, 0);
       } else {
-        const int tiles = rest_cnt * (rest_cnt + 1);
-        chol_syrk_kernel<<<min(tiles, 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 0, -1, tiles, 0, fail_flag, rl);
+        syrk(k0, -1, 2 * pairs_own, list, cnt, nullptr, 0, 0);
       }
-      ++*launches;
-      if (la) { cudaEventRecord(aux->ev_rest, s); rest_pending = true; }
+      if (ct > 0) syrk(k0, -1, ct * (ct + 1), list + n_own, ct, Ctail, ldt, own_end);
+      if (la) { cudaEventRecord(cs.ev_rest, s); rest_pending = true; }
     }
   }
+  // leave with the chain stream caught up with its bulk stream
+  if (la && rest_pending) cudaStreamWaitEvent(s2, cs.ev_rest, 0);
+}
+
+// S[tail, tail] += T over the lower block triangle of the tail (row blocks >= t0): the join of the two-chain schedule.
+__global__ void __launch_bounds__(256) tail_add_kernel(double* __restrict__ S, int n, int t0, const double* __restrict__ T, int ldt) {
+  const int r = t0 * NB + blockIdx.x;  // matrix row
+  if (r >= n) return;
+  const int c_end = min(n, (r / NB + 1) * NB) - t0 * NB;  // columns up to the end of the row's diagonal block
+  double2* dst = reinterpret_cast<double2*>(S + (size_t)r * n + (size_t)t0 * NB);
+  const double2* src = reinterpret_cast<const double2*>(T + (size_t)blockIdx.x * ldt);
+  for (int e = threadIdx.x; e < c_end / 2; e += 256) {
+    double2 v = dst[e];
+    const double2 a = src[e];
+    v.x += a.x; v.y += a.y;
+    dst[e] = v;
+  }
+}
+
+// One chain over all panels, or — when the plan carries a two-chain schedule (two-ended camera order, ba_order.cpp)
+// — chain A = panels [0, a) and chain B = [a, t0) concurrently on their own stream pairs, then the tail [t0, panels)
+// as a single chain.  Both chains update the tail blocks (>= t0): chain B in S, chain A in the side matrix T (after the
+// L11^-1 blocks in the workspace), which is added to S at the join — the two never write the same memory and the
+// summation order is fixed.
+static void launch_cholesky_struct(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches,
+                                   const CholPlan& pl, int n_sm) {
+  static const bool no_la = getenv("HSFM_NO_LOOKAHEAD") != nullptr;
+  const bool la = aux && aux->stream && !no_la;
+  ChainStreams A{la ? aux->stream : s, s, la ? aux->ev_panel : nullptr, la ? aux->ev_next : nullptr, la ? aux->ev_rest : nullptr, la};
+  const bool two = la && pl.split_a > 0 && pl.split_t0 > pl.split_a && aux->chainB.chain;
+  double* T = ws + cholesky_workspace_doubles(n);
+  if (two) cudaMemsetAsync(T, 0, sizeof(double) * (size_t)pl.tail_doubles(), s);
   if (la) {
-    cudaEventRecord(aux->ev_join, s2);
+    cudaEventRecord(aux->ev_fork, s);
+    cudaStreamWaitEvent(A.chain, aux->ev_fork, 0);
+  }
+  if (!two) {
+    run_chain(S, n, ws, fail_flag, A, launches, pl, n_sm, 0, pl.panels, pl.panels, nullptr, nullptr);
+  } else {
+    const CholChain& cb = aux->chainB;
+    ChainStreams B{cb.chain, cb.bulk, cb.ev_panel, cb.ev_next, cb.ev_rest, true};
+    cudaStreamWaitEvent(B.chain, aux->ev_fork, 0);
+    cudaStreamWaitEvent(B.bulk, aux->ev_fork, 0);
+    const int a = pl.split_a, t0 = pl.split_t0;
+    run_chain(S, n, ws, fail_flag, A, launches, pl, n_sm, 0, a, t0, T, nullptr);
+    run_chain(S, n, ws, fail_flag, B, launches, pl, n_sm, a, t0, pl.panels, nullptr, nullptr);
+    // join: s (= A.bulk) waits for A.chain, B.chain and B.bulk
+    cudaEventRecord(aux->ev_doneA, A.chain);
+    cudaStreamWaitEvent(s, aux->ev_doneA, 0);
+    cudaEventRecord(cb.ev_panel, B.chain);
+    cudaStreamWaitEvent(B.bulk, cb.ev_panel, 0);
+    cudaEventRecord(cb.ev_done, B.bulk);
+    cudaStreamWaitEvent(s, cb.ev_done, 0);
+    tail_add_kernel<<<n - t0 * NB, 256, 0, s>>>(S, n, t0, T, (pl.panels - t0) * NB);
+    ++*launches;
+    cudaEventRecord(aux->ev_fork, s);
+    run_chain(S, n, ws, fail_flag, A, launches, pl, n_sm, t0, pl.panels, pl.panels, nullptr, aux->ev_fork);
+  }
+  if (la) {
+    cudaEventRecord(aux->ev_join, A.chain);
     cudaStreamWaitEvent(s, aux->ev_join, 0);
   }
 }
@@ -1771,7 +1909,7 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
         cudaGraph_t g = nullptr;
         int64_t counted = 0;
         if (cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
-          launch_cholesky_env(S, n, ws, fail_flag, s, aux, &counted, *plan, n_sm);
+          launch_cholesky_struct(S, n, ws, fail_flag, s, aux, &counted, *plan, n_sm);
           if (cudaStreamEndCapture(s, &g) == cudaSuccess && g && cudaGraphInstantiate(&aux->graph, g, 0) == cudaSuccess) {
             aux->g_S = S; aux->g_ws = ws; aux->g_fail = fail_flag; aux->g_stream = (const void*)s; aux->g_n = n;
             aux->g_version = plan->version; aux->g_launches = counted;
@@ -1788,7 +1926,7 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
       }
       cudaGetLastError();
     }
-    launch_cholesky_env(S, n, ws, fail_flag, s, aux, launches, *plan, n_sm);
+    launch_cholesky_struct(S, n, ws, fail_flag, s, aux, launches, *plan, n_sm);
     return;
   }
   const int panels = (n + NB - 1) / NB;
@@ -1816,16 +1954,16 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
       cudaEventRecord(aux->ev_panel, s2);
       if (panel > 0) cudaStreamWaitEvent(s2, aux->ev_rest, 0);  // "ahead k-1": cb 2,3 of the previous step = cb 0,1 of this one
     }
-    chol_syrk_kernel<<<min(2 * rb, 2 * n_sm), 128, kGemmSmem, s2>>>(S, n, k0, 0, 0, 2 * rb, 0, fail_flag, nullptr);
+    chol_syrk_kernel<<<min(2 * rb, 2 * n_sm), 128, kGemmSmem, s2>>>(S, n, k0, 0, 0, 2 * rb, 0, fail_flag, nullptr, 0, nullptr, 0, 0);
     ++*launches;
     if (rb > 1) {
       if (la) cudaStreamWaitEvent(s, aux->ev_panel, 0);
-      chol_syrk_kernel<<<min(2 * (rb - 1), 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 1, 2, 2 * (rb - 1), 0, fail_flag, nullptr);
+      chol_syrk_kernel<<<min(2 * (rb - 1), 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 1, 2, 2 * (rb - 1), 0, fail_flag, nullptr, 0, nullptr, 0, 0);
       ++*launches;
     }
     if (la) cudaEventRecord(aux->ev_rest, s);
     if (rb > 2) {
-      chol_syrk_kernel<<<min((rb - 2) * (rb - 1), bulk_ctas), 128, kGemmSmem, s>>>(S, n, k0, 0, -4, (rb - 2) * (rb - 1), 0, fail_flag, nullptr);
+      chol_syrk_kernel<<<min((rb - 2) * (rb - 1), bulk_ctas), 128, kGemmSmem, s>>>(S, n, k0, 0, -4, (rb - 2) * (rb - 1), 0, fail_flag, nullptr, 0, nullptr, 0, 0);
       ++*launches;
     }
   }
@@ -1849,8 +1987,14 @@ void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream
     int* ff = flags;
     int* fb = flags + panels;
     int nn = n;
-    const int* env = (plan && plan->use && plan->n == n) ? plan->d_fb : nullptr;
-    void* args[] = {(void*)&L, (void*)&nn, (void*)&LinvAll, (void*)&b, (void*)&w, (void*)&ff, (void*)&fb, (void*)&env};
+    const bool st = plan && plan->use && plan->n == n;
+    const int* row_off = st ? plan->d_row_off : nullptr;
+    const int* row_list = st ? plan->d_row_list : nullptr;
+    const int* col_off = st ? plan->d_col_off : nullptr;
+    const int* col_cnt = st ? plan->d_col_cnt : nullptr;
+    const int* col_list = st ? plan->d_list : nullptr;
+    void* args[] = {(void*)&L,  (void*)&nn,      (void*)&LinvAll,  (void*)&b,       (void*)&w,       (void*)&ff,
+                    (void*)&fb, (void*)&row_off, (void*)&row_list, (void*)&col_off, (void*)&col_cnt, (void*)&col_list};
     const int grid = std::min(panels, n_sm);
     if (cudaLaunchCooperativeKernel((const void*)trsv_coop_kernel, dim3(grid), dim3(256), args, kTrsvSmem, s) == cudaSuccess) {
       ++*launches;

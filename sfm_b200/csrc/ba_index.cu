@@ -119,6 +119,19 @@ __global__ void min_cam_kernel(int n, const int* __restrict__ pt, const int* __r
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) atomicMin(min_cam + pt[i], cam[i]);
 }
+// the same on indices that have not been validated yet (out-of-range entries are skipped; the upload then fails)
+__global__ void min_cam_checked_kernel(int n, const int* __restrict__ pt, const int* __restrict__ cam, int n_cams, int n_pts,
+                                       int* __restrict__ min_cam) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && (unsigned)cam[i] < (unsigned)n_cams && (unsigned)pt[i] < (unsigned)n_pts) atomicMin(min_cam + pt[i], cam[i]);
+}
+// first[c] = smallest camera that shares a point with camera c (first[] preset to c): the envelope of the reduced
+// camera matrix in the CALLER's camera order.  Integer atomicMin: order-independent, once per upload.
+__global__ void cam_first_raw_kernel(int n, const int* __restrict__ pt, const int* __restrict__ cam, int n_cams, int n_pts,
+                                     const int* __restrict__ min_cam, int* __restrict__ first) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && (unsigned)cam[i] < (unsigned)n_cams && (unsigned)pt[i] < (unsigned)n_pts) atomicMin(first + cam[i], min_cam[pt[i]]);
+}
 __global__ void invert_perm_kernel(int n, const int* __restrict__ old_of_new, int* __restrict__ new_of_old) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k < n) new_of_old[old_of_new[k]] = k;
@@ -156,24 +169,16 @@ void launch_rows_to_caller(Problem& P, int w, const double* internal_order, doub
   P.launches++;
 }
 
+void launch_cam_rows_to_caller(Problem& P, int w, const double* internal_order, double* caller_order, cudaStream_t s) {
+  if (P.n_cams == 0) return;
+  gather_rows_kernel<<<cdivz((size_t)P.n_cams * w, 256), 256, 0, s>>>(P.n_cams, w, P.cam_new_of_old, internal_order, caller_order);
+  P.launches++;
+}
+
 __global__ void validate_idx_kernel(int n, const int* __restrict__ cam, const int* __restrict__ pt, int n_cams, int n_pts,
                                     int* __restrict__ bad) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n && ((unsigned)cam[i] >= (unsigned)n_cams || (unsigned)pt[i] >= (unsigned)n_pts)) *bad = 1;
-}
-
-// cam_first[c] = smallest camera that shares a point with camera c: the envelope of S.  Internal point ids
-// are ordered by their smallest observing camera, so it is min_cam_sorted[smallest internal point id among
-// the camera's observations]; one warp per camera over the camera-major list, no atomics.
-__global__ void cam_first_kernel(int n_cams, const int* __restrict__ cam_start, const int* __restrict__ pt_cs,
-                                 const int* __restrict__ min_cam_sorted, int* __restrict__ first) {
-  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (c >= n_cams) return;
-  int m = 0x7fffffff;
-  for (int j = cam_start[c] + lane; j < cam_start[c + 1]; j += 32) m = min(m, pt_cs[j]);
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) m = min(m, __shfl_xor_sync(0xffffffffu, m, d));
-  if (lane == 0) first[c] = (m == 0x7fffffff) ? c : min(c, min_cam_sorted[m]);
 }
 
 // One CTA per tile: the tile's distinct cameras in ascending order and the slot of every observation's
@@ -206,7 +211,7 @@ __global__ void __launch_bounds__(TILE) tile_cams_kernel(const int* __restrict__
 
 int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
                   int32_t n_cams, const double* K9, const double* dist, const double* cam_rt, int64_t n_pts64, const double* pts,
-                  Comm& comm, cudaStream_t s, double* setup_ms, double* h2d_ms) {
+                  Comm& comm, cudaStream_t s, double* setup_ms, double* h2d_ms, bool natural_order) {
   P.release();
   if (n_obs64 >= (int64_t)1 << 31 || n_pts64 >= (int64_t)1 << 30) return HSFM_BA_ERR_UNSUPPORTED;
   const int n = (int)n_obs64, n_pts = (int)n_pts64;
@@ -222,7 +227,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     int* nullk = nullptr;
     cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp, nullk, nullk, nullk, nullk, std::max({n, n_pts, 1}), 0, 32, s);
     t2 = sort_tmp;
-    const size_t need = 336 * no + 360 * np + 2400 * nc + 280 * (no / 128 + nc + np / 256 + 8) + 2 * t2 + ((size_t)1 << 20);
+    const size_t need = 344 * no + 360 * np + 2600 * nc + 280 * (no / 128 + nc + np / 256 + 8) + 2 * t2 + ((size_t)1 << 20);
     int rc = P.arena_reserve(need);
     if (rc) return rc;
   }
@@ -240,7 +245,25 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   else HSFM_CUDA(cudaMemsetAsync(P.dist, 0, sizeof(double) * 2 * std::max(1, n_cams), s));
   HSFM_CUDA(cudaMemcpyAsync(P.cam_x0, cam_rt, sizeof(double) * 6 * n_cams, cudaMemcpyHostToDevice, s));
   HSFM_CUDA(cudaMemcpyAsync(P.pts_io, pts, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyHostToDevice, s));
-  HSFM_CUDA(cudaMemcpyAsync(P.cam_x, P.cam_x0, sizeof(double) * 6 * n_cams, cudaMemcpyDeviceToDevice, s));
+  // Envelope of the reduced camera matrix in the caller's camera order (over all ranks): what the camera ordering and
+  // the block structure of the Cholesky are derived from.  Only where a structured factorisation can pay (>= 4 panels).
+  int *min_cam, *min_cam_sorted;
+  ALLOC(min_cam, n_pts); ALLOC(min_cam_sorted, n_pts);
+  const bool want_structure = mode == 2 && n > 0 && n_pts > 0 && 6 * (int64_t)n_cams >= 4 * 128;
+  int* d_first = nullptr;
+  if (want_structure) {
+    ALLOC(d_first, n_cams);
+    fill_int_kernel<<<cdiv(n_pts, 256), 256, 0, s>>>(n_pts, n_cams, min_cam);
+    min_cam_checked_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, pt_in, cam_in, n_cams, n_pts, min_cam);
+    iota_kernel<<<cdiv(n_cams, 256), 256, 0, s>>>(n_cams, d_first);
+    cam_first_raw_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, pt_in, cam_in, n_cams, n_pts, min_cam, d_first);
+    if (comm.n_ranks > 1) {
+      int rc = comm.allreduce_min_i32(d_first, (size_t)n_cams, s);
+      if (rc) return rc;
+    }
+    P.cam_first.assign((size_t)n_cams, 0);
+    HSFM_CUDA(cudaMemcpyAsync(P.cam_first.data(), d_first, sizeof(int) * (size_t)n_cams, cudaMemcpyDeviceToHost, s));
+  }
   {
     int* d_bad;
     ALLOC(d_bad, 1);
@@ -254,13 +277,33 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   const double t_setup0 = now_ms();
   if (h2d_ms) *h2d_ms = t_setup0 - t_h2d0;
 
+  // ---- internal camera order (ba_order.cpp): a band is eliminated from both ends at once ----
+  if (want_structure && !natural_order && choose_camera_order(n_cams, P.cam_first.data(), P.h_cam_new_of_old, &P.split_cams)) {
+    int* cam_tmp;
+    ALLOC(P.cam_new_of_old, n_cams); ALLOC(P.cam_old_of_new, n_cams); ALLOC(cam_tmp, n); ALLOC(P.cam_io, 9 * (size_t)n_cams);
+    HSFM_CUDA(cudaMemcpyAsync(P.cam_new_of_old, P.h_cam_new_of_old.data(), sizeof(int) * (size_t)n_cams, cudaMemcpyHostToDevice, s));
+    invert_perm_kernel<<<cdiv(n_cams, 256), 256, 0, s>>>(n_cams, P.cam_new_of_old, P.cam_old_of_new);
+    gather_int_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, cam_in, P.cam_new_of_old, cam_tmp);
+    cam_in = cam_tmp;
+    // camera tables: row k of the internal order = row old_of_new[k] of the caller's
+    struct { double* a; int w; } tabs[3] = {{P.K9, 9}, {P.dist, 2}, {P.cam_x0, 6}};
+    for (auto& t : tabs) {
+      gather_rows_kernel<<<cdivz((size_t)n_cams * t.w, 256), 256, 0, s>>>(n_cams, t.w, P.cam_old_of_new, t.a, P.cam_io);
+      HSFM_CUDA(cudaMemcpyAsync(t.a, P.cam_io, sizeof(double) * (size_t)t.w * n_cams, cudaMemcpyDeviceToDevice, s));
+    }
+  } else {
+    P.h_cam_new_of_old.clear();
+    P.split_cams = -1;
+  }
+  HSFM_CUDA(cudaMemcpyAsync(P.cam_x, P.cam_x0, sizeof(double) * 6 * n_cams, cudaMemcpyDeviceToDevice, s));
+
   // ---- static arrays ----
-  double2 *obs, *obs_cs; int *cam, *pt, *pt_cs, *pt_start, *cam_start, *iota, *pos_cs, *cam_sorted, *order1, *key2, *min_cam, *min_cam_sorted;
+  double2 *obs, *obs_cs; int *cam, *pt, *pt_cs, *pt_start, *cam_start, *iota, *pos_cs, *cam_sorted, *order1, *key2;
   ALLOC(obs, n); ALLOC(cam, n); ALLOC(pt, n); ALLOC(obs_cs, n); ALLOC(pt_cs, n);
   ALLOC(pt_start, (size_t)n_pts + 1); ALLOC(cam_start, (size_t)n_cams + 1);
   const int n_iota = std::max(n, n_pts);
   ALLOC(iota, n_iota); ALLOC(P.order_pm, n); ALLOC(pos_cs, n); ALLOC(cam_sorted, n); ALLOC(order1, n); ALLOC(key2, n);
-  ALLOC(min_cam, n_pts); ALLOC(min_cam_sorted, n_pts); ALLOC(P.pt_old_of_new, n_pts); ALLOC(P.pt_new_of_old, n_pts);
+  ALLOC(P.pt_old_of_new, n_pts); ALLOC(P.pt_new_of_old, n_pts);
   if (n_iota > 0) iota_kernel<<<cdiv(n_iota, 256), 256, 0, s>>>(n_iota, iota);
   int pbits = 1; while ((1ll << pbits) < std::max(2, n_pts)) ++pbits;
   int cbits = 1; while ((1ll << cbits) < std::max(2, (int)n_cams) + 1) ++cbits;
@@ -297,20 +340,6 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   } else {
     HSFM_CUDA(cudaMemsetAsync(pt_start, 0, sizeof(int) * ((size_t)n_pts + 1), s));
     HSFM_CUDA(cudaMemsetAsync(cam_start, 0, sizeof(int) * ((size_t)n_cams + 1), s));
-  }
-  {
-    // envelope of the reduced camera matrix (over all ranks), kept on the host for the Cholesky plan
-    int* d_first;
-    ALLOC(d_first, n_cams);
-    P.cam_first.assign((size_t)n_cams, 0);
-    if (n_cams > 0) {
-      cam_first_kernel<<<cdiv(n_cams * 32, 256), 256, 0, s>>>(n_cams, cam_start, pt_cs, min_cam_sorted, d_first);
-      if (comm.n_ranks > 1) {
-        int rc = comm.allreduce_min_i32(d_first, (size_t)n_cams, s);
-        if (rc) return rc;
-      }
-      HSFM_CUDA(cudaMemcpyAsync(P.cam_first.data(), d_first, sizeof(int) * (size_t)n_cams, cudaMemcpyDeviceToHost, s));
-    }
   }
   HSFM_CUDA(cudaStreamSynchronize(s));
 

@@ -59,7 +59,13 @@ struct Problem {
   int max_track = 0;
   int n_sm = 148;         // SM count of the context's device (set by hsfm_ba_create; survives release())
   int max_tile_cams = 0;  // largest number of distinct cameras in one tile (sizes the shared-memory row staging)
-  std::vector<int> cam_first;  // [n_cams] smallest camera sharing a point with camera c (all ranks) — envelope of S
+  std::vector<int> cam_first;  // [n_cams] CALLER order: smallest camera sharing a point with camera c (all ranks) — envelope of S
+  // internal camera order (ba_order.cpp): null / empty = the caller's order
+  std::vector<int> h_cam_new_of_old;
+  int* cam_new_of_old = nullptr;  // device [n_cams]
+  int* cam_old_of_new = nullptr;  // device [n_cams]
+  int split_cams = -1;            // first internal camera of the second chain (two-ended order) or -1
+  double* cam_io = nullptr;       // [n_cams][9] staging in the caller's camera order (upload / download / taps)
   Dev d{};
   // Device arena: ONE grow-only allocation per context that every per-problem buffer is carved from, so the
   // per-keyframe calls of CSfM::mapping (CSfM.cpp:252-259) pay for cudaMalloc/cudaFree only when the problem
@@ -134,7 +140,9 @@ int comm_init(Comm& c, const void* id128, int rank, int n_ranks);
 // ---- index build (ba_index.cu) ----
 int build_problem(Problem& P, int mode, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
                   int32_t n_cams, const double* K9, const double* dist, const double* cam_rt, int64_t n_pts, const double* pts,
-                  Comm& comm, cudaStream_t s, double* setup_ms, double* h2d_ms);
+                  Comm& comm, cudaStream_t s, double* setup_ms, double* h2d_ms, bool natural_order = false);
+// camera-indexed rows between the caller's camera order and the internal one
+void launch_cam_rows_to_caller(Problem& P, int w, const double* internal_order, double* caller_order, cudaStream_t s);
 
 // point-indexed rows between the caller's point order and the internal one (ba_index.cu)
 void launch_rows_to_internal(Problem& P, int w, const double* caller_order, double* internal_order, cudaStream_t s);
@@ -173,9 +181,16 @@ void launch_mirror_lower(Problem& P, cudaStream_t s);   // S upper <- lower (par
 // In-place lower Cholesky of row-major n×n S (lower triangle read/written); *fail_flag set to
 // non-zero on a non-positive pivot.  Then solve S y = b in place in b.
 // auxiliary high-priority stream + events for the panel look-ahead of the factorisation
+struct CholChain {  // streams + events of one panel chain of the structured factorisation
+  cudaStream_t chain = nullptr;  // high priority: diagonal blocks and next-diagonal-tile kernels
+  cudaStream_t bulk = nullptr;   // panel solves and trailing updates, one step behind
+  cudaEvent_t ev_panel = nullptr, ev_next = nullptr, ev_rest = nullptr, ev_done = nullptr;
+};
 struct CholAux {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_panel = nullptr, ev_rest = nullptr, ev_join = nullptr, ev_next = nullptr;
+  CholChain chainB;        // second chain of the two-ended schedule (the first one runs on `stream` + the caller's stream)
+  cudaEvent_t ev_doneA = nullptr;
   // captured launch sequence of the envelope factorisation (static per problem: same S, workspace and plan)
   cudaGraphExec_t graph = nullptr;
   const void* g_S = nullptr; const void* g_ws = nullptr; const void* g_fail = nullptr; const void* g_stream = nullptr;
@@ -185,31 +200,46 @@ struct CholAux {
   int init();              // also opts the factorisation kernels into their dynamic shared memory ON THE CURRENT DEVICE
   void destroy();
 };
-// Block envelope of the reduced camera matrix (static per problem).  Camera c shares points with no camera
-// below cam_first[c], so row block I of S (128 rows) is exactly zero left of column block fb[I], and so is L: the
-// Cholesky factor has the envelope of the matrix.  Panel K then only has to touch the ACTIVE row blocks
-// R_K = { I > K : fb[I] <= K }.  For a scan trajectory (keyframes see points of nearby keyframes, plus a few loop
-// closures) that is a band: the factorisation of the Venice-shaped problem costs 2-3 % of the dense flops.
+// Block structure of the reduced camera matrix and of its Cholesky factor (static per problem), at the granularity
+// of the factorisation's 128-row panels.  Block (I,J) of S is non-zero only when a camera of row block I shares a
+// point with a camera of column block J; closing that pattern under elimination (ba_order.cpp) gives the structure
+// of L.  Panel K then only has to touch the row blocks R_K = { I > K : L(I,K) != 0 } — everything else is an exact
+// zero that is never computed, so the result is the factor a dense LLT (CTracker.cpp:574) would produce.  For a scan
+// trajectory (keyframes see the points of nearby keyframes, plus a few loop closures) the structure is a band, or —
+// in the two-ended camera order chosen at upload — two bands meeting in a tail block: the factorisation of the
+// Venice-shaped problem costs 2-3 % of the dense flops.
 struct CholPlan {
   int n = 0, panels = 0;
-  int version = 0;             // bumped by every build(): invalidates captured launch graphs
-  bool use = false;            // false: treat the matrix as dense (the envelope is most of the triangle)
-  double fill = 1.0;           // envelope blocks / lower-triangle blocks
-  std::vector<int> fb;         // [panels] first column block in the envelope of row block I
-  std::vector<int> off, cnt;   // per panel K: list[off[K] .. off[K]+cnt[K]) = R_K ascending
+  int version = 0;             // bumped when the structure changes: invalidates captured launch graphs
+  bool use = false;            // false: treat the matrix as dense (the structure is most of the triangle)
+  double fill = 1.0;           // structural blocks / lower-triangle blocks
+  std::vector<int> off, cnt;   // per panel K: list[off[K] .. off[K]+cnt[K]) = R_K ascending  (column structure)
   std::vector<int> list;
-  int* d_fb = nullptr;         // device copy: fb, then the lists
-  int* d_list = nullptr;
+  std::vector<int> row_off, row_list;  // per row block I: row_list[row_off[I] .. row_off[I+1]) = { J <= I : L(I,J) != 0 } ascending (ends with I)
+  // Two-chain schedule (two-ended camera order): panels [0, split_a) and [split_a, split_t0) are independent chains,
+  // factored concurrently; split_t0 is the first panel that receives updates from both.  -1: one chain.
+  int split_a = -1, split_t0 = -1;
+  int* d_ints = nullptr;       // device copy: list | row_off | row_list | col_off | col_cnt
+  int* d_list = nullptr; int* d_row_off = nullptr; int* d_row_list = nullptr; int* d_col_off = nullptr; int* d_col_cnt = nullptr;
   size_t d_cap = 0;
-  // packed envelope (multi-GPU: only these entries of S are summed across ranks): row r of block I occupies
-  // packed[blk_off[I] + (r - 128 I) * width(I)) .. + width(I)), width(I) = 128 (I + 1 - fb[I]) columns from 128 fb[I]
+  // packed structure (multi-GPU: only these entries of S are summed across ranks): row r of block I occupies
+  // packed[blk_off[I] + (r - 128 I) * width(I)) .. + width(I)), width(I) = 128 * (blocks in row I), blocks in row_list order
   std::vector<long long> blk_off;  // [panels + 1]
   long long* d_blk_off = nullptr;
   size_t d_blk_cap = 0;
+  std::vector<uint8_t> key;    // the pattern the plan was built from: an unchanged structure keeps plan, version and graph
   long long packed_doubles() const { return blk_off.empty() ? 0 : blk_off.back(); }
-  int build(int n_cams, const int* cam_first, cudaStream_t s);  // cam_first on the host; nullptr = dense
+  // side matrix of the two-chain schedule: the tail blocks [split_t0, panels), square, after the L11^-1 blocks in the workspace
+  long long tail_doubles() const { return (use && split_a > 0) ? (long long)(panels - split_t0) * 128 * (panels - split_t0) * 128 : 0; }
+  // pattern: P x P bytes, lower triangle, NOT yet closed under elimination (nullptr = dense); split_hint: first panel of the second chain or -1
+  int build(int n_cams, const uint8_t* pattern, int P, int split_hint, cudaStream_t s);
+  bool compute(int n_cams, const uint8_t* pattern, int P, int split_hint);  // host part only (no device); false: unchanged
   void destroy();
 };
+// host-side structure code (ba_order.cpp)
+bool choose_camera_order(int n_cams, const int* first, std::vector<int>& new_of_old, int* split_cams);
+void block_pattern_from_envelope(int n_cams, const int* first, const int* new_of_old, std::vector<uint8_t>& pattern, int* panels);
+void symbolic_block_factor(int P, std::vector<uint8_t>& pattern);
 size_t cholesky_workspace_doubles(int n);  // L11^-1 blocks (one 128×128 per panel) + flags of the cooperative triangular solve
 void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches,
                      const CholPlan* plan = nullptr);
@@ -218,6 +248,7 @@ void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream
 
 // S envelope <-> packed buffer (to_packed: gather; else scatter)
 void launch_envelope_pack(const CholPlan& pl, double* S, double* packed, bool to_packed, cudaStream_t s);
+void launch_structure_zero(const CholPlan& pl, double* S, cudaStream_t s);  // zero the structural blocks of S only
 void launch_spd_fill(double* A, int n, double* b /*null = matrix only*/, cudaStream_t s);  // bench tap: synthetic SPD matrix, b = A 1
 void launch_spd_err(int n, const double* x, double* err, cudaStream_t s);                 // max |x - 1|
 
@@ -232,6 +263,8 @@ struct Ctx {
   bool chol_plan_valid = false;
   Problem prob;
   bool has_problem = false;
+  int ordering = 0;         // 0 = automatic camera order, 1 = the caller's (hsfm_ba_set_ordering)
+  bool tap_upload = false;  // upload on behalf of a parity tap: caller's camera order
   std::vector<cudaEvent_t> phase_events;  // pool reused across solves (phase timing of lm_solve)
 };
 int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary);

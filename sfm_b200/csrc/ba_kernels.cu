@@ -1493,19 +1493,11 @@ void launch_pcg_step(Problem& P, double tol, int max_it, cudaStream_t s) {
   P.launches++;
 }
 
-// Zero the envelope of S only: one CTA per matrix row, columns [128 fb[I], 128 (I+1)) of its row block I.
-__global__ void __launch_bounds__(256) envelope_zero_kernel(double* __restrict__ S, int n, const int* __restrict__ fb) {
-  const int r = blockIdx.x, I = r / 128;
-  const int c0 = __ldg(fb + I) * 128, c1 = min(n, 128 * (I + 1));
-  double2* row = reinterpret_cast<double2*>(S + (size_t)r * n + c0);
-  for (int e = threadIdx.x; e < (c1 - c0) / 2; e += 256) row[e] = make_double2(0.0, 0.0);
-}
-
 void launch_dense_init(Problem& P, bool with_diag, cudaStream_t s, const CholPlan* plan) {
   const size_t n = 6 * (size_t)P.n_cams;
   if (plan && plan->use && plan->n == (int)n) {
-    // nothing outside the envelope is ever read by the envelope factorisation / solves
-    envelope_zero_kernel<<<(int)n, 256, 0, s>>>(P.S, (int)n, plan->d_fb);
+    // nothing outside the block structure is ever read by the structured factorisation / solves
+    launch_structure_zero(*plan, P.S, s);
     P.launches++;
   } else {
     cudaMemsetAsync(P.S, 0, sizeof(double) * n * n, s);

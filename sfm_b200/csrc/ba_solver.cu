@@ -103,7 +103,7 @@ struct Driver {
           if (pl.use && pl.n == n6 && !(o.dense_flags & 1)) {
             // only the envelope of S can be non-zero on any rank: sum that (packed behind the factorisation's
             // workspace) instead of the whole n x n matrix
-            double* packed = P.S + (size_t)n6 * n6 + cholesky_workspace_doubles(n6);
+            double* packed = P.S + (size_t)n6 * n6 + cholesky_workspace_doubles(n6) + (size_t)pl.tail_doubles();
             launch_envelope_pack(pl, P.S, packed, true, s);
             chk(ctx.comm.allreduce_sum(packed, (size_t)pl.packed_doubles(), s));
             launch_envelope_pack(pl, P.S, packed, false, s);
@@ -180,7 +180,15 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
   if (P.mode == 2) {
     auto ensure_plan = [&]() -> int {  // static per problem: which 128-blocks of S (and of L) can be non-zero
       if (ctx.chol_plan_valid) return 0;
-      int rc = ctx.chol_plan.build(P.n_cams, (int)P.cam_first.size() == P.n_cams ? P.cam_first.data() : nullptr, s);
+      int rc;
+      if ((int)P.cam_first.size() == P.n_cams && P.n_cams > 0) {
+        std::vector<uint8_t> pattern;
+        int panels = 0;
+        block_pattern_from_envelope(P.n_cams, P.cam_first.data(), P.h_cam_new_of_old.empty() ? nullptr : P.h_cam_new_of_old.data(), pattern, &panels);
+        rc = ctx.chol_plan.build(P.n_cams, pattern.data(), panels, P.split_cams > 0 ? (6 * P.split_cams) / 128 : -1, s);
+      } else {
+        rc = ctx.chol_plan.build(P.n_cams, nullptr, 0, -1, s);
+      }
       if (rc) return rc;
       ctx.chol_plan_valid = true;
       return 0;
@@ -198,7 +206,7 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
         if (rc) return rc;
         size_t free_b = 0, total_b = 0;
         cudaMemGetInfo(&free_b, &total_b);
-        const size_t need_b = sizeof(double) * ((size_t)n6 * n6 + cholesky_workspace_doubles(n6) + (size_t)ctx.chol_plan.packed_doubles()) +
+        const size_t need_b = sizeof(double) * ((size_t)n6 * n6 + cholesky_workspace_doubles(n6) + (size_t)ctx.chol_plan.packed_doubles() + (size_t)ctx.chol_plan.tail_doubles()) +
                               sizeof(unsigned) * (size_t)std::max<long long>(P.total_pairs, 0);
         const size_t have_b = free_b + sizeof(double) * P.S_capacity;
         if (ctx.chol_plan.use && ctx.chol_plan.fill < 0.15 && have_b > need_b + ((size_t)4 << 30)) D.dense = true;
@@ -209,7 +217,7 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
       if (rc) return rc;
       // workspace after S: L11^-1 blocks + flags, then (multi-GPU) the packed envelope for the all-reduce
       const size_t packed = (ctx.comm.n_ranks > 1 && ctx.chol_plan.use) ? (size_t)ctx.chol_plan.packed_doubles() : 0;
-      const size_t need = (size_t)n6 * n6 + cholesky_workspace_doubles(n6) + packed;
+      const size_t need = (size_t)n6 * n6 + cholesky_workspace_doubles(n6) + (size_t)ctx.chol_plan.tail_doubles() + packed;
       if (P.S_capacity < need) {
         if (P.S) cudaFree(P.S);
         P.S = nullptr; P.S_capacity = 0;
@@ -224,6 +232,13 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
     }
   }
   S.linear_solver_used = (P.mode == 2 && !D.dense) ? HSFM_BA_LINEAR_PCG : HSFM_BA_LINEAR_DENSE_SCHUR;
+  S.cameras_reordered = P.cam_new_of_old ? 1 : 0;
+  if (P.mode == 2 && D.dense) {
+    const CholPlan& pl = ctx.chol_plan;
+    S.chol_panels = (n6 + 127) / 128;
+    S.chol_critical_panels = S.chol_panels;
+    if (!(o.dense_flags & 1) && pl.use && pl.split_a > 0) S.chol_critical_panels = std::max(pl.split_a, pl.split_t0 - pl.split_a) + (pl.panels - pl.split_t0);
+  }
 
   cudaEvent_t ev0, ev1;
   HSFM_CUDA(cudaEventCreate(&ev0));

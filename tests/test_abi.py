@@ -32,7 +32,7 @@ def test_exports_every_declared_symbol(lib):
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/hsfm_ba.h but not exported"
     assert set(names) == set(api.SYMBOLS), set(names) ^ set(api.SYMBOLS)
-    assert lib.hsfm_ba_abi_version() == 1
+    assert lib.hsfm_ba_abi_version() == 2
 
 
 def test_struct_layout_and_defaults(lib):
@@ -41,7 +41,7 @@ def test_struct_layout_and_defaults(lib):
 
     assert C.sizeof(Options) == 8 * 4 + 10 * 8
     assert C.sizeof(Iteration) == 7 * 8 + 4 * 4
-    assert C.sizeof(Summary) == 3 * 8 + 6 * 4 + 8 + 4 * 8 + 8 + 2 * 4 + 8 * 8
+    assert C.sizeof(Summary) == 3 * 8 + 6 * 4 + 8 + 4 * 8 + 8 + 2 * 4 + 8 * 8 + 8 + 4 * 4
     o = api.default_options()
     # ceres::Solver::Options defaults; the reference overrides only the linear solver
     assert (o.max_num_iterations, o.max_consecutive_invalid_steps, o.jacobi_scaling) == (50, 5, 1)
