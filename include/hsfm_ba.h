@@ -267,6 +267,28 @@ int64_t hsfm_ba_problem_algorithmic_bytes(hsfm_ba_ctx* ctx, const char* kernel);
  * events on the context's stream; returns average ms per launch in *ms. */
 int hsfm_ba_problem_time_kernel(hsfm_ba_ctx* ctx, const char* kernel, int reps, double* ms);
 
+/* ---- allocation-free entry point ---------------------------------------------------------------- */
+
+/* No counterpart in the reference; added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * Reprojection cost 1/2 sum |r|^2 of n_obs observations at the given parameters — the candidate-cost evaluation of
+ * the trust-region loop (functor of CTracker.cpp:585-604, residuals only) — with every input and the output in
+ * DEVICE memory owned by the caller:
+ *   d_obs_xy [n_obs][2], d_cam_idx [n_obs], d_pt_idx [n_obs], d_K9 [n_cams][9], d_cam_rt [n_cams][6], d_pts [n_pts][3],
+ *   d_cost   [1] (written).
+ * The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine): its scratch memory, one
+ * partial sum per 256 observations, is a static device array of HSFM_BA_NOALLOC_MAX_OBS / 256 doubles (128 KB) that
+ * every GPU using the library holds until exit.  n_obs > HSFM_BA_NOALLOC_MAX_OBS returns HSFM_BA_ERR_UNSUPPORTED and
+ * launches nothing.  The work is enqueued on the context's stream (hsfm_ba_set_stream) and NOT waited for: d_cost is
+ * valid once that stream has been synchronised.  An out-of-range camera / point index makes the cost NaN.
+ * All calls on one GPU share the scratch array (it keeps the last call's contents; nothing in it has to start at
+ * zero): calls that overlap on the GPU — other streams or other contexts of the same device — race on it. */
+#define HSFM_BA_NOALLOC_MAX_OBS 4194304 /* 2^22 observations */
+int hsfm_ba_cost_noalloc(hsfm_ba_ctx* ctx, int64_t n_obs, const double* d_obs_xy, const int32_t* d_cam_idx,
+                         const int32_t* d_pt_idx, int32_t n_cams, const double* d_K9, const double* d_cam_rt,
+                         int64_t n_pts, const double* d_pts, double* d_cost);
+
 #ifdef __cplusplus
 }
 #endif

@@ -56,7 +56,12 @@ SYMBOLS = {
     "hsfm_ba_problem_download": (C.c_int, [C.c_void_p, _dp, _dp]),
     "hsfm_ba_problem_algorithmic_bytes": (C.c_int64, [C.c_void_p, C.c_char_p]),
     "hsfm_ba_problem_time_kernel": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, _dp]),
+    # device pointers (the caller's buffers), passed as integers
+    "hsfm_ba_cost_noalloc": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                       C.c_int64, C.c_void_p, C.c_void_p]),
 }
+
+NOALLOC_MAX_OBS = 1 << 22  # HSFM_BA_NOALLOC_MAX_OBS
 
 _lib = None
 
@@ -307,6 +312,13 @@ class Context:
         if rc:
             raise BAError(rc, "hsfm_ba_problem_download")
         return cam, pts
+
+    def cost_noalloc(self, n_obs, d_obs, d_cam_idx, d_pt_idx, n_cams, d_K9, d_cam_rt, n_pts, d_pts, d_cost):
+        """hsfm_ba_cost_noalloc: all d_* are DEVICE addresses (ints) of caller-owned buffers; allocates nothing; the
+        result lands in d_cost once the context's stream has been synchronised."""
+        rc = self.lib.hsfm_ba_cost_noalloc(self.h, n_obs, d_obs, d_cam_idx, d_pt_idx, n_cams, d_K9, d_cam_rt, n_pts, d_pts, d_cost)
+        if rc:
+            raise BAError(rc, "hsfm_ba_cost_noalloc")
 
     def algorithmic_bytes(self, kernel: str) -> int:
         return int(self.lib.hsfm_ba_problem_algorithmic_bytes(self.h, kernel.encode()))

@@ -53,7 +53,9 @@ const char* hsfm_ba_error_string(int code) {
     case HSFM_BA_ERR_ARG: return "invalid argument";
     case HSFM_BA_ERR_NO_DEVICE: return "no usable sm_100 CUDA device (this library has no CPU path)";
     case HSFM_BA_ERR_STATE: return "invalid call order / no resident problem";
-    case HSFM_BA_ERR_UNSUPPORTED: return "unsupported problem (a point with more than 256 observations, or sizes beyond int32)";
+    case HSFM_BA_ERR_UNSUPPORTED:
+      return "unsupported problem (a point with more than 256 observations, sizes beyond int32, or more observations than "
+             "HSFM_BA_NOALLOC_MAX_OBS in hsfm_ba_cost_noalloc)";
     case HSFM_BA_ERR_NOMEM: return "out of device memory";
     case HSFM_BA_ERR_COMM: return "NCCL unavailable or communicator initialisation failed";
     default: break;
@@ -101,6 +103,7 @@ int hsfm_ba_create(hsfm_ba_ctx** out, int device_id) {
   { int rc2 = h->c.chol_aux.init(); if (rc2) { cudaStreamDestroy(h->c.own_stream); delete h; return rc2; } }
   { int rc2 = init_kernel_attributes(); if (rc2) { h->c.chol_aux.destroy(); cudaStreamDestroy(h->c.own_stream); delete h; return rc2; } }
   h->c.prob.n_sm = h->c.chol_aux.n_sm;
+  { int rc2 = noalloc_setup(device_id); if (rc2) { h->c.chol_aux.destroy(); cudaStreamDestroy(h->c.own_stream); delete h; return rc2; } }
   *out = h;
   return 0;
 }
@@ -396,6 +399,17 @@ int hsfm_ba_solve_ptr(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double* obs
     for (int64_t p = 0; p < n_pts; ++p)
       for (int k = 0; k < 3; ++k) uniq[(size_t)p][k] = pts[3 * (size_t)p + k];
   return 0;
+}
+
+// ---- allocation-free entry point (ba_noalloc.cu) ---------------------------------------------------
+int hsfm_ba_cost_noalloc(hsfm_ba_ctx* h, int64_t n_obs, const double* d_obs_xy, const int32_t* d_cam_idx, const int32_t* d_pt_idx,
+                         int32_t n_cams, const double* d_K9, const double* d_cam_rt, int64_t n_pts, const double* d_pts, double* d_cost) {
+  if (!h || n_obs < 0 || n_cams < 0 || n_pts < 0 || !d_cost) return HSFM_BA_ERR_ARG;
+  if (n_obs > 0 && (!d_obs_xy || !d_cam_idx || !d_pt_idx || !d_K9 || !d_cam_rt || !d_pts)) return HSFM_BA_ERR_ARG;
+  if (n_obs > HSFM_BA_NOALLOC_MAX_OBS || n_pts >= ((int64_t)1 << 31)) return HSFM_BA_ERR_UNSUPPORTED;  // beyond the static scratch array
+  HSFM_CUDA(cudaSetDevice(h->c.device));
+  return launch_cost_noalloc(h->c.device, (int)n_obs, d_obs_xy, d_cam_idx, d_pt_idx, n_cams, d_K9, d_cam_rt, (int)n_pts, d_pts, d_cost,
+                             h->c.stream);
 }
 
 // ---- parity taps --------------------------------------------------------------------------------

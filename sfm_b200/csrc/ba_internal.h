@@ -252,6 +252,11 @@ void launch_structure_zero(const CholPlan& pl, double* S, cudaStream_t s);  // z
 void launch_spd_fill(double* A, int n, double* b /*null = matrix only*/, cudaStream_t s);  // bench tap: synthetic SPD matrix, b = A 1
 void launch_spd_err(int n, const double* x, double* err, cudaStream_t s);                 // max |x - 1|
 
+// ---- allocation-free cost evaluation (ba_noalloc.cu) ----
+int noalloc_setup(int device);  // once per device, with that device current: device address of the static scratch array
+int launch_cost_noalloc(int device, int n_obs, const double* obs_xy, const int* cam_idx, const int* pt_idx, int n_cams, const double* K9,
+                        const double* cam_rt, int n_pts, const double* pts, double* cost, cudaStream_t s);
+
 // ---- LM driver (ba_solver.cu) ----
 struct Ctx {
   int device = 0;
