@@ -197,6 +197,18 @@ int hsfm_ba_solve_packed(hsfm_ba_ctx* ctx, int mode, int64_t n_obs, const double
                          const double* K9, const double* dist, double* cam_rt, int64_t n_pts,
                          double* pts, const hsfm_ba_options* opts, hsfm_ba_summary* summary);
 
+/* Packed form with CONSTANT parameter blocks (gauge fixing / windowed BA; the reference intends a
+ * covisibility-limited camera set with the oldest keyframe fixed — CMap.cpp:80-112,317-330, CSfM.cpp:123,254 — and
+ * would express it with ceres::Problem::SetParameterBlockConstant on R[c], t[c] / pts3D[i]).
+ *   cam_fixed [n_cams], pt_fixed [n_pts]: non-zero = the camera (both its R and t block) / the point keeps its value
+ *   bit for bit; either may be NULL (= none).  Residuals whose blocks are all constant leave the reduced program;
+ *   their cost is reported as summary->fixed_cost and included in initial_cost / final_cost, as Ceres does. */
+int hsfm_ba_solve_packed_ex(hsfm_ba_ctx* ctx, int mode, int64_t n_obs, const double* obs_xy,
+                            const int32_t* cam_idx, const int32_t* pt_idx, int32_t n_cams, const double* K9,
+                            const double* dist, double* cam_rt, int64_t n_pts, double* pts,
+                            const uint8_t* cam_fixed, const uint8_t* pt_fixed, const hsfm_ba_options* opts,
+                            hsfm_ba_summary* summary);
+
 /* ---- parity taps on HOST buffers ---------------------------------------------------------- */
 
 /* Residuals and Jacobians exactly as ceres::AutoDiffCostFunction<…,2,3,3,3> lays them out:
@@ -245,6 +257,9 @@ int hsfm_ba_problem_upload(hsfm_ba_ctx* ctx, int mode, int64_t n_obs, const doub
                            const int32_t* cam_idx, const int32_t* pt_idx, int32_t n_cams,
                            const double* K9, const double* dist, const double* cam_rt,
                            int64_t n_pts, const double* pts);
+/* Constant-block masks of the resident problem (see hsfm_ba_solve_packed_ex), caller's camera / point order; both NULL
+ * clears them.  They stay in force for every later solve of this problem (a new upload clears them). */
+int hsfm_ba_problem_set_constant(hsfm_ba_ctx* ctx, const uint8_t* cam_fixed, const uint8_t* pt_fixed);
 /* Restore the uploaded initial parameters on the device (no host traffic). */
 int hsfm_ba_problem_reset(hsfm_ba_ctx* ctx);
 /* LM solve on the resident problem; parameters stay on the device. */

@@ -26,6 +26,7 @@ LIB_PATH = os.environ.get("HSFM_BA_LIB", os.path.join(_HERE, "libhsfm_ba.so"))  
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int32)
 _pp = C.POINTER(C.c_void_p)
+_bp = C.POINTER(C.c_uint8)
 
 # name -> (restype, argtypes): every symbol include/hsfm_ba.h declares
 SYMBOLS = {
@@ -43,6 +44,9 @@ SYMBOLS = {
                                     C.POINTER(Options), C.POINTER(Summary)]),
     "hsfm_ba_solve_packed": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64,
                                        _dp, C.POINTER(Options), C.POINTER(Summary)]),
+    "hsfm_ba_solve_packed_ex": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64,
+                                          _dp, _bp, _bp, C.POINTER(Options), C.POINTER(Summary)]),
+    "hsfm_ba_problem_set_constant": (C.c_int, [C.c_void_p, _bp, _bp]),
     "hsfm_ba_eval": (C.c_int, [C.c_void_p, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp, _dp, _dp, _dp]),
     "hsfm_ba_schur": (C.c_int, [C.c_void_p, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp,
                                 C.POINTER(Options), C.c_double, _dp, _dp, _dp, _dp, _dp, _dp, _dp]),
@@ -98,6 +102,15 @@ def _d(a):
 
 def _i(a):
     return a.ctypes.data_as(_ip)
+
+
+def _mask(a, n):
+    if a is None:
+        return None, None
+    a = np.ascontiguousarray(np.asarray(a).astype(bool), dtype=np.uint8)
+    if a.shape != (n,):
+        raise ValueError("mask must have one entry per block")
+    return a, a.ctypes.data_as(_bp)
 
 
 def _f64(a, shape=None):
@@ -205,15 +218,17 @@ class Context:
             raise BAError(rc, "hsfm_ba_comm_init")
 
     # -- one-shot calls on host buffers --
-    def solve_packed(self, prob, mode=STRUCT_AND_POSE, opts=None, trace_capacity=64, inplace=False):
+    def solve_packed(self, prob, mode=STRUCT_AND_POSE, opts=None, trace_capacity=64, inplace=False, cam_fixed=None, pt_fixed=None):
         """Solves a sfm_b200.synth.Problem-like object; returns (cam, pts, summary dict).  ``inplace=True`` is the
         reference's own contract (CTracker.cpp:670-702 updates the caller's pose/point storage): prob.cam / prob.pts
         are read as the initial guess and overwritten with the result, no copies on the Python side."""
         cam, pts = (prob.cam, prob.pts) if inplace else (prob.cam.copy(), prob.pts.copy())
         box = _SummaryBox(trace_capacity)
-        rc = self.lib.hsfm_ba_solve_packed(self.h, mode, prob.n_obs, _d(prob.obs), _i(prob.cam_idx), _i(prob.pt_idx), prob.n_cams,
-                                           _d(prob.K), _d(prob.dist), _d(cam), prob.n_pts, _d(pts),
-                                           C.byref(opts) if opts is not None else None, C.byref(box.s))
+        cf, cfp = _mask(cam_fixed, prob.n_cams)
+        pf, pfp = _mask(pt_fixed, prob.n_pts)
+        rc = self.lib.hsfm_ba_solve_packed_ex(self.h, mode, prob.n_obs, _d(prob.obs), _i(prob.cam_idx), _i(prob.pt_idx), prob.n_cams,
+                                              _d(prob.K), _d(prob.dist), _d(cam), prob.n_pts, _d(pts), cfp, pfp,
+                                              C.byref(opts) if opts is not None else None, C.byref(box.s))
         if rc:
             raise BAError(rc, "hsfm_ba_solve_packed")
         return cam, pts, box.as_dict()
@@ -274,6 +289,14 @@ class Context:
                                              _d(prob.K), _d(prob.dist), _d(prob.cam), prob.n_pts, _d(prob.pts))
         if rc:
             raise BAError(rc, "hsfm_ba_problem_upload")
+
+    def set_constant(self, cam_fixed=None, pt_fixed=None):
+        """Hold cameras / points of the resident problem constant (boolean masks, caller order); None, None clears."""
+        cf, cfp = _mask(cam_fixed, self._keep.n_cams)
+        pf, pfp = _mask(pt_fixed, self._keep.n_pts)
+        rc = self.lib.hsfm_ba_problem_set_constant(self.h, cfp, pfp)
+        if rc:
+            raise BAError(rc, "hsfm_ba_problem_set_constant")
 
     def reset(self):
         rc = self.lib.hsfm_ba_problem_reset(self.h)

@@ -197,6 +197,25 @@ int hsfm_ba_problem_upload(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double
   return 0;
 }
 
+int hsfm_ba_problem_set_constant(hsfm_ba_ctx* h, const uint8_t* cam_fixed, const uint8_t* pt_fixed) {
+  if (!h) return HSFM_BA_ERR_ARG;
+  if (!h->c.has_problem) return HSFM_BA_ERR_STATE;
+  Problem& P = h->c.prob;
+  cudaStream_t s = h->c.stream;
+  HSFM_CUDA(cudaSetDevice(h->c.device));
+  unsigned char* stage = nullptr;
+  const size_t nc = (size_t)P.n_cams, np = (size_t)P.n_pts;
+  if (cam_fixed || pt_fixed) {
+    if (cudaMalloc(&stage, std::max<size_t>(1, nc + np)) != cudaSuccess) { cudaGetLastError(); return HSFM_BA_ERR_NOMEM; }
+    if (cam_fixed && nc) cudaMemcpyAsync(stage, cam_fixed, nc, cudaMemcpyHostToDevice, s);
+    if (pt_fixed && np) cudaMemcpyAsync(stage + nc, pt_fixed, np, cudaMemcpyHostToDevice, s);
+  }
+  launch_set_fixed(P, cam_fixed ? stage : nullptr, pt_fixed ? stage + nc : nullptr, s);
+  const cudaError_t e = cudaStreamSynchronize(s);
+  if (stage) cudaFree(stage);
+  return e == cudaSuccess ? 0 : 1000 + (int)e;
+}
+
 int hsfm_ba_problem_reset(hsfm_ba_ctx* h) {
   if (!h || !h->c.has_problem) return HSFM_BA_ERR_STATE;
   Problem& P = h->c.prob;
@@ -346,12 +365,22 @@ int hsfm_ba_problem_time_kernel(hsfm_ba_ctx* h, const char* kernel, int reps, do
 int hsfm_ba_solve_packed(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
                          int32_t n_cams, const double* K9, const double* dist, double* cam_rt, int64_t n_pts, double* pts,
                          const hsfm_ba_options* opts, hsfm_ba_summary* summary) {
+  return hsfm_ba_solve_packed_ex(h, mode, n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, dist, cam_rt, n_pts, pts, nullptr, nullptr, opts, summary);
+}
+
+int hsfm_ba_solve_packed_ex(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
+                            int32_t n_cams, const double* K9, const double* dist, double* cam_rt, int64_t n_pts, double* pts,
+                            const uint8_t* cam_fixed, const uint8_t* pt_fixed, const hsfm_ba_options* opts, hsfm_ba_summary* summary) {
   if (!h) return HSFM_BA_ERR_ARG;
   if (!valid_mode(mode)) return HSFM_BA_OK;  // CTracker.cpp:692-693: nothing is added, Solve() is a no-op
   hsfm_ba_options def;
   if (!opts) { hsfm_ba_default_options(&def); opts = &def; }
   int rc = hsfm_ba_problem_upload(h, mode, n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, dist, cam_rt, n_pts, pts);
   if (rc) return rc;
+  if (cam_fixed || pt_fixed) {
+    rc = hsfm_ba_problem_set_constant(h, cam_fixed, pt_fixed);
+    if (rc) return rc;
+  }
   rc = hsfm_ba_problem_solve(h, opts, summary);
   if (rc) return rc;
   const double t0 = now_ms();

@@ -169,6 +169,24 @@ void launch_rows_to_caller(Problem& P, int w, const double* internal_order, doub
   P.launches++;
 }
 
+__global__ void gather_bytes_kernel(int n, const int* __restrict__ row_of, const unsigned char* __restrict__ src, unsigned char* __restrict__ dst) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) dst[k] = src[row_of ? row_of[k] : k] ? 1 : 0;
+}
+// Constant-block masks from the caller's camera / point order (device staging buffers) into the internal order.
+void launch_set_fixed(Problem& P, const unsigned char* cam_caller, const unsigned char* pt_caller, cudaStream_t s) {
+  if (P.n_cams > 0) {
+    if (cam_caller) gather_bytes_kernel<<<cdiv(P.n_cams, 256), 256, 0, s>>>(P.n_cams, P.cam_old_of_new, cam_caller, P.cam_fixed);
+    else cudaMemsetAsync(P.cam_fixed, 0, (size_t)P.n_cams, s);
+  }
+  if (P.n_pts > 0) {
+    if (pt_caller) gather_bytes_kernel<<<cdiv(P.n_pts, 256), 256, 0, s>>>(P.n_pts, P.pt_old_of_new, pt_caller, P.pt_fixed);
+    else cudaMemsetAsync(P.pt_fixed, 0, (size_t)P.n_pts, s);
+  }
+  P.launches += 2;
+  P.has_fixed = cam_caller || pt_caller;
+}
+
 void launch_cam_rows_to_caller(Problem& P, int w, const double* internal_order, double* caller_order, cudaStream_t s) {
   if (P.n_cams == 0) return;
   gather_rows_kernel<<<cdivz((size_t)P.n_cams * w, 256), 256, 0, s>>>(P.n_cams, w, P.cam_new_of_old, internal_order, caller_order);
@@ -441,6 +459,8 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   // ---- observation counts per camera over ALL ranks (cameras without observations are not
   //      parameter blocks of the reference problem: CTracker.cpp:676-696 adds blocks per residual) ----
   ALLOC(P.cam_nobs, (size_t)n_cams);
+  ALLOC(P.cam_fixed, (size_t)n_cams); ALLOC(P.pt_fixed, (size_t)n_pts);
+  P.has_fixed = false;
   diff_kernel<<<cdiv(std::max(1, (int)n_cams), 256), 256, 0, s>>>(n_cams, cam_start, P.cam_nobs);
   if (comm.n_ranks > 1) {
     int rc = comm.allreduce_sum_i32(P.cam_nobs, (size_t)n_cams, s);

@@ -89,6 +89,9 @@ struct Problem {
   CamRow *rows_x = nullptr, *rows_c = nullptr;      // prepared camera tables for x / candidate
   double *scale_c = nullptr, *scale_p = nullptr;    // Jacobi scaling [6 n_cams], [3 n_pts]
   int *cam_nobs = nullptr, *pt_nobs_mask = nullptr; // global observation count per camera (all ranks)
+  // constant parameter blocks (hsfm_ba_problem_set_constant), internal camera / point order
+  unsigned char *cam_fixed = nullptr, *pt_fixed = nullptr;  // [n_cams], [n_pts]; valid when has_fixed
+  bool has_fixed = false;
   // normal-equation blocks
   double *Hpp = nullptr, *gp = nullptr, *Hpp_inv = nullptr, *zp = nullptr;  // [n_pts][6],[3],[6],[3]
   double *Hcc = nullptr, *gc = nullptr;             // [n_cams][21] upper-tri row-major, [n_cams][6]
@@ -121,7 +124,7 @@ struct Problem {
 enum PartSlot { P_COST = 0, P_MCC, P_DN_P, P_XN_P, P_DN_C, P_XN_C, P_GMAX_C, P_GMAX_P, PART_SLOTS };
 // slots 0..4 are per-rank partial sums (all-reduced with SUM under a communicator), S_GMAX_P with MAX;
 // the camera-side slots are computed from replicated data and are identical on every rank.
-enum ScalSlot { S_COST = 0, S_MCC, S_DN_P, S_XN_P, S_CAND_COST, S_GMAX_P, S_DN_C, S_XN_C, S_GMAX_C, S_PCG_RHO0, S_PCG_RHO, SCAL_SLOTS = 32 };
+enum ScalSlot { S_COST = 0, S_MCC, S_DN_P, S_XN_P, S_CAND_COST, S_GMAX_P, S_DN_C, S_XN_C, S_GMAX_C, S_PCG_RHO0, S_PCG_RHO, S_FIXED_COST, SCAL_SLOTS = 32 };
 enum FlagSlot { F_INVALID = 0, F_PCG_DONE = 1, F_PCG_ITERS = 2, F_CHOL_FAIL = 3, FLAG_SLOTS = 8 };
 
 // ---- communicator (NCCL, loaded at run time; ba_comm.cu) ----
@@ -141,6 +144,7 @@ int comm_init(Comm& c, const void* id128, int rank, int n_ranks);
 int build_problem(Problem& P, int mode, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
                   int32_t n_cams, const double* K9, const double* dist, const double* cam_rt, int64_t n_pts, const double* pts,
                   Comm& comm, cudaStream_t s, double* setup_ms, double* h2d_ms, bool natural_order = false);
+void launch_set_fixed(Problem& P, const unsigned char* cam_caller, const unsigned char* pt_caller, cudaStream_t s);  // device staging -> internal order
 // camera-indexed rows between the caller's camera order and the internal one
 void launch_cam_rows_to_caller(Problem& P, int w, const double* internal_order, double* caller_order, cudaStream_t s);
 
@@ -156,7 +160,8 @@ void launch_rj(Problem& P, const CamRow* rows, const double* pts, const double* 
 void launch_cost(Problem& P, const CamRow* rows, const double* pts, int part_slot, cudaStream_t s);
 // camera-major passes: mode 0 → Hcc,gc ; mode 1 → E (needs Hpp_inv)
 void launch_cam_major(Problem& P, const CamRow* rows, const double* pts, const double* scale_p, int what, cudaStream_t s);
-void launch_jacobi_scale(Problem& P, bool enabled, cudaStream_t s);  // from Hcc / Hpp diagonals (unscaled pass)
+void launch_jacobi_scale(Problem& P, bool enabled, cudaStream_t s);  // from Hcc / Hpp diagonals (unscaled pass); 0 for constant blocks
+void launch_fixed_cost(Problem& P, const CamRow* rows, const double* pts, cudaStream_t s);  // -> scal[S_FIXED_COST]
 void launch_point_invert(Problem& P, double radius, double min_diag, double max_diag, cudaStream_t s);
 void launch_cam_diag(Problem& P, double radius, double min_diag, double max_diag, cudaStream_t s);  // Dc2
 void launch_precond_invert(Problem& P, bool with_E, cudaStream_t s);  // Minv = (Hcc + Dc2 - E)^-1

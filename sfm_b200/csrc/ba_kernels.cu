@@ -540,19 +540,49 @@ __global__ void cam_reduce_kernel(int n_cams, int nv, const int* __restrict__ ca
   else out6[(size_t)c * 6 + (k - 21)] = s;
 }
 
+// A CONSTANT parameter block (hsfm_ba_problem_set_constant; what ceres::Problem::SetParameterBlockConstant does) gets
+// column scale 0: its Jacobian columns, gradient, normal-equation blocks and step vanish, the candidate keeps the
+// block's value bit for bit, and "scale == 0" is how every other kernel recognises such a block (a free block's
+// scale 1/(1+|col|) is never 0).
 __global__ void jacobi_scale_kernel(int n_cams, int n_pts, const double* __restrict__ Hcc, const double* __restrict__ Hpp,
-                                    double* __restrict__ scale_c, double* __restrict__ scale_p, int enabled) {
+                                    double* __restrict__ scale_c, double* __restrict__ scale_p, int enabled,
+                                    const unsigned char* __restrict__ cam_fixed, const unsigned char* __restrict__ pt_fixed) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int nc6 = 6 * n_cams;
   if (idx < nc6) {
     const int c = idx / 6, a = idx % 6;
-    scale_c[idx] = enabled ? 1.0 / (1.0 + sqrt(Hcc[(size_t)c * 21 + tri6(a, a)])) : 1.0;
+    double v = enabled ? 1.0 / (1.0 + sqrt(Hcc[(size_t)c * 21 + tri6(a, a)])) : 1.0;
+    if (cam_fixed && cam_fixed[c]) v = 0.0;
+    scale_c[idx] = v;
   } else if (idx < nc6 + 3 * n_pts) {
     const int j = idx - nc6;
     const int p = j / 3, a = j % 3;
     const int diag = (a == 0) ? 0 : (a == 1 ? 3 : 5);
-    scale_p[j] = enabled ? 1.0 / (1.0 + sqrt(Hpp[(size_t)p * 6 + diag])) : 1.0;
+    double v = enabled ? 1.0 / (1.0 + sqrt(Hpp[(size_t)p * 6 + diag])) : 1.0;
+    if (pt_fixed && pt_fixed[p]) v = 0.0;
+    scale_p[j] = v;
   }
+}
+
+// 1/2 sum |r|^2 over the observations whose parameter blocks are ALL constant (by mask or by mode): such residuals
+// are not part of the reduced program (ceres Summary::fixed_cost) and never change during a solve.  Once per solve.
+__global__ void __launch_bounds__(TILE) fixed_cost_kernel(Dev d, const CamRow* __restrict__ rows, const double* __restrict__ pts,
+                                                           const unsigned char* __restrict__ cam_fixed, const unsigned char* __restrict__ pt_fixed,
+                                                           int cams_free, int pts_free, double* __restrict__ part) {
+  __shared__ double sm[8];
+  const int i = blockIdx.x * TILE + threadIdx.x;
+  double e = 0.0;
+  if (i < d.n_obs) {
+    const int c = __ldg(d.cam + i), p = __ldg(d.pt + i);
+    if ((!cams_free || cam_fixed[c]) && (!pts_free || pt_fixed[p])) {
+      double r0, r1;
+      const double2 o = __ldg(d.obs + i);
+      reproject_r(load_row(rows, c), pts[3 * (size_t)p], pts[3 * (size_t)p + 1], pts[3 * (size_t)p + 2], o.x, o.y, r0, r1);
+      e = r0 * r0 + r1 * r1;
+    }
+  }
+  const double cs = block_sum_256(e, sm);
+  if (threadIdx.x == 0) part[blockIdx.x] = cs;
 }
 
 // Per attempt: Hpp_inv = (Hpp + D_p^2)^-1 with D = sqrt(clamp(diag)/radius) (a7), z_p = Hpp_inv g_p.
@@ -727,7 +757,7 @@ __global__ void __launch_bounds__(TILE, MODE == 0 ? 8 : 4) schur_pass_kernel(Dev
         pts_c[q] = c0; pts_c[q + 1] = c1; pts_c[q + 2] = c2;
         const double e0 = x0 - c0, e1 = x1 - c1, e2 = x2 - c2;
         dn = e0 * e0 + e1 * e1 + e2 * e2;
-        xn = x0 * x0 + x1 * x1 + x2 * x2;
+        if (scale_p[q] != 0.0) xn = x0 * x0 + x1 * x1 + x2 * x2;  // |x| runs over the free blocks only
       }
       w0 = y0; w1 = y1; w2 = y2;
     }
@@ -783,7 +813,7 @@ __global__ void __launch_bounds__(256) cam_step_kernel(int n6, const double* __r
       cv = xv + (-y) * scale_c[k];
       const double e = xv - cv;
       dn = e * e;
-      xn = xv * xv;
+      if (scale_c[k] != 0.0) xn = xv * xv;  // |x| runs over the free blocks only
     }
     cand[k] = cv;
   }
@@ -813,7 +843,7 @@ __global__ void __launch_bounds__(256) grad_norm_kernel(int n, const double* __r
   __shared__ double sm[8];
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   double v = 0.0;
-  if (k < n) v = fabs(g[k] / scale[k]);
+  if (k < n && scale[k] != 0.0) v = fabs(g[k] / scale[k]);  // constant blocks (scale 0) have no gradient
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) v = fmax(v, __shfl_down_sync(FULL, v, d));
   if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
@@ -1374,8 +1404,18 @@ void launch_cam_major(Problem& P, const CamRow* rows, const double* pts, const d
 
 void launch_jacobi_scale(Problem& P, bool enabled, cudaStream_t s) {
   const int n = 6 * P.n_cams + 3 * P.n_pts;
-  jacobi_scale_kernel<<<cdiv(n, 256), 256, 0, s>>>(P.n_cams, P.n_pts, P.Hcc, P.Hpp, P.scale_c, P.scale_p, enabled ? 1 : 0);
+  jacobi_scale_kernel<<<cdiv(n, 256), 256, 0, s>>>(P.n_cams, P.n_pts, P.Hcc, P.Hpp, P.scale_c, P.scale_p, enabled ? 1 : 0,
+                                                   P.has_fixed ? P.cam_fixed : nullptr, P.has_fixed ? P.pt_fixed : nullptr);
   P.launches++;
+}
+
+void launch_fixed_cost(Problem& P, const CamRow* rows, const double* pts, cudaStream_t s) {
+  if (P.n_obs == 0) return;
+  const int g = cdiv(P.n_obs, TILE);  // <= n_tiles <= part_stride (tiles hold at most TILE observations)
+  fixed_cost_kernel<<<g, TILE, 0, s>>>(P.d, rows, pts, P.cam_fixed, P.pt_fixed, P.mode != 0 ? 1 : 0, P.mode != 1 ? 1 : 0,
+                                       P.part + (size_t)P_GMAX_C * P.part_stride);
+  P.launches++;
+  add_task(P, P_GMAX_C, g, S_FIXED_COST, 2);
 }
 
 void launch_point_invert(Problem& P, double radius, double min_diag, double max_diag, cudaStream_t s) {

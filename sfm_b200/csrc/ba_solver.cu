@@ -246,6 +246,12 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
   HSFM_CUDA(cudaEventRecord(ev0, s));
 
   D.compute_scaling();
+  if (P.has_fixed) {
+    // residuals whose blocks are all constant: not part of the reduced program, constant over the solve
+    launch_fixed_cost(P, P.rows_x, P.pts_x, s);
+    launch_finalize_scalars(P, s);  // now: the partial-sum slot is reused by the gradient norm
+    if (D.multi()) D.chk(ctx.comm.allreduce_sum(P.scal + S_FIXED_COST, 1, s));
+  }
   D.linearize();
   if (D.rc) return D.rc;
   { int r = D.read_back(); if (r) return r; }
@@ -255,9 +261,12 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
     if (D.pts_free) g = std::max(g, P.scal_host[S_GMAX_P]);
     return g;
   };
-  double x_cost = P.scal_host[S_COST];
+  // the costs the trust-region loop sees are those of the reduced program (ceres: fixed_cost is added in the summary only)
+  const double fixed_cost = P.has_fixed ? P.scal_host[S_FIXED_COST] : 0.0;
+  double x_cost = P.scal_host[S_COST] - fixed_cost;
   double gmax = gmax_of();
-  S.initial_cost = x_cost;
+  S.initial_cost = x_cost + fixed_cost;
+  S.fixed_cost = fixed_cost;
   double radius = o.initial_trust_region_radius, decrease_factor = 2.0;
   int invalid_run = 0, num_success = 0, total_lin = 0, iter = 0;
   int term = HSFM_BA_NO_CONVERGENCE;
@@ -282,7 +291,7 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
       total_lin += lin;
       its.linear_iterations = lin;
       const double mcc = P.scal_host[S_MCC];
-      const double cand_cost_raw = P.scal_host[S_CAND_COST];
+      const double cand_cost_raw = P.scal_host[S_CAND_COST] - fixed_cost;
       const double dn2 = (D.cams_free ? P.scal_host[S_DN_C] : 0.0) + (D.pts_free ? P.scal_host[S_DN_P] : 0.0);
       const double xn2 = (D.cams_free ? P.scal_host[S_XN_C] : 0.0) + (D.pts_free ? P.scal_host[S_XN_P] : 0.0);
       const bool bad = P.flags_host[F_INVALID] != 0 || P.flags_host[F_CHOL_FAIL] != 0 || !std::isfinite(mcc) || !(mcc > 0.0) ||
@@ -318,7 +327,7 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
         D.linearize();
         if (D.rc) return D.rc;
         { int r = D.read_back(); if (r) return r; }
-        x_cost = P.scal_host[S_COST];
+        x_cost = P.scal_host[S_COST] - fixed_cost;
         gmax = gmax_of();
         ++num_success;
         its.step_is_successful = 1;
@@ -351,7 +360,7 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
   cudaEventDestroy(ev0);
   cudaEventDestroy(ev1);
   S.solve_ms = ms;
-  S.final_cost = x_cost;
+  S.final_cost = x_cost + fixed_cost;
   int64_t n_obs_total = P.n_obs;
   S.rms_px = 0.0;  // filled by the caller when the global observation count is known
   (void)n_obs_total;

@@ -92,3 +92,76 @@ def test_final_shape_three_iterations_match_oracle_table(ctx):
     for k, it in enumerate(s["trace"]):
         assert it["cost"] == pytest.approx(float(want[k]), rel=TOL_COST), k
         assert it["step_is_successful"] == int(g["c5_successful"][k])
+
+
+def _window_masks(p, free_cams):
+    """Windowed BA: the cameras of the window are free, every other camera is constant; a point is free when a free
+    camera observes it (the reference's intent: CMap.cpp:80-112, 317-330; CSfM.cpp:123, 254)."""
+    cf = np.ones(p.n_cams, np.uint8)
+    cf[free_cams] = 0
+    seen = np.zeros(p.n_pts, bool)
+    seen[p.pt_idx[cf[p.cam_idx] == 0]] = True
+    return cf, (~seen).astype(np.uint8)
+
+
+@pytest.mark.parametrize("case", ["gauge-c1", "window-10", "gauge-pcg", "window-pose-only"])
+def test_constant_blocks_match_oracle(ctx, case):
+    """SURVEY.md 8f row 2: constant parameter blocks (what ceres::Problem::SetParameterBlockConstant does).  Same LM
+    trajectory as the oracle with the same masks; constant blocks come back bit for bit; residuals between constant
+    blocks are reported as fixed_cost."""
+    mode, linear = api.STRUCT_AND_POSE, api.LINEAR_DENSE_SCHUR
+    if case == "gauge-c1":
+        p = synth.make_config("c1")
+        cf, pf = np.zeros(p.n_cams, np.uint8), None
+        cf[0] = 1                                           # the oldest keyframe fixes the gauge
+    elif case == "gauge-pcg":
+        p = synth.make_ring(12, 500, 7, seed=31)
+        cf, pf = np.zeros(p.n_cams, np.uint8), np.zeros(p.n_pts, np.uint8)
+        cf[0] = 1; pf[::7] = 1
+        linear = api.LINEAR_PCG
+    else:
+        p = _trajectory(n_cams=60, window=12, n_pts=1500, seed=8, closure=False)
+        cf, pf = _window_masks(p, np.arange(50, 60))        # the last ten keyframes
+        if case == "window-pose-only":
+            mode = api.POSE_ONLY
+    o = api.default_options(linear_solver=linear, pcg_max_iterations=3000)
+    cam, pts, s = ctx.solve_packed(p, mode=mode, opts=o, cam_fixed=cf, pt_fixed=pf)
+    cam0, pts0, so, tro = po.solve(p, mode=mode, opts=po.default_options(num_threads=4), cam_fixed=cf, pt_fixed=pf)
+    assert s["num_iterations"] == so["num_iterations"] and s["num_successful_steps"] == so["num_successful_steps"]
+    assert s["termination_type"] == so["termination_type"]
+    assert s["final_cost"] == pytest.approx(so["final_cost"], rel=TOL_COST)
+    assert s["initial_cost"] == pytest.approx(so["initial_cost"], rel=1e-12)
+    assert s["fixed_cost"] == pytest.approx(so["fixed_cost"], rel=1e-12, abs=1e-300)
+    for a, b in zip(s["trace"], tro):
+        assert a["cost"] == pytest.approx(b["cost"], rel=TOL_COST)
+        assert a["trust_region_radius"] == pytest.approx(b["trust_region_radius"], rel=1e-6)
+        assert a["step_is_successful"] == b["step_is_successful"]
+    fixed_c = cf.astype(bool)
+    assert np.array_equal(cam[fixed_c], p.cam[fixed_c])
+    if pf is not None:
+        assert np.array_equal(pts[pf.astype(bool)], p.pts[pf.astype(bool)])
+    if mode == api.POSE_ONLY:
+        assert np.array_equal(pts, p.pts)
+    assert np.abs(cam - cam0).max() < 1e-6 and np.abs(pts - pts0).max() < 1e-6
+    assert not np.array_equal(cam[~fixed_c], p.cam[~fixed_c])
+    if case.startswith("window"):
+        assert s["fixed_cost"] > 0.0
+
+
+def test_constant_masks_on_a_resident_problem(ctx):
+    p = synth.make_ring(10, 300, 6, seed=4)
+    o = api.default_options(linear_solver=api.LINEAR_DENSE_SCHUR)
+    ctx.upload(p)
+    free = ctx.solve_resident(o)
+    cf = np.zeros(p.n_cams, np.uint8); cf[:3] = 1
+    ctx.reset()
+    ctx.set_constant(cf, None)
+    held = ctx.solve_resident(o)
+    cam, _ = ctx.download()
+    assert np.array_equal(cam[:3], p.cam[:3]) and held["final_cost"] > free["final_cost"]
+    so = po.solve(p, opts=po.default_options(), cam_fixed=cf)[2]
+    assert held["final_cost"] == pytest.approx(so["final_cost"], rel=TOL_COST) and held["num_iterations"] == so["num_iterations"]
+    ctx.reset()
+    ctx.set_constant(None, None)   # cleared: back to the free problem
+    again = ctx.solve_resident(o)
+    assert again["final_cost"] == pytest.approx(free["final_cost"], rel=1e-12) and again["fixed_cost"] == 0.0
