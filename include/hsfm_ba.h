@@ -257,6 +257,27 @@ int hsfm_ba_problem_upload(hsfm_ba_ctx* ctx, int mode, int64_t n_obs, const doub
                            const int32_t* cam_idx, const int32_t* pt_idx, int32_t n_cams,
                            const double* K9, const double* dist, const double* cam_rt,
                            int64_t n_pts, const double* pts);
+/* ---- scan: a resident problem that grows by a keyframe per call ----------------------
+ * The reference re-gathers and re-sends its whole map at every keyframe (CSfM::mapping -> CSfM::bundleAdjustment,
+ * CSfM.cpp:252-259, 310-348; two heap objects and a hash insert per observation in CTracker.cpp:676-696).  A scan keeps
+ * the raw arrays of the problem in device memory between the calls:
+ *   hsfm_ba_scan_begin            = hsfm_ba_problem_upload that also starts the device-resident table;
+ *   hsfm_ba_scan_append_keyframe  adds n_new_cams cameras (ids n_cams, n_cams+1, ...), n_new_pts points (ids n_pts, ...) and
+ *                                 n_new_obs observations between ANY cameras / points of the grown problem (a new map point
+ *                                 brings its observations in older keyframes with it).  Only these rows cross PCIe; the
+ *                                 poses / points refined by earlier solves are taken from the device as they are.
+ * After either call the problem is resident and indexed exactly as a one-shot upload of the concatenated arrays would
+ * be: hsfm_ba_problem_solve / _download / _frame_stats / _set_constant apply (constant-block masks are cleared by an
+ * append).  bytes_uploaded (optional) receives the host->device bytes of the call.  Invalid new indices return
+ * HSFM_BA_ERR_ARG and leave the scan as it was. */
+int hsfm_ba_scan_begin(hsfm_ba_ctx* ctx, int mode, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx,
+                       const int32_t* pt_idx, int32_t n_cams, const double* K9, const double* dist,
+                       const double* cam_rt, int64_t n_pts, const double* pts, int64_t* bytes_uploaded);
+int hsfm_ba_scan_append_keyframe(hsfm_ba_ctx* ctx, int32_t n_new_cams, const double* K9, const double* dist,
+                                 const double* cam_rt, int64_t n_new_pts, const double* pts, int64_t n_new_obs,
+                                 const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
+                                 int64_t* bytes_uploaded);
+
 /* Constant-block masks of the resident problem (see hsfm_ba_solve_packed_ex), caller's camera / point order; both NULL
  * clears them.  They stay in force for every later solve of this problem (a new upload clears them). */
 int hsfm_ba_problem_set_constant(hsfm_ba_ctx* ctx, const uint8_t* cam_fixed, const uint8_t* pt_fixed);

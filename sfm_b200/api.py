@@ -47,6 +47,10 @@ SYMBOLS = {
     "hsfm_ba_solve_packed_ex": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64,
                                           _dp, _bp, _bp, C.POINTER(Options), C.POINTER(Summary)]),
     "hsfm_ba_problem_set_constant": (C.c_int, [C.c_void_p, _bp, _bp]),
+    "hsfm_ba_scan_begin": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp,
+                                     C.POINTER(C.c_int64)]),
+    "hsfm_ba_scan_append_keyframe": (C.c_int, [C.c_void_p, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp, C.c_int64, _dp, _ip, _ip,
+                                               C.POINTER(C.c_int64)]),
     "hsfm_ba_eval": (C.c_int, [C.c_void_p, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp, _dp, _dp, _dp]),
     "hsfm_ba_schur": (C.c_int, [C.c_void_p, C.c_int64, _dp, _ip, _ip, C.c_int32, _dp, _dp, _dp, C.c_int64, _dp,
                                 C.POINTER(Options), C.c_double, _dp, _dp, _dp, _dp, _dp, _dp, _dp]),
@@ -289,6 +293,35 @@ class Context:
                                              _d(prob.K), _d(prob.dist), _d(prob.cam), prob.n_pts, _d(prob.pts))
         if rc:
             raise BAError(rc, "hsfm_ba_problem_upload")
+
+    def scan_begin(self, prob, mode=STRUCT_AND_POSE):
+        """Upload ``prob`` as the start of a scan (device-resident observation table); returns the bytes sent."""
+        import dataclasses
+
+        sent = C.c_int64()
+        rc = self.lib.hsfm_ba_scan_begin(self.h, mode, prob.n_obs, _d(prob.obs), _i(prob.cam_idx), _i(prob.pt_idx), prob.n_cams,
+                                         _d(prob.K), _d(prob.dist), _d(prob.cam), prob.n_pts, _d(prob.pts), C.byref(sent))
+        if rc:
+            raise BAError(rc, "hsfm_ba_scan_begin")
+        self._keep = dataclasses.replace(prob)
+        return sent.value
+
+    def scan_append_keyframe(self, K_new, cam_new, pts_new, obs, cam_idx, pt_idx, dist_new=None):
+        """Append cameras (rows of K_new [k,9] / cam_new [k,6]), points (pts_new [m,3]) and observations (global camera /
+        point ids) to the scan; returns the bytes sent.  Only these rows are uploaded."""
+        K_new, cam_new, pts_new = _f64(K_new, (-1, 9)), _f64(cam_new, (-1, 6)), _f64(pts_new, (-1, 3))
+        obs = _f64(obs, (-1, 2))
+        cam_idx = np.ascontiguousarray(cam_idx, dtype=np.int32)
+        pt_idx = np.ascontiguousarray(pt_idx, dtype=np.int32)
+        dist_new = None if dist_new is None else _f64(dist_new, (-1, 2))
+        sent = C.c_int64()
+        rc = self.lib.hsfm_ba_scan_append_keyframe(self.h, K_new.shape[0], _d(K_new), _d(dist_new), _d(cam_new), pts_new.shape[0], _d(pts_new),
+                                                   obs.shape[0], _d(obs), _i(cam_idx), _i(pt_idx), C.byref(sent))
+        if rc:
+            raise BAError(rc, "hsfm_ba_scan_append_keyframe")
+        k = self._keep
+        k.cam = np.concatenate([k.cam, cam_new]); k.pts = np.concatenate([k.pts, pts_new])  # sizes for download()
+        return sent.value
 
     def set_constant(self, cam_fixed=None, pt_fixed=None):
         """Hold cameras / points of the resident problem constant (boolean masks, caller order); None, None clears."""

@@ -113,6 +113,7 @@ void hsfm_ba_destroy(hsfm_ba_ctx* h) {
   cudaSetDevice(h->c.device);
   cudaStreamSynchronize(h->c.stream);
   h->c.prob.destroy();
+  h->c.scan.destroy();
   h->c.comm.destroy();
   h->c.chol_aux.destroy();
   h->c.chol_plan.destroy();
@@ -186,6 +187,7 @@ int hsfm_ba_problem_upload(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double
   HSFM_CUDA(cudaSetDevice(h->c.device));
   h->c.has_problem = false;
   h->c.chol_plan_valid = false;
+  h->c.scan.active = false;  // the resident problem no longer is the scan store's
   double setup = 0, h2d = 0;
   const bool natural = h->c.ordering == 1 || h->c.tap_upload;
   int rc = build_problem(h->c.prob, mode, n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, dist, cam_rt, n_pts, pts, h->c.comm, h->c.stream, &setup, &h2d, natural);
@@ -195,6 +197,34 @@ int hsfm_ba_problem_upload(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double
   h->c.prob.scal_host[21] = h2d;
   h->c.has_problem = true;
   return 0;
+}
+
+int hsfm_ba_scan_begin(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
+                       int32_t n_cams, const double* K9, const double* dist, const double* cam_rt, int64_t n_pts, const double* pts,
+                       int64_t* bytes_uploaded) {
+  if (!h || !valid_mode(mode) || n_obs < 0 || n_cams < 0 || n_pts < 0) return HSFM_BA_ERR_ARG;
+  if (n_obs > 0 && (!obs_xy || !cam_idx || !pt_idx)) return HSFM_BA_ERR_ARG;
+  if (n_cams > 0 && (!K9 || !cam_rt)) return HSFM_BA_ERR_ARG;
+  if (n_pts > 0 && !pts) return HSFM_BA_ERR_ARG;
+  if (n_obs >= ((int64_t)1 << 31) || n_pts >= ((int64_t)1 << 30)) return HSFM_BA_ERR_UNSUPPORTED;
+  HSFM_CUDA(cudaSetDevice(h->c.device));
+  const int rc = scan_begin(h->c, mode, n_obs, obs_xy, cam_idx, pt_idx, n_cams, K9, dist, cam_rt, n_pts, pts);
+  if (bytes_uploaded) *bytes_uploaded = rc ? 0 : h->c.scan.bytes_uploaded;
+  return rc;
+}
+
+int hsfm_ba_scan_append_keyframe(hsfm_ba_ctx* h, int32_t n_new_cams, const double* K9, const double* dist, const double* cam_rt,
+                                 int64_t n_new_pts, const double* pts, int64_t n_new_obs, const double* obs_xy, const int32_t* cam_idx,
+                                 const int32_t* pt_idx, int64_t* bytes_uploaded) {
+  if (!h || n_new_cams < 0 || n_new_pts < 0 || n_new_obs < 0) return HSFM_BA_ERR_ARG;
+  if (n_new_obs > 0 && (!obs_xy || !cam_idx || !pt_idx)) return HSFM_BA_ERR_ARG;
+  if (n_new_cams > 0 && (!K9 || !cam_rt)) return HSFM_BA_ERR_ARG;
+  if (n_new_pts > 0 && !pts) return HSFM_BA_ERR_ARG;
+  if (!h->c.scan.active) return HSFM_BA_ERR_STATE;
+  HSFM_CUDA(cudaSetDevice(h->c.device));
+  const int rc = scan_append(h->c, n_new_cams, K9, dist, cam_rt, n_new_pts, pts, n_new_obs, obs_xy, cam_idx, pt_idx, nullptr, nullptr);
+  if (bytes_uploaded) *bytes_uploaded = rc ? 0 : h->c.scan.bytes_uploaded;
+  return rc;
 }
 
 int hsfm_ba_problem_set_constant(hsfm_ba_ctx* h, const uint8_t* cam_fixed, const uint8_t* pt_fixed) {

@@ -255,14 +255,15 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   ALLOC(P.K9, 9 * (size_t)n_cams); ALLOC(P.dist, 2 * (size_t)n_cams);
   ALLOC(P.cam_x, 6 * (size_t)n_cams); ALLOC(P.pts_x, 3 * (size_t)n_pts);
   ALLOC(P.cam_x0, 6 * (size_t)n_cams); ALLOC(P.pts_x0, 3 * (size_t)n_pts); ALLOC(P.pts_io, 3 * (size_t)n_pts);
-  HSFM_CUDA(cudaMemcpyAsync(obs_in, obs_xy, sizeof(double) * 2 * n, cudaMemcpyHostToDevice, s));
-  HSFM_CUDA(cudaMemcpyAsync(cam_in, cam_idx, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, s));
-  HSFM_CUDA(cudaMemcpyAsync(pt_in, pt_idx, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, s));
-  HSFM_CUDA(cudaMemcpyAsync(P.K9, K9, sizeof(double) * 9 * n_cams, cudaMemcpyHostToDevice, s));
-  if (dist) HSFM_CUDA(cudaMemcpyAsync(P.dist, dist, sizeof(double) * 2 * n_cams, cudaMemcpyHostToDevice, s));
+  // cudaMemcpyDefault: the sources are host buffers (one-shot calls) or the device-resident scan store (ba_scan.cu)
+  HSFM_CUDA(cudaMemcpyAsync(obs_in, obs_xy, sizeof(double) * 2 * n, cudaMemcpyDefault, s));
+  HSFM_CUDA(cudaMemcpyAsync(cam_in, cam_idx, sizeof(int) * (size_t)n, cudaMemcpyDefault, s));
+  HSFM_CUDA(cudaMemcpyAsync(pt_in, pt_idx, sizeof(int) * (size_t)n, cudaMemcpyDefault, s));
+  HSFM_CUDA(cudaMemcpyAsync(P.K9, K9, sizeof(double) * 9 * n_cams, cudaMemcpyDefault, s));
+  if (dist) HSFM_CUDA(cudaMemcpyAsync(P.dist, dist, sizeof(double) * 2 * n_cams, cudaMemcpyDefault, s));
   else HSFM_CUDA(cudaMemsetAsync(P.dist, 0, sizeof(double) * 2 * std::max(1, n_cams), s));
-  HSFM_CUDA(cudaMemcpyAsync(P.cam_x0, cam_rt, sizeof(double) * 6 * n_cams, cudaMemcpyHostToDevice, s));
-  HSFM_CUDA(cudaMemcpyAsync(P.pts_io, pts, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyHostToDevice, s));
+  HSFM_CUDA(cudaMemcpyAsync(P.cam_x0, cam_rt, sizeof(double) * 6 * n_cams, cudaMemcpyDefault, s));
+  HSFM_CUDA(cudaMemcpyAsync(P.pts_io, pts, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDefault, s));
   // Envelope of the reduced camera matrix in the caller's camera order (over all ranks): what the camera ordering and
   // the block structure of the Cholesky are derived from.  Only where a structured factorisation can pay (>= 4 panels).
   int *min_cam, *min_cam_sorted;

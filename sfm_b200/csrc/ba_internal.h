@@ -263,6 +263,24 @@ int launch_cost_noalloc(int device, int n_obs, const double* obs_xy, const int* 
                         const double* cam_rt, int n_pts, const double* pts, double* cost, cudaStream_t s);
 
 // ---- LM driver (ba_solver.cu) ----
+// Persistent device-resident observation table of a scan: the raw arrays of the problem in the
+// CALLER's order — what CSfM::bundleAdjustment re-gathers from the map and re-sends at every keyframe
+// (CSfM.cpp:310-348, CTracker.cpp:676-696) — kept in grow-only device buffers outside the per-problem arena, so that a
+// new keyframe uploads only its own rows (ba_scan.cu).
+struct ScanStore {
+  bool active = false;
+  int mode = 2;
+  int64_t n_obs = 0, n_pts = 0, cap_obs = 0, cap_pts = 0;
+  int n_cams = 0, cap_cams = 0;
+  bool has_dist = false;
+  double* obs = nullptr;      // [cap_obs][2]
+  int *cam_idx = nullptr, *pt_idx = nullptr;  // [cap_obs]
+  double *K9 = nullptr, *dist = nullptr, *cam = nullptr;  // [cap_cams][9], [2], [6]
+  double* pts = nullptr;      // [cap_pts][3]
+  int64_t bytes_uploaded = 0; // host->device bytes of the last append
+  void destroy();
+};
+
 struct Ctx {
   int device = 0;
   cudaStream_t own_stream = nullptr;
@@ -276,7 +294,13 @@ struct Ctx {
   int ordering = 0;         // 0 = automatic camera order, 1 = the caller's (hsfm_ba_set_ordering)
   bool tap_upload = false;  // upload on behalf of a parity tap: caller's camera order
   std::vector<cudaEvent_t> phase_events;  // pool reused across solves (phase timing of lm_solve)
+  ScanStore scan;
 };
+// ba_scan.cu
+int scan_begin(Ctx& c, int mode, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx, int32_t n_cams,
+               const double* K9, const double* dist, const double* cam_rt, int64_t n_pts, const double* pts);
+int scan_append(Ctx& c, int32_t n_new_cams, const double* K9, const double* dist, const double* cam_rt, int64_t n_new_pts, const double* pts,
+                int64_t n_new_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx, double* setup_ms, double* h2d_ms);
 int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary);
 
 }  // namespace hsfm

@@ -297,3 +297,56 @@ def shard_by_point(prob: Problem, n_ranks: int):
                      dist=prob.dist, name=f"{prob.name}[{r}/{n_ranks}]")
         shards.append((sh, gids))
     return shards
+
+
+def keyframe_stream(prob: Problem, k0: int):
+    """Replay ``prob`` as a scan (what CSfM::mapping produces keyframe by keyframe, CSfM.cpp:252-259): a start problem
+    over the first ``k0`` keyframes and one append per further keyframe.  A map point enters the stream when its second
+    observation arrives (a point is triangulated from two views) and brings its earlier observation with it; point ids
+    of the stream are in order of entry.  Returns (start Problem, [dict(K, cam, pts, obs, cam_idx, pt_idx)], final
+    Problem = the concatenation, numbered as the stream numbers it)."""
+    order = np.lexsort((prob.pt_idx, prob.cam_idx))
+    cam_idx, pt_idx, obs = prob.cam_idx[order], prob.pt_idx[order], prob.obs[order]
+    n_seen = np.zeros(prob.n_pts, dtype=np.int64)
+    new_id = np.full(prob.n_pts, -1, dtype=np.int64)
+    pending = {}  # original point id -> index (into the sorted arrays) of its single observation so far
+    stages, next_id = [], 0
+    bounds = np.searchsorted(cam_idx, np.arange(prob.n_cams + 1))
+    cur = dict(obs=[], cam=[], pt=[], new_pts=[])
+
+    def close(c_lo, c_hi):
+        nonlocal cur
+        st = dict(K=prob.K[c_lo:c_hi].copy(), cam=prob.cam[c_lo:c_hi].copy(), cam_true=prob.cam_true[c_lo:c_hi],
+                  pts=prob.pts[cur["new_pts"]].copy() if cur["new_pts"] else np.zeros((0, 3)),
+                  pts_true=prob.pts_true[cur["new_pts"]] if cur["new_pts"] else np.zeros((0, 3)),
+                  obs=np.ascontiguousarray(np.array(cur["obs"]).reshape(-1, 2)), cam_idx=np.array(cur["cam"], dtype=np.int32),
+                  pt_idx=np.array(cur["pt"], dtype=np.int32))
+        stages.append(st)
+        cur = dict(obs=[], cam=[], pt=[], new_pts=[])
+
+    for c in range(prob.n_cams):
+        for j in range(bounds[c], bounds[c + 1]):
+            p = int(pt_idx[j])
+            n_seen[p] += 1
+            if n_seen[p] == 1:
+                pending[p] = j
+                continue
+            if n_seen[p] == 2:
+                new_id[p] = next_id
+                next_id += 1
+                cur["new_pts"].append(p)
+                j0 = pending.pop(p)
+                cur["obs"].append(obs[j0]); cur["cam"].append(int(cam_idx[j0])); cur["pt"].append(int(new_id[p]))
+            cur["obs"].append(obs[j]); cur["cam"].append(c); cur["pt"].append(int(new_id[p]))
+        if c == k0 - 1:
+            close(0, k0)
+        elif c >= k0:
+            close(c, c + 1)
+    first = stages[0]
+    start = Problem(obs=first["obs"], cam_idx=first["cam_idx"], pt_idx=first["pt_idx"], K=np.ascontiguousarray(first["K"]),
+                    cam=np.ascontiguousarray(first["cam"]), pts=np.ascontiguousarray(first["pts"]), cam_true=first["cam_true"],
+                    pts_true=first["pts_true"], name=prob.name + "[start]")
+    cat = lambda k: np.ascontiguousarray(np.concatenate([s[k] for s in stages]))  # noqa: E731
+    final = Problem(obs=cat("obs"), cam_idx=cat("cam_idx"), pt_idx=cat("pt_idx"), K=cat("K"), cam=cat("cam"), pts=cat("pts"),
+                    cam_true=cat("cam_true"), pts_true=cat("pts_true"), name=prob.name + "[stream]")
+    return start, stages[1:], final

@@ -165,3 +165,68 @@ def test_constant_masks_on_a_resident_problem(ctx):
     ctx.set_constant(None, None)   # cleared: back to the free problem
     again = ctx.solve_resident(o)
     assert again["final_cost"] == pytest.approx(free["final_cost"], rel=1e-12) and again["fixed_cost"] == 0.0
+
+
+def _append(ctx, st):
+    return ctx.scan_append_keyframe(st["K"], st["cam"], st["pts"], st["obs"], st["cam_idx"], st["pt_idx"])
+
+
+@pytest.mark.parametrize("linear", [api.LINEAR_PCG, api.LINEAR_DENSE_SCHUR], ids=["pcg", "dense"])
+def test_scan_appends_equal_one_shot_upload(ctx, linear):
+    """k keyframe appends to the device-resident observation table == one upload of the
+    concatenated arrays — same index, same LM trajectory — while each append sends only its own rows."""
+    p = synth.make_ring(16, 600, 6, seed=13, name="scan")
+    start, stages, final = synth.keyframe_stream(p, 4)
+    o = api.default_options(linear_solver=linear, pcg_max_iterations=3000)
+    sent0 = ctx.scan_begin(start)
+    assert sent0 == start.obs.nbytes + start.cam_idx.nbytes + start.pt_idx.nbytes + start.K.nbytes + start.cam.nbytes + start.pts.nbytes
+    total = sent0
+    for st in stages:
+        sent = _append(ctx, st)
+        assert sent == st["obs"].nbytes + st["cam_idx"].nbytes + st["pt_idx"].nbytes + st["K"].nbytes + st["cam"].nbytes + st["pts"].nbytes
+        total += sent
+        assert sent < 0.5 * total  # O(new), not O(scan)
+    assert total == final.obs.nbytes + final.cam_idx.nbytes + final.pt_idx.nbytes + final.K.nbytes + final.cam.nbytes + final.pts.nbytes
+    a = ctx.solve_resident(o)
+    cam_a, pts_a = ctx.download()
+    cam_b, pts_b, b = ctx.solve_packed(final, opts=o)
+    assert a["num_iterations"] == b["num_iterations"] and a["num_successful_steps"] == b["num_successful_steps"]
+    tol = 0.0 if linear == api.LINEAR_PCG else 1e-12   # PCG path: no atomics anywhere, the two runs are bit-identical
+    for x, y in zip(a["trace"], b["trace"]):
+        assert abs(x["cost"] - y["cost"]) <= tol * y["cost"] and x["trust_region_radius"] == pytest.approx(y["trust_region_radius"], rel=1e-12)
+    assert np.abs(cam_a - cam_b).max() <= (0.0 if tol == 0.0 else 1e-9) and np.abs(pts_a - pts_b).max() <= (0.0 if tol == 0.0 else 1e-9)
+    so = po.solve(final, opts=po.default_options(num_threads=4))[2]
+    assert a["final_cost"] == pytest.approx(so["final_cost"], rel=TOL_COST) and a["num_iterations"] == so["num_iterations"]
+
+
+def test_scan_solve_per_keyframe_matches_oracle(ctx):
+    """The production loop (CSfM::mapping, CSfM.cpp:252-259): global BA after EVERY keyframe.  On the scan the refined
+    poses and points stay on the device between the keyframes; the oracle is restarted per keyframe from the previous
+    result plus the new keyframe's initial values."""
+    import dataclasses
+
+    p = synth.make_ring(12, 400, 6, seed=17, name="scan-loop")
+    start, stages, final = synth.keyframe_stream(p, 5)
+    o = api.default_options(linear_solver=api.LINEAR_DENSE_SCHUR)
+    ctx.scan_begin(start)
+    s = ctx.solve_resident(o)
+    cur = start
+    cam_o, pts_o, so, _ = po.solve(cur)
+    assert s["final_cost"] == pytest.approx(so["final_cost"], rel=TOL_COST)
+    for st in stages:
+        _append(ctx, st)
+        s = ctx.solve_resident(o)
+        cur = dataclasses.replace(cur, obs=np.concatenate([cur.obs, st["obs"]]), cam_idx=np.concatenate([cur.cam_idx, st["cam_idx"]]),
+                                  pt_idx=np.concatenate([cur.pt_idx, st["pt_idx"]]), K=np.concatenate([cur.K, st["K"]]),
+                                  cam=np.concatenate([cam_o, st["cam"]]), pts=np.concatenate([pts_o, st["pts"]]))
+        cam_o, pts_o, so, _ = po.solve(cur)
+        assert s["num_iterations"] == so["num_iterations"]
+        assert s["initial_cost"] == pytest.approx(so["initial_cost"], rel=1e-9)
+        assert s["final_cost"] == pytest.approx(so["final_cost"], rel=TOL_COST)
+    cam, pts = ctx.download()
+    assert cam.shape == (p.n_cams, 6) and np.abs(cam - cam_o).max() < 1e-6 and np.abs(pts - pts_o).max() < 1e-6
+    # an append with an index beyond the grown problem is refused and leaves the scan usable
+    bad = dict(stages[-1]); bad["cam_idx"] = bad["cam_idx"] + 100
+    with pytest.raises(api.BAError):
+        _append(ctx, bad)
+    assert ctx.eval_resident() == pytest.approx(so["final_cost"], rel=1e-9)
