@@ -131,6 +131,9 @@ typedef struct hsfm_ba_summary {
   int32_t chol_critical_panels; /* panels on the serial chain of the factorisation: = chol_panels with one chain, fewer with two */
   int32_t cameras_reordered;    /* 1: the problem is held in the library's two-ended camera order (hsfm_ba_set_ordering) */
   int32_t reserved1;
+  double chol_flops;            /* FP64 flops of ONE factorisation of the reduced camera system over its block structure:
+                                   sum over panels of 128^3/3 (diagonal block) + |R_K| 128^3 (panel solve) + |R_K|(|R_K|+1) 128^3
+                                   (trailing update); n^3/3 when factored as a dense matrix */
 } hsfm_ba_summary;
 
 typedef struct hsfm_ba_ctx hsfm_ba_ctx;

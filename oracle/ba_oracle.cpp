@@ -693,6 +693,7 @@ int ba_oracle_solve_ex(int mode, int64_t n_obs, const double* obs_xy, const int3
   };
 
   linearize();
+  const double setup_s = now_s() - t_begin;
   S.initial_cost = x_cost;
   double radius = o.initial_trust_region_radius;
   double decrease_factor = 2.0;
@@ -831,6 +832,7 @@ int ba_oracle_solve_ex(int mode, int64_t n_obs, const double* obs_xy, const int3
   S.initial_cost += fixed_cost;
   S.final_cost = x_cost + fixed_cost;
   S.fixed_cost = fixed_cost;
+  S.setup_seconds = setup_s;
   S.rms_px = n_obs > 0 ? std::sqrt(2.0 * S.final_cost / (double)n_obs) : 0.0;
   S.num_iterations = iter;
   S.num_successful_steps = num_success;

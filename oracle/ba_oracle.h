@@ -53,6 +53,7 @@ typedef struct ba_oracle_summary {
   ba_oracle_iteration* trace;
   int32_t trace_capacity, trace_count;
   double fixed_cost;     /* 1/2 sum r^2 over residuals whose parameter blocks are all constant (Ceres Summary::fixed_cost) */
+  double setup_seconds;  /* index build + Jacobi scaling + the initial linearisation: everything before the first trust-region attempt */
 } ba_oracle_summary;
 
 void ba_oracle_default_options(ba_oracle_options* o);

@@ -43,7 +43,7 @@ class OSummary(C.Structure):
         ("linear_solver_used", C.c_int32), ("total_linear_iterations", C.c_int32), ("n_threads", C.c_int32),
         ("eval_seconds", C.c_double), ("linear_seconds", C.c_double), ("total_seconds", C.c_double),
         ("trace", C.POINTER(OIteration)), ("trace_capacity", C.c_int32), ("trace_count", C.c_int32),
-        ("fixed_cost", C.c_double),
+        ("fixed_cost", C.c_double), ("setup_seconds", C.c_double),
     ]
 
 

@@ -237,6 +237,21 @@ class Context:
             raise BAError(rc, "hsfm_ba_solve_packed")
         return cam, pts, box.as_dict()
 
+    def solve_ptr(self, obs, cam_idx, K9, R_ptrs, t_ptrs, pt_ptrs, mode=STRUCT_AND_POSE, opts=None, trace_capacity=64):
+        """hsfm_ba_solve_ptr with the pointer arrays given as uint64 numpy arrays of host addresses (R_ptrs, t_ptrs: one per
+        camera; pt_ptrs: one per observation, equal addresses = the same map point).  Optimises in place through them."""
+        obs = _f64(obs, (-1, 2))
+        cam_idx = np.ascontiguousarray(cam_idx, dtype=np.int32)
+        K9 = _f64(K9, (-1, 9))
+        R_ptrs, t_ptrs, pt_ptrs = (np.ascontiguousarray(a, dtype=np.uint64) for a in (R_ptrs, t_ptrs, pt_ptrs))
+        box = _SummaryBox(trace_capacity)
+        rc = self.lib.hsfm_ba_solve_ptr(self.h, int(mode), obs.shape[0], _d(obs), _i(cam_idx), K9.shape[0], _d(K9),
+                                        R_ptrs.ctypes.data_as(_pp), t_ptrs.ctypes.data_as(_pp), pt_ptrs.ctypes.data_as(_pp),
+                                        C.byref(opts) if opts is not None else None, C.byref(box.s))
+        if rc:
+            raise BAError(rc, "hsfm_ba_solve_ptr")
+        return box.as_dict()
+
     def evaluate(self, prob, cam=None, pts=None, want_jac=True):
         cam = prob.cam if cam is None else cam
         pts = prob.pts if pts is None else pts

@@ -3,7 +3,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
-#include <unordered_map>
+#include <thread>
 
 #include "ba_internal.h"
 
@@ -28,6 +28,18 @@ int check_device(int device_id) {
 }
 
 int valid_mode(int mode) { return mode >= 0 && mode <= 2; }
+
+// fn(begin, end) over [0, n) on a few host threads (plain copies through pointers; small inputs stay on the caller's thread)
+template <class F>
+void parallel_rows(int64_t n, F fn) {
+  const int T = n < (1 << 16) ? 1 : 4;
+  if (T == 1) { fn(0, n); return; }
+  std::vector<std::thread> th;
+  const int64_t step = (n + T - 1) / T;
+  for (int k = 1; k < T; ++k) th.emplace_back([=] { fn(std::min(n, k * step), std::min(n, (k + 1) * step)); });
+  fn(0, std::min(n, step));
+  for (auto& t : th) t.join();
+}
 
 int64_t global_obs(Ctx& c) {
   // sum of the (already all-reduced) per-camera observation counts
@@ -114,6 +126,7 @@ void hsfm_ba_destroy(hsfm_ba_ctx* h) {
   cudaStreamSynchronize(h->c.stream);
   h->c.prob.destroy();
   h->c.scan.destroy();
+  h->c.ptr_ws.destroy();
   h->c.comm.destroy();
   h->c.chol_aux.destroy();
   h->c.chol_plan.destroy();
@@ -426,37 +439,45 @@ int hsfm_ba_solve_ptr(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double* obs
   if (!valid_mode(mode)) return HSFM_BA_OK;
   if (n_obs > 0 && (!obs_xy || !cam_idx || !pts3d)) return HSFM_BA_ERR_ARG;
   if (n_cams > 0 && (!K9 || !R || !t)) return HSFM_BA_ERR_ARG;
-  // pointer identity -> compact point ids, in order of first appearance (CSfM.cpp:331, CMap.cpp:215)
-  std::unordered_map<const double*, int32_t> ids;
-  ids.reserve((size_t)n_obs / 2 + 16);
-  std::vector<int32_t> pt_idx((size_t)n_obs);
+  // pointer identity -> compact point ids (CSfM.cpp:331, CMap.cpp:215), on the device: the 8-byte pointers are uploaded,
+  // radix-sorted and numbered there; the host only touches the distinct points (not every observation)
+  HSFM_CUDA(cudaSetDevice(h->c.device));
+  static const bool timing = getenv("HSFM_PTR_TIMING") != nullptr;  // experiment knob: where the call's host time goes
+  const double tt0 = now_ms();
   std::vector<double*> uniq;
-  for (int64_t i = 0; i < n_obs; ++i) {
-    double* p = pts3d[i];
-    if (!p) return HSFM_BA_ERR_ARG;
-    auto it = ids.find(p);
-    if (it == ids.end()) {
-      it = ids.emplace(p, (int32_t)uniq.size()).first;
-      uniq.push_back(p);
-    }
-    pt_idx[(size_t)i] = it->second;
+  int* d_pt_idx = nullptr;
+  {
+    const int rc0 = dedupe_pointers(h->c.ptr_ws, n_obs, pts3d, &d_pt_idx, uniq, h->c.stream);
+    if (rc0) return rc0;
   }
+  const double tt1 = now_ms();
   const int64_t n_pts = (int64_t)uniq.size();
   std::vector<double> cam((size_t)n_cams * 6), pts((size_t)n_pts * 3);
   for (int c = 0; c < n_cams; ++c) {
     if (!R[c] || !t[c]) return HSFM_BA_ERR_ARG;
     for (int k = 0; k < 3; ++k) { cam[6 * (size_t)c + k] = R[c][k]; cam[6 * (size_t)c + 3 + k] = t[c][k]; }
   }
-  for (int64_t p = 0; p < n_pts; ++p)
-    for (int k = 0; k < 3; ++k) pts[3 * (size_t)p + k] = uniq[(size_t)p][k];
-  int rc = hsfm_ba_solve_packed(h, mode, n_obs, obs_xy, cam_idx, pt_idx.data(), n_cams, K9, nullptr, cam.data(), n_pts, pts.data(), opts, summary);
+  // the distinct points, through their pointers (ids are in address order: a mostly sequential walk of the map's storage)
+  parallel_rows(n_pts, [&](int64_t b, int64_t e) {
+    for (int64_t p = b; p < e; ++p)
+      for (int k = 0; k < 3; ++k) pts[3 * (size_t)p + k] = uniq[(size_t)p][k];
+  });
+  const double tt2 = now_ms();
+  // pt_idx is a DEVICE array: the upload copies with cudaMemcpyDefault
+  int rc = hsfm_ba_solve_packed(h, mode, n_obs, obs_xy, cam_idx, d_pt_idx, n_cams, K9, nullptr, cam.data(), n_pts, pts.data(), opts, summary);
   if (rc) return rc;  // parameters untouched on failure
+  const double tt3 = now_ms();
   if (mode != HSFM_BA_STRUCT_ONLY)
     for (int c = 0; c < n_cams; ++c)
       for (int k = 0; k < 3; ++k) { R[c][k] = cam[6 * (size_t)c + k]; t[c][k] = cam[6 * (size_t)c + 3 + k]; }
   if (mode != HSFM_BA_POSE_ONLY)
-    for (int64_t p = 0; p < n_pts; ++p)
-      for (int k = 0; k < 3; ++k) uniq[(size_t)p][k] = pts[3 * (size_t)p + k];
+    parallel_rows(n_pts, [&](int64_t b, int64_t e) {
+      for (int64_t p = b; p < e; ++p)
+        for (int k = 0; k < 3; ++k) uniq[(size_t)p][k] = pts[3 * (size_t)p + k];
+    });
+  if (timing && summary)
+    std::fprintf(stderr, "[hsfm_ba_solve_ptr] dedupe %.2f ms, gather %.2f, packed call %.2f (h2d %.2f setup %.2f solve %.2f d2h %.2f), scatter %.2f\n", tt1 - tt0,
+                 tt2 - tt1, tt3 - tt2, summary->h2d_ms, summary->setup_ms, summary->solve_ms, summary->d2h_ms, now_ms() - tt3);
   return 0;
 }
 

@@ -227,6 +227,90 @@ __global__ void __launch_bounds__(TILE) tile_cams_kernel(const int* __restrict__
   }
 }
 
+// ---- pointer identity -> point ids (hsfm_ba_solve_ptr) -------------------------------------------------------
+namespace {
+__global__ void ptr_heads_kernel(int n, const unsigned long long* __restrict__ sorted, int* __restrict__ head) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) head[i] = (i == 0 || sorted[i] != sorted[i - 1]) ? 1 : 0;
+}
+// id of sorted element i = (inclusive scan of heads) - 1; scattered to the observation it came from; distinct pointers by id
+__global__ void ptr_ids_kernel(int n, const unsigned long long* __restrict__ sorted, const int* __restrict__ src, const int* __restrict__ head,
+                               const int* __restrict__ incl, int* __restrict__ pt_idx, unsigned long long* __restrict__ uniq) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int id = incl[i] - 1;
+  pt_idx[src[i]] = id;
+  if (head[i]) uniq[id] = sorted[i];
+}
+}  // namespace
+
+void PtrScratch::destroy() {
+  if (buf) cudaFree(buf);
+  if (uniq_host) cudaFreeHost(uniq_host);
+  *this = PtrScratch();
+}
+
+int dedupe_pointers(PtrScratch& W, int64_t n64, double* const* host_ptrs, int** d_pt_idx_out, std::vector<double*>& uniq_out, cudaStream_t s) {
+  uniq_out.clear();
+  *d_pt_idx_out = nullptr;
+  if (n64 >= (int64_t)1 << 31) return HSFM_BA_ERR_UNSUPPORTED;
+  const int n = (int)n64;
+  if (n == 0) return 0;
+  static_assert(sizeof(double*) == sizeof(unsigned long long), "64-bit pointers");
+  size_t t_sort = 0, t_scan = 0;
+  unsigned long long* nullk = nullptr;
+  int* nulli = nullptr;
+  cub::DeviceRadixSort::SortPairs(nullptr, t_sort, nullk, nullk, nulli, nulli, n, 0, 48, s);  // user-space addresses: 48 significant bits
+  cub::DeviceScan::InclusiveSum(nullptr, t_scan, nulli, nulli, n, s);
+  const size_t tmp = (std::max(t_sort, t_scan) + 255) & ~(size_t)255;
+  const size_t n8 = ((size_t)n * 8 + 255) & ~(size_t)255, n4 = ((size_t)n * 4 + 255) & ~(size_t)255;
+  const size_t need = 3 * n8 + 5 * n4 + tmp;
+  if (W.cap < need) {
+    if (W.buf) cudaFree(W.buf);
+    W.buf = nullptr; W.cap = 0;
+    if (cudaMalloc(&W.buf, need + need / 4) != cudaSuccess) { cudaGetLastError(); return HSFM_BA_ERR_NOMEM; }
+    W.cap = need + need / 4;
+  }
+  char* b = W.buf;
+  auto take = [&](size_t bytes) { char* p = b; b += bytes; return p; };
+  unsigned long long* keys = (unsigned long long*)take(n8);
+  unsigned long long* sorted = (unsigned long long*)take(n8);
+  unsigned long long* uniq = (unsigned long long*)take(n8);
+  int* iota = (int*)take(n4);
+  int* src = (int*)take(n4);
+  int* head = (int*)take(n4);
+  int* incl = (int*)take(n4);
+  int* pt_idx = (int*)take(n4);
+  void* d_tmp = take(tmp);
+  HSFM_CUDA(cudaMemcpyAsync(keys, host_ptrs, sizeof(unsigned long long) * (size_t)n, cudaMemcpyHostToDevice, s));
+  iota_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, iota);
+  size_t tb = tmp;
+  cub::DeviceRadixSort::SortPairs(d_tmp, tb, keys, sorted, iota, src, n, 0, 48, s);
+  ptr_heads_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, sorted, head);
+  tb = tmp;
+  cub::DeviceScan::InclusiveSum(d_tmp, tb, head, incl, n, s);
+  ptr_ids_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, sorted, src, head, incl, pt_idx, uniq);
+  int n_uniq = 0;
+  unsigned long long first = 0;
+  HSFM_CUDA(cudaMemcpyAsync(&n_uniq, incl + (n - 1), sizeof(int), cudaMemcpyDeviceToHost, s));
+  HSFM_CUDA(cudaMemcpyAsync(&first, sorted, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+  HSFM_CUDA(cudaStreamSynchronize(s));
+  if (first == 0ull) return HSFM_BA_ERR_ARG;  // a NULL point pointer (sorted first)
+  if (W.uniq_cap < (size_t)n_uniq) {
+    if (W.uniq_host) cudaFreeHost(W.uniq_host);
+    W.uniq_host = nullptr; W.uniq_cap = 0;
+    const size_t want = (size_t)n_uniq + (size_t)n_uniq / 4 + 1024;
+    HSFM_CUDA(cudaMallocHost(&W.uniq_host, sizeof(unsigned long long) * want));
+    W.uniq_cap = want;
+  }
+  HSFM_CUDA(cudaMemcpyAsync(W.uniq_host, uniq, sizeof(unsigned long long) * (size_t)n_uniq, cudaMemcpyDeviceToHost, s));
+  HSFM_CUDA(cudaStreamSynchronize(s));
+  uniq_out.resize((size_t)n_uniq);
+  for (int k = 0; k < n_uniq; ++k) uniq_out[(size_t)k] = reinterpret_cast<double*>(W.uniq_host[k]);
+  *d_pt_idx_out = pt_idx;
+  return 0;
+}
+
 int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
                   int32_t n_cams, const double* K9, const double* dist, const double* cam_rt, int64_t n_pts64, const double* pts,
                   Comm& comm, cudaStream_t s, double* setup_ms, double* h2d_ms, bool natural_order) {

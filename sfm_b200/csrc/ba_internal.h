@@ -281,6 +281,19 @@ struct ScanStore {
   void destroy();
 };
 
+// Pointer identity -> compact point ids ON THE DEVICE (hsfm_ba_solve_ptr; CSfM.cpp:331 / CMap.cpp:215: the same
+// double* repeated for every observation of a map point).  Grow-only scratch, kept across the per-keyframe calls.
+struct PtrScratch {
+  char* buf = nullptr;
+  size_t cap = 0;
+  unsigned long long* uniq_host = nullptr;  // pinned [uniq_cap]
+  size_t uniq_cap = 0;
+  void destroy();
+};
+// d_pt_idx_out: device array [n] of compact ids (valid until the next call), ids in ascending pointer order;
+// uniq_out: the distinct pointers by id.  HSFM_BA_ERR_ARG when a pointer is NULL.
+int dedupe_pointers(PtrScratch& W, int64_t n, double* const* host_ptrs, int** d_pt_idx_out, std::vector<double*>& uniq_out, cudaStream_t s);
+
 struct Ctx {
   int device = 0;
   cudaStream_t own_stream = nullptr;
@@ -295,6 +308,7 @@ struct Ctx {
   bool tap_upload = false;  // upload on behalf of a parity tap: caller's camera order
   std::vector<cudaEvent_t> phase_events;  // pool reused across solves (phase timing of lm_solve)
   ScanStore scan;
+  PtrScratch ptr_ws;
 };
 // ba_scan.cu
 int scan_begin(Ctx& c, int mode, int64_t n_obs, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx, int32_t n_cams,

@@ -237,6 +237,12 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
     const CholPlan& pl = ctx.chol_plan;
     S.chol_panels = (n6 + 127) / 128;
     S.chol_critical_panels = S.chol_panels;
+    const double b3 = 128.0 * 128.0 * 128.0;
+    S.chol_flops = (double)n6 * n6 * n6 / 3.0;
+    if (!(o.dense_flags & 1) && pl.use) {
+      S.chol_flops = 0.0;
+      for (int K = 0; K < pl.panels; ++K) S.chol_flops += b3 / 3.0 + pl.cnt[K] * b3 + (double)pl.cnt[K] * (pl.cnt[K] + 1) * b3;
+    }
     if (!(o.dense_flags & 1) && pl.use && pl.split_a > 0) S.chol_critical_panels = std::max(pl.split_a, pl.split_t0 - pl.split_a) + (pl.panels - pl.split_t0);
   }
 

@@ -41,7 +41,7 @@ def test_struct_layout_and_defaults(lib):
 
     assert C.sizeof(Options) == 8 * 4 + 10 * 8
     assert C.sizeof(Iteration) == 7 * 8 + 4 * 4
-    assert C.sizeof(Summary) == 3 * 8 + 6 * 4 + 8 + 4 * 8 + 8 + 2 * 4 + 8 * 8 + 8 + 4 * 4
+    assert C.sizeof(Summary) == 3 * 8 + 6 * 4 + 8 + 4 * 8 + 8 + 2 * 4 + 8 * 8 + 8 + 4 * 4 + 8
     o = api.default_options()
     # ceres::Solver::Options defaults; the reference overrides only the linear solver
     assert (o.max_num_iterations, o.max_consecutive_invalid_steps, o.jacobi_scaling) == (50, 5, 1)
