@@ -200,6 +200,7 @@ int hsfm_ba_problem_upload(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double
   HSFM_CUDA(cudaSetDevice(h->c.device));
   h->c.has_problem = false;
   h->c.chol_plan_valid = false;
+  h->c.form_valid = false;
   h->c.scan.active = false;  // the resident problem no longer is the scan store's
   double setup = 0, h2d = 0;
   const bool natural = h->c.ordering == 1 || h->c.tap_upload;

@@ -1569,6 +1569,7 @@ int CholAux::init() {
   HSFM_CUDA(cudaEventCreateWithFlags(&chainB.ev_next, cudaEventDisableTiming));
   HSFM_CUDA(cudaEventCreateWithFlags(&chainB.ev_rest, cudaEventDisableTiming));
   HSFM_CUDA(cudaEventCreateWithFlags(&chainB.ev_done, cudaEventDisableTiming));
+  HSFM_CUDA(cudaStreamCreateWithPriority(&form_stream, cudaStreamNonBlocking, lo));
   return 0;
 }
 void CholAux::destroy() {
@@ -1585,6 +1586,12 @@ void CholAux::destroy() {
   if (chainB.ev_done) cudaEventDestroy(chainB.ev_done);
   chainB = CholChain();
   ev_doneA = nullptr;
+  if (form_stream) cudaStreamDestroy(form_stream);
+  form_stream = nullptr;
+  for (cudaEvent_t e : ev_form) cudaEventDestroy(e);
+  ev_form.clear();
+  if (form_counters) cudaFree(form_counters);
+  form_counters = nullptr; form_counters_cap = 0;
   stream = nullptr;
 }
 
@@ -1731,8 +1738,10 @@ struct ChainStreams {
   bool la;  // chain and bulk are different streams
 };
 static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainStreams& cs, int64_t* launches, const CholPlan& pl, int n_sm,
-                      int K_begin, int K_end, int own_end, double* Ctail, cudaEvent_t start_ev) {
+                      int K_begin, int K_end, int own_end, double* Ctail, cudaEvent_t start_ev, const FormSchedule* form = nullptr,
+                      const std::vector<cudaEvent_t>* ev_form = nullptr) {
   const bool la = cs.la;
+  int form_waited = -1;  // chunks of the fused formation of S this chain has already waited for
   cudaStream_t s = cs.bulk, s2 = cs.chain;
   const int ldt = (pl.panels - own_end) * NB;
   auto trsm = [&](cudaStream_t st, int k0, double* Linv, const int* list, int cnt) {
@@ -1763,6 +1772,11 @@ static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainS
   for (int K = K_begin, k0 = K_begin * NB; K < K_end; ++K, k0 += NB) {
     const int kb = min(NB, n - k0);
     double* Linv = ws + (size_t)K * NB * NB;
+    if (form && form->need_chunk[(size_t)K] > form_waited) {
+      // every column of S this panel step reads or writes must have received all its contributions
+      form_waited = form->need_chunk[(size_t)K];
+      cudaStreamWaitEvent(s2, (*ev_form)[(size_t)form_waited], 0);
+    }
     {
       cudaLaunchConfig_t cfg = chain_cfg(1, 256, kDiagSmem);
       cudaLaunchKernelEx(&cfg, chol_diag_kernel, S, n, k0, kb, Linv, fail_flag);
@@ -1829,16 +1843,19 @@ static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainS
 }
 
 // S[tail, tail] += T over the lower block triangle of the tail (row blocks >= t0): the join of the two-chain schedule.
-__global__ void __launch_bounds__(256) tail_add_kernel(double* __restrict__ S, int n, int t0, const double* __restrict__ T, int ldt) {
+__global__ void __launch_bounds__(256) tail_add_kernel(double* __restrict__ S, int n, int t0, const double* __restrict__ T, int ldt,
+                                                       const double* __restrict__ T2) {
   const int r = t0 * NB + blockIdx.x;  // matrix row
   if (r >= n) return;
   const int c_end = min(n, (r / NB + 1) * NB) - t0 * NB;  // columns up to the end of the row's diagonal block
   double2* dst = reinterpret_cast<double2*>(S + (size_t)r * n + (size_t)t0 * NB);
   const double2* src = reinterpret_cast<const double2*>(T + (size_t)blockIdx.x * ldt);
+  const double2* src2 = T2 ? reinterpret_cast<const double2*>(T2 + (size_t)blockIdx.x * ldt) : nullptr;
   for (int e = threadIdx.x; e < c_end / 2; e += 256) {
     double2 v = dst[e];
     const double2 a = src[e];
     v.x += a.x; v.y += a.y;
+    if (src2) { const double2 b = src2[e]; v.x += b.x; v.y += b.y; }  // fixed order: S + T_A + T_B
     dst[e] = v;
   }
 }
@@ -1849,18 +1866,26 @@ __global__ void __launch_bounds__(256) tail_add_kernel(double* __restrict__ S, i
 // L11^-1 blocks in the workspace), which is added to S at the join — the two never write the same memory and the
 // summation order is fixed.
 static void launch_cholesky_struct(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches,
-                                   const CholPlan& pl, int n_sm) {
+                                   const CholPlan& pl, int n_sm, const FormSchedule* form) {
   static const bool no_la = getenv("HSFM_NO_LOOKAHEAD") != nullptr;
   const bool la = aux && aux->stream && !no_la;
   ChainStreams A{la ? aux->stream : s, s, la ? aux->ev_panel : nullptr, la ? aux->ev_next : nullptr, la ? aux->ev_rest : nullptr, la};
   const bool two = la && pl.split_a > 0 && pl.split_t0 > pl.split_a && aux->chainB.chain;
+  const bool fused = two && form && form->use && aux->form_stream && aux->ev_form.size() >= form->chunk_tile0.size() && aux->form_counters;
+  const int nt = (pl.panels - pl.split_t0) * NB;  // order of the tail
   double* T = ws + cholesky_workspace_doubles(n);
-  if (two) cudaMemsetAsync(T, 0, sizeof(double) * (size_t)pl.tail_doubles(), s);
+  double* T_B = T + (size_t)nt * nt;
+  if (two) cudaMemsetAsync(T, 0, sizeof(double) * (size_t)nt * nt * (fused ? 2 : 1), s);
+  if (form && form->use) cudaMemsetAsync(aux->form_counters, 0, sizeof(int) * form->chunk_tile0.size(), s);
   if (la) {
     cudaEventRecord(aux->ev_fork, s);
     cudaStreamWaitEvent(A.chain, aux->ev_fork, 0);
   }
   if (!two) {
+    if (form && form->use) {  // no second chain after all: form S in one go, then factor
+      for (size_t g = 0; g < form->chunk_tile0.size(); ++g) { form->launch_chunk(form->chunk_tile0[g], form->chunk_count[g], aux->form_counters + g, s); ++*launches; }
+      if (la) { cudaEventRecord(aux->ev_fork, s); cudaStreamWaitEvent(A.chain, aux->ev_fork, 0); }
+    }
     run_chain(S, n, ws, fail_flag, A, launches, pl, n_sm, 0, pl.panels, pl.panels, nullptr, nullptr);
   } else {
     const CholChain& cb = aux->chainB;
@@ -1868,16 +1893,35 @@ static void launch_cholesky_struct(double* S, int n, double* ws, int* fail_flag,
     cudaStreamWaitEvent(B.chain, aux->ev_fork, 0);
     cudaStreamWaitEvent(B.bulk, aux->ev_fork, 0);
     const int a = pl.split_a, t0 = pl.split_t0;
-    run_chain(S, n, ws, fail_flag, A, launches, pl, n_sm, 0, a, t0, T, nullptr);
-    run_chain(S, n, ws, fail_flag, B, launches, pl, n_sm, a, t0, pl.panels, nullptr, nullptr);
-    // join: s (= A.bulk) waits for A.chain, B.chain and B.bulk
+    if (fused) {
+      // S is formed chunk by chunk on its own stream; the chains follow the frontier (run_chain waits per panel)
+      cudaStream_t fs = aux->form_stream;
+      cudaStreamWaitEvent(fs, aux->ev_fork, 0);
+      for (size_t g = 0; g < form->chunk_tile0.size(); ++g) {
+        form->launch_chunk(form->chunk_tile0[g], form->chunk_count[g], aux->form_counters + g, fs);
+        ++*launches;
+        cudaEventRecord(aux->ev_form[g], fs);
+      }
+    } else if (form && form->use) {
+      for (size_t g = 0; g < form->chunk_tile0.size(); ++g) { form->launch_chunk(form->chunk_tile0[g], form->chunk_count[g], aux->form_counters + g, s); ++*launches; }
+      cudaEventRecord(aux->ev_fork, s);
+      cudaStreamWaitEvent(A.chain, aux->ev_fork, 0);
+      cudaStreamWaitEvent(B.chain, aux->ev_fork, 0);
+      cudaStreamWaitEvent(B.bulk, aux->ev_fork, 0);
+    }
+    run_chain(S, n, ws, fail_flag, A, launches, pl, n_sm, 0, a, t0, T, nullptr, fused ? form : nullptr, &aux->ev_form);
+    // chain B: into S directly — or, while S is still being formed beside it, into its own side matrix like chain A
+    run_chain(S, n, ws, fail_flag, B, launches, pl, n_sm, a, t0, fused ? t0 : pl.panels, fused ? T_B : nullptr, nullptr, fused ? form : nullptr,
+              &aux->ev_form);
+    // join: s (= A.bulk) waits for A.chain, B.chain, B.bulk and the formation stream
     cudaEventRecord(aux->ev_doneA, A.chain);
     cudaStreamWaitEvent(s, aux->ev_doneA, 0);
     cudaEventRecord(cb.ev_panel, B.chain);
     cudaStreamWaitEvent(B.bulk, cb.ev_panel, 0);
     cudaEventRecord(cb.ev_done, B.bulk);
     cudaStreamWaitEvent(s, cb.ev_done, 0);
-    tail_add_kernel<<<n - t0 * NB, 256, 0, s>>>(S, n, t0, T, (pl.panels - t0) * NB);
+    if (fused && !form->chunk_tile0.empty()) cudaStreamWaitEvent(s, aux->ev_form[form->chunk_tile0.size() - 1], 0);
+    tail_add_kernel<<<n - t0 * NB, 256, 0, s>>>(S, n, t0, T, nt, fused ? T_B : nullptr);
     ++*launches;
     cudaEventRecord(aux->ev_fork, s);
     run_chain(S, n, ws, fail_flag, A, launches, pl, n_sm, t0, pl.panels, pl.panels, nullptr, aux->ev_fork);
@@ -1888,7 +1932,84 @@ static void launch_cholesky_struct(double* S, int n, double* ws, int* fail_flag,
   }
 }
 
-void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches, const CholPlan* plan) {
+// Which chunks of tiles must be done before each panel step (see FormSchedule, ba_internal.h).
+void build_form_schedule(const CholPlan& pl, const Problem& P, int n_sm, FormSchedule& F) {
+  F.use = false;
+  F.chunk_tile0.clear(); F.chunk_count.clear(); F.need_chunk.clear();
+  // Measured at Venice shape (profiles/r02_fused_formation.md): the chunked formation does run beside the chains, but its
+  // FP64 atomics saturate the L2 slices the latency-bound chain kernels wait on — the chains slow down by what the overlap
+  // gains (3.57 ms against 1.41 + 2.27 = 3.68 ms in sequence).  Kept as an experiment knob, off by default.
+  static const bool off = getenv("HSFM_FUSED_FORM") == nullptr;
+  const int nT = P.n_tiles;
+  if (off || !pl.use || pl.split_a <= 0 || P.split_cams <= 0 || P.tail_cams <= P.split_cams || (int)P.h_tile_cmin.size() != nT || nT == 0) return;
+  const std::vector<int>& cm = P.h_tile_cmin;
+  // regions of the tile order: A = points whose smallest camera is in chain A, B = ... in chain B, tail.  The tile
+  // that straddles A | B goes to B (it may hold points of both; chain A's last columns then wait for B's first chunk).
+  const int tA = (int)(std::lower_bound(cm.begin(), cm.end(), P.split_cams) - cm.begin());
+  const int tB = (int)(std::lower_bound(cm.begin(), cm.end(), P.tail_cams) - cm.begin());
+  const int bA = std::max(tA - 1, 0);
+  static const int chunk_env = getenv("HSFM_FORM_CHUNK") ? atoi(getenv("HSFM_FORM_CHUNK")) : 0;
+  const int CH = chunk_env > 0 ? chunk_env : 8 * n_sm;  // a few waves of the SM-affine formation kernel per chunk
+  std::vector<int> order((size_t)nT, 0);
+  auto push = [&](int t0, int t1) {
+    F.chunk_tile0.push_back(t0); F.chunk_count.push_back(t1 - t0);
+    for (int t = t0; t < t1; ++t) order[(size_t)t] = (int)F.chunk_tile0.size() - 1;
+  };
+  int pa = 0, pb = bA;  // next tile of region A / B: interleave so that both regions finish together
+  while (pa < bA || pb < tB) {
+    const double fa = bA > 0 ? (double)pa / bA : 2.0, fb = tB > bA ? (double)(pb - bA) / (tB - bA) : 2.0;
+    if (pa < bA && (fa <= fb || pb >= tB)) { const int e = std::min(bA, pa + CH); push(pa, e); pa = e; }
+    else { const int e = std::min(tB, pb + CH); push(pb, e); pb = e; }
+  }
+  for (int t = tB; t < nT; t += CH) push(t, std::min(nT, t + CH));
+  const int last = (int)F.chunk_tile0.size() - 1;
+  // prefix maxima of the launch order: over [0, t) and over [bA, t)
+  std::vector<int> pm_all((size_t)nT + 1, -1), pm_b((size_t)nT + 1, -1);
+  for (int t = 0; t < nT; ++t) {
+    pm_all[(size_t)t + 1] = std::max(pm_all[(size_t)t], order[(size_t)t]);
+    pm_b[(size_t)t + 1] = t >= bA ? std::max(pm_b[(size_t)t], order[(size_t)t]) : -1;
+  }
+  F.need_chunk.assign((size_t)pl.panels, last);
+  for (int K = 0; K < pl.split_t0; ++K) {
+    int maxcol = K;
+    for (int q = 0; q < pl.cnt[(size_t)K]; ++q) {
+      const int I = pl.list[(size_t)pl.off[(size_t)K] + q];
+      if (I < pl.split_t0) maxcol = std::max(maxcol, I);
+    }
+    const int lastcam = std::min(P.n_cams - 1, (NB * maxcol + NB - 1) / 6);
+    const int ub = (int)(std::upper_bound(cm.begin(), cm.end(), lastcam) - cm.begin());  // tiles [0, ub) have cmin <= lastcam
+    if (lastcam >= P.tail_cams) F.need_chunk[(size_t)K] = last;
+    else if (K >= pl.split_a) F.need_chunk[(size_t)K] = pm_b[(size_t)ub];  // chain B: points of region A never touch its columns
+    else F.need_chunk[(size_t)K] = pm_all[(size_t)ub];
+  }
+  F.use = true;
+  if (getenv("HSFM_FORM_DEBUG")) {
+    std::fprintf(stderr, "[form] tiles %d (A [0,%d) B [%d,%d) tail [%d,%d)), %d chunks of <= %d; panels %d a %d t0 %d; split_cams %d tail_cams %d\n", nT, bA, bA, tB, tB,
+                 nT, (int)F.chunk_tile0.size(), CH, pl.panels, pl.split_a, pl.split_t0, P.split_cams, P.tail_cams);
+    for (int K = 0; K < pl.panels; ++K) std::fprintf(stderr, "%d:%d ", K, F.need_chunk[(size_t)K]);
+    std::fprintf(stderr, "\n");
+  }
+}
+
+// events and work counters of the fused formation: created outside any capture
+static void provision_form(CholAux* aux, const FormSchedule* form) {
+  if (!(form && form->use && aux && aux->form_stream)) return;
+  const int G = (int)form->chunk_tile0.size();
+  while ((int)aux->ev_form.size() < G) {
+    cudaEvent_t e;
+    if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) break;
+    aux->ev_form.push_back(e);
+  }
+  if (aux->form_counters_cap < G) {
+    if (aux->form_counters) cudaFree(aux->form_counters);
+    aux->form_counters = nullptr; aux->form_counters_cap = 0;
+    if (cudaMalloc(&aux->form_counters, sizeof(int) * (size_t)(G + 64)) == cudaSuccess) aux->form_counters_cap = G + 64;
+    else cudaGetLastError();
+  }
+}
+
+void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches, const CholPlan* plan,
+                     const FormSchedule* form) {
   const int n_sm = (aux && aux->n_sm > 0) ? aux->n_sm : 148;
   static int bulk_ctas = 0;
   if (!bulk_ctas) {
@@ -1902,17 +2023,19 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
     // capture it once and replay it as a CUDA graph — no host launch cost, tighter kernel-to-kernel hand-over.
     static const bool no_graph = getenv("HSFM_NO_GRAPH") != nullptr;  // experiment knob
     if (aux && aux->stream && !no_graph) {
+      provision_form(aux, form);
+      const std::string fkey = (form && form->use) ? form->key : std::string();
       const bool valid = aux->graph && aux->g_S == S && aux->g_ws == ws && aux->g_fail == fail_flag && aux->g_stream == (const void*)s &&
-                         aux->g_n == n && aux->g_version == plan->version;
+                         aux->g_n == n && aux->g_version == plan->version && aux->g_form_key == fkey;
       if (!valid) {
         if (aux->graph) { cudaGraphExecDestroy(aux->graph); aux->graph = nullptr; }
         cudaGraph_t g = nullptr;
         int64_t counted = 0;
         if (cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
-          launch_cholesky_struct(S, n, ws, fail_flag, s, aux, &counted, *plan, n_sm);
+          launch_cholesky_struct(S, n, ws, fail_flag, s, aux, &counted, *plan, n_sm, form);
           if (cudaStreamEndCapture(s, &g) == cudaSuccess && g && cudaGraphInstantiate(&aux->graph, g, 0) == cudaSuccess) {
             aux->g_S = S; aux->g_ws = ws; aux->g_fail = fail_flag; aux->g_stream = (const void*)s; aux->g_n = n;
-            aux->g_version = plan->version; aux->g_launches = counted;
+            aux->g_version = plan->version; aux->g_launches = counted; aux->g_form_key = fkey;
           } else {
             aux->graph = nullptr;
           }
@@ -1926,7 +2049,8 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
       }
       cudaGetLastError();
     }
-    launch_cholesky_struct(S, n, ws, fail_flag, s, aux, launches, *plan, n_sm);
+    provision_form(aux, form);
+    launch_cholesky_struct(S, n, ws, fail_flag, s, aux, launches, *plan, n_sm, form);
     return;
   }
   const int panels = (n + NB - 1) / NB;

@@ -381,7 +381,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   if (h2d_ms) *h2d_ms = t_setup0 - t_h2d0;
 
   // ---- internal camera order (ba_order.cpp): a band is eliminated from both ends at once ----
-  if (want_structure && !natural_order && choose_camera_order(n_cams, P.cam_first.data(), P.h_cam_new_of_old, &P.split_cams)) {
+  if (want_structure && !natural_order && choose_camera_order(n_cams, P.cam_first.data(), P.h_cam_new_of_old, &P.split_cams, &P.tail_cams)) {
     int* cam_tmp;
     ALLOC(P.cam_new_of_old, n_cams); ALLOC(P.cam_old_of_new, n_cams); ALLOC(cam_tmp, n); ALLOC(P.cam_io, 9 * (size_t)n_cams);
     HSFM_CUDA(cudaMemcpyAsync(P.cam_new_of_old, P.h_cam_new_of_old.data(), sizeof(int) * (size_t)n_cams, cudaMemcpyHostToDevice, s));
@@ -397,6 +397,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   } else {
     P.h_cam_new_of_old.clear();
     P.split_cams = -1;
+    P.tail_cams = -1;
   }
   HSFM_CUDA(cudaMemcpyAsync(P.cam_x, P.cam_x0, sizeof(double) * 6 * n_cams, cudaMemcpyDeviceToDevice, s));
 
@@ -519,6 +520,11 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     HSFM_CUDA(cudaMemsetAsync(d_max_ncam, 0, sizeof(int), s));
     tile_cams_kernel<<<P.n_tiles, TILE, 0, s>>>(tile_start, cam, slot, tile_cams, tile_hdr, d_max_ncam);
     HSFM_CUDA(cudaMemcpyAsync(&P.max_tile_cams, d_max_ncam, sizeof(int), cudaMemcpyDeviceToHost, s));
+    P.h_tile_cmin.clear();
+    if (want_structure) {  // first entry of every tile's ascending camera list
+      P.h_tile_cmin.resize((size_t)P.n_tiles);
+      HSFM_CUDA(cudaMemcpy2DAsync(P.h_tile_cmin.data(), sizeof(int), tile_cams, sizeof(int) * TILE, sizeof(int), (size_t)P.n_tiles, cudaMemcpyDeviceToHost, s));
+    }
     HSFM_CUDA(cudaStreamSynchronize(s));  // hdr is a local vector; max_tile_cams is needed by the launches
   }
 

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <functional>
 #include <string>
 #include <vector>
 
@@ -65,6 +66,8 @@ struct Problem {
   int* cam_new_of_old = nullptr;  // device [n_cams]
   int* cam_old_of_new = nullptr;  // device [n_cams]
   int split_cams = -1;            // first internal camera of the second chain (two-ended order) or -1
+  int tail_cams = -1;             // first internal camera of the tail (cameras coupled to both chains) or -1
+  std::vector<int> h_tile_cmin;   // [n_tiles] smallest internal camera of every tile (tiles are ordered by it): which columns of S a prefix of tiles completes
   double* cam_io = nullptr;       // [n_cams][9] staging in the caller's camera order (upload / download / taps)
   Dev d{};
   // Device arena: ONE grow-only allocation per context that every per-problem buffer is carved from, so the
@@ -178,6 +181,8 @@ void launch_pcg_step(Problem& P, double tol, int max_it, cudaStream_t s);
 struct CholPlan;
 void launch_dense_init(Problem& P, bool with_diag, cudaStream_t s, const CholPlan* plan = nullptr);  // S = 0 (+ blockdiag(Hcc + D^2)); plan: zero the envelope only
 void launch_dense_schur(Problem& P, cudaStream_t s, bool sorted_pairs = true);    // S -= sum_p W Hpp^-1 W^T (lower block triangle)
+bool dense_schur_prepare(Problem& P, cudaStream_t s);  // sorted pair lists ready?
+void launch_dense_schur_chunk(const Problem& P, int tile0, int count, int* counter, int reserve_mod, cudaStream_t s);  // tiles [tile0, tile0+count), sorted, SM-affine
 void launch_scatter_eval(Problem& P, double* r_out, double* jac_out, cudaStream_t s);  // back to input order, Ceres layout
 void launch_export_blocks(Problem& P, double* Hcc36, double* Hpp9, cudaStream_t s);  // parity tap (adds LM diagonal)
 void launch_mirror_lower(Problem& P, cudaStream_t s);   // S upper <- lower (parity tap)
@@ -186,6 +191,20 @@ void launch_mirror_lower(Problem& P, cudaStream_t s);   // S upper <- lower (par
 // In-place lower Cholesky of row-major n×n S (lower triangle read/written); *fail_flag set to
 // non-zero on a non-positive pivot.  Then solve S y = b in place in b.
 // auxiliary high-priority stream + events for the panel look-ahead of the factorisation
+// Formation of S fused into the factorisation (two-chain schedule, one GPU): S is formed in CHUNKS of point-major tiles on
+// its own stream while the panel chains already factor the columns that are complete.  Tiles are ordered by their
+// smallest internal camera and a block (ci, cj), cj <= ci, only receives contributions from points whose smallest
+// camera is <= cj: once every tile with smallest camera <= c is done, all columns of S up to camera c are final.
+// A panel step of a chain may run as soon as the columns it reads AND writes (its own columns; tail columns go to the
+// chains' side matrices) are final — need_chunk[K].  Built per problem by build_form_schedule (ba_chol.cu).
+struct FormSchedule {
+  bool use = false;
+  std::vector<int> chunk_tile0, chunk_count;  // in launch order
+  std::vector<int> need_chunk;                // [panels] index (launch order) of the last chunk panel K waits for; -1: none
+  std::function<void(int tile0, int count, int* counter, cudaStream_t s)> launch_chunk;  // counter: zeroed device int of the chunk
+  std::string key;                            // bytes of everything the chunk launches bake into a captured graph
+};
+
 struct CholChain {  // streams + events of one panel chain of the structured factorisation
   cudaStream_t chain = nullptr;  // high priority: diagonal blocks and next-diagonal-tile kernels
   cudaStream_t bulk = nullptr;   // panel solves and trailing updates, one step behind
@@ -196,6 +215,11 @@ struct CholAux {
   cudaEvent_t ev_fork = nullptr, ev_panel = nullptr, ev_rest = nullptr, ev_join = nullptr, ev_next = nullptr;
   CholChain chainB;        // second chain of the two-ended schedule (the first one runs on `stream` + the caller's stream)
   cudaEvent_t ev_doneA = nullptr;
+  cudaStream_t form_stream = nullptr;   // the experimental chunked formation of S beside the chains (FormSchedule)
+  std::vector<cudaEvent_t> ev_form;     // one per chunk, grown on demand (outside graph capture)
+  int* form_counters = nullptr;         // device: one work counter per chunk
+  int form_counters_cap = 0;
+  std::string g_form_key;
   // captured launch sequence of the envelope factorisation (static per problem: same S, workspace and plan)
   cudaGraphExec_t graph = nullptr;
   const void* g_S = nullptr; const void* g_ws = nullptr; const void* g_fail = nullptr; const void* g_stream = nullptr;
@@ -235,19 +259,21 @@ struct CholPlan {
   std::vector<uint8_t> key;    // the pattern the plan was built from: an unchanged structure keeps plan, version and graph
   long long packed_doubles() const { return blk_off.empty() ? 0 : blk_off.back(); }
   // side matrix of the two-chain schedule: the tail blocks [split_t0, panels), square, after the L11^-1 blocks in the workspace
-  long long tail_doubles() const { return (use && split_a > 0) ? (long long)(panels - split_t0) * 128 * (panels - split_t0) * 128 : 0; }
+  // (two of them: one per chain when the formation of S runs beside the chains)
+  long long tail_doubles() const { return (use && split_a > 0) ? 2ll * (panels - split_t0) * 128 * (panels - split_t0) * 128 : 0; }
   // pattern: P x P bytes, lower triangle, NOT yet closed under elimination (nullptr = dense); split_hint: first panel of the second chain or -1
   int build(int n_cams, const uint8_t* pattern, int P, int split_hint, cudaStream_t s);
   bool compute(int n_cams, const uint8_t* pattern, int P, int split_hint);  // host part only (no device); false: unchanged
   void destroy();
 };
 // host-side structure code (ba_order.cpp)
-bool choose_camera_order(int n_cams, const int* first, std::vector<int>& new_of_old, int* split_cams);
+bool choose_camera_order(int n_cams, const int* first, std::vector<int>& new_of_old, int* split_cams, int* tail_cams = nullptr);
 void block_pattern_from_envelope(int n_cams, const int* first, const int* new_of_old, std::vector<uint8_t>& pattern, int* panels);
 void symbolic_block_factor(int P, std::vector<uint8_t>& pattern);
 size_t cholesky_workspace_doubles(int n);  // L11^-1 blocks (one 128×128 per panel) + flags of the cooperative triangular solve
 void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches,
-                     const CholPlan* plan = nullptr);
+                     const CholPlan* plan = nullptr, const FormSchedule* form = nullptr);
+void build_form_schedule(const CholPlan& pl, const Problem& P, int n_sm, FormSchedule& F);  // F.launch_chunk / F.key are set by the caller
 void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream_t s, int64_t* launches, const CholAux* aux,
                        const CholPlan* plan = nullptr);
 
@@ -302,6 +328,8 @@ struct Ctx {
   CholAux chol_aux;
   CholPlan chol_plan;     // envelope plan of the resident problem (built on first dense solve)
   bool chol_plan_valid = false;
+  FormSchedule form;      // fused formation of S (built on first dense solve of a two-chain problem)
+  bool form_valid = false;
   Problem prob;
   bool has_problem = false;
   int ordering = 0;         // 0 = automatic camera order, 1 = the caller's (hsfm_ba_set_ordering)

@@ -97,10 +97,10 @@ struct TileThread {
   bool valid;
 };
 
-__device__ __forceinline__ TileThread tile_thread(const Dev& d) {
+__device__ __forceinline__ TileThread tile_thread(const Dev& d, int tile) {
   TileThread t;
-  t.tile_b = __ldg(d.tile_start + blockIdx.x);
-  t.tile_e = __ldg(d.tile_start + blockIdx.x + 1);
+  t.tile_b = __ldg(d.tile_start + tile);
+  t.tile_e = __ldg(d.tile_start + tile + 1);
   t.i = t.tile_b + (int)threadIdx.x;
   t.valid = t.i < t.tile_e;
   t.p = t.valid ? __ldg(d.pt + t.i) : 0;
@@ -108,6 +108,7 @@ __device__ __forceinline__ TileThread tile_thread(const Dev& d) {
   t.seg_e = t.valid ? __ldg(d.pt_start + t.p + 1) : 0;
   return t;
 }
+__device__ __forceinline__ TileThread tile_thread(const Dev& d) { return tile_thread(d, (int)blockIdx.x); }
 
 // ------------------------------------------------------------------------------------------
 __global__ void cam_prep_kernel(int n_cams, const double* __restrict__ cam, const double* __restrict__ K9,
@@ -997,8 +998,9 @@ __global__ void dense_init_kernel(int n_cams, const double* __restrict__ Hcc, co
 constexpr int kDenseSchurSmem = TILE * 36 * (int)sizeof(double) + (3 * TILE + 8) * (int)sizeof(int) + 8 * 8 * 36 * (int)sizeof(double) + 8 * 8 * (int)sizeof(long long);
 // The sorted path runs 16 warps on a tile (512 threads; the first 256 stage the tile's observations), each with four
 // staging slots: twice the warps per SM at the same shared-memory footprint — the pair loop is latency-bound.
+// tile0: first tile of the launch (the fused formation + factorisation schedule forms S in chunks of tiles, ba_chol.cu).
 template <bool SORTED>
-__global__ void __launch_bounds__(SORTED ? 2 * TILE : TILE, 2) dense_schur_kernel(Dev d, const double* __restrict__ Hpp_inv, double* __restrict__ S) {
+__device__ __forceinline__ void dense_schur_tile(const Dev& d, const double* __restrict__ Hpp_inv, double* __restrict__ S, const int tile) {
   extern __shared__ __align__(16) unsigned char ds_raw[];
   double (*sA)[18] = reinterpret_cast<double (*)[18]>(ds_raw);
   double (*sW)[18] = reinterpret_cast<double (*)[18]>(ds_raw + TILE * 18 * sizeof(double));
@@ -1006,7 +1008,7 @@ __global__ void __launch_bounds__(SORTED ? 2 * TILE : TILE, 2) dense_schur_kerne
   int* sOff = sCam + TILE;      // exclusive pair offsets per observation
   int* sSeg = sOff + TILE;      // tile-local index of the first observation of the point
   int* sWarpTot = sSeg + TILE;  // [8]
-  const TileThread t = tile_thread(d);
+  const TileThread t = tile_thread(d, tile);
   const size_t n = (size_t)d.n_obs;
   if (t.valid) {
     double jc[12], jp[6], W[18], Hi[6];
@@ -1101,8 +1103,8 @@ __global__ void __launch_bounds__(SORTED ? 2 * TILE : TILE, 2) dense_schur_kerne
     // The tile's pairs come from the static list SORTED BY DESTINATION BLOCK (ba_index / tile_pairs_kernel): a
     // warp walks a contiguous piece of the list and keeps accumulating into the same tensor-core fragment while
     // the destination stays the same, so the ~2.1 pairs per distinct block of a tile cost one reduction, not 2.1.
-    const int p_off = __ldg(d.pair_off + blockIdx.x);
-    const int n_pairs = __ldg(d.pair_off + blockIdx.x + 1) - p_off;
+    const int p_off = __ldg(d.pair_off + tile);
+    const int n_pairs = __ldg(d.pair_off + tile + 1) - p_off;
     const unsigned* __restrict__ list = d.pair_list + p_off;
     const int chunk = (n_pairs + NW - 1) / NW;
     const int beg = warp * chunk, end = min(n_pairs, beg + chunk);
@@ -1212,6 +1214,34 @@ __global__ void __launch_bounds__(SORTED ? 2 * TILE : TILE, 2) dense_schur_kerne
       if (frag_ok) *reinterpret_cast<double2*>(sC + pl * 36 + fr * 6 + 2 * fk) = make_double2(c0, c1);
     }
     reduce_staged(cnt);
+  }
+}
+
+template <bool SORTED>
+__global__ void __launch_bounds__(SORTED ? 2 * TILE : TILE, 2) dense_schur_kernel(Dev d, const double* __restrict__ Hpp_inv, double* __restrict__ S, int tile0) {
+  dense_schur_tile<SORTED>(d, Hpp_inv, S, (int)blockIdx.x + tile0);
+}
+
+// The same formation for the schedule that forms S BESIDE the factorisation (FormSchedule, ba_chol.cu).  The panel chains
+// are latency chains: a diagonal-block kernel that shares its SM with sixteen formation warps runs ~1.6x slower, and the
+// chains then lose what the overlap gains.  So this variant keeps whole SMs free: CTAs that find themselves on a
+// reserved SM (%smid % reserve_mod == reserve_mod - 1) exit at once, the others take the tiles of the chunk from an
+// atomic counter.  The SMs they run on are full (2 x 96 KB of shared memory), so the chain / panel kernels can only be
+// placed on the reserved ones.
+__global__ void __launch_bounds__(2 * TILE, 2) dense_schur_affine_kernel(Dev d, const double* __restrict__ Hpp_inv, double* __restrict__ S, int tile0,
+                                                                         int count, int* __restrict__ counter, int reserve_mod) {
+  __shared__ int s_tile;
+  unsigned smid;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+  if (reserve_mod > 1 && (int)(smid % (unsigned)reserve_mod) == reserve_mod - 1) return;
+  for (;;) {
+    if (threadIdx.x == 0) s_tile = atomicAdd(counter, 1);
+    __syncthreads();
+    const int k = s_tile;
+    __syncthreads();
+    if (k >= count) return;
+    dense_schur_tile<true>(d, Hpp_inv, S, tile0 + k);
+    __syncthreads();
   }
 }
 
@@ -1365,6 +1395,7 @@ int init_kernel_attributes() {
   allow_stage_smem(cost_kernel);
   cudaFuncSetAttribute(dense_schur_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDenseSchurSmem);
   cudaFuncSetAttribute(dense_schur_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDenseSchurSmem);
+  cudaFuncSetAttribute(dense_schur_affine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDenseSchurSmem);
   const cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : 1000 + (int)e;
 }
@@ -1576,9 +1607,39 @@ void launch_dense_schur(Problem& P, cudaStream_t s, bool sorted_pairs) {
       P.pairs_ready = true;
     }
   }
-  if (P.pairs_ready && sorted_pairs) dense_schur_kernel<true><<<P.n_tiles, 2 * TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S);
-  else dense_schur_kernel<false><<<P.n_tiles, TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S);
+  if (P.pairs_ready && sorted_pairs) dense_schur_kernel<true><<<P.n_tiles, 2 * TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S, 0);
+  else dense_schur_kernel<false><<<P.n_tiles, TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S, 0);
   P.launches++;
+}
+
+// Builds the sorted pair lists if needed; true when the sorted kernel can run (what the chunked formation uses).
+bool dense_schur_prepare(Problem& P, cudaStream_t s) {
+  if (P.n_tiles == 0 || !P.d.pair_off) return false;
+  static const bool no_sort = getenv("HSFM_SCHUR_UNSORTED") != nullptr;
+  if (no_sort) return false;
+  if (!P.pairs_ready) {
+    const size_t need = (size_t)std::max<long long>(P.total_pairs, 1);
+    if (P.pair_capacity < need) {
+      if (P.pair_list) cudaFree(P.pair_list);
+      P.pair_list = nullptr; P.pair_capacity = 0;
+      if (cudaMalloc(&P.pair_list, sizeof(unsigned) * need) == cudaSuccess) P.pair_capacity = need;
+      else cudaGetLastError();
+    }
+    if (!P.pair_list) return false;
+    tile_pairs_kernel<<<P.n_tiles, TILE, 0, s>>>(P.d, P.pair_list);
+    P.launches++;
+    P.d.pair_list = P.pair_list;
+    P.pairs_ready = true;
+  }
+  return true;
+}
+// tiles [tile0, tile0 + count) of the sorted formation on the non-reserved SMs; counter: a zeroed device int of this chunk
+// (no launch accounting: the caller counts)
+void launch_dense_schur_chunk(const Problem& P, int tile0, int count, int* counter, int reserve_mod, cudaStream_t s) {
+  static const bool noop = getenv("HSFM_FORM_NOOP") != nullptr;  // timing experiment only (wrong results): the chunk kernels start and exit
+  if (noop) count = 1;
+  if (count > 0)
+    dense_schur_affine_kernel<<<std::min(count, 2 * P.n_sm), 2 * TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S, tile0, count, counter, reserve_mod);
 }
 
 void launch_mirror_lower(Problem& P, cudaStream_t s) {

@@ -35,9 +35,10 @@ constexpr int CAM_ALIGN = 64;  // 64 cameras = 384 rows = 3 panels: chain bounda
 
 // Decide the internal camera order from the caller-order envelope first[c] (smallest camera sharing a point with c).
 // Returns true and fills new_of_old when a reordering pays; *split_cams receives m (the first camera position of the
-// second chain) or -1.
-bool choose_camera_order(int n_cams, const int* first, std::vector<int>& new_of_old, int* split_cams) {
+// second chain) or -1, *tail_cams (optional) the first camera position of the tail.
+bool choose_camera_order(int n_cams, const int* first, std::vector<int>& new_of_old, int* split_cams, int* tail_cams) {
   *split_cams = -1;
+  if (tail_cams) *tail_cams = -1;
   new_of_old.clear();
   static const bool off = getenv("HSFM_NO_TWIST") != nullptr;  // experiment knob
   if (off || n_cams < 4 * CAM_ALIGN) return false;
@@ -72,6 +73,7 @@ bool choose_camera_order(int n_cams, const int* first, std::vector<int>& new_of_
   for (int c = n_cams - 1; c >= m; --c)
     if (in_tail[c]) new_of_old[c] = pos++;
   *split_cams = m;
+  if (tail_cams) *tail_cams = n_cams - n_tail;
   return true;
 }
 

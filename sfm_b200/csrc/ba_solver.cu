@@ -45,6 +45,25 @@ struct Driver {
   }
 
   bool multi() const { return ctx.comm.n_ranks > 1; }
+
+  // The fused formation schedule of the resident problem, built on first use (needs the sorted pair lists).
+  bool form_ready() {
+    FormSchedule& F = ctx.form;
+    if (ctx.form_valid) return F.use;
+    ctx.form_valid = true;
+    F.use = false;
+    if (!dense_schur_prepare(P, s)) return false;
+    build_form_schedule(ctx.chol_plan, P, ctx.chol_aux.n_sm, F);
+    if (!F.use) return false;
+    Problem* pp = &P;
+    static const int reserve_mod = getenv("HSFM_FORM_RESERVE") ? atoi(getenv("HSFM_FORM_RESERVE")) : 5;  // every 5th SM stays free for the chains
+    F.launch_chunk = [pp](int tile0, int count, int* counter, cudaStream_t st) { launch_dense_schur_chunk(*pp, tile0, count, counter, reserve_mod, st); };
+    // what a captured chunk launch bakes in: the Dev block (pointers and sizes), Hpp_inv and S
+    F.key.assign(reinterpret_cast<const char*>(&P.d), sizeof(P.d));
+    const void* extra[2] = {P.Hpp_inv, P.S};
+    F.key.append(reinterpret_cast<const char*>(extra), sizeof(extra));
+    return true;
+  }
   void chk(int r) { if (r && !rc) rc = r; }
 
   int read_back() {
@@ -95,8 +114,11 @@ struct Driver {
     if (P.mode == 2) {
       const bool lead = ctx.comm.rank == 0;
       if (dense) {
+        // One GPU, two-chain plan: S is formed in chunks INSIDE the factorisation's launch graph, beside the panel chains
+        // (FormSchedule); otherwise formed here, before the factorisation.
+        const bool fused = !multi() && !(o.dense_flags & 3) && ctx.chol_plan.use && ctx.chol_plan.n == n6 && form_ready();
         launch_dense_init(P, lead, s, (o.dense_flags & 1) ? nullptr : &ctx.chol_plan);
-        launch_dense_schur(P, s, !(o.dense_flags & 2));
+        if (!fused) launch_dense_schur(P, s, !(o.dense_flags & 2));
         launch_schur_rhs(P, lead, s);
         if (multi()) {
           const CholPlan& pl = ctx.chol_plan;
@@ -114,7 +136,8 @@ struct Driver {
           chk(ctx.comm.allreduce_sum(P.rhs, n6, s));
         }
         mark(2);
-        launch_cholesky(P.S, n6, P.S + (size_t)n6 * n6, P.flags + F_CHOL_FAIL, s, &ctx.chol_aux, &P.launches, (o.dense_flags & 1) ? nullptr : &ctx.chol_plan);
+        launch_cholesky(P.S, n6, P.S + (size_t)n6 * n6, P.flags + F_CHOL_FAIL, s, &ctx.chol_aux, &P.launches, (o.dense_flags & 1) ? nullptr : &ctx.chol_plan,
+                        fused ? &ctx.form : nullptr);
         mark(3);
         HSFM_CUDA(cudaMemcpyAsync(P.yc, P.rhs, sizeof(double) * n6, cudaMemcpyDeviceToDevice, s));
         launch_chol_solve(P.S, n6, P.S + (size_t)n6 * n6, P.yc, s, &P.launches, &ctx.chol_aux, (o.dense_flags & 1) ? nullptr : &ctx.chol_plan);
