@@ -1570,6 +1570,9 @@ int CholAux::init() {
   HSFM_CUDA(cudaEventCreateWithFlags(&chainB.ev_rest, cudaEventDisableTiming));
   HSFM_CUDA(cudaEventCreateWithFlags(&chainB.ev_done, cudaEventDisableTiming));
   HSFM_CUDA(cudaStreamCreateWithPriority(&form_stream, cudaStreamNonBlocking, lo));
+  HSFM_CUDA(cudaStreamCreateWithPriority(&tailA, cudaStreamNonBlocking, lo));
+  HSFM_CUDA(cudaStreamCreateWithPriority(&tailB, cudaStreamNonBlocking, lo));
+  for (cudaEvent_t* e : {&ev_trsmA, &ev_trsmB, &ev_tailA, &ev_tailB}) HSFM_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
   return 0;
 }
 void CholAux::destroy() {
@@ -1588,6 +1591,10 @@ void CholAux::destroy() {
   ev_doneA = nullptr;
   if (form_stream) cudaStreamDestroy(form_stream);
   form_stream = nullptr;
+  if (tailA) cudaStreamDestroy(tailA);
+  if (tailB) cudaStreamDestroy(tailB);
+  tailA = tailB = nullptr;
+  for (cudaEvent_t* e : {&ev_trsmA, &ev_trsmB, &ev_tailA, &ev_tailB}) { if (*e) cudaEventDestroy(*e); *e = nullptr; }
   for (cudaEvent_t e : ev_form) cudaEventDestroy(e);
   ev_form.clear();
   if (form_counters) cudaFree(form_counters);
@@ -1736,6 +1743,9 @@ struct ChainStreams {
   cudaStream_t chain, bulk;
   cudaEvent_t ev_panel, ev_next, ev_rest;
   bool la;  // chain and bulk are different streams
+  // updates of the side matrix (tail x tail pairs) need only the panel solve and are wanted only at the join: their own stream
+  cudaStream_t tail = nullptr;
+  cudaEvent_t ev_trsm = nullptr;
 };
 static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainStreams& cs, int64_t* launches, const CholPlan& pl, int n_sm,
                       int K_begin, int K_end, int own_end, double* Ctail, cudaEvent_t start_ev, const FormSchedule* form = nullptr,
@@ -1744,17 +1754,36 @@ static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainS
   int form_waited = -1;  // chunks of the fused formation of S this chain has already waited for
   cudaStream_t s = cs.bulk, s2 = cs.chain;
   const int ldt = (pl.panels - own_end) * NB;
+  // Grid caps of the panel solves / trailing updates: experiment knobs.  (Measured with two chains in flight, c4: capping
+  // them to 48 CTAs so that the other chain's kernels find empty SMs makes the factorisation SLOWER, 2.27 -> 3.0 ms: the
+  // bulk step, ~180 tiles of 8 us of DMMA issue each, is itself close to the panel period.)
+  static const int cap_syrk_env = getenv("HSFM_BULK_SYRK_CTAS") ? atoi(getenv("HSFM_BULK_SYRK_CTAS")) : 0;
+  static const int cap_trsm_env = getenv("HSFM_BULK_TRSM_CTAS") ? atoi(getenv("HSFM_BULK_TRSM_CTAS")) : 0;
+  const bool shared_gpu = pl.split_a > 0 && K_end <= pl.split_t0;  // one of the two concurrent chains
+  const int cap_syrk = cap_syrk_env > 0 ? cap_syrk_env : 2 * n_sm;
+  const int cap_trsm = cap_trsm_env > 0 ? cap_trsm_env : n_sm;
   auto trsm = [&](cudaStream_t st, int k0, double* Linv, const int* list, int cnt) {
     int rows_per = 64;  // strips of 8..64 rows: as many CTAs as fit in ONE wave (the kernel runs one CTA per SM)
-    while (rows_per > 8 && cnt * (NB / (rows_per >> 1)) <= n_sm) rows_per >>= 1;
+    while (rows_per > 8 && cnt * (NB / (rows_per >> 1)) <= cap_trsm) rows_per >>= 1;
     const int spb = NB / rows_per;
     chol_trsm_strip_kernel<<<cnt * spb, 256, rows_per * TS_LD * (int)sizeof(double), st>>>(S, n, k0, Linv, rows_per, fail_flag, list, spb);
     ++*launches;
   };
-  auto syrk = [&](int k0, int col_first, int tiles, const int* list, int cnt, double* C, int ldc, int blk0) {
+  auto syrk = [&](cudaStream_t st, int k0, int col_first, int tiles, const int* list, int cnt, double* C, int ldc, int blk0) {
     if (tiles <= 0) return;
-    chol_syrk_kernel<<<min(tiles, 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 0, col_first, tiles, 0, fail_flag, list, cnt, C, ldc, blk0);
+    chol_syrk_kernel<<<min(tiles, cap_syrk), 128, kGemmSmem, st>>>(S, n, k0, 0, col_first, tiles, 0, fail_flag, list, cnt, C, ldc, blk0);
     ++*launches;
+  };
+  // tail x tail pairs of the panel -> side matrix, right after the panel solve; off the bulk stream when the chain has a tail stream
+  auto tail_update = [&](int k0, const int* list, int n_own, int ct) {
+    if (ct <= 0) return;
+    cudaStream_t st = s;
+    if (la && cs.tail) {
+      cudaEventRecord(cs.ev_trsm, s);
+      cudaStreamWaitEvent(cs.tail, cs.ev_trsm, 0);
+      st = cs.tail;
+    }
+    syrk(st, k0, -1, ct * (ct + 1), list + n_own, ct, Ctail, ldt, own_end);
   };
   // chain-stream launches carry the programmatic-serialisation attribute (see pdl_enter)
   static const bool no_pdl = getenv("HSFM_NO_PDL") != nullptr;  // experiment knob
@@ -1794,7 +1823,10 @@ static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainS
     const bool has_col = hl[0] == K + 1 && n_own > 0;
     if (la) cudaEventRecord(cs.ev_panel, s2);  // diag(K) done
     const int pairs_own = n_own * cnt - n_own * (n_own - 1) / 2;  // pairs (a, b), b < n_own, a = b .. cnt-1
-    static const bool split_chain = getenv("HSFM_CHAIN_SPLIT") != nullptr;  // experiment knob: panel solve + tile update as two kernels
+    // experiment knob HSFM_CHAIN_SPLIT=1: panel solve of row block K+1 + 32x32 tile update as two light kernels instead of the
+    // one-kernel form (c4, two chains with the side-matrix updates on their own streams: 2.01 vs 1.88 ms; one chain: 3.41 vs 3.16)
+    static const int split_env = getenv("HSFM_CHAIN_SPLIT") ? atoi(getenv("HSFM_CHAIN_SPLIT")) : -1;
+    const bool split_chain = split_env > 0;
     if (has_col && !split_chain) {
       // tile (K+1, K+1) straight from the unsolved block A(K+1, K): one kernel between two diagonal blocks
       cudaLaunchConfig_t cfg = chain_cfg(2 * (NB / 8), 256, kChainTileSmem);
@@ -1804,8 +1836,8 @@ static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainS
       if (la) cudaStreamWaitEvent(s, cs.ev_panel, 0);
       if (la) cudaStreamWaitEvent(s, cs.ev_next, 0);
       trsm(s, k0, Linv, list, cnt);
-      syrk(k0, -2, 2 * (pairs_own - 1), list, cnt, nullptr, 0, 0);
-      if (ct > 0) syrk(k0, -1, ct * (ct + 1), list + n_own, ct, Ctail, ldt, own_end);
+      tail_update(k0, list, n_own, ct);
+      syrk(s, k0, -2, 2 * (pairs_own - 1), list, cnt, nullptr, 0, 0);
       if (la) { cudaEventRecord(cs.ev_rest, s); rest_pending = true; }
       continue;
     }
@@ -1827,14 +1859,14 @@ static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainS
       const int* rl = has_col ? list + 1 : list;
       if (la) cudaStreamWaitEvent(s, cs.ev_panel, 0);
       trsm(s, k0, Linv, rl, rest_cnt);
+      tail_update(k0, list, n_own, ct);
       if (has_col) {
         // one update launch for column K+1 below its diagonal tile and every other active pair
         if (la) cudaStreamWaitEvent(s, cs.ev_next, 0);
-        syrk(k0, -2, 2 * (pairs_own - 1), list, cnt, nullptr, 0, 0);
+        syrk(s, k0, -2, 2 * (pairs_own - 1), list, cnt, nullptr, 0, 0);
       } else {
-        syrk(k0, -1, 2 * pairs_own, list, cnt, nullptr, 0, 0);
+        syrk(s, k0, -1, 2 * pairs_own, list, cnt, nullptr, 0, 0);
       }
-      if (ct > 0) syrk(k0, -1, ct * (ct + 1), list + n_own, ct, Ctail, ldt, own_end);
       if (la) { cudaEventRecord(cs.ev_rest, s); rest_pending = true; }
     }
   }
@@ -1890,6 +1922,11 @@ static void launch_cholesky_struct(double* S, int n, double* ws, int* fail_flag,
   } else {
     const CholChain& cb = aux->chainB;
     ChainStreams B{cb.chain, cb.bulk, cb.ev_panel, cb.ev_next, cb.ev_rest, true};
+    static const bool no_tail_stream = getenv("HSFM_NO_TAIL_STREAM") != nullptr;  // experiment knob
+    if (!no_tail_stream && aux->tailA && aux->tailB) {
+      A.tail = aux->tailA; A.ev_trsm = aux->ev_trsmA;
+      B.tail = aux->tailB; B.ev_trsm = aux->ev_trsmB;
+    }
     cudaStreamWaitEvent(B.chain, aux->ev_fork, 0);
     cudaStreamWaitEvent(B.bulk, aux->ev_fork, 0);
     const int a = pl.split_a, t0 = pl.split_t0;
@@ -1920,6 +1957,16 @@ static void launch_cholesky_struct(double* S, int n, double* ws, int* fail_flag,
     cudaStreamWaitEvent(B.bulk, cb.ev_panel, 0);
     cudaEventRecord(cb.ev_done, B.bulk);
     cudaStreamWaitEvent(s, cb.ev_done, 0);
+    if (A.tail) {  // the side-matrix streams (they join only if they were forked into the work)
+      cudaEventRecord(aux->ev_trsmA, s);
+      cudaStreamWaitEvent(A.tail, aux->ev_trsmA, 0);
+      cudaEventRecord(aux->ev_tailA, A.tail);
+      cudaStreamWaitEvent(s, aux->ev_tailA, 0);
+      cudaEventRecord(aux->ev_trsmB, s);
+      cudaStreamWaitEvent(B.tail, aux->ev_trsmB, 0);
+      cudaEventRecord(aux->ev_tailB, B.tail);
+      cudaStreamWaitEvent(s, aux->ev_tailB, 0);
+    }
     if (fused && !form->chunk_tile0.empty()) cudaStreamWaitEvent(s, aux->ev_form[form->chunk_tile0.size() - 1], 0);
     tail_add_kernel<<<n - t0 * NB, 256, 0, s>>>(S, n, t0, T, nt, fused ? T_B : nullptr);
     ++*launches;

@@ -216,6 +216,8 @@ struct CholAux {
   CholChain chainB;        // second chain of the two-ended schedule (the first one runs on `stream` + the caller's stream)
   cudaEvent_t ev_doneA = nullptr;
   cudaStream_t form_stream = nullptr;   // the experimental chunked formation of S beside the chains (FormSchedule)
+  cudaStream_t tailA = nullptr, tailB = nullptr;  // side-matrix (tail x tail) updates of the two chains
+  cudaEvent_t ev_trsmA = nullptr, ev_trsmB = nullptr, ev_tailA = nullptr, ev_tailB = nullptr;
   std::vector<cudaEvent_t> ev_form;     // one per chunk, grown on demand (outside graph capture)
   int* form_counters = nullptr;         // device: one work counter per chunk
   int form_counters_cap = 0;
