@@ -20,6 +20,9 @@ FLAGS = [
 ]
 
 
+FLAGS += os.environ.get("HSFM_EXTRA_NVCC", "").split()  # experiment builds, e.g. -DSCHUR_MATVEC_CTAS=5
+
+
 def _stale() -> bool:
     if not os.path.exists(OUT):
         return True

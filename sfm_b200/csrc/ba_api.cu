@@ -355,11 +355,11 @@ int64_t hsfm_ba_problem_algorithmic_bytes(hsfm_ba_ctx* h, const char* kernel) {
   // SURVEY.md §8(d) / DESIGN.md §5
   if (!std::strcmp(kernel, "rj")) return 184 * N + 88 * C + 24 * Q;              // obs 24 + r,J 160 per obs; unique parameters
   if (!std::strcmp(kernel, "rj_form")) return 184 * N + 88 * C + 24 * Q + 72 * Q;  // + Hpp (48) and g_p (24) per point
-  if (!std::strcmp(kernel, "schur_matvec")) return 152 * N + 48 * Q + 96 * C;      // Jc 96 + Jp 48 + cam 4 + pt 4 ; Hpp^-1 ; p, q
+  if (!std::strcmp(kernel, "schur_matvec")) return 150 * N + 48 * Q + 96 * C;      // Jc 96 + Jp 48 + pt 4 + slot 1 + rank 1 ; Hpp^-1 ; p, q
   if (!std::strcmp(kernel, "backsub")) return 168 * N + 120 * Q + 48 * C;          // + r 16 ; Hpp^-1 48, z_p 24, y_p 24, cand 24
   if (!std::strcmp(kernel, "cam_form")) return 20 * N + 24 * Q + 88 * C + 216 * C; // obs_cs 16 + pt 4 ; point gather ; rows ; Hcc+gc out
   if (!std::strcmp(kernel, "cost")) return 24 * N + 24 * Q + 88 * C;
-  if (!std::strcmp(kernel, "schur_rhs")) return 148 * N + 24 * Q + 96 * C;         // Jc 96 + Jp 48 + pt 4 ; z_p ; g_c in, rhs out
+  if (!std::strcmp(kernel, "schur_rhs")) return 149 * N + 24 * Q + 96 * C;         // Jc 96 + Jp 48 + pt 4 + rank 1 ; z_p ; g_c in, rhs out
   if (!std::strcmp(kernel, "dense_schur")) return 152 * N + 48 * Q;                // Jc, Jp, cam, pt ; Hpp^-1 (S blocks stay in L2)
   return 0;
 }

@@ -17,6 +17,7 @@ void Problem::release() {
   char* a = arena; const size_t cap = arena_cap;
   double* s_keep = S; const size_t s_cap = S_capacity;
   unsigned* pl_keep = pair_list; const size_t pl_cap = pair_capacity;
+  double* ep_keep = ent_part; const size_t ep_cap = ent_part_cap;
   double* sh = scal_host; int* fh = flags_host;
   int* ih = idx_host; const size_t ih_cap = idx_host_cap;
   const int sm = n_sm;
@@ -25,6 +26,7 @@ void Problem::release() {
   arena = a; arena_cap = cap; arena_off = 0;
   S = s_keep; S_capacity = s_cap;
   pair_list = pl_keep; pair_capacity = pl_cap;
+  ent_part = ep_keep; ent_part_cap = ep_cap;
   scal_host = sh; flags_host = fh;
   idx_host = ih; idx_host_cap = ih_cap;
 }
@@ -33,6 +35,7 @@ void Problem::destroy() {
   if (arena) cudaFree(arena);
   if (S) cudaFree(S);
   if (pair_list) cudaFree(pair_list);
+  if (ent_part) cudaFree(ent_part);
   if (scal_host) cudaFreeHost(scal_host);
   if (flags_host) cudaFreeHost(flags_host);
   if (idx_host) cudaFreeHost(idx_host);
@@ -210,9 +213,12 @@ __global__ void validate_idx_kernel(int n, const int* __restrict__ cam, const in
 // camera in that list.  O(TILE^2) comparisons through shared-memory broadcasts; runs once per upload.
 __global__ void __launch_bounds__(TILE) tile_cams_kernel(const int* __restrict__ tile_start, const int* __restrict__ cam,
                                                           unsigned char* __restrict__ slot, int* __restrict__ tile_cams,
-                                                          int* __restrict__ tile_hdr, int* __restrict__ max_ncam) {
+                                                          int* __restrict__ tile_hdr, int* __restrict__ max_ncam,
+                                                          unsigned char* __restrict__ srank, unsigned char* __restrict__ sorder,
+                                                          unsigned short* __restrict__ slot_begin, int* __restrict__ tile_ncam) {
   __shared__ int sc[TILE];
   __shared__ int sfirst[TILE];
+  __shared__ int sslot[TILE];
   const int b = tile_start[blockIdx.x], e = tile_start[blockIdx.x + 1];
   const int tid = threadIdx.x, i = b + tid, cnt = e - b;
   const int c = i < e ? cam[i] : 0x7fffffff;
@@ -224,13 +230,37 @@ __global__ void __launch_bounds__(TILE) tile_cams_kernel(const int* __restrict__
   const int ncam = __syncthreads_count(first);
   int rank = 0;
   for (int j = 0; j < cnt; ++j) rank += (sfirst[j] && sc[j] < c);
+  sslot[tid] = i < e ? rank : 0x7fffffff;
+  __syncthreads();
   if (i < e) {
     slot[i] = (unsigned char)rank;
-    if (first) tile_cams[(size_t)blockIdx.x * TILE + rank] = c;
+    // position of this observation when the tile is ordered by slot (ties keep tile order): camera-keyed sums of a
+    // tile are then sums over contiguous runs of a shared-memory array, in a fixed order
+    int before = 0, same_before = 0;
+    for (int j = 0; j < cnt; ++j) {
+      before += sslot[j] < rank;
+      same_before += (sslot[j] == rank) & (j < tid);
+    }
+    srank[i] = (unsigned char)(before + same_before);
+    sorder[b + before + same_before] = (unsigned char)tid;  // inverse: which observation of the tile sits at that position
+    if (first) {
+      tile_cams[(size_t)blockIdx.x * TILE + rank] = c;
+      slot_begin[(size_t)blockIdx.x * TILE + rank] = (unsigned short)before;
+    }
   }
   if (tid == 0) {
     tile_hdr[8 * (size_t)blockIdx.x + 4] = ncam;
+    tile_ncam[blockIdx.x] = ncam;
     atomicMax(max_ncam, ncam);
+  }
+}
+// entry e = ent_off[tile] + slot of the (tile, slot) list: its camera (sort key) and itself (value)
+__global__ void __launch_bounds__(TILE) tile_entries_kernel(const int* __restrict__ ent_off, const int* __restrict__ tile_cams, int* __restrict__ key,
+                                                             int* __restrict__ val) {
+  const int o = ent_off[blockIdx.x], n = ent_off[blockIdx.x + 1] - o;
+  if ((int)threadIdx.x < n) {
+    key[o + threadIdx.x] = tile_cams[(size_t)blockIdx.x * TILE + threadIdx.x];
+    val[o + threadIdx.x] = o + threadIdx.x;
   }
 }
 
@@ -336,7 +366,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     int* nullk = nullptr;
     cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp, nullk, nullk, nullk, nullk, std::max({n, n_pts, 1}), 0, 32, s);
     t2 = sort_tmp;
-    const size_t need = 344 * no + 360 * np + 2600 * nc + 280 * (no / 128 + nc + np / 256 + 8) + 2 * t2 + ((size_t)1 << 20);
+    const size_t need = 368 * no + 360 * np + 2600 * nc + 1400 * (no / 128 + nc + np / 256 + 8) + 2 * t2 + ((size_t)1 << 20);
     int rc = P.arena_reserve(need);
     if (rc) return rc;
   }
@@ -421,6 +451,8 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   size_t tmp_bytes = 0, tmp2 = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, pt_in, pt, iota, P.order_pm, std::max(n, 1), 0, pbits, s);
   cub::DeviceRadixSort::SortPairs(nullptr, tmp2, cam, cam_sorted, iota, pos_cs, std::max({n, n_pts, 1}), 0, cbits, s);
+  tmp_bytes = std::max(tmp_bytes, tmp2);
+  cub::DeviceScan::InclusiveSum(nullptr, tmp2, iota, iota, std::max({n, n_pts, 1}), s);  // prefix sum over the tiles' camera counts
   tmp_bytes = std::max(tmp_bytes, tmp2);
   void* tmp = P.arena_take(tmp_bytes);
   if (!tmp) return HSFM_BA_ERR_NOMEM;
@@ -514,8 +546,12 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
       HSFM_CUDA(cudaStreamSynchronize(s));
     }
   }
-  unsigned char* slot; int *tile_cams, *tile_hdr, *d_max_ncam;
+  unsigned char *slot, *srank, *sorder; unsigned short* slot_begin; int *tile_cams, *tile_hdr, *d_max_ncam, *ent_off;
   ALLOC(slot, n); ALLOC(tile_cams, (size_t)P.n_tiles * TILE); ALLOC(tile_hdr, 8 * (size_t)std::max(1, P.n_tiles)); ALLOC(d_max_ncam, 1);
+  ALLOC(srank, n); ALLOC(sorder, n); ALLOC(slot_begin, (size_t)P.n_tiles * TILE); ALLOC(ent_off, (size_t)P.n_tiles + 2);
+  int *cs_start = nullptr, *cs_ent = nullptr;
+  ALLOC(cs_start, (size_t)n_cams + 1);
+  P.n_entries = 0;
   P.max_tile_cams = 0;
   if (P.n_tiles) {
     std::vector<int> hdr(8 * (size_t)P.n_tiles, 0);
@@ -525,7 +561,16 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     }
     HSFM_CUDA(cudaMemcpyAsync(tile_hdr, hdr.data(), sizeof(int) * hdr.size(), cudaMemcpyHostToDevice, s));
     HSFM_CUDA(cudaMemsetAsync(d_max_ncam, 0, sizeof(int), s));
-    tile_cams_kernel<<<P.n_tiles, TILE, 0, s>>>(tile_start, cam, slot, tile_cams, tile_hdr, d_max_ncam);
+    HSFM_CUDA(cudaMemsetAsync(ent_off, 0, sizeof(int), s));
+    tile_cams_kernel<<<P.n_tiles, TILE, 0, s>>>(tile_start, cam, slot, tile_cams, tile_hdr, d_max_ncam, srank, sorder, slot_begin, ent_off + 1);
+    {  // (tile, slot) entries: ent_off = prefix sum of the tiles' camera counts
+      size_t tb = tmp_bytes;
+      size_t need_scan = 0;
+      cub::DeviceScan::InclusiveSum(nullptr, need_scan, ent_off + 1, ent_off + 1, P.n_tiles, s);
+      if (need_scan > tmp_bytes) return HSFM_BA_ERR_NOMEM;
+      cub::DeviceScan::InclusiveSum(tmp, tb, ent_off + 1, ent_off + 1, P.n_tiles, s);
+      HSFM_CUDA(cudaMemcpyAsync(&P.n_entries, ent_off + P.n_tiles, sizeof(int), cudaMemcpyDeviceToHost, s));
+    }
     HSFM_CUDA(cudaMemcpyAsync(&P.max_tile_cams, d_max_ncam, sizeof(int), cudaMemcpyDeviceToHost, s));
     P.h_tile_cmin.clear();
     if (want_structure) {  // first entry of every tile's ascending camera list
@@ -533,6 +578,20 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
       HSFM_CUDA(cudaMemcpy2DAsync(P.h_tile_cmin.data(), sizeof(int), tile_cams, sizeof(int) * TILE, sizeof(int), (size_t)P.n_tiles, cudaMemcpyDeviceToHost, s));
     }
     HSFM_CUDA(cudaStreamSynchronize(s));  // hdr is a local vector; max_tile_cams is needed by the launches
+    // every camera's (tile, slot) entries, in tile order: what the camera-keyed gathers walk (stable sort by camera)
+    int *ek, *ev, *ek2;
+    ALLOC(ek, P.n_entries); ALLOC(ev, P.n_entries); ALLOC(ek2, P.n_entries); ALLOC(cs_ent, P.n_entries);
+    tile_entries_kernel<<<P.n_tiles, TILE, 0, s>>>(ent_off, tile_cams, ek, ev);
+    {
+      size_t need_sort = 0, tb = tmp_bytes;
+      cub::DeviceRadixSort::SortPairs(nullptr, need_sort, ek, ek2, ev, cs_ent, P.n_entries, 0, cbits, s);
+      if (need_sort > tmp_bytes) return HSFM_BA_ERR_NOMEM;
+      cub::DeviceRadixSort::SortPairs(tmp, tb, ek, ek2, ev, cs_ent, P.n_entries, 0, cbits, s);
+    }
+    lower_bound_kernel<<<cdiv(n_cams + 1, 256), 256, 0, s>>>(P.n_entries, ek2, n_cams, cs_start);
+  } else {
+    HSFM_CUDA(cudaMemsetAsync(cs_start, 0, sizeof(int) * ((size_t)n_cams + 1), s));
+    HSFM_CUDA(cudaMemsetAsync(ent_off, 0, sizeof(int) * 2, s));
   }
 
   // ---- camera-major warp chunks ----
@@ -574,7 +633,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   ALLOC(P.Hpp, 6 * (size_t)n_pts); ALLOC(P.gp, 3 * (size_t)n_pts); ALLOC(P.Hpp_inv, 6 * (size_t)n_pts); ALLOC(P.zp, 3 * (size_t)n_pts);
   ALLOC(P.Hcc, 21 * (size_t)n_cams); ALLOC(P.gc, 6 * (size_t)n_cams); ALLOC(P.E, 21 * (size_t)n_cams);
   ALLOC(P.chunk_part, 27 * (size_t)std::max(1, P.n_chunks));
-  ALLOC(P.tobs, 6 * (size_t)n);
+  P.tobs = nullptr;  // (round 1: per-observation camera-space vectors; replaced by per-(tile, slot) entry partials, Problem::ent_part)
   ALLOC(P.Dc2, 6 * (size_t)n_cams); ALLOC(P.Minv, 36 * (size_t)n_cams);
   ALLOC(P.rhs, 6 * (size_t)n_cams); ALLOC(P.yc, 12 * (size_t)n_cams); ALLOC(P.yp, 3 * (size_t)n_pts);
   ALLOC(P.pcg_x, 6 * (size_t)n_cams); ALLOC(P.pcg_r, 6 * (size_t)n_cams); ALLOC(P.pcg_z, 6 * (size_t)n_cams);
@@ -594,11 +653,21 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   HSFM_CUDA(cudaMemsetAsync(P.yc, 0, sizeof(double) * 12 * std::max<size_t>(1, n_cams), s));
   HSFM_CUDA(cudaMemcpyAsync(P.pts_c, P.pts_x, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToDevice, s));
 
+  {
+    const size_t need_ep = 6 * (size_t)std::max(1, P.n_entries);
+    if (P.ent_part_cap < need_ep) {
+      if (P.ent_part) cudaFree(P.ent_part);
+      P.ent_part = nullptr; P.ent_part_cap = 0;
+      if (cudaMalloc(&P.ent_part, sizeof(double) * (need_ep + need_ep / 4)) != cudaSuccess) { cudaGetLastError(); return HSFM_BA_ERR_NOMEM; }
+      P.ent_part_cap = need_ep + need_ep / 4;
+    }
+  }
   Dev& d = P.d;
   d.n_obs = n; d.n_cams = n_cams; d.n_pts = n_pts; d.n_tiles = P.n_tiles; d.n_chunks = P.n_chunks;
   d.obs = obs; d.cam = cam; d.pt = pt; d.pt_start = pt_start; d.tile_start = tile_start;
   d.tile_cams = tile_cams; d.tile_hdr = reinterpret_cast<const int4*>(tile_hdr); d.slot = slot;
   d.pair_off = pair_off; d.pair_list = nullptr;
+  d.srank = srank; d.sorder = sorder; d.slot_begin = slot_begin; d.ent_off = ent_off; d.cs_start = cs_start; d.cs_ent = cs_ent; d.n_entries = P.n_entries;
   d.obs_cs = obs_cs; d.pt_cs = pt_cs; d.pos_cs = pos_cs; d.chunk_cam = d_ch_cam; d.chunk_b = d_ch_b; d.chunk_e = d_ch_e; d.cam_chunk_start = d_cam_ch_start;
   d.r = r; d.Jc = Jc; d.Jp = Jp;
   HSFM_CUDA(cudaStreamSynchronize(s));

@@ -39,6 +39,16 @@ struct Dev {
   const int* pair_off;        // [n_tiles+1] first entry of each tile in pair_list (null: more than 2^31 pairs)
   const unsigned* pair_list;  // per tile: the (i,j) observation pairs of its points SORTED by destination block of S,
                               // (slot_i << 24 | slot_j << 16 | i << 8 | j); built lazily by the first dense solve
+  // camera-keyed sums without atomics and without a per-observation round trip: inside a tile the observations'
+  // contributions are summed per camera slot in shared memory (srank = position in slot order, slot_begin = first
+  // position of every slot), one partial per (tile, slot) ENTRY goes to HBM, and a camera's sum is the sum of its entries
+  const unsigned char* srank;        // [n_obs]
+  const unsigned char* sorder;       // [n_obs] inverse within the tile: tile-local index of the observation at slot-order position j
+  const unsigned short* slot_begin;  // [n_tiles][TILE] (first hdr.ncam entries valid)
+  const int* ent_off;                // [n_tiles+1] first entry of each tile; entry = ent_off[tile] + slot
+  const int* cs_start;               // [n_cams+1] CSR over cs_ent
+  const int* cs_ent;                 // [n_entries] entries of every camera, in tile order
+  int n_entries;
   // static, camera-major order
   const double2* obs_cs; // [n_obs]
   const int* pt_cs;      // [n_obs]
@@ -59,6 +69,9 @@ struct Problem {
   int n_obs = 0, n_cams = 0, n_pts = 0, n_tiles = 0, n_chunks = 0;
   int max_track = 0;
   int n_sm = 148;         // SM count of the context's device (set by hsfm_ba_create; survives release())
+  int n_entries = 0;      // (tile, slot) pairs: sum over tiles of their distinct cameras
+  double* ent_part = nullptr;  // [n_entries][6] per-entry partial sums (grow-only, outside the arena like S)
+  size_t ent_part_cap = 0;
   int max_tile_cams = 0;  // largest number of distinct cameras in one tile (sizes the shared-memory row staging)
   std::vector<int> cam_first;  // [n_cams] CALLER order: smallest camera sharing a point with camera c (all ranks) — envelope of S
   // internal camera order (ba_order.cpp): null / empty = the caller's order

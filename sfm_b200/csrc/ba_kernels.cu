@@ -489,44 +489,63 @@ __global__ void frame_stats_reduce_kernel(int n_cams, const int* __restrict__ ca
   out[c] = sum; out[n_cams + c] = cnt; out[2 * n_cams + c] = mx;
 }
 
-// Camera-major gather of the per-observation 6-vectors written point-major by schur_pass_kernel<0>:
-// one warp per chunk (<= 256 observations of one camera), 48-byte records fetched through the
-// camera-major → point-major permutation, warp-reduced into chunk_part[chunk][0..5].
-__global__ void __launch_bounds__(256) cam_gather6_kernel(Dev d, const double* __restrict__ tobs, double* __restrict__ chunk_part,
-                                                          const int* __restrict__ skip_flag) {
+// ---- camera-keyed sums through (tile, slot) entries ---------------------------------------------------------
+// Every observation has staged K values at sq[k * SV_LD + srank] (srank = its position when the tile is ordered by
+// camera slot).  One thread per (slot, k) adds the slot's contiguous run in a fixed order and writes the entry's
+// partial: part[(ent_off[tile] + slot) * part_ld + k0 + k].  Call between two barriers.
+// s_sb: the tile's slot_begin table in shared memory (stage_slot_begin: ncam entries + the observation count).
+__device__ __forceinline__ void stage_slot_begin(const Dev& d, int tile, int ncam, int cnt, unsigned short* s_sb) {
+  const unsigned short* sb = d.slot_begin + (size_t)tile * TILE;
+  for (int q = threadIdx.x; q <= ncam; q += TILE) s_sb[q] = q < ncam ? __ldg(sb + q) : (unsigned short)cnt;
+}
+template <int K>
+__device__ __forceinline__ void slot_reduce(int e0, int ncam, const unsigned short* s_sb, const double* sq, double* __restrict__ part, int part_ld, int k0) {
+  for (int task = threadIdx.x; task < ncam * K; task += TILE) {
+    const int sl = task / K, k = task - sl * K;
+    const int b = s_sb[sl], e = s_sb[sl + 1];
+    const double* src = sq + k * SV_LD;
+    double a0 = 0.0, a1 = 0.0;
+    int l = b;
+    for (; l + 1 < e; l += 2) { a0 += src[l]; a1 += src[l + 1]; }
+    if (l < e) a0 += src[l];
+    part[(size_t)(e0 + sl) * part_ld + k0 + k] = a0 + a1;
+  }
+}
+
+// A camera's sum = the sum of its entries' partials, in tile order: one warp per camera, lanes stride the entry list,
+// fixed shuffle tree.  out[c][k] = (base ? base[c][k] : 0) + sign * sum (reduced rhs, implicit mat-vec).
+template <int K>
+__global__ void __launch_bounds__(256) slot_gather_kernel(Dev d, const double* __restrict__ part, const double* __restrict__ base, double sign,
+                                                          double* __restrict__ out, const int* __restrict__ skip_flag) {
+  // two cameras per CTA, four warps each (a camera has a few hundred entries: one warp alone is latency-bound)
+  __shared__ double sp[2][4][K];
   if (skip_flag && *skip_flag) return;
-  const int lane = threadIdx.x & 31;
-  const int wc = blockIdx.x * 8 + (threadIdx.x >> 5);
-  if (wc >= d.n_chunks) return;
-  const int b = __ldg(d.chunk_b + wc), e = __ldg(d.chunk_e + wc);
-  double acc[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-  for (int j = b + lane; j < e; j += 32) {
-    const double2* src = reinterpret_cast<const double2*>(tobs + 6 * (size_t)__ldg(d.pos_cs + j));
-    const double2 v0 = __ldg(src), v1 = __ldg(src + 1), v2 = __ldg(src + 2);
-    acc[0] += v0.x; acc[1] += v0.y; acc[2] += v1.x; acc[3] += v1.y; acc[4] += v2.x; acc[5] += v2.y;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = warp & 3, half = warp >> 2;
+  const int c = blockIdx.x * 2 + half;
+  double acc[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) acc[k] = 0.0;
+  if (c < d.n_cams) {
+    const int b = __ldg(d.cs_start + c), e = __ldg(d.cs_start + c + 1);
+    for (int q = b + sub * 32 + lane; q < e; q += 128) {
+      const double* src = part + (size_t)__ldg(d.cs_ent + q) * K;
+#pragma unroll
+      for (int k = 0; k < K; ++k) acc[k] += __ldg(src + k);
+    }
   }
 #pragma unroll
-  for (int k = 0; k < 6; ++k) {
+  for (int k = 0; k < K; ++k) {
     double v = acc[k];
 #pragma unroll
     for (int dd = 16; dd > 0; dd >>= 1) v += __shfl_xor_sync(FULL, v, dd);
-    acc[k] = v;
+    if (lane == 0) sp[half][sub][k] = v;
   }
-  if (lane == 0) {
-#pragma unroll
-    for (int k = 0; k < 6; ++k) chunk_part[(size_t)wc * 27 + k] = acc[k];
+  __syncthreads();
+  if (sub == 0 && lane < K && c < d.n_cams) {
+    const int k = lane;
+    const double v = ((sp[half][0][k] + sp[half][1][k]) + sp[half][2][k]) + sp[half][3][k];  // fixed order
+    out[(size_t)c * K + k] = (base ? base[(size_t)c * K + k] : 0.0) + sign * v;
   }
-}
-// out[c][k] = (base ? base[c][k] : 0) + sign * sum over the camera's chunks, in chunk order
-__global__ void cam_reduce6_kernel(int n_cams, const int* __restrict__ cam_chunk_start, const double* __restrict__ chunk_part,
-                                   const double* __restrict__ base, double sign, double* __restrict__ out, const int* __restrict__ skip_flag) {
-  if (skip_flag && *skip_flag) return;
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= n_cams * 6) return;
-  const int c = idx / 6, k = idx % 6;
-  double s = 0.0;
-  for (int w = cam_chunk_start[c]; w < cam_chunk_start[c + 1]; ++w) s += chunk_part[(size_t)w * 27 + k];
-  out[idx] = (base ? base[idx] : 0.0) + sign * s;
 }
 
 // Fold the chunk partials of each camera in chunk order (deterministic).
@@ -653,16 +672,24 @@ __global__ void precond_invert_kernel(int n_cams, const double* __restrict__ Hcc
 //   MODE 1 (MATVEC) : q[c]   += Jc^T (I - Jp Hpp^-1 Jp^T) Jc p      (implicit S p without the D_c^2 p term)
 //   MODE 2 (BACKSUB): y_p = z_p - Hpp^-1 W^T y_c ; candidate point ; model cost change ; norms   (a8, a9)
 // Algorithmic bytes / observation: Jc 96 + Jp 48 + cam 4 + pt 4 (+ r 16 in MODE 2).
+#ifndef SCHUR_MATVEC_CTAS
+#define SCHUR_MATVEC_CTAS 4
+#endif
 template <int MODE>
-__global__ void __launch_bounds__(TILE, MODE == 0 ? 8 : 4) schur_pass_kernel(Dev d, const double* __restrict__ Hpp_inv, const double* __restrict__ zp,
+__global__ void __launch_bounds__(TILE, MODE == 0 ? 8 : (MODE == 1 ? SCHUR_MATVEC_CTAS : 4)) schur_pass_kernel(Dev d, const double* __restrict__ Hpp_inv, const double* __restrict__ zp,
                                                           const double* __restrict__ vec_in /* p or y_c */, double* __restrict__ vec_out,
                                                           const double* __restrict__ pts_x, const double* __restrict__ scale_p,
                                                           double* __restrict__ yp, double* __restrict__ pts_c,
                                                           double* __restrict__ part, int part_stride, const int* __restrict__ flags,
                                                           int cams_free, int pts_free) {
+  // MODE 0/1: sq = the observations' camera-space 6-vectors, in slot order.  In MODE 1 it shares its storage with sP (the
+  // staged vec_in blocks are dead once u = Jc p has been formed, two barriers before sq is written).
+  __shared__ __align__(16) double sq_sp[MODE == 2 ? 6 * TILE : 6 * SV_LD];
+  double* const sq = sq_sp;
+  double2* const sP = reinterpret_cast<double2*>(sq_sp);  // MODE 1/2: vec_in blocks of the tile's cameras, by slot [3 * TILE]
+  __shared__ unsigned short s_sb[MODE == 2 ? 2 : TILE + 1];
   __shared__ double sv[MODE == 0 ? 1 : 3 * SV_LD];  // per-observation W^T(.) pieces
   __shared__ double sw[MODE == 0 ? 1 : 3 * TILE];   // per-point result handed back to the observations
-  __shared__ double2 sP[MODE == 0 ? 1 : 3 * TILE];  // vec_in blocks of the tile's cameras, by slot
   __shared__ double sm[8];
   if (MODE == 1) {
     if (flags[F_PCG_DONE]) return;
@@ -672,6 +699,11 @@ __global__ void __launch_bounds__(TILE, MODE == 0 ? 8 : 4) schur_pass_kernel(Dev
   const bool valid = i < t.e;
   const size_t n = (size_t)d.n_obs;
   const bool use_vec = MODE == 1 || (MODE == 2 && cams_free);
+  int e0 = 0;
+  if (MODE != 2) {
+    e0 = __ldg(d.ent_off + blockIdx.x);
+    stage_slot_begin(d, (int)blockIdx.x, t.ncam, t.e - t.b, s_sb);
+  }
   if (MODE != 0 && use_vec) {
     const int* list = d.tile_cams + (size_t)blockIdx.x * TILE;
     for (int q = threadIdx.x; q < 3 * t.ncam; q += TILE) {
@@ -680,9 +712,10 @@ __global__ void __launch_bounds__(TILE, MODE == 0 ? 8 : 4) schur_pass_kernel(Dev
     }
   }
   double jc[12], jp[6];
-  int slot = 0, pl = 0;
+  int slot = 0, pl = 0, rk = 0;
   if (valid) {
     if (MODE != 0) slot = __ldg(d.slot + i);
+    if (MODE != 2) rk = __ldg(d.srank + i);
     pl = __ldg(d.pt + i) - t.p_first;
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
@@ -696,18 +729,18 @@ __global__ void __launch_bounds__(TILE, MODE == 0 ? 8 : 4) schur_pass_kernel(Dev
     }
   }
   if (MODE == 0) {
-    // t_i = Jc_i^T (Jp_i z_p), stored per observation (48 B, point-major); the camera-major gather
-    // pass (cam_gather6_kernel) sums them per camera — no atomics, fixed summation order.
+    // t_i = Jc_i^T (Jp_i z_p): summed per camera slot of the tile in shared memory, one partial per (tile, slot) entry goes
+    // out; slot_gather_kernel<6> adds a camera's entries — no atomics, fixed order, no per-observation round trip
     if (valid) {
       const size_t p = (size_t)(t.p_first + pl);
       const double z0 = __ldg(zp + 3 * p), z1 = __ldg(zp + 3 * p + 1), z2 = __ldg(zp + 3 * p + 2);
       const double y0 = jp[0] * z0 + jp[1] * z1 + jp[2] * z2;
       const double y1 = jp[3] * z0 + jp[4] * z1 + jp[5] * z2;
-      double2* dst = reinterpret_cast<double2*>(vec_out + 6 * (size_t)i);
 #pragma unroll
-      for (int k = 0; k < 3; ++k)
-        dst[k] = make_double2(jc[2 * k] * y0 + jc[6 + 2 * k] * y1, jc[2 * k + 1] * y0 + jc[7 + 2 * k] * y1);
+      for (int k = 0; k < 6; ++k) sq[k * SV_LD + rk] = jc[k] * y0 + jc[6 + k] * y1;
     }
+    __syncthreads();
+    slot_reduce<6>(e0, t.ncam, s_sb, sq, vec_out, 6, 0);
     return;
   }
   // the per-point thread's inputs depend on the tile header only: fetch them before the barrier
@@ -768,15 +801,15 @@ __global__ void __launch_bounds__(TILE, MODE == 0 ? 8 : 4) schur_pass_kernel(Dev
   double w0 = 0.0, w1 = 0.0, w2 = 0.0;
   if (valid) { w0 = sw[3 * pl]; w1 = sw[3 * pl + 1]; w2 = sw[3 * pl + 2]; }
   if (MODE == 1) {
-    // t_i = Jc_i^T (I - Jp Hpp^-1 Jp^T)(Jc p) per observation; summed per camera by the gather pass
+    // t_i = Jc_i^T (I - Jp Hpp^-1 Jp^T)(Jc p) per observation, summed per camera slot of the tile (see MODE 0)
     if (valid) {
       const double y0 = u0 - (jp[0] * w0 + jp[1] * w1 + jp[2] * w2);
       const double y1 = u1 - (jp[3] * w0 + jp[4] * w1 + jp[5] * w2);
-      double2* dst = reinterpret_cast<double2*>(vec_out + 6 * (size_t)i);
 #pragma unroll
-      for (int k = 0; k < 3; ++k)
-        dst[k] = make_double2(jc[2 * k] * y0 + jc[6 + 2 * k] * y1, jc[2 * k + 1] * y0 + jc[7 + 2 * k] * y1);
+      for (int k = 0; k < 6; ++k) sq[k * SV_LD + rk] = jc[k] * y0 + jc[6 + k] * y1;
     }
+    __syncthreads();
+    slot_reduce<6>(e0, t.ncam, s_sb, sq, vec_out, 6, 0);
     return;
   }
   // MODE 2: model cost change of step = -y;  m = J step
@@ -1422,6 +1455,10 @@ void launch_cost(Problem& P, const CamRow* rows, const double* pts, int part_slo
   add_task(P, part_slot, P.n_tiles, S_CAND_COST, 2);
 }
 
+// Camera-major passes: what 0 -> Hcc, g_c ; what 1 -> E (diagonal blocks of W Hpp^-1 W^T, needs Hpp_inv).  Both recompute the
+// Jacobian from 20 B/observation + a point gather.  (Round 2 measured the alternative for what 0 — a streaming pass over the
+// stored Jc, r with per-(tile, slot) shared-memory sums of the 27 values and a per-camera gather: 0.33 ms against 0.22 ms
+// for this recompute at Venice shape; the 27-value slot reduction costs more than re-deriving the Jacobian.  Not adopted.)
 void launch_cam_major(Problem& P, const CamRow* rows, const double* pts, const double* scale_p, int what, cudaStream_t s) {
   if (P.n_chunks > 0) {
     if (what == 0) cam_major_kernel<0><<<cdiv(P.n_chunks, 8), 256, 0, s>>>(P.d, rows, pts, scale_p, P.Hpp_inv, P.chunk_part);
@@ -1467,16 +1504,12 @@ void launch_precond_invert(Problem& P, bool with_E, cudaStream_t s) {
 
 void launch_schur_rhs(Problem& P, bool preload_gc, cudaStream_t s) {
   if (P.n_tiles > 0) {
-    schur_pass_kernel<0><<<P.n_tiles, TILE, 0, s>>>(P.d, P.Hpp_inv, P.zp, nullptr, P.tobs, nullptr, nullptr, nullptr, nullptr, P.part,
+    schur_pass_kernel<0><<<P.n_tiles, TILE, 0, s>>>(P.d, P.Hpp_inv, P.zp, nullptr, P.ent_part, nullptr, nullptr, nullptr, nullptr, P.part,
                                                     P.part_stride, P.flags, 1, 1);
     P.launches++;
   }
-  if (P.n_chunks > 0) {
-    cam_gather6_kernel<<<cdiv(P.n_chunks, 8), 256, 0, s>>>(P.d, P.tobs, P.chunk_part, nullptr);
-    P.launches++;
-  }
   if (P.n_cams > 0) {
-    cam_reduce6_kernel<<<cdiv(P.n_cams * 6, 256), 256, 0, s>>>(P.n_cams, P.d.cam_chunk_start, P.chunk_part, preload_gc ? P.gc : nullptr, -1.0, P.rhs, nullptr);
+    slot_gather_kernel<6><<<cdiv(P.n_cams, 2), 256, 0, s>>>(P.d, P.ent_part, preload_gc ? P.gc : nullptr, -1.0, P.rhs, nullptr);
     P.launches++;
   }
 }
@@ -1484,16 +1517,12 @@ void launch_schur_rhs(Problem& P, bool preload_gc, cudaStream_t s) {
 void launch_schur_matvec(Problem& P, const double* pvec, double* q, cudaStream_t s) {
   // q = (Jc^T (I - Jp Hpp^-1 Jp^T) Jc) p  (overwrites q; honours F_PCG_DONE)
   if (P.n_tiles > 0) {
-    schur_pass_kernel<1><<<P.n_tiles, TILE, 0, s>>>(P.d, P.Hpp_inv, P.zp, pvec, P.tobs, nullptr, nullptr, nullptr, nullptr, P.part,
+    schur_pass_kernel<1><<<P.n_tiles, TILE, 0, s>>>(P.d, P.Hpp_inv, P.zp, pvec, P.ent_part, nullptr, nullptr, nullptr, nullptr, P.part,
                                                     P.part_stride, P.flags, 1, 1);
     P.launches++;
   }
-  if (P.n_chunks > 0) {
-    cam_gather6_kernel<<<cdiv(P.n_chunks, 8), 256, 0, s>>>(P.d, P.tobs, P.chunk_part, P.flags + F_PCG_DONE);
-    P.launches++;
-  }
   if (P.n_cams > 0) {
-    cam_reduce6_kernel<<<cdiv(P.n_cams * 6, 256), 256, 0, s>>>(P.n_cams, P.d.cam_chunk_start, P.chunk_part, nullptr, 1.0, q, P.flags + F_PCG_DONE);
+    slot_gather_kernel<6><<<cdiv(P.n_cams, 2), 256, 0, s>>>(P.d, P.ent_part, nullptr, 1.0, q, P.flags + F_PCG_DONE);
     P.launches++;
   }
 }
