@@ -503,7 +503,7 @@ int hsfm_ba_dense_spd_solve(hsfm_ba_ctx* h, int32_t n, const double* A, const do
   double *dA = nullptr, *db = nullptr;
   int* dflag = nullptr;
   if (cudaMalloc(&dA, sizeof(double) * (nn + cholesky_workspace_doubles(n))) != cudaSuccess) { cudaGetLastError(); return HSFM_BA_ERR_NOMEM; }
-  if (cudaMalloc(&db, sizeof(double) * 2 * n) != cudaSuccess || cudaMalloc(&dflag, sizeof(int)) != cudaSuccess) {
+  if (cudaMalloc(&db, sizeof(double) * 3 * n) != cudaSuccess || cudaMalloc(&dflag, sizeof(int)) != cudaSuccess) {
     cudaGetLastError(); cudaFree(dA); if (db) cudaFree(db); return HSFM_BA_ERR_NOMEM;
   }
   int rc = 0, flag = 0;
@@ -536,7 +536,7 @@ int hsfm_ba_bench_cholesky(hsfm_ba_ctx* h, int32_t n, int reps, double* factor_m
   double *dA = nullptr, *db = nullptr, *derr = nullptr;
   int* dflag = nullptr;
   if (cudaMalloc(&dA, sizeof(double) * (nn + cholesky_workspace_doubles(n))) != cudaSuccess) { cudaGetLastError(); return HSFM_BA_ERR_NOMEM; }
-  if (cudaMalloc(&db, sizeof(double) * 3 * n) != cudaSuccess || cudaMalloc(&dflag, sizeof(int)) != cudaSuccess ||
+  if (cudaMalloc(&db, sizeof(double) * 4 * n) != cudaSuccess || cudaMalloc(&dflag, sizeof(int)) != cudaSuccess ||
       cudaMalloc(&derr, sizeof(double)) != cudaSuccess) {
     cudaGetLastError(); cudaFree(dA); if (db) cudaFree(db); if (dflag) cudaFree(dflag); return HSFM_BA_ERR_NOMEM;
   }
@@ -548,8 +548,8 @@ int hsfm_ba_bench_cholesky(hsfm_ba_ctx* h, int32_t n, int reps, double* factor_m
   double err = 0.0;
   auto run = [&]() -> int {
     for (int it = 0; it <= reps; ++it) {
-      launch_spd_fill(dA, n, it == 0 ? db + 2 * n : nullptr, s);
-      HSFM_CUDA(cudaMemcpyAsync(db, db + 2 * n, sizeof(double) * n, cudaMemcpyDeviceToDevice, s));
+      launch_spd_fill(dA, n, it == 0 ? db + 3 * n : nullptr, s);
+      HSFM_CUDA(cudaMemcpyAsync(db, db + 3 * n, sizeof(double) * n, cudaMemcpyDeviceToDevice, s));
       HSFM_CUDA(cudaMemsetAsync(dflag, 0, sizeof(int), s));
       HSFM_CUDA(cudaEventRecord(e0, s));
       launch_cholesky(dA, n, dA + nn, dflag, s, &h->c.chol_aux, &launches);

@@ -1390,8 +1390,23 @@ __device__ __forceinline__ void inv_stage(double* sInv, const double* __restrict
 
 // Structure (optional, all null = dense): row_off/row_list = the column blocks of every row block (ascending, the
 // diagonal block last), col_off/col_cnt/col_list = the row blocks below the diagonal of every column block.
+// Hand-over of a solved 128-vector between CTAs WITHOUT a flag: the vectors w (forward) and x (backward) are preset to a
+// sentinel bit pattern (all ones: a NaN no arithmetic produces) and every consumer thread polls ITS element until it
+// differs — one L2 round trip instead of flag acquire + vector load, and no release fence on the producer side (an
+// aligned 8-byte store is atomic; the value is its own flag).
+__device__ __forceinline__ double poll_value(const double* p) {
+  unsigned long long v;
+  do {
+    asm volatile("ld.relaxed.gpu.global.b64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  } while (v == 0xffffffffffffffffull);
+  return __longlong_as_double((long long)v);
+}
+__device__ __forceinline__ void publish_value(double* p, double v) {
+  // a genuine all-ones result cannot occur (not a canonical NaN); canonical NaNs pass through and end the consumers' waits
+  asm volatile("st.relaxed.gpu.global.b64 [%0], %1;" ::"l"(p), "l"(__double_as_longlong(v)) : "memory");
+}
 __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict__ L, int n, const double* __restrict__ LinvAll, double* b,
-                                                        double* w, int* flag_fwd, int* flag_bwd, const int* __restrict__ row_off,
+                                                        double* w, double* x, const int* __restrict__ row_off,
                                                         const int* __restrict__ row_list, const int* __restrict__ col_off,
                                                         const int* __restrict__ col_cnt, const int* __restrict__ col_list) {
   extern __shared__ __align__(16) double sInv[];  // [128][TI_LD]
@@ -1400,7 +1415,7 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
   __shared__ double sp[NB];
   const int tid = threadIdx.x;
   const int P = (n + NB - 1) / NB, G = gridDim.x;
-  // ---- forward ----
+  // ---- forward: L y = b, y -> w ----
   for (int i = blockIdx.x; i < P; i += G) {
     const int r0 = i * NB, nr = min(NB, n - r0);
     __syncthreads();
@@ -1410,13 +1425,12 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
     for (int q = row_off ? __ldg(row_off + i) : 0; q < q_end; ++q) {
       const int k = row_off ? __ldg(row_list + q) : q;
       RowFrag f;
-      row_fetch(f, L + (size_t)r0 * n + (size_t)k * NB, (size_t)n, nr, tid);
-      if (tid == 0) { while (ld_acquire(flag_fwd + k) == 0) { } }
+      row_fetch(f, L + (size_t)r0 * n + (size_t)k * NB, (size_t)n, nr, tid);  // issued before the wait
+      __syncthreads();                                                        // sv of the previous block has been consumed
+      if (tid < NB) sv[tid] = poll_value(w + k * NB + tid);                   // k < i: a full block
       __syncthreads();
-      if (tid < NB) sv[tid] = __ldcg(w + k * NB + tid);
-      __syncthreads();
-      const double d = row_dot(f, sv, tid);
-      if (!(tid & 1)) sacc[tid >> 1] -= d;
+      const double dd = row_dot(f, sv, tid);
+      if (!(tid & 1)) sacc[tid >> 1] -= dd;
     }
     cp_async_wait<0>();
     __syncthreads();
@@ -1433,29 +1447,24 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
       }
       double y = (a[0] + a[1]) + (a[2] + a[3]);
       y += __shfl_xor_sync(0xffffffffu, y, 1);
-      if (!h && r < nr) w[r0 + r] = y;
+      if (!h && r < nr) publish_value(w + r0 + r, y);
     }
-    __syncthreads();
-    if (tid == 0) st_release(flag_fwd + i, 1);  // release after the barrier: cumulative over the CTA's writes of w (no separate fence: it costs a second MEMBAR and an L1 invalidate per step of the chain)
   }
-  // ---- backward ----
+  // ---- backward: L^T x = y, x published in its own vector ----
   const int j = tid & (NB - 1), half = tid >> 7;
   for (int kk = P - 1 - (int)blockIdx.x; kk >= 0; kk -= G) {
     const int c0 = kk * NB, kb = min(NB, n - c0);
     __syncthreads();
     inv_stage(sInv, LinvAll + (size_t)kk * NB * NB, tid);
-    if (tid == 0) { while (ld_acquire(flag_fwd + kk) == 0) { } }
-    __syncthreads();
-    if (tid < NB) sacc[tid] = (tid < kb) ? __ldcg(w + c0 + tid) : 0.0;
+    if (tid < NB) sacc[tid] = (tid < kb) ? poll_value(w + c0 + tid) : 0.0;  // this block's forward result (another CTA's)
     const int c_beg = col_off ? __ldg(col_off + kk) : 0, c_cnt = col_off ? __ldg(col_cnt + kk) : P - 1 - kk;
     for (int q = c_cnt - 1; q >= 0; --q) {  // structural blocks of column kk, bottom up
       const int i = col_off ? __ldg(col_list + c_beg + q) : kk + 1 + q;
       const int r0 = i * NB, nr = min(NB, n - r0);
       ColFrag f;
       col_fetch(f, L + (size_t)r0 * n + c0, (size_t)n, nr, kb, tid);
-      if (tid == 0) { while (ld_acquire(flag_bwd + i) == 0) { } }
       __syncthreads();
-      if (tid < NB) sv[tid] = (tid < nr) ? __ldcg(b + r0 + tid) : 0.0;
+      if (tid < NB) sv[tid] = (tid < nr) ? poll_value(x + r0 + tid) : 0.0;
       __syncthreads();
       const double acc = col_dot(f, sv, tid);
       if (half) sp[j] = acc;
@@ -1477,10 +1486,8 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
       const double acc = (a[0] + a[1]) + (a[2] + a[3]);
       if (half) sp[j] = acc;
       __syncthreads();
-      if (!half && j < kb) b[c0 + j] = acc + sp[j];
+      if (!half && j < kb) publish_value(x + c0 + j, acc + sp[j]);
     }
-    __syncthreads();
-    if (tid == 0) st_release(flag_bwd + kk, 1);
   }
 }
 
@@ -2144,8 +2151,8 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
   }
 }
 
-// Solves S y = b with the factor from launch_cholesky.  b holds 2n doubles: [0,n) right-hand side
-// in / solution out, [n,2n) scratch for the intermediate vector.
+// Solves S y = b with the factor from launch_cholesky.  b holds 3n doubles: [0,n) right-hand side
+// in / solution out, [n,2n) the forward vector, [2n,3n) the backward vector (scratch).
 void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream_t s, int64_t* launches, const CholAux* aux, const CholPlan* plan) {
   double* w = b + n;
   const int panels = (n + NB - 1) / NB;
@@ -2153,10 +2160,9 @@ void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream
   const int n_sm = (aux && aux->n_sm > 0) ? aux->n_sm : 148;
   const int coop = aux ? aux->coop : 0;
   if (coop) {
-    cudaMemsetAsync(flags, 0, sizeof(int) * 2 * panels, s);
+    double* x = b + 2 * (size_t)n;  // backward result; copied to b afterwards
+    cudaMemsetAsync(w, 0xff, sizeof(double) * 2 * (size_t)n, s);  // w and x: the sentinel the consumers poll against
     const double* LinvAll = ws;
-    int* ff = flags;
-    int* fb = flags + panels;
     int nn = n;
     const bool st = plan && plan->use && plan->n == n;
     const int* row_off = st ? plan->d_row_off : nullptr;
@@ -2164,11 +2170,12 @@ void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream
     const int* col_off = st ? plan->d_col_off : nullptr;
     const int* col_cnt = st ? plan->d_col_cnt : nullptr;
     const int* col_list = st ? plan->d_list : nullptr;
-    void* args[] = {(void*)&L,  (void*)&nn,      (void*)&LinvAll,  (void*)&b,       (void*)&w,       (void*)&ff,
-                    (void*)&fb, (void*)&row_off, (void*)&row_list, (void*)&col_off, (void*)&col_cnt, (void*)&col_list};
+    void* args[] = {(void*)&L,       (void*)&nn,       (void*)&LinvAll, (void*)&b,       (void*)&w,       (void*)&x,
+                    (void*)&row_off, (void*)&row_list, (void*)&col_off, (void*)&col_cnt, (void*)&col_list};
     const int grid = std::min(panels, n_sm);
     if (cudaLaunchCooperativeKernel((const void*)trsv_coop_kernel, dim3(grid), dim3(256), args, kTrsvSmem, s) == cudaSuccess) {
       ++*launches;
+      cudaMemcpyAsync(b, x, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s);
       return;
     }
     cudaGetLastError();  // fall through to the per-panel launches

@@ -635,7 +635,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   ALLOC(P.chunk_part, 27 * (size_t)std::max(1, P.n_chunks));
   P.tobs = nullptr;  // (round 1: per-observation camera-space vectors; replaced by per-(tile, slot) entry partials, Problem::ent_part)
   ALLOC(P.Dc2, 6 * (size_t)n_cams); ALLOC(P.Minv, 36 * (size_t)n_cams);
-  ALLOC(P.rhs, 6 * (size_t)n_cams); ALLOC(P.yc, 12 * (size_t)n_cams); ALLOC(P.yp, 3 * (size_t)n_pts);
+  ALLOC(P.rhs, 6 * (size_t)n_cams); ALLOC(P.yc, 18 * (size_t)n_cams);  /* solution | forward vector | backward vector of the triangular solves */ ALLOC(P.yp, 3 * (size_t)n_pts);
   ALLOC(P.pcg_x, 6 * (size_t)n_cams); ALLOC(P.pcg_r, 6 * (size_t)n_cams); ALLOC(P.pcg_z, 6 * (size_t)n_cams);
   ALLOC(P.pcg_p, 6 * (size_t)n_cams); ALLOC(P.pcg_q, 6 * (size_t)n_cams);
   P.part_stride = std::max({P.n_tiles, cdiv(6 * n_cams, 256), cdiv(3 * n_pts, 256), 1});
@@ -650,7 +650,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   HSFM_CUDA(cudaMemsetAsync(P.Hpp, 0, sizeof(double) * 6 * std::max<size_t>(1, n_pts), s));
   HSFM_CUDA(cudaMemsetAsync(P.gp, 0, sizeof(double) * 3 * std::max<size_t>(1, n_pts), s));
   HSFM_CUDA(cudaMemsetAsync(P.yp, 0, sizeof(double) * 3 * std::max<size_t>(1, n_pts), s));
-  HSFM_CUDA(cudaMemsetAsync(P.yc, 0, sizeof(double) * 12 * std::max<size_t>(1, n_cams), s));
+  HSFM_CUDA(cudaMemsetAsync(P.yc, 0, sizeof(double) * 18 * std::max<size_t>(1, n_cams), s));
   HSFM_CUDA(cudaMemcpyAsync(P.pts_c, P.pts_x, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToDevice, s));
 
   {
