@@ -153,19 +153,25 @@ void hsfm_ba_default_options(hsfm_ba_options* opts);
 int hsfm_ba_set_stream(hsfm_ba_ctx* ctx, void* cuda_stream);
 
 /* Internal camera order of subsequently uploaded problems.  0 (default): chosen by the library — a banded camera
- * graph (a scan trajectory) is numbered from both ends towards the middle, so that the Cholesky of the reduced camera
- * system runs as two concurrent panel chains; results are returned in the caller's order either way.  1: keep the
- * caller's order (one chain).  The solution is the same up to rounding. */
+ * graph (a scan trajectory) is cut into two or four pieces, each numbered from both ends towards its middle, so that
+ * the Cholesky of the reduced camera system runs as concurrent panel chains that meet in small separator blocks;
+ * results are returned in the caller's order either way.  1: keep the caller's order (one chain).  The solution is the
+ * same up to rounding. */
 int hsfm_ba_set_ordering(hsfm_ba_ctx* ctx, int ordering);
 
 /* Host-only tap (no device needed): the camera order, the 128-row block structure of the Cholesky factor and the
  * panel-chain schedule the library derives from an envelope cam_first[c] = smallest camera sharing a point with
- * camera c (caller order).  natural != 0: keep the caller's order.  new_of_old [n_cams] (optional) internal position
- * of every camera; info [8] = {panels, first panel of the second chain or -1, first common panel or -1, structured
- * factorisation used (0/1), reordered (0/1), first camera of the second chain, 0, 0}; fill (optional) = structural
- * blocks / triangle blocks; structure (optional) [panels][panels] bytes, lower triangle, 1 = block of L may be non-zero. */
+ * camera c (caller order).  natural > 0: keep the caller's order; natural = -1 - d: the nested two-ended order of
+ * dissection depth d (2, 4, 8 chains for d = 0, 1, 2) whatever the cost model prefers.  new_of_old [n_cams] (optional) internal position
+ * of every camera; info [8] = {panels, first panel of the second chain or -1, first common panel or -1 (both set only
+ * for the plain two-chain schedule), structured factorisation used (0/1), reordered (0/1), first camera of the second
+ * chain or -1, panel chains (segments; 0 = one chain), panels on the critical path}; fill (optional) = structural
+ * blocks / triangle blocks; structure (optional) [panels][panels] bytes, lower triangle, 1 = block of L may be non-zero;
+ * seg3 (optional) [3 * info[6]] = {first panel, end panel, parent segment or -1} of every panel chain, children before
+ * parents: chains that are not ancestor / descendant run concurrently (size it for 3 * 32 ints). */
 int hsfm_ba_debug_structure(int32_t n_cams, const int32_t* cam_first, int32_t natural, int32_t* new_of_old, int32_t* info,
                             double* fill, uint8_t* structure);
+int hsfm_ba_debug_schedule(int32_t n_cams, const int32_t* cam_first, int32_t natural, int32_t* seg3);
 
 /* Multi-GPU (one process per GPU, observations sharded by point, cameras replicated).
  * unique_id: the 128-byte ncclUniqueId produced by hsfm_ba_comm_unique_id() on rank 0 and

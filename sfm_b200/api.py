@@ -38,6 +38,7 @@ SYMBOLS = {
     "hsfm_ba_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "hsfm_ba_set_ordering": (C.c_int, [C.c_void_p, C.c_int]),
     "hsfm_ba_debug_structure": (C.c_int, [C.c_int32, _ip, C.c_int32, _ip, _ip, _dp, C.POINTER(C.c_uint8)]),
+    "hsfm_ba_debug_schedule": (C.c_int, [C.c_int32, _ip, C.c_int32, _ip]),
     "hsfm_ba_comm_unique_id": (C.c_int, [C.c_void_p]),
     "hsfm_ba_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "hsfm_ba_solve_ptr": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, _dp, _ip, C.c_int32, _dp, _pp, _pp, _pp,
@@ -148,9 +149,9 @@ class _SummaryBox:
         return d
 
 
-def debug_structure(cam_first, natural=False):
+def debug_structure(cam_first, natural=False, depth=None):
     """Host-only: camera order, block structure of the Cholesky factor and chain schedule for an envelope
-    (hsfm_ba_debug_structure).  Returns a dict."""
+    (hsfm_ba_debug_structure).  depth: force that dissection depth of the nested two-ended order.  Returns a dict."""
     first = np.ascontiguousarray(cam_first, dtype=np.int32)
     n = first.shape[0]
     perm = np.empty(n, dtype=np.int32)
@@ -158,12 +159,19 @@ def debug_structure(cam_first, natural=False):
     fill = C.c_double()
     panels = (6 * n + 127) // 128
     st = np.zeros((panels, panels), dtype=np.uint8)
-    rc = load_library().hsfm_ba_debug_structure(n, _i(first), int(bool(natural)), _i(perm), _i(info), C.byref(fill),
+    natural = -1 - int(depth) if depth is not None else int(bool(natural))
+    rc = load_library().hsfm_ba_debug_structure(n, _i(first), natural, _i(perm), _i(info), C.byref(fill),
                                                 st.ctypes.data_as(C.POINTER(C.c_uint8)))
     if rc:
         raise BAError(rc, "hsfm_ba_debug_structure")
+    seg3 = np.full(3 * 32, -1, dtype=np.int32)
+    rc = load_library().hsfm_ba_debug_schedule(n, _i(first), natural, _i(seg3))
+    if rc:
+        raise BAError(rc, "hsfm_ba_debug_schedule")
+    segments = [tuple(int(v) for v in seg3[3 * g:3 * g + 3]) for g in range(int(info[6]))]  # (first panel, end panel, parent)
     return dict(new_of_old=perm, panels=int(info[0]), split_a=int(info[1]), split_t0=int(info[2]), structured=bool(info[3]),
-                reordered=bool(info[4]), split_cams=int(info[5]), fill=fill.value, structure=st)
+                reordered=bool(info[4]), split_cams=int(info[5]), fill=fill.value, structure=st, segments=segments,
+                critical_panels=int(info[7]))
 
 
 class Context:

@@ -148,24 +148,34 @@ int hsfm_ba_set_ordering(hsfm_ba_ctx* h, int ordering) {
   return 0;
 }
 
-int hsfm_ba_debug_structure(int32_t n_cams, const int32_t* cam_first, int32_t natural, int32_t* new_of_old, int32_t* info, double* fill,
-                            uint8_t* structure) {
-  if (n_cams <= 0 || !cam_first || !info) return HSFM_BA_ERR_ARG;
+static int debug_plan(int32_t n_cams, const int32_t* cam_first, int32_t natural, std::vector<int>& perm, bool* re, CholPlan& pl, int* split_cams) {
+  if (n_cams <= 0 || !cam_first) return HSFM_BA_ERR_ARG;
   for (int c = 0; c < n_cams; ++c)
     if (cam_first[c] < 0 || cam_first[c] > c) return HSFM_BA_ERR_ARG;
-  std::vector<int> perm;
-  int split_cams = -1;
-  const bool re = !natural && choose_camera_order(n_cams, cam_first, perm, &split_cams);
-  if (!re) { perm.clear(); split_cams = -1; }
-  if (new_of_old)
-    for (int c = 0; c < n_cams; ++c) new_of_old[c] = re ? perm[(size_t)c] : c;
+  *split_cams = -1;
+  *re = natural <= 0 && choose_camera_order(n_cams, cam_first, perm, split_cams, nullptr, natural < 0 ? -natural - 1 : -1);
+  if (!*re) { perm.clear(); *split_cams = -1; }
   std::vector<uint8_t> pattern;
   int panels = 0;
-  block_pattern_from_envelope(n_cams, cam_first, re ? perm.data() : nullptr, pattern, &panels);
+  block_pattern_from_envelope(n_cams, cam_first, *re ? perm.data() : nullptr, pattern, &panels);
+  pl.compute(n_cams, pattern.data(), panels);
+  return 0;
+}
+
+int hsfm_ba_debug_structure(int32_t n_cams, const int32_t* cam_first, int32_t natural, int32_t* new_of_old, int32_t* info, double* fill,
+                            uint8_t* structure) {
+  if (!info) return HSFM_BA_ERR_ARG;
+  std::vector<int> perm;
   CholPlan pl;
-  pl.compute(n_cams, pattern.data(), panels, split_cams > 0 ? (6 * split_cams) / 128 : -1);
+  bool re = false;
+  int split_cams = -1;
+  const int rc = debug_plan(n_cams, cam_first, natural, perm, &re, pl, &split_cams);
+  if (rc) return rc;
+  if (new_of_old)
+    for (int c = 0; c < n_cams; ++c) new_of_old[c] = re ? perm[(size_t)c] : c;
+  const int panels = pl.panels;
   info[0] = panels; info[1] = pl.split_a; info[2] = pl.split_t0; info[3] = pl.use ? 1 : 0; info[4] = re ? 1 : 0; info[5] = split_cams;
-  info[6] = info[7] = 0;
+  info[6] = (int)pl.segs.size(); info[7] = pl.critical;
   if (fill) *fill = pl.fill;
   if (structure) {
     std::memset(structure, 0, (size_t)panels * panels);
@@ -173,6 +183,18 @@ int hsfm_ba_debug_structure(int32_t n_cams, const int32_t* cam_first, int32_t na
       for (int I = 0; I < panels; ++I)
         for (int q = pl.row_off[(size_t)I]; q < pl.row_off[(size_t)I + 1]; ++q) structure[(size_t)I * panels + pl.row_list[(size_t)q]] = 1;
   }
+  return 0;
+}
+
+int hsfm_ba_debug_schedule(int32_t n_cams, const int32_t* cam_first, int32_t natural, int32_t* seg3) {
+  if (!seg3) return HSFM_BA_ERR_ARG;
+  std::vector<int> perm;
+  CholPlan pl;
+  bool re = false;
+  int split_cams = -1;
+  const int rc = debug_plan(n_cams, cam_first, natural, perm, &re, pl, &split_cams);
+  if (rc) return rc;
+  for (size_t g = 0; g < pl.segs.size(); ++g) { seg3[3 * g] = pl.segs[g].begin; seg3[3 * g + 1] = pl.segs[g].end; seg3[3 * g + 2] = pl.segs[g].parent; }
   return 0;
 }
 
@@ -200,7 +222,6 @@ int hsfm_ba_problem_upload(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double
   HSFM_CUDA(cudaSetDevice(h->c.device));
   h->c.has_problem = false;
   h->c.chol_plan_valid = false;
-  h->c.form_valid = false;
   h->c.scan.active = false;  // the resident problem no longer is the scan store's
   double setup = 0, h2d = 0;
   const bool natural = h->c.ordering == 1 || h->c.tap_upload;

@@ -675,13 +675,14 @@ struct GemmSmem {
 };
 constexpr int kGemmSmem = (int)sizeof(GemmSmem);
 
+constexpr int SY_THREADS = 256;  // trailing-update CTA: 8 warps as 4 x 2, 32 x 32 each
 template <int ROWS>
 __device__ __forceinline__ void load_tile_async(double (*dst)[LDS_], const double* __restrict__ src, int ld, int row0, int rows_valid,
                                                 int col0) {
-  // ROWS rows × 32 doubles = ROWS*16 chunks of 16 B over 128 threads
+  // ROWS rows × 32 doubles = ROWS*16 chunks of 16 B over the CTA's threads
 #pragma unroll
-  for (int q = 0; q < ROWS / 8; ++q) {
-    const int e = threadIdx.x + 128 * q;
+  for (int q = 0; q < ROWS * 16 / SY_THREADS; ++q) {
+    const int e = threadIdx.x + SY_THREADS * q;
     const int row = e >> 4, ch = e & 15;
     double* d = &dst[row][ch * 2];
     if (row < rows_valid) cp_async16(d, src + (size_t)(row0 + row) * ld + col0 + ch * 2);
@@ -689,13 +690,14 @@ __device__ __forceinline__ void load_tile_async(double (*dst)[LDS_], const doubl
   }
 }
 
-struct SyrkTile { int ri, ni, rj, nj; };
+struct SyrkTile { int ri, ni, rj, nj, oi, oj; };  // operand rows in S; oi, oj: row / column of the output tile in its matrix
 // rb_list != nullptr: structured mode — the tiles are pairs (a, b), b <= a, of the panel's ACTIVE 128-row blocks
 // rb_list[0 .. cnt) (global block indices, ascending), two 64-wide tiles per pair, enumerated column by column:
 // column b holds the rows a = b .. cnt-1.  A launch with fewer tiles than all pairs covers the first block columns
 // only (the two-chain schedule defers the others); col_first == -2 skips pair (0, 0), which the chain stream
 // updates itself.
-__device__ __forceinline__ SyrkTile syrk_tile(int t, int n, int base, int row_first, int col_first, const int* __restrict__ rb_list, int cnt) {
+__device__ __forceinline__ SyrkTile syrk_tile(int t, int n, int base, int row_first, int col_first, const int* __restrict__ rb_list, int cnt,
+                                              const int* __restrict__ side_list) {
   SyrkTile T;
   if (rb_list) {
     const int half = t & 1;
@@ -705,6 +707,8 @@ __device__ __forceinline__ SyrkTile syrk_tile(int t, int n, int base, int row_fi
     const int a = b + pp;
     T.ri = __ldg(rb_list + a) * NB; T.ni = min(NB, n - T.ri);
     T.rj = __ldg(rb_list + b) * NB + half * TN; T.nj = min(TN, n - T.rj);
+    T.oi = side_list ? __ldg(side_list + a) * NB : T.ri;
+    T.oj = side_list ? __ldg(side_list + b) * NB + half * TN : T.rj;
     return T;
   }
   int bi, bj;
@@ -721,12 +725,13 @@ __device__ __forceinline__ SyrkTile syrk_tile(int t, int n, int base, int row_fi
   }
   T.ri = base + bi * NB; T.ni = min(NB, n - T.ri);
   T.rj = base + bj * TN; T.nj = min(TN, n - T.rj);
+  T.oi = T.ri; T.oj = T.rj;
   return T;
 }
 
-__global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ S, int n, int k0, int row_first, int col_first, int n_tiles,
+__global__ void __launch_bounds__(SY_THREADS, 2) chol_syrk_kernel(double* __restrict__ S, int n, int k0, int row_first, int col_first, int n_tiles,
                                                            int stagger, const int* __restrict__ fail, const int* __restrict__ rb_list, int rb_cnt,
-                                                           double* __restrict__ Cside, int ldc_side, int side_blk0) {
+                                                           double* __restrict__ Cside, int ldc_side, const int* __restrict__ side_list) {
   extern __shared__ __align__(16) unsigned char gsm_raw[];
   GemmSmem& sm = *reinterpret_cast<GemmSmem*>(gsm_raw);
   int t = blockIdx.x;
@@ -734,7 +739,7 @@ __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ 
   const int failed = *fail;
   const int base = k0 + NB;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int wr = warp >> 1, wc = warp & 1;  // 2 × 2 warps, 64 × 32 each
+  const int wr = warp >> 1, wc = warp & 1;  // 4 × 2 warps, 32 × 32 each
   const int fr = lane >> 2, fk = lane & 3;
 
   // All CTAs of a launch start together; left alone, the two CTAs of an SM (and the whole GPU) stay in
@@ -745,7 +750,7 @@ __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ 
     const long long t0 = clock64();
     while (clock64() - t0 < 16000) { }
   }
-  SyrkTile cur = syrk_tile(t, n, base, row_first, col_first, rb_list, rb_cnt);
+  SyrkTile cur = syrk_tile(t, n, base, row_first, col_first, rb_list, rb_cnt, side_list);
   load_tile_async<NB>(sm.a[0], S, n, cur.ri, cur.ni, k0);
   load_tile_async<TN>(sm.b[0], S, n, cur.rj, cur.nj, k0);
   cp_async_commit();
@@ -756,29 +761,28 @@ __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ 
     const int t_next = t + gridDim.x;
     const bool has_next = t_next < n_tiles;
     SyrkTile nxt = cur;
-    if (has_next) nxt = syrk_tile(t_next, n, base, row_first, col_first, rb_list, rb_cnt);
+    if (has_next) nxt = syrk_tile(t_next, n, base, row_first, col_first, rb_list, rb_cnt, side_list);
     // C → accumulators.  Full tiles take an unpredicated path: one row pointer per 8-row group, the four
     // column tiles at immediate offsets, every load straight into its accumulator pair — nothing recycles a
     // register, so all 32 loads are in flight at once.
-    double acc[8][4][2];
-    // the output tile: in place in S, or (Cside) in the side matrix whose block (0, 0) is block (side_blk0, side_blk0) of S
+    double acc[4][4][2];
+    // the output tile: in place in S, or (Cside) in a side matrix at the block positions side_list gives (CholPlan::Seg)
     double* const cbase = Cside ? Cside : S;
     const size_t ldc = Cside ? (size_t)ldc_side : (size_t)n;
-    const int coff = Cside ? side_blk0 * NB : 0;
-    double* const crow = cbase + (size_t)(cur.ri - coff + wr * 64 + fr) * ldc + (cur.rj - coff) + wc * 32 + 2 * fk;
+    double* const crow = cbase + (size_t)(cur.oi + wr * 32 + fr) * ldc + cur.oj + wc * 32 + 2 * fk;
     const size_t rstep = 8 * ldc;
     const bool full = (cur.ni == NB) && (cur.nj == TN);
 #ifdef HSFM_SYRK_NOLOAD
     if (full) {
 #pragma unroll
-      for (int a = 0; a < 8; ++a)
+      for (int a = 0; a < 4; ++a)
 #pragma unroll
         for (int b = 0; b < 4; ++b) { acc[a][b][0] = 0.0; acc[a][b][1] = 0.0; }
     } else
 #endif
     if (full) {
 #pragma unroll
-      for (int a = 0; a < 8; ++a) {
+      for (int a = 0; a < 4; ++a) {
         const double2* p = reinterpret_cast<const double2*>(crow + a * rstep);
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
@@ -788,11 +792,11 @@ __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ 
       }
     } else {
 #pragma unroll
-      for (int a = 0; a < 8; ++a)
+      for (int a = 0; a < 4; ++a)
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
           acc[a][b][0] = 0.0; acc[a][b][1] = 0.0;
-          const int row = wr * 64 + a * 8 + fr, col = wc * 32 + b * 8 + 2 * fk;
+          const int row = wr * 32 + a * 8 + fr, col = wc * 32 + b * 8 + 2 * fk;
           if (row < cur.ni && col < cur.nj) {
             const double2 c = __ldcs(reinterpret_cast<const double2*>(crow + a * rstep) + b * 4);
             acc[a][b][0] = c.x; acc[a][b][1] = c.y;
@@ -802,11 +806,11 @@ __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ 
     if (has_next) {
       // next tile's C → L2: 128 rows × 512 B = 4 lines per row, one line per thread per pass
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int e = threadIdx.x + 128 * q;
+      for (int q = 0; q < 512 / SY_THREADS; ++q) {
+        const int e = threadIdx.x + SY_THREADS * q;
         const int row = e >> 2, seg = e & 3;
         if (row < nxt.ni && seg * 16 < nxt.nj)
-          asm volatile("prefetch.global.L2 [%0];" ::"l"(cbase + (size_t)(nxt.ri - coff + row) * ldc + (nxt.rj - coff) + seg * 16));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(cbase + (size_t)(nxt.oi + row) * ldc + nxt.oj + seg * 16));
       }
     }
 #pragma unroll 1
@@ -823,13 +827,13 @@ __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ 
       __syncthreads();
 #pragma unroll
       for (int ks = 0; ks < KC / 4; ++ks) {
-        double af[8], bf[4];
+        double af[4], bf[4];
 #pragma unroll
-        for (int a = 0; a < 8; ++a) af[a] = -sm.a[stage][wr * 64 + a * 8 + fr][ks * 4 + fk];
+        for (int a = 0; a < 4; ++a) af[a] = -sm.a[stage][wr * 32 + a * 8 + fr][ks * 4 + fk];
 #pragma unroll
         for (int b = 0; b < 4; ++b) bf[b] = sm.b[stage][wc * 32 + b * 8 + fr][ks * 4 + fk];
 #pragma unroll
-        for (int a = 0; a < 8; ++a)
+        for (int a = 0; a < 4; ++a)
 #pragma unroll
           for (int b = 0; b < 4; ++b) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
       }
@@ -844,15 +848,15 @@ __global__ void __launch_bounds__(128, 2) chol_syrk_kernel(double* __restrict__ 
 #endif
     if (full) {
 #pragma unroll
-      for (int a = 0; a < 8; ++a) {
+      for (int a = 0; a < 4; ++a) {
         double2* p = reinterpret_cast<double2*>(crow + a * rstep);
 #pragma unroll
         for (int b = 0; b < 4; ++b) p[b * 4] = make_double2(acc[a][b][0], acc[a][b][1]);
       }
     } else {
 #pragma unroll
-      for (int a = 0; a < 8; ++a) {
-        const int row = wr * 64 + a * 8 + fr;
+      for (int a = 0; a < 4; ++a) {
+        const int row = wr * 32 + a * 8 + fr;
         if (row >= cur.ni) continue;
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
@@ -1569,43 +1573,35 @@ int CholAux::init() {
   HSFM_CUDA(cudaEventCreateWithFlags(&ev_rest, cudaEventDisableTiming));
   HSFM_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
   HSFM_CUDA(cudaEventCreateWithFlags(&ev_next, cudaEventDisableTiming));
-  HSFM_CUDA(cudaEventCreateWithFlags(&ev_doneA, cudaEventDisableTiming));
-  HSFM_CUDA(cudaStreamCreateWithPriority(&chainB.chain, cudaStreamNonBlocking, hi));
-  HSFM_CUDA(cudaStreamCreateWithPriority(&chainB.bulk, cudaStreamNonBlocking, lo));
-  HSFM_CUDA(cudaEventCreateWithFlags(&chainB.ev_panel, cudaEventDisableTiming));
-  HSFM_CUDA(cudaEventCreateWithFlags(&chainB.ev_next, cudaEventDisableTiming));
-  HSFM_CUDA(cudaEventCreateWithFlags(&chainB.ev_rest, cudaEventDisableTiming));
-  HSFM_CUDA(cudaEventCreateWithFlags(&chainB.ev_done, cudaEventDisableTiming));
-  HSFM_CUDA(cudaStreamCreateWithPriority(&form_stream, cudaStreamNonBlocking, lo));
-  HSFM_CUDA(cudaStreamCreateWithPriority(&tailA, cudaStreamNonBlocking, lo));
-  HSFM_CUDA(cudaStreamCreateWithPriority(&tailB, cudaStreamNonBlocking, lo));
-  for (cudaEvent_t* e : {&ev_trsmA, &ev_trsmB, &ev_tailA, &ev_tailB}) HSFM_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+  HSFM_CUDA(cudaEventCreateWithFlags(&ev_zero, cudaEventDisableTiming));
+  sets.resize(CHOL_STREAM_SETS);
+  for (CholChainSet& c : sets) {
+    HSFM_CUDA(cudaStreamCreateWithPriority(&c.chain, cudaStreamNonBlocking, hi));
+    HSFM_CUDA(cudaStreamCreateWithPriority(&c.bulk, cudaStreamNonBlocking, lo));
+    HSFM_CUDA(cudaStreamCreateWithPriority(&c.tail, cudaStreamNonBlocking, lo));
+    for (cudaEvent_t* e : {&c.ev_panel, &c.ev_next, &c.ev_rest, &c.ev_trsm, &c.ev_tail, &c.ev_joined}) HSFM_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+  }
+  ev_seg.assign(MAX_CHOL_SEGMENTS, nullptr);
+  for (cudaEvent_t& e : ev_seg) HSFM_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   return 0;
 }
 void CholAux::destroy() {
   if (graph) { cudaGraphExecDestroy(graph); graph = nullptr; }
+  for (CholChainSet& c : sets) {
+    if (c.chain) cudaStreamDestroy(c.chain);
+    if (c.bulk) cudaStreamDestroy(c.bulk);
+    if (c.tail) cudaStreamDestroy(c.tail);
+    for (cudaEvent_t e : {c.ev_panel, c.ev_next, c.ev_rest, c.ev_trsm, c.ev_tail, c.ev_joined})
+      if (e) cudaEventDestroy(e);
+  }
+  sets.clear();
+  for (cudaEvent_t e : ev_seg)
+    if (e) cudaEventDestroy(e);
+  ev_seg.clear();
+  if (ev_zero) { cudaEventDestroy(ev_zero); ev_zero = nullptr; }
   if (!stream) return;
   cudaStreamDestroy(stream);
   cudaEventDestroy(ev_fork); cudaEventDestroy(ev_panel); cudaEventDestroy(ev_rest); cudaEventDestroy(ev_join); cudaEventDestroy(ev_next);
-  if (ev_doneA) cudaEventDestroy(ev_doneA);
-  if (chainB.chain) cudaStreamDestroy(chainB.chain);
-  if (chainB.bulk) cudaStreamDestroy(chainB.bulk);
-  if (chainB.ev_panel) cudaEventDestroy(chainB.ev_panel);
-  if (chainB.ev_next) cudaEventDestroy(chainB.ev_next);
-  if (chainB.ev_rest) cudaEventDestroy(chainB.ev_rest);
-  if (chainB.ev_done) cudaEventDestroy(chainB.ev_done);
-  chainB = CholChain();
-  ev_doneA = nullptr;
-  if (form_stream) cudaStreamDestroy(form_stream);
-  form_stream = nullptr;
-  if (tailA) cudaStreamDestroy(tailA);
-  if (tailB) cudaStreamDestroy(tailB);
-  tailA = tailB = nullptr;
-  for (cudaEvent_t* e : {&ev_trsmA, &ev_trsmB, &ev_tailA, &ev_tailB}) { if (*e) cudaEventDestroy(*e); *e = nullptr; }
-  for (cudaEvent_t e : ev_form) cudaEventDestroy(e);
-  ev_form.clear();
-  if (form_counters) cudaFree(form_counters);
-  form_counters = nullptr; form_counters_cap = 0;
   stream = nullptr;
 }
 
@@ -1620,14 +1616,13 @@ void CholAux::destroy() {
 // Envelope plan
 // ---------------------------------------------------------------------------------------------
 // Host part of build(): structure lists and schedule.  Returns false when the plan already holds this structure.
-bool CholPlan::compute(int n_cams, const uint8_t* pattern, int P, int split_hint) {
+bool CholPlan::compute(int n_cams, const uint8_t* pattern, int P) {
   const int n_new = 6 * n_cams, panels_new = (n_new + NB - 1) / NB;
   {
     // same structure as the plan already holds (the per-keyframe calls of a scan mostly re-solve an unchanged camera
     // graph, and bench restarts the same problem): keep plan, device lists, version — and the captured launch graph
     std::vector<uint8_t> k;
     if (pattern && P == panels_new) k.assign(pattern, pattern + (size_t)P * P);
-    k.push_back((uint8_t)(split_hint & 0xff)); k.push_back((uint8_t)((split_hint >> 8) & 0xff));
     if (n == n_new && version > 0 && k == key) return false;
     key.swap(k);
   }
@@ -1638,15 +1633,11 @@ bool CholPlan::compute(int n_cams, const uint8_t* pattern, int P, int split_hint
   off.assign((size_t)panels, 0); cnt.assign((size_t)panels, 0); list.clear();
   row_off.assign((size_t)panels + 1, 0); row_list.clear();
   blk_off.clear();
+  segs.clear(); side.clear(); anc_all.clear(); map_all.clear(); side_total = 0; critical = panels;
   if (!pattern || P != panels || panels < 4) return true;
   std::vector<uint8_t> st(pattern, pattern + (size_t)P * P);
   symbolic_block_factor(P, st);
-  for (int K = 0; K < P; ++K) {
-    off[K] = (int)list.size();
-    for (int I = K + 1; I < P; ++I)
-      if (st[(size_t)I * P + K]) list.push_back(I);
-    cnt[K] = (int)list.size() - off[K];
-  }
+  structure_lists(P, st, off, cnt, list);
   for (int I = 0; I < P; ++I) {
     row_off[I] = (int)row_list.size();
     for (int J = 0; J < I; ++J)
@@ -1658,15 +1649,44 @@ bool CholPlan::compute(int n_cams, const uint8_t* pattern, int P, int split_hint
   static const bool force_dense = getenv("HSFM_CHOL_DENSE") != nullptr;  // experiment knob
   use = fill < 0.6 && !force_dense;
   if (!use) return true;
-  // two-chain schedule: chain 0 = [0, a), chain 1 = [a, t0) with t0 the first panel >= a that chain 0 updates
-  if (split_hint > 0 && split_hint < P) {
-    int t0 = P;
-    for (int K = 0; K < split_hint; ++K)
-      for (int q = 0; q < cnt[K]; ++q)
-        if (list[(size_t)off[K] + q] >= split_hint) { t0 = std::min(t0, list[(size_t)off[K] + q]); break; }
-    // worth it only if the second chain has a real share of the panels to itself
+  // panel chains: the paths of the block elimination tree
+  {
+    std::vector<PanelSeg> ps;
+    std::vector<int> seg_of;
+    panel_segments(P, off, cnt, list, ps, seg_of);
     static const bool one_chain = getenv("HSFM_ONE_CHAIN") != nullptr;  // experiment knob
-    if (!one_chain && t0 - split_hint >= 4 && t0 - split_hint >= split_hint / 4) { split_a = split_hint; split_t0 = t0; }
+    const int crit = critical_panels(ps);
+    // worth it only when the concurrent chains shorten the critical path for real
+    if (!one_chain && ps.size() > 1 && ps.size() <= (size_t)MAX_CHOL_SEGMENTS && crit <= (9 * P) / 10) {
+      segs.resize(ps.size());
+      int next_slot = 0;
+      for (size_t g = 0; g < ps.size(); ++g) { segs[g].begin = ps[g].begin; segs[g].end = ps[g].end; segs[g].parent = ps[g].parent; }
+      for (size_t g = 0; g < ps.size(); ++g)
+        if (segs[g].parent >= 0) segs[(size_t)segs[g].parent].children.push_back((int)g);
+      for (size_t g = 0; g < segs.size(); ++g) {
+        Seg& sg = segs[g];
+        sg.slot = sg.children.empty() ? next_slot++ : segs[(size_t)sg.children[0]].slot;  // a parent carries on where its first child ran
+        for (int a = sg.parent; a >= 0; a = segs[(size_t)a].parent)
+          for (int K = segs[(size_t)a].begin; K < segs[(size_t)a].end; ++K) sg.anc.push_back(K);
+        sg.anc_off = (int)anc_all.size();
+        anc_all.insert(anc_all.end(), sg.anc.begin(), sg.anc.end());
+        sg.side_off = side_total;
+        side_total += (long long)sg.anc.size() * NB * (long long)sg.anc.size() * NB;
+      }
+      map_all.assign(segs.size() * (size_t)P, -1);
+      for (size_t g = 0; g < segs.size(); ++g)
+        for (size_t q = 0; q < segs[g].anc.size(); ++q) map_all[g * (size_t)P + (size_t)segs[g].anc[q]] = (int)q;
+      side.assign(list.size(), -1);
+      for (int K = 0; K < P; ++K) {
+        const int g = seg_of[(size_t)K];
+        for (int q = 0; q < cnt[K]; ++q) {
+          const int I = list[(size_t)off[K] + q];
+          if (I >= segs[(size_t)g].end) side[(size_t)off[K] + q] = map_all[(size_t)g * P + (size_t)I];  // -1 here would break the etree property
+        }
+      }
+      critical = crit;
+      if (segs.size() == 3 && segs[0].parent == 2 && segs[1].parent == 2) { split_a = segs[1].begin; split_t0 = segs[2].begin; }
+    }
   }
   blk_off.assign((size_t)panels + 1, 0);
   for (int I = 0; I < panels; ++I) {
@@ -1676,9 +1696,9 @@ bool CholPlan::compute(int n_cams, const uint8_t* pattern, int P, int split_hint
   return true;
 }
 
-int CholPlan::build(int n_cams, const uint8_t* pattern, int P, int split_hint, cudaStream_t s) {
-  if (!compute(n_cams, pattern, P, split_hint) || !use) return 0;
-  const size_t need = list.size() + row_off.size() + row_list.size() + 2 * (size_t)panels + 1;
+int CholPlan::build(int n_cams, const uint8_t* pattern, int P, cudaStream_t s) {
+  if (!compute(n_cams, pattern, P) || !use) return 0;
+  const size_t need = 2 * list.size() + row_off.size() + row_list.size() + 2 * (size_t)panels + anc_all.size() + map_all.size() + 1;
   if (need > d_cap) {
     if (d_ints) cudaFree(d_ints);
     d_ints = nullptr; d_cap = 0;
@@ -1690,6 +1710,9 @@ int CholPlan::build(int n_cams, const uint8_t* pattern, int P, int split_hint, c
   d_row_list = d_row_off + row_off.size();
   d_col_off = d_row_list + row_list.size();
   d_col_cnt = d_col_off + panels;
+  d_side = d_col_cnt + panels;
+  d_anc = d_side + list.size();
+  d_map = d_anc + anc_all.size();
   if ((size_t)panels + 1 > d_blk_cap) {
     if (d_blk_off) cudaFree(d_blk_off);
     d_blk_off = nullptr; d_blk_cap = 0;
@@ -1702,6 +1725,9 @@ int CholPlan::build(int n_cams, const uint8_t* pattern, int P, int split_hint, c
   HSFM_CUDA(cudaMemcpyAsync(d_row_list, row_list.data(), sizeof(int) * row_list.size(), cudaMemcpyHostToDevice, s));
   HSFM_CUDA(cudaMemcpyAsync(d_col_off, off.data(), sizeof(int) * (size_t)panels, cudaMemcpyHostToDevice, s));
   HSFM_CUDA(cudaMemcpyAsync(d_col_cnt, cnt.data(), sizeof(int) * (size_t)panels, cudaMemcpyHostToDevice, s));
+  if (!side.empty()) HSFM_CUDA(cudaMemcpyAsync(d_side, side.data(), sizeof(int) * side.size(), cudaMemcpyHostToDevice, s));
+  if (!anc_all.empty()) HSFM_CUDA(cudaMemcpyAsync(d_anc, anc_all.data(), sizeof(int) * anc_all.size(), cudaMemcpyHostToDevice, s));
+  if (!map_all.empty()) HSFM_CUDA(cudaMemcpyAsync(d_map, map_all.data(), sizeof(int) * map_all.size(), cudaMemcpyHostToDevice, s));
   HSFM_CUDA(cudaStreamSynchronize(s));  // the host vectors may be rebuilt by the next problem
   return 0;
 }
@@ -1755,18 +1781,14 @@ struct ChainStreams {
   cudaEvent_t ev_trsm = nullptr;
 };
 static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainStreams& cs, int64_t* launches, const CholPlan& pl, int n_sm,
-                      int K_begin, int K_end, int own_end, double* Ctail, cudaEvent_t start_ev, const FormSchedule* form = nullptr,
-                      const std::vector<cudaEvent_t>* ev_form = nullptr) {
+                      int K_begin, int K_end, int own_end, double* Cside, int ld_side, cudaEvent_t start_ev) {
   const bool la = cs.la;
-  int form_waited = -1;  // chunks of the fused formation of S this chain has already waited for
   cudaStream_t s = cs.bulk, s2 = cs.chain;
-  const int ldt = (pl.panels - own_end) * NB;
   // Grid caps of the panel solves / trailing updates: experiment knobs.  (Measured with two chains in flight, c4: capping
   // them to 48 CTAs so that the other chain's kernels find empty SMs makes the factorisation SLOWER, 2.27 -> 3.0 ms: the
   // bulk step, ~180 tiles of 8 us of DMMA issue each, is itself close to the panel period.)
   static const int cap_syrk_env = getenv("HSFM_BULK_SYRK_CTAS") ? atoi(getenv("HSFM_BULK_SYRK_CTAS")) : 0;
   static const int cap_trsm_env = getenv("HSFM_BULK_TRSM_CTAS") ? atoi(getenv("HSFM_BULK_TRSM_CTAS")) : 0;
-  const bool shared_gpu = pl.split_a > 0 && K_end <= pl.split_t0;  // one of the two concurrent chains
   const int cap_syrk = cap_syrk_env > 0 ? cap_syrk_env : 2 * n_sm;
   const int cap_trsm = cap_trsm_env > 0 ? cap_trsm_env : n_sm;
   auto trsm = [&](cudaStream_t st, int k0, double* Linv, const int* list, int cnt) {
@@ -1776,13 +1798,14 @@ static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainS
     chol_trsm_strip_kernel<<<cnt * spb, 256, rows_per * TS_LD * (int)sizeof(double), st>>>(S, n, k0, Linv, rows_per, fail_flag, list, spb);
     ++*launches;
   };
-  auto syrk = [&](cudaStream_t st, int k0, int col_first, int tiles, const int* list, int cnt, double* C, int ldc, int blk0) {
+  auto syrk = [&](cudaStream_t st, int k0, int col_first, int tiles, const int* list, int cnt, double* C, int ldc, const int* side_list) {
     if (tiles <= 0) return;
-    chol_syrk_kernel<<<min(tiles, cap_syrk), 128, kGemmSmem, st>>>(S, n, k0, 0, col_first, tiles, 0, fail_flag, list, cnt, C, ldc, blk0);
+    chol_syrk_kernel<<<min(tiles, cap_syrk), SY_THREADS, kGemmSmem, st>>>(S, n, k0, 0, col_first, tiles, 0, fail_flag, list, cnt, C, ldc, side_list);
     ++*launches;
   };
-  // tail x tail pairs of the panel -> side matrix, right after the panel solve; off the bulk stream when the chain has a tail stream
-  auto tail_update = [&](int k0, const int* list, int n_own, int ct) {
+  // pairs of the panel's rows beyond its own segment -> side matrix, right after the panel solve; off the bulk stream when the
+  // chain has a tail stream (they are wanted only when the parent segment starts)
+  auto tail_update = [&](int K, int k0, const int* list, int n_own, int ct) {
     if (ct <= 0) return;
     cudaStream_t st = s;
     if (la && cs.tail) {
@@ -1790,7 +1813,7 @@ static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainS
       cudaStreamWaitEvent(cs.tail, cs.ev_trsm, 0);
       st = cs.tail;
     }
-    syrk(st, k0, -1, ct * (ct + 1), list + n_own, ct, Ctail, ldt, own_end);
+    syrk(st, k0, -1, ct * (ct + 1), list + n_own, ct, Cside, ld_side, pl.d_side + pl.off[K] + n_own);
   };
   // chain-stream launches carry the programmatic-serialisation attribute (see pdl_enter)
   static const bool no_pdl = getenv("HSFM_NO_PDL") != nullptr;  // experiment knob
@@ -1808,11 +1831,6 @@ static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainS
   for (int K = K_begin, k0 = K_begin * NB; K < K_end; ++K, k0 += NB) {
     const int kb = min(NB, n - k0);
     double* Linv = ws + (size_t)K * NB * NB;
-    if (form && form->need_chunk[(size_t)K] > form_waited) {
-      // every column of S this panel step reads or writes must have received all its contributions
-      form_waited = form->need_chunk[(size_t)K];
-      cudaStreamWaitEvent(s2, (*ev_form)[(size_t)form_waited], 0);
-    }
     {
       cudaLaunchConfig_t cfg = chain_cfg(1, 256, kDiagSmem);
       cudaLaunchKernelEx(&cfg, chol_diag_kernel, S, n, k0, kb, Linv, fail_flag);
@@ -1843,8 +1861,8 @@ static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainS
       if (la) cudaStreamWaitEvent(s, cs.ev_panel, 0);
       if (la) cudaStreamWaitEvent(s, cs.ev_next, 0);
       trsm(s, k0, Linv, list, cnt);
-      tail_update(k0, list, n_own, ct);
-      syrk(s, k0, -2, 2 * (pairs_own - 1), list, cnt, nullptr, 0, 0);
+      tail_update(K, k0, list, n_own, ct);
+      syrk(s, k0, -2, 2 * (pairs_own - 1), list, cnt, nullptr, 0, nullptr);
       if (la) { cudaEventRecord(cs.ev_rest, s); rest_pending = true; }
       continue;
     }
@@ -1866,13 +1884,13 @@ static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainS
       const int* rl = has_col ? list + 1 : list;
       if (la) cudaStreamWaitEvent(s, cs.ev_panel, 0);
       trsm(s, k0, Linv, rl, rest_cnt);
-      tail_update(k0, list, n_own, ct);
+      tail_update(K, k0, list, n_own, ct);
       if (has_col) {
         // one update launch for column K+1 below its diagonal tile and every other active pair
         if (la) cudaStreamWaitEvent(s, cs.ev_next, 0);
-        syrk(s, k0, -2, 2 * (pairs_own - 1), list, cnt, nullptr, 0, 0);
+        syrk(s, k0, -2, 2 * (pairs_own - 1), list, cnt, nullptr, 0, nullptr);
       } else {
-        syrk(s, k0, -1, 2 * pairs_own, list, cnt, nullptr, 0, 0);
+        syrk(s, k0, -1, 2 * pairs_own, list, cnt, nullptr, 0, nullptr);
       }
       if (la) { cudaEventRecord(cs.ev_rest, s); rest_pending = true; }
     }
@@ -1881,189 +1899,108 @@ static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainS
   if (la && rest_pending) cudaStreamWaitEvent(s2, cs.ev_rest, 0);
 }
 
-// S[tail, tail] += T over the lower block triangle of the tail (row blocks >= t0): the join of the two-chain schedule.
-__global__ void __launch_bounds__(256) tail_add_kernel(double* __restrict__ S, int n, int t0, const double* __restrict__ T, int ldt,
-                                                       const double* __restrict__ T2) {
-  const int r = t0 * NB + blockIdx.x;  // matrix row
+// Join of the segment tree: a segment that starts folds the side matrix of one child (order na_c * 128, over the child's
+// ancestor panels anc_c) into S — the blocks of its OWN columns [own_begin, own_end) — and into its own side matrix — the
+// blocks of ITS ancestors' columns (map_p: panel -> position in the parent's side matrix).  One CTA per row of the child's
+// side matrix, lower block triangle, whole diagonal blocks.  Children are folded one after the other on one stream: the
+// summation order is fixed.
+__global__ void __launch_bounds__(256) side_join_kernel(double* __restrict__ S, int n, const double* __restrict__ Tc, int na_c,
+                                                        const int* __restrict__ anc_c, int own_begin, int own_end, double* __restrict__ Tp,
+                                                        int ld_p, const int* __restrict__ map_p) {
+  const int lr = blockIdx.x, lb = lr / NB, rr = lr - lb * NB;
+  const int I = __ldg(anc_c + lb), r = I * NB + rr;
   if (r >= n) return;
-  const int c_end = min(n, (r / NB + 1) * NB) - t0 * NB;  // columns up to the end of the row's diagonal block
-  double2* dst = reinterpret_cast<double2*>(S + (size_t)r * n + (size_t)t0 * NB);
-  const double2* src = reinterpret_cast<const double2*>(T + (size_t)blockIdx.x * ldt);
-  const double2* src2 = T2 ? reinterpret_cast<const double2*>(T2 + (size_t)blockIdx.x * ldt) : nullptr;
-  for (int e = threadIdx.x; e < c_end / 2; e += 256) {
-    double2 v = dst[e];
+  const int ld_c = na_c * NB;
+  const double2* src = reinterpret_cast<const double2*>(Tc + (size_t)lr * ld_c);
+  for (int e = threadIdx.x; e < (lb + 1) * (NB / 2); e += 256) {
+    const int q = e / (NB / 2), c2 = (e - q * (NB / 2)) * 2;
+    const int J = __ldg(anc_c + q);
+    if (J * NB + c2 >= n) continue;
+    double2* dst;
+    if (J >= own_begin && J < own_end) dst = reinterpret_cast<double2*>(S + (size_t)r * n + (size_t)J * NB + c2);
+    else dst = reinterpret_cast<double2*>(Tp + (size_t)(__ldg(map_p + I) * NB + rr) * ld_p + (size_t)__ldg(map_p + J) * NB + c2);
+    double2 v = *dst;
     const double2 a = src[e];
     v.x += a.x; v.y += a.y;
-    if (src2) { const double2 b = src2[e]; v.x += b.x; v.y += b.y; }  // fixed order: S + T_A + T_B
-    dst[e] = v;
+    *dst = v;
   }
 }
 
-// One chain over all panels, or — when the plan carries a two-chain schedule (two-ended camera order, ba_order.cpp)
-// — chain A = panels [0, a) and chain B = [a, t0) concurrently on their own stream pairs, then the tail [t0, panels)
-// as a single chain.  Both chains update the tail blocks (>= t0): chain B in S, chain A in the side matrix T (after the
-// L11^-1 blocks in the workspace), which is added to S at the join — the two never write the same memory and the
-// summation order is fixed.
+// One chain over all panels, or — when the plan carries a segment tree (CholPlan::segs: the two-ended / nested camera
+// orders of ba_order.cpp) — every segment as a chain of its own on one of the stream sets of CholAux, started as soon as
+// its children are done.  Updates a segment makes to its ancestors' blocks go to its side matrix (after the L11^-1 blocks
+// in the workspace) and are folded in by side_join_kernel when the parent starts: concurrent segments never write the
+// same memory and the summation order is fixed.
 static void launch_cholesky_struct(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches,
-                                   const CholPlan& pl, int n_sm, const FormSchedule* form) {
+                                   const CholPlan& pl, int n_sm) {
   static const bool no_la = getenv("HSFM_NO_LOOKAHEAD") != nullptr;
   const bool la = aux && aux->stream && !no_la;
-  ChainStreams A{la ? aux->stream : s, s, la ? aux->ev_panel : nullptr, la ? aux->ev_next : nullptr, la ? aux->ev_rest : nullptr, la};
-  const bool two = la && pl.split_a > 0 && pl.split_t0 > pl.split_a && aux->chainB.chain;
-  const bool fused = two && form && form->use && aux->form_stream && aux->ev_form.size() >= form->chunk_tile0.size() && aux->form_counters;
-  const int nt = (pl.panels - pl.split_t0) * NB;  // order of the tail
-  double* T = ws + cholesky_workspace_doubles(n);
-  double* T_B = T + (size_t)nt * nt;
-  if (two) cudaMemsetAsync(T, 0, sizeof(double) * (size_t)nt * nt * (fused ? 2 : 1), s);
-  if (form && form->use) cudaMemsetAsync(aux->form_counters, 0, sizeof(int) * form->chunk_tile0.size(), s);
-  if (la) {
-    cudaEventRecord(aux->ev_fork, s);
-    cudaStreamWaitEvent(A.chain, aux->ev_fork, 0);
-  }
-  if (!two) {
-    if (form && form->use) {  // no second chain after all: form S in one go, then factor
-      for (size_t g = 0; g < form->chunk_tile0.size(); ++g) { form->launch_chunk(form->chunk_tile0[g], form->chunk_count[g], aux->form_counters + g, s); ++*launches; }
-      if (la) { cudaEventRecord(aux->ev_fork, s); cudaStreamWaitEvent(A.chain, aux->ev_fork, 0); }
-    }
-    run_chain(S, n, ws, fail_flag, A, launches, pl, n_sm, 0, pl.panels, pl.panels, nullptr, nullptr);
-  } else {
-    const CholChain& cb = aux->chainB;
-    ChainStreams B{cb.chain, cb.bulk, cb.ev_panel, cb.ev_next, cb.ev_rest, true};
-    static const bool no_tail_stream = getenv("HSFM_NO_TAIL_STREAM") != nullptr;  // experiment knob
-    if (!no_tail_stream && aux->tailA && aux->tailB) {
-      A.tail = aux->tailA; A.ev_trsm = aux->ev_trsmA;
-      B.tail = aux->tailB; B.ev_trsm = aux->ev_trsmB;
-    }
-    cudaStreamWaitEvent(B.chain, aux->ev_fork, 0);
-    cudaStreamWaitEvent(B.bulk, aux->ev_fork, 0);
-    const int a = pl.split_a, t0 = pl.split_t0;
-    if (fused) {
-      // S is formed chunk by chunk on its own stream; the chains follow the frontier (run_chain waits per panel)
-      cudaStream_t fs = aux->form_stream;
-      cudaStreamWaitEvent(fs, aux->ev_fork, 0);
-      for (size_t g = 0; g < form->chunk_tile0.size(); ++g) {
-        form->launch_chunk(form->chunk_tile0[g], form->chunk_count[g], aux->form_counters + g, fs);
-        ++*launches;
-        cudaEventRecord(aux->ev_form[g], fs);
-      }
-    } else if (form && form->use) {
-      for (size_t g = 0; g < form->chunk_tile0.size(); ++g) { form->launch_chunk(form->chunk_tile0[g], form->chunk_count[g], aux->form_counters + g, s); ++*launches; }
+  if (!la || pl.segs.size() < 2 || aux->sets.empty() || aux->ev_seg.size() < pl.segs.size()) {
+    ChainStreams A{la ? aux->stream : s, s, la ? aux->ev_panel : nullptr, la ? aux->ev_next : nullptr, la ? aux->ev_rest : nullptr, la};
+    if (la) {
       cudaEventRecord(aux->ev_fork, s);
       cudaStreamWaitEvent(A.chain, aux->ev_fork, 0);
-      cudaStreamWaitEvent(B.chain, aux->ev_fork, 0);
-      cudaStreamWaitEvent(B.bulk, aux->ev_fork, 0);
     }
-    run_chain(S, n, ws, fail_flag, A, launches, pl, n_sm, 0, a, t0, T, nullptr, fused ? form : nullptr, &aux->ev_form);
-    // chain B: into S directly — or, while S is still being formed beside it, into its own side matrix like chain A
-    run_chain(S, n, ws, fail_flag, B, launches, pl, n_sm, a, t0, fused ? t0 : pl.panels, fused ? T_B : nullptr, nullptr, fused ? form : nullptr,
-              &aux->ev_form);
-    // join: s (= A.bulk) waits for A.chain, B.chain, B.bulk and the formation stream
-    cudaEventRecord(aux->ev_doneA, A.chain);
-    cudaStreamWaitEvent(s, aux->ev_doneA, 0);
-    cudaEventRecord(cb.ev_panel, B.chain);
-    cudaStreamWaitEvent(B.bulk, cb.ev_panel, 0);
-    cudaEventRecord(cb.ev_done, B.bulk);
-    cudaStreamWaitEvent(s, cb.ev_done, 0);
-    if (A.tail) {  // the side-matrix streams (they join only if they were forked into the work)
-      cudaEventRecord(aux->ev_trsmA, s);
-      cudaStreamWaitEvent(A.tail, aux->ev_trsmA, 0);
-      cudaEventRecord(aux->ev_tailA, A.tail);
-      cudaStreamWaitEvent(s, aux->ev_tailA, 0);
-      cudaEventRecord(aux->ev_trsmB, s);
-      cudaStreamWaitEvent(B.tail, aux->ev_trsmB, 0);
-      cudaEventRecord(aux->ev_tailB, B.tail);
-      cudaStreamWaitEvent(s, aux->ev_tailB, 0);
+    run_chain(S, n, ws, fail_flag, A, launches, pl, n_sm, 0, pl.panels, pl.panels, nullptr, 0, nullptr);
+    if (la) {
+      cudaEventRecord(aux->ev_join, A.chain);
+      cudaStreamWaitEvent(s, aux->ev_join, 0);
     }
-    if (fused && !form->chunk_tile0.empty()) cudaStreamWaitEvent(s, aux->ev_form[form->chunk_tile0.size() - 1], 0);
-    tail_add_kernel<<<n - t0 * NB, 256, 0, s>>>(S, n, t0, T, nt, fused ? T_B : nullptr);
-    ++*launches;
-    cudaEventRecord(aux->ev_fork, s);
-    run_chain(S, n, ws, fail_flag, A, launches, pl, n_sm, t0, pl.panels, pl.panels, nullptr, aux->ev_fork);
+    return;
   }
-  if (la) {
-    cudaEventRecord(aux->ev_join, A.chain);
-    cudaStreamWaitEvent(s, aux->ev_join, 0);
+  double* side0 = ws + cholesky_workspace_doubles(n);
+  const int n_sets = (int)aux->sets.size();
+  std::vector<char> forked((size_t)n_sets, 0);
+  cudaEventRecord(aux->ev_fork, s);
+  // the side matrices start at zero: cleared on the first set's tail stream while the leaf chains are already running
+  {
+    CholChainSet& z = aux->sets[0];
+    cudaStreamWaitEvent(z.tail, aux->ev_fork, 0);
+    cudaMemsetAsync(side0, 0, sizeof(double) * (size_t)pl.side_total, z.tail);
+    cudaEventRecord(aux->ev_zero, z.tail);
   }
+  for (size_t g = 0; g < pl.segs.size(); ++g) {
+    const CholPlan::Seg& sg = pl.segs[g];
+    CholChainSet& st = aux->sets[(size_t)(sg.slot % n_sets)];
+    if (!forked[(size_t)(sg.slot % n_sets)]) {
+      forked[(size_t)(sg.slot % n_sets)] = 1;
+      cudaStreamWaitEvent(st.chain, aux->ev_fork, 0);
+      cudaStreamWaitEvent(st.bulk, aux->ev_fork, 0);
+      cudaStreamWaitEvent(st.tail, aux->ev_zero, 0);
+    }
+    const int na = (int)sg.anc.size();
+    double* side = side0 + sg.side_off;
+    cudaEvent_t start_ev = nullptr;
+    if (!sg.children.empty()) {
+      cudaStreamWaitEvent(st.bulk, aux->ev_zero, 0);
+      for (int c : sg.children) cudaStreamWaitEvent(st.bulk, aux->ev_seg[(size_t)c], 0);
+      for (int c : sg.children) {
+        const CholPlan::Seg& ch = pl.segs[(size_t)c];
+        side_join_kernel<<<(int)ch.anc.size() * NB, 256, 0, st.bulk>>>(S, n, side0 + ch.side_off, (int)ch.anc.size(), pl.d_anc + ch.anc_off, sg.begin,
+                                                                       sg.end, side, na * NB, pl.d_map + g * (size_t)pl.panels);
+        ++*launches;
+      }
+      cudaEventRecord(st.ev_joined, st.bulk);
+      cudaStreamWaitEvent(st.tail, st.ev_joined, 0);  // the segment's own side-matrix updates come after the folded-in ones
+      start_ev = st.ev_joined;
+    }
+    ChainStreams cs{st.chain, st.bulk, st.ev_panel, st.ev_next, st.ev_rest, true};
+    cs.tail = st.tail; cs.ev_trsm = st.ev_trsm;
+    run_chain(S, n, ws, fail_flag, cs, launches, pl, n_sm, sg.begin, sg.end, sg.parent >= 0 ? sg.end : pl.panels, side, na * NB, start_ev);
+    // done = chain, bulk and tail streams of the segment
+    cudaEventRecord(st.ev_panel, st.chain);
+    cudaStreamWaitEvent(st.bulk, st.ev_panel, 0);
+    cudaEventRecord(st.ev_tail, st.tail);
+    cudaStreamWaitEvent(st.bulk, st.ev_tail, 0);
+    cudaEventRecord(aux->ev_seg[g], st.bulk);
+  }
+  // every segment is a descendant of a root, but every stream that was forked has to join the caller's stream (graph capture)
+  for (size_t g = 0; g < pl.segs.size(); ++g)
+    if (pl.segs[g].parent < 0) cudaStreamWaitEvent(s, aux->ev_seg[g], 0);
+  cudaStreamWaitEvent(s, aux->ev_zero, 0);
 }
 
-// Which chunks of tiles must be done before each panel step (see FormSchedule, ba_internal.h).
-void build_form_schedule(const CholPlan& pl, const Problem& P, int n_sm, FormSchedule& F) {
-  F.use = false;
-  F.chunk_tile0.clear(); F.chunk_count.clear(); F.need_chunk.clear();
-  // Measured at Venice shape (profiles/r02_fused_formation.md): the chunked formation does run beside the chains, but its
-  // FP64 atomics saturate the L2 slices the latency-bound chain kernels wait on — the chains slow down by what the overlap
-  // gains (3.57 ms against 1.41 + 2.27 = 3.68 ms in sequence).  Kept as an experiment knob, off by default.
-  static const bool off = getenv("HSFM_FUSED_FORM") == nullptr;
-  const int nT = P.n_tiles;
-  if (off || !pl.use || pl.split_a <= 0 || P.split_cams <= 0 || P.tail_cams <= P.split_cams || (int)P.h_tile_cmin.size() != nT || nT == 0) return;
-  const std::vector<int>& cm = P.h_tile_cmin;
-  // regions of the tile order: A = points whose smallest camera is in chain A, B = ... in chain B, tail.  The tile
-  // that straddles A | B goes to B (it may hold points of both; chain A's last columns then wait for B's first chunk).
-  const int tA = (int)(std::lower_bound(cm.begin(), cm.end(), P.split_cams) - cm.begin());
-  const int tB = (int)(std::lower_bound(cm.begin(), cm.end(), P.tail_cams) - cm.begin());
-  const int bA = std::max(tA - 1, 0);
-  static const int chunk_env = getenv("HSFM_FORM_CHUNK") ? atoi(getenv("HSFM_FORM_CHUNK")) : 0;
-  const int CH = chunk_env > 0 ? chunk_env : 8 * n_sm;  // a few waves of the SM-affine formation kernel per chunk
-  std::vector<int> order((size_t)nT, 0);
-  auto push = [&](int t0, int t1) {
-    F.chunk_tile0.push_back(t0); F.chunk_count.push_back(t1 - t0);
-    for (int t = t0; t < t1; ++t) order[(size_t)t] = (int)F.chunk_tile0.size() - 1;
-  };
-  int pa = 0, pb = bA;  // next tile of region A / B: interleave so that both regions finish together
-  while (pa < bA || pb < tB) {
-    const double fa = bA > 0 ? (double)pa / bA : 2.0, fb = tB > bA ? (double)(pb - bA) / (tB - bA) : 2.0;
-    if (pa < bA && (fa <= fb || pb >= tB)) { const int e = std::min(bA, pa + CH); push(pa, e); pa = e; }
-    else { const int e = std::min(tB, pb + CH); push(pb, e); pb = e; }
-  }
-  for (int t = tB; t < nT; t += CH) push(t, std::min(nT, t + CH));
-  const int last = (int)F.chunk_tile0.size() - 1;
-  // prefix maxima of the launch order: over [0, t) and over [bA, t)
-  std::vector<int> pm_all((size_t)nT + 1, -1), pm_b((size_t)nT + 1, -1);
-  for (int t = 0; t < nT; ++t) {
-    pm_all[(size_t)t + 1] = std::max(pm_all[(size_t)t], order[(size_t)t]);
-    pm_b[(size_t)t + 1] = t >= bA ? std::max(pm_b[(size_t)t], order[(size_t)t]) : -1;
-  }
-  F.need_chunk.assign((size_t)pl.panels, last);
-  for (int K = 0; K < pl.split_t0; ++K) {
-    int maxcol = K;
-    for (int q = 0; q < pl.cnt[(size_t)K]; ++q) {
-      const int I = pl.list[(size_t)pl.off[(size_t)K] + q];
-      if (I < pl.split_t0) maxcol = std::max(maxcol, I);
-    }
-    const int lastcam = std::min(P.n_cams - 1, (NB * maxcol + NB - 1) / 6);
-    const int ub = (int)(std::upper_bound(cm.begin(), cm.end(), lastcam) - cm.begin());  // tiles [0, ub) have cmin <= lastcam
-    if (lastcam >= P.tail_cams) F.need_chunk[(size_t)K] = last;
-    else if (K >= pl.split_a) F.need_chunk[(size_t)K] = pm_b[(size_t)ub];  // chain B: points of region A never touch its columns
-    else F.need_chunk[(size_t)K] = pm_all[(size_t)ub];
-  }
-  F.use = true;
-  if (getenv("HSFM_FORM_DEBUG")) {
-    std::fprintf(stderr, "[form] tiles %d (A [0,%d) B [%d,%d) tail [%d,%d)), %d chunks of <= %d; panels %d a %d t0 %d; split_cams %d tail_cams %d\n", nT, bA, bA, tB, tB,
-                 nT, (int)F.chunk_tile0.size(), CH, pl.panels, pl.split_a, pl.split_t0, P.split_cams, P.tail_cams);
-    for (int K = 0; K < pl.panels; ++K) std::fprintf(stderr, "%d:%d ", K, F.need_chunk[(size_t)K]);
-    std::fprintf(stderr, "\n");
-  }
-}
-
-// events and work counters of the fused formation: created outside any capture
-static void provision_form(CholAux* aux, const FormSchedule* form) {
-  if (!(form && form->use && aux && aux->form_stream)) return;
-  const int G = (int)form->chunk_tile0.size();
-  while ((int)aux->ev_form.size() < G) {
-    cudaEvent_t e;
-    if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) break;
-    aux->ev_form.push_back(e);
-  }
-  if (aux->form_counters_cap < G) {
-    if (aux->form_counters) cudaFree(aux->form_counters);
-    aux->form_counters = nullptr; aux->form_counters_cap = 0;
-    if (cudaMalloc(&aux->form_counters, sizeof(int) * (size_t)(G + 64)) == cudaSuccess) aux->form_counters_cap = G + 64;
-    else cudaGetLastError();
-  }
-}
-
-void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches, const CholPlan* plan,
-                     const FormSchedule* form) {
+void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches, const CholPlan* plan) {
   const int n_sm = (aux && aux->n_sm > 0) ? aux->n_sm : 148;
   static int bulk_ctas = 0;
   if (!bulk_ctas) {
@@ -2077,19 +2014,17 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
     // capture it once and replay it as a CUDA graph — no host launch cost, tighter kernel-to-kernel hand-over.
     static const bool no_graph = getenv("HSFM_NO_GRAPH") != nullptr;  // experiment knob
     if (aux && aux->stream && !no_graph) {
-      provision_form(aux, form);
-      const std::string fkey = (form && form->use) ? form->key : std::string();
       const bool valid = aux->graph && aux->g_S == S && aux->g_ws == ws && aux->g_fail == fail_flag && aux->g_stream == (const void*)s &&
-                         aux->g_n == n && aux->g_version == plan->version && aux->g_form_key == fkey;
+                         aux->g_n == n && aux->g_version == plan->version;
       if (!valid) {
         if (aux->graph) { cudaGraphExecDestroy(aux->graph); aux->graph = nullptr; }
         cudaGraph_t g = nullptr;
         int64_t counted = 0;
         if (cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
-          launch_cholesky_struct(S, n, ws, fail_flag, s, aux, &counted, *plan, n_sm, form);
+          launch_cholesky_struct(S, n, ws, fail_flag, s, aux, &counted, *plan, n_sm);
           if (cudaStreamEndCapture(s, &g) == cudaSuccess && g && cudaGraphInstantiate(&aux->graph, g, 0) == cudaSuccess) {
             aux->g_S = S; aux->g_ws = ws; aux->g_fail = fail_flag; aux->g_stream = (const void*)s; aux->g_n = n;
-            aux->g_version = plan->version; aux->g_launches = counted; aux->g_form_key = fkey;
+            aux->g_version = plan->version; aux->g_launches = counted;
           } else {
             aux->graph = nullptr;
           }
@@ -2103,8 +2038,7 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
       }
       cudaGetLastError();
     }
-    provision_form(aux, form);
-    launch_cholesky_struct(S, n, ws, fail_flag, s, aux, launches, *plan, n_sm, form);
+    launch_cholesky_struct(S, n, ws, fail_flag, s, aux, launches, *plan, n_sm);
     return;
   }
   const int panels = (n + NB - 1) / NB;
@@ -2132,16 +2066,16 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
       cudaEventRecord(aux->ev_panel, s2);
       if (panel > 0) cudaStreamWaitEvent(s2, aux->ev_rest, 0);  // "ahead k-1": cb 2,3 of the previous step = cb 0,1 of this one
     }
-    chol_syrk_kernel<<<min(2 * rb, 2 * n_sm), 128, kGemmSmem, s2>>>(S, n, k0, 0, 0, 2 * rb, 0, fail_flag, nullptr, 0, nullptr, 0, 0);
+    chol_syrk_kernel<<<min(2 * rb, 2 * n_sm), SY_THREADS, kGemmSmem, s2>>>(S, n, k0, 0, 0, 2 * rb, 0, fail_flag, nullptr, 0, nullptr, 0, nullptr);
     ++*launches;
     if (rb > 1) {
       if (la) cudaStreamWaitEvent(s, aux->ev_panel, 0);
-      chol_syrk_kernel<<<min(2 * (rb - 1), 2 * n_sm), 128, kGemmSmem, s>>>(S, n, k0, 1, 2, 2 * (rb - 1), 0, fail_flag, nullptr, 0, nullptr, 0, 0);
+      chol_syrk_kernel<<<min(2 * (rb - 1), 2 * n_sm), SY_THREADS, kGemmSmem, s>>>(S, n, k0, 1, 2, 2 * (rb - 1), 0, fail_flag, nullptr, 0, nullptr, 0, nullptr);
       ++*launches;
     }
     if (la) cudaEventRecord(aux->ev_rest, s);
     if (rb > 2) {
-      chol_syrk_kernel<<<min((rb - 2) * (rb - 1), bulk_ctas), 128, kGemmSmem, s>>>(S, n, k0, 0, -4, (rb - 2) * (rb - 1), 0, fail_flag, nullptr, 0, nullptr, 0, 0);
+      chol_syrk_kernel<<<min((rb - 2) * (rb - 1), bulk_ctas), SY_THREADS, kGemmSmem, s>>>(S, n, k0, 0, -4, (rb - 2) * (rb - 1), 0, fail_flag, nullptr, 0, nullptr, 0, nullptr);
       ++*launches;
     }
   }

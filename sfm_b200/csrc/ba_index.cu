@@ -572,11 +572,6 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
       HSFM_CUDA(cudaMemcpyAsync(&P.n_entries, ent_off + P.n_tiles, sizeof(int), cudaMemcpyDeviceToHost, s));
     }
     HSFM_CUDA(cudaMemcpyAsync(&P.max_tile_cams, d_max_ncam, sizeof(int), cudaMemcpyDeviceToHost, s));
-    P.h_tile_cmin.clear();
-    if (want_structure) {  // first entry of every tile's ascending camera list
-      P.h_tile_cmin.resize((size_t)P.n_tiles);
-      HSFM_CUDA(cudaMemcpy2DAsync(P.h_tile_cmin.data(), sizeof(int), tile_cams, sizeof(int) * TILE, sizeof(int), (size_t)P.n_tiles, cudaMemcpyDeviceToHost, s));
-    }
     HSFM_CUDA(cudaStreamSynchronize(s));  // hdr is a local vector; max_tile_cams is needed by the launches
     // every camera's (tile, slot) entries, in tile order: what the camera-keyed gathers walk (stable sort by camera)
     int *ek, *ev, *ek2;

@@ -4,7 +4,6 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-#include <functional>
 #include <string>
 #include <vector>
 
@@ -80,7 +79,6 @@ struct Problem {
   int* cam_old_of_new = nullptr;  // device [n_cams]
   int split_cams = -1;            // first internal camera of the second chain (two-ended order) or -1
   int tail_cams = -1;             // first internal camera of the tail (cameras coupled to both chains) or -1
-  std::vector<int> h_tile_cmin;   // [n_tiles] smallest internal camera of every tile (tiles are ordered by it): which columns of S a prefix of tiles completes
   double* cam_io = nullptr;       // [n_cams][9] staging in the caller's camera order (upload / download / taps)
   Dev d{};
   // Device arena: ONE grow-only allocation per context that every per-problem buffer is carved from, so the
@@ -195,7 +193,6 @@ struct CholPlan;
 void launch_dense_init(Problem& P, bool with_diag, cudaStream_t s, const CholPlan* plan = nullptr);  // S = 0 (+ blockdiag(Hcc + D^2)); plan: zero the envelope only
 void launch_dense_schur(Problem& P, cudaStream_t s, bool sorted_pairs = true);    // S -= sum_p W Hpp^-1 W^T (lower block triangle)
 bool dense_schur_prepare(Problem& P, cudaStream_t s);  // sorted pair lists ready?
-void launch_dense_schur_chunk(const Problem& P, int tile0, int count, int* counter, int reserve_mod, cudaStream_t s);  // tiles [tile0, tile0+count), sorted, SM-affine
 void launch_scatter_eval(Problem& P, double* r_out, double* jac_out, cudaStream_t s);  // back to input order, Ceres layout
 void launch_export_blocks(Problem& P, double* Hcc36, double* Hpp9, cudaStream_t s);  // parity tap (adds LM diagonal)
 void launch_mirror_lower(Problem& P, cudaStream_t s);   // S upper <- lower (parity tap)
@@ -204,37 +201,19 @@ void launch_mirror_lower(Problem& P, cudaStream_t s);   // S upper <- lower (par
 // In-place lower Cholesky of row-major n×n S (lower triangle read/written); *fail_flag set to
 // non-zero on a non-positive pivot.  Then solve S y = b in place in b.
 // auxiliary high-priority stream + events for the panel look-ahead of the factorisation
-// Formation of S fused into the factorisation (two-chain schedule, one GPU): S is formed in CHUNKS of point-major tiles on
-// its own stream while the panel chains already factor the columns that are complete.  Tiles are ordered by their
-// smallest internal camera and a block (ci, cj), cj <= ci, only receives contributions from points whose smallest
-// camera is <= cj: once every tile with smallest camera <= c is done, all columns of S up to camera c are final.
-// A panel step of a chain may run as soon as the columns it reads AND writes (its own columns; tail columns go to the
-// chains' side matrices) are final — need_chunk[K].  Built per problem by build_form_schedule (ba_chol.cu).
-struct FormSchedule {
-  bool use = false;
-  std::vector<int> chunk_tile0, chunk_count;  // in launch order
-  std::vector<int> need_chunk;                // [panels] index (launch order) of the last chunk panel K waits for; -1: none
-  std::function<void(int tile0, int count, int* counter, cudaStream_t s)> launch_chunk;  // counter: zeroed device int of the chunk
-  std::string key;                            // bytes of everything the chunk launches bake into a captured graph
-};
-
-struct CholChain {  // streams + events of one panel chain of the structured factorisation
+constexpr int MAX_CHOL_SEGMENTS = 32;  // more panel chains than this: the factorisation runs as ONE chain
+struct CholChainSet {  // streams + events one panel chain (segment) of the structured factorisation runs on
   cudaStream_t chain = nullptr;  // high priority: diagonal blocks and next-diagonal-tile kernels
   cudaStream_t bulk = nullptr;   // panel solves and trailing updates, one step behind
-  cudaEvent_t ev_panel = nullptr, ev_next = nullptr, ev_rest = nullptr, ev_done = nullptr;
+  cudaStream_t tail = nullptr;   // side-matrix updates: wanted only when the parent segment starts
+  cudaEvent_t ev_panel = nullptr, ev_next = nullptr, ev_rest = nullptr, ev_trsm = nullptr, ev_tail = nullptr, ev_joined = nullptr;
 };
+constexpr int CHOL_STREAM_SETS = 8;  // concurrent segments beyond this share a set (still correct: stream order)
 struct CholAux {
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_panel = nullptr, ev_rest = nullptr, ev_join = nullptr, ev_next = nullptr;
-  CholChain chainB;        // second chain of the two-ended schedule (the first one runs on `stream` + the caller's stream)
-  cudaEvent_t ev_doneA = nullptr;
-  cudaStream_t form_stream = nullptr;   // the experimental chunked formation of S beside the chains (FormSchedule)
-  cudaStream_t tailA = nullptr, tailB = nullptr;  // side-matrix (tail x tail) updates of the two chains
-  cudaEvent_t ev_trsmA = nullptr, ev_trsmB = nullptr, ev_tailA = nullptr, ev_tailB = nullptr;
-  std::vector<cudaEvent_t> ev_form;     // one per chunk, grown on demand (outside graph capture)
-  int* form_counters = nullptr;         // device: one work counter per chunk
-  int form_counters_cap = 0;
-  std::string g_form_key;
+  cudaEvent_t ev_fork = nullptr, ev_panel = nullptr, ev_rest = nullptr, ev_join = nullptr, ev_next = nullptr, ev_zero = nullptr;
+  std::vector<CholChainSet> sets;     // segment tree schedule (CholPlan::segs)
+  std::vector<cudaEvent_t> ev_seg;    // [MAX_CHOL_SEGMENTS] segment g complete (all its streams)
   // captured launch sequence of the envelope factorisation (static per problem: same S, workspace and plan)
   cudaGraphExec_t graph = nullptr;
   const void* g_S = nullptr; const void* g_ws = nullptr; const void* g_fail = nullptr; const void* g_stream = nullptr;
@@ -260,11 +239,28 @@ struct CholPlan {
   std::vector<int> off, cnt;   // per panel K: list[off[K] .. off[K]+cnt[K]) = R_K ascending  (column structure)
   std::vector<int> list;
   std::vector<int> row_off, row_list;  // per row block I: row_list[row_off[I] .. row_off[I+1]) = { J <= I : L(I,J) != 0 } ascending (ends with I)
-  // Two-chain schedule (two-ended camera order): panels [0, split_a) and [split_a, split_t0) are independent chains,
-  // factored concurrently; split_t0 is the first panel that receives updates from both.  -1: one chain.
-  int split_a = -1, split_t0 = -1;
-  int* d_ints = nullptr;       // device copy: list | row_off | row_list | col_off | col_cnt
+  // Panel chains (ba_order.cpp: panel_segments): the paths of the block elimination tree.  Segments that are not
+  // ancestor / descendant of each other are factored concurrently.  A segment with a parent must not write the blocks of
+  // its ancestors' columns in S (its siblings and cousins update the same blocks at the same time): those updates go to
+  // the segment's SIDE MATRIX, a dense square over its ancestors' panels anc(s) (ascending), which the parent folds into
+  // S (its own columns) and into its own side matrix (the columns of ITS ancestors) when it starts.  One segment: none.
+  struct Seg {
+    int begin = 0, end = 0, parent = -1;
+    int slot = 0;                // stream set the segment runs on (CholAux)
+    std::vector<int> children;   // ascending
+    std::vector<int> anc;        // panels of all ancestor segments, ascending
+    int anc_off = 0;             // position of anc in d_anc
+    long long side_off = 0;      // doubles from the start of the side-matrix area of the workspace
+  };
+  std::vector<Seg> segs;         // empty or one entry: a single chain over all panels
+  std::vector<int> side;         // parallel to list: position of list[q] in anc(segment of K), or -1 inside K's own segment
+  std::vector<int> anc_all, map_all;  // anc lists of all segments; per segment [panels]: panel -> position in its anc (or -1)
+  long long side_total = 0;      // doubles of all side matrices
+  int critical = 0;              // panels on the longest root-to-leaf path
+  int split_a = -1, split_t0 = -1;  // set when the schedule is the plain two-chain one (chains [0,a) and [a,t0), tail [t0,P)); reporting only
+  int* d_ints = nullptr;       // device copy: list | row_off | row_list | col_off | col_cnt | side | anc_all | map_all
   int* d_list = nullptr; int* d_row_off = nullptr; int* d_row_list = nullptr; int* d_col_off = nullptr; int* d_col_cnt = nullptr;
+  int* d_side = nullptr; int* d_anc = nullptr; int* d_map = nullptr;
   size_t d_cap = 0;
   // packed structure (multi-GPU: only these entries of S are summed across ranks): row r of block I occupies
   // packed[blk_off[I] + (r - 128 I) * width(I)) .. + width(I)), width(I) = 128 * (blocks in row I), blocks in row_list order
@@ -273,22 +269,26 @@ struct CholPlan {
   size_t d_blk_cap = 0;
   std::vector<uint8_t> key;    // the pattern the plan was built from: an unchanged structure keeps plan, version and graph
   long long packed_doubles() const { return blk_off.empty() ? 0 : blk_off.back(); }
-  // side matrix of the two-chain schedule: the tail blocks [split_t0, panels), square, after the L11^-1 blocks in the workspace
-  // (two of them: one per chain when the formation of S runs beside the chains)
-  long long tail_doubles() const { return (use && split_a > 0) ? 2ll * (panels - split_t0) * 128 * (panels - split_t0) * 128 : 0; }
-  // pattern: P x P bytes, lower triangle, NOT yet closed under elimination (nullptr = dense); split_hint: first panel of the second chain or -1
-  int build(int n_cams, const uint8_t* pattern, int P, int split_hint, cudaStream_t s);
-  bool compute(int n_cams, const uint8_t* pattern, int P, int split_hint);  // host part only (no device); false: unchanged
+  // side matrices of the segments, after the L11^-1 blocks in the workspace
+  long long tail_doubles() const { return use ? side_total : 0; }
+  // pattern: P x P bytes, lower triangle, NOT yet closed under elimination (nullptr = dense)
+  int build(int n_cams, const uint8_t* pattern, int P, cudaStream_t s);
+  bool compute(int n_cams, const uint8_t* pattern, int P);  // host part only (no device); false: unchanged
   void destroy();
 };
 // host-side structure code (ba_order.cpp)
-bool choose_camera_order(int n_cams, const int* first, std::vector<int>& new_of_old, int* split_cams, int* tail_cams = nullptr);
+struct PanelSeg { int begin, end, parent; };  // panels [begin, end) form one chain; parent: index of the segment that continues it, or -1
+void structure_lists(int P, const std::vector<uint8_t>& st, std::vector<int>& off, std::vector<int>& cnt, std::vector<int>& list);
+void panel_segments(int P, const std::vector<int>& off, const std::vector<int>& cnt, const std::vector<int>& list, std::vector<PanelSeg>& segs,
+                    std::vector<int>& seg_of);
+int critical_panels(const std::vector<PanelSeg>& segs);
+bool choose_camera_order(int n_cams, const int* first, std::vector<int>& new_of_old, int* split_cams, int* tail_cams = nullptr,
+                         int force_depth = -1);
 void block_pattern_from_envelope(int n_cams, const int* first, const int* new_of_old, std::vector<uint8_t>& pattern, int* panels);
 void symbolic_block_factor(int P, std::vector<uint8_t>& pattern);
 size_t cholesky_workspace_doubles(int n);  // L11^-1 blocks (one 128×128 per panel) + flags of the cooperative triangular solve
 void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t s, CholAux* aux, int64_t* launches,
-                     const CholPlan* plan = nullptr, const FormSchedule* form = nullptr);
-void build_form_schedule(const CholPlan& pl, const Problem& P, int n_sm, FormSchedule& F);  // F.launch_chunk / F.key are set by the caller
+                     const CholPlan* plan = nullptr);
 void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream_t s, int64_t* launches, const CholAux* aux,
                        const CholPlan* plan = nullptr);
 
@@ -343,8 +343,6 @@ struct Ctx {
   CholAux chol_aux;
   CholPlan chol_plan;     // envelope plan of the resident problem (built on first dense solve)
   bool chol_plan_valid = false;
-  FormSchedule form;      // fused formation of S (built on first dense solve of a two-chain problem)
-  bool form_valid = false;
   Problem prob;
   bool has_problem = false;
   int ordering = 0;         // 0 = automatic camera order, 1 = the caller's (hsfm_ba_set_ordering)

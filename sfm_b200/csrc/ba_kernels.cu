@@ -1031,7 +1031,7 @@ __global__ void dense_init_kernel(int n_cams, const double* __restrict__ Hcc, co
 constexpr int kDenseSchurSmem = TILE * 36 * (int)sizeof(double) + (3 * TILE + 8) * (int)sizeof(int) + 8 * 8 * 36 * (int)sizeof(double) + 8 * 8 * (int)sizeof(long long);
 // The sorted path runs 16 warps on a tile (512 threads; the first 256 stage the tile's observations), each with four
 // staging slots: twice the warps per SM at the same shared-memory footprint — the pair loop is latency-bound.
-// tile0: first tile of the launch (the fused formation + factorisation schedule forms S in chunks of tiles, ba_chol.cu).
+// tile0: first tile of the launch.
 template <bool SORTED>
 __device__ __forceinline__ void dense_schur_tile(const Dev& d, const double* __restrict__ Hpp_inv, double* __restrict__ S, const int tile) {
   extern __shared__ __align__(16) unsigned char ds_raw[];
@@ -1255,29 +1255,6 @@ __global__ void __launch_bounds__(SORTED ? 2 * TILE : TILE, 2) dense_schur_kerne
   dense_schur_tile<SORTED>(d, Hpp_inv, S, (int)blockIdx.x + tile0);
 }
 
-// The same formation for the schedule that forms S BESIDE the factorisation (FormSchedule, ba_chol.cu).  The panel chains
-// are latency chains: a diagonal-block kernel that shares its SM with sixteen formation warps runs ~1.6x slower, and the
-// chains then lose what the overlap gains.  So this variant keeps whole SMs free: CTAs that find themselves on a
-// reserved SM (%smid % reserve_mod == reserve_mod - 1) exit at once, the others take the tiles of the chunk from an
-// atomic counter.  The SMs they run on are full (2 x 96 KB of shared memory), so the chain / panel kernels can only be
-// placed on the reserved ones.
-__global__ void __launch_bounds__(2 * TILE, 2) dense_schur_affine_kernel(Dev d, const double* __restrict__ Hpp_inv, double* __restrict__ S, int tile0,
-                                                                         int count, int* __restrict__ counter, int reserve_mod) {
-  __shared__ int s_tile;
-  unsigned smid;
-  asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-  if (reserve_mod > 1 && (int)(smid % (unsigned)reserve_mod) == reserve_mod - 1) return;
-  for (;;) {
-    if (threadIdx.x == 0) s_tile = atomicAdd(counter, 1);
-    __syncthreads();
-    const int k = s_tile;
-    __syncthreads();
-    if (k >= count) return;
-    dense_schur_tile<true>(d, Hpp_inv, S, tile0 + k);
-    __syncthreads();
-  }
-}
-
 // Static pair lists of dense_schur (one CTA per tile, once per problem): every (i, j) pair of observations of one
 // point, j <= i, keyed by its destination block (slot of camera i, slot of camera j) and sorted by that key with
 // a bitonic network in shared memory.  Tiles with more pairs than the network holds keep generation order (the
@@ -1428,7 +1405,6 @@ int init_kernel_attributes() {
   allow_stage_smem(cost_kernel);
   cudaFuncSetAttribute(dense_schur_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDenseSchurSmem);
   cudaFuncSetAttribute(dense_schur_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDenseSchurSmem);
-  cudaFuncSetAttribute(dense_schur_affine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDenseSchurSmem);
   const cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : 1000 + (int)e;
 }
@@ -1641,7 +1617,7 @@ void launch_dense_schur(Problem& P, cudaStream_t s, bool sorted_pairs) {
   P.launches++;
 }
 
-// Builds the sorted pair lists if needed; true when the sorted kernel can run (what the chunked formation uses).
+// Builds the sorted pair lists if needed; true when the sorted kernel can run.
 bool dense_schur_prepare(Problem& P, cudaStream_t s) {
   if (P.n_tiles == 0 || !P.d.pair_off) return false;
   static const bool no_sort = getenv("HSFM_SCHUR_UNSORTED") != nullptr;
@@ -1662,15 +1638,6 @@ bool dense_schur_prepare(Problem& P, cudaStream_t s) {
   }
   return true;
 }
-// tiles [tile0, tile0 + count) of the sorted formation on the non-reserved SMs; counter: a zeroed device int of this chunk
-// (no launch accounting: the caller counts)
-void launch_dense_schur_chunk(const Problem& P, int tile0, int count, int* counter, int reserve_mod, cudaStream_t s) {
-  static const bool noop = getenv("HSFM_FORM_NOOP") != nullptr;  // timing experiment only (wrong results): the chunk kernels start and exit
-  if (noop) count = 1;
-  if (count > 0)
-    dense_schur_affine_kernel<<<std::min(count, 2 * P.n_sm), 2 * TILE, kDenseSchurSmem, s>>>(P.d, P.Hpp_inv, P.S, tile0, count, counter, reserve_mod);
-}
-
 void launch_mirror_lower(Problem& P, cudaStream_t s) {
   const int n = 6 * P.n_cams;
   if (n == 0) return;

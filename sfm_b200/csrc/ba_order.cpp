@@ -33,47 +33,190 @@ constexpr int NB = 128;
 constexpr int CAM_ALIGN = 64;  // 64 cameras = 384 rows = 3 panels: chain boundaries must be panel boundaries
 }  // namespace
 
+// ---- recursive two-ended dissection of a band ----
+// A set of cameras (ascending caller ids) that form a band among themselves is eliminated as
+//   depth 0:  [ first part ascending | second part descending | T = cameras of the second part coupled to the first ]
+//   depth d:  [ order(lower half, d-1) | order(upper half minus M, d-1) | M = cameras of the upper half coupled to the lower ]
+// Every piece but the very last one of the whole order holds a multiple of CAM_ALIGN cameras (chain boundaries are
+// panel boundaries): a separator's surplus cameras move UP into the separator of the enclosing level (always valid:
+// that one is eliminated later still), returned in `up`.
+namespace {
+bool order_band(const std::vector<int>& cams, const int* first, int depth, bool is_root, std::vector<int>& out, std::vector<int>& up,
+                int* two_ended_sizes = nullptr /*[2]: cameras of the first and of the second chain (root, depth 0)*/) {
+  const int k = (int)cams.size();
+  if (k < 4 * CAM_ALIGN) return false;
+  std::vector<int> sep;
+  if (depth == 0) {
+    std::vector<int> w((size_t)k);
+    for (int q = 0; q < k; ++q) w[q] = cams[q] - std::min(first[cams[q]], cams[q]);
+    std::nth_element(w.begin(), w.begin() + (size_t)(0.9 * (k - 1)), w.end());
+    const int bw = std::min(w[(size_t)(0.9 * (k - 1))], k / 2);  // typical half-bandwidth in cameras (closure rows are outliers)
+    const int mpos = ((k - bw) / 2) / CAM_ALIGN * CAM_ALIGN;
+    if (mpos < CAM_ALIGN) return false;
+    const int m = cams[(size_t)mpos];
+    std::vector<int> second;
+    for (int q = mpos; q < k; ++q) (first[cams[q]] < m ? sep : second).push_back(cams[q]);
+    // the second chain must hold whole panels as well: its cameras nearest to the split join the separator
+    const size_t ex = second.size() % CAM_ALIGN;
+    sep.insert(sep.end(), second.begin(), second.begin() + ex);
+    second.erase(second.begin(), second.begin() + ex);
+    if ((int)second.size() < CAM_ALIGN) return false;
+    out.insert(out.end(), cams.begin(), cams.begin() + mpos);
+    out.insert(out.end(), second.rbegin(), second.rend());
+    if (two_ended_sizes) { two_ended_sizes[0] = mpos; two_ended_sizes[1] = (int)second.size(); }
+  } else {
+    const int hpos = (k / 2) / CAM_ALIGN * CAM_ALIGN;
+    const int h = cams[(size_t)hpos];
+    std::vector<int> lower(cams.begin(), cams.begin() + hpos), upper, moved;
+    for (int q = hpos; q < k; ++q) (first[cams[q]] < h ? sep : upper).push_back(cams[q]);
+    if (!order_band(lower, first, depth - 1, false, out, moved)) return false;
+    if (!order_band(upper, first, depth - 1, false, out, moved)) return false;
+    sep.insert(sep.end(), moved.begin(), moved.end());
+  }
+  std::sort(sep.begin(), sep.end());
+  if (!is_root) {
+    const size_t ex = sep.size() % CAM_ALIGN;
+    up.insert(up.end(), sep.end() - ex, sep.end());
+    sep.resize(sep.size() - ex);
+  }
+  out.insert(out.end(), sep.begin(), sep.end());
+  return true;
+}
+}  // namespace
+
+// Column structure of L from a pattern closed under elimination: R_K ascending per panel.
+void structure_lists(int P, const std::vector<uint8_t>& st, std::vector<int>& off, std::vector<int>& cnt, std::vector<int>& list) {
+  off.assign((size_t)P, 0); cnt.assign((size_t)P, 0); list.clear();
+  for (int K = 0; K < P; ++K) {
+    off[K] = (int)list.size();
+    for (int I = K + 1; I < P; ++I)
+      if (st[(size_t)I * P + K]) list.push_back(I);
+    cnt[K] = (int)list.size() - off[K];
+  }
+}
+
+// Panel chains of the factorisation = paths of the block elimination tree (parent(K) = min R_K): a new segment starts
+// at every panel that is not the only child of its predecessor.  Segments are numbered in panel order, so children
+// precede parents.
+void panel_segments(int P, const std::vector<int>& off, const std::vector<int>& cnt, const std::vector<int>& list, std::vector<PanelSeg>& segs,
+                    std::vector<int>& seg_of) {
+  segs.clear();
+  seg_of.assign((size_t)P, 0);
+  std::vector<int> parent((size_t)P, -1), nchild((size_t)P, 0);
+  for (int K = 0; K < P; ++K)
+    if (cnt[K] > 0) { parent[K] = list[(size_t)off[K]]; ++nchild[(size_t)parent[K]]; }
+  for (int K = 0; K < P; ++K) {
+    if (K == 0 || parent[K - 1] != K || nchild[K] != 1) segs.push_back(PanelSeg{K, K, -1});
+    seg_of[K] = (int)segs.size() - 1;
+    segs.back().end = K + 1;
+  }
+  for (auto& g : segs) g.parent = parent[g.end - 1] >= 0 ? seg_of[(size_t)parent[g.end - 1]] : -1;
+  // A chain of one or two panels that its parent continues directly is not worth a start of its own (a join and a
+  // stream hand-over): it becomes the head of the parent, which then waits for the children of both.
+  for (bool merged = true; merged;) {
+    merged = false;
+    for (size_t g = 0; g + 1 < segs.size(); ++g) {
+      if (segs[g].parent != (int)g + 1 || segs[g].end - segs[g].begin > 2) continue;
+      segs[g + 1].begin = segs[g].begin;
+      segs.erase(segs.begin() + (long)g);
+      for (auto& t : segs) {
+        if (t.parent == (int)g) t.parent = (int)g;            // its children now hang off the merged segment (which took index g)
+        else if (t.parent > (int)g) --t.parent;
+      }
+      merged = true;
+      break;
+    }
+  }
+  for (size_t g = 0; g < segs.size(); ++g)
+    for (int K = segs[g].begin; K < segs[g].end; ++K) seg_of[(size_t)K] = (int)g;
+}
+
+// Longest root-to-leaf path of the segment tree, in panels.
+int critical_panels(const std::vector<PanelSeg>& segs) {
+  std::vector<int> depth(segs.size(), 0);
+  int best = 0;
+  for (int g = (int)segs.size() - 1; g >= 0; --g) {  // parents have larger indices: their depth is final first
+    depth[g] = (segs[g].end - segs[g].begin) + (segs[g].parent >= 0 ? depth[(size_t)segs[g].parent] : 0);
+    best = std::max(best, depth[g]);
+  }
+  return best;
+}
+
+namespace {
+// Estimated time of the structured factorisation in a given camera order.  Segments at the same depth below the root run
+// concurrently; a level costs the larger of its longest chain (38 us per panel step, 20 % more per concurrent chain
+// beyond two: the chains' kernels share SMs and L2 with each other's bulk updates) and the tensor-pipe time of its
+// structural flops (18 TFLOP/s: what the 128-deep trailing updates sustain with several chains in flight).  Constants
+// fitted to c3 / c4 at order depths 0-2 on a B200; deep trees are over-estimated (levels overlap).
+double order_cost(int n_cams, const int* first, const int* new_of_old, int* crit_out) {
+  std::vector<uint8_t> pat;
+  int P = 0;
+  block_pattern_from_envelope(n_cams, first, new_of_old, pat, &P);
+  symbolic_block_factor(P, pat);
+  std::vector<int> off, cnt, list, seg_of;
+  structure_lists(P, pat, off, cnt, list);
+  std::vector<PanelSeg> segs;
+  panel_segments(P, off, cnt, list, segs, seg_of);
+  if (segs.size() > (size_t)MAX_CHOL_SEGMENTS) { segs.assign(1, PanelSeg{0, P, -1}); }
+  if (crit_out) *crit_out = critical_panels(segs);
+  int levels = 0;
+  std::vector<int> lev(segs.size(), 0);
+  for (int g = (int)segs.size() - 1; g >= 0; --g) {
+    lev[(size_t)g] = segs[(size_t)g].parent >= 0 ? lev[(size_t)segs[(size_t)g].parent] + 1 : 0;
+    levels = std::max(levels, lev[(size_t)g] + 1);
+  }
+  double total = 0.0;
+  for (int l = 0; l < levels; ++l) {
+    int chains = 0, longest = 0;
+    double tiles = 0.0;  // 128^3 products: diagonal block, panel solve, pairs
+    for (size_t g = 0; g < segs.size(); ++g) {
+      if (lev[g] != l) continue;
+      ++chains;
+      longest = std::max(longest, segs[g].end - segs[g].begin);
+      for (int K = segs[g].begin; K < segs[g].end; ++K) tiles += 0.5 * cnt[K] * (cnt[K] + 1.0) + 0.5 * cnt[K] + 1.0 / 6;
+    }
+    const double t_chain = longest * 38e-6 * (1.0 + 0.2 * std::max(0, chains - 2)), t_flops = tiles * 2.0 * NB * NB * NB / 18e12;
+    total += std::max(t_chain, t_flops);
+  }
+  return total;
+}
+}  // namespace
+
 // Decide the internal camera order from the caller-order envelope first[c] (smallest camera sharing a point with c).
-// Returns true and fills new_of_old when a reordering pays; *split_cams receives m (the first camera position of the
-// second chain) or -1, *tail_cams (optional) the first camera position of the tail.
-bool choose_camera_order(int n_cams, const int* first, std::vector<int>& new_of_old, int* split_cams, int* tail_cams) {
+// Returns true and fills new_of_old when a reordering pays; *split_cams / *tail_cams: first camera position of the second
+// chain / of the tail when the order is the plain two-ended one (depth 0), else -1.  force_depth >= 0 (tests): that
+// dissection depth, whatever the cost model says.
+bool choose_camera_order(int n_cams, const int* first, std::vector<int>& new_of_old, int* split_cams, int* tail_cams, int force_depth) {
   *split_cams = -1;
   if (tail_cams) *tail_cams = -1;
   new_of_old.clear();
   static const bool off = getenv("HSFM_NO_TWIST") != nullptr;  // experiment knob
+  static const int max_depth = getenv("HSFM_ORDER_DEPTH") ? atoi(getenv("HSFM_ORDER_DEPTH")) : 2;
   if (off || n_cams < 4 * CAM_ALIGN) return false;
   // how banded is the natural order?
   double env = 0.0;
-  std::vector<int> w((size_t)n_cams);
-  for (int c = 0; c < n_cams; ++c) { w[c] = c - std::min(first[c], c); env += w[c] + 1; }
+  for (int c = 0; c < n_cams; ++c) env += c - std::min(first[c], c) + 1;
   const double fill = env / (0.5 * (double)n_cams * (n_cams + 1));
   if (fill > 0.35) return false;
-  std::vector<int> ws(w);
-  std::nth_element(ws.begin(), ws.begin() + (size_t)(0.9 * (n_cams - 1)), ws.end());
-  const int bw = ws[(size_t)(0.9 * (n_cams - 1))];  // typical half-bandwidth in cameras (closure rows are outliers)
-  int m = ((n_cams - bw) / 2) / CAM_ALIGN * CAM_ALIGN;
-  if (m < CAM_ALIGN) return false;
-  // cameras of the second part coupled to the first part: ordered last
-  std::vector<char> in_tail((size_t)n_cams, 0);
-  int n_tail = 0;
-  for (int c = m; c < n_cams; ++c)
-    if (first[c] < m) { in_tail[c] = 1; ++n_tail; }
-  // the tail must start on a panel boundary as well: move the nearest cameras of the second chain into it
-  int rest = n_cams - m - n_tail;
-  for (int c = m; c < n_cams && rest % CAM_ALIGN != 0; ++c)
-    if (!in_tail[c]) { in_tail[c] = 1; ++n_tail; --rest; }
-  if (rest < CAM_ALIGN) return false;
-  // critical path (in cameras) of the two-chain schedule against the single chain
-  if ((double)(std::max(m, rest) + n_tail) > 0.8 * n_cams) return false;
-  new_of_old.resize((size_t)n_cams);
-  int pos = 0;
-  for (int c = 0; c < m; ++c) new_of_old[c] = pos++;
-  for (int c = n_cams - 1; c >= m; --c)
-    if (!in_tail[c]) new_of_old[c] = pos++;
-  for (int c = n_cams - 1; c >= m; --c)
-    if (in_tail[c]) new_of_old[c] = pos++;
-  *split_cams = m;
-  if (tail_cams) *tail_cams = n_cams - n_tail;
+  std::vector<int> cams((size_t)n_cams), best;
+  std::iota(cams.begin(), cams.end(), 0);
+  int crit = 0;
+  double best_cost = order_cost(n_cams, first, nullptr, &crit);
+  int best_depth = -1, best_sizes[2] = {-1, -1};
+  for (int depth = force_depth >= 0 ? force_depth : 0; depth <= (force_depth >= 0 ? force_depth : max_depth); ++depth) {
+    std::vector<int> order, up, cand((size_t)n_cams);
+    order.reserve((size_t)n_cams);
+    int sizes[2] = {-1, -1};
+    if (!order_band(cams, first, depth, true, order, up, sizes) || (int)order.size() != n_cams) break;
+    for (int pos = 0; pos < n_cams; ++pos) cand[(size_t)order[(size_t)pos]] = pos;
+    const double cost = order_cost(n_cams, first, cand.data(), &crit);
+    static const bool verbose = getenv("HSFM_ORDER_VERBOSE") != nullptr;
+    if (verbose) std::fprintf(stderr, "[order] depth %d: critical panels %d, estimated %.3f ms (best so far %.3f)\n", depth, crit, 1e3 * cost, 1e3 * best_cost);
+    if (cost < 0.9 * best_cost || force_depth >= 0) { best_cost = cost; best.swap(cand); best_depth = depth; best_sizes[0] = sizes[0]; best_sizes[1] = sizes[1]; }
+  }
+  if (best_depth < 0) return false;
+  new_of_old.swap(best);
+  if (best_depth == 0) { *split_cams = best_sizes[0]; if (tail_cams) *tail_cams = best_sizes[0] + best_sizes[1]; }
   return true;
 }
 

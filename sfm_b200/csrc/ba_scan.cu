@@ -96,7 +96,6 @@ int reindex(Ctx& c, double* setup_ms, double* h2d_ms) {
   ScanStore& S = c.scan;
   c.has_problem = false;
   c.chol_plan_valid = false;
-  c.form_valid = false;
   double setup = 0, h2d = 0;
   int rc = build_problem(c.prob, S.mode, S.n_obs, S.obs, S.cam_idx, S.pt_idx, S.n_cams, S.K9, S.has_dist ? S.dist : nullptr, S.cam, S.n_pts, S.pts,
                          c.comm, c.stream, &setup, &h2d, c.ordering == 1);

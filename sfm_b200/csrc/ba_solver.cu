@@ -46,24 +46,6 @@ struct Driver {
 
   bool multi() const { return ctx.comm.n_ranks > 1; }
 
-  // The fused formation schedule of the resident problem, built on first use (needs the sorted pair lists).
-  bool form_ready() {
-    FormSchedule& F = ctx.form;
-    if (ctx.form_valid) return F.use;
-    ctx.form_valid = true;
-    F.use = false;
-    if (!dense_schur_prepare(P, s)) return false;
-    build_form_schedule(ctx.chol_plan, P, ctx.chol_aux.n_sm, F);
-    if (!F.use) return false;
-    Problem* pp = &P;
-    static const int reserve_mod = getenv("HSFM_FORM_RESERVE") ? atoi(getenv("HSFM_FORM_RESERVE")) : 5;  // every 5th SM stays free for the chains
-    F.launch_chunk = [pp](int tile0, int count, int* counter, cudaStream_t st) { launch_dense_schur_chunk(*pp, tile0, count, counter, reserve_mod, st); };
-    // what a captured chunk launch bakes in: the Dev block (pointers and sizes), Hpp_inv and S
-    F.key.assign(reinterpret_cast<const char*>(&P.d), sizeof(P.d));
-    const void* extra[2] = {P.Hpp_inv, P.S};
-    F.key.append(reinterpret_cast<const char*>(extra), sizeof(extra));
-    return true;
-  }
   void chk(int r) { if (r && !rc) rc = r; }
 
   int read_back() {
@@ -114,11 +96,8 @@ struct Driver {
     if (P.mode == 2) {
       const bool lead = ctx.comm.rank == 0;
       if (dense) {
-        // One GPU, two-chain plan: S is formed in chunks INSIDE the factorisation's launch graph, beside the panel chains
-        // (FormSchedule); otherwise formed here, before the factorisation.
-        const bool fused = !multi() && !(o.dense_flags & 3) && ctx.chol_plan.use && ctx.chol_plan.n == n6 && form_ready();
         launch_dense_init(P, lead, s, (o.dense_flags & 1) ? nullptr : &ctx.chol_plan);
-        if (!fused) launch_dense_schur(P, s, !(o.dense_flags & 2));
+        launch_dense_schur(P, s, !(o.dense_flags & 2));
         launch_schur_rhs(P, lead, s);
         if (multi()) {
           const CholPlan& pl = ctx.chol_plan;
@@ -136,8 +115,7 @@ struct Driver {
           chk(ctx.comm.allreduce_sum(P.rhs, n6, s));
         }
         mark(2);
-        launch_cholesky(P.S, n6, P.S + (size_t)n6 * n6, P.flags + F_CHOL_FAIL, s, &ctx.chol_aux, &P.launches, (o.dense_flags & 1) ? nullptr : &ctx.chol_plan,
-                        fused ? &ctx.form : nullptr);
+        launch_cholesky(P.S, n6, P.S + (size_t)n6 * n6, P.flags + F_CHOL_FAIL, s, &ctx.chol_aux, &P.launches, (o.dense_flags & 1) ? nullptr : &ctx.chol_plan);
         mark(3);
         HSFM_CUDA(cudaMemcpyAsync(P.yc, P.rhs, sizeof(double) * n6, cudaMemcpyDeviceToDevice, s));
         launch_chol_solve(P.S, n6, P.S + (size_t)n6 * n6, P.yc, s, &P.launches, &ctx.chol_aux, (o.dense_flags & 1) ? nullptr : &ctx.chol_plan);
@@ -208,9 +186,9 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
         std::vector<uint8_t> pattern;
         int panels = 0;
         block_pattern_from_envelope(P.n_cams, P.cam_first.data(), P.h_cam_new_of_old.empty() ? nullptr : P.h_cam_new_of_old.data(), pattern, &panels);
-        rc = ctx.chol_plan.build(P.n_cams, pattern.data(), panels, P.split_cams > 0 ? (6 * P.split_cams) / 128 : -1, s);
+        rc = ctx.chol_plan.build(P.n_cams, pattern.data(), panels, s);
       } else {
-        rc = ctx.chol_plan.build(P.n_cams, nullptr, 0, -1, s);
+        rc = ctx.chol_plan.build(P.n_cams, nullptr, 0, s);
       }
       if (rc) return rc;
       ctx.chol_plan_valid = true;
@@ -266,7 +244,7 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
       S.chol_flops = 0.0;
       for (int K = 0; K < pl.panels; ++K) S.chol_flops += b3 / 3.0 + pl.cnt[K] * b3 + (double)pl.cnt[K] * (pl.cnt[K] + 1) * b3;
     }
-    if (!(o.dense_flags & 1) && pl.use && pl.split_a > 0) S.chol_critical_panels = std::max(pl.split_a, pl.split_t0 - pl.split_a) + (pl.panels - pl.split_t0);
+    if (!(o.dense_flags & 1) && pl.use) S.chol_critical_panels = pl.critical;
   }
 
   cudaEvent_t ev0, ev1;

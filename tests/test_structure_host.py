@@ -1,5 +1,5 @@
 """Host side of the structured Cholesky (sfm_b200/csrc/ba_order.cpp + CholPlan::compute), no GPU needed: the camera
-order chosen for a banded camera graph, the closed block structure, and the two-chain schedule — checked against a
+order chosen for a banded camera graph, the closed block structure, and the segment-tree schedule — checked against a
 dense numpy factorisation and against a block-level emulation of the schedule the CUDA launcher follows."""
 import numpy as np
 import pytest
@@ -39,41 +39,84 @@ def permuted(A, new_of_old):
     return A[np.ix_(idx, idx)]
 
 
-def emulate(A, st, split_a, split_t0):
-    """Right-looking block factorisation over the structure, as launch_cholesky_struct schedules it: chain A = panels
-    [0, a) whose updates into block columns >= t0 go to a side matrix T, chain B = [a, t0) updating S directly, then
-    S_tail += T and the tail [t0, P).  Only structural blocks are ever touched."""
+def emulate(A, st, segments):
+    """Right-looking block factorisation over the structure, as launch_cholesky_struct schedules it: every segment
+    (panel chain) factors its panels; updates to blocks of its ancestors' columns go to the segment's own side matrix
+    (indexed by its ancestors' panels only), which the parent folds into S (its own columns) and into its own side
+    matrix (the rest) before it starts.  Concurrent segments are run here in an order that would expose a missing
+    dependency: all leaves first, interleaved panel by panel.  Only structural blocks are ever touched."""
     n = A.shape[0]
     P = st.shape[0]
     S = np.tril(A).copy()
-    T = np.zeros_like(S)
     blk = lambda I: slice(I * NB, min(n, (I + 1) * NB))  # noqa: E731
     col = [[I for I in range(K + 1, P) if st[I, K]] for K in range(P)]
+    if not segments:
+        segments = [(0, P, -1)]
+    G = len(segments)
+    anc = []
+    for g, (b, e, par) in enumerate(segments):
+        a = []
+        while par >= 0:
+            assert par > g, "parents are numbered after their children"
+            a += list(range(segments[par][0], segments[par][1]))
+            par = segments[par][2]
+        anc.append(sorted(a))
+    side = [dict() for _ in range(G)]  # (I, J) -> block, only ancestors' panels are legal keys
 
-    def panel(K, own_end, side):
+    def side_blk(g, I, J):
+        assert I in anc[g] and J in anc[g], "side-matrix update outside the segment's ancestors"
+        return side[g].setdefault((I, J), np.zeros((NB, NB)))
+
+    def panel(g, K):
+        b, e, par = segments[g]
+        own_end = e if par >= 0 else P
         S[blk(K), blk(K)] = np.linalg.cholesky(S[blk(K), blk(K)] + np.tril(S[blk(K), blk(K)], -1).T)
         Linv = np.linalg.inv(S[blk(K), blk(K)])
         for I in col[K]:
+            assert I < e or I in anc[g], "a panel couples to a panel that is neither its own segment's nor an ancestor's"
             S[blk(I), blk(K)] = S[blk(I), blk(K)] @ Linv.T
         for bi, J in enumerate(col[K]):
-            C = side if J >= own_end else S
             for I in col[K][bi:]:
                 assert st[I, J], "update outside the structure"
-                C[blk(I), blk(J)] -= S[blk(I), blk(K)] @ S[blk(J), blk(K)].T
+                upd = S[blk(I), blk(K)] @ S[blk(J), blk(K)].T
+                if J >= own_end:
+                    t = side_blk(g, I, J)
+                    t[: upd.shape[0], : upd.shape[1]] -= upd
+                else:
+                    S[blk(I), blk(J)] -= upd
 
-    if split_a > 0:
-        for K in range(split_a):
-            assert not [I for I in col[K] if split_a <= I < split_t0], "chain A touches chain B's private panels"
-            panel(K, split_t0, T)
-        for K in range(split_a, split_t0):
-            panel(K, P, None)
-        S += T
-        rest = range(split_t0, P)
-    else:
-        rest = range(P)
-    for K in rest:
-        panel(K, P, None)
+    def join(g):
+        b, e, par = segments[g]
+        for c in [c for c in range(G) if segments[c][2] == g]:
+            for (I, J), t in side[c].items():
+                if b <= J < e:
+                    r, cc = S[blk(I), blk(J)].shape
+                    S[blk(I), blk(J)] += t[:r, :cc]
+                else:
+                    side_blk(g, I, J)[...] += t
+
+    children = [[c for c in range(G) if segments[c][2] == g] for g in range(G)]
+    done = [False] * G
+    while not all(done):
+        ready = [g for g in range(G) if not done[g] and all(done[c] for c in children[g])]
+        for g in ready:
+            join(g)
+        cursors = {g: segments[g][0] for g in ready}
+        while cursors:  # interleave the concurrent segments panel by panel
+            for g in list(cursors):
+                panel(g, cursors[g])
+                cursors[g] += 1
+                if cursors[g] == segments[g][1]:
+                    del cursors[g]
+                    done[g] = True
     return np.tril(S)
+
+
+def check_segments(segments, P):
+    assert segments[0][0] == 0 and segments[-1][1] == P
+    for (b0, e0, _), (b1, _, _) in zip(segments, segments[1:]):
+        assert b0 < e0 == b1
+    assert sum(1 for _, _, par in segments if par < 0) == 1  # one root: the last separator
 
 
 @pytest.mark.parametrize("case", ["band", "closure", "ring"])
@@ -84,13 +127,14 @@ def test_two_ended_order_structure_and_schedule(case):
     d = api.debug_structure(first)
     nat = api.debug_structure(first, natural=True)
     assert sorted(d["new_of_old"]) == list(range(n))
-    assert nat["structured"] and not nat["reordered"] and nat["split_a"] == -1
+    assert nat["structured"] and not nat["reordered"] and nat["split_a"] == -1 and not nat["segments"]
     assert d["reordered"] and d["structured"]
     a, t0, P = d["split_a"], d["split_t0"], d["panels"]
     assert 0 < a < t0 < P
+    assert d["segments"] == [(0, a, 2), (a, t0, 2), (t0, P, -1)]
     # the point of the exercise: the serial chain (in panels) is much shorter than one chain over all panels ...
     crit = max(a, t0 - a) + (P - t0)
-    assert crit <= 0.75 * P, (a, t0, P)
+    assert crit == d["critical_panels"] and crit <= 0.75 * P, (a, t0, P)
     # ... at (nearly) no extra arithmetic: the structure holds about as many blocks as the envelope of the natural order
     assert d["structure"].sum() <= 1.2 * nat["structure"].sum()
     A = random_spd(first, seed=9)
@@ -99,12 +143,37 @@ def test_two_ended_order_structure_and_schedule(case):
     # nothing of L lies outside the structure (exact zeros: no fill is ever computed there)
     mask = np.kron(d["structure"], np.ones((NB, NB)))[: 6 * n, : 6 * n].astype(bool)
     assert np.abs(L[~mask]).max() == 0.0
-    # the schedule (side-matrix tail updates included) reproduces the factor
-    Le = emulate(Ap, d["structure"], a, t0)
+    # the schedule (side-matrix updates included) reproduces the factor
+    Le = emulate(Ap, d["structure"], d["segments"])
     assert np.abs(Le - L).max() <= 1e-10 * np.abs(L).max()
     # and so does the single chain in the natural order
-    Ln = emulate(A, nat["structure"], -1, -1)
+    Ln = emulate(A, nat["structure"], [])
     assert np.abs(Ln - np.linalg.cholesky(A)).max() <= 1e-10 * np.abs(L).max()
+
+
+@pytest.mark.parametrize("case", ["band", "closures"])
+def test_nested_order_runs_four_or_more_chains(case):
+    """The band is cut in halves around a separator and each half eliminated from both ends — four concurrent chains,
+    inner separators, one root separator (ba_order.cpp: order_band).  The depth is forced: at this size the cost model
+    prefers two chains."""
+    n = 840
+    closures = {"band": (), "closures": ((800, 3), (801, 3), (500, 100))}[case]
+    first = band_first(n, 20, 45, seed=11, closures=closures)
+    d = api.debug_structure(first, depth=1)
+    P, segs = d["panels"], d["segments"]
+    assert d["reordered"] and d["structured"] and sorted(d["new_of_old"]) == list(range(n))
+    check_segments(segs, P)
+    leaves = [g for g in range(len(segs)) if all(par != g for _, _, par in segs)]
+    assert len(leaves) >= 4 and len(segs) >= 6, segs
+    assert all(par > g or par == -1 for g, (_, _, par) in enumerate(segs))
+    assert d["critical_panels"] <= 0.55 * P, (d["critical_panels"], P)
+    A = random_spd(first, seed=3)
+    Ap = permuted(A, d["new_of_old"])
+    L = np.linalg.cholesky(Ap)
+    mask = np.kron(d["structure"], np.ones((NB, NB)))[: 6 * n, : 6 * n].astype(bool)
+    assert np.abs(L[~mask]).max() == 0.0
+    Le = emulate(Ap, d["structure"], segs)
+    assert np.abs(Le - L).max() <= 1e-10 * np.abs(L).max()
 
 
 def test_small_or_dense_graphs_keep_the_callers_order():
