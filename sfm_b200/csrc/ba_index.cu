@@ -21,7 +21,10 @@ void Problem::release() {
   double* sh = scal_host; int* fh = flags_host;
   int* ih = idx_host; const size_t ih_cap = idx_host_cap;
   const int sm = n_sm;
+  OrderCache oc;
+  std::swap(oc, order_cache);
   *this = Problem();
+  std::swap(oc, order_cache);
   n_sm = sm;
   arena = a; arena_cap = cap; arena_off = 0;
   S = s_keep; S_capacity = s_cap;
@@ -112,6 +115,22 @@ __global__ void lower_bound_kernel(int n, const int* __restrict__ keys, int n_ke
     if (keys[mid] < k) lo = mid + 1; else hi = mid;
   }
   start[k] = lo;
+}
+// pairs[p] = L (L + 1) / 2 observation pairs of point p (L = its track length), pairs[n_pts] = 0; *max_track = longest track
+__global__ void point_pairs_kernel(int n_pts, const int* __restrict__ pt_start, long long* __restrict__ pairs, int* __restrict__ max_track) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  int L = 0;
+  if (p < n_pts) L = pt_start[p + 1] - pt_start[p];
+  if (p <= n_pts) pairs[p] = (long long)L * (L + 1) / 2;
+  const int m = __reduce_max_sync(0xffffffffu, L);
+  if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(max_track, m);
+}
+// pair_off[k] = pairs before the first point of tile k (k = n_tiles: before the end point of the last tile = all pairs)
+__global__ void tile_pair_off_kernel(int n_tiles, const int* __restrict__ tile_hdr, const long long* __restrict__ pairs_before, int* __restrict__ pair_off) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > n_tiles) return;
+  const int p = k < n_tiles ? tile_hdr[8 * (size_t)k + 2] : tile_hdr[8 * (size_t)(n_tiles - 1) + 3];
+  pair_off[k] = (int)pairs_before[p];
 }
 // ---- point renumbering: internal id = rank of (smallest observing camera, caller id) ----
 __global__ void fill_int_kernel(int n, int v, int* out) {
@@ -416,9 +435,29 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   }
   const double t_setup0 = now_ms();
   if (h2d_ms) *h2d_ms = t_setup0 - t_h2d0;
+  static const bool stage_timing = getenv("HSFM_SETUP_TIMING") != nullptr;  // experiment knob: where the index build spends its time
+  double t_stage = t_setup0;
+  auto stamp = [&](const char* what) {
+    if (!stage_timing) return;
+    cudaStreamSynchronize(s);
+    const double t = now_ms();
+    std::fprintf(stderr, "[setup] %-28s %7.3f ms\n", what, t - t_stage);
+    t_stage = t;
+  };
 
   // ---- internal camera order (ba_order.cpp): a band is eliminated from both ends at once ----
-  if (want_structure && !natural_order && choose_camera_order(n_cams, P.cam_first.data(), P.h_cam_new_of_old, &P.split_cams, &P.tail_cams)) {
+  bool reorder = false;
+  if (want_structure && !natural_order) {
+    Problem::OrderCache& oc = P.order_cache;
+    if (!(oc.valid && oc.first == P.cam_first)) {
+      oc.reordered = choose_camera_order(n_cams, P.cam_first.data(), oc.new_of_old, &oc.split_cams, &oc.tail_cams);
+      oc.first = P.cam_first;
+      oc.valid = true;
+    }
+    reorder = oc.reordered;
+    if (reorder) { P.h_cam_new_of_old = oc.new_of_old; P.split_cams = oc.split_cams; P.tail_cams = oc.tail_cams; }
+  }
+  if (reorder) {
     int* cam_tmp;
     ALLOC(P.cam_new_of_old, n_cams); ALLOC(P.cam_old_of_new, n_cams); ALLOC(cam_tmp, n); ALLOC(P.cam_io, 9 * (size_t)n_cams);
     HSFM_CUDA(cudaMemcpyAsync(P.cam_new_of_old, P.h_cam_new_of_old.data(), sizeof(int) * (size_t)n_cams, cudaMemcpyHostToDevice, s));
@@ -437,6 +476,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     P.tail_cams = -1;
   }
   HSFM_CUDA(cudaMemcpyAsync(P.cam_x, P.cam_x0, sizeof(double) * 6 * n_cams, cudaMemcpyDeviceToDevice, s));
+  stamp("camera order");
 
   // ---- static arrays ----
   double2 *obs, *obs_cs; int *cam, *pt, *pt_cs, *pt_start, *cam_start, *iota, *pos_cs, *cam_sorted, *order1, *key2;
@@ -453,6 +493,11 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   cub::DeviceRadixSort::SortPairs(nullptr, tmp2, cam, cam_sorted, iota, pos_cs, std::max({n, n_pts, 1}), 0, cbits, s);
   tmp_bytes = std::max(tmp_bytes, tmp2);
   cub::DeviceScan::InclusiveSum(nullptr, tmp2, iota, iota, std::max({n, n_pts, 1}), s);  // prefix sum over the tiles' camera counts
+  tmp_bytes = std::max(tmp_bytes, tmp2);
+  long long* pt_pairs;   // [n_pts + 1] observation pairs per point, then (exclusive scan) before every point
+  int* d_max_track;
+  ALLOC(pt_pairs, (size_t)n_pts + 1); ALLOC(d_max_track, 1);
+  cub::DeviceScan::ExclusiveSum(nullptr, tmp2, pt_pairs, pt_pairs, n_pts + 1, s);
   tmp_bytes = std::max(tmp_bytes, tmp2);
   void* tmp = P.arena_take(tmp_bytes);
   if (!tmp) return HSFM_BA_ERR_NOMEM;
@@ -480,72 +525,71 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     gather_cs_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, pos_cs, obs, pt, obs_cs, pt_cs);
     lower_bound_kernel<<<cdiv(n_pts + 1, 256), 256, 0, s>>>(n, pt, n_pts, pt_start);
     lower_bound_kernel<<<cdiv(n_cams + 1, 256), 256, 0, s>>>(n, cam_sorted, n_cams, cam_start);
+    HSFM_CUDA(cudaMemsetAsync(d_max_track, 0, sizeof(int), s));
+    point_pairs_kernel<<<cdiv(n_pts + 1, 256), 256, 0, s>>>(n_pts, pt_start, pt_pairs, d_max_track);
+    size_t tb = tmp_bytes;
+    cub::DeviceScan::ExclusiveSum(tmp, tb, pt_pairs, pt_pairs, n_pts + 1, s);
   } else {
     HSFM_CUDA(cudaMemsetAsync(pt_start, 0, sizeof(int) * ((size_t)n_pts + 1), s));
     HSFM_CUDA(cudaMemsetAsync(cam_start, 0, sizeof(int) * ((size_t)n_cams + 1), s));
   }
   HSFM_CUDA(cudaStreamSynchronize(s));
+  stamp("sorts (point / camera major)");
 
-  // ---- tiles: greedy packing of whole points into <= TILE observations (host, O(n_pts)) ----
+  // ---- tiles: greedy packing of whole points into <= TILE observations ----
+  // The host walks the point offsets tile by tile (one binary search per tile, ~n_obs / 250 of them: a loop over all
+  // points cost 2.8 ms at Venice size); track lengths and pair counts are reduced on the device.
   // the point offsets come back through a pinned, grow-only staging buffer (a pageable 4 MB copy per call costs ~1 ms)
-  if (P.idx_host_cap < (size_t)n_pts + 1) {
+  if (P.idx_host_cap < (size_t)n_pts + 8) {
     if (P.idx_host) cudaFreeHost(P.idx_host);
     P.idx_host = nullptr; P.idx_host_cap = 0;
-    const size_t want = ((size_t)n_pts + 1) * 5 / 4 + 1024;
+    const size_t want = ((size_t)n_pts + 8) * 5 / 4 + 1024;
     HSFM_CUDA(cudaMallocHost(&P.idx_host, sizeof(int) * want));
     P.idx_host_cap = want;
   }
   int* const h_pt_start = P.idx_host;
+  int* const h_small = P.idx_host + (size_t)n_pts + 2;  // [0] longest track
   std::vector<int> h_cam_start((size_t)n_cams + 1);
   HSFM_CUDA(cudaMemcpyAsync(h_pt_start, pt_start, sizeof(int) * ((size_t)n_pts + 1), cudaMemcpyDeviceToHost, s));
   HSFM_CUDA(cudaMemcpyAsync(h_cam_start.data(), cam_start, sizeof(int) * ((size_t)n_cams + 1), cudaMemcpyDeviceToHost, s));
-  HSFM_CUDA(cudaStreamSynchronize(s));
-  std::vector<int> tiles, tile_p;  // first observation / first point of every tile (+ end sentinels)
-  std::vector<long long> pair_cum; // observation pairs (sum over points of L(L+1)/2) before every tile (+ total)
-  tiles.reserve((size_t)n / (TILE - 32) + 2);
-  tile_p.reserve((size_t)n / (TILE - 32) + 2);
-  pair_cum.reserve((size_t)n / (TILE - 32) + 2);
-  int max_track = 0;
-  {
-    int tile_b = 0, p_end = 0;  // p_end: one past the last point that has observations (the others are sorted last)
-    long long acc = 0;
-    tiles.push_back(0); tile_p.push_back(0); pair_cum.push_back(0);
-    for (int p = 0; p < n_pts; ++p) {
-      const int b = h_pt_start[p], e = h_pt_start[p + 1];
-      max_track = std::max(max_track, e - b);
-      if (e > b) p_end = p + 1;
-      if (e - tile_b > TILE) {  // point p does not fit: close the tile before it
-        if (b > tile_b) { tiles.push_back(b); tile_p.push_back(p); pair_cum.push_back(acc); tile_b = b; }
-      }
-      acc += (long long)(e - b) * (e - b + 1) / 2;
-    }
-    if (n > tile_b) { tiles.push_back(n); tile_p.push_back(p_end); pair_cum.push_back(acc); }
-    if (tiles.size() == 1) { tiles.clear(); tile_p.clear(); pair_cum.clear(); }
+  long long h_total_pairs = 0;
+  h_small[0] = 0;
+  if (n > 0) {
+    HSFM_CUDA(cudaMemcpyAsync(h_small, d_max_track, sizeof(int), cudaMemcpyDeviceToHost, s));
+    HSFM_CUDA(cudaMemcpyAsync(&h_total_pairs, pt_pairs + n_pts, sizeof(long long), cudaMemcpyDeviceToHost, s));
   }
+  HSFM_CUDA(cudaStreamSynchronize(s));
+  const int max_track = h_small[0];
   P.max_track = max_track;
   if (max_track > MAX_TRACK) return HSFM_BA_ERR_UNSUPPORTED;
+  std::vector<int> tiles, tile_p;  // first observation / first point of every tile (+ end sentinels)
+  tiles.reserve((size_t)n / (TILE - 32) + 2);
+  tile_p.reserve((size_t)n / (TILE - 32) + 2);
+  if (n > 0) {
+    // points without observations are sorted last: p_end = one past the last point that has some
+    const int p_end = (int)(std::lower_bound(h_pt_start, h_pt_start + n_pts + 1, n) - h_pt_start);
+    int p = 0;
+    tiles.push_back(0); tile_p.push_back(0);
+    while (p < p_end) {
+      // the tile takes the points p .. q-1 with h_pt_start[q] - h_pt_start[p] <= TILE (at least one: max_track <= TILE)
+      const int q = (int)(std::upper_bound(h_pt_start + p + 1, h_pt_start + p_end + 1, h_pt_start[p] + TILE) - h_pt_start) - 1;
+      p = std::max(q, p + 1);
+      tiles.push_back(h_pt_start[p]); tile_p.push_back(p);
+    }
+  }
+  stamp("tile packing (host)");
   P.n_tiles = tiles.empty() ? 0 : (int)tiles.size() - 1;
   int* tile_start;
   ALLOC(tile_start, tiles.size() + 1);
   if (!tiles.empty()) HSFM_CUDA(cudaMemcpyAsync(tile_start, tiles.data(), sizeof(int) * tiles.size(), cudaMemcpyHostToDevice, s));
+  // per-tile offsets into the (lazily built) sorted pair lists of dense_schur: sum over the tile's points of L(L+1)/2
+  // (filled on the device once the tile headers are there)
+  int* pair_off = nullptr;
+  P.total_pairs = h_total_pairs;
+  P.pairs_ready = false;
+  if (h_total_pairs < (1ll << 31) && P.n_tiles > 0) ALLOC(pair_off, (size_t)P.n_tiles + 1);
   // distinct cameras of every tile + each observation's slot in that list: the streaming kernels stage the
   // tile's camera rows / camera vectors in shared memory once instead of gathering them per observation
-  // per-tile offsets into the (lazily built) sorted pair lists of dense_schur: sum over the tile's points of L(L+1)/2
-  int* pair_off = nullptr;
-  {
-    std::vector<int> po((size_t)P.n_tiles + 1, 0);
-    const long long acc = P.n_tiles ? pair_cum[(size_t)P.n_tiles] : 0;
-    if (acc < (1ll << 31))
-      for (int k = 0; k < P.n_tiles; ++k) po[k] = (int)pair_cum[(size_t)k];
-    P.total_pairs = acc;
-    P.pairs_ready = false;
-    if (acc < (1ll << 31) && P.n_tiles > 0) {
-      po[P.n_tiles] = (int)acc;
-      ALLOC(pair_off, (size_t)P.n_tiles + 1);
-      HSFM_CUDA(cudaMemcpyAsync(pair_off, po.data(), sizeof(int) * po.size(), cudaMemcpyHostToDevice, s));
-      HSFM_CUDA(cudaStreamSynchronize(s));
-    }
-  }
   unsigned char *slot, *srank, *sorder; unsigned short* slot_begin; int *tile_cams, *tile_hdr, *d_max_ncam, *ent_off;
   ALLOC(slot, n); ALLOC(tile_cams, (size_t)P.n_tiles * TILE); ALLOC(tile_hdr, 8 * (size_t)std::max(1, P.n_tiles)); ALLOC(d_max_ncam, 1);
   ALLOC(srank, n); ALLOC(sorder, n); ALLOC(slot_begin, (size_t)P.n_tiles * TILE); ALLOC(ent_off, (size_t)P.n_tiles + 2);
@@ -560,6 +604,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
       hdr[8 * (size_t)k + 2] = tile_p[k]; hdr[8 * (size_t)k + 3] = tile_p[k + 1];
     }
     HSFM_CUDA(cudaMemcpyAsync(tile_hdr, hdr.data(), sizeof(int) * hdr.size(), cudaMemcpyHostToDevice, s));
+    if (pair_off) tile_pair_off_kernel<<<cdiv(P.n_tiles + 1, 256), 256, 0, s>>>(P.n_tiles, tile_hdr, pt_pairs, pair_off);
     HSFM_CUDA(cudaMemsetAsync(d_max_ncam, 0, sizeof(int), s));
     HSFM_CUDA(cudaMemsetAsync(ent_off, 0, sizeof(int), s));
     tile_cams_kernel<<<P.n_tiles, TILE, 0, s>>>(tile_start, cam, slot, tile_cams, tile_hdr, d_max_ncam, srank, sorder, slot_begin, ent_off + 1);
@@ -589,6 +634,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     HSFM_CUDA(cudaMemsetAsync(ent_off, 0, sizeof(int) * 2, s));
   }
 
+  stamp("tile cameras / entries");
   // ---- camera-major warp chunks ----
   std::vector<int> ch_cam, ch_b, ch_e, cam_ch_start((size_t)n_cams + 1, 0);
   for (int c = 0; c < n_cams; ++c) {
@@ -666,6 +712,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   d.obs_cs = obs_cs; d.pt_cs = pt_cs; d.pos_cs = pos_cs; d.chunk_cam = d_ch_cam; d.chunk_b = d_ch_b; d.chunk_e = d_ch_e; d.cam_chunk_start = d_cam_ch_start;
   d.r = r; d.Jc = Jc; d.Jp = Jp;
   HSFM_CUDA(cudaStreamSynchronize(s));
+  stamp("chunks, state, clears");
   if (setup_ms) *setup_ms = now_ms() - t_setup0;
   return 0;
 }

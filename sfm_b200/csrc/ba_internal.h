@@ -80,6 +80,14 @@ struct Problem {
   int split_cams = -1;            // first internal camera of the second chain (two-ended order) or -1
   int tail_cams = -1;             // first internal camera of the tail (cameras coupled to both chains) or -1
   double* cam_io = nullptr;       // [n_cams][9] staging in the caller's camera order (upload / download / taps)
+  // The last ordering decision (survives release()): the per-keyframe calls of a scan and repeated solves mostly bring
+  // the camera graph of the previous call back, and the host-side choice (a few ms of symbolic work per candidate
+  // order at Venice size) is then skipped.
+  struct OrderCache {
+    bool valid = false, reordered = false;
+    std::vector<int> first, new_of_old;
+    int split_cams = -1, tail_cams = -1;
+  } order_cache;
   Dev d{};
   // Device arena: ONE grow-only allocation per context that every per-problem buffer is carved from, so the
   // per-keyframe calls of CSfM::mapping (CSfM.cpp:252-259) pay for cudaMalloc/cudaFree only when the problem
@@ -343,6 +351,7 @@ struct Ctx {
   CholAux chol_aux;
   CholPlan chol_plan;     // envelope plan of the resident problem (built on first dense solve)
   bool chol_plan_valid = false;
+  std::vector<int> plan_first, plan_new_of_old;  // the envelope and camera order chol_plan was built from
   Problem prob;
   bool has_problem = false;
   int ordering = 0;         // 0 = automatic camera order, 1 = the caller's (hsfm_ba_set_ordering)

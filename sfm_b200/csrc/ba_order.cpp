@@ -213,6 +213,7 @@ bool choose_camera_order(int n_cams, const int* first, std::vector<int>& new_of_
     static const bool verbose = getenv("HSFM_ORDER_VERBOSE") != nullptr;
     if (verbose) std::fprintf(stderr, "[order] depth %d: critical panels %d, estimated %.3f ms (best so far %.3f)\n", depth, crit, 1e3 * cost, 1e3 * best_cost);
     if (cost < 0.9 * best_cost || force_depth >= 0) { best_cost = cost; best.swap(cand); best_depth = depth; best_sizes[0] = sizes[0]; best_sizes[1] = sizes[1]; }
+    else if (depth > 0) break;  // a deeper dissection that does not pay ends the search
   }
   if (best_depth < 0) return false;
   new_of_old.swap(best);
@@ -226,14 +227,24 @@ void block_pattern_from_envelope(int n_cams, const int* first, const int* new_of
   const int n = 6 * n_cams, P = (n + NB - 1) / NB;
   *panels = P;
   pattern.assign((size_t)P * P, 0);
+  // first and last 128-row block of every camera, by CALLER index (a camera's six rows straddle a block boundary at most once)
+  std::vector<int> pos((size_t)n_cams), b0((size_t)n_cams), b1((size_t)n_cams);
   for (int c = 0; c < n_cams; ++c) {
     const int ic = new_of_old ? new_of_old[c] : c;
+    pos[c] = ic; b0[c] = (6 * ic) / NB; b1[c] = (6 * ic + 5) / NB;
+  }
+  uint8_t* pat = pattern.data();
+  for (int c = 0; c < n_cams; ++c) {
+    const int ic = pos[c], cb0 = b0[c], cb1 = b1[c];
     for (int d = std::min(first[c], c); d <= c; ++d) {
-      const int id = new_of_old ? new_of_old[d] : d;
-      const int hi = std::max(ic, id), lo = std::min(ic, id);
-      const int bi0 = (6 * hi) / NB, bi1 = (6 * hi + 5) / NB, bj0 = (6 * lo) / NB, bj1 = (6 * lo + 5) / NB;
-      for (int bi = bi0; bi <= bi1; ++bi)
-        for (int bj = bj0; bj <= std::min(bj1, bi); ++bj) pattern[(size_t)bi * P + bj] = 1;
+      // block rows of the later camera (in the internal order) x block columns of the earlier one, lower triangle
+      const bool c_later = ic >= pos[d];
+      const int r0 = c_later ? cb0 : b0[d], r1 = c_later ? cb1 : b1[d], q0 = c_later ? b0[d] : cb0, q1 = c_later ? b1[d] : cb1;
+      pat[(size_t)r0 * P + q0] = 1;
+      if (r1 != r0 || q1 != q0) {
+        for (int bi = r0; bi <= r1; ++bi)
+          for (int bj = q0; bj <= std::min(q1, bi); ++bj) pat[(size_t)bi * P + bj] = 1;
+      }
     }
   }
   for (int I = 0; I < P; ++I) pattern[(size_t)I * P + I] = 1;

@@ -183,11 +183,18 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
       if (ctx.chol_plan_valid) return 0;
       int rc;
       if ((int)P.cam_first.size() == P.n_cams && P.n_cams > 0) {
+        // the same camera graph in the same internal order as the plan was built from: nothing to do
+        if (ctx.chol_plan.version > 0 && ctx.chol_plan.n == n6 && ctx.plan_first == P.cam_first && ctx.plan_new_of_old == P.h_cam_new_of_old) {
+          ctx.chol_plan_valid = true;
+          return 0;
+        }
         std::vector<uint8_t> pattern;
         int panels = 0;
         block_pattern_from_envelope(P.n_cams, P.cam_first.data(), P.h_cam_new_of_old.empty() ? nullptr : P.h_cam_new_of_old.data(), pattern, &panels);
         rc = ctx.chol_plan.build(P.n_cams, pattern.data(), panels, s);
+        ctx.plan_first = P.cam_first; ctx.plan_new_of_old = P.h_cam_new_of_old;
       } else {
+        ctx.plan_first.clear(); ctx.plan_new_of_old.clear();
         rc = ctx.chol_plan.build(P.n_cams, nullptr, 0, s);
       }
       if (rc) return rc;
