@@ -23,8 +23,10 @@ void Problem::release() {
   const int sm = n_sm;
   OrderCache oc;
   std::swap(oc, order_cache);
+  cudaStream_t cs = copy_stream; cudaEvent_t e0 = ev_copy_go, e1 = ev_copy_done;
   *this = Problem();
   std::swap(oc, order_cache);
+  copy_stream = cs; ev_copy_go = e0; ev_copy_done = e1;
   n_sm = sm;
   arena = a; arena_cap = cap; arena_off = 0;
   S = s_keep; S_capacity = s_cap;
@@ -42,6 +44,9 @@ void Problem::destroy() {
   if (scal_host) cudaFreeHost(scal_host);
   if (flags_host) cudaFreeHost(flags_host);
   if (idx_host) cudaFreeHost(idx_host);
+  if (copy_stream) cudaStreamDestroy(copy_stream);
+  if (ev_copy_go) cudaEventDestroy(ev_copy_go);
+  if (ev_copy_done) cudaEventDestroy(ev_copy_done);
   *this = Problem();
 }
 
@@ -89,21 +94,18 @@ __global__ void iota_kernel(int n, int* out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = i;
 }
-__global__ void gather_obs_kernel(int n, const int* __restrict__ order, const double2* __restrict__ obs_in, const int* __restrict__ cam_in,
-                                  double2* __restrict__ obs, int* __restrict__ cam) {
+// Point-major / camera-major gathers, integer keys and pixel coordinates apart: the index build only needs the keys, so
+// the observations' coordinates (the bulk of the upload) can still be on their way while it runs.
+__global__ void gather_key_kernel(int n, const int* __restrict__ order, const int* __restrict__ key_in, int* __restrict__ key) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int o = order[i];
-  obs[i] = obs_in[o];
-  cam[i] = cam_in[o];
+  if (i < n) key[i] = key_in[order[i]];
 }
-__global__ void gather_cs_kernel(int n, const int* __restrict__ pos, const double2* __restrict__ obs, const int* __restrict__ pt,
-                                 double2* __restrict__ obs_cs, int* __restrict__ pt_cs) {
+__global__ void gather_xy_kernel(int n, const int* __restrict__ order_pm, const int* __restrict__ pos_cs, const double2* __restrict__ obs_in,
+                                 double2* __restrict__ obs, double2* __restrict__ obs_cs) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const int j = pos[i];
-  obs_cs[i] = obs[j];
-  pt_cs[i] = pt[j];
+  obs[i] = obs_in[order_pm[i]];
+  obs_cs[i] = obs_in[order_pm[pos_cs[i]]];
 }
 // start[k] = first index i with keys[i] >= k   (keys sorted ascending), k = 0..n_keys
 __global__ void lower_bound_kernel(int n, const int* __restrict__ keys, int n_keys, int* __restrict__ start) {
@@ -370,6 +372,7 @@ int dedupe_pointers(PtrScratch& W, int64_t n64, double* const* host_ptrs, int** 
 int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
                   int32_t n_cams, const double* K9, const double* dist, const double* cam_rt, int64_t n_pts64, const double* pts,
                   Comm& comm, cudaStream_t s, double* setup_ms, double* h2d_ms, bool natural_order) {
+  if (P.copy_stream) cudaStreamSynchronize(P.copy_stream);  // a previous upload that returned early may still be copying into the arena
   P.release();
   if (n_obs64 >= (int64_t)1 << 31 || n_pts64 >= (int64_t)1 << 30) return HSFM_BA_ERR_UNSUPPORTED;
   const int n = (int)n_obs64, n_pts = (int)n_pts64;
@@ -390,20 +393,32 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     if (rc) return rc;
   }
   const double t_h2d0 = now_ms();
+  double copy_wait_ms = 0.0;
   double2* obs_in; int *cam_in, *pt_in;
   ALLOC(obs_in, n); ALLOC(cam_in, n); ALLOC(pt_in, n);
   ALLOC(P.K9, 9 * (size_t)n_cams); ALLOC(P.dist, 2 * (size_t)n_cams);
   ALLOC(P.cam_x, 6 * (size_t)n_cams); ALLOC(P.pts_x, 3 * (size_t)n_pts);
   ALLOC(P.cam_x0, 6 * (size_t)n_cams); ALLOC(P.pts_x0, 3 * (size_t)n_pts); ALLOC(P.pts_io, 3 * (size_t)n_pts);
-  // cudaMemcpyDefault: the sources are host buffers (one-shot calls) or the device-resident scan store (ba_scan.cu)
-  HSFM_CUDA(cudaMemcpyAsync(obs_in, obs_xy, sizeof(double) * 2 * n, cudaMemcpyDefault, s));
+  // cudaMemcpyDefault: the sources are host buffers (one-shot calls) or the device-resident scan store (ba_scan.cu).
+  // The index arrays go first on the solver's stream; pixel coordinates and points (two thirds of the bytes) follow on a
+  // copy stream of their own and are only waited for at the end of the index build, which needs none of them.
+  if (!P.copy_stream) {
+    HSFM_CUDA(cudaStreamCreateWithFlags(&P.copy_stream, cudaStreamNonBlocking));
+    HSFM_CUDA(cudaEventCreateWithFlags(&P.ev_copy_go, cudaEventDisableTiming));
+    HSFM_CUDA(cudaEventCreateWithFlags(&P.ev_copy_done, cudaEventDisableTiming));
+  }
   HSFM_CUDA(cudaMemcpyAsync(cam_in, cam_idx, sizeof(int) * (size_t)n, cudaMemcpyDefault, s));
   HSFM_CUDA(cudaMemcpyAsync(pt_in, pt_idx, sizeof(int) * (size_t)n, cudaMemcpyDefault, s));
   HSFM_CUDA(cudaMemcpyAsync(P.K9, K9, sizeof(double) * 9 * n_cams, cudaMemcpyDefault, s));
   if (dist) HSFM_CUDA(cudaMemcpyAsync(P.dist, dist, sizeof(double) * 2 * n_cams, cudaMemcpyDefault, s));
   else HSFM_CUDA(cudaMemsetAsync(P.dist, 0, sizeof(double) * 2 * std::max(1, n_cams), s));
   HSFM_CUDA(cudaMemcpyAsync(P.cam_x0, cam_rt, sizeof(double) * 6 * n_cams, cudaMemcpyDefault, s));
-  HSFM_CUDA(cudaMemcpyAsync(P.pts_io, pts, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDefault, s));
+  // after the index arrays (they are needed first and share the link), and after everything that used the arena before
+  HSFM_CUDA(cudaEventRecord(P.ev_copy_go, s));
+  HSFM_CUDA(cudaStreamWaitEvent(P.copy_stream, P.ev_copy_go, 0));
+  HSFM_CUDA(cudaMemcpyAsync(obs_in, obs_xy, sizeof(double) * 2 * n, cudaMemcpyDefault, P.copy_stream));
+  HSFM_CUDA(cudaMemcpyAsync(P.pts_io, pts, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDefault, P.copy_stream));
+  HSFM_CUDA(cudaEventRecord(P.ev_copy_done, P.copy_stream));
   // Envelope of the reduced camera matrix in the caller's camera order (over all ranks): what the camera ordering and
   // the block structure of the Cholesky are derived from.  Only where a structured factorisation can pay (>= 4 panels).
   int *min_cam, *min_cam_sorted;
@@ -509,9 +524,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     if (n > 0) min_cam_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, pt_in, cam_in, min_cam);
     cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, min_cam, min_cam_sorted, iota, P.pt_old_of_new, n_pts, 0, cbits, s);
     invert_perm_kernel<<<cdiv(n_pts, 256), 256, 0, s>>>(n_pts, P.pt_old_of_new, P.pt_new_of_old);
-    gather_rows_kernel<<<cdivz((size_t)n_pts * 3, 256), 256, 0, s>>>(n_pts, 3, P.pt_old_of_new, P.pts_io, P.pts_x0);
   }
-  HSFM_CUDA(cudaMemcpyAsync(P.pts_x, P.pts_x0, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToDevice, s));
   if (n > 0) {
     // point-major with cameras ascending inside a point: stable sort by camera, then stable sort by
     // internal point id (ties keep input order, so every later floating-point sum has a fixed order)
@@ -519,10 +532,10 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     gather_int_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, order1, pt_in, key2);
     gather_int_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, key2, P.pt_new_of_old, pos_cs /*scratch*/);
     cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, pos_cs, pt, order1, P.order_pm, n, 0, pbits, s);
-    gather_obs_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, P.order_pm, obs_in, cam_in, obs, cam);
+    gather_key_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, P.order_pm, cam_in, cam);
     // camera-major: stable sort of point-major positions by camera
     cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, cam, cam_sorted, iota, pos_cs, n, 0, cbits, s);
-    gather_cs_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, pos_cs, obs, pt, obs_cs, pt_cs);
+    gather_key_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, pos_cs, pt, pt_cs);
     lower_bound_kernel<<<cdiv(n_pts + 1, 256), 256, 0, s>>>(n, pt, n_pts, pt_start);
     lower_bound_kernel<<<cdiv(n_cams + 1, 256), 256, 0, s>>>(n, cam_sorted, n_cams, cam_start);
     HSFM_CUDA(cudaMemsetAsync(d_max_track, 0, sizeof(int), s));
@@ -692,6 +705,17 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   HSFM_CUDA(cudaMemsetAsync(P.gp, 0, sizeof(double) * 3 * std::max<size_t>(1, n_pts), s));
   HSFM_CUDA(cudaMemsetAsync(P.yp, 0, sizeof(double) * 3 * std::max<size_t>(1, n_pts), s));
   HSFM_CUDA(cudaMemsetAsync(P.yc, 0, sizeof(double) * 18 * std::max<size_t>(1, n_cams), s));
+  // ---- the bulk of the upload has had the whole index build to arrive: pixel coordinates and points into their orders ----
+  {
+    const double t_w0 = now_ms();
+    if (stage_timing) cudaStreamSynchronize(s);
+    HSFM_CUDA(cudaEventSynchronize(P.ev_copy_done));
+    copy_wait_ms = now_ms() - t_w0;
+    if (stage_timing) std::fprintf(stderr, "[setup] index arrays + envelope: %.3f ms; wait for the rest of the upload: %.3f ms\n", t_setup0 - t_h2d0, copy_wait_ms);
+  }
+  if (n > 0) gather_xy_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, P.order_pm, pos_cs, obs_in, obs, obs_cs);
+  if (n_pts > 0) gather_rows_kernel<<<cdivz((size_t)n_pts * 3, 256), 256, 0, s>>>(n_pts, 3, P.pt_old_of_new, P.pts_io, P.pts_x0);
+  HSFM_CUDA(cudaMemcpyAsync(P.pts_x, P.pts_x0, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToDevice, s));
   HSFM_CUDA(cudaMemcpyAsync(P.pts_c, P.pts_x, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDeviceToDevice, s));
 
   {
@@ -713,7 +737,9 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   d.r = r; d.Jc = Jc; d.Jp = Jp;
   HSFM_CUDA(cudaStreamSynchronize(s));
   stamp("chunks, state, clears");
-  if (setup_ms) *setup_ms = now_ms() - t_setup0;
+  // the wait for the tail of the upload is transfer time, not index-build time
+  if (setup_ms) *setup_ms = now_ms() - t_setup0 - copy_wait_ms;
+  if (h2d_ms) *h2d_ms += copy_wait_ms;
   return 0;
 }
 

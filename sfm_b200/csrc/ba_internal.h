@@ -80,6 +80,8 @@ struct Problem {
   int split_cams = -1;            // first internal camera of the second chain (two-ended order) or -1
   int tail_cams = -1;             // first internal camera of the tail (cameras coupled to both chains) or -1
   double* cam_io = nullptr;       // [n_cams][9] staging in the caller's camera order (upload / download / taps)
+  cudaStream_t copy_stream = nullptr;  // upload of the observations' coordinates and the points beside the index build (survives release())
+  cudaEvent_t ev_copy_go = nullptr, ev_copy_done = nullptr;
   // The last ordering decision (survives release()): the per-keyframe calls of a scan and repeated solves mostly bring
   // the camera graph of the previous call back, and the host-side choice (a few ms of symbolic work per candidate
   // order at Venice size) is then skipped.
