@@ -10,7 +10,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libhsfm_ba.so")
-SOURCES = ["ba_kernels.cu", "ba_chol.cu", "ba_index.cu", "ba_comm.cu", "ba_solver.cu", "ba_api.cu", "ba_order.cpp", "ba_noalloc.cu", "ba_scan.cu"]
+SOURCES = ["ba_kernels.cu", "ba_chol.cu", "ba_index.cu", "ba_comm.cu", "ba_solver.cu", "ba_api.cu", "ba_order.cpp", "ba_noalloc.cu", "ba_scan.cu", "ba_stage.cu"]
 HEADERS = ["ba_internal.h", "ba_math.cuh", os.path.join("..", "..", "include", "hsfm_ba.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [

@@ -466,15 +466,16 @@ int hsfm_ba_solve_ptr(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double* obs
   HSFM_CUDA(cudaSetDevice(h->c.device));
   static const bool timing = getenv("HSFM_PTR_TIMING") != nullptr;  // experiment knob: where the call's host time goes
   const double tt0 = now_ms();
-  std::vector<double*> uniq;
+  double* const* uniq = nullptr;
+  int64_t n_pts = 0;
   int* d_pt_idx = nullptr;
   {
-    const int rc0 = dedupe_pointers(h->c.ptr_ws, n_obs, pts3d, &d_pt_idx, uniq, h->c.stream);
+    const int rc0 = dedupe_pointers(h->c.ptr_ws, n_obs, pts3d, &d_pt_idx, &uniq, &n_pts, h->c.stream, &h->c.prob.stager);
     if (rc0) return rc0;
   }
   const double tt1 = now_ms();
-  const int64_t n_pts = (int64_t)uniq.size();
-  std::vector<double> cam((size_t)n_cams * 6), pts((size_t)n_pts * 3);
+  std::vector<double> cam((size_t)n_cams * 6);
+  double* const pts = h->c.ptr_ws.pts_host;  // pinned, sized by dedupe_pointers
   for (int c = 0; c < n_cams; ++c) {
     if (!R[c] || !t[c]) return HSFM_BA_ERR_ARG;
     for (int k = 0; k < 3; ++k) { cam[6 * (size_t)c + k] = R[c][k]; cam[6 * (size_t)c + 3 + k] = t[c][k]; }
@@ -486,7 +487,7 @@ int hsfm_ba_solve_ptr(hsfm_ba_ctx* h, int mode, int64_t n_obs, const double* obs
   });
   const double tt2 = now_ms();
   // pt_idx is a DEVICE array: the upload copies with cudaMemcpyDefault
-  int rc = hsfm_ba_solve_packed(h, mode, n_obs, obs_xy, cam_idx, d_pt_idx, n_cams, K9, nullptr, cam.data(), n_pts, pts.data(), opts, summary);
+  int rc = hsfm_ba_solve_packed(h, mode, n_obs, obs_xy, cam_idx, d_pt_idx, n_cams, K9, nullptr, cam.data(), n_pts, pts, opts, summary);
   if (rc) return rc;  // parameters untouched on failure
   const double tt3 = now_ms();
   if (mode != HSFM_BA_STRUCT_ONLY)

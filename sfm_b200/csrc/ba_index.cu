@@ -24,9 +24,11 @@ void Problem::release() {
   OrderCache oc;
   std::swap(oc, order_cache);
   cudaStream_t cs = copy_stream; cudaEvent_t e0 = ev_copy_go, e1 = ev_copy_done;
+  const HostStager st = stager;
   *this = Problem();
   std::swap(oc, order_cache);
   copy_stream = cs; ev_copy_go = e0; ev_copy_done = e1;
+  stager = st;
   n_sm = sm;
   arena = a; arena_cap = cap; arena_off = 0;
   S = s_keep; S_capacity = s_cap;
@@ -44,6 +46,7 @@ void Problem::destroy() {
   if (scal_host) cudaFreeHost(scal_host);
   if (flags_host) cudaFreeHost(flags_host);
   if (idx_host) cudaFreeHost(idx_host);
+  stager.destroy();
   if (copy_stream) cudaStreamDestroy(copy_stream);
   if (ev_copy_go) cudaEventDestroy(ev_copy_go);
   if (ev_copy_done) cudaEventDestroy(ev_copy_done);
@@ -305,11 +308,15 @@ __global__ void ptr_ids_kernel(int n, const unsigned long long* __restrict__ sor
 void PtrScratch::destroy() {
   if (buf) cudaFree(buf);
   if (uniq_host) cudaFreeHost(uniq_host);
+  if (pts_host) cudaFreeHost(pts_host);
+  pts_host = nullptr; pts_cap = 0;
   *this = PtrScratch();
 }
 
-int dedupe_pointers(PtrScratch& W, int64_t n64, double* const* host_ptrs, int** d_pt_idx_out, std::vector<double*>& uniq_out, cudaStream_t s) {
-  uniq_out.clear();
+int dedupe_pointers(PtrScratch& W, int64_t n64, double* const* host_ptrs, int** d_pt_idx_out, double* const** uniq_out, int64_t* n_uniq_out,
+                    cudaStream_t s, HostStager* stager) {
+  *uniq_out = nullptr;
+  *n_uniq_out = 0;
   *d_pt_idx_out = nullptr;
   if (n64 >= (int64_t)1 << 31) return HSFM_BA_ERR_UNSUPPORTED;
   const int n = (int)n64;
@@ -340,7 +347,14 @@ int dedupe_pointers(PtrScratch& W, int64_t n64, double* const* host_ptrs, int** 
   int* incl = (int*)take(n4);
   int* pt_idx = (int*)take(n4);
   void* d_tmp = take(tmp);
-  HSFM_CUDA(cudaMemcpyAsync(keys, host_ptrs, sizeof(unsigned long long) * (size_t)n, cudaMemcpyHostToDevice, s));
+  if (stager && sizeof(unsigned long long) * (size_t)n >= HostStager::MIN_BYTES && HostStager::pageable(host_ptrs)) {
+    int device = 0;
+    HSFM_CUDA(cudaGetDevice(&device));
+    const int rc = stager->copy({{keys, host_ptrs, sizeof(unsigned long long) * (size_t)n}}, s, device);
+    if (rc) return rc;
+  } else {
+    HSFM_CUDA(cudaMemcpyAsync(keys, host_ptrs, sizeof(unsigned long long) * (size_t)n, cudaMemcpyHostToDevice, s));
+  }
   iota_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, iota);
   size_t tb = tmp;
   cub::DeviceRadixSort::SortPairs(d_tmp, tb, keys, sorted, iota, src, n, 0, 48, s);
@@ -363,8 +377,16 @@ int dedupe_pointers(PtrScratch& W, int64_t n64, double* const* host_ptrs, int** 
   }
   HSFM_CUDA(cudaMemcpyAsync(W.uniq_host, uniq, sizeof(unsigned long long) * (size_t)n_uniq, cudaMemcpyDeviceToHost, s));
   HSFM_CUDA(cudaStreamSynchronize(s));
-  uniq_out.resize((size_t)n_uniq);
-  for (int k = 0; k < n_uniq; ++k) uniq_out[(size_t)k] = reinterpret_cast<double*>(W.uniq_host[k]);
+  *uniq_out = reinterpret_cast<double* const*>(W.uniq_host);  // the pinned mirror itself: valid until the next call
+  *n_uniq_out = n_uniq;
+  // pinned staging of the distinct points for the packed call (grow-only)
+  if (W.pts_cap < 3 * (size_t)n_uniq) {
+    if (W.pts_host) cudaFreeHost(W.pts_host);
+    W.pts_host = nullptr; W.pts_cap = 0;
+    const size_t want = 3 * ((size_t)n_uniq + (size_t)n_uniq / 4 + 1024);
+    HSFM_CUDA(cudaMallocHost(&W.pts_host, sizeof(double) * want));
+    W.pts_cap = want;
+  }
   *d_pt_idx_out = pt_idx;
   return 0;
 }
@@ -407,8 +429,21 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     HSFM_CUDA(cudaEventCreateWithFlags(&P.ev_copy_go, cudaEventDisableTiming));
     HSFM_CUDA(cudaEventCreateWithFlags(&P.ev_copy_done, cudaEventDisableTiming));
   }
-  HSFM_CUDA(cudaMemcpyAsync(cam_in, cam_idx, sizeof(int) * (size_t)n, cudaMemcpyDefault, s));
-  HSFM_CUDA(cudaMemcpyAsync(pt_in, pt_idx, sizeof(int) * (size_t)n, cudaMemcpyDefault, s));
+  int device = 0;
+  HSFM_CUDA(cudaGetDevice(&device));
+  // pageable sources (the reference's std::vectors) are staged through pinned rings by a few threads (HostStager)
+  auto staged = [&](const void* p, size_t bytes) { return bytes >= HostStager::MIN_BYTES && HostStager::pageable(p); };
+  {
+    std::vector<HostStager::Job> jobs;
+    if (staged(cam_idx, sizeof(int) * (size_t)n)) jobs.push_back({cam_in, cam_idx, sizeof(int) * (size_t)n});
+    else HSFM_CUDA(cudaMemcpyAsync(cam_in, cam_idx, sizeof(int) * (size_t)n, cudaMemcpyDefault, s));
+    if (staged(pt_idx, sizeof(int) * (size_t)n)) jobs.push_back({pt_in, pt_idx, sizeof(int) * (size_t)n});
+    else HSFM_CUDA(cudaMemcpyAsync(pt_in, pt_idx, sizeof(int) * (size_t)n, cudaMemcpyDefault, s));
+    if (!jobs.empty()) {
+      const int rc = P.stager.copy(jobs, s, device);
+      if (rc) return rc;
+    }
+  }
   HSFM_CUDA(cudaMemcpyAsync(P.K9, K9, sizeof(double) * 9 * n_cams, cudaMemcpyDefault, s));
   if (dist) HSFM_CUDA(cudaMemcpyAsync(P.dist, dist, sizeof(double) * 2 * n_cams, cudaMemcpyDefault, s));
   else HSFM_CUDA(cudaMemsetAsync(P.dist, 0, sizeof(double) * 2 * std::max(1, n_cams), s));
@@ -416,9 +451,20 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   // after the index arrays (they are needed first and share the link), and after everything that used the arena before
   HSFM_CUDA(cudaEventRecord(P.ev_copy_go, s));
   HSFM_CUDA(cudaStreamWaitEvent(P.copy_stream, P.ev_copy_go, 0));
-  HSFM_CUDA(cudaMemcpyAsync(obs_in, obs_xy, sizeof(double) * 2 * n, cudaMemcpyDefault, P.copy_stream));
-  HSFM_CUDA(cudaMemcpyAsync(P.pts_io, pts, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDefault, P.copy_stream));
-  HSFM_CUDA(cudaEventRecord(P.ev_copy_done, P.copy_stream));
+  struct Joiner {  // background staging threads reference this frame: no return without them
+    std::vector<std::thread> th;
+    void join() { for (auto& t : th) if (t.joinable()) t.join(); th.clear(); }
+    ~Joiner() { join(); }
+  } bg;
+  int bg_rc = 0;
+  {
+    std::vector<HostStager::Job> jobs;
+    if (staged(obs_xy, sizeof(double) * 2 * (size_t)n)) jobs.push_back({obs_in, obs_xy, sizeof(double) * 2 * (size_t)n});
+    else HSFM_CUDA(cudaMemcpyAsync(obs_in, obs_xy, sizeof(double) * 2 * n, cudaMemcpyDefault, P.copy_stream));
+    if (staged(pts, sizeof(double) * 3 * (size_t)n_pts)) jobs.push_back({P.pts_io, pts, sizeof(double) * 3 * (size_t)n_pts});
+    else HSFM_CUDA(cudaMemcpyAsync(P.pts_io, pts, sizeof(double) * 3 * (size_t)n_pts, cudaMemcpyDefault, P.copy_stream));
+    if (!jobs.empty()) P.stager.start(jobs, P.copy_stream, device, bg.th, &bg_rc);
+  }
   // Envelope of the reduced camera matrix in the caller's camera order (over all ranks): what the camera ordering and
   // the block structure of the Cholesky are derived from.  Only where a structured factorisation can pay (>= 4 panels).
   int *min_cam, *min_cam_sorted;
@@ -709,6 +755,9 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   {
     const double t_w0 = now_ms();
     if (stage_timing) cudaStreamSynchronize(s);
+    bg.join();
+    if (bg_rc) return bg_rc;
+    HSFM_CUDA(cudaEventRecord(P.ev_copy_done, P.copy_stream));
     HSFM_CUDA(cudaEventSynchronize(P.ev_copy_done));
     copy_wait_ms = now_ms() - t_w0;
     if (stage_timing) std::fprintf(stderr, "[setup] index arrays + envelope: %.3f ms; wait for the rest of the upload: %.3f ms\n", t_setup0 - t_h2d0, copy_wait_ms);

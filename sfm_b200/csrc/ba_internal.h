@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/hsfm_ba.h"
@@ -62,6 +63,27 @@ struct Dev {
   double2* Jp;           // [3][n_obs]
 };
 
+// Pageable host memory -> device at link speed.  cudaMemcpyAsync from pageable memory goes through the driver's own
+// staging at ~10 GB/s and blocks the caller; the reference's containers (std::vector, CSfM.cpp:311-343) are pageable.
+// Here worker threads copy slices of the source into pinned rings and the DMA of one chunk runs while the next one is
+// being copied: ~4 threads keep up with the link.  Sources that are pinned or device memory never come here.
+struct HostStager {
+  static constexpr int LANES = 4, CHUNKS = 3;
+  static constexpr size_t CHUNK = (size_t)2 << 20, MIN_BYTES = (size_t)4 << 20;
+  char* pinned = nullptr;  // [LANES][CHUNKS][CHUNK], allocated on first use
+  cudaEvent_t ev[LANES][CHUNKS] = {};
+  bool used[LANES][CHUNKS] = {};
+  struct Job { void* dst; const void* src; size_t bytes; };
+  static bool pageable(const void* p);  // plain host memory (neither registered / pinned nor device)
+  int init();
+  void destroy();
+  int lane_copy(int lane, void* dst, const void* src, size_t bytes, cudaStream_t st);
+  // lanes first_lane .. LANES-1 each take their slice of every job; on the calling thread (blocking) ...
+  int copy(const std::vector<Job>& jobs, cudaStream_t st, int device);
+  // ... or on background threads of their own: join() them before relying on the stream
+  void start(const std::vector<Job>& jobs, cudaStream_t st, int device, std::vector<std::thread>& threads, int* rc);
+};
+
 // Everything the solver keeps on the device for one problem.
 struct Problem {
   int mode = 2;
@@ -80,6 +102,7 @@ struct Problem {
   int split_cams = -1;            // first internal camera of the second chain (two-ended order) or -1
   int tail_cams = -1;             // first internal camera of the tail (cameras coupled to both chains) or -1
   double* cam_io = nullptr;       // [n_cams][9] staging in the caller's camera order (upload / download / taps)
+  HostStager stager;                   // pageable uploads (survives release())
   cudaStream_t copy_stream = nullptr;  // upload of the observations' coordinates and the points beside the index build (survives release())
   cudaEvent_t ev_copy_go = nullptr, ev_copy_done = nullptr;
   // The last ordering decision (survives release()): the per-keyframe calls of a scan and repeated solves mostly bring
@@ -339,11 +362,15 @@ struct PtrScratch {
   size_t cap = 0;
   unsigned long long* uniq_host = nullptr;  // pinned [uniq_cap]
   size_t uniq_cap = 0;
+  double* pts_host = nullptr;               // pinned [pts_cap]: the distinct points, packed, on their way to / from the device
+  size_t pts_cap = 0;
   void destroy();
 };
 // d_pt_idx_out: device array [n] of compact ids (valid until the next call), ids in ascending pointer order;
-// uniq_out: the distinct pointers by id.  HSFM_BA_ERR_ARG when a pointer is NULL.
-int dedupe_pointers(PtrScratch& W, int64_t n, double* const* host_ptrs, int** d_pt_idx_out, std::vector<double*>& uniq_out, cudaStream_t s);
+// uniq_out [n_uniq_out]: the distinct pointers by id (pinned mirror, valid until the next call); W.pts_host is sized for
+// them.  HSFM_BA_ERR_ARG when a pointer is NULL.
+int dedupe_pointers(PtrScratch& W, int64_t n, double* const* host_ptrs, int** d_pt_idx_out, double* const** uniq_out, int64_t* n_uniq_out,
+                    cudaStream_t s, HostStager* stager = nullptr);
 
 struct Ctx {
   int device = 0;
