@@ -1344,11 +1344,24 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 // the flag arrives only the vector load and a short multiply-add tree are left on the critical path.
 // Row form: thread t owns row t>>1, columns (t&1)*64 .. +63 (32 x 16-byte loads).  Rows >= nrows read as zero.
 struct RowFrag { double2 v[32]; };
+// 32-byte loads (whole sectors) that do not allocate in L1: a CTA has 8192 of them in flight for one block, and with the
+// L11^-1 block in shared memory the L1 that is left cannot track that many lines (the sweep time follows the L1 size)
+__device__ __forceinline__ void ld_sector(const double* p, double2& a, double2& b) {
+  asm volatile("ld.global.L1::no_allocate.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(a.x), "=d"(a.y), "=d"(b.x), "=d"(b.y) : "l"(p));
+}
 __device__ __forceinline__ void row_fetch(RowFrag& f, const double* __restrict__ M, size_t ld, int nrows, int tid) {
   const int r = tid >> 1, h = tid & 1;
-  const double2* p = reinterpret_cast<const double2*>(M + (size_t)r * ld + h * 64);
+  const double* p = M + (size_t)r * ld + h * 64;
+  if (r < nrows && !(ld & 3)) {  // rows 32-byte aligned (n a multiple of 4)
 #pragma unroll
-  for (int q = 0; q < 32; ++q) f.v[q] = (r < nrows) ? __ldg(p + q) : make_double2(0.0, 0.0);
+    for (int q = 0; q < 16; ++q) ld_sector(p + 4 * q, f.v[2 * q], f.v[2 * q + 1]);
+  } else if (r < nrows) {
+#pragma unroll
+    for (int q = 0; q < 32; ++q) f.v[q] = __ldg(reinterpret_cast<const double2*>(p) + q);
+  } else {
+#pragma unroll
+    for (int q = 0; q < 32; ++q) f.v[q] = make_double2(0.0, 0.0);
+  }
 }
 __device__ __forceinline__ double row_dot(const RowFrag& f, const double* __restrict__ sv, int tid) {  // valid on even threads
   const int h = tid & 1;
@@ -1362,22 +1375,31 @@ __device__ __forceinline__ double row_dot(const RowFrag& f, const double* __rest
   s += __shfl_xor_sync(0xffffffffu, s, 1);
   return s;
 }
-// Column form: thread t owns column t&127, rows (t>>7)*64 .. +63.
-struct ColFrag { double v[64]; };
+// Column form: thread t owns the column pair 2 (t & 63), 2 (t & 63) + 1 and the rows (t >> 6) * 32 .. +31: 32 loads of
+// 16 bytes, a warp's load one contiguous 512-byte piece of a row (whole sectors, nothing for L1 to keep).
+struct ColFrag { double2 v[32]; };
 __device__ __forceinline__ void col_fetch(ColFrag& f, const double* __restrict__ M, size_t ld, int nrows, int ncols, int tid) {
-  const int c = tid & (NB - 1), r0 = (tid >> 7) * 64;
+  const int c = 2 * (tid & 63), r0 = (tid >> 6) * 32;
+  const double* p = M + (size_t)r0 * ld + c;
 #pragma unroll
-  for (int q = 0; q < 64; ++q) {
-    const int r = r0 + q;
-    f.v[q] = (r < nrows && c < ncols) ? __ldg(M + (size_t)r * ld + c) : 0.0;
+  for (int q = 0; q < 32; ++q) {
+    double2 v = make_double2(0.0, 0.0);
+    if (r0 + q < nrows && c < ncols) {  // ncols is even (6 per camera): a pair is in or out as a whole
+      asm volatile("ld.global.L1::no_allocate.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p + (size_t)q * ld));
+    }
+    f.v[q] = v;
   }
 }
-__device__ __forceinline__ double col_dot(const ColFrag& f, const double* __restrict__ sv, int tid) {  // partial sum of this half
-  const int r0 = (tid >> 7) * 64;
-  double a[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+__device__ __forceinline__ double2 col_dot(const ColFrag& f, const double* __restrict__ sv, int tid) {  // partial sums of this quarter
+  const int r0 = (tid >> 6) * 32;
+  double ax[4] = {0.0, 0.0, 0.0, 0.0}, ay[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
-  for (int q = 0; q < 64; ++q) a[q & 7] = fma(f.v[q], sv[r0 + q], a[q & 7]);
-  return ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
+  for (int q = 0; q < 32; ++q) {
+    const double s = sv[r0 + q];
+    ax[q & 3] = fma(f.v[q].x, s, ax[q & 3]);
+    ay[q & 3] = fma(f.v[q].y, s, ay[q & 3]);
+  }
+  return make_double2((ax[0] + ax[1]) + (ax[2] + ax[3]), (ay[0] + ay[1]) + (ay[2] + ay[3]));
 }
 
 // L11^-1 block in shared memory (row stride 130 doubles: the 16 rows a warp reads together fall in distinct
@@ -1409,32 +1431,54 @@ __device__ __forceinline__ void publish_value(double* p, double v) {
   // a genuine all-ones result cannot occur (not a canonical NaN); canonical NaNs pass through and end the consumers' waits
   asm volatile("st.relaxed.gpu.global.b64 [%0], %1;" ::"l"(p), "l"(__double_as_longlong(v)) : "memory");
 }
+// Forward sweep, FAN-OUT: the CTA that owns block column k waits for the contributions to its rows (one 128-vector per
+// structural block of block row k, each in a SLOT of its own: slot = position of the block in row_list, or
+// i (i + 1) / 2 + k dense), forms y_k = L11^-1 (b_k - sum of the slots, in list order: the result does not depend on
+// arrival order), and then multiplies y_k into the blocks below its diagonal, the first of them — the one the next
+// column waits for — from registers it filled BEFORE it started waiting.  Every CTA touches the blocks of its own
+// columns only (about as many per column everywhere), where a row-wise gather leaves the loop-closure rows with one
+// block per panel of the whole matrix.
 __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict__ L, int n, const double* __restrict__ LinvAll, double* b,
-                                                        double* w, double* x, const int* __restrict__ row_off,
-                                                        const int* __restrict__ row_list, const int* __restrict__ col_off,
-                                                        const int* __restrict__ col_cnt, const int* __restrict__ col_list) {
+                                                        double* w, double* x, double* slots, const int* __restrict__ row_off,
+                                                        const int* __restrict__ col_off, const int* __restrict__ col_cnt,
+                                                        const int* __restrict__ col_list, const int* __restrict__ col_slot) {
   extern __shared__ __align__(16) double sInv[];  // [128][TI_LD]
   __shared__ double sv[NB];    // vector of the block being folded in (y_k / x_i)
   __shared__ double sacc[NB];  // running right-hand side of the owned block
-  __shared__ double sp[NB];
+  __shared__ __align__(16) double sp[4][NB];  // partial sums of the four row quarters (backward), of the two halves (L11^-T)
   const int tid = threadIdx.x;
   const int P = (n + NB - 1) / NB, G = gridDim.x;
   // ---- forward: L y = b, y -> w ----
-  for (int i = blockIdx.x; i < P; i += G) {
-    const int r0 = i * NB, nr = min(NB, n - r0);
+  for (int k = blockIdx.x; k < P; k += G) {
+    const int r0 = k * NB, nr = min(NB, n - r0);
     __syncthreads();
-    inv_stage(sInv, LinvAll + (size_t)i * NB * NB, tid);
-    if (tid < NB) sacc[tid] = (tid < nr) ? b[r0 + tid] : 0.0;
-    const int q_end = row_off ? __ldg(row_off + i + 1) - 1 : i;  // structural blocks only: the others are exactly zero
-    for (int q = row_off ? __ldg(row_off + i) : 0; q < q_end; ++q) {
-      const int k = row_off ? __ldg(row_list + q) : q;
-      RowFrag f;
-      row_fetch(f, L + (size_t)r0 * n + (size_t)k * NB, (size_t)n, nr, tid);  // issued before the wait
-      __syncthreads();                                                        // sv of the previous block has been consumed
-      if (tid < NB) sv[tid] = poll_value(w + k * NB + tid);                   // k < i: a full block
-      __syncthreads();
-      const double dd = row_dot(f, sv, tid);
-      if (!(tid & 1)) sacc[tid >> 1] -= dd;
+    inv_stage(sInv, LinvAll + (size_t)k * NB * NB, tid);
+    const int c_beg = col_off ? __ldg(col_off + k) : 0, c_cnt = col_off ? __ldg(col_cnt + k) : P - 1 - k;
+    RowFrag f;
+    int i_next = c_cnt > 0 ? (col_off ? __ldg(col_list + c_beg) : k + 1) : -1;
+    if (i_next >= 0) row_fetch(f, L + (size_t)i_next * NB * n + (size_t)k * NB, (size_t)n, min(NB, n - i_next * NB), tid);  // before the wait
+    if (tid < NB) {
+      double a = 0.0;
+      if (tid < nr) {
+        a = b[r0 + tid];
+        const int q_beg = row_off ? __ldg(row_off + k) : k * (k + 1) / 2;
+        const int q_end = row_off ? __ldg(row_off + k + 1) - 1 : q_beg + k;  // the diagonal entry (last) has no slot content
+        const double* sl = slots + (size_t)q_beg * NB + tid;
+        int q = q_beg;
+        for (; q + 4 <= q_end; q += 4, sl += 4 * NB) {  // four loads in flight; the sum keeps list order
+          unsigned long long v0, v1, v2, v3;
+          asm volatile("ld.relaxed.gpu.global.b64 %0, [%1];" : "=l"(v0) : "l"(sl) : "memory");
+          asm volatile("ld.relaxed.gpu.global.b64 %0, [%1];" : "=l"(v1) : "l"(sl + NB) : "memory");
+          asm volatile("ld.relaxed.gpu.global.b64 %0, [%1];" : "=l"(v2) : "l"(sl + 2 * NB) : "memory");
+          asm volatile("ld.relaxed.gpu.global.b64 %0, [%1];" : "=l"(v3) : "l"(sl + 3 * NB) : "memory");
+          a -= (v0 == 0xffffffffffffffffull) ? poll_value(sl) : __longlong_as_double((long long)v0);
+          a -= (v1 == 0xffffffffffffffffull) ? poll_value(sl + NB) : __longlong_as_double((long long)v1);
+          a -= (v2 == 0xffffffffffffffffull) ? poll_value(sl + 2 * NB) : __longlong_as_double((long long)v2);
+          a -= (v3 == 0xffffffffffffffffull) ? poll_value(sl + 3 * NB) : __longlong_as_double((long long)v3);
+        }
+        for (; q < q_end; ++q, sl += NB) a -= poll_value(sl);
+      }
+      sacc[tid] = a;
     }
     cp_async_wait<0>();
     __syncthreads();
@@ -1451,10 +1495,27 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
       }
       double y = (a[0] + a[1]) + (a[2] + a[3]);
       y += __shfl_xor_sync(0xffffffffu, y, 1);
-      if (!h && r < nr) publish_value(w + r0 + r, y);
+      if (!h) {
+        sv[r] = (r < nr) ? y : 0.0;
+        if (r < nr) publish_value(w + r0 + r, y);  // kept for the backward sweep
+      }
+    }
+    __syncthreads();
+    for (int q = 0; q < c_cnt; ++q) {
+      const int i = i_next;
+      const double dd = row_dot(f, sv, tid);
+      if (q + 1 < c_cnt) {  // the next block is on its way while this one goes out
+        i_next = col_off ? __ldg(col_list + c_beg + q + 1) : k + 2 + q;
+        row_fetch(f, L + (size_t)i_next * NB * n + (size_t)k * NB, (size_t)n, min(NB, n - i_next * NB), tid);
+      }
+      const int slot = col_slot ? __ldg(col_slot + c_beg + q) : i * (i + 1) / 2 + k;
+      if (!(tid & 1) && (tid >> 1) < min(NB, n - i * NB)) publish_value(slots + (size_t)slot * NB + (tid >> 1), dd);
     }
   }
   // ---- backward: L^T x = y, x published in its own vector ----
+  // (Measured and dropped: the block whose x arrives last kept in shared memory beside a packed lower triangle of
+  // L11^-1 — 200 KB of shared memory leave ~28 KB of L1, and the register fetches of the other blocks, 16 / 8 bytes per
+  // thread along rows, then miss L1 on every second half of a sector: the sweep took 1.2 ms instead of 0.45 at c4.)
   const int j = tid & (NB - 1), half = tid >> 7;
   for (int kk = P - 1 - (int)blockIdx.x; kk >= 0; kk -= G) {
     const int c0 = kk * NB, kb = min(NB, n - c0);
@@ -1470,10 +1531,10 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
       __syncthreads();
       if (tid < NB) sv[tid] = (tid < nr) ? poll_value(x + r0 + tid) : 0.0;
       __syncthreads();
-      const double acc = col_dot(f, sv, tid);
-      if (half) sp[j] = acc;
+      const double2 acc = col_dot(f, sv, tid);
+      *reinterpret_cast<double2*>(&sp[tid >> 6][2 * (tid & 63)]) = acc;
       __syncthreads();
-      if (!half) sacc[j] -= acc + sp[j];
+      if (tid < NB) sacc[tid] -= (sp[0][tid] + sp[1][tid]) + (sp[2][tid] + sp[3][tid]);
     }
     cp_async_wait<0>();
     __syncthreads();
@@ -1488,9 +1549,9 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
         a[q & 3] = fma(m, sacc[r], a[q & 3]);
       }
       const double acc = (a[0] + a[1]) + (a[2] + a[3]);
-      if (half) sp[j] = acc;
+      if (half) sp[0][j] = acc;
       __syncthreads();
-      if (!half && j < kb) publish_value(x + c0 + j, acc + sp[j]);
+      if (!half && j < kb) publish_value(x + c0 + j, acc + sp[0][j]);
     }
   }
 }
@@ -1546,7 +1607,9 @@ extern "C" int hsfm_ba_debug_chain_ts(unsigned long long* out, int n) {
 #endif
 size_t cholesky_workspace_doubles(int n) {
   const size_t panels = (size_t)((n + NB - 1) / NB);
-  return (panels * NB * NB + panels + 1) & ~(size_t)1;  // one L11^-1 block per panel + 2 x panels int flags of the cooperative triangular solve (even: what follows stays 16-byte aligned)
+  // one L11^-1 block per panel + 2 x panels ints (even: what follows stays 16-byte aligned) + the contribution slots of the
+  // forward triangular solve (one 128-vector per block of the lower block triangle: the dense case)
+  return ((panels * NB * NB + panels + 1) & ~(size_t)1) + panels * (panels + 1) / 2 * NB;
 }
 
 int CholAux::init() {
@@ -1698,7 +1761,16 @@ bool CholPlan::compute(int n_cams, const uint8_t* pattern, int P) {
 
 int CholPlan::build(int n_cams, const uint8_t* pattern, int P, cudaStream_t s) {
   if (!compute(n_cams, pattern, P) || !use) return 0;
-  const size_t need = 2 * list.size() + row_off.size() + row_list.size() + 2 * (size_t)panels + anc_all.size() + map_all.size() + 1;
+  // slot of every structural block (I, K), I in R_K: its position in row I's list (the triangular solve's forward sweep)
+  col_slot.assign(list.size(), 0);
+  for (int K = 0; K < panels; ++K)
+    for (int q = 0; q < cnt[K]; ++q) {
+      const int I = list[(size_t)off[K] + q];
+      const int* rb = row_list.data() + row_off[(size_t)I];
+      const int* re = row_list.data() + row_off[(size_t)I + 1];
+      col_slot[(size_t)off[K] + q] = (int)(std::lower_bound(rb, re, K) - row_list.data());
+    }
+  const size_t need = 3 * list.size() + row_off.size() + row_list.size() + 2 * (size_t)panels + anc_all.size() + map_all.size() + 1;
   if (need > d_cap) {
     if (d_ints) cudaFree(d_ints);
     d_ints = nullptr; d_cap = 0;
@@ -1713,6 +1785,7 @@ int CholPlan::build(int n_cams, const uint8_t* pattern, int P, cudaStream_t s) {
   d_side = d_col_cnt + panels;
   d_anc = d_side + list.size();
   d_map = d_anc + anc_all.size();
+  d_col_slot = d_map + map_all.size();
   if ((size_t)panels + 1 > d_blk_cap) {
     if (d_blk_off) cudaFree(d_blk_off);
     d_blk_off = nullptr; d_blk_cap = 0;
@@ -1728,6 +1801,7 @@ int CholPlan::build(int n_cams, const uint8_t* pattern, int P, cudaStream_t s) {
   if (!side.empty()) HSFM_CUDA(cudaMemcpyAsync(d_side, side.data(), sizeof(int) * side.size(), cudaMemcpyHostToDevice, s));
   if (!anc_all.empty()) HSFM_CUDA(cudaMemcpyAsync(d_anc, anc_all.data(), sizeof(int) * anc_all.size(), cudaMemcpyHostToDevice, s));
   if (!map_all.empty()) HSFM_CUDA(cudaMemcpyAsync(d_map, map_all.data(), sizeof(int) * map_all.size(), cudaMemcpyHostToDevice, s));
+  if (!col_slot.empty()) HSFM_CUDA(cudaMemcpyAsync(d_col_slot, col_slot.data(), sizeof(int) * col_slot.size(), cudaMemcpyHostToDevice, s));
   HSFM_CUDA(cudaStreamSynchronize(s));  // the host vectors may be rebuilt by the next problem
   return 0;
 }
@@ -2095,17 +2169,21 @@ void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream
   const int coop = aux ? aux->coop : 0;
   if (coop) {
     double* x = b + 2 * (size_t)n;  // backward result; copied to b afterwards
-    cudaMemsetAsync(w, 0xff, sizeof(double) * 2 * (size_t)n, s);  // w and x: the sentinel the consumers poll against
+    const bool st = plan && plan->use && plan->n == n;
+    double* slots = ws + (((size_t)panels * NB * NB + panels + 1) & ~(size_t)1);
+    const size_t n_slots = st ? plan->row_list.size() : (size_t)panels * (panels + 1) / 2;
+    // w, x and the slots: the sentinel the consumers poll against
+    cudaMemsetAsync(w, 0xff, sizeof(double) * 2 * (size_t)n, s);
+    cudaMemsetAsync(slots, 0xff, sizeof(double) * n_slots * NB, s);
     const double* LinvAll = ws;
     int nn = n;
-    const bool st = plan && plan->use && plan->n == n;
     const int* row_off = st ? plan->d_row_off : nullptr;
-    const int* row_list = st ? plan->d_row_list : nullptr;
     const int* col_off = st ? plan->d_col_off : nullptr;
     const int* col_cnt = st ? plan->d_col_cnt : nullptr;
     const int* col_list = st ? plan->d_list : nullptr;
-    void* args[] = {(void*)&L,       (void*)&nn,       (void*)&LinvAll, (void*)&b,       (void*)&w,       (void*)&x,
-                    (void*)&row_off, (void*)&row_list, (void*)&col_off, (void*)&col_cnt, (void*)&col_list};
+    const int* col_slot = st ? plan->d_col_slot : nullptr;
+    void* args[] = {(void*)&L,       (void*)&nn,      (void*)&LinvAll, (void*)&b,        (void*)&w,        (void*)&x,
+                    (void*)&slots,   (void*)&row_off, (void*)&col_off, (void*)&col_cnt,  (void*)&col_list, (void*)&col_slot};
     const int grid = std::min(panels, n_sm);
     if (cudaLaunchCooperativeKernel((const void*)trsv_coop_kernel, dim3(grid), dim3(256), args, kTrsvSmem, s) == cudaSuccess) {
       ++*launches;
