@@ -51,7 +51,7 @@ __device__ __forceinline__ double ld_now(const double* p) {
 }
 __device__ __forceinline__ double2 ld_now2(const double* p) {
   double2 v;
-  asm volatile("ld.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
+  asm volatile("ld.global.L1::no_allocate.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
   return v;
 }
 
