@@ -173,6 +173,13 @@ int hsfm_ba_debug_structure(int32_t n_cams, const int32_t* cam_first, int32_t na
                             double* fill, uint8_t* structure);
 int hsfm_ba_debug_schedule(int32_t n_cams, const int32_t* cam_first, int32_t natural, int32_t* seg3);
 
+/* Host-only tap: the reverse Cuthill-McKee camera order the upload falls back to when the cameras do NOT arrive in a
+ * banded order (envelope of the delivered order > 35 % of the triangle; the reference's dense LLT is indifferent to the
+ * order, CTracker.cpp:574).  edges [2 * n_edges]: undirected camera pairs (each once); position [n_cams] receives the
+ * new position of every camera.  On the device the graph is one edge per observation (camera, smallest camera of its
+ * point), and the envelope of the new order is measured before it is adopted. */
+int hsfm_ba_debug_rcm(int32_t n_cams, int64_t n_edges, const int32_t* edges, int32_t* position);
+
 /* Multi-GPU (one process per GPU, observations sharded by point, cameras replicated).
  * unique_id: the 128-byte ncclUniqueId produced by hsfm_ba_comm_unique_id() on rank 0 and
  * broadcast by the host (torch.distributed / MPI / a file).  After this call every solve on

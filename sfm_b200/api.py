@@ -39,6 +39,7 @@ SYMBOLS = {
     "hsfm_ba_set_ordering": (C.c_int, [C.c_void_p, C.c_int]),
     "hsfm_ba_debug_structure": (C.c_int, [C.c_int32, _ip, C.c_int32, _ip, _ip, _dp, C.POINTER(C.c_uint8)]),
     "hsfm_ba_debug_schedule": (C.c_int, [C.c_int32, _ip, C.c_int32, _ip]),
+    "hsfm_ba_debug_rcm": (C.c_int, [C.c_int32, C.c_int64, _ip, _ip]),
     "hsfm_ba_comm_unique_id": (C.c_int, [C.c_void_p]),
     "hsfm_ba_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "hsfm_ba_solve_ptr": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, _dp, _ip, C.c_int32, _dp, _pp, _pp, _pp,
@@ -172,6 +173,16 @@ def debug_structure(cam_first, natural=False, depth=None):
     return dict(new_of_old=perm, panels=int(info[0]), split_a=int(info[1]), split_t0=int(info[2]), structured=bool(info[3]),
                 reordered=bool(info[4]), split_cams=int(info[5]), fill=fill.value, structure=st, segments=segments,
                 critical_panels=int(info[7]))
+
+
+def debug_rcm(n_cams, edges):
+    """Host-only: reverse Cuthill-McKee position of every camera for an undirected edge list [n_edges, 2] (hsfm_ba_debug_rcm)."""
+    e = np.ascontiguousarray(edges, dtype=np.int32).reshape(-1, 2)
+    pos = np.empty(n_cams, dtype=np.int32)
+    rc = load_library().hsfm_ba_debug_rcm(n_cams, e.shape[0], _i(e), _i(pos))
+    if rc:
+        raise BAError(rc, "hsfm_ba_debug_rcm")
+    return pos
 
 
 class Context:

@@ -198,6 +198,21 @@ int hsfm_ba_debug_schedule(int32_t n_cams, const int32_t* cam_first, int32_t nat
   return 0;
 }
 
+int hsfm_ba_debug_rcm(int32_t n_cams, int64_t n_edges, const int32_t* edges, int32_t* position) {
+  if (n_cams <= 0 || n_edges < 0 || (n_edges > 0 && !edges) || !position) return HSFM_BA_ERR_ARG;
+  std::vector<std::pair<int, int>> e;
+  e.reserve((size_t)n_edges);
+  for (int64_t k = 0; k < n_edges; ++k) {
+    const int a = edges[2 * k], b = edges[2 * k + 1];
+    if (a < 0 || b < 0 || a >= n_cams || b >= n_cams) return HSFM_BA_ERR_ARG;
+    if (a != b) e.emplace_back(std::min(a, b), std::max(a, b));
+  }
+  std::vector<int> pos;
+  rcm_order(n_cams, e, pos);
+  for (int c = 0; c < n_cams; ++c) position[c] = pos[(size_t)c];
+  return 0;
+}
+
 int hsfm_ba_comm_unique_id(void* unique_id_128) {
   if (!unique_id_128) return HSFM_BA_ERR_ARG;
   return comm_unique_id(unique_id_128);

@@ -166,6 +166,16 @@ __global__ void cam_first_raw_kernel(int n, const int* __restrict__ pt, const in
   v = __reduce_min_sync(peers, v);
   if (ok && (int)(__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicMin(first + c, v);
 }
+// One edge of the camera graph per observation: (its camera, the smallest camera observing its point) — a star per point,
+// a subgraph of the co-visibility graph with the same connected components and distances within a factor of two, n_obs
+// edges instead of sum of track^2.  Key = (larger << 32 | smaller); an observation of the hub itself gives no edge.
+__global__ void star_edges_kernel(int n, const int* __restrict__ pt, const int* __restrict__ cam, const int* __restrict__ min_cam,
+                                  unsigned long long* __restrict__ keys) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int c = cam[i], m = min_cam[pt[i]];
+  keys[i] = (c == m) ? ~0ull : (((unsigned long long)(unsigned)max(c, m) << 32) | (unsigned)min(c, m));
+}
 __global__ void invert_perm_kernel(int n, const int* __restrict__ old_of_new, int* __restrict__ new_of_old) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k < n) new_of_old[old_of_new[k]] = k;
@@ -391,6 +401,47 @@ int dedupe_pointers(PtrScratch& W, int64_t n64, double* const* host_ptrs, int** 
   return 0;
 }
 
+// Camera graph -> reverse Cuthill-McKee positions (host), for a problem whose cameras do not arrive in a banded order.
+// Transient device scratch (this is the slow path of an upload); indices are validated already.
+static int rcm_positions(int n, const int* pt_in, const int* cam_in, const int* min_cam, int n_cams, int cbits, std::vector<int>& pos, cudaStream_t s) {
+  unsigned long long *keys = nullptr, *sorted = nullptr, *uniq = nullptr;
+  int* d_num = nullptr;
+  void* tmp = nullptr;
+  size_t t_sort = 0, t_uniq = 0;
+  cub::DeviceRadixSort::SortKeys(nullptr, t_sort, keys, sorted, n, 0, 64, s);
+  cub::DeviceSelect::Unique(nullptr, t_uniq, sorted, uniq, d_num, n, s);
+  const size_t n8 = ((size_t)n * 8 + 255) & ~(size_t)255, tb = std::max(t_sort, t_uniq);
+  char* buf = nullptr;
+  if (cudaMalloc(&buf, 3 * n8 + 256 + tb) != cudaSuccess) { cudaGetLastError(); return HSFM_BA_ERR_NOMEM; }
+  keys = (unsigned long long*)buf; sorted = (unsigned long long*)(buf + n8); uniq = (unsigned long long*)(buf + 2 * n8);
+  d_num = (int*)(buf + 3 * n8); tmp = buf + 3 * n8 + 256;
+  int rc = 0, h_num = 0;
+  std::vector<unsigned long long> h_edges;
+  auto run = [&]() -> int {
+    star_edges_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, pt_in, cam_in, min_cam, keys);
+    size_t t1 = tb, t2 = tb;
+    cub::DeviceRadixSort::SortKeys(tmp, t1, keys, sorted, n, 0, 32 + cbits, s);  // the sentinel's high bits are not sorted on: it may land anywhere ...
+    cub::DeviceSelect::Unique(tmp, t2, sorted, uniq, d_num, n, s);
+    HSFM_CUDA(cudaMemcpyAsync(&h_num, d_num, sizeof(int), cudaMemcpyDeviceToHost, s));
+    HSFM_CUDA(cudaStreamSynchronize(s));
+    h_edges.resize((size_t)h_num);
+    HSFM_CUDA(cudaMemcpyAsync(h_edges.data(), uniq, sizeof(unsigned long long) * (size_t)h_num, cudaMemcpyDeviceToHost, s));
+    HSFM_CUDA(cudaStreamSynchronize(s));
+    return 0;
+  };
+  rc = run();
+  cudaFree(buf);
+  if (rc) return rc;
+  std::vector<std::pair<int, int>> edges;
+  edges.reserve(h_edges.size());
+  for (unsigned long long k : h_edges) {
+    if (k == ~0ull) continue;  // ... and is dropped here
+    edges.emplace_back((int)(unsigned)(k & 0xffffffffu), (int)(unsigned)(k >> 32));
+  }
+  rcm_order(n_cams, edges, pos);
+  return 0;
+}
+
 int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, const int32_t* cam_idx, const int32_t* pt_idx,
                   int32_t n_cams, const double* K9, const double* dist, const double* cam_rt, int64_t n_pts64, const double* pts,
                   Comm& comm, cudaStream_t s, double* setup_ms, double* h2d_ms, bool natural_order) {
@@ -410,7 +461,7 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     int* nullk = nullptr;
     cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp, nullk, nullk, nullk, nullk, std::max({n, n_pts, 1}), 0, 32, s);
     t2 = sort_tmp;
-    const size_t need = 368 * no + 360 * np + 2600 * nc + 1400 * (no / 128 + nc + np / 256 + 8) + 2 * t2 + ((size_t)1 << 20);
+    const size_t need = 376 * no + 360 * np + 2600 * nc + 1400 * (no / 128 + nc + np / 256 + 8) + 2 * t2 + ((size_t)1 << 20);
     int rc = P.arena_reserve(need);
     if (rc) return rc;
   }
@@ -506,8 +557,51 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     t_stage = t;
   };
 
+  // ---- cameras that do not arrive in a banded order: reverse Cuthill-McKee first (one GPU; the ranks of a multi-GPU
+  //      solve would each see their shard's graph only) ----
+  // "Base order" below = the caller's order, or the RCM order when that is adopted; the envelope (P.cam_first) and the
+  // structure code work in base order, P.h_cam_new_of_old maps the CALLER's cameras to internal ones.
+  std::vector<int> base_of_caller;  // empty: base order = caller order
+  static const bool no_rcm = getenv("HSFM_NO_RCM") != nullptr;  // experiment knob
+  if (want_structure && !natural_order && !no_rcm && comm.n_ranks == 1 && n_cams >= 256) {
+    auto env_fill = [&](const std::vector<int>& first) {
+      double env = 0.0;
+      for (int c = 0; c < n_cams; ++c) env += c - std::min(first[(size_t)c], c) + 1;
+      return env / (0.5 * (double)n_cams * (n_cams + 1));
+    };
+    const double fill_caller = env_fill(P.cam_first);
+    if (fill_caller > 0.35) {
+      Problem::OrderCache& oc = P.order_cache;
+      if (!(oc.rcm_valid && oc.first_caller == P.cam_first)) {
+        int cb = 1; while ((1ll << cb) < std::max(2, (int)n_cams) + 1) ++cb;
+        const int rc = rcm_positions(n, pt_in, cam_in, min_cam, n_cams, cb, oc.base_of_caller, s);
+        if (rc) return rc;
+        oc.first_caller = P.cam_first;
+        oc.rcm_valid = true;
+      }
+      // the envelope in RCM order, measured on the data (a cached permutation stays valid for any graph: it is a permutation)
+      int *d_base, *cam_rcm;
+      ALLOC(d_base, n_cams); ALLOC(cam_rcm, n);
+      HSFM_CUDA(cudaMemcpyAsync(d_base, oc.base_of_caller.data(), sizeof(int) * (size_t)n_cams, cudaMemcpyHostToDevice, s));
+      gather_int_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, cam_in, d_base, cam_rcm);
+      fill_int_kernel<<<cdiv(n_pts, 256), 256, 0, s>>>(n_pts, n_cams, min_cam);
+      min_cam_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, pt_in, cam_rcm, min_cam);
+      iota_kernel<<<cdiv(n_cams, 256), 256, 0, s>>>(n_cams, d_first);
+      cam_first_raw_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, pt_in, cam_rcm, n_cams, n_pts, min_cam, d_first);
+      std::vector<int> first_rcm((size_t)n_cams);
+      HSFM_CUDA(cudaMemcpyAsync(first_rcm.data(), d_first, sizeof(int) * (size_t)n_cams, cudaMemcpyDeviceToHost, s));
+      HSFM_CUDA(cudaStreamSynchronize(s));
+      if (env_fill(first_rcm) < 0.6 * fill_caller) {
+        base_of_caller = oc.base_of_caller;
+        P.cam_first.swap(first_rcm);
+      }
+    }
+  }
+  stamp("camera graph / RCM");
+
   // ---- internal camera order (ba_order.cpp): a band is eliminated from both ends at once ----
   bool reorder = false;
+  P.h_struct_new_of_base.clear();
   if (want_structure && !natural_order) {
     Problem::OrderCache& oc = P.order_cache;
     if (!(oc.valid && oc.first == P.cam_first)) {
@@ -515,8 +609,17 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
       oc.first = P.cam_first;
       oc.valid = true;
     }
-    reorder = oc.reordered;
-    if (reorder) { P.h_cam_new_of_old = oc.new_of_old; P.split_cams = oc.split_cams; P.tail_cams = oc.tail_cams; }
+    if (oc.reordered) { P.h_struct_new_of_base = oc.new_of_old; P.split_cams = oc.split_cams; P.tail_cams = oc.tail_cams; }
+    // caller -> internal: through the base order
+    if (!base_of_caller.empty()) {
+      P.h_cam_new_of_old.resize((size_t)n_cams);
+      for (int c = 0; c < n_cams; ++c)
+        P.h_cam_new_of_old[(size_t)c] = oc.reordered ? oc.new_of_old[(size_t)base_of_caller[(size_t)c]] : base_of_caller[(size_t)c];
+      reorder = true;
+    } else if (oc.reordered) {
+      P.h_cam_new_of_old = oc.new_of_old;
+      reorder = true;
+    }
   }
   if (reorder) {
     int* cam_tmp;

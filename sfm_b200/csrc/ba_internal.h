@@ -6,6 +6,7 @@
 
 #include <string>
 #include <thread>
+#include <utility>
 #include <vector>
 
 #include "../../include/hsfm_ba.h"
@@ -96,7 +97,8 @@ struct Problem {
   int max_tile_cams = 0;  // largest number of distinct cameras in one tile (sizes the shared-memory row staging)
   std::vector<int> cam_first;  // [n_cams] CALLER order: smallest camera sharing a point with camera c (all ranks) — envelope of S
   // internal camera order (ba_order.cpp): null / empty = the caller's order
-  std::vector<int> h_cam_new_of_old;
+  std::vector<int> h_cam_new_of_old;      // caller's camera -> internal camera
+  std::vector<int> h_struct_new_of_base;  // base order (the caller's, or reverse Cuthill-McKee: what cam_first is in) -> internal; empty = identity
   int* cam_new_of_old = nullptr;  // device [n_cams]
   int* cam_old_of_new = nullptr;  // device [n_cams]
   int split_cams = -1;            // first internal camera of the second chain (two-ended order) or -1
@@ -110,8 +112,10 @@ struct Problem {
   // order at Venice size) is then skipped.
   struct OrderCache {
     bool valid = false, reordered = false;
-    std::vector<int> first, new_of_old;
+    std::vector<int> first, new_of_old;  // envelope in base order -> base position to internal position
     int split_cams = -1, tail_cams = -1;
+    bool rcm_valid = false;
+    std::vector<int> first_caller, base_of_caller;  // envelope in the caller's order -> reverse Cuthill-McKee position of every camera
   } order_cache;
   Dev d{};
   // Device arena: ONE grow-only allocation per context that every per-problem buffer is carved from, so the
@@ -318,6 +322,7 @@ void panel_segments(int P, const std::vector<int>& off, const std::vector<int>& 
 int critical_panels(const std::vector<PanelSeg>& segs);
 bool choose_camera_order(int n_cams, const int* first, std::vector<int>& new_of_old, int* split_cams, int* tail_cams = nullptr,
                          int force_depth = -1);
+void rcm_order(int n, const std::vector<std::pair<int, int>>& edges, std::vector<int>& pos_of_cam);  // reverse Cuthill-McKee
 void block_pattern_from_envelope(int n_cams, const int* first, const int* new_of_old, std::vector<uint8_t>& pattern, int* panels);
 void symbolic_block_factor(int P, std::vector<uint8_t>& pattern);
 size_t cholesky_workspace_doubles(int n);  // L11^-1 blocks (one 128×128 per panel) + flags of the cooperative triangular solve

@@ -266,3 +266,58 @@ void symbolic_block_factor(int P, std::vector<uint8_t>& pattern) {
 }
 
 }  // namespace hsfm
+
+namespace hsfm {
+
+// Reverse Cuthill-McKee on the camera graph (undirected edges a < b, each once; any order): new position of every
+// camera.  For a camera graph that is a band in SOME order (a scan whose keyframes arrive shuffled) this finds such an
+// order again; the envelope of the result is then measured, not assumed.  Components are ordered one after the other,
+// each from a pseudo-peripheral start node (two rounds of breadth-first search from a minimum-degree node).
+void rcm_order(int n, const std::vector<std::pair<int, int>>& edges, std::vector<int>& pos_of_cam) {
+  std::vector<int> deg((size_t)n, 0), off((size_t)n + 1, 0);
+  for (const auto& e : edges) { ++deg[(size_t)e.first]; ++deg[(size_t)e.second]; }
+  for (int c = 0; c < n; ++c) off[(size_t)c + 1] = off[(size_t)c] + deg[(size_t)c];
+  std::vector<int> adj((size_t)off[(size_t)n]), fillp(off.begin(), off.end() - 1);
+  for (const auto& e : edges) { adj[(size_t)fillp[(size_t)e.first]++] = e.second; adj[(size_t)fillp[(size_t)e.second]++] = e.first; }
+  for (int c = 0; c < n; ++c)  // neighbours by ascending degree (ties: index): the Cuthill-McKee visiting order
+    std::sort(adj.begin() + off[(size_t)c], adj.begin() + off[(size_t)c + 1],
+              [&](int a, int b) { return deg[(size_t)a] != deg[(size_t)b] ? deg[(size_t)a] < deg[(size_t)b] : a < b; });
+  std::vector<int> order, level((size_t)n, -1), queue;
+  order.reserve((size_t)n);
+  std::vector<char> done((size_t)n, 0);
+  // breadth-first search over the not-yet-ordered part from `start`; returns the last node of the deepest level with the smallest degree
+  auto bfs = [&](int start, std::vector<int>& out) {
+    out.clear();
+    out.push_back(start);
+    level[(size_t)start] = 0;
+    for (size_t h = 0; h < out.size(); ++h) {
+      const int u = out[h];
+      for (int q = off[(size_t)u]; q < off[(size_t)u + 1]; ++q) {
+        const int v = adj[(size_t)q];
+        if (done[(size_t)v] || level[(size_t)v] >= 0) continue;
+        level[(size_t)v] = level[(size_t)u] + 1;
+        out.push_back(v);
+      }
+    }
+    const int deepest = level[(size_t)out.back()];
+    int best = out.back();
+    for (size_t h = out.size(); h-- > 0 && level[(size_t)out[h]] == deepest;)
+      if (deg[(size_t)out[h]] < deg[(size_t)best]) best = out[h];
+    for (int u : out) level[(size_t)u] = -1;
+    return best;
+  };
+  std::vector<int> by_degree((size_t)n);
+  std::iota(by_degree.begin(), by_degree.end(), 0);
+  std::stable_sort(by_degree.begin(), by_degree.end(), [&](int a, int b) { return deg[(size_t)a] < deg[(size_t)b]; });
+  for (int seed : by_degree) {
+    if (done[(size_t)seed]) continue;
+    int start = seed;
+    for (int round = 0; round < 2; ++round) start = bfs(start, queue);  // towards one end of the component
+    bfs(start, queue);                                                   // the Cuthill-McKee order of the component
+    for (int u : queue) { done[(size_t)u] = 1; order.push_back(u); }
+  }
+  pos_of_cam.assign((size_t)n, 0);
+  for (int k = 0; k < n; ++k) pos_of_cam[(size_t)order[(size_t)(n - 1 - k)]] = k;  // reversed
+}
+
+}  // namespace hsfm

@@ -184,15 +184,15 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
       int rc;
       if ((int)P.cam_first.size() == P.n_cams && P.n_cams > 0) {
         // the same camera graph in the same internal order as the plan was built from: nothing to do
-        if (ctx.chol_plan.version > 0 && ctx.chol_plan.n == n6 && ctx.plan_first == P.cam_first && ctx.plan_new_of_old == P.h_cam_new_of_old) {
+        if (ctx.chol_plan.version > 0 && ctx.chol_plan.n == n6 && ctx.plan_first == P.cam_first && ctx.plan_new_of_old == P.h_struct_new_of_base) {
           ctx.chol_plan_valid = true;
           return 0;
         }
         std::vector<uint8_t> pattern;
         int panels = 0;
-        block_pattern_from_envelope(P.n_cams, P.cam_first.data(), P.h_cam_new_of_old.empty() ? nullptr : P.h_cam_new_of_old.data(), pattern, &panels);
+        block_pattern_from_envelope(P.n_cams, P.cam_first.data(), P.h_struct_new_of_base.empty() ? nullptr : P.h_struct_new_of_base.data(), pattern, &panels);
         rc = ctx.chol_plan.build(P.n_cams, pattern.data(), panels, s);
-        ctx.plan_first = P.cam_first; ctx.plan_new_of_old = P.h_cam_new_of_old;
+        ctx.plan_first = P.cam_first; ctx.plan_new_of_old = P.h_struct_new_of_base;
       } else {
         ctx.plan_first.clear(); ctx.plan_new_of_old.clear();
         rc = ctx.chol_plan.build(P.n_cams, nullptr, 0, s);

@@ -299,6 +299,18 @@ def shard_by_point(prob: Problem, n_ranks: int):
     return shards
 
 
+def shuffle_cameras(prob: Problem, seed: int):
+    """The same problem with its cameras renumbered at random (a scan whose keyframes arrive in no particular order:
+    the camera graph is still a band in SOME order, but not in the delivered one).  Returns (Problem, new_of_old)."""
+    rng = np.random.default_rng(seed)
+    new_of_old = rng.permutation(prob.n_cams).astype(np.int32)
+    old_of_new = np.empty_like(new_of_old)
+    old_of_new[new_of_old] = np.arange(prob.n_cams, dtype=np.int32)
+    take = lambda a: None if a is None else np.ascontiguousarray(a[old_of_new])  # noqa: E731
+    return dataclasses.replace(prob, cam_idx=np.ascontiguousarray(new_of_old[prob.cam_idx]), K=take(prob.K), cam=take(prob.cam),
+                               cam_true=take(prob.cam_true), dist=take(prob.dist), name=prob.name + "-shuffled"), new_of_old
+
+
 def keyframe_stream(prob: Problem, k0: int):
     """Replay ``prob`` as a scan (what CSfM::mapping produces keyframe by keyframe, CSfM.cpp:252-259): a start problem
     over the first ``k0`` keyframes and one append per further keyframe.  A map point enters the stream when its second

@@ -48,6 +48,46 @@ def test_two_ended_camera_order_equals_callers_order(ctx, closure):
     assert np.abs(rms - want).max() <= 1e-9
 
 
+@pytest.mark.parametrize("closure", [False, True], ids=["band", "band+loop-closure"])
+def test_shuffled_cameras_get_a_banded_order_back(ctx, closure):
+    """The reference's DENSE_SCHUR does not care in which order the keyframes are numbered (CTracker.cpp:574).  A scan whose
+    cameras arrive shuffled has a full envelope in the delivered order; the upload then finds a banded order again
+    (reverse Cuthill-McKee on the camera graph, ba_order.cpp: rcm_order) and the structured factorisation runs as for the
+    ordered scan: same solver, same LM trajectory, results in the caller's (shuffled) numbering."""
+    p = _trajectory(n_cams=640, n_pts=9000, closure=closure)
+    q, new_of_old = synth.shuffle_cameras(p, seed=3)
+    o = api.default_options(linear_solver=api.LINEAR_DENSE_SCHUR, max_num_iterations=6)
+    cp_, pp_, sp = ctx.solve_packed(p, opts=o)
+    cq, pq, sq = ctx.solve_packed(q, opts=o)
+    assert sq["cameras_reordered"] == 1
+    if not closure:
+        # the automatic choice beyond dense_max_cams (Cholesky only where the structure is sparse) is the same for both
+        auto = api.default_options(linear_solver=api.LINEAR_AUTO, max_num_iterations=1, dense_max_cams=100)
+        assert ctx.solve_packed(p, opts=auto)[2]["linear_solver_used"] == ctx.solve_packed(q, opts=auto)[2]["linear_solver_used"] == api.LINEAR_DENSE_SCHUR
+    # the band is found again: the critical path and the work are those of the ordered scan, within a small factor
+    assert sq["chol_critical_panels"] <= 0.8 * sq["chol_panels"]
+    assert sq["chol_flops"] <= 2.0 * sp["chol_flops"]
+    assert sq["num_iterations"] == sp["num_iterations"] and sq["num_successful_steps"] == sp["num_successful_steps"]
+    for a, b in zip(sq["trace"], sp["trace"]):
+        assert a["cost"] == pytest.approx(b["cost"], rel=1e-9) and a["step_is_successful"] == b["step_is_successful"]
+    assert np.abs(cq[new_of_old] - cp_).max() < 1e-7 and np.abs(pq - pp_).max() < 1e-7
+    # per-keyframe statistics in the caller's numbering
+    ctx.upload(q)
+    ctx.solve_resident(o)
+    rms_q, _ = ctx.frame_stats()
+    ctx.upload(p)
+    ctx.solve_resident(o)
+    rms_p, _ = ctx.frame_stats()
+    assert np.abs(rms_q[new_of_old] - rms_p).max() <= 1e-8
+    # without the reordering (experiment: the caller's order kept) the same problem has a dense structure
+    try:
+        ctx.set_ordering(1)
+        sn = ctx.solve_packed(q, opts=api.default_options(linear_solver=api.LINEAR_DENSE_SCHUR, max_num_iterations=1))[2]
+    finally:
+        ctx.set_ordering(0)
+    assert sn["chol_flops"] > 3.0 * sq["chol_flops"]
+
+
 def _table(name):
     path = os.path.join(os.path.dirname(__file__), "golden", "lm_fullsize.npz")
     g = np.load(path)

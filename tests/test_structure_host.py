@@ -181,3 +181,26 @@ def test_small_or_dense_graphs_keep_the_callers_order():
     assert not api.debug_structure(band_first(100, 5, 10, 1))["reordered"]          # too few cameras for two chains
     d = api.debug_structure(np.zeros(300, np.int32))
     assert not d["structured"] and d["fill"] == 1.0
+
+
+@pytest.mark.parametrize("case", ["band", "band+closures", "two components"])
+def test_reverse_cuthill_mckee_finds_the_band_of_a_shuffled_scan(case):
+    """Cameras of a scan delivered in random order: rcm_order (ba_order.cpp) numbers them so that the graph is a band again
+    (the fallback of the upload when the delivered order has a full envelope)."""
+    rng = np.random.default_rng(7)
+    n, bw = 900, 25
+    edges = [(c, d) for c in range(n) for d in range(max(0, c - int(rng.integers(5, bw))), c)]
+    if case == "band+closures":
+        edges += [(800, 3), (801, 4), (450, 20)]
+    if case == "two components":
+        edges = [(a, b) for a, b in edges if not (a >= 500 > b)]
+    shuffle = rng.permutation(n)
+    e = shuffle[np.array(edges)]
+    pos = api.debug_rcm(n, e)
+    assert sorted(pos) == list(range(n))
+    width = np.abs(pos[e[:, 0]] - pos[e[:, 1]])
+    assert np.abs(shuffle[np.array(edges)][:, 0] - shuffle[np.array(edges)][:, 1]).mean() > 200  # delivered order: no band at all
+    if case == "band+closures":
+        assert np.sort(width)[:-3].max() <= 3 * bw  # the closures stay long edges; the rest is a band
+    else:
+        assert width.max() <= 2 * bw
