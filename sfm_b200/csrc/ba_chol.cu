@@ -669,20 +669,22 @@ __global__ void __launch_bounds__(256, 2) chol_diag_kernel(double* __restrict__ 
 //   col_first <  0 : bulk — column blocks c0 = -col_first (even, >= 2) and beyond, lower tiles only
 // ---------------------------------------------------------------------------------------------
 constexpr int TN = 64;  // tile columns
+// TM = tile rows: 128 (8 warps as 4 x 2 of 32 x 32, two CTAs per SM) or 64 (4 warps as 2 x 2, three CTAs per SM: the
+// structured factorisation's launches are single partial waves, and half-size tiles spread them evenly over the SMs)
+template <int TM>
 struct GemmSmem {
-  double a[2][NB][LDS_];
+  double a[2][TM][LDS_];
   double b[2][TN][LDS_];
 };
-constexpr int kGemmSmem = (int)sizeof(GemmSmem);
+constexpr int kGemmSmem = (int)sizeof(GemmSmem<NB>), kGemmSmemHalf = (int)sizeof(GemmSmem<64>);
 
-constexpr int SY_THREADS = 256;  // trailing-update CTA: 8 warps as 4 x 2, 32 x 32 each
-template <int ROWS>
+template <int ROWS, int THREADS>
 __device__ __forceinline__ void load_tile_async(double (*dst)[LDS_], const double* __restrict__ src, int ld, int row0, int rows_valid,
                                                 int col0) {
   // ROWS rows × 32 doubles = ROWS*16 chunks of 16 B over the CTA's threads
 #pragma unroll
-  for (int q = 0; q < ROWS * 16 / SY_THREADS; ++q) {
-    const int e = threadIdx.x + SY_THREADS * q;
+  for (int q = 0; q < ROWS * 16 / THREADS; ++q) {
+    const int e = threadIdx.x + THREADS * q;
     const int row = e >> 4, ch = e & 15;
     double* d = &dst[row][ch * 2];
     if (row < rows_valid) cp_async16(d, src + (size_t)(row0 + row) * ld + col0 + ch * 2);
@@ -696,18 +698,20 @@ struct SyrkTile { int ri, ni, rj, nj, oi, oj; };  // operand rows in S; oi, oj: 
 // column b holds the rows a = b .. cnt-1.  A launch with fewer tiles than all pairs covers the first block columns
 // only (the two-chain schedule defers the others); col_first == -2 skips pair (0, 0), which the chain stream
 // updates itself.
+template <int TM>
 __device__ __forceinline__ SyrkTile syrk_tile(int t, int n, int base, int row_first, int col_first, const int* __restrict__ rb_list, int cnt,
                                               const int* __restrict__ side_list) {
   SyrkTile T;
   if (rb_list) {
     const int half = t & 1;
-    int pp = (t >> 1) + (col_first == -2 ? 1 : 0);
+    const int rh = TM == NB ? 0 : (t >> 1) & 1;  // row half of the pair's block (64-row tiles: four tiles per pair)
+    int pp = (t >> (TM == NB ? 1 : 2)) + (col_first == -2 ? 1 : 0);
     int b = 0, rem = cnt;
     while (pp >= rem) { pp -= rem; --rem; ++b; }
     const int a = b + pp;
-    T.ri = __ldg(rb_list + a) * NB; T.ni = min(NB, n - T.ri);
-    T.rj = __ldg(rb_list + b) * NB + half * TN; T.nj = min(TN, n - T.rj);
-    T.oi = side_list ? __ldg(side_list + a) * NB : T.ri;
+    T.ri = __ldg(rb_list + a) * NB + rh * TM; T.ni = max(0, min(TM, n - T.ri));
+    T.rj = __ldg(rb_list + b) * NB + half * TN; T.nj = max(0, min(TN, n - T.rj));
+    T.oi = side_list ? __ldg(side_list + a) * NB + rh * TM : T.ri;
     T.oj = side_list ? __ldg(side_list + b) * NB + half * TN : T.rj;
     return T;
   }
@@ -729,17 +733,19 @@ __device__ __forceinline__ SyrkTile syrk_tile(int t, int n, int base, int row_fi
   return T;
 }
 
-__global__ void __launch_bounds__(SY_THREADS, 2) chol_syrk_kernel(double* __restrict__ S, int n, int k0, int row_first, int col_first, int n_tiles,
+template <int TM>
+__global__ void __launch_bounds__(2 * TM, TM == NB ? 2 : 3) chol_syrk_kernel(double* __restrict__ S, int n, int k0, int row_first, int col_first, int n_tiles,
                                                            int stagger, const int* __restrict__ fail, const int* __restrict__ rb_list, int rb_cnt,
                                                            double* __restrict__ Cside, int ldc_side, const int* __restrict__ side_list) {
   extern __shared__ __align__(16) unsigned char gsm_raw[];
-  GemmSmem& sm = *reinterpret_cast<GemmSmem*>(gsm_raw);
+  constexpr int THREADS = 2 * TM;
+  GemmSmem<TM>& sm = *reinterpret_cast<GemmSmem<TM>*>(gsm_raw);
   int t = blockIdx.x;
   if (t >= n_tiles) return;
   const int failed = *fail;
   const int base = k0 + NB;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int wr = warp >> 1, wc = warp & 1;  // 4 × 2 warps, 32 × 32 each
+  const int wr = warp >> 1, wc = warp & 1;  // (TM / 32) × 2 warps, 32 × 32 each
   const int fr = lane >> 2, fk = lane & 3;
 
   // All CTAs of a launch start together; left alone, the two CTAs of an SM (and the whole GPU) stay in
@@ -750,9 +756,9 @@ __global__ void __launch_bounds__(SY_THREADS, 2) chol_syrk_kernel(double* __rest
     const long long t0 = clock64();
     while (clock64() - t0 < 16000) { }
   }
-  SyrkTile cur = syrk_tile(t, n, base, row_first, col_first, rb_list, rb_cnt, side_list);
-  load_tile_async<NB>(sm.a[0], S, n, cur.ri, cur.ni, k0);
-  load_tile_async<TN>(sm.b[0], S, n, cur.rj, cur.nj, k0);
+  SyrkTile cur = syrk_tile<TM>(t, n, base, row_first, col_first, rb_list, rb_cnt, side_list);
+  load_tile_async<TM, THREADS>(sm.a[0], S, n, cur.ri, cur.ni, k0);
+  load_tile_async<TN, THREADS>(sm.b[0], S, n, cur.rj, cur.nj, k0);
   cp_async_commit();
   if (failed) { cp_async_wait<0>(); return; }
   int stage = 0;
@@ -761,7 +767,7 @@ __global__ void __launch_bounds__(SY_THREADS, 2) chol_syrk_kernel(double* __rest
     const int t_next = t + gridDim.x;
     const bool has_next = t_next < n_tiles;
     SyrkTile nxt = cur;
-    if (has_next) nxt = syrk_tile(t_next, n, base, row_first, col_first, rb_list, rb_cnt, side_list);
+    if (has_next) nxt = syrk_tile<TM>(t_next, n, base, row_first, col_first, rb_list, rb_cnt, side_list);
     // C → accumulators.  Full tiles take an unpredicated path: one row pointer per 8-row group, the four
     // column tiles at immediate offsets, every load straight into its accumulator pair — nothing recycles a
     // register, so all 32 loads are in flight at once.
@@ -771,7 +777,7 @@ __global__ void __launch_bounds__(SY_THREADS, 2) chol_syrk_kernel(double* __rest
     const size_t ldc = Cside ? (size_t)ldc_side : (size_t)n;
     double* const crow = cbase + (size_t)(cur.oi + wr * 32 + fr) * ldc + cur.oj + wc * 32 + 2 * fk;
     const size_t rstep = 8 * ldc;
-    const bool full = (cur.ni == NB) && (cur.nj == TN);
+    const bool full = (cur.ni == TM) && (cur.nj == TN);
 #ifdef HSFM_SYRK_NOLOAD
     if (full) {
 #pragma unroll
@@ -806,8 +812,8 @@ __global__ void __launch_bounds__(SY_THREADS, 2) chol_syrk_kernel(double* __rest
     if (has_next) {
       // next tile's C → L2: 128 rows × 512 B = 4 lines per row, one line per thread per pass
 #pragma unroll
-      for (int q = 0; q < 512 / SY_THREADS; ++q) {
-        const int e = threadIdx.x + SY_THREADS * q;
+      for (int q = 0; q < 4 * TM / THREADS; ++q) {
+        const int e = threadIdx.x + THREADS * q;
         const int row = e >> 2, seg = e & 3;
         if (row < nxt.ni && seg * 16 < nxt.nj)
           asm volatile("prefetch.global.L2 [%0];" ::"l"(cbase + (size_t)(nxt.oi + row) * ldc + nxt.oj + seg * 16));
@@ -816,11 +822,11 @@ __global__ void __launch_bounds__(SY_THREADS, 2) chol_syrk_kernel(double* __rest
 #pragma unroll 1
     for (int ch = 0; ch < NB / KC; ++ch) {
       if (ch + 1 < NB / KC) {
-        load_tile_async<NB>(sm.a[stage ^ 1], S, n, cur.ri, cur.ni, k0 + (ch + 1) * KC);
-        load_tile_async<TN>(sm.b[stage ^ 1], S, n, cur.rj, cur.nj, k0 + (ch + 1) * KC);
+        load_tile_async<TM, THREADS>(sm.a[stage ^ 1], S, n, cur.ri, cur.ni, k0 + (ch + 1) * KC);
+        load_tile_async<TN, THREADS>(sm.b[stage ^ 1], S, n, cur.rj, cur.nj, k0 + (ch + 1) * KC);
       } else if (has_next) {
-        load_tile_async<NB>(sm.a[stage ^ 1], S, n, nxt.ri, nxt.ni, k0);
-        load_tile_async<TN>(sm.b[stage ^ 1], S, n, nxt.rj, nxt.nj, k0);
+        load_tile_async<TM, THREADS>(sm.a[stage ^ 1], S, n, nxt.ri, nxt.ni, k0);
+        load_tile_async<TN, THREADS>(sm.b[stage ^ 1], S, n, nxt.rj, nxt.nj, k0);
       }
       cp_async_commit();
       cp_async_wait<1>();
@@ -1623,7 +1629,8 @@ int CholAux::init() {
   if (getenv("HSFM_TRSV_LAUNCHES")) coop = 0;
   HSFM_CUDA(cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDiagSmem));
   HSFM_CUDA(cudaFuncSetAttribute(chol_trsm_strip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_MAXROWS * TS_LD * (int)sizeof(double)));
-  HSFM_CUDA(cudaFuncSetAttribute(chol_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+  HSFM_CUDA(cudaFuncSetAttribute(chol_syrk_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+  HSFM_CUDA(cudaFuncSetAttribute(chol_syrk_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemHalf));
   HSFM_CUDA(cudaFuncSetAttribute(chol_syrk_col_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrkLatSmem));
   HSFM_CUDA(cudaFuncSetAttribute(chol_syrk_col_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrkLatSmem / 2));
   HSFM_CUDA(cudaFuncSetAttribute(chol_chain_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kChainTileSmem));
@@ -1874,7 +1881,9 @@ static void run_chain(double* S, int n, double* ws, int* fail_flag, const ChainS
   };
   auto syrk = [&](cudaStream_t st, int k0, int col_first, int tiles, const int* list, int cnt, double* C, int ldc, const int* side_list) {
     if (tiles <= 0) return;
-    chol_syrk_kernel<<<min(tiles, cap_syrk), SY_THREADS, kGemmSmem, st>>>(S, n, k0, 0, col_first, tiles, 0, fail_flag, list, cnt, C, ldc, side_list);
+    static const bool big_tiles = getenv("HSFM_SYRK_BIG_TILES") != nullptr;  // experiment knob: 128 x 64 tiles, two CTAs per SM
+    if (big_tiles) chol_syrk_kernel<NB><<<min(tiles, cap_syrk), 2 * NB, kGemmSmem, st>>>(S, n, k0, 0, col_first, tiles, 0, fail_flag, list, cnt, C, ldc, side_list);
+    else chol_syrk_kernel<64><<<min(2 * tiles, (3 * cap_syrk) / 2), 128, kGemmSmemHalf, st>>>(S, n, k0, 0, col_first, 2 * tiles, 0, fail_flag, list, cnt, C, ldc, side_list);
     ++*launches;
   };
   // pairs of the panel's rows beyond its own segment -> side matrix, right after the panel solve; off the bulk stream when the
@@ -2140,16 +2149,16 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
       cudaEventRecord(aux->ev_panel, s2);
       if (panel > 0) cudaStreamWaitEvent(s2, aux->ev_rest, 0);  // "ahead k-1": cb 2,3 of the previous step = cb 0,1 of this one
     }
-    chol_syrk_kernel<<<min(2 * rb, 2 * n_sm), SY_THREADS, kGemmSmem, s2>>>(S, n, k0, 0, 0, 2 * rb, 0, fail_flag, nullptr, 0, nullptr, 0, nullptr);
+    chol_syrk_kernel<NB><<<min(2 * rb, 2 * n_sm), 2 * NB, kGemmSmem, s2>>>(S, n, k0, 0, 0, 2 * rb, 0, fail_flag, nullptr, 0, nullptr, 0, nullptr);
     ++*launches;
     if (rb > 1) {
       if (la) cudaStreamWaitEvent(s, aux->ev_panel, 0);
-      chol_syrk_kernel<<<min(2 * (rb - 1), 2 * n_sm), SY_THREADS, kGemmSmem, s>>>(S, n, k0, 1, 2, 2 * (rb - 1), 0, fail_flag, nullptr, 0, nullptr, 0, nullptr);
+      chol_syrk_kernel<NB><<<min(2 * (rb - 1), 2 * n_sm), 2 * NB, kGemmSmem, s>>>(S, n, k0, 1, 2, 2 * (rb - 1), 0, fail_flag, nullptr, 0, nullptr, 0, nullptr);
       ++*launches;
     }
     if (la) cudaEventRecord(aux->ev_rest, s);
     if (rb > 2) {
-      chol_syrk_kernel<<<min((rb - 2) * (rb - 1), bulk_ctas), SY_THREADS, kGemmSmem, s>>>(S, n, k0, 0, -4, (rb - 2) * (rb - 1), 0, fail_flag, nullptr, 0, nullptr, 0, nullptr);
+      chol_syrk_kernel<NB><<<min((rb - 2) * (rb - 1), bulk_ctas), 2 * NB, kGemmSmem, s>>>(S, n, k0, 0, -4, (rb - 2) * (rb - 1), 0, fail_flag, nullptr, 0, nullptr, 0, nullptr);
       ++*launches;
     }
   }
