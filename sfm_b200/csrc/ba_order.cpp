@@ -143,7 +143,7 @@ int critical_panels(const std::vector<PanelSeg>& segs) {
 }
 
 namespace {
-// Estimated time of the structured factorisation in a given camera order.  Segments at the same depth below the root run
+// Estimated time of the structured factorisation + triangular solves in a given camera order.  Segments at the same depth below the root run
 // concurrently; a level costs the larger of its longest chain (38 us per panel step, 20 % more per concurrent chain
 // beyond two: the chains' kernels share SMs and L2 with each other's bulk updates) and the tensor-pipe time of its
 // structural flops (18 TFLOP/s: what the 128-deep trailing updates sustain with several chains in flight).  Constants
@@ -178,7 +178,8 @@ double order_cost(int n_cams, const int* first, const int* new_of_old, int* crit
     const double t_chain = longest * 38e-6 * (1.0 + 0.2 * std::max(0, chains - 2)), t_flops = tiles * 2.0 * NB * NB * NB / 18e12;
     total += std::max(t_chain, t_flops);
   }
-  return total;
+  // the two triangular sweeps follow the same chains: two hand-overs of ~4.2 us per critical panel
+  return total + 8.4e-6 * critical_panels(segs);
 }
 }  // namespace
 
@@ -192,6 +193,8 @@ bool choose_camera_order(int n_cams, const int* first, std::vector<int>& new_of_
   new_of_old.clear();
   static const bool off = getenv("HSFM_NO_TWIST") != nullptr;  // experiment knob
   static const int max_depth = getenv("HSFM_ORDER_DEPTH") ? atoi(getenv("HSFM_ORDER_DEPTH")) : 2;
+  static const int force_env = getenv("HSFM_ORDER_FORCE") ? atoi(getenv("HSFM_ORDER_FORCE")) : -1;  // experiment knob: that depth, no cost model
+  if (force_depth < 0) force_depth = force_env;
   if (off || n_cams < 4 * CAM_ALIGN) return false;
   // how banded is the natural order?
   double env = 0.0;
@@ -212,7 +215,7 @@ bool choose_camera_order(int n_cams, const int* first, std::vector<int>& new_of_
     const double cost = order_cost(n_cams, first, cand.data(), &crit);
     static const bool verbose = getenv("HSFM_ORDER_VERBOSE") != nullptr;
     if (verbose) std::fprintf(stderr, "[order] depth %d: critical panels %d, estimated %.3f ms (best so far %.3f)\n", depth, crit, 1e3 * cost, 1e3 * best_cost);
-    if (cost < 0.9 * best_cost || force_depth >= 0) { best_cost = cost; best.swap(cand); best_depth = depth; best_sizes[0] = sizes[0]; best_sizes[1] = sizes[1]; }
+    if (cost < (depth == 0 ? 0.9 : 0.98) * best_cost || force_depth >= 0) { best_cost = cost; best.swap(cand); best_depth = depth; best_sizes[0] = sizes[0]; best_sizes[1] = sizes[1]; }
     else if (depth > 0) break;  // a deeper dissection that does not pay ends the search
   }
   if (best_depth < 0) return false;

@@ -217,7 +217,12 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
         const size_t need_b = sizeof(double) * ((size_t)n6 * n6 + cholesky_workspace_doubles(n6) + (size_t)ctx.chol_plan.packed_doubles() + (size_t)ctx.chol_plan.tail_doubles()) +
                               sizeof(unsigned) * (size_t)std::max<long long>(P.total_pairs, 0);
         const size_t have_b = free_b + sizeof(double) * P.S_capacity;
-        if (ctx.chol_plan.use && ctx.chol_plan.fill < 0.15 && have_b > need_b + ((size_t)4 << 30)) D.dense = true;
+        // "narrow": the envelope in base order (what the camera graph is) or the block structure of the chosen order
+        // (which carries the separator rows of a nested order on top) holds < 15 % of the triangle
+        double env = 0.0;
+        for (int c = 0; c < P.n_cams && c < (int)P.cam_first.size(); ++c) env += c - std::min(P.cam_first[(size_t)c], c) + 1;
+        const double band_fill = P.cam_first.empty() ? 1.0 : env / (0.5 * (double)P.n_cams * (P.n_cams + 1));
+        if (ctx.chol_plan.use && std::min(ctx.chol_plan.fill, band_fill) < 0.15 && have_b > need_b + ((size_t)4 << 30)) D.dense = true;
       }
     }
     if (D.dense) {
