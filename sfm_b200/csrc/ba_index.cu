@@ -541,6 +541,10 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
     int h_bad = 0;
     HSFM_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(int), s));
     if (n > 0) validate_idx_kernel<<<cdiv(n, 256), 256, 0, s>>>(n, cam_in, pt_in, n_cams, n_pts, d_bad);
+    if (comm.n_ranks > 1) {  // a bad index in one shard: every rank refuses (nobody is left waiting in a later collective)
+      const int rc = comm.allreduce_sum_i32(d_bad, 1, s);
+      if (rc) return rc;
+    }
     HSFM_CUDA(cudaMemcpyAsync(&h_bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, s));
     HSFM_CUDA(cudaStreamSynchronize(s));
     if (h_bad) return HSFM_BA_ERR_ARG;
@@ -723,7 +727,18 @@ int build_problem(Problem& P, int mode, int64_t n_obs64, const double* obs_xy, c
   HSFM_CUDA(cudaStreamSynchronize(s));
   const int max_track = h_small[0];
   P.max_track = max_track;
-  if (max_track > MAX_TRACK) return HSFM_BA_ERR_UNSUPPORTED;
+  {
+    // all ranks leave together (the next collective is the observation count per camera): a long track in ONE shard
+    int too_long = max_track > MAX_TRACK ? 1 : 0;
+    if (comm.n_ranks > 1) {
+      HSFM_CUDA(cudaMemcpyAsync(d_max_track, &too_long, sizeof(int), cudaMemcpyHostToDevice, s));
+      const int rc = comm.allreduce_sum_i32(d_max_track, 1, s);
+      if (rc) return rc;
+      HSFM_CUDA(cudaMemcpyAsync(&too_long, d_max_track, sizeof(int), cudaMemcpyDeviceToHost, s));
+      HSFM_CUDA(cudaStreamSynchronize(s));
+    }
+    if (too_long) return HSFM_BA_ERR_UNSUPPORTED;
+  }
   std::vector<int> tiles, tile_p;  // first observation / first point of every tile (+ end sentinels)
   tiles.reserve((size_t)n / (TILE - 32) + 2);
   tile_p.reserve((size_t)n / (TILE - 32) + 2);

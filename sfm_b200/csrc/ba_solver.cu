@@ -201,6 +201,20 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
       ctx.chol_plan_valid = true;
       return 0;
     };
+    // Under a communicator every rank must take the same branch (the solve is a fixed sequence of collectives): decisions
+    // that depend on rank-local state — free memory, an allocation that may fail — are taken on the minimum over ranks.
+    auto agree = [&](bool local, bool* all) -> int {
+      *all = local;
+      if (ctx.comm.n_ranks <= 1) return 0;
+      int v = local ? 1 : 0;
+      HSFM_CUDA(cudaMemcpyAsync(P.flags + FLAG_SLOTS - 1, &v, sizeof(int), cudaMemcpyHostToDevice, s));
+      const int rc = ctx.comm.allreduce_min_i32(P.flags + FLAG_SLOTS - 1, 1, s);
+      if (rc) return rc;
+      HSFM_CUDA(cudaMemcpyAsync(&v, P.flags + FLAG_SLOTS - 1, sizeof(int), cudaMemcpyDeviceToHost, s));
+      HSFM_CUDA(cudaStreamSynchronize(s));
+      *all = v != 0;
+      return 0;
+    };
     if (o.linear_solver == HSFM_BA_LINEAR_DENSE_SCHUR) D.dense = true;
     else if (o.linear_solver == HSFM_BA_LINEAR_PCG) D.dense = false;
     else {
@@ -222,7 +236,10 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
         double env = 0.0;
         for (int c = 0; c < P.n_cams && c < (int)P.cam_first.size(); ++c) env += c - std::min(P.cam_first[(size_t)c], c) + 1;
         const double band_fill = P.cam_first.empty() ? 1.0 : env / (0.5 * (double)P.n_cams * (P.n_cams + 1));
-        if (ctx.chol_plan.use && std::min(ctx.chol_plan.fill, band_fill) < 0.15 && have_b > need_b + ((size_t)4 << 30)) D.dense = true;
+        bool fits = false;
+        rc = agree(have_b > need_b + ((size_t)4 << 30), &fits);  // free memory differs from rank to rank
+        if (rc) return rc;
+        if (ctx.chol_plan.use && std::min(ctx.chol_plan.fill, band_fill) < 0.15 && fits) D.dense = true;
       }
     }
     if (D.dense) {
@@ -231,16 +248,23 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
       // workspace after S: L11^-1 blocks + flags, then (multi-GPU) the packed envelope for the all-reduce
       const size_t packed = (ctx.comm.n_ranks > 1 && ctx.chol_plan.use) ? (size_t)ctx.chol_plan.packed_doubles() : 0;
       const size_t need = (size_t)n6 * n6 + cholesky_workspace_doubles(n6) + (size_t)ctx.chol_plan.tail_doubles() + packed;
+      bool have = true;
       if (P.S_capacity < need) {
         if (P.S) cudaFree(P.S);
         P.S = nullptr; P.S_capacity = 0;
         if (cudaMalloc(&P.S, sizeof(double) * std::max<size_t>(need, 1)) != cudaSuccess) {
           cudaGetLastError();
-          if (o.linear_solver == HSFM_BA_LINEAR_DENSE_SCHUR) return HSFM_BA_ERR_NOMEM;
-          D.dense = false;
+          have = false;
         } else {
           P.S_capacity = need;
         }
+      }
+      bool all_have = have;
+      rc = agree(have, &all_have);  // one rank out of memory: every rank falls back (or fails) together
+      if (rc) return rc;
+      if (!all_have) {
+        if (o.linear_solver == HSFM_BA_LINEAR_DENSE_SCHUR) return HSFM_BA_ERR_NOMEM;
+        D.dense = false;
       }
     }
   }
@@ -259,9 +283,13 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
     if (!(o.dense_flags & 1) && pl.use) S.chol_critical_panels = pl.critical;
   }
 
-  cudaEvent_t ev0, ev1;
-  HSFM_CUDA(cudaEventCreate(&ev0));
-  HSFM_CUDA(cudaEventCreate(&ev1));
+  struct EventPair {  // destroyed on every return path
+    cudaEvent_t a = nullptr, b = nullptr;
+    ~EventPair() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+  } evs;
+  HSFM_CUDA(cudaEventCreate(&evs.a));
+  HSFM_CUDA(cudaEventCreate(&evs.b));
+  const cudaEvent_t ev0 = evs.a, ev1 = evs.b;
   HSFM_CUDA(cudaEventRecord(ev0, s));
 
   D.compute_scaling();
@@ -297,7 +325,7 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
   }
   if (!std::isfinite(x_cost)) {
     term = HSFM_BA_FAILURE;
-  } else if (gmax <= o.gradient_tolerance || P.n_obs == 0) {
+  } else if (gmax <= o.gradient_tolerance || (!D.multi() && P.n_obs == 0)) {  // an empty SHARD is not an empty problem
     term = HSFM_BA_CONVERGENCE;
   } else {
     while (true) {
@@ -376,8 +404,6 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
   D.collect(S.phase_ms);
   float ms = 0.f;
   cudaEventElapsedTime(&ms, ev0, ev1);
-  cudaEventDestroy(ev0);
-  cudaEventDestroy(ev1);
   S.solve_ms = ms;
   S.final_cost = x_cost + fixed_cost;
   int64_t n_obs_total = P.n_obs;

@@ -35,6 +35,21 @@ def main():
     dist.broadcast_object_list(uid, src=0)
     ctx.comm_init(uid[0], rank, world)
     opts = api.default_options(linear_solver=linear, pcg_max_iterations=3000)
+    # a refused upload is refused by EVERY rank (a bad index in one shard must not leave the others in a collective)
+    if rank == world - 1:
+        import dataclasses
+        bad_idx = prob.cam_idx.copy()
+        bad_idx[0] = prob.n_cams + 5
+        bad = dataclasses.replace(prob, cam_idx=bad_idx)
+    else:
+        bad = prob
+    try:
+        ctx.upload(bad)
+        refused = 0
+    except api.BAError as e:
+        refused = int(e.code == -1)  # HSFM_BA_ERR_ARG
+    all_refused = [None] * world
+    dist.all_gather_object(all_refused, refused)
     ctx.upload(prob)
     s = ctx.solve_resident(opts)
     cam, pts = ctx.download()
@@ -58,7 +73,7 @@ def main():
                    final_cost=s["final_cost"], final_cost_single=s1["final_cost"], final_cost_oracle=so["final_cost"], rms=s["rms_px"],
                    rms_oracle=so["rms_px"], cam_spread_across_ranks=cam_spread, cam_err_single=float(np.abs(cam - c1).max()),
                    pts_err_single=float(np.abs(gp - p1).max()), cam_err_oracle=float(np.abs(cam - c0).max()),
-                   pts_err_oracle=float(np.abs(gp - p0).max()), linear_solver_used=s["linear_solver_used"],
+                   pts_err_oracle=float(np.abs(gp - p0).max()), linear_solver_used=s["linear_solver_used"], refused_by=sum(all_refused),
                    trace_cost=[t["cost"] for t in s["trace"]], trace_cost_single=[t["cost"] for t in s1["trace"]])
     ctx.close()
     dist.barrier()

@@ -29,6 +29,7 @@ def _run(n, linear, which):
 def test_two_rank_solve_matches_single_gpu_and_oracle(linear, which):
     d = _run(2, linear, which)
     assert d["n_ranks"] == 2
+    assert d["refused_by"] == 2  # the upload with a bad index in rank 1's shard was refused by both ranks
     assert d["iterations"] == d["iterations_single"] == d["iterations_oracle"]
     assert abs(d["final_cost"] - d["final_cost_single"]) <= 1e-10 * d["final_cost_single"]
     assert abs(d["final_cost"] - d["final_cost_oracle"]) <= 1e-6 * d["final_cost_oracle"]      # north star: cost within 1e-6 relative
