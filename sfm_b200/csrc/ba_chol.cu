@@ -1329,21 +1329,13 @@ __global__ void __launch_bounds__(256) trsv_bwd_kernel(const double* __restrict_
 }
 
 // ---------------------------------------------------------------------------------------------
-// Both triangular solves in ONE cooperative launch.  CTA c owns the 128-row blocks c, c+G, … .
-// Forward (L y = b): the owner of block i folds L[i,k] y_k into its right-hand side as soon as block k
-// publishes y_k (flag with release/acquire at gpu scope), then applies L11^-1 of its own block and publishes.
-// Backward (L^T x = y) runs the same protocol down the columns.  Blocks only ever wait on blocks with a
-// smaller (forward) / larger (backward) index and every CTA walks its blocks in that order, so the waits
-// cannot cycle; the cooperative launch guarantees all CTAs are resident.  The dependency chain is two
-// 128x128 mat-vecs plus one flag hand-off per block instead of two kernel launches.
+// Both triangular solves in ONE cooperative launch.  CTA c owns the 128-row blocks c, c+G, … .  A block's result is
+// handed to its consumers through the data itself: vectors and contribution slots are preset to a sentinel bit pattern
+// and every consumer thread polls its own element (poll_value / publish_value below) — no flags.  Blocks only ever wait
+// on blocks with a smaller (forward) / larger (backward) index and every CTA walks its blocks in that order, so the
+// waits cannot cycle; the cooperative launch guarantees all CTAs are resident.  The dependency chain is two 128x128
+// mat-vecs plus one hand-over per block instead of two kernel launches.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ int ld_acquire(const int* p) {
-  int v;
-  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release(int* p, int v) { asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
-__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 // Block mat-vec pieces of the triangular solves, split into "fetch the matrix block into registers" and "multiply
 // with the vector", so that the fetch is issued BEFORE the CTA waits for the flag of the vector's producer: when
@@ -2173,7 +2165,6 @@ void launch_cholesky(double* S, int n, double* ws, int* fail_flag, cudaStream_t 
 void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream_t s, int64_t* launches, const CholAux* aux, const CholPlan* plan) {
   double* w = b + n;
   const int panels = (n + NB - 1) / NB;
-  int* flags = reinterpret_cast<int*>(ws + (size_t)panels * NB * NB);  // [2 * panels]
   const int n_sm = (aux && aux->n_sm > 0) ? aux->n_sm : 148;
   const int coop = aux ? aux->coop : 0;
   if (coop) {

@@ -229,7 +229,6 @@ void launch_pcg_step(Problem& P, double tol, int max_it, cudaStream_t s);
 struct CholPlan;
 void launch_dense_init(Problem& P, bool with_diag, cudaStream_t s, const CholPlan* plan = nullptr);  // S = 0 (+ blockdiag(Hcc + D^2)); plan: zero the envelope only
 void launch_dense_schur(Problem& P, cudaStream_t s, bool sorted_pairs = true);    // S -= sum_p W Hpp^-1 W^T (lower block triangle)
-bool dense_schur_prepare(Problem& P, cudaStream_t s);  // sorted pair lists ready?
 void launch_scatter_eval(Problem& P, double* r_out, double* jac_out, cudaStream_t s);  // back to input order, Ceres layout
 void launch_export_blocks(Problem& P, double* Hcc36, double* Hpp9, cudaStream_t s);  // parity tap (adds LM diagonal)
 void launch_mirror_lower(Problem& P, cudaStream_t s);   // S upper <- lower (parity tap)

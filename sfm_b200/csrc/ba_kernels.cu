@@ -1132,7 +1132,7 @@ __device__ __forceinline__ void dense_schur_tile(const Dev& d, const double* __r
     }
     __syncwarp();
   };
-  if (SORTED) {
+  if constexpr (SORTED) {
     // The tile's pairs come from the static list SORTED BY DESTINATION BLOCK (ba_index / tile_pairs_kernel): a
     // warp walks a contiguous piece of the list and keeps accumulating into the same tensor-core fragment while
     // the destination stays the same, so the ~2.1 pairs per distinct block of a tile cost one reduction, not 2.1.
@@ -1201,8 +1201,7 @@ __device__ __forceinline__ void dense_schur_tile(const Dev& d, const double* __r
     }
     if (cur != 0x10000u) flush();
     if (nbuf) reduce_sorted(nbuf);
-    return;
-  }
+  } else {
   // Unsorted fallback (no pair list): every warp takes 8 pairs (288 block elements) at a time, round-robin over the
   // tile, so the work of a long track is spread over all warps.
   for (int base = warp * 8; base < total_pairs; base += (TILE / 32) * 8) {
@@ -1247,6 +1246,7 @@ __device__ __forceinline__ void dense_schur_tile(const Dev& d, const double* __r
       if (frag_ok) *reinterpret_cast<double2*>(sC + pl * 36 + fr * 6 + 2 * fk) = make_double2(c0, c1);
     }
     reduce_staged(cnt);
+  }
   }
 }
 
@@ -1617,27 +1617,6 @@ void launch_dense_schur(Problem& P, cudaStream_t s, bool sorted_pairs) {
   P.launches++;
 }
 
-// Builds the sorted pair lists if needed; true when the sorted kernel can run.
-bool dense_schur_prepare(Problem& P, cudaStream_t s) {
-  if (P.n_tiles == 0 || !P.d.pair_off) return false;
-  static const bool no_sort = getenv("HSFM_SCHUR_UNSORTED") != nullptr;
-  if (no_sort) return false;
-  if (!P.pairs_ready) {
-    const size_t need = (size_t)std::max<long long>(P.total_pairs, 1);
-    if (P.pair_capacity < need) {
-      if (P.pair_list) cudaFree(P.pair_list);
-      P.pair_list = nullptr; P.pair_capacity = 0;
-      if (cudaMalloc(&P.pair_list, sizeof(unsigned) * need) == cudaSuccess) P.pair_capacity = need;
-      else cudaGetLastError();
-    }
-    if (!P.pair_list) return false;
-    tile_pairs_kernel<<<P.n_tiles, TILE, 0, s>>>(P.d, P.pair_list);
-    P.launches++;
-    P.d.pair_list = P.pair_list;
-    P.pairs_ready = true;
-  }
-  return true;
-}
 void launch_mirror_lower(Problem& P, cudaStream_t s) {
   const int n = 6 * P.n_cams;
   if (n == 0) return;

@@ -406,9 +406,7 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
   cudaEventElapsedTime(&ms, ev0, ev1);
   S.solve_ms = ms;
   S.final_cost = x_cost + fixed_cost;
-  int64_t n_obs_total = P.n_obs;
   S.rms_px = 0.0;  // filled by the caller when the global observation count is known
-  (void)n_obs_total;
   S.num_iterations = iter;
   S.num_successful_steps = num_success;
   S.termination_type = term;
