@@ -397,9 +397,9 @@ def main():
             roofline = {"kernel": "structured Cholesky of the reduced camera system (chol_diag / chol_chain_tile / chol_trsm_strip / chol_syrk, DMMA m8n8k4)",
                         "bound": "tensor", "achieved": tf, "peak": FP64_DMMA_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": tf / FP64_DMMA_PEAK_TFLOPS,
                         "traffic": None, "share_of_step": phases["factor"] / step_ms, "ms_per_factorisation": f_ms,
-                        "flops_per_factorisation": summ["chol_flops"], "panels": summ["chol_panels"], "critical_panels": summ["chol_critical_panels"],
+                        "flops_per_factorisation": summ["chol_flops"], "panels": summ["chol_panels"], "critical_panels": summ["chol_critical_panels"], "chains": summ["chol_chains"],
                         "peak_source": "FP64 DMMA peak measured with scripts/micro/fp64_peaks.cu on this pool (MEASURED_PEAKS.json has no FP64 figure)",
-                        "note": "latency-bound panel chain(s): the time is set by critical_panels serial panel steps, not by the flops"}
+                        "note": "concurrent panel chains along the block elimination tree: critical_panels serial panel steps of ~38 us each, the chains' trailing updates share the tensor pipes beside them"}
         dominant_phase = {"phase": dominant, "share_of_step": phases[dominant] / step_ms,
                           "note": "factor = envelope Cholesky of the reduced camera system: a chain of 128-column panel steps "
                                   "(diagonal block on one CTA -> panel solve -> next-column update); latency-bound" if dominant == "factor" else ""}

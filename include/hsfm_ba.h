@@ -130,7 +130,7 @@ typedef struct hsfm_ba_summary {
   int32_t chol_panels;          /* 128-column panels of the reduced camera system (0: no Cholesky in this solve) */
   int32_t chol_critical_panels; /* panels on the serial chain of the factorisation: = chol_panels with one chain, fewer with two */
   int32_t cameras_reordered;    /* 1: the problem is held in the library's two-ended camera order (hsfm_ba_set_ordering) */
-  int32_t reserved1;
+  int32_t chol_chains;           /* panel chains (segments of the block elimination tree) the factorisation ran as; 1 = one chain */
   double chol_flops;            /* FP64 flops of ONE factorisation of the reduced camera system over its block structure:
                                    sum over panels of 128^3/3 (diagonal block) + |R_K| 128^3 (panel solve) + |R_K|(|R_K|+1) 128^3
                                    (trailing update); n^3/3 when factored as a dense matrix */

@@ -69,7 +69,7 @@ class Summary(C.Structure):
         ("chol_panels", C.c_int32),
         ("chol_critical_panels", C.c_int32),
         ("cameras_reordered", C.c_int32),
-        ("reserved1", C.c_int32),
+        ("chol_chains", C.c_int32),
         ("chol_flops", C.c_double),
     ]
 

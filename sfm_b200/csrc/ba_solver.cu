@@ -280,7 +280,8 @@ int lm_solve(Ctx& ctx, const hsfm_ba_options& o, hsfm_ba_summary* summary) {
       S.chol_flops = 0.0;
       for (int K = 0; K < pl.panels; ++K) S.chol_flops += b3 / 3.0 + pl.cnt[K] * b3 + (double)pl.cnt[K] * (pl.cnt[K] + 1) * b3;
     }
-    if (!(o.dense_flags & 1) && pl.use) S.chol_critical_panels = pl.critical;
+    S.chol_chains = 1;
+    if (!(o.dense_flags & 1) && pl.use) { S.chol_critical_panels = pl.critical; S.chol_chains = std::max<int>(1, (int)pl.segs.size()); }
   }
 
   struct EventPair {  // destroyed on every return path

@@ -15,8 +15,9 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("closure", [False, True], ids=["band", "band+loop-closure"])
 def test_two_ended_camera_order_equals_callers_order(ctx, closure):
-    """A banded camera graph is renumbered from both ends towards the middle (loop-closure cameras last) and factored
-    as two concurrent panel chains.  Same problem, same LM trajectory, results in the caller's order."""
+    """A banded camera graph is cut around separators and every piece renumbered from both ends towards its middle
+    (loop-closure cameras last): the factorisation runs as concurrent panel chains — at this size four of them plus their
+    separators — against ONE chain in the caller's order.  Same problem, same LM trajectory, results in the caller's order."""
     p = _trajectory(n_cams=640, n_pts=9000, closure=closure)
     o = api.default_options(linear_solver=api.LINEAR_DENSE_SCHUR, max_num_iterations=6)
     try:
@@ -28,6 +29,7 @@ def test_two_ended_camera_order_equals_callers_order(ctx, closure):
         ctx.set_ordering(0)
     assert sn["cameras_reordered"] == 0 and sn["chol_critical_panels"] == sn["chol_panels"] == 30
     assert sa["cameras_reordered"] == 1 and sa["chol_critical_panels"] <= 0.75 * sa["chol_panels"]
+    assert sn["chol_chains"] == 1 and sa["chol_chains"] >= 3  # two chains + tail, or four chains + separators
     assert sa["num_iterations"] == sn["num_iterations"] and sa["num_successful_steps"] == sn["num_successful_steps"]
     assert sa["final_cost"] == pytest.approx(sn["final_cost"], rel=1e-10)
     for a, b in zip(sa["trace"], sn["trace"]):
