@@ -250,31 +250,35 @@ __global__ void __launch_bounds__(TILE) tile_cams_kernel(const int* __restrict__
                                                           int* __restrict__ tile_hdr, int* __restrict__ max_ncam,
                                                           unsigned char* __restrict__ srank, unsigned char* __restrict__ sorder,
                                                           unsigned short* __restrict__ slot_begin, int* __restrict__ tile_ncam) {
-  __shared__ int sc[TILE];
-  __shared__ int sfirst[TILE];
-  __shared__ int sslot[TILE];
+  __shared__ __align__(16) int sc[TILE];
+  __shared__ __align__(16) int sfirst[TILE];
   const int b = tile_start[blockIdx.x], e = tile_start[blockIdx.x + 1];
-  const int tid = threadIdx.x, i = b + tid, cnt = e - b;
-  const int c = i < e ? cam[i] : 0x7fffffff;
+  const int tid = threadIdx.x, i = b + tid;
+  const int c = i < e ? cam[i] : 0x7fffffff;  // past the tile: larger than every camera, never "smaller than"
   sc[tid] = c;
   __syncthreads();
-  int first = i < e;
-  for (int j = 0; j < tid; ++j) first &= (sc[j] != c);
-  sfirst[tid] = first;
+  // position of this observation when the tile is ordered by camera (ties keep tile order) — camera-keyed sums of a tile
+  // are then sums over contiguous runs of a shared-memory array, in a fixed order — in ONE pass over the tile's cameras
+  // (four per shared-memory broadcast); an observation is the first of its camera when none of the same camera precedes it
+  int before = 0, same_before = 0;
+#pragma unroll 4
+  for (int j = 0; j < TILE; j += 4) {
+    const int4 v = *reinterpret_cast<const int4*>(sc + j);
+    before += (v.x < c) + (v.y < c) + (v.z < c) + (v.w < c);
+    same_before += ((v.x == c) & (j < tid)) + ((v.y == c) & (j + 1 < tid)) + ((v.z == c) & (j + 2 < tid)) + ((v.w == c) & (j + 3 < tid));
+  }
+  const int first = (i < e) && same_before == 0;
+  sfirst[tid] = first ? c : 0x7fffffff;  // the camera where an observation is the first of it, else "none"
   const int ncam = __syncthreads_count(first);
+  // slot = number of distinct cameras below this one
   int rank = 0;
-  for (int j = 0; j < cnt; ++j) rank += (sfirst[j] && sc[j] < c);
-  sslot[tid] = i < e ? rank : 0x7fffffff;
-  __syncthreads();
+#pragma unroll 4
+  for (int j = 0; j < TILE; j += 4) {
+    const int4 v = *reinterpret_cast<const int4*>(sfirst + j);
+    rank += (v.x < c) + (v.y < c) + (v.z < c) + (v.w < c);
+  }
   if (i < e) {
     slot[i] = (unsigned char)rank;
-    // position of this observation when the tile is ordered by slot (ties keep tile order): camera-keyed sums of a
-    // tile are then sums over contiguous runs of a shared-memory array, in a fixed order
-    int before = 0, same_before = 0;
-    for (int j = 0; j < cnt; ++j) {
-      before += sslot[j] < rank;
-      same_before += (sslot[j] == rank) & (j < tid);
-    }
     srank[i] = (unsigned char)(before + same_before);
     sorder[b + before + same_before] = (unsigned char)tid;  // inverse: which observation of the tile sits at that position
     if (first) {
