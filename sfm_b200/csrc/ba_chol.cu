@@ -1439,15 +1439,21 @@ __device__ __forceinline__ void publish_value(double* p, double v) {
 __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict__ L, int n, const double* __restrict__ LinvAll, double* b,
                                                         double* w, double* x, double* slots, const int* __restrict__ row_off,
                                                         const int* __restrict__ col_off, const int* __restrict__ col_cnt,
-                                                        const int* __restrict__ col_list, const int* __restrict__ col_slot) {
+                                                        const int* __restrict__ col_list, const int* __restrict__ col_slot,
+                                                        const int* __restrict__ sweep) {
   extern __shared__ __align__(16) double sInv[];  // [128][TI_LD]
   __shared__ double sv[NB];    // vector of the block being folded in (y_k / x_i)
   __shared__ double sacc[NB];  // running right-hand side of the owned block
   __shared__ __align__(16) double sp[4][NB];  // partial sums of the four row quarters (backward), of the two halves (L11^-T)
   const int tid = threadIdx.x;
   const int P = (n + NB - 1) / NB, G = gridDim.x;
+  // Columns are dealt to the CTAs in SWEEP order (sweep[]: by height in the block elimination tree; null = by index):
+  // with more columns than CTAs a CTA owns columns of several concurrent chains, and in index order the early columns
+  // of a later chain would wait behind the late columns of an earlier one.  Dependencies point to strictly lower (forward)
+  // / higher (backward) positions of the sweep order, every CTA walks its columns in that order: no wait can cycle.
   // ---- forward: L y = b, y -> w ----
-  for (int k = blockIdx.x; k < P; k += G) {
+  for (int idx = blockIdx.x; idx < P; idx += G) {
+    const int k = sweep ? __ldg(sweep + idx) : idx;
     const int r0 = k * NB, nr = min(NB, n - r0);
     __syncthreads();
     inv_stage(sInv, LinvAll + (size_t)k * NB * NB, tid);
@@ -1515,7 +1521,8 @@ __global__ void __launch_bounds__(256) trsv_coop_kernel(const double* __restrict
   // L11^-1 — 200 KB of shared memory leave ~28 KB of L1, and the register fetches of the other blocks, 16 / 8 bytes per
   // thread along rows, then miss L1 on every second half of a sector: the sweep took 1.2 ms instead of 0.45 at c4.)
   const int j = tid & (NB - 1), half = tid >> 7;
-  for (int kk = P - 1 - (int)blockIdx.x; kk >= 0; kk -= G) {
+  for (int idx = P - 1 - (int)blockIdx.x; idx >= 0; idx -= G) {
+    const int kk = sweep ? __ldg(sweep + idx) : idx;
     const int c0 = kk * NB, kb = min(NB, n - c0);
     __syncthreads();
     inv_stage(sInv, LinvAll + (size_t)kk * NB * NB, tid);
@@ -1769,7 +1776,16 @@ int CholPlan::build(int n_cams, const uint8_t* pattern, int P, cudaStream_t s) {
       const int* re = row_list.data() + row_off[(size_t)I + 1];
       col_slot[(size_t)off[K] + q] = (int)(std::lower_bound(rb, re, K) - row_list.data());
     }
-  const size_t need = 3 * list.size() + row_off.size() + row_list.size() + 2 * (size_t)panels + anc_all.size() + map_all.size() + 1;
+  // sweep order of the triangular solves: columns by height in the block elimination tree (leaves first), ties by index
+  {
+    std::vector<int> height((size_t)panels, 0);
+    for (int K = 0; K < panels; ++K)
+      if (cnt[K] > 0) { const int par = list[(size_t)off[K]]; height[(size_t)par] = std::max(height[(size_t)par], height[(size_t)K] + 1); }
+    sweep.resize((size_t)panels);
+    for (int K = 0; K < panels; ++K) sweep[(size_t)K] = K;
+    std::stable_sort(sweep.begin(), sweep.end(), [&](int a, int b) { return height[(size_t)a] < height[(size_t)b]; });
+  }
+  const size_t need = 3 * list.size() + row_off.size() + row_list.size() + 3 * (size_t)panels + anc_all.size() + map_all.size() + 1;
   if (need > d_cap) {
     if (d_ints) cudaFree(d_ints);
     d_ints = nullptr; d_cap = 0;
@@ -1785,6 +1801,7 @@ int CholPlan::build(int n_cams, const uint8_t* pattern, int P, cudaStream_t s) {
   d_anc = d_side + list.size();
   d_map = d_anc + anc_all.size();
   d_col_slot = d_map + map_all.size();
+  d_sweep = d_col_slot + list.size();
   if ((size_t)panels + 1 > d_blk_cap) {
     if (d_blk_off) cudaFree(d_blk_off);
     d_blk_off = nullptr; d_blk_cap = 0;
@@ -1801,6 +1818,7 @@ int CholPlan::build(int n_cams, const uint8_t* pattern, int P, cudaStream_t s) {
   if (!anc_all.empty()) HSFM_CUDA(cudaMemcpyAsync(d_anc, anc_all.data(), sizeof(int) * anc_all.size(), cudaMemcpyHostToDevice, s));
   if (!map_all.empty()) HSFM_CUDA(cudaMemcpyAsync(d_map, map_all.data(), sizeof(int) * map_all.size(), cudaMemcpyHostToDevice, s));
   if (!col_slot.empty()) HSFM_CUDA(cudaMemcpyAsync(d_col_slot, col_slot.data(), sizeof(int) * col_slot.size(), cudaMemcpyHostToDevice, s));
+  HSFM_CUDA(cudaMemcpyAsync(d_sweep, sweep.data(), sizeof(int) * sweep.size(), cudaMemcpyHostToDevice, s));
   HSFM_CUDA(cudaStreamSynchronize(s));  // the host vectors may be rebuilt by the next problem
   return 0;
 }
@@ -2182,8 +2200,9 @@ void launch_chol_solve(const double* L, int n, double* ws, double* b, cudaStream
     const int* col_cnt = st ? plan->d_col_cnt : nullptr;
     const int* col_list = st ? plan->d_list : nullptr;
     const int* col_slot = st ? plan->d_col_slot : nullptr;
+    const int* sweep = (st && panels > n_sm) ? plan->d_sweep : nullptr;  // every column has a CTA of its own otherwise
     void* args[] = {(void*)&L,       (void*)&nn,      (void*)&LinvAll, (void*)&b,        (void*)&w,        (void*)&x,
-                    (void*)&slots,   (void*)&row_off, (void*)&col_off, (void*)&col_cnt,  (void*)&col_list, (void*)&col_slot};
+                    (void*)&slots,   (void*)&row_off, (void*)&col_off, (void*)&col_cnt,  (void*)&col_list, (void*)&col_slot, (void*)&sweep};
     const int grid = std::min(panels, n_sm);
     if (cudaLaunchCooperativeKernel((const void*)trsv_coop_kernel, dim3(grid), dim3(256), args, kTrsvSmem, s) == cudaSuccess) {
       ++*launches;

@@ -296,7 +296,8 @@ struct CholPlan {
   int split_a = -1, split_t0 = -1;  // set when the schedule is the plain two-chain one (chains [0,a) and [a,t0), tail [t0,P)); reporting only
   int* d_ints = nullptr;       // device copy: list | row_off | row_list | col_off | col_cnt | side | anc_all | map_all
   int* d_list = nullptr; int* d_row_off = nullptr; int* d_row_list = nullptr; int* d_col_off = nullptr; int* d_col_cnt = nullptr;
-  int* d_side = nullptr; int* d_anc = nullptr; int* d_map = nullptr; int* d_col_slot = nullptr;
+  int* d_side = nullptr; int* d_anc = nullptr; int* d_map = nullptr; int* d_col_slot = nullptr; int* d_sweep = nullptr;
+  std::vector<int> sweep;      // columns by height in the block elimination tree: the order the triangular solves deal them to CTAs
   std::vector<int> col_slot;   // parallel to list: position of block (list[q], K) in row_list (slot of the forward triangular solve)
   size_t d_cap = 0;
   // packed structure (multi-GPU: only these entries of S are summed across ranks): row r of block I occupies
