@@ -128,8 +128,9 @@ typedef struct hsfm_ba_summary {
   double fixed_cost;            /* 1/2 sum r^2 of residuals whose parameter blocks are all constant (ceres Summary::fixed_cost);
                                    included in initial_cost / final_cost, not in the per-iteration costs */
   int32_t chol_panels;          /* 128-column panels of the reduced camera system (0: no Cholesky in this solve) */
-  int32_t chol_critical_panels; /* panels on the serial chain of the factorisation: = chol_panels with one chain, fewer with two */
-  int32_t cameras_reordered;    /* 1: the problem is held in the library's two-ended camera order (hsfm_ba_set_ordering) */
+  int32_t chol_critical_panels; /* panels on the longest serial chain of the factorisation: = chol_panels with one chain, fewer with concurrent chains */
+  int32_t cameras_reordered;    /* 1: the problem is held in an internal camera order (nested two-ended order and / or reverse
+                                   Cuthill-McKee, hsfm_ba_set_ordering); results come back in the caller's order */
   int32_t chol_chains;           /* panel chains (segments of the block elimination tree) the factorisation ran as; 1 = one chain */
   double chol_flops;            /* FP64 flops of ONE factorisation of the reduced camera system over its block structure:
                                    sum over panels of 128^3/3 (diagonal block) + |R_K| 128^3 (panel solve) + |R_K|(|R_K|+1) 128^3
