@@ -183,6 +183,29 @@ def test_small_or_dense_graphs_keep_the_callers_order():
     assert not d["structured"] and d["fill"] == 1.0
 
 
+def test_depth_two_order_runs_eight_chains():
+    """Two levels of dissection: eight leaf chains, four inner separators, two middle ones, one root — the general
+    segment tree (side matrices forwarded through two levels of joins)."""
+    n = 1300
+    first = band_first(n, 10, 22, seed=17, closures=((1250, 5),))
+    d = api.debug_structure(first, depth=2)
+    P, segs = d["panels"], d["segments"]
+    assert d["reordered"] and d["structured"] and sorted(d["new_of_old"]) == list(range(n))
+    check_segments(segs, P)
+    leaves = [g for g in range(len(segs)) if all(par != g for _, _, par in segs)]
+    assert len(leaves) >= 8, segs
+    depth_of = lambda g: 0 if segs[g][2] < 0 else 1 + depth_of(segs[g][2])  # noqa: E731
+    assert max(depth_of(g) for g in range(len(segs))) >= 3
+    assert d["critical_panels"] <= 0.45 * P, (d["critical_panels"], P)
+    A = random_spd(first, seed=4)
+    Ap = permuted(A, d["new_of_old"])
+    L = np.linalg.cholesky(Ap)
+    mask = np.kron(d["structure"], np.ones((NB, NB)))[: 6 * n, : 6 * n].astype(bool)
+    assert np.abs(L[~mask]).max() == 0.0
+    Le = emulate(Ap, d["structure"], segs)
+    assert np.abs(Le - L).max() <= 1e-10 * np.abs(L).max()
+
+
 @pytest.mark.parametrize("case", ["band", "band+closures", "two components"])
 def test_reverse_cuthill_mckee_finds_the_band_of_a_shuffled_scan(case):
     """Cameras of a scan delivered in random order: rcm_order (ba_order.cpp) numbers them so that the graph is a band again
