@@ -47,3 +47,34 @@ def test_fallback_schedule_gives_the_same_solve(knob):
     for a, b in zip(ref["cost"], alt["cost"]):
         assert abs(a - b) <= 1e-9 * abs(a)
     assert abs(ref["cam"] - alt["cam"]) <= 1e-7 * ref["cam"]
+
+
+DEPTH_SNIPPET = r"""
+import json, sys
+sys.path.insert(0, %r)
+from sfm_b200 import api, synth
+p = synth.make_config("c3")
+ctx = api.Context(0)
+ctx.upload(p)
+s = ctx.solve_resident(api.default_options(linear_solver=api.LINEAR_DENSE_SCHUR))
+print("RESULT " + json.dumps(dict(cost=[t["cost"] for t in s["trace"]], chains=s["chol_chains"], critical=s["chol_critical_panels"],
+                                  panels=s["chol_panels"], final=s["final_cost"], its=s["num_iterations"])))
+""" % ROOT
+
+
+@pytest.mark.parametrize("depth,min_chains", [(0, 3), (1, 6), (2, 12)])
+def test_every_dissection_depth_follows_the_oracle_table(depth, min_chains):
+    """Full-size c3 (1723 cameras) with the order depth forced: 2, 4 and 8 concurrent chains all reproduce the oracle's
+    per-iteration table (tests/golden/lm_fullsize.npz) — the segment-tree schedule on the device, not only its emulation."""
+    import numpy as np
+
+    g = np.load(os.path.join(ROOT, "tests", "golden", "lm_fullsize.npz"))
+    env = dict(os.environ, HSFM_ORDER_FORCE=str(depth))
+    r = subprocess.run([sys.executable, "-c", DEPTH_SNIPPET], capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    d = json.loads([l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1][len("RESULT "):])
+    assert d["chains"] >= min_chains and d["critical"] < d["panels"]
+    want = g["c3_cost"]
+    assert len(d["cost"]) == len(want)
+    for a, b in zip(d["cost"], want):
+        assert abs(a - b) <= 1e-9 * abs(b)
